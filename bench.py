@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 DDP bf16 training throughput (samples/s), config #2 of
+BASELINE.json ("PyTorchJob ResNet-50 DDP bf16 ... one GPU per pod, synthetic 224² images").
+
+    python bench.py --gpus N --steps K --warmup W [--impl ours|stock|reference]
+
+  ours       kubedl_b200 worker: explicit fwd/bwd on our sm_100a kernels, fused NVLink
+             all-reduce, fused SGD, CUDA-graph replay.
+  stock      what the reference operator's stock worker image does: torchvision ResNet-50,
+             torch DDP over NCCL, bf16 autocast, channels_last, torch.optim.SGD (cuDNN/cuBLAS).
+             Our own A/B arm; not the driver's "reference" arm.
+  reference  the unmodified reference through its own API.  The reference is a Go Kubernetes
+             operator with no Python package, no worker and no GPU code, so this
+             arm reports `unavailable` and exits 0 (see DESIGN.md "Reference arm").
+
+Timing: W untimed warm-up steps, then exactly K steps between barrier+synchronize fences, CUDA
+events on the launching stream, max over ranks.  Per-step working set (≈20 GB of activations)
+is far larger than the 126 MB L2, so no explicit L2 flush is needed (recorded in `config`).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+REF_UNAVAILABLE = ("reference is a pure-Go Kubernetes operator (no setup.py/pyproject, no Go "
+                   "toolchain or kube-apiserver here); pip install --target baseline/_ref failed: "
+                   "'/root/reference is not installable'")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "stock", "reference"])
+    ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (weak scaling)")
+    ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-gemm", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi sampler running for the duration of the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def maybe_respawn_under_torchrun(args):
+    if args.gpus > 1 and "RANK" not in os.environ:
+        port = 29500 + (os.getpid() % 2000)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+               f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1", "--master-port", str(port),
+               os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+
+
+def synth_batches(batch, n, size=224):
+    import torch
+    g = torch.Generator().manual_seed(1234 + int(os.environ.get("RANK", "0")))
+    out = []
+    for _ in range(n):
+        img = torch.randint(0, 256, (batch, size, size, 3), dtype=torch.uint8, generator=g).pin_memory()
+        lab = torch.randint(0, 1000, (batch,), dtype=torch.int64, generator=g).pin_memory()
+        out.append((img, lab))
+    return out
+
+
+def timed(fn_step, steps, world):
+    """Run `steps` calls of fn_step between fences; return max-over-ranks device milliseconds."""
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn_step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    return ms
+
+
+def run_ours(args):
+    import torch
+    from kubedl_b200.ops import lib as L
+    from kubedl_b200.worker.ddp_trainer import DDPTrainer
+    tr = DDPTrainer(batch_per_gpu=args.batch, comm=args.comm, use_graph=not args.no_graph,
+                    use_gemm=False if args.no_gemm else None)
+    world, rank = tr.world, tr.rank
+    pool = synth_batches(args.batch, 4)
+    for s in range(2):
+        tr.images[s].copy_(pool[s][0])
+        tr.labels[s].copy_(pool[s][1])
+    tr.warmup(max(args.warmup, 3))
+    for i in range(args.warmup):
+        tr.run_device_step(i & 1)
+    sampler = ClockSampler(torch.cuda.current_device())
+    sampler.start()
+    l0 = L.launch_count()
+    ms = timed(lambda i: tr.run_device_step(i & 1), args.steps, world)
+    launches = L.launch_count() - l0
+    clocks = sampler.stop()
+    e2e = None
+    if not args.no_e2e:
+        for i in range(2):
+            tr.train_step(*pool[i % len(pool)])
+        tr.last_loss()
+        ms_e = timed(lambda i: tr.train_step(*pool[i % len(pool)]), args.steps, world)
+        # the last step's loss read-back lands inside the fence (timed() synchronises)
+        loss = tr.last_loss()
+        h2d = pool[0][0].numel() * pool[0][0].element_size() + pool[0][1].numel() * 8
+        e2e = {"value": args.batch * world * args.steps / (ms_e / 1e3), "unit": "samples/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "ms_per_step": ms_e / args.steps,
+               "last_loss": loss}
+    if rank == 0:
+        emit(args, world, ms, clocks, e2e, launches, impl="ours",
+             extra={"comm": tr.comm, "symm_transport": getattr(tr.heap, "transport", None),
+                    "nvls": bool(getattr(tr.heap, "mc_ptr", 0)), "cuda_graph": not args.no_graph,
+                    "tcgen05_gemm": tr.model.gemm is not None,
+                    "launches_per_step": tr.launches_per_step,
+                    "kernel_lib": L.lib_path()})
+    finish(world)
+
+
+def run_stock(args):
+    import torch
+    import torch.distributed as dist
+    import torchvision
+    from kubedl_b200.worker.ddp_trainer import init_distributed
+    rank, world, _ = init_distributed("nccl")
+    torch.backends.cudnn.benchmark = True
+    model = torchvision.models.resnet50().cuda().to(memory_format=torch.channels_last)
+    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    if world > 1:
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[torch.cuda.current_device()])
+    crit = torch.nn.CrossEntropyLoss()
+    pool = synth_batches(args.batch, 4)
+    mean = torch.tensor([0.485, 0.456, 0.406], device="cuda").view(1, 3, 1, 1) * 255
+    std = torch.tensor([0.229, 0.224, 0.225], device="cuda").view(1, 3, 1, 1) * 255
+    dev = [(p[0].cuda(), p[1].cuda()) for p in pool[:2]]
+
+    def step_dev(img_u8, lab):
+        x = img_u8.permute(0, 3, 1, 2).float().sub_(mean).div_(std).contiguous(memory_format=torch.channels_last)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = crit(model(x), lab)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        return loss
+
+    for i in range(max(args.warmup, 3)):
+        step_dev(*dev[i & 1])
+    sampler = ClockSampler(torch.cuda.current_device())
+    sampler.start()
+    ms = timed(lambda i: step_dev(*dev[i & 1]), args.steps, world)
+    clocks = sampler.stop()
+    e2e = None
+    if not args.no_e2e:
+        def e2e_step(i):
+            img, lab = pool[i % len(pool)]
+            loss = step_dev(img.cuda(non_blocking=True), lab.cuda(non_blocking=True))
+            return float(loss.item())
+        e2e_step(0)
+        ms_e = timed(e2e_step, args.steps, world)
+        h2d = pool[0][0].numel() + pool[0][1].numel() * 8
+        e2e = {"value": args.batch * world * args.steps / (ms_e / 1e3), "unit": "samples/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "ms_per_step": ms_e / args.steps}
+    if rank == 0:
+        emit(args, world, ms, clocks, e2e, 0, impl="stock", extra={"comm": "nccl (torch DDP)"})
+    finish(world)
+
+
+def emit(args, world, ms, clocks, e2e, launches, impl, extra):
+    value = args.batch * world * args.steps / (ms / 1e3)
+    rec = {
+        "metric": "DDP samples/sec (ResNet-50 bf16 training, synthetic 224x224)",
+        "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic uint8 224x224x3 images + random labels, random-init weights",
+        "impl": impl,
+        "config": {"model": "resnet50", "global_batch": args.batch * world, "per_gpu_batch": args.batch,
+                   "seq_len": None, "image_size": 224, "parallelism": f"dp{world}",
+                   "optimizer": "sgd momentum 0.9 wd 1e-4, fp32 master weights",
+                   "l2_policy": "inputs_larger_than_l2 (per-step working set ~20 GB >> 126 MB L2)",
+                   **extra},
+        "clocks": clocks, "gpu_launches": launches,
+    }
+    if e2e is not None:
+        rec["e2e"] = e2e
+    print(json.dumps(rec), flush=True)
+
+
+def finish(world):
+    import torch.distributed as dist
+    if world > 1 and dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps({"impl": "reference", "unavailable": REF_UNAVAILABLE}), flush=True)
+        return 0
+    maybe_respawn_under_torchrun(args)
+    if args.impl == "stock":
+        run_stock(args)
+    else:
+        run_ours(args)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

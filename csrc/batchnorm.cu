@@ -1,0 +1,482 @@
+// Fused training-mode BatchNorm kernels for NHWC bf16 activations viewed as [M, C]
+// (M = N*H*W rows, C channels contiguous).
+//
+//   forward : (1) per-channel sum / sum-of-squares with the finalisation (mean, rstd,
+//                 running stats, scale/shift vectors) done by the last-arriving block,
+//             (2) y = relu(a*x + b + residual) in one pass.
+//   backward: (1) dbeta/dgamma reduction fused with the ReLU mask, finalised in-kernel into
+//                 the three per-channel coefficient vectors of the dx formula,
+//             (2) dx = A*dz + B*x + D (and dz written out for the residual branch).
+//
+// Replaces cuDNN BN + separate ReLU + separate residual add of the stock worker
+// (SURVEY.md §2.4 row N8).  No counterpart in the reference operator: it only launches
+// opaque worker images (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15).
+#include "common.cuh"
+#include "../include/kubedl_b200.h"
+
+namespace kdl {
+
+struct BnReduceParams {
+  // MODE 0 (fwd): a = x.  MODE 1 (bwd): a = dy, b = y (relu output, mask), c = x.
+  const bf16* a;
+  const bf16* b;
+  const bf16* c;
+  int64_t M;
+  int C;
+  int CS;        // channels per slice (blockIdx.y)
+  int tpr;       // threads per row-slice = CS/8
+  int rpb;       // rows per block iteration
+  float* partial;     // [nslices][gx][2*CS]
+  unsigned* counter;  // [nslices], zero on entry, zero on exit
+  // fwd finalisation
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  float eps;
+  float momentum;
+  float* mean_rstd;  // [2][C] saved for backward (fwd: out, bwd: in)
+  float* coef;       // fwd: [2][C] (a,b); bwd: [3][C] (A,B,D)
+  // bwd finalisation
+  bf16* dgamma;
+  bf16* dbeta;
+  int relu;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
+  __shared__ float red[256 * 16];
+  __shared__ int is_last;
+  const int tid = threadIdx.x;
+  const int nthreads = blockDim.x;
+  const int cg = tid % p.tpr;
+  const int r0 = tid / p.tpr;
+  const int slice = blockIdx.y;
+  const int ch0 = slice * p.CS + cg * 8;
+  const int64_t step = (int64_t)gridDim.x * p.rpb;
+
+  float s0[8], s1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
+
+  float mean[8], rstd[8];
+  if (MODE == 1) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      mean[j] = p.mean_rstd[ch0 + j];
+      rstd[j] = p.mean_rstd[p.C + ch0 + j];
+    }
+  }
+
+  constexpr int U = 4;
+  for (int64_t row = (int64_t)blockIdx.x * p.rpb + r0; row < p.M; row += step * U) {
+    uint4 va[U], vb[U], vc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t r = row + u * step;
+      if (r < p.M) {
+        int64_t off = r * p.C + ch0;
+        va[u] = ld_stream(p.a + off);
+        if (MODE == 1) {
+          vc[u] = ld_stream(p.c + off);
+          if (p.relu) vb[u] = ld_stream(p.b + off);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t r = row + u * step;
+      if (r < p.M) {
+        float fa[8];
+        unpack8(va[u], fa);
+        if (MODE == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s0[j] += fa[j];
+            s1[j] = fmaf(fa[j], fa[j], s1[j]);
+          }
+        } else {
+          float fx[8];
+          unpack8(vc[u], fx);
+          if (p.relu) {
+            float fy[8];
+            unpack8(vb[u], fy);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) fa[j] = fy[j] > 0.f ? fa[j] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            s0[j] += fa[j];
+            s1[j] = fmaf(fa[j], (fx[j] - mean[j]) * rstd[j], s1[j]);
+          }
+        }
+      }
+    }
+  }
+
+  // block reduce over the rpb row lanes
+  const int W2 = 2 * p.CS;
+  float* mine = red + (size_t)r0 * W2;
+  // NOTE: rpb*2*CS <= 256*16 by construction (tpr*rpb <= 256, 16 values per thread)
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[cg * 8 + j] = s0[j];
+    mine[p.CS + cg * 8 + j] = s1[j];
+  }
+  __syncthreads();
+  float* my_partial = p.partial + ((size_t)slice * gridDim.x + blockIdx.x) * W2;
+  for (int o = tid; o < W2; o += nthreads) {
+    float acc = 0.f;
+    for (int r = 0; r < p.rpb; ++r) acc += red[(size_t)r * W2 + o];
+    my_partial[o] = acc;
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    unsigned prev = atomicAdd(p.counter + slice, 1u);
+    is_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+
+  // ---- finalisation by the last block of this slice (fixed summation order) ----
+  const float* base = p.partial + (size_t)slice * gridDim.x * W2;
+  const int nf4 = W2 / 4;
+  const int gx = gridDim.x;
+  float* fin = red;  // [parts][W2] or [W2]
+  if (nf4 <= nthreads) {
+    const int parts = nthreads / nf4;
+    const int part = tid / nf4;
+    const int c4 = tid % nf4;
+    if (part < parts) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int bx = part; bx < gx; bx += parts) {
+        float4 v = __ldcg(reinterpret_cast<const float4*>(base + (size_t)bx * W2) + c4);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      reinterpret_cast<float4*>(fin + (size_t)part * W2)[c4] = acc;
+    }
+    __syncthreads();
+    float* fin2 = red + 2048;  // parts*W2 <= 1024 floats, so the two regions are disjoint
+    for (int o = tid; o < W2; o += nthreads) {
+      float acc = 0.f;
+      for (int q = 0; q < parts; ++q) acc += fin[(size_t)q * W2 + o];
+      fin2[o] = acc;
+    }
+    fin = fin2;
+  } else {
+    for (int c4 = tid; c4 < nf4; c4 += nthreads) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int bx = 0; bx < gx; ++bx) {
+        float4 v = __ldcg(reinterpret_cast<const float4*>(base + (size_t)bx * W2) + c4);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      reinterpret_cast<float4*>(fin)[c4] = acc;
+    }
+  }
+  __syncthreads();
+  const float invM = 1.f / (float)p.M;
+  for (int cl = tid; cl < p.CS; cl += nthreads) {
+    const int c = slice * p.CS + cl;
+    const float S0 = fin[cl], S1 = fin[p.CS + cl];
+    if (MODE == 0) {
+      float mu = S0 * invM;
+      float var = fmaxf(S1 * invM - mu * mu, 0.f);
+      float rs = rsqrtf(var + p.eps);
+      float g = p.gamma ? p.gamma[c] : 1.f;
+      float bt = p.beta ? p.beta[c] : 0.f;
+      float a = g * rs;
+      p.mean_rstd[c] = mu;
+      p.mean_rstd[p.C + c] = rs;
+      p.coef[c] = a;
+      p.coef[p.C + c] = bt - mu * a;
+      if (p.running_mean) {
+        float unbiased = p.M > 1 ? var * ((float)p.M / (float)(p.M - 1)) : var;
+        p.running_mean[c] = (1.f - p.momentum) * p.running_mean[c] + p.momentum * mu;
+        p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * unbiased;
+      }
+    } else {
+      float mu = p.mean_rstd[c], rs = p.mean_rstd[p.C + c];
+      float g = p.gamma ? p.gamma[c] : 1.f;
+      float a = g * rs;
+      float c1 = S0 * invM, c2 = S1 * invM;
+      if (p.dbeta) p.dbeta[c] = __float2bfloat16(S0);
+      if (p.dgamma) p.dgamma[c] = __float2bfloat16(S1);
+      // dx = a*(dz - c1 - xhat*c2) = A*dz + B*x + D
+      p.coef[c] = a;
+      p.coef[p.C + c] = -a * c2 * rs;
+      p.coef[2 * p.C + c] = a * (c2 * rs * mu - c1);
+    }
+  }
+  if (tid == 0) p.counter[slice] = 0u;
+}
+
+// y = relu?(a*x + b (+res)).  Flat vector index; when the total thread count is a multiple
+// of C/8 each thread keeps its channel group (and a,b in registers) across iterations.
+template <bool FIXED_CG>
+__global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ x,
+                                                       const bf16* __restrict__ res,
+                                                       bf16* __restrict__ y, int64_t nvec, int cvec,
+                                                       int C, const float* __restrict__ coef,
+                                                       int relu) {
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float a[8], b[8];
+  if (FIXED_CG) {
+    int cg = (int)(i % cvec);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      a[j] = coef[cg * 8 + j];
+      b[j] = coef[C + cg * 8 + j];
+    }
+  }
+  constexpr int U = 4;
+  for (; i < nvec; i += T * U) {
+    uint4 vx[U], vr[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t k = i + u * T;
+      if (k < nvec) {
+        vx[u] = ld_stream(x + k * 8);
+        if (res) vr[u] = ld_stream(res + k * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t k = i + u * T;
+      if (k < nvec) {
+        if (!FIXED_CG) {
+          int cg = (int)(k % cvec);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            a[j] = coef[cg * 8 + j];
+            b[j] = coef[C + cg * 8 + j];
+          }
+        }
+        float f[8];
+        unpack8(vx[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaf(a[j], f[j], b[j]);
+        if (res) {
+          float r[8];
+          unpack8(vr[u], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] += r[j];
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        *reinterpret_cast<uint4*>(y + k * 8) = pack8(f);
+      }
+    }
+  }
+}
+
+// dx = A*dz + B*x + D with dz = dy * (y > 0); optionally dres = dz.
+template <bool FIXED_CG>
+__global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
+                                                    const bf16* __restrict__ x,
+                                                    const bf16* __restrict__ y, bf16* dx, bf16* dres,
+                                                    int64_t nvec, int cvec, int C,
+                                                    const float* __restrict__ coef, int relu) {
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float A[8], B[8], D[8];
+  if (FIXED_CG) {
+    int cg = (int)(i % cvec);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      A[j] = coef[cg * 8 + j];
+      B[j] = coef[C + cg * 8 + j];
+      D[j] = coef[2 * C + cg * 8 + j];
+    }
+  }
+  constexpr int U = 2;
+  for (; i < nvec; i += T * U) {
+    uint4 vd[U], vx[U], vy[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t k = i + u * T;
+      if (k < nvec) {
+        vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
+        vx[u] = ld_stream(x + k * 8);
+        if (relu) vy[u] = ld_stream(y + k * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t k = i + u * T;
+      if (k < nvec) {
+        if (!FIXED_CG) {
+          int cg = (int)(k % cvec);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            A[j] = coef[cg * 8 + j];
+            B[j] = coef[C + cg * 8 + j];
+            D[j] = coef[2 * C + cg * 8 + j];
+          }
+        }
+        float fd[8], fx[8];
+        unpack8(vd[u], fd);
+        unpack8(vx[u], fx);
+        if (relu) {
+          float fy[8];
+          unpack8(vy[u], fy);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) fd[j] = fy[j] > 0.f ? fd[j] : 0.f;
+        }
+        if (dres) *reinterpret_cast<uint4*>(dres + k * 8) = pack8(fd);
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = fmaf(A[j], fd[j], fmaf(B[j], fx[j], D[j]));
+        *reinterpret_cast<uint4*>(dx + k * 8) = pack8(o);
+      }
+    }
+  }
+}
+
+struct BnPlan {
+  int CS, tpr, rpb, threads, nslices, gx;
+  size_t partial_floats;
+};
+
+static bool make_plan(int64_t M, int C, BnPlan* pl) {
+  if (C % 8 != 0 || C <= 0 || M <= 0) return false;
+  if (C % 64 == 0) {
+    pl->CS = 64;
+  } else {
+    if (C > 2048) return false;
+    pl->CS = C;
+  }
+  pl->tpr = pl->CS / 8;
+  pl->rpb = 256 / pl->tpr;
+  if (pl->rpb < 1) pl->rpb = 1;
+  pl->threads = pl->tpr * pl->rpb;
+  pl->nslices = C / pl->CS;
+  int64_t want = (M + (int64_t)pl->rpb * 8 - 1) / ((int64_t)pl->rpb * 8);  // >= 8 iterations each
+  int64_t cap = (148 * 4) / pl->nslices;
+  if (cap < 1) cap = 1;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  pl->gx = (int)want;
+  pl->partial_floats = (size_t)pl->nslices * pl->gx * 2 * pl->CS;
+  return true;
+}
+
+static const size_t kCounterBytes = 256;  // up to 64 slice counters
+
+}  // namespace kdl
+
+using namespace kdl;
+
+extern "C" size_t kdl_bn_workspace_bytes(int64_t M, int C) {
+  BnPlan pl;
+  if (!make_plan(M, C, &pl)) return 0;
+  // counters | coef[3][C] | partials
+  return kCounterBytes + (size_t)3 * C * sizeof(float) + pl.partial_floats * sizeof(float);
+}
+
+static int carve(void* ws, size_t ws_bytes, int64_t M, int C, BnPlan* pl, unsigned** counter,
+                 float** coef, float** partial) {
+  if (!make_plan(M, C, pl)) {
+    kdl_set_error("bn: unsupported shape M=%lld C=%d (need C%%8==0)", (long long)M, C);
+    return KDL_ERR_ARG;
+  }
+  if (pl->nslices > 64) {
+    kdl_set_error("bn: C=%d too large", C);
+    return KDL_ERR_ARG;
+  }
+  size_t need = kdl_bn_workspace_bytes(M, C);
+  if (ws == nullptr || ws_bytes < need) {
+    kdl_set_error("bn: workspace too small (%zu < %zu)", ws_bytes, need);
+    return KDL_ERR_WORKSPACE;
+  }
+  char* b = (char*)ws;
+  *counter = (unsigned*)b;
+  *coef = (float*)(b + kCounterBytes);
+  *partial = *coef + (size_t)3 * C;
+  return KDL_OK;
+}
+
+static int apply_grid(int64_t nvec) {
+  int64_t g = (nvec + 256 * 4 - 1) / (256 * 4);
+  if (g > 148 * 8) g = 148 * 8;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+extern "C" int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, int C,
+                          const float* gamma, const float* beta, float* running_mean,
+                          float* running_var, float eps, float momentum, int relu,
+                          float* save_mean_rstd, void* workspace, size_t workspace_bytes,
+                          cudaStream_t stream) {
+  BnPlan pl;
+  unsigned* counter;
+  float *coef, *partial;
+  int rc = carve(workspace, workspace_bytes, M, C, &pl, &counter, &coef, &partial);
+  if (rc) return rc;
+  BnReduceParams p = {};
+  p.a = (const bf16*)x;
+  p.M = M; p.C = C; p.CS = pl.CS; p.tpr = pl.tpr; p.rpb = pl.rpb;
+  p.partial = partial; p.counter = counter;
+  p.gamma = gamma; p.beta = beta;
+  p.running_mean = running_mean; p.running_var = running_var;
+  p.eps = eps; p.momentum = momentum;
+  p.mean_rstd = save_mean_rstd; p.coef = coef;
+  bn_reduce_kernel<0><<<dim3(pl.gx, pl.nslices), pl.threads, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  int64_t nvec = M * C / 8;
+  int cvec = C / 8;
+  int g = apply_grid(nvec);
+  bool fixed = (256 % cvec) == 0;
+  if (fixed)
+    bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec,
+                                                 cvec, C, coef, relu);
+  else
+    bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec,
+                                                  cvec, C, coef, relu);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dres,
+                          int64_t M, int C, const float* gamma, const float* save_mean_rstd,
+                          int relu, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
+                          size_t workspace_bytes, cudaStream_t stream) {
+  BnPlan pl;
+  unsigned* counter;
+  float *coef, *partial;
+  int rc = carve(workspace, workspace_bytes, M, C, &pl, &counter, &coef, &partial);
+  if (rc) return rc;
+  if (relu && y == nullptr) {
+    kdl_set_error("bn_bwd: relu mask needs y");
+    return KDL_ERR_ARG;
+  }
+  BnReduceParams p = {};
+  p.a = (const bf16*)dy; p.b = (const bf16*)y; p.c = (const bf16*)x;
+  p.M = M; p.C = C; p.CS = pl.CS; p.tpr = pl.tpr; p.rpb = pl.rpb;
+  p.partial = partial; p.counter = counter;
+  p.gamma = gamma;
+  p.mean_rstd = const_cast<float*>(save_mean_rstd);
+  p.coef = coef;
+  p.dgamma = (bf16*)dgamma_bf16; p.dbeta = (bf16*)dbeta_bf16;
+  p.relu = relu;
+  bn_reduce_kernel<1><<<dim3(pl.gx, pl.nslices), pl.threads, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  int64_t nvec = M * C / 8;
+  int cvec = C / 8;
+  int64_t g64 = (nvec + 256 * 2 - 1) / (256 * 2);
+  if (g64 > 148 * 8) g64 = 148 * 8;
+  int g = (int)(g64 < 1 ? 1 : g64);
+  bool fixed = (256 % cvec) == 0;
+  if (fixed)
+    bn_dx_kernel<true><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
+                                              (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu);
+  else
+    bn_dx_kernel<false><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
+                                               (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}

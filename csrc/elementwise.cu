@@ -1,0 +1,421 @@
+// Memory-bound fused kernels of the DDP worker: input normalisation,
+// softmax cross-entropy forward+backward, momentum-SGD with fp32 master weights, NHWC max-pool /
+// global average pool, residual gradient add.  All 128-bit vectorised, bf16 storage, fp32 math.
+// The reference operator has no worker code; these replace the ATen/cuDNN kernels of the stock
+// image it would launch (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15).
+#include "common.cuh"
+#include "../include/kubedl_b200.h"
+#include <float.h>
+
+namespace kdl {
+
+// uint8 NHWC (C=3) -> bf16 NHWC with per-channel (x/255 - mean)/std, optionally zero-padded to
+// Cpad channels (Cpad = 3, 4 or 8) so the stem convolution can run as a tensor-core GEMM.
+__global__ void __launch_bounds__(256) u8_normalize_kernel(const uint8_t* __restrict__ in,
+                                                           bf16* __restrict__ out, int64_t npix,
+                                                           int cpad, float m0, float m1, float m2,
+                                                           float s0, float s1, float s2) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  const float k = 1.f / 255.f;
+  for (; i < npix; i += T) {
+    const uint8_t* p = in + i * 3;
+    float r = ((float)p[0] * k - m0) * s0;
+    float g = ((float)p[1] * k - m1) * s1;
+    float b = ((float)p[2] * k - m2) * s2;
+    bf16* o = out + i * cpad;
+    o[0] = __float2bfloat16(r);
+    o[1] = __float2bfloat16(g);
+    o[2] = __float2bfloat16(b);
+    for (int c = 3; c < cpad; ++c) o[c] = __float2bfloat16(0.f);
+  }
+}
+
+// One block per row: loss_i = logsumexp(z) - z[label]; dlogits = (softmax - onehot) * gscale.
+// The mean loss is produced by the last-arriving block (fixed order sum over rows).
+template <typename TIn>
+__global__ void __launch_bounds__(256) softmax_xent_kernel(const TIn* __restrict__ logits,
+                                                           const int64_t* __restrict__ labels,
+                                                           bf16* __restrict__ dlogits,
+                                                           float* __restrict__ row_loss,
+                                                           float* __restrict__ loss_out,
+                                                           unsigned* counter, int B, int V, int ldv,
+                                                           float gscale) {
+  __shared__ float sred[32];
+  __shared__ float sval;
+  __shared__ int is_last;
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const TIn* z = logits + (size_t)row * ldv;
+  float mx = -FLT_MAX;
+  for (int j = tid; j < V; j += blockDim.x) mx = fmaxf(mx, (float)z[j]);
+  mx = warp_max(mx);
+  if (lane == 0) sred[warp] = mx;
+  __syncthreads();
+  if (warp == 0) {
+    float v = lane < nw ? sred[lane] : -FLT_MAX;
+    v = warp_max(v);
+    if (lane == 0) sval = v;
+  }
+  __syncthreads();
+  mx = sval;
+  __syncthreads();
+  float sum = 0.f;
+  for (int j = tid; j < V; j += blockDim.x) sum += __expf((float)z[j] - mx);
+  sum = warp_sum(sum);
+  if (lane == 0) sred[warp] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    float v = lane < nw ? sred[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) sval = v;
+  }
+  __syncthreads();
+  sum = sval;
+  const float inv = 1.f / sum;
+  const int lab = (int)labels[row];
+  if (dlogits) {
+    bf16* d = dlogits + (size_t)row * ldv;
+    for (int j = tid; j < V; j += blockDim.x) {
+      float pj = __expf((float)z[j] - mx) * inv;
+      d[j] = __float2bfloat16((pj - (j == lab ? 1.f : 0.f)) * gscale);
+    }
+    for (int j = V + tid; j < ldv; j += blockDim.x) d[j] = __float2bfloat16(0.f);
+  }
+  if (tid == 0) {
+    float zl = (lab >= 0 && lab < V) ? (float)z[lab] : mx;
+    row_loss[row] = logf(sum) + mx - zl;
+    __threadfence();
+    unsigned prev = atomicAdd(counter, 1u);
+    is_last = (prev == (unsigned)B - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  float acc = 0.f;
+  for (int j = tid; j < B; j += blockDim.x) acc += __ldcg(row_loss + j);
+  acc = warp_sum(acc);
+  __syncthreads();
+  if (lane == 0) sred[warp] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+    for (int w = 0; w < nw; ++w) t += sred[w];
+    *loss_out = t / (float)B;
+    *counter = 0u;
+  }
+}
+
+// Momentum SGD over a flat parameter arena: fp32 master + fp32 momentum, bf16 gradient in,
+// bf16 compute copy out.  Elements [0, wd_count) get weight decay (conv/fc weights), the rest
+// (BN scale/shift, biases) do not.  grad_scale folds in any deferred averaging.
+__global__ void __launch_bounds__(256) sgd_momentum_kernel(float* __restrict__ p32,
+                                                           float* __restrict__ mom,
+                                                           const bf16* __restrict__ g16,
+                                                           bf16* __restrict__ p16, int64_t n,
+                                                           int64_t wd_count, float lr, float mu,
+                                                           float wd, float grad_scale) {
+  const int64_t nvec = n / 8;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += T) {
+    uint4 vg = ld_stream(g16 + i * 8);
+    float4 pa = reinterpret_cast<const float4*>(p32)[2 * i];
+    float4 pb = reinterpret_cast<const float4*>(p32)[2 * i + 1];
+    float4 ma = reinterpret_cast<const float4*>(mom)[2 * i];
+    float4 mb = reinterpret_cast<const float4*>(mom)[2 * i + 1];
+    float g[8], p[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w},
+                m[8] = {ma.x, ma.y, ma.z, ma.w, mb.x, mb.y, mb.z, mb.w};
+    unpack8(vg, g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float d = (i * 8 + j) < wd_count ? wd : 0.f;
+      float gj = fmaf(d, p[j], g[j] * grad_scale);
+      m[j] = fmaf(mu, m[j], gj);
+      p[j] = fmaf(-lr, m[j], p[j]);
+    }
+    reinterpret_cast<float4*>(p32)[2 * i] = make_float4(p[0], p[1], p[2], p[3]);
+    reinterpret_cast<float4*>(p32)[2 * i + 1] = make_float4(p[4], p[5], p[6], p[7]);
+    reinterpret_cast<float4*>(mom)[2 * i] = make_float4(m[0], m[1], m[2], m[3]);
+    reinterpret_cast<float4*>(mom)[2 * i + 1] = make_float4(m[4], m[5], m[6], m[7]);
+    *reinterpret_cast<uint4*>(p16 + i * 8) = pack8(p);
+  }
+  // tail (n not a multiple of 8)
+  if (blockIdx.x == 0) {
+    for (int64_t k = nvec * 8 + threadIdx.x; k < n; k += blockDim.x) {
+      float d = k < wd_count ? wd : 0.f;
+      float gj = fmaf(d, p32[k], __bfloat162float(g16[k]) * grad_scale);
+      float mk = fmaf(mu, mom[k], gj);
+      mom[k] = mk;
+      float pk = fmaf(-lr, mk, p32[k]);
+      p32[k] = pk;
+      p16[k] = __float2bfloat16(pk);
+    }
+  }
+}
+
+// out = a + b  (bf16, 128-bit); out may alias a or b.
+__global__ void __launch_bounds__(256) add_bf16_kernel(const bf16* a, const bf16* b, bf16* out,
+                                                       int64_t nvec) {
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += T) {
+    uint4 va = ld_plain(a + i * 8), vb = ld_plain(b + i * 8);
+    float fa[8], fb[8];
+    unpack8(va, fa);
+    unpack8(vb, fb);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) fa[j] += fb[j];
+    *reinterpret_cast<uint4*>(out + i * 8) = pack8(fa);
+  }
+}
+
+// 3x3 stride-2 pad-1 max-pool on NHWC bf16; saves the argmax (0..8) per output vector lane so
+// the backward pass is a gather (each input pixel looks at the <=4 windows that cover it).
+__global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __restrict__ x,
+                                                               bf16* __restrict__ y,
+                                                               uint8_t* __restrict__ idx, int N,
+                                                               int H, int W, int C, int OH, int OW) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * OH * OW * cvec;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
+    int cg = (int)(i % cvec);
+    int64_t t = i / cvec;
+    int ow = (int)(t % OW); t /= OW;
+    int oh = (int)(t % OH);
+    int n = (int)(t / OH);
+    float best[8];
+    int bi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -FLT_MAX; bi[j] = 4; }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      int ih = oh * 2 - 1 + kh;
+      if (ih < 0 || ih >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        int iw = ow * 2 - 1 + kw;
+        if (iw < 0 || iw >= W) continue;
+        uint4 v = ld_plain(x + (((int64_t)n * H + ih) * W + iw) * C + cg * 8);
+        float f[8];
+        unpack8(v, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > best[j]) { best[j] = f[j]; bi[j] = kh * 3 + kw; }
+      }
+    }
+    *reinterpret_cast<uint4*>(y + i * 8) = pack8(best);
+    uint2 pk;
+    pk.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+    pk.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+    *reinterpret_cast<uint2*>(idx + i * 8) = pk;
+  }
+}
+
+__global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __restrict__ dy,
+                                                               const uint8_t* __restrict__ idx,
+                                                               bf16* __restrict__ dx, int N, int H,
+                                                               int W, int C, int OH, int OW) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * H * W * cvec;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
+    int cg = (int)(i % cvec);
+    int64_t t = i / cvec;
+    int iw = (int)(t % W); t /= W;
+    int ih = (int)(t % H);
+    int n = (int)(t / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    // windows (oh, ow) with ih = 2*oh-1+kh, kh in 0..2  ->  oh in {(ih+1)/2, (ih+1)/2 - 1(if valid)}
+    for (int oh = (ih + 1) / 2 - 1; oh <= (ih + 1) / 2; ++oh) {
+      if (oh < 0 || oh >= OH) continue;
+      int kh = ih - (oh * 2 - 1);
+      if (kh < 0 || kh > 2) continue;
+      for (int ow = (iw + 1) / 2 - 1; ow <= (iw + 1) / 2; ++ow) {
+        if (ow < 0 || ow >= OW) continue;
+        int kw = iw - (ow * 2 - 1);
+        if (kw < 0 || kw > 2) continue;
+        int64_t o = (((int64_t)n * OH + oh) * OW + ow) * cvec + cg;
+        uint2 pk = *reinterpret_cast<const uint2*>(idx + o * 8);
+        uint4 v = ld_plain(dy + o * 8);
+        float f[8];
+        unpack8(v, f);
+        const int code = kh * 3 + kw;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          int b = (j < 4 ? (pk.x >> (8 * j)) : (pk.y >> (8 * (j - 4)))) & 0xff;
+          if (b == code) acc[j] += f[j];
+        }
+      }
+    }
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(acc);
+  }
+}
+
+// Global average pool NHWC [N, HW, C] -> [N, C] and its backward (broadcast / HW).
+__global__ void __launch_bounds__(256) avgpool_fwd_kernel(const bf16* __restrict__ x,
+                                                          bf16* __restrict__ y, int N, int HW,
+                                                          int C) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * cvec;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int cg = (int)(i % cvec);
+  int n = (int)(i / cvec);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int p = 0; p < HW; ++p) {
+    uint4 v = ld_stream(x + ((int64_t)n * HW + p) * C + cg * 8);
+    float f[8];
+    unpack8(v, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += f[j];
+  }
+  const float inv = 1.f / (float)HW;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] *= inv;
+  *reinterpret_cast<uint4*>(y + i * 8) = pack8(acc);
+}
+
+__global__ void __launch_bounds__(256) avgpool_bwd_kernel(const bf16* __restrict__ dy,
+                                                          bf16* __restrict__ dx, int N, int HW,
+                                                          int C) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * HW * cvec;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  const float inv = 1.f / (float)HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
+    int cg = (int)(i % cvec);
+    int n = (int)(i / ((int64_t)HW * cvec));
+    uint4 v = ld_plain(dy + ((int64_t)n * cvec + cg) * 8);
+    float f[8];
+    unpack8(v, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= inv;
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(f);
+  }
+}
+
+static int grid_for(int64_t n, int per_block) {
+  int64_t g = (n + per_block - 1) / per_block;
+  if (g > 148 * 16) g = 148 * 16;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace kdl
+
+using namespace kdl;
+
+extern "C" int kdl_u8_normalize(const void* in_u8, void* out_bf16, int64_t npix, int cpad,
+                                const float* mean3, const float* std3, cudaStream_t stream) {
+  if (cpad < 3 || cpad > 8) {
+    kdl_set_error("u8_normalize: cpad must be in [3,8]");
+    return KDL_ERR_ARG;
+  }
+  u8_normalize_kernel<<<grid_for(npix, 256 * 4), 256, 0, stream>>>(
+      (const uint8_t*)in_u8, (bf16*)out_bf16, npix, cpad, mean3[0], mean3[1], mean3[2],
+      1.f / std3[0], 1.f / std3[1], 1.f / std3[2]);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" size_t kdl_softmax_xent_workspace_bytes(int B) { return 256 + (size_t)B * sizeof(float); }
+
+extern "C" int kdl_softmax_xent(const void* logits, int logits_is_fp32, const int64_t* labels,
+                                void* dlogits_bf16, float* loss_out, int B, int V, int ldv,
+                                float grad_scale, void* workspace, size_t workspace_bytes,
+                                cudaStream_t stream) {
+  if (workspace_bytes < kdl_softmax_xent_workspace_bytes(B)) {
+    kdl_set_error("softmax_xent: workspace too small");
+    return KDL_ERR_WORKSPACE;
+  }
+  unsigned* counter = (unsigned*)workspace;
+  float* row_loss = (float*)((char*)workspace + 256);
+  if (logits_is_fp32)
+    softmax_xent_kernel<float><<<B, 256, 0, stream>>>((const float*)logits, labels,
+                                                      (bf16*)dlogits_bf16, row_loss, loss_out,
+                                                      counter, B, V, ldv, grad_scale);
+  else
+    softmax_xent_kernel<bf16><<<B, 256, 0, stream>>>((const bf16*)logits, labels,
+                                                     (bf16*)dlogits_bf16, row_loss, loss_out,
+                                                     counter, B, V, ldv, grad_scale);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_sgd_momentum(float* p32, float* mom, const void* g16, void* p16, int64_t n,
+                                int64_t wd_count, float lr, float mu, float wd, float grad_scale,
+                                cudaStream_t stream) {
+  sgd_momentum_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, stream>>>(
+      p32, mom, (const bf16*)g16, (bf16*)p16, n, wd_count, lr, mu, wd, grad_scale);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_add_bf16(const void* a, const void* b, void* out, int64_t n,
+                            cudaStream_t stream) {
+  if (n % 8) {
+    kdl_set_error("add_bf16: n must be a multiple of 8");
+    return KDL_ERR_ARG;
+  }
+  add_bf16_kernel<<<grid_for(n / 8, 256), 256, 0, stream>>>((const bf16*)a, (const bf16*)b,
+                                                            (bf16*)out, n / 8);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_maxpool3x3s2_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W,
+                                    int C, cudaStream_t stream) {
+  if (C % 8) {
+    kdl_set_error("maxpool: C must be a multiple of 8");
+    return KDL_ERR_ARG;
+  }
+  int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+  int64_t total = (int64_t)N * OH * OW * (C / 8);
+  maxpool3x3s2_fwd_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
+      (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, OH, OW);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_maxpool3x3s2_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H,
+                                    int W, int C, cudaStream_t stream) {
+  if (C % 8) {
+    kdl_set_error("maxpool: C must be a multiple of 8");
+    return KDL_ERR_ARG;
+  }
+  int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+  int64_t total = (int64_t)N * H * W * (C / 8);
+  maxpool3x3s2_bwd_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
+      (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, N, H, W, C, OH, OW);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, cudaStream_t stream) {
+  if (C % 8) {
+    kdl_set_error("avgpool: C must be a multiple of 8");
+    return KDL_ERR_ARG;
+  }
+  int64_t total = (int64_t)N * (C / 8);
+  avgpool_fwd_kernel<<<(int)((total + 255) / 256), 256, 0, stream>>>((const bf16*)x, (bf16*)y, N,
+                                                                     HW, C);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C,
+                               cudaStream_t stream) {
+  if (C % 8) {
+    kdl_set_error("avgpool: C must be a multiple of 8");
+    return KDL_ERR_ARG;
+  }
+  int64_t total = (int64_t)N * HW * (C / 8);
+  avgpool_bwd_kernel<<<grid_for(total, 256), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, N, HW,
+                                                               C);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}

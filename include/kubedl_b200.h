@@ -1,0 +1,114 @@
+/* C ABI of libkubedl_b200.so — the hand-written sm_100a kernel library of the kubedl_b200
+ * worker runtime.  Every entry point returns 0 (KDL_OK) on success; on failure it returns a
+ * non-zero code and kdl_last_error() describes what went wrong.  Pointers are device pointers
+ * unless the name says otherwise; `stream` is a cudaStream_t passed as void*-compatible handle.
+ *
+ * The reference (jiaqianjing/kubedl) is a pure-Go operator with no device code at all
+ * (SURVEY.md §2.2); each block below cites the stock-worker behaviour it replaces and the
+ * reference file that wires that worker up.
+ */
+#ifndef KUBEDL_B200_H_
+#define KUBEDL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#else
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KDL_MAX_WORLD 8
+#define KDL_AR_MAX_BLOCKS 512
+
+/* dtype codes */
+#define KDL_BF16 0
+#define KDL_F32 1
+
+const char* kdl_last_error(void);
+int kdl_version(void);
+
+/* ---- N8: fused BatchNorm(+residual)(+ReLU), NHWC bf16 viewed as [M, C] ------------------
+ * Replaces cuDNN BN + ReLU + add of the stock PyTorch worker image
+ * (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15).  `workspace` is caller-owned
+ * scratch of kdl_bn_workspace_bytes(M, C) bytes whose first 256 bytes must be zero before the
+ * first use (the kernels restore them to zero). */
+size_t kdl_bn_workspace_bytes(int64_t M, int C);
+int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,
+               const float* beta, float* running_mean, float* running_var, float eps,
+               float momentum, int relu, float* save_mean_rstd, void* workspace,
+               size_t workspace_bytes, cudaStream_t stream);
+int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dres, int64_t M,
+               int C, const float* gamma, const float* save_mean_rstd, int relu,
+               void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
+               cudaStream_t stream);
+
+/* ---- N8: other memory-bound fused ops of the DDP worker --------------------------------- */
+int kdl_u8_normalize(const void* in_u8, void* out_bf16, int64_t npix, int cpad,
+                     const float* mean3_host, const float* std3_host, cudaStream_t stream);
+size_t kdl_softmax_xent_workspace_bytes(int B);
+int kdl_softmax_xent(const void* logits, int logits_is_fp32, const int64_t* labels,
+                     void* dlogits_bf16, float* loss_out, int B, int V, int ldv, float grad_scale,
+                     void* workspace, size_t workspace_bytes, cudaStream_t stream);
+int kdl_sgd_momentum(float* p32, float* mom, const void* g16, void* p16, int64_t n,
+                     int64_t wd_count, float lr, float mu, float wd, float grad_scale,
+                     cudaStream_t stream);
+int kdl_add_bf16(const void* a, const void* b, void* out, int64_t n, cudaStream_t stream);
+int kdl_maxpool3x3s2_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C,
+                         cudaStream_t stream);
+int kdl_maxpool3x3s2_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H, int W, int C,
+                         cudaStream_t stream);
+int kdl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, cudaStream_t stream);
+int kdl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t stream);
+
+/* ---- N1/N2: fused gradient-bucket all-reduce over NVLink peer memory ---------------------
+ * Replaces ncclAllReduce + div_ + cast of torch DDP, for which the reference only injects
+ * MASTER_ADDR/MASTER_PORT/WORLD_SIZE/RANK (reference
+ * controllers/pytorch/pytorchjob_controller.go:180-233).  in/out/flag pointer tables are HOST
+ * arrays of `world` device pointers (peer mappings of the same symmetric offset); flags must be
+ * kdl_allreduce_flags_bytes(channels) bytes per rank, zero-initialised once.  `epoch_state`
+ * is LOCAL device memory of the same size, zero-initialised once; the kernels keep the barrier
+ * epochs there, so launches can be captured into a CUDA graph and replayed.  Calls on one
+ * channel must be issued in the same order on all ranks.  mc_in/mc_out: optional NVLS
+ * multicast aliases (NULL -> P2P path).  emulate=1 runs all ranks inside one cooperative
+ * launch on one GPU (protocol test). */
+size_t kdl_allreduce_flags_bytes(int channels);
+int kdl_allreduce_fused(const void* const* in_ptrs, void* const* out_ptrs, void* const* flag_ptrs,
+                        const void* mc_in, void* mc_out, int world, int rank, int64_t n,
+                        int in_dtype, int out_dtype, float scale, void* epoch_state, int channels,
+                        int channel, int max_blocks, int emulate, void* status, unsigned long long timeout_ns,
+                        cudaStream_t stream);
+
+/* ---- symmetric memory plumbing ------------------------------------------
+ * Legacy CUDA IPC path (cudaMalloc + cudaIpc handles) and VMM path (cuMemCreate + POSIX fd
+ * export, needed for NVLS multicast).  The reference has no communication backend at all; it
+ * only provides DNS names and ports (reference pkg/job_controller/service.go:237-295). */
+int kdl_symm_malloc(size_t bytes, void** ptr);
+int kdl_symm_free(void* ptr);
+int kdl_ipc_get_handle(void* ptr, void* handle64_out);
+int kdl_ipc_open_handle(const void* handle64, void** ptr_out);
+int kdl_ipc_close_handle(void* ptr);
+int kdl_enable_peer_access(int peer_device);
+int kdl_vmm_supported(int device, int* posix_fd_ok, int* multicast_ok);
+size_t kdl_vmm_granularity(int device, int multicast_world);
+int kdl_vmm_alloc(int device, size_t bytes, unsigned long long* handle_out, void** ptr_out,
+                  int* fd_out);
+int kdl_vmm_import(int device, int fd, size_t bytes, unsigned long long* handle_out,
+                   void** ptr_out);
+int kdl_vmm_release(unsigned long long handle, void* ptr, size_t bytes);
+int kdl_mc_create(int world, size_t bytes, unsigned long long* mc_out, int* fd_out);
+int kdl_mc_import(int fd, unsigned long long* mc_out);
+int kdl_mc_add_device(unsigned long long mc, int device);
+int kdl_mc_bind_and_map(unsigned long long mc, unsigned long long mem_handle, int device,
+                        size_t bytes, void** mc_ptr_out);
+int kdl_mc_release(unsigned long long mc, void* mc_ptr, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KUBEDL_B200_H_ */

@@ -1,0 +1,256 @@
+"""ResNet-50 (v1.5, torchvision topology) as an explicit forward/backward program over the
+kubedl_b200 kernels — no autograd.
+
+Why explicit: every activation is NHWC bf16, every BN(+residual)(+ReLU) is one fused pass,
+gradients are written straight into the flat arena that the fused all-reduce works on, the
+reducer is told "prefix ready" right after each layer's wgrad, and the whole step (forward,
+backward, bucket all-reduces on a side stream, fused SGD) is a static launch sequence that
+can be captured once into a CUDA graph.
+
+Convolutions: 1x1 stride-1 convolutions and the FC layer are GEMMs on the [N*H*W, C] view and
+go to the tcgen05 GEMM kernel when it is enabled (ops.gemm); 7x7/3x3/strided convolutions go to
+cuDNN through ATen (library code, like the stock worker).  This is config #2 of
+BASELINE.json ("PyTorchJob ResNet-50 DDP bf16 ... synthetic 224² images").
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+
+from ..ops import nn as K
+from .arena import ParamArena
+
+_conv_bwd = torch.ops.aten.convolution_backward
+
+
+def _nchw(x_nhwc: torch.Tensor) -> torch.Tensor:
+    return x_nhwc.permute(0, 3, 1, 2)
+
+
+def _nhwc(x_nchw: torch.Tensor) -> torch.Tensor:
+    y = x_nchw.permute(0, 2, 3, 1)
+    return y if y.is_contiguous() else y.contiguous()
+
+
+class Conv:
+    def __init__(self, net: "ResNet50", name: str, cin: int, cout: int, k: int, stride: int, pad: int):
+        self.net, self.name = net, name
+        self.cin, self.cout, self.k, self.stride, self.pad = cin, cout, k, stride, pad
+        net.arena.declare(name, (cout, k, k, cin), decay=True, init="kaiming", fan=cout * k * k)
+
+    def bind(self):
+        a = self.net.arena
+        self.w = a.w16(self.name)                       # [Cout, kh, kw, Cin] physical
+        self.w_nchw = self.w.permute(0, 3, 1, 2)        # channels_last logical view for cuDNN
+        self.gw = a.grad(self.name).permute(0, 3, 1, 2)
+        self.g_end = a.end_offset(self.name)
+        self.is_gemm = (self.k == 1 and self.stride == 1)
+
+    def fwd(self, x: torch.Tensor) -> torch.Tensor:
+        net = self.net
+        if self.is_gemm and net.gemm is not None:
+            N, H, W, Cin = x.shape
+            y = net.gemm.nt(x.view(-1, Cin), self.w.view(self.cout, Cin))
+            return y.view(N, H, W, self.cout)
+        y = torch.ops.aten.convolution(_nchw(x), self.w_nchw, None, [self.stride] * 2,
+                                       [self.pad] * 2, [1, 1], False, [0, 0], 1)
+        return _nhwc(y)
+
+    def bwd(self, dy: torch.Tensor, x: torch.Tensor, need_dx: bool = True) -> Optional[torch.Tensor]:
+        net = self.net
+        if self.is_gemm and net.gemm is not None:
+            N, H, W, Cin = x.shape
+            dy2, x2 = dy.view(-1, self.cout), x.view(-1, Cin)
+            # dW[Cout, Cin] = dy^T x ; dx[M, Cin] = dy W
+            net.gemm.tn(dy2, x2, out=net.arena.grad(self.name).view(self.cout, Cin))
+            dx = net.gemm.nn(dy2, self.w.view(self.cout, Cin)).view(N, H, W, Cin) if need_dx else None
+        else:
+            dxn, dw, _ = _conv_bwd(_nchw(dy), _nchw(x), self.w_nchw, None, [self.stride] * 2,
+                                   [self.pad] * 2, [1, 1], False, [0, 0], 1, [need_dx, True, False])
+            self.gw.copy_(dw)
+            dx = _nhwc(dxn) if need_dx else None
+        net.reducer_ready(self.g_end)
+        return dx
+
+
+class BN:
+    def __init__(self, net: "ResNet50", name: str, c: int, relu: bool, zero_init: bool = False):
+        self.net, self.name, self.c, self.relu = net, name, c, relu
+        net.arena.declare(name + ".weight", (c,), decay=False, init="zeros" if zero_init else "ones")
+        net.arena.declare(name + ".bias", (c,), decay=False, init="zeros")
+
+    def bind(self):
+        a, dev = self.net.arena, self.net.device
+        self.gamma, self.beta = a.w32(self.name + ".weight"), a.w32(self.name + ".bias")
+        self.dgamma, self.dbeta = a.grad(self.name + ".weight"), a.grad(self.name + ".bias")
+        self.running_mean = torch.zeros(self.c, dtype=torch.float32, device=dev)
+        self.running_var = torch.ones(self.c, dtype=torch.float32, device=dev)
+        self.save = torch.empty(2, self.c, dtype=torch.float32, device=dev)
+
+    def fwd(self, x, res=None):
+        y, _ = K.bn_fwd(x, self.gamma, self.beta, self.running_mean, self.running_var, res=res,
+                        relu=self.relu, save=self.save)
+        return y
+
+    def bwd(self, dy, x, y, dres=None):
+        return K.bn_bwd(dy, x, y if self.relu else None, self.gamma, self.save, self.relu,
+                        self.dgamma, self.dbeta, dres=dres)
+
+
+class Bottleneck:
+    def __init__(self, net, name, cin, width, stride, downsample):
+        cout = width * 4
+        self.c1 = Conv(net, f"{name}.conv1", cin, width, 1, 1, 0)
+        self.b1 = BN(net, f"{name}.bn1", width, relu=True)
+        self.c2 = Conv(net, f"{name}.conv2", width, width, 3, stride, 1)
+        self.b2 = BN(net, f"{name}.bn2", width, relu=True)
+        self.c3 = Conv(net, f"{name}.conv3", width, cout, 1, 1, 0)
+        self.b3 = BN(net, f"{name}.bn3", cout, relu=True, zero_init=True)
+        self.cd = self.bd = None
+        if downsample:
+            self.cd = Conv(net, f"{name}.downsample.0", cin, cout, 1, stride, 0)
+            self.bd = BN(net, f"{name}.downsample.1", cout, relu=False)
+        self.saved = None
+
+    def modules(self):
+        ms = [self.c1, self.b1, self.c2, self.b2, self.c3, self.b3]
+        if self.cd is not None:
+            ms += [self.cd, self.bd]
+        return ms
+
+    def backward_param_order(self) -> List[str]:
+        names = [self.c3.name, self.b3.name + ".weight", self.b3.name + ".bias",
+                 self.c2.name, self.b2.name + ".weight", self.b2.name + ".bias",
+                 self.c1.name, self.b1.name + ".weight", self.b1.name + ".bias"]
+        if self.cd is not None:
+            names += [self.cd.name, self.bd.name + ".weight", self.bd.name + ".bias"]
+        return names
+
+    def fwd(self, x, train=True):
+        c1 = self.c1.fwd(x)
+        a1 = self.b1.fwd(c1)
+        c2 = self.c2.fwd(a1)
+        a2 = self.b2.fwd(c2)
+        c3 = self.c3.fwd(a2)
+        if self.cd is not None:
+            cdo = self.cd.fwd(x)
+            idn = self.bd.fwd(cdo)
+        else:
+            cdo, idn = None, x
+        out = self.b3.fwd(c3, res=idn)
+        if train:
+            self.saved = (x, c1, a1, c2, a2, c3, cdo, out)
+        return out
+
+    def bwd(self, dout, need_dx=True):
+        x, c1, a1, c2, a2, c3, cdo, out = self.saved
+        self.saved = None
+        dc3 = self.b3.bwd(dout, c3, out, dres=dout)  # dout now holds dz (grad of the residual)
+        dres = dout
+        da2 = self.c3.bwd(dc3, a2)
+        dc2 = self.b2.bwd(da2, c2, a2)
+        da1 = self.c2.bwd(dc2, a1)
+        dc1 = self.b1.bwd(da1, c1, a1)
+        dx = self.c1.bwd(dc1, x)
+        if self.cd is not None:
+            dcd = self.bd.bwd(dres, cdo, None)
+            dx2 = self.cd.bwd(dcd, x)
+            K.add_(dx, dx2)
+        else:
+            K.add_(dx, dres)
+        return dx
+
+
+class ResNet50:
+    LAYERS = [(64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)]
+
+    def __init__(self, device="cuda", num_classes: int = 1000, heap=None, gemm=None, seed: int = 0):
+        self.device = torch.device(device)
+        self.num_classes = num_classes
+        self.arena = ParamArena()
+        self.gemm = gemm
+        self.reducer = None
+        self.stem = Conv(self, "conv1", 3, 64, 7, 2, 3)
+        self.stem_bn = BN(self, "bn1", 64, relu=True)
+        self.blocks: List[Bottleneck] = []
+        cin = 64
+        for li, (width, n, stride) in enumerate(self.LAYERS, start=1):
+            for bi in range(n):
+                s = stride if bi == 0 else 1
+                self.blocks.append(Bottleneck(self, f"layer{li}.{bi}", cin, width, s, bi == 0))
+                cin = width * 4
+        self.fc_in = cin
+        self.arena.declare("fc.weight", (num_classes, cin), decay=True, init="fc", fan=cin)
+        self.arena.declare("fc.bias", (num_classes,), decay=False, init="fc", fan=cin)
+        order = ["fc.weight", "fc.bias"]
+        for b in reversed(self.blocks):
+            order += b.backward_param_order()
+        order += ["conv1", "bn1.weight", "bn1.bias"]
+        self.arena.finalize(self.device, order, heap=heap, seed=seed)
+        for m in [self.stem, self.stem_bn] + [m for b in self.blocks for m in b.modules()]:
+            m.bind()
+        self.fc_w = self.arena.w16("fc.weight")
+        self.fc_b = self.arena.w16("fc.bias")
+        self.saved = None
+
+    @property
+    def num_params(self) -> int:
+        return sum(s.numel for s in self.arena.layout)
+
+    def reducer_ready(self, end_elem: int) -> None:
+        if self.reducer is not None:
+            self.reducer.ready_upto(end_elem)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x_bf16_nhwc: torch.Tensor, train: bool = True) -> torch.Tensor:
+        c = self.stem.fwd(x_bf16_nhwc)
+        a = self.stem_bn.fwd(c)
+        p, idx = K.maxpool3x3s2_fwd(a)
+        h = p
+        for b in self.blocks:
+            h = b.fwd(h, train)
+        pooled = K.avgpool_fwd(h)
+        if self.gemm is not None:
+            logits = self.gemm.nt(pooled, self.fc_w, bias=self.fc_b)
+        else:
+            logits = torch.addmm(self.fc_b, pooled, self.fc_w.t())
+        if train:
+            self.saved = (x_bf16_nhwc, c, a, idx, h.shape, pooled)
+        return logits
+
+    # ------------------------------------------------------------------ backward
+    def backward(self, dlogits: torch.Tensor) -> None:
+        x, c, a, idx, hshape, pooled = self.saved
+        self.saved = None
+        if self.reducer is not None:
+            self.reducer.start()
+        a_ = self.arena
+        gfc = a_.grad("fc.weight")
+        if self.gemm is not None:
+            self.gemm.tn(dlogits, pooled, out=gfc)
+            dpooled = self.gemm.nn(dlogits, self.fc_w)
+        else:
+            torch.mm(dlogits.t(), pooled, out=gfc)
+            dpooled = torch.mm(dlogits, self.fc_w)
+        torch.sum(dlogits, dim=0, out=a_.grad("fc.bias"))
+        self.reducer_ready(a_.end_offset("fc.weight"))
+        dh = K.avgpool_bwd(dpooled, hshape)
+        for b in reversed(self.blocks):
+            dh = b.bwd(dh)
+        da = K.maxpool3x3s2_bwd(dh, idx, a.shape)
+        dc = self.stem_bn.bwd(da, c, a)
+        self.stem.bwd(dc, x, need_dx=False)
+        if self.reducer is not None:
+            self.reducer.finish()
+
+    def loss_and_grad(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        x = K.u8_normalize(images_u8, cpad=3)
+        logits = self.forward(x, train=True)
+        loss, dlogits = K.softmax_xent(logits, labels, V=self.num_classes)
+        self.backward(dlogits)
+        return loss
+
+    def sgd_step(self, lr: float, momentum: float = 0.9, weight_decay: float = 1e-4) -> None:
+        a = self.arena
+        K.sgd_momentum(a.p32, a.mom, a.g16, a.p16, lr, momentum, weight_decay, wd_count=a.wd_count)

@@ -1,0 +1,186 @@
+"""Tensor-level wrappers over the fused memory-bound kernels (csrc/batchnorm.cu,
+csrc/elementwise.cu).  All activations are NHWC bf16; a [N,H,W,C] tensor is passed as the
+[M, C] matrix it is in memory.  Each wrapper launches on torch's current stream, so the calls
+can be captured into CUDA graphs and ordered against cuDNN/cuBLAS work issued through torch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import lib as L
+
+_workspaces: dict = {}
+
+
+def workspace(nbytes: int, device=None, key: str = "default") -> torch.Tensor:
+    """Zero-initialised scratch arena, grown on demand, one per (device, key)."""
+    device = torch.device(device if device is not None else torch.cuda.current_device())
+    if device.type == "cuda" and device.index is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    k = (device, key)
+    ws = _workspaces.get(k)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[k] = ws
+    return ws
+
+
+def _chk_bf16(*ts):
+    for t in ts:
+        if t is not None:
+            assert t.dtype == torch.bfloat16 and t.is_contiguous() and t.is_cuda, \
+                f"need contiguous CUDA bf16, got {t.dtype} {tuple(t.shape)}"
+
+
+def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+           running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
+           res: Optional[torch.Tensor] = None, relu: bool = True, eps: float = 1e-5,
+           momentum: float = 0.1, out: Optional[torch.Tensor] = None,
+           save: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """y = relu(bn_train(x) + res) on x:[M,C] (or [N,H,W,C]) bf16. Returns (y, save_mean_rstd[2,C])."""
+    _chk_bf16(x, res)
+    Cn = x.shape[-1]
+    M = x.numel() // Cn
+    y = out if out is not None else torch.empty_like(x)
+    if save is None:
+        save = torch.empty(2, Cn, dtype=torch.float32, device=x.device)
+    lib = L.lib()
+    need = lib.kdl_bn_workspace_bytes(M, Cn)
+    if need == 0:
+        raise L.KernelError(f"bn_fwd: unsupported shape M={M} C={Cn}")
+    ws = workspace(need, x.device)
+    L.check(lib.kdl_bn_fwd(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
+                           beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps, momentum,
+                           int(relu), save.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()),
+            "kdl_bn_fwd")
+    L.count(2)
+    return y, save
+
+
+def bn_bwd(dy: torch.Tensor, x: torch.Tensor, y: Optional[torch.Tensor], gamma: torch.Tensor,
+           save: torch.Tensor, relu: bool, dgamma: torch.Tensor, dbeta: torch.Tensor,
+           dx: Optional[torch.Tensor] = None, dres: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Backward of bn_fwd.  dgamma/dbeta: bf16 [C] (views into the gradient arena).  If `dres`
+    is given it receives dz = dy * relu_mask (the gradient of the residual input); it may alias
+    dy."""
+    _chk_bf16(dy, x, y, dx, dres, dgamma, dbeta)
+    Cn = x.shape[-1]
+    M = x.numel() // Cn
+    if dx is None:
+        dx = torch.empty_like(x)
+    lib = L.lib()
+    need = lib.kdl_bn_workspace_bytes(M, Cn)
+    ws = workspace(need, x.device)
+    L.check(lib.kdl_bn_bwd(dy.data_ptr(), x.data_ptr(), L.ptr(y), dx.data_ptr(), L.ptr(dres), M, Cn,
+                           gamma.data_ptr(), save.data_ptr(), int(relu), dgamma.data_ptr(),
+                           dbeta.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()),
+            "kdl_bn_bwd")
+    L.count(2)
+    return dx
+
+
+_IMAGENET_MEAN = (C.c_float * 3)(0.485, 0.456, 0.406)
+_IMAGENET_STD = (C.c_float * 3)(0.229, 0.224, 0.225)
+
+
+def u8_normalize(img_u8: torch.Tensor, cpad: int = 3, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 NHWC [N,H,W,3] -> normalised bf16 NHWC [N,H,W,cpad]."""
+    assert img_u8.dtype == torch.uint8 and img_u8.shape[-1] == 3 and img_u8.is_contiguous()
+    npix = img_u8.numel() // 3
+    if out is None:
+        out = torch.empty(*img_u8.shape[:-1], cpad, dtype=torch.bfloat16, device=img_u8.device)
+    L.check(L.lib().kdl_u8_normalize(img_u8.data_ptr(), out.data_ptr(), npix, cpad, _IMAGENET_MEAN,
+                                     _IMAGENET_STD, L.stream_ptr()), "kdl_u8_normalize")
+    L.count(1)
+    return out
+
+
+def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, V: Optional[int] = None,
+                 grad_scale: Optional[float] = None, dlogits: Optional[torch.Tensor] = None,
+                 loss: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Mean softmax cross-entropy over rows of logits[B, ldv] (first V columns valid) and its
+    gradient (bf16, already scaled by grad_scale, default 1/B)."""
+    assert logits.dim() == 2 and logits.is_contiguous() and labels.dtype == torch.int64
+    B, ldv = logits.shape
+    V = V if V is not None else ldv
+    if grad_scale is None:
+        grad_scale = 1.0 / B
+    if dlogits is None:
+        dlogits = torch.empty(B, ldv, dtype=torch.bfloat16, device=logits.device)
+    if loss is None:
+        loss = torch.empty(1, dtype=torch.float32, device=logits.device)
+    lib = L.lib()
+    need = lib.kdl_softmax_xent_workspace_bytes(B)
+    ws = workspace(need, logits.device, key="xent")
+    L.check(lib.kdl_softmax_xent(logits.data_ptr(), int(logits.dtype == torch.float32),
+                                 labels.data_ptr(), dlogits.data_ptr(), loss.data_ptr(), B, V, ldv,
+                                 grad_scale, ws.data_ptr(), ws.numel(), L.stream_ptr()),
+            "kdl_softmax_xent")
+    L.count(1)
+    return loss, dlogits
+
+
+def sgd_momentum(p32: torch.Tensor, mom: torch.Tensor, g16: torch.Tensor, p16: torch.Tensor,
+                 lr: float, momentum: float = 0.9, weight_decay: float = 0.0,
+                 wd_count: Optional[int] = None, grad_scale: float = 1.0) -> None:
+    n = p32.numel()
+    assert mom.numel() == n and g16.numel() == n and p16.numel() == n
+    assert p32.dtype == torch.float32 and g16.dtype == torch.bfloat16 and p16.dtype == torch.bfloat16
+    L.check(L.lib().kdl_sgd_momentum(p32.data_ptr(), mom.data_ptr(), g16.data_ptr(), p16.data_ptr(),
+                                     n, n if wd_count is None else wd_count, lr, momentum,
+                                     weight_decay, grad_scale, L.stream_ptr()), "kdl_sgd_momentum")
+    L.count(1)
+
+
+def add_(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _chk_bf16(a, b, out)
+    out = a if out is None else out
+    L.check(L.lib().kdl_add_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), a.numel(),
+                                 L.stream_ptr()), "kdl_add_bf16")
+    L.count(1)
+    return out
+
+
+def maxpool3x3s2_fwd(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    _chk_bf16(x)
+    N, H, W, Cn = x.shape
+    OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    y = torch.empty(N, OH, OW, Cn, dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty(N, OH, OW, Cn, dtype=torch.uint8, device=x.device)
+    L.check(L.lib().kdl_maxpool3x3s2_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, Cn,
+                                         L.stream_ptr()), "kdl_maxpool3x3s2_fwd")
+    L.count(1)
+    return y, idx
+
+
+def maxpool3x3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, in_shape) -> torch.Tensor:
+    _chk_bf16(dy)
+    N, H, W, Cn = in_shape
+    dx = torch.empty(N, H, W, Cn, dtype=torch.bfloat16, device=dy.device)
+    L.check(L.lib().kdl_maxpool3x3s2_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, Cn,
+                                         L.stream_ptr()), "kdl_maxpool3x3s2_bwd")
+    L.count(1)
+    return dx
+
+
+def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
+    _chk_bf16(x)
+    N, H, W, Cn = x.shape
+    y = torch.empty(N, Cn, dtype=torch.bfloat16, device=x.device)
+    L.check(L.lib().kdl_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, H * W, Cn, L.stream_ptr()),
+            "kdl_avgpool_fwd")
+    L.count(1)
+    return y
+
+
+def avgpool_bwd(dy: torch.Tensor, in_shape) -> torch.Tensor:
+    _chk_bf16(dy)
+    N, H, W, Cn = in_shape
+    dx = torch.empty(N, H, W, Cn, dtype=torch.bfloat16, device=dy.device)
+    L.check(L.lib().kdl_avgpool_bwd(dy.data_ptr(), dx.data_ptr(), N, H * W, Cn, L.stream_ptr()),
+            "kdl_avgpool_bwd")
+    L.count(1)
+    return dx

@@ -1,0 +1,107 @@
+"""Fused collectives over the symmetric heap (kernel N1, csrc/allreduce.cu).
+
+`FusedAllReduce` is what the DDP reducer calls per gradient bucket.  It never touches NCCL:
+the kernel does barrier -> reduce-scatter -> scale/cast -> all-gather -> barrier over peer
+pointers (or NVLS multicast when the heap has a multicast mapping).  `NcclAllReduce` is the
+stock path kept for A/B timing only (the baseline worker of BASELINE.md §3).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+from ..ops import lib as L
+from .symm import FLAG_CHANNELS, SymmetricHeap
+
+_DT = {torch.bfloat16: 0, torch.float32: 1}
+
+
+class FusedAllReduce:
+    def __init__(self, heap: SymmetricHeap, timeout_s: float = 30.0, max_blocks: int = 0,
+                 use_nvls: Optional[bool] = None):
+        self.heap = heap
+        self.lib = L.lib()
+        self.timeout_ns = int(timeout_s * 1e9)
+        self.max_blocks = max_blocks
+        if use_nvls is None:
+            use_nvls = os.environ.get("KUBEDL_NVLS", "1") != "0"
+        self.use_nvls = bool(use_nvls and heap.mc_ptr)
+        self._flag_tab = heap.ptr_table(heap.flags_off)
+        self._status_ptr = heap.peer_ptrs[heap.rank] + heap.status_off
+        self._tabs: dict = {}
+
+    def _tab(self, off: int):
+        t = self._tabs.get(off)
+        if t is None:
+            t = self.heap.ptr_table(off)
+            self._tabs[off] = t
+        return t
+
+    def __call__(self, in_off: int, n: int, in_dtype: torch.dtype = torch.bfloat16,
+                 out_off: Optional[int] = None, out_dtype: Optional[torch.dtype] = None,
+                 scale: Optional[float] = None, channel: int = 0) -> None:
+        """All-reduce n elements at heap byte offset `in_off` (in place unless out_off given);
+        result = sum * scale (default 1/world)."""
+        h = self.heap
+        out_off = in_off if out_off is None else out_off
+        out_dtype = in_dtype if out_dtype is None else out_dtype
+        scale = (1.0 / h.world) if scale is None else scale
+        nvls = self.use_nvls and in_dtype == out_dtype
+        rc = self.lib.kdl_allreduce_fused(
+            self._tab(in_off), self._tab(out_off), self._flag_tab,
+            h.mc(in_off) if nvls else None, h.mc(out_off) if nvls else None,
+            h.world, h.rank, n, _DT[in_dtype], _DT[out_dtype], scale,
+            h.epoch_state.data_ptr(), FLAG_CHANNELS, channel, self.max_blocks, 0,
+            self._status_ptr, self.timeout_ns, L.stream_ptr())
+        L.check(rc, "kdl_allreduce_fused")
+        if h.world > 1 or in_off != out_off or scale != 1.0:
+            L.count(1)
+
+
+class NcclAllReduce:
+    """Baseline: torch.distributed all_reduce (NCCL) followed by the separate scale kernel."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def __call__(self, t: torch.Tensor, scale: Optional[float] = None) -> None:
+        import torch.distributed as dist
+        if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(t, group=self.group)
+            t.mul_(scale if scale is not None else 1.0 / dist.get_world_size(self.group))
+
+
+def emulated_allreduce(bufs, out_dtype=None, scale=None, max_blocks: int = 0):
+    """Single-GPU protocol test: run all `len(bufs)` ranks of the P2P kernel inside one
+    cooperative launch.  bufs: same-shape tensors on one device, reduced IN PLACE (or into new
+    tensors when out_dtype differs).  Returns the list of per-rank outputs."""
+    lib = L.lib()
+    W = len(bufs)
+    dev = bufs[0].device
+    n = bufs[0].numel()
+    in_dtype = bufs[0].dtype
+    out_dtype = out_dtype or in_dtype
+    outs = bufs if out_dtype == in_dtype else [torch.empty(n, dtype=out_dtype, device=dev) for _ in bufs]
+    fb = lib.kdl_allreduce_flags_bytes(FLAG_CHANNELS)
+    flags = [torch.zeros(fb // 4, dtype=torch.int32, device=dev) for _ in range(W)]
+    epochs = torch.zeros(W * fb // 4, dtype=torch.int32, device=dev)
+    status = torch.zeros(64, dtype=torch.int32, device=dev)
+    it, ot, ft = (C.c_void_p * 8)(), (C.c_void_p * 8)(), (C.c_void_p * 8)()
+    for r in range(W):
+        it[r], ot[r], ft[r] = bufs[r].data_ptr(), outs[r].data_ptr(), flags[r].data_ptr()
+    state = dict(flags=flags, epochs=epochs, status=status)
+
+    def run():
+        rc = lib.kdl_allreduce_fused(it, ot, ft, None, None, W, 0, n, _DT[in_dtype], _DT[out_dtype],
+                                     (1.0 / W) if scale is None else scale, epochs.data_ptr(),
+                                     FLAG_CHANNELS, 0, max_blocks, 1, status.data_ptr(),
+                                     int(10e9), L.stream_ptr())
+        L.check(rc, "kdl_allreduce_fused(emulate)")
+        L.count(1)
+        return outs
+
+    run.state = state
+    return run

@@ -120,10 +120,16 @@ def timed(fn_step, steps, world):
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    prof = os.environ.get("KUBEDL_NCU") == "1"
+    if prof:
+        torch.cuda.profiler.start()
     e0.record()
     for i in range(steps):
         fn_step(i)
     e1.record()
+    if prof:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     if world > 1:

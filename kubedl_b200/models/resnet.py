@@ -106,7 +106,7 @@ class Bottleneck:
         self.c2 = Conv(net, f"{name}.conv2", width, width, 3, stride, 1)
         self.b2 = BN(net, f"{name}.bn2", width, relu=True)
         self.c3 = Conv(net, f"{name}.conv3", width, cout, 1, 1, 0)
-        self.b3 = BN(net, f"{name}.bn3", cout, relu=True, zero_init=True)
+        self.b3 = BN(net, f"{name}.bn3", cout, relu=True, zero_init=net.zero_init_residual)
         self.cd = self.bd = None
         if downsample:
             self.cd = Conv(net, f"{name}.downsample.0", cin, cout, 1, stride, 0)
@@ -165,8 +165,10 @@ class Bottleneck:
 class ResNet50:
     LAYERS = [(64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)]
 
-    def __init__(self, device="cuda", num_classes: int = 1000, heap=None, gemm=None, seed: int = 0):
+    def __init__(self, device="cuda", num_classes: int = 1000, heap=None, gemm=None, seed: int = 0,
+                 zero_init_residual: bool = False):
         self.device = torch.device(device)
+        self.zero_init_residual = zero_init_residual
         self.num_classes = num_classes
         self.arena = ParamArena()
         self.gemm = gemm

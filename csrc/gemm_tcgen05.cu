@@ -1,0 +1,652 @@
+// N6: bf16 GEMM on the 5th-generation tensor cores.
+//
+//   C[M,N] = op(A) * op(B)  (+ bias[N]) (+ addend[M,N]) (ReLU?)      bf16 in, fp32 accumulate
+//
+// Persistent, warp-specialised kernel, one CTA per SM:
+//   warp 0   TMA producer   cp.async.bulk.tensor (128B-swizzled tiles) -> smem ring, mbarrier tx
+//   warp 1   MMA issuer     one thread issues tcgen05.mma (M=128, N=BN, K=16) from smem
+//                           descriptors into a TMEM accumulator; tcgen05.commit frees the stage
+//   warp 2   TMEM allocator tcgen05.alloc / dealloc (2 accumulator stages of BN columns)
+//   warp 4-7 epilogue       tcgen05.ld TMEM -> registers -> bias/addend/ReLU -> bf16 -> global
+// so the epilogue of tile i overlaps the loads and MMAs of tile i+1.  Operands may be K-major
+// or MN-major (the transposes needed by dgrad / wgrad are done by the UMMA descriptors, not by
+// copies): nt = fwd (x W^T), nn = dgrad (dy W), tn = wgrad (dy^T x).  wgrad has a tiny output
+// and a huge K, so it is split over K across CTAs; partial tiles go to an fp32 scratch and a
+// second kernel reduces them in a fixed order (deterministic) and casts to bf16.
+//
+// Replaces the cuBLAS/cuDNN GEMMs the stock worker would call for ResNet-50's 1x1 convolutions
+// and FC layer and for the DIN MLP; the reference operator itself has no math at all
+// (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15 just names a worker image).
+#include "common.cuh"
+#include "../include/kubedl_b200.h"
+#include <cuda.h>
+#include <string.h>
+
+namespace kdl {
+
+constexpr int BM = 128;       // UMMA M (cta_group::1)
+constexpr int BK = 64;        // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 256;
+constexpr int kEpiWarp0 = 4;
+
+struct GemmParams {
+  bf16* C;              // bf16 output (mode 0)
+  float* partial;       // fp32 split-K partials [splits][M][N] (mode 1)
+  const bf16* bias;     // [N] or null
+  const bf16* addend;   // [M, ldc] or null
+  int M, N, K;
+  int ldc;
+  int relu;
+  int splits;
+  int kb_per_split;
+  int num_m, num_n;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1,
+                                             int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (sm_100 "version 1", 128-byte swizzle).
+//   K-major : rows of 128 B (64 bf16 along K); 8-row atoms 1024 B apart (SBO); LBO unused.
+//   MN-major: rows of 128 B (64 bf16 along M/N) for consecutive K; atoms of 8 K-rows 1024 B
+//             apart (SBO), 64-wide M/N atoms BK*128 B apart (LBO).
+template <int MN_MAJOR>
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  const uint32_t lbo = MN_MAJOR ? (BK * 128) : 0;
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((1024 >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+// byte advance of the start address for the k-th UMMA_K slice inside a BK block
+template <int MN_MAJOR>
+__device__ __forceinline__ uint32_t k_advance_bytes(int k) {
+  return MN_MAJOR ? (uint32_t)k * UMMA_K * 128u : (uint32_t)k * UMMA_K * 2u;
+}
+
+template <int A_MN, int B_MN, int BN>
+__host__ __device__ constexpr uint32_t make_idesc() {
+  return (1u << 4)            // D format f32
+         | (1u << 7)          // A bf16
+         | (1u << 10)         // B bf16
+         | ((uint32_t)A_MN << 15) | ((uint32_t)B_MN << 16) | ((uint32_t)(BN >> 3) << 17) |
+         ((uint32_t)(BM >> 4) << 24);
+}
+
+template <int BN, int STAGES>
+struct SmemLayout {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagingOffset = STAGES * kStageBytes;   // 1024-aligned
+  static constexpr int kStagingPerWarp = 2 * 4096;             // two 32-row x 128-B buffers
+  static constexpr int kBarOffset = kStagingOffset + 4 * kStagingPerWarp;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+};
+
+template <int A_MN, int B_MN, int BN, int STAGES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
+                    const __grid_constant__ CUtensorMap tma_b,
+                    const __grid_constant__ CUtensorMap tma_c, const GemmParams p) {
+  using SL = SmemLayout<BN, STAGES>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar_base = smem_base + SL::kBarOffset;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SL::kBarOffset + (2 * STAGES + 4) * 8);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;  // power of two for BN in {32,64,128,256}
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_c) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 4);  // one arrive per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_ptr_smem)),
+                 "r"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int total_tiles = p.num_m * p.num_n * p.splits;
+  const int kb_total = (p.K + BK - 1) / BK;
+
+  if (warp == 0) {
+    // ============================== TMA producer ==============================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int n_idx = t % p.num_n;
+        const int m_idx = (t / p.num_n) % p.num_m;
+        const int split = t / (p.num_n * p.num_m);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * SL::kStageBytes;
+          const uint32_t sb = sa + SL::kABytes;
+          mbar_expect_tx(full_bar(stage), SL::kStageBytes);
+          if (A_MN) {
+#pragma unroll
+            for (int a = 0; a < BM / 64; ++a)
+              tma_load_2d(sa + a * (BK * 128), &tma_a, full_bar(stage), m_idx * BM + a * 64, kb * BK);
+          } else {
+            tma_load_2d(sa, &tma_a, full_bar(stage), kb * BK, m_idx * BM);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int a = 0; a < BN / 64; ++a)
+              tma_load_2d(sb + a * (BK * 128), &tma_b, full_bar(stage), n_idx * BN + a * 64, kb * BK);
+          } else {
+            tma_load_2d(sb, &tma_b, full_bar(stage), kb * BK, n_idx * BN);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================== MMA issuer ==============================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc<A_MN, B_MN, BN>();
+      int stage = 0;
+      uint32_t phase = 0;
+      int iter = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
+        const int split = t / (p.num_n * p.num_m);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        const int as = iter & 1;
+        const uint32_t aphase = (iter >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + stage * SL::kStageBytes;
+          const uint32_t sb = sa + SL::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = make_desc<A_MN>(sa + k_advance_bytes<A_MN>(k));
+            const uint64_t bd = make_desc<B_MN>(sb + k_advance_bytes<B_MN>(k));
+            umma_bf16(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));  // frees the smem stage once these MMAs retire
+          if (kb == kb1 - 1) umma_commit(tfull_bar(as));
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // ============================== epilogue ==============================
+    // TMEM -> registers -> (bias, addend, ReLU) -> bf16 -> 128B-swizzled smem staging -> TMA
+    // store.  Each warp owns 32 accumulator rows and two 4 KB staging buffers, so the bulk
+    // store of chunk i overlaps the TMEM read + math of chunk i+1; TMA clips M/N tails.
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const uint32_t stg_base = smem_base + SL::kStagingOffset + q * SL::kStagingPerWarp;
+    uint8_t* stg_ptr = smem + SL::kStagingOffset + q * SL::kStagingPerWarp;
+    int iter = 0;
+    int buf = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
+      const int n_idx = t % p.num_n;
+      const int m_idx = (t / p.num_n) % p.num_m;
+      const int split = t / (p.num_n * p.num_m);
+      const int as = iter & 1;
+      const uint32_t aphase = (iter >> 1) & 1;
+      mbar_wait(tfull_bar(as), aphase);
+      tcgen05_fence_after();
+      const int row0 = m_idx * BM + q * 32;
+      const int row = row0 + lane;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+      if (p.partial != nullptr) {
+        // split-K: fp32 partial tile, 32 columns (128 B) per staging row
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld32(taddr + c0, r);
+          tmem_ld_wait();
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
+                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d(&tma_c, stg_base + buf * 4096, n_idx * BN + c0, row0, split);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        }
+      } else {
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 64) {
+          uint32_t r[64];
+          tmem_ld32(taddr + c0, r);
+          tmem_ld32(taddr + c0 + 32, r + 32);
+          tmem_ld_wait();
+          const int col = n_idx * BN + c0;
+          float f[64];
+#pragma unroll
+          for (int j = 0; j < 64; ++j) f[j] = __uint_as_float(r[j]);
+          if (p.bias) {
+            if (col + 64 <= p.N) {
+#pragma unroll
+              for (int j = 0; j < 64; j += 8) {
+                float b[8];
+                unpack8(*reinterpret_cast<const uint4*>(p.bias + col + j), b);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[j + i] += b[i];
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 64; ++j)
+                if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
+            }
+          }
+          if (p.addend && row < p.M) {
+            const bf16* ad = p.addend + (size_t)row * p.ldc + col;
+            if (col + 64 <= p.N) {
+#pragma unroll
+              for (int j = 0; j < 64; j += 8) {
+                float b[8];
+                unpack8(ld_plain(ad + j), b);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[j + i] += b[i];
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 64; ++j)
+                if (col + j < p.N) f[j] += __bfloat162float(ad[j]);
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          if (lane == 0) tma_store_wait_read<1>();  // the buffer written two chunks ago is free
+          __syncwarp();
+          uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tma_c, stg_base + buf * 4096, col, row0);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(as));
+    }
+    if (lane == 0) tma_store_wait_read<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(kTmemCols)
+                 : "memory");
+  }
+}
+
+// Deterministic split-K reduction: out = bf16(sum_s partial[s]) (fixed order).
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partial,
+                                                            bf16* __restrict__ out, int64_t MN,
+                                                            int N, int ldc, int splits) {
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < MN; i += T) {
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += __ldcg(partial + (size_t)s * MN + i);
+    const int64_t r = i / N, c = i % N;
+    out[r * ldc + c] = __float2bfloat16(acc);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+    else
+      cudaGetLastError();
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor map: inner (contiguous) extent d0, outer extent d1, row pitch ld elements.
+static int make_map(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t ld,
+                    uint32_t box0, uint32_t box1) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    kdl_set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return KDL_ERR_UNSUPPORTED;
+  }
+  cuuint64_t dims[2] = {d0, d1};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    kdl_set_error("cuTensorMapEncodeTiled failed (%d): base=%p dims=%llu,%llu ld=%llu box=%u,%u",
+                  (int)r, base, (unsigned long long)d0, (unsigned long long)d1,
+                  (unsigned long long)ld, box0, box1);
+    return KDL_ERR_CUDA;
+  }
+  return KDL_OK;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+// Output maps: bf16 [M][ldc] with box {64, 32}, or fp32 [splits][M][N] with box {32, 32, 1}.
+static int make_c_map(CUtensorMap* map, void* base, int fp32_partial, uint64_t M, uint64_t N,
+                      uint64_t ldc, uint64_t splits) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    kdl_set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return KDL_ERR_UNSUPPORTED;
+  }
+  CUresult r;
+  if (fp32_partial) {
+    cuuint64_t dims[3] = {N, M, splits};
+    cuuint64_t strides[2] = {N * 4, M * N * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    cuuint64_t dims[2] = {N, M};
+    cuuint64_t strides[1] = {ldc * 2};
+    cuuint32_t box[2] = {64, 32};
+    cuuint32_t estr[2] = {1, 1};
+    r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (r != CUDA_SUCCESS) {
+    kdl_set_error("cuTensorMapEncodeTiled(C) failed (%d): M=%llu N=%llu ldc=%llu", (int)r,
+                  (unsigned long long)M, (unsigned long long)N, (unsigned long long)ldc);
+    return KDL_ERR_CUDA;
+  }
+  return KDL_OK;
+}
+
+template <int A_MN, int B_MN, int BN, int STAGES>
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+                  const GemmParams& p, cudaStream_t stream) {
+  using SL = SmemLayout<BN, STAGES>;
+  auto kern = gemm_tcgen05_kernel<A_MN, B_MN, BN, STAGES>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    KDL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::kTotal + 1024));
+    attr_done = true;
+  }
+  int tiles = p.num_m * p.num_n * p.splits;
+  int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, kGemmThreads, SL::kTotal + 1024, stream>>>(ma, mb, mc, p);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+template <int BN, int STAGES>
+static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
+                          const CUtensorMap& mc, const GemmParams& p, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch<0, 0, BN, STAGES>(ma, mb, mc, p, s);
+  if (!a_mn && b_mn) return launch<0, 1, BN, STAGES>(ma, mb, mc, p, s);
+  if (a_mn && b_mn) return launch<1, 1, BN, STAGES>(ma, mb, mc, p, s);
+  return launch<1, 0, BN, STAGES>(ma, mb, mc, p, s);
+}
+
+}  // namespace kdl
+
+using namespace kdl;
+
+static int pick_bn(int N) { return N <= 64 ? 64 : 128; }
+
+static int pick_splits(int M, int N, int K, int requested) {
+  int bn = pick_bn(N);
+  int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+  int kb_total = (K + BK - 1) / BK;
+  int s = requested;
+  if (s <= 0) {
+    // auto: only split when the output grid cannot fill the machine and K is deep
+    s = 1;
+    if (tiles < 148 && kb_total >= 16) {
+      s = (148 * 2) / tiles;
+      if (s > kb_total / 4) s = kb_total / 4;
+      if (s < 1) s = 1;
+      if (s > 128) s = 128;
+    }
+  }
+  if (s > kb_total) s = kb_total;
+  int per = (kb_total + s - 1) / s;
+  s = (kb_total + per - 1) / per;
+  return s;
+}
+
+extern "C" int kdl_gemm_splits(int M, int N, int K, int requested) {
+  return pick_splits(M, N, K, requested);
+}
+
+extern "C" size_t kdl_gemm_scratch_bytes(int M, int N, int K, int split_k) {
+  int s = pick_splits(M, N, K, split_k);
+  return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
+}
+
+extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                             int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
+                             const void* bias, const void* addend, int relu, int split_k,
+                             void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) {
+    kdl_set_error("gemm: bad shape %dx%dx%d", M, N, K);
+    return KDL_ERR_ARG;
+  }
+  if ((lda & 7) || (ldb & 7) || (ldc & 7) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) ||
+      ((uintptr_t)C & 15)) {
+    kdl_set_error("gemm: operands must be 16-byte aligned with leading dims %% 8 == 0 (lda=%d ldb=%d ldc=%d)",
+                  lda, ldb, ldc);
+    return KDL_ERR_ARG;
+  }
+  const int bn = pick_bn(N);
+  const int splits = pick_splits(M, N, K, split_k);
+  GemmParams p = {};
+  p.C = (bf16*)C;
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+  p.bias = (const bf16*)bias;
+  p.addend = (const bf16*)addend;
+  p.relu = relu;
+  p.splits = splits;
+  const int kb_total = (K + BK - 1) / BK;
+  p.kb_per_split = (kb_total + splits - 1) / splits;
+  p.num_m = (M + BM - 1) / BM;
+  p.num_n = (N + bn - 1) / bn;
+  if (splits > 1) {
+    if (bias || addend || relu) {
+      kdl_set_error("gemm: split-K does not support fused bias/addend/relu");
+      return KDL_ERR_UNSUPPORTED;
+    }
+    if (N & 3) {
+      kdl_set_error("gemm: split-K needs N %% 4 == 0");
+      return KDL_ERR_UNSUPPORTED;
+    }
+    size_t need = (size_t)splits * M * N * sizeof(float);
+    if (scratch == nullptr || scratch_bytes < need) {
+      kdl_set_error("gemm: split-K scratch too small (%zu < %zu)", scratch_bytes, need);
+      return KDL_ERR_WORKSPACE;
+    }
+    p.partial = (float*)scratch;
+  }
+  CUtensorMap ma, mb;
+  int rc;
+  // K-major: global [rows=MN extent][K] ; MN-major: global [K][MN extent]
+  if (a_mn_major) rc = make_map(&ma, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
+  else rc = make_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
+  if (rc) return rc;
+  if (b_mn_major) rc = make_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
+  else rc = make_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)bn);
+  if (rc) return rc;
+  CUtensorMap mc;
+  if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)N, (uint64_t)N, (uint64_t)splits);
+  else rc = make_c_map(&mc, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);
+  if (rc) return rc;
+  if (bn == 64) rc = dispatch_major<64, 8>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
+  else rc = dispatch_major<128, 5>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
+  if (rc) return rc;
+  if (splits > 1) {
+    int64_t MN = (int64_t)M * N;
+    int64_t g = (MN + 255) / 256;
+    if (g > 148 * 8) g = 148 * 8;
+    splitk_reduce_kernel<<<(int)g, 256, 0, stream>>>(p.partial, (bf16*)C, MN, N, ldc, splits);
+    KDL_CHECK_LAUNCH();
+  }
+  return KDL_OK;
+}

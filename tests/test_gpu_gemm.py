@@ -1,0 +1,70 @@
+"""tcgen05 GEMM (kernel N6) vs torch.matmul in fp32 (GPU only)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel_err(out, ref):
+    return float((out.float() - ref).abs().max() / (ref.abs().max() + 1e-6))
+
+
+@pytest.mark.parametrize("M,N,K", [
+    (128, 128, 64), (256, 64, 64), (1000, 256, 64), (4096, 512, 2048), (16, 1000, 2048),
+    (3136, 64, 256), (777, 192, 328), (12544, 2048, 512),
+])
+def test_gemm_nt(cuda, M, N, K):
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device=cuda).bfloat16()
+    b = torch.randn(N, K, device=cuda).bfloat16()
+    out = g.nt(a, b)
+    ref = a.float() @ b.float().t()
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+
+
+def test_gemm_nt_epilogue(cuda):
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(1)
+    M, N, K = 512, 1000, 256
+    a = torch.randn(M, K, device=cuda).bfloat16()
+    b = torch.randn(N, K, device=cuda).bfloat16()
+    bias = torch.randn(N, device=cuda).bfloat16()
+    add = torch.randn(M, N, device=cuda).bfloat16()
+    out = g.nt(a, b, bias=bias, addend=add, relu=True)
+    ref = torch.relu(a.float() @ b.float().t() + bias.float() + add.float())
+    assert _rel_err(out, ref) < 1e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 128, 64), (1024, 64, 256), (3000, 256, 1024), (640, 2048, 512)])
+def test_gemm_nn(cuda, M, N, K):
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(2)
+    a = torch.randn(M, K, device=cuda).bfloat16()
+    b = torch.randn(K, N, device=cuda).bfloat16()
+    add = torch.randn(M, N, device=cuda).bfloat16()
+    out = g.nn(a, b)
+    ref = a.float() @ b.float()
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+    out2 = g.nn(a, b, addend=add)
+    assert _rel_err(out2, ref + add.float()) < 1e-2
+
+
+@pytest.mark.parametrize("K,M,N,split", [
+    (4096, 64, 64, 0), (50000, 256, 64, 0), (1024, 128, 128, 1), (8192, 2048, 512, 0),
+    (3000, 1000, 2048, 0), (100352, 64, 256, 0),
+])
+def test_gemm_tn_splitk(cuda, K, M, N, split):
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(3)
+    a = torch.randn(K, M, device=cuda).bfloat16()
+    b = torch.randn(K, N, device=cuda).bfloat16()
+    out = g.tn(a, b, split_k=split)
+    ref = a.float().t() @ b.float()
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+    out2 = g.tn(a, b, split_k=split)
+    assert torch.equal(out, out2)  # deterministic split-K

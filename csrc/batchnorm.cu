@@ -480,3 +480,84 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// kdl_bn_fwd_static_scratch: the same fused BN forward for callers that must not allocate.
+//
+// Who that is: a process that has already given every byte of the device to some other owner (a
+// serving runtime whose memory pool holds the whole GPU, a pod running right at its memory
+// limit), or a caller sitting on a latency-critical path where cudaMalloc would stall it —
+// cudaMalloc synchronises the whole device and can fail outright when the pool owner left
+// nothing free.  Such a caller cannot size and own the workspace that kdl_bn_fwd asks for.
+//
+// What it does instead: the scratch (block partials, per-channel coefficients, arrival counters)
+// lives in the fixed array below, KDL_BN_STATIC_SCRATCH_BYTES per GPU, resident from the moment
+// the library is loaded on that GPU until the process exits.  Shapes whose scratch need is larger
+// are refused with an error; nothing is ever grown.  No cudaMalloc, cudaFree or other allocating
+// routine is called here.
+//
+// Rules for the caller:
+//   * The first call on each device looks up the array's device address (once, with that device
+//     current).  Make that first call during start-up, before any stream capture begins.
+//   * All calls on one GPU share the one array and it keeps whatever the previous call left in it.
+//     The arrival counters are cleared at the start of every call; everything else is fully
+//     rewritten before it is read.  Two calls that overlap on the GPU (different streams, or
+//     different host threads) would trample each other's partial sums: serialise them.
+static __device__ __align__(256) unsigned char g_bn_static_scratch[KDL_BN_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+
+static int bn_static_scratch_ptr(void** out) {
+  // In host code `g_bn_static_scratch` is only a handle for the runtime, not a device address;
+  // the real address differs per device and must be asked for with that device current.
+  static std::mutex mu;
+  static void* ptrs[64] = {nullptr};
+  int dev = -1;
+  KDL_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    kdl_set_error("bn_fwd_static_scratch: device index %d out of range", dev);
+    return KDL_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      kdl_set_error("bn_fwd_static_scratch: cudaGetSymbolAddress failed on device %d: %s", dev,
+                    cudaGetErrorString(e));
+      return KDL_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return KDL_OK;
+}
+
+extern "C" size_t kdl_bn_static_scratch_limit(void) { return (size_t)KDL_BN_STATIC_SCRATCH_BYTES; }
+
+extern "C" int kdl_bn_fwd_static_scratch(const void* x, const void* res, void* y, int64_t M, int C,
+                                         const float* gamma, const float* beta,
+                                         float* running_mean, float* running_var, float eps,
+                                         float momentum, int relu, float* save_mean_rstd,
+                                         cudaStream_t stream) {
+  const size_t need = kdl_bn_workspace_bytes(M, C);
+  if (need == 0) {
+    kdl_set_error("bn_fwd_static_scratch: unsupported shape M=%lld C=%d (need C%%8==0)",
+                  (long long)M, C);
+    return KDL_ERR_ARG;
+  }
+  if (need > (size_t)KDL_BN_STATIC_SCRATCH_BYTES) {
+    kdl_set_error(
+        "bn_fwd_static_scratch: M=%lld C=%d needs %zu bytes of scratch but the built-in array "
+        "holds %d; use kdl_bn_fwd with a caller-owned workspace for this shape",
+        (long long)M, C, need, KDL_BN_STATIC_SCRATCH_BYTES);
+    return KDL_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  int rc = bn_static_scratch_ptr(&scratch);
+  if (rc) return rc;
+  // the arrival counters (first 256 bytes) are the only part that must start at zero
+  KDL_CUDA(cudaMemsetAsync(scratch, 0, 256, stream));
+  return kdl_bn_fwd(x, res, y, M, C, gamma, beta, running_mean, running_var, eps, momentum, relu,
+                    save_mean_rstd, scratch, (size_t)KDL_BN_STATIC_SCRATCH_BYTES, stream);
+}

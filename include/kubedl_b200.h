@@ -48,6 +48,21 @@ int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dre
                void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
 
+/* kdl_bn_fwd for callers that cannot allocate device memory (the GPU's memory is wholly owned by
+ * someone else's pool, or cudaMalloc's device-wide synchronisation is not acceptable where the
+ * call is made).  This entry point has no counterpart in the reference.  Same arguments as
+ * kdl_bn_fwd minus the workspace: the scratch is a fixed KDL_BN_STATIC_SCRATCH_BYTES array built
+ * into the library (held on every GPU that loads it, until exit).  Shapes with
+ * kdl_bn_workspace_bytes(M, C) above that limit are rejected.  The first call on a device
+ * resolves the array's address: make it before any stream capture.  Calls on one GPU share the
+ * array, so calls that overlap on the GPU race; run them one after another. */
+#define KDL_BN_STATIC_SCRATCH_BYTES (512 * 1024)
+size_t kdl_bn_static_scratch_limit(void);
+int kdl_bn_fwd_static_scratch(const void* x, const void* res, void* y, int64_t M, int C,
+                              const float* gamma, const float* beta, float* running_mean,
+                              float* running_var, float eps, float momentum, int relu,
+                              float* save_mean_rstd, cudaStream_t stream);
+
 /* ---- N8: other memory-bound fused ops of the DDP worker --------------------------------- */
 int kdl_u8_normalize(const void* in_u8, void* out_bf16, int64_t npix, int cpad,
                      const float* mean3_host, const float* std3_host, cudaStream_t stream);

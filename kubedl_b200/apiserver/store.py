@@ -1,0 +1,302 @@
+"""In-process API server: the cluster state the control plane reconciles against.
+
+The reference talks to a real kube-apiserver through controller-runtime (main.go:70-75) and its
+tests use controller-runtime's fake client (api/pytorch/v1/v1_suite_test.go:31-41).  This store
+is the B200-box equivalent of both: typed-by-kind object storage with uid / resourceVersion /
+creationTimestamp, optimistic concurrency, the status subresource, label-selector LIST, WATCH
+streams (ADDED / MODIFIED / DELETED), ownerReference garbage collection, CRD discovery and
+Events.  Objects are Kubernetes wire-format dicts.
+"""
+from __future__ import annotations
+
+import collections
+import copy
+import threading
+import uuid
+from typing import Callable, Deque, Dict, List, Optional, Tuple
+
+from ..api import common as c
+from ..api.kinds import SCHEME
+
+ADDED, MODIFIED, DELETED = "ADDED", "MODIFIED", "DELETED"
+
+
+class ApiError(Exception):
+    reason = "InternalError"
+    code = 500
+
+
+class NotFound(ApiError):
+    reason, code = "NotFound", 404
+
+
+class AlreadyExists(ApiError):
+    reason, code = "AlreadyExists", 409
+
+
+class Conflict(ApiError):
+    reason, code = "Conflict", 409
+
+
+class Invalid(ApiError):
+    reason, code = "Invalid", 422
+
+
+class Timeout(ApiError):
+    reason, code = "Timeout", 504
+
+
+def is_not_found(e: Exception) -> bool: return isinstance(e, NotFound)
+def is_already_exists(e: Exception) -> bool: return isinstance(e, AlreadyExists)
+def is_conflict(e: Exception) -> bool: return isinstance(e, Conflict)
+def is_timeout(e: Exception) -> bool: return isinstance(e, Timeout)
+
+
+WatchHandler = Callable[[str, dict, Optional[dict]], None]  # (event_type, obj, old_obj)
+
+
+class APIServer:
+    def __init__(self, scheme=SCHEME, install_all_crds: bool = True):
+        self.scheme = scheme
+        self._lock = threading.RLock()
+        self._objs: Dict[str, Dict[Tuple[str, str], dict]] = collections.defaultdict(dict)
+        self._rv = 0
+        self._watchers: Dict[str, List[WatchHandler]] = collections.defaultdict(list)
+        self._pending: Deque[Tuple[str, str, dict, Optional[dict]]] = collections.deque()
+        self._dispatch_lock = threading.RLock()
+        self._dispatching = threading.local()
+        self._crds: Dict[str, dict] = {}
+        self.fail_next: Dict[Tuple[str, str], Exception] = {}  # fault injection: (verb, kind) -> error
+        self.request_log: List[Tuple[str, str, str]] = []      # (verb, kind, ns/name) for launch-delay analysis
+        if install_all_crds:
+            for info in scheme.workload_kinds():
+                self.install_crd(info.kind)
+
+    # ------------------------------------------------------------------ discovery / CRDs
+    def install_crd(self, kind: str) -> None:
+        info = self.scheme.info(kind)
+        self._crds[kind] = {"group": info.group, "version": info.version, "plural": info.plural}
+
+    def uninstall_crd(self, kind: str) -> None:
+        self._crds.pop(kind, None)
+
+    def crd_installed(self, kind: str) -> bool:
+        """Discovery: is the kind served? (reference workload_gate.go:90-106)"""
+        return kind in self._crds
+
+    def server_resources_for_group_version(self, gv: str) -> List[str]:
+        return [k for k, v in self._crds.items() if f"{v['group']}/{v['version']}" == gv]
+
+    # ------------------------------------------------------------------ helpers
+    def _next_rv(self) -> str:
+        self._rv += 1
+        return str(self._rv)
+
+    def _maybe_fail(self, verb: str, kind: str) -> None:
+        err = self.fail_next.pop((verb, kind), None)
+        if err is not None:
+            raise err
+
+    def _check_kind(self, kind: str) -> None:
+        if self.scheme.is_workload(kind) and kind not in self._crds:
+            raise NotFound(f"the server could not find the requested resource ({kind})")
+
+    @staticmethod
+    def _key(obj: dict) -> Tuple[str, str]:
+        return (c.namespace_of(obj), c.name_of(obj))
+
+    # ------------------------------------------------------------------ verbs
+    def create(self, obj: dict) -> dict:
+        kind = obj.get("kind")
+        if not kind or not c.name_of(obj):
+            raise Invalid("object needs kind and metadata.name")
+        self._check_kind(kind)
+        with self._lock:
+            self._maybe_fail("create", kind)
+            key = self._key(obj)
+            self.request_log.append(("create", kind, f"{key[0]}/{key[1]}"))
+            if key in self._objs[kind]:
+                raise AlreadyExists(f'{kind.lower()} "{key[1]}" already exists')
+            o = copy.deepcopy(obj)
+            o.setdefault("apiVersion", self.scheme.api_version(kind) if self.scheme.knows(kind) else "v1")
+            m = o.setdefault("metadata", {})
+            m["namespace"] = key[0]
+            m["uid"] = m.get("uid") or str(uuid.uuid4())
+            m["resourceVersion"] = self._next_rv()
+            m["creationTimestamp"] = m.get("creationTimestamp") or c.now_precise()
+            m.setdefault("generation", 1)
+            self._objs[kind][key] = o
+            out = copy.deepcopy(o)
+            self._pending.append((kind, ADDED, out, None))
+        self._dispatch()
+        return copy.deepcopy(out)
+
+    def get(self, kind: str, namespace: str, name: str) -> dict:
+        with self._lock:
+            o = self._objs[kind].get((namespace or "default", name))
+            if o is None:
+                raise NotFound(f'{kind.lower()} "{name}" not found')
+            return copy.deepcopy(o)
+
+    def list(self, kind: str, namespace: Optional[str] = None,
+             label_selector: Optional[Dict[str, str]] = None) -> List[dict]:
+        with self._lock:
+            out = []
+            for (ns, _), o in self._objs[kind].items():
+                if namespace and ns != namespace:
+                    continue
+                if label_selector:
+                    lab = o.get("metadata", {}).get("labels") or {}
+                    if any(lab.get(k) != v for k, v in label_selector.items()):
+                        continue
+                out.append(copy.deepcopy(o))
+            out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
+            return out
+
+    def _update(self, obj: dict, status_only: bool, spec_only: bool) -> dict:
+        kind = obj.get("kind")
+        with self._lock:
+            self._maybe_fail("update_status" if status_only else "update", kind)
+            key = self._key(obj)
+            self.request_log.append(("update_status" if status_only else "update", kind, f"{key[0]}/{key[1]}"))
+            cur = self._objs[kind].get(key)
+            if cur is None:
+                raise NotFound(f'{kind.lower()} "{key[1]}" not found')
+            rv = obj.get("metadata", {}).get("resourceVersion")
+            if rv and rv != cur["metadata"]["resourceVersion"]:
+                raise Conflict(f"Operation cannot be fulfilled on {kind.lower()} \"{key[1]}\": the object "
+                               f"has been modified; please apply your changes to the latest version")
+            old = copy.deepcopy(cur)
+            new = copy.deepcopy(cur)
+            if status_only:
+                new["status"] = copy.deepcopy(obj.get("status", {}))
+            else:
+                incoming = copy.deepcopy(obj)
+                keep_meta = {k: cur["metadata"][k] for k in ("uid", "creationTimestamp", "namespace") if k in cur["metadata"]}
+                if spec_only and "status" in cur:
+                    incoming["status"] = copy.deepcopy(cur["status"])
+                new = incoming
+                new.setdefault("metadata", {}).update(keep_meta)
+                if new.get("spec") != cur.get("spec"):
+                    new["metadata"]["generation"] = int(cur["metadata"].get("generation", 1)) + 1
+                else:
+                    new["metadata"]["generation"] = cur["metadata"].get("generation", 1)
+            new["metadata"]["resourceVersion"] = self._next_rv()
+            self._objs[kind][key] = new
+            out = copy.deepcopy(new)
+            self._pending.append((kind, MODIFIED, out, old))
+        self._dispatch()
+        return copy.deepcopy(out)
+
+    def update(self, obj: dict) -> dict:
+        """PUT of the main resource; for workload kinds .status is ignored (status subresource)."""
+        return self._update(obj, status_only=False, spec_only=self.scheme.is_workload(obj.get("kind", "")))
+
+    def update_status(self, obj: dict) -> dict:
+        """PUT of the /status subresource: only .status changes."""
+        return self._update(obj, status_only=True, spec_only=False)
+
+    def patch_labels(self, kind: str, namespace: str, name: str, labels: Dict[str, Optional[str]]) -> dict:
+        o = self.get(kind, namespace, name)
+        lab = o.setdefault("metadata", {}).setdefault("labels", {})
+        for k, v in labels.items():
+            if v is None:
+                lab.pop(k, None)
+            else:
+                lab[k] = v
+        o["metadata"].pop("resourceVersion", None)
+        return self._update(o, status_only=False, spec_only=False)
+
+    def delete(self, kind: str, namespace: str, name: str, cascade: bool = True) -> None:
+        with self._lock:
+            self._maybe_fail("delete", kind)
+            key = (namespace or "default", name)
+            self.request_log.append(("delete", kind, f"{key[0]}/{key[1]}"))
+            cur = self._objs[kind].pop(key, None)
+            if cur is None:
+                raise NotFound(f'{kind.lower()} "{name}" not found')
+            gone = copy.deepcopy(cur)
+            gone.setdefault("metadata", {})["deletionTimestamp"] = c.now_rfc3339()
+            self._pending.append((kind, DELETED, gone, None))
+            dependents = []
+            if cascade:
+                uid = cur["metadata"].get("uid")
+                for k2, objs in self._objs.items():
+                    for key2, o2 in objs.items():
+                        for ref in o2.get("metadata", {}).get("ownerReferences") or []:
+                            if ref.get("uid") == uid:
+                                dependents.append((k2, key2[0], key2[1]))
+                                break
+        self._dispatch()
+        for k2, ns2, n2 in dependents:
+            try:
+                self.delete(k2, ns2, n2, cascade=True)  # background garbage collection
+            except NotFound:
+                pass
+
+    # ------------------------------------------------------------------ watch
+    def watch(self, kind: str, handler: WatchHandler, replay: bool = True) -> Callable[[], None]:
+        """Register a watch.  With replay=True the handler first receives ADDED for every
+        existing object (informer LIST+WATCH).  Returns an unsubscribe function."""
+        with self._lock:
+            existing = [copy.deepcopy(o) for o in self._objs[kind].values()] if replay else []
+            self._watchers[kind].append(handler)
+        for o in existing:
+            handler(ADDED, o, None)
+
+        def stop():
+            with self._lock:
+                if handler in self._watchers[kind]:
+                    self._watchers[kind].remove(handler)
+        return stop
+
+    def _dispatch(self) -> None:
+        if getattr(self._dispatching, "active", False):
+            return  # the outer frame of this thread drains the queue (keeps event order)
+        with self._dispatch_lock:
+            self._dispatching.active = True
+            try:
+                while True:
+                    with self._lock:
+                        if not self._pending:
+                            break
+                        kind, ev, obj, old = self._pending.popleft()
+                        handlers = list(self._watchers.get(kind, ()))
+                    for h in handlers:
+                        h(ev, copy.deepcopy(obj), copy.deepcopy(old) if old is not None else None)
+            finally:
+                self._dispatching.active = False
+
+    # ------------------------------------------------------------------ events
+    def record_event(self, involved: dict, etype: str, reason: str, message: str, source: str = "kubedl") -> dict:
+        ns = c.namespace_of(involved)
+        name = f"{c.name_of(involved)}.{uuid.uuid4().hex[:12]}"
+        now = c.now_rfc3339()
+        ev = {"apiVersion": "v1", "kind": "Event", "metadata": {"name": name, "namespace": ns},
+              "involvedObject": {"kind": involved.get("kind", ""), "namespace": ns, "name": c.name_of(involved),
+                                 "uid": c.uid_of(involved), "apiVersion": involved.get("apiVersion", "")},
+              "type": etype, "reason": reason, "message": message, "count": 1,
+              "firstTimestamp": now, "lastTimestamp": now, "source": {"component": source}}
+        return self.create(ev)
+
+    def events_for(self, involved: dict) -> List[dict]:
+        uid = c.uid_of(involved)
+        return [e for e in self.list("Event", c.namespace_of(involved))
+                if e.get("involvedObject", {}).get("uid") == uid]
+
+    # ------------------------------------------------------------------ convenience
+    def apply(self, obj: dict) -> dict:
+        """kubectl-apply-like: create, or replace spec/metadata if it exists."""
+        try:
+            return self.create(obj)
+        except AlreadyExists:
+            cur = self.get(obj["kind"], c.namespace_of(obj), c.name_of(obj))
+            merged = copy.deepcopy(obj)
+            merged.setdefault("metadata", {}).pop("resourceVersion", None)
+            if "status" in cur:
+                merged["status"] = cur["status"]
+            return self.update(merged)
+
+    def kinds_present(self) -> List[str]:
+        with self._lock:
+            return [k for k, v in self._objs.items() if v]

@@ -1,0 +1,371 @@
+"""controller-runtime equivalents: Client (cached reads), EventRecorder, Controller, Manager.
+
+Mirrors what main.go builds (reference main.go:48-115): a manager holding the scheme, a cached
+client, an event recorder factory, N controllers each with a rate-limited work queue and
+`MaxConcurrentReconciles` workers, optional leader election, and start/stop.  Watches deliver
+(event, obj, old) to per-controller handlers which map events to reconcile `Request`s —
+`EnqueueRequestForOwner` and predicate functions are expressed as plain callables.
+
+Two ways to run: `start()` spawns worker threads (production, `cmd.manager`); `run_until_idle()`
+drains every queue on the calling thread (deterministic tests — the stronger harness SURVEY.md
+§4 asks for, since the reference never runs a reconcile loop in its tests).
+"""
+from __future__ import annotations
+
+import copy
+import fcntl
+import os
+import threading
+import time
+import traceback
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Tuple
+
+from ..api import common as c
+from ..api.kinds import SCHEME
+from ..apiserver.store import ADDED, DELETED, MODIFIED, APIServer, NotFound
+from ..utils.logger import logger
+from .workqueue import RateLimitingQueue
+
+log = logger("kubedl.runtime")
+
+
+@dataclass(frozen=True)
+class Request:
+    namespace: str
+    name: str
+
+    @property
+    def key(self) -> str:
+        return f"{self.namespace}/{self.name}"
+
+
+@dataclass
+class Result:
+    requeue: bool = False
+    requeue_after: float = 0.0
+
+
+class Client:
+    """Reads come from an informer cache kept current by watches; writes go to the API server.
+    `reader()` gives uncached reads (reference pkg/util/runtime.go:29-48)."""
+
+    def __init__(self, api: APIServer):
+        self.api = api
+        self._cache: Dict[str, Dict[Tuple[str, str], dict]] = {}
+        self._lock = threading.RLock()
+        self._stops: List[Callable[[], None]] = []
+
+    def ensure_informer(self, kind: str) -> None:
+        with self._lock:
+            if kind in self._cache:
+                return
+            self._cache[kind] = {}
+
+        def on_event(ev, obj, old):
+            key = (c.namespace_of(obj), c.name_of(obj))
+            with self._lock:
+                if ev == DELETED:
+                    self._cache[kind].pop(key, None)
+                else:
+                    self._cache[kind][key] = obj
+        self._stops.append(self.api.watch(kind, on_event, replay=True))
+
+    def get(self, kind: str, namespace: str, name: str) -> dict:
+        self.ensure_informer(kind)
+        with self._lock:
+            o = self._cache[kind].get((namespace or "default", name))
+            if o is None:
+                raise NotFound(f'{kind.lower()} "{name}" not found')
+            return copy.deepcopy(o)
+
+    def list(self, kind: str, namespace: Optional[str] = None,
+             label_selector: Optional[Dict[str, str]] = None) -> List[dict]:
+        self.ensure_informer(kind)
+        with self._lock:
+            out = []
+            for (ns, _), o in self._cache[kind].items():
+                if namespace and ns != namespace:
+                    continue
+                if label_selector:
+                    lab = o.get("metadata", {}).get("labels") or {}
+                    if any(lab.get(k) != v for k, v in label_selector.items()):
+                        continue
+                out.append(copy.deepcopy(o))
+            out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
+            return out
+
+    def reader(self) -> APIServer:
+        return self.api
+
+    # writes
+    def create(self, obj: dict) -> dict: return self.api.create(obj)
+    def update(self, obj: dict) -> dict: return self.api.update(obj)
+    def update_status(self, obj: dict) -> dict: return self.api.update_status(obj)
+    def delete(self, kind: str, namespace: str, name: str) -> None: self.api.delete(kind, namespace, name)
+
+    def stop(self) -> None:
+        for s in self._stops:
+            s()
+        self._stops.clear()
+
+
+class EventRecorder:
+    """record.EventRecorder: Events are stored in the API server and kept in memory."""
+
+    def __init__(self, api: APIServer, component: str):
+        self.api, self.component = api, component
+        self.events: List[Tuple[str, str, str, str]] = []  # (object key, type, reason, message)
+        self._lock = threading.Lock()
+
+    def event(self, obj: dict, etype: str, reason: str, message: str) -> None:
+        with self._lock:
+            self.events.append((c.key_of(obj), etype, reason, message))
+        try:
+            self.api.record_event(obj, etype, reason, message, source=self.component)
+        except Exception:  # events are best effort
+            pass
+
+    def eventf(self, obj: dict, etype: str, reason: str, fmt: str, *args) -> None:
+        self.event(obj, etype, reason, fmt % args if args else fmt)
+
+    def reasons(self) -> List[str]:
+        with self._lock:
+            return [e[2] for e in self.events]
+
+
+EventHandler = Callable[[str, dict, Optional[dict]], List[Request]]
+
+
+def enqueue_request_for_object(ev: str, obj: dict, old: Optional[dict]) -> List[Request]:
+    return [Request(c.namespace_of(obj), c.name_of(obj))]
+
+
+def enqueue_request_for_owner(owner_kind: str, is_controller: bool = True) -> EventHandler:
+    """handler.EnqueueRequestForOwner{OwnerType, IsController}."""
+    def handler(ev: str, obj: dict, old: Optional[dict]) -> List[Request]:
+        out = []
+        for o in (obj, old):
+            if o is None:
+                continue
+            for ref in o.get("metadata", {}).get("ownerReferences") or []:
+                if ref.get("kind") != owner_kind:
+                    continue
+                if is_controller and not ref.get("controller"):
+                    continue
+                r = Request(c.namespace_of(o), ref.get("name", ""))
+                if r not in out:
+                    out.append(r)
+        return out
+    return handler
+
+
+@dataclass
+class Predicates:
+    """predicate.Funcs: return False to drop the event before it reaches the handler."""
+    create: Callable[[dict], bool] = lambda obj: True
+    update: Callable[[dict, dict], bool] = lambda old, new: True
+    delete: Callable[[dict], bool] = lambda obj: True
+
+
+class Controller:
+    def __init__(self, name: str, reconciler: Callable[[Request], Result], manager: "Manager",
+                 max_concurrent_reconciles: int = 1):
+        self.name = name
+        self.reconciler = reconciler
+        self.manager = manager
+        self.max_concurrent = max(1, int(max_concurrent_reconciles))
+        self.queue = RateLimitingQueue(name)
+        self._watches: List[Tuple[str, EventHandler, Predicates]] = []
+        self._stops: List[Callable[[], None]] = []
+        self._threads: List[threading.Thread] = []
+        self.reconcile_count = 0
+        self.error_count = 0
+        self.trace: List[dict] = []  # per-reconcile span log
+
+    def watch(self, kind: str, handler: EventHandler = enqueue_request_for_object,
+              predicates: Optional[Predicates] = None) -> None:
+        self._watches.append((kind, handler, predicates or Predicates()))
+
+    def _on_event(self, handler: EventHandler, pred: Predicates):
+        def cb(ev: str, obj: dict, old: Optional[dict]):
+            try:
+                if ev == ADDED and not pred.create(obj):
+                    return
+                if ev == MODIFIED and not pred.update(old if old is not None else obj, obj):
+                    return
+                if ev == DELETED and not pred.delete(obj):
+                    return
+                for req in handler(ev, obj, old):
+                    if req.name:
+                        self.queue.add(req)
+            except Exception:
+                log.error("event handler of %s failed: %s", self.name, traceback.format_exc())
+        return cb
+
+    def start_watches(self) -> None:
+        for kind, handler, pred in self._watches:
+            self.manager.client.ensure_informer(kind)
+            self._stops.append(self.manager.api.watch(kind, self._on_event(handler, pred), replay=True))
+
+    def process_one(self, block: bool = False, timeout: Optional[float] = None) -> bool:
+        req, shutdown = self.queue.get(block=block, timeout=timeout)
+        if req is None:
+            return False
+        t0 = time.perf_counter()
+        err = None
+        res = Result()
+        try:
+            res = self.reconciler(req) or Result()
+        except Exception as e:  # reconcile error -> rate-limited requeue
+            err = e
+            self.error_count += 1
+            log.warning("reconcile %s %s failed: %s", self.name, req.key, e)
+            log.debug(traceback.format_exc())
+        finally:
+            self.reconcile_count += 1
+            self.trace.append({"controller": self.name, "key": req.key, "seconds": time.perf_counter() - t0,
+                               "error": repr(err) if err else None})
+            if len(self.trace) > 4096:
+                del self.trace[:2048]
+        if err is not None:
+            self.queue.add_rate_limited(req)
+        elif res.requeue_after > 0:
+            self.queue.forget(req)
+            self.queue.add_after(req, res.requeue_after)
+        elif res.requeue:
+            self.queue.add_rate_limited(req)
+        else:
+            self.queue.forget(req)
+        self.queue.done(req)
+        return True
+
+    def _worker(self) -> None:
+        while not self.manager.stopping.is_set():
+            self.process_one(block=True, timeout=0.2)
+
+    def start_workers(self) -> None:
+        for i in range(self.max_concurrent):
+            t = threading.Thread(target=self._worker, name=f"{self.name}-{i}", daemon=True)
+            t.start()
+            self._threads.append(t)
+
+    def stop(self) -> None:
+        for s in self._stops:
+            s()
+        self._stops.clear()
+        self.queue.shutdown()
+
+
+class LeaderElector:
+    """Lease-based single-active-manager guard (reference main.go:56-57,73).  On one box the lease
+    is an flock on a file; `acquire` blocks (or returns False when non-blocking)."""
+
+    def __init__(self, lock_path: str = "/tmp/kubedl-b200-leader.lock", identity: Optional[str] = None):
+        self.lock_path = lock_path
+        self.identity = identity or f"{os.uname().nodename}_{os.getpid()}"
+        self._fd = None
+
+    def acquire(self, blocking: bool = True) -> bool:
+        self._fd = os.open(self.lock_path, os.O_CREAT | os.O_RDWR, 0o644)
+        try:
+            fcntl.flock(self._fd, fcntl.LOCK_EX if blocking else fcntl.LOCK_EX | fcntl.LOCK_NB)
+        except BlockingIOError:
+            os.close(self._fd)
+            self._fd = None
+            return False
+        os.ftruncate(self._fd, 0)
+        os.write(self._fd, self.identity.encode())
+        return True
+
+    def release(self) -> None:
+        if self._fd is not None:
+            fcntl.flock(self._fd, fcntl.LOCK_UN)
+            os.close(self._fd)
+            self._fd = None
+
+
+class Manager:
+    def __init__(self, api: Optional[APIServer] = None, scheme=SCHEME, leader_election: bool = False,
+                 leader_lock_path: str = "/tmp/kubedl-b200-leader.lock"):
+        self.api = api or APIServer(scheme)
+        self.scheme = scheme
+        self.client = Client(self.api)
+        self.controllers: List[Controller] = []
+        self.stopping = threading.Event()
+        self._recorders: Dict[str, EventRecorder] = {}
+        self.leader_election = leader_election
+        self.elector = LeaderElector(leader_lock_path) if leader_election else None
+        self.runnables: List[Callable[["Manager"], None]] = []   # started with the manager (gpulet, metrics...)
+        self._started = False
+
+    def get_event_recorder_for(self, name: str) -> EventRecorder:
+        if name not in self._recorders:
+            self._recorders[name] = EventRecorder(self.api, name)
+        return self._recorders[name]
+
+    def new_controller(self, name: str, reconciler: Callable[[Request], Result],
+                       max_concurrent_reconciles: int = 1) -> Controller:
+        ctl = Controller(name, reconciler, self, max_concurrent_reconciles)
+        self.controllers.append(ctl)
+        if self._started:
+            ctl.start_watches()
+        return ctl
+
+    def add_runnable(self, fn: Callable[["Manager"], None]) -> None:
+        self.runnables.append(fn)
+
+    # ---- threaded mode
+    def start(self, block: bool = False) -> None:
+        if self.elector is not None:
+            self.elector.acquire(blocking=True)
+        self._started = True
+        for ctl in self.controllers:
+            ctl.start_watches()
+        for ctl in self.controllers:
+            ctl.start_workers()
+        for fn in self.runnables:
+            fn(self)
+        if block:
+            try:
+                while not self.stopping.is_set():
+                    time.sleep(0.2)
+            except KeyboardInterrupt:
+                pass
+            self.stop()
+
+    def stop(self) -> None:
+        self.stopping.set()
+        for ctl in self.controllers:
+            ctl.stop()
+        self.client.stop()
+        if self.elector is not None:
+            self.elector.release()
+
+    # ---- deterministic mode (tests, single-threaded drivers)
+    def start_watches(self) -> None:
+        if not self._started:
+            self._started = True
+            for ctl in self.controllers:
+                ctl.start_watches()
+
+    def run_until_idle(self, max_iterations: int = 10000, advance_delayed: bool = False) -> int:
+        """Process queued requests on this thread until every queue is empty.  Delayed items
+        (add_after / rate-limited requeues) are waited for only when advance_delayed=True and
+        their delay is short (< 50 ms)."""
+        self.start_watches()
+        n = 0
+        for _ in range(max_iterations):
+            progressed = False
+            for ctl in self.controllers:
+                while ctl.process_one(block=False):
+                    progressed = True
+                    n += 1
+            if not progressed:
+                if advance_delayed:
+                    delays = [d for d in (ctl.queue.next_delay() for ctl in self.controllers) if d is not None]
+                    if delays and min(delays) < 0.05:
+                        time.sleep(max(min(delays), 0) + 0.001)
+                        continue
+                break
+        return n

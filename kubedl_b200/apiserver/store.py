@@ -173,8 +173,11 @@ class APIServer:
             else:
                 incoming = copy.deepcopy(obj)
                 keep_meta = {k: cur["metadata"][k] for k in ("uid", "creationTimestamp", "namespace") if k in cur["metadata"]}
-                if spec_only and "status" in cur:
-                    incoming["status"] = copy.deepcopy(cur["status"])
+                if spec_only:
+                    if "status" in cur:
+                        incoming["status"] = copy.deepcopy(cur["status"])
+                    else:
+                        incoming.pop("status", None)
                 new = incoming
                 new.setdefault("metadata", {}).update(keep_meta)
                 if new.get("spec") != cur.get("spec"):

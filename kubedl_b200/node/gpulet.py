@@ -1,0 +1,497 @@
+"""gpulet — the node agent for one 8×B200 box: scheduler + kubelet + service DNS in one.
+
+The reference stops at "create Pod and Service objects"; a real cluster's scheduler, kubelet and
+kube-dns do the rest (SURVEY.md §1 boundaries).  On a single box gpulet plays those parts:
+
+  * scheduling: every pod gets at most one GPU (`nvidia.com/gpu` limit or the job's gang), bound
+    by index through KUBEDL_GPU_INDEX / LOCAL_RANK — all 8 devices stay visible so CUDA IPC and
+    NVLS multicast work across pods.  Gang-scheduled pods
+    (`schedulerName: gpu-gang` / `kube-batch`) are admitted all-or-nothing per PodGroup.
+  * container runtime: an image name maps to a local command (`ImageRegistry`); otherwise the
+    container's own command/args run.  `$(VAR)` references are expanded like the kubelet does;
+    init containers run first, sequentially (git-sync is emulated with `git clone`).
+  * DNS: headless-service names (`<job>-<rtype>-<idx>`, also `<name>.<ns>.svc[...]`) found in env
+    values are rewritten to 127.0.0.1; service ports are remapped to free host ports per job so
+    several jobs with the same default port can coexist.
+  * status: phase, PodScheduled/Initialized/Ready conditions with precise transition times (the
+    launch-delay metrics read PodReady), containerStatuses with state/exitCode/restartCount;
+    OnFailure/Always restart in place, Never/ExitCode end the pod.
+  * fault injection: `kill_pod`, `fail_pod_after` (reference has none).
+
+`FakeKubelet` is the process-free variant for control-plane tests: phases are flipped by hand.
+"""
+from __future__ import annotations
+
+import os
+import re
+import shlex
+import signal
+import socket
+import subprocess
+import sys
+import threading
+import time
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Tuple
+
+from ..api import common as c
+from ..apiserver.store import ADDED, DELETED, MODIFIED, APIServer, NotFound
+from ..utils.logger import logger
+
+log = logger("kubedl.gpulet")
+
+GANG_SCHEDULERS = ("kube-batch", "gpu-gang")
+_VAR = re.compile(r"\$\(([A-Za-z_][A-Za-z0-9_]*)\)")
+
+
+def expand_vars(s: str, env: Dict[str, str]) -> str:
+    """Kubernetes `$(VAR)` expansion; `$$(VAR)` escapes; unknown names are left as is."""
+    out, i = [], 0
+    while i < len(s):
+        if s.startswith("$$(", i):
+            j = s.find(")", i)
+            if j > 0:
+                out.append(s[i + 1:j + 1])
+                i = j + 1
+                continue
+        m = _VAR.match(s, i)
+        if m:
+            name = m.group(1)
+            out.append(env[name] if name in env else m.group(0))
+            i = m.end()
+        else:
+            out.append(s[i])
+            i += 1
+    return "".join(out)
+
+
+class ImageRegistry:
+    """image name -> local argv.  The stock images of the reference examples are mapped to the
+    worker entrypoints of this repo, so the example YAMLs run unchanged."""
+
+    def __init__(self):
+        py = sys.executable
+        self.images: Dict[str, List[str]] = {
+            "kubedl/pytorch-dist-example": [py, "-m", "kubedl_b200.worker.mnist_ddp"],
+            "kubedl/tf-mnist-with-summaries:1.0": [py, "-m", "kubedl_b200.worker.tf_stub"],
+            "docker.io/merlintang/xgboost-dist-iris:1.1": [py, "-m", "kubedl_b200.worker.xgb_train"],
+            "kubedl/xdl-mnist-example": [py, "-m", "kubedl_b200.worker.xdl_train"],
+            "kubedl/git-sync:v1": [py, "-m", "kubedl_b200.node.git_sync"],
+            "kubedl-b200/resnet50-ddp": [py, "-m", "kubedl_b200.worker.ddp"],
+        }
+
+    def register(self, image: str, argv: List[str]) -> None:
+        self.images[image] = list(argv)
+
+    def resolve(self, container: dict, env: Dict[str, str]) -> List[str]:
+        image = container.get("image", "")
+        cmd = [expand_vars(x, env) for x in (container.get("command") or [])]
+        args = [expand_vars(x, env) for x in (container.get("args") or [])]
+        if image in self.images:
+            base = self.images[image]
+            # image ENTRYPOINT is replaced by `command`; for mapped images the pod's command was
+            # written for the original image filesystem, so the mapped entrypoint wins and the
+            # original command line is handed over for argument parsing.
+            if cmd:
+                return base + ["--original-command", " ".join(shlex.quote(x) for x in cmd)] + args
+            return base + args
+        if cmd:
+            return cmd + args
+        raise RuntimeError(f"image {image!r} is not in the local image registry and the container has no command")
+
+
+def free_port() -> int:
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@dataclass
+class _Proc:
+    pod_key: Tuple[str, str]
+    container: str
+    popen: subprocess.Popen
+    gpu: Optional[int]
+    restart_count: int = 0
+    started_at: str = ""
+    log_path: str = ""
+
+
+class Gpulet:
+    def __init__(self, api: APIServer, num_gpus: Optional[int] = None, registry: Optional[ImageRegistry] = None,
+                 log_dir: str = "/tmp/kubedl-b200/pods", node_name: str = "b200-node-0",
+                 default_gpu_per_pod: bool = False):
+        self.api = api
+        self.registry = registry or ImageRegistry()
+        if num_gpus is None:
+            try:
+                import torch
+                num_gpus = torch.cuda.device_count()
+            except Exception:
+                num_gpus = 0
+        self.num_gpus = num_gpus
+        self.free_gpus: List[int] = list(range(num_gpus))
+        self.node_name = node_name
+        self.log_dir = log_dir
+        self.default_gpu_per_pod = default_gpu_per_pod
+        os.makedirs(log_dir, exist_ok=True)
+        self._lock = threading.RLock()
+        self._procs: Dict[Tuple[str, str], _Proc] = {}
+        self._gpu_of: Dict[Tuple[str, str], int] = {}
+        self._ports: Dict[Tuple[str, str, int], int] = {}     # (ns, job, declared port) -> host port
+        self._pending: Dict[Tuple[str, str], dict] = {}
+        self._stop = threading.Event()
+        self._threads: List[threading.Thread] = []
+        self._unwatch: List[Callable[[], None]] = []
+        self.launched = 0
+
+    # ------------------------------------------------------------------ lifecycle
+    def start(self) -> None:
+        self._unwatch.append(self.api.watch("Pod", self._on_pod, replay=True))
+        self._unwatch.append(self.api.watch("PodGroup", lambda *a: self._kick(), replay=False))
+        t = threading.Thread(target=self._loop, name="gpulet", daemon=True)
+        t.start()
+        self._threads.append(t)
+
+    def stop(self) -> None:
+        self._stop.set()
+        for u in self._unwatch:
+            u()
+        with self._lock:
+            procs = list(self._procs.values())
+        for p in procs:
+            self._kill(p)
+
+    def _kick(self) -> None:
+        pass  # the loop polls; the hook exists so watches wake it in future revisions
+
+    def _on_pod(self, ev: str, pod: dict, old: Optional[dict]) -> None:
+        key = (c.namespace_of(pod), c.name_of(pod))
+        with self._lock:
+            if ev == DELETED:
+                self._pending.pop(key, None)
+                p = self._procs.pop(key, None)
+                gpu = self._gpu_of.pop(key, None)
+                if gpu is not None:
+                    self.free_gpus.append(gpu)
+                    self.free_gpus.sort()
+            elif ev == ADDED and not (pod.get("status") or {}).get("phase"):
+                self._pending[key] = pod
+                p = None
+            else:
+                p = None
+        if ev == DELETED and p is not None:
+            self._kill(p)
+
+    # ------------------------------------------------------------------ scheduling
+    def _wants_gpu(self, pod: dict) -> bool:
+        for ctr in pod.get("spec", {}).get("containers") or []:
+            lim = (ctr.get("resources") or {}).get("limits") or {}
+            if int(lim.get("nvidia.com/gpu", 0) or 0) > 0:
+                return True
+        return self.default_gpu_per_pod and self.num_gpus > 0
+
+    def _gang_ready(self, pod: dict, pending: Dict[Tuple[str, str], dict]) -> bool:
+        """All-or-nothing: admit a gang-scheduled pod only when minMember pods of its job are
+        waiting (or already placed) and enough GPUs are free for all waiting ones."""
+        if pod.get("spec", {}).get("schedulerName") not in GANG_SCHEDULERS:
+            return True
+        job_name = c.labels_of(pod).get(c.JOB_NAME_LABEL, "")
+        ns = c.namespace_of(pod)
+        try:
+            pg = self.api.get("PodGroup", ns, job_name)
+        except NotFound:
+            return False
+        min_member = int(pg.get("spec", {}).get("minMember", 1))
+        mates = [p for p in pending.values()
+                 if c.namespace_of(p) == ns and c.labels_of(p).get(c.JOB_NAME_LABEL) == job_name]
+        with self._lock:
+            placed = sum(1 for (pns, pname) in self._procs
+                         if pns == ns and self._job_of.get((pns, pname)) == job_name)
+        if len(mates) + placed < min_member:
+            return False
+        need = sum(1 for p in mates if self._wants_gpu(p))
+        return need <= len(self.free_gpus)
+
+    @property
+    def _job_of(self) -> Dict[Tuple[str, str], str]:
+        if not hasattr(self, "_job_of_map"):
+            self._job_of_map: Dict[Tuple[str, str], str] = {}
+        return self._job_of_map
+
+    def _loop(self) -> None:
+        while not self._stop.is_set():
+            try:
+                self._admit()
+                self._reap()
+            except Exception as e:  # keep the node alive
+                log.error("gpulet loop error: %s", e)
+            time.sleep(0.01)
+
+    def _admit(self) -> None:
+        with self._lock:
+            pending = dict(self._pending)
+        for key, pod in sorted(pending.items()):
+            if not self._gang_ready(pod, pending):
+                continue
+            gpu = None
+            if self._wants_gpu(pod):
+                with self._lock:
+                    if not self.free_gpus:
+                        continue  # stays Pending until a GPU frees up
+                    gpu = self.free_gpus.pop(0)
+                    self._gpu_of[key] = gpu
+            with self._lock:
+                self._pending.pop(key, None)
+            try:
+                self._launch(pod, gpu)
+            except Exception as e:
+                log.warning("launch of %s failed: %s", key, e)
+                self._set_status(pod, c.POD_FAILED, reason=str(e), exit_code=127)
+                with self._lock:
+                    g = self._gpu_of.pop(key, None)
+                    if g is not None:
+                        self.free_gpus.append(g)
+
+    # ------------------------------------------------------------------ env / DNS
+    def _service_names(self, ns: str) -> Dict[str, dict]:
+        return {c.name_of(s): s for s in self.api.list("Service", ns)}
+
+    def _host_port(self, ns: str, job: str, port: int) -> int:
+        with self._lock:
+            k = (ns, job, port)
+            if k not in self._ports:
+                self._ports[k] = free_port()
+            return self._ports[k]
+
+    def _rewrite_endpoint(self, value: str, ns: str, job: str, svc_names: Dict[str, dict]) -> str:
+        """Replace service DNS names by loopback and declared service ports by host ports."""
+        def repl(m):
+            host, port = m.group(1), m.group(3)
+            short = host.split(".")[0]
+            if short not in svc_names and not host.startswith(job + "-"):
+                return m.group(0)
+            out = "127.0.0.1"
+            if port:
+                out += ":" + str(self._host_port(ns, job, int(port)))
+            return out
+        pat = re.compile(r"\b(" + re.escape(job) + r"-[a-z0-9]+-\d+(\.[A-Za-z0-9.\-]+)?)(?::(\d+))?")
+        return pat.sub(repl, value)
+
+    def build_env(self, pod: dict, container: dict, gpu: Optional[int]) -> Dict[str, str]:
+        ns = c.namespace_of(pod)
+        job = c.labels_of(pod).get(c.JOB_NAME_LABEL, "")
+        svc_names = self._service_names(ns)
+        env = dict(os.environ)
+        env["PYTHONPATH"] = os.pathsep.join(filter(None, [os.getcwd(), env.get("PYTHONPATH", "")]))
+        declared: Dict[str, str] = {}
+        for e in container.get("env") or []:
+            if "value" in e:
+                declared[e["name"]] = expand_vars(str(e["value"]), {**env, **declared})
+        for name, v in list(declared.items()):
+            v2 = self._rewrite_endpoint(v, ns, job, svc_names)
+            if name == "MASTER_ADDR" and v2 == "localhost":
+                v2 = "127.0.0.1"
+            declared[name] = v2
+        if "MASTER_PORT" in declared and job:
+            declared["MASTER_PORT"] = str(self._host_port(ns, job, int(declared["MASTER_PORT"])))
+        env.update(declared)
+        env["KUBEDL_POD_NAME"] = c.name_of(pod)
+        env["KUBEDL_POD_NAMESPACE"] = ns
+        env["KUBEDL_JOB_NAME"] = job
+        env["KUBEDL_REPLICA_TYPE"] = c.labels_of(pod).get(c.REPLICA_TYPE_LABEL, "")
+        env["KUBEDL_REPLICA_INDEX"] = c.labels_of(pod).get(c.REPLICA_INDEX_LABEL, "")
+        if gpu is not None:
+            env["KUBEDL_GPU_INDEX"] = str(gpu)
+            env["LOCAL_RANK"] = str(gpu)
+        return env
+
+    # ------------------------------------------------------------------ launch / status
+    def _launch(self, pod: dict, gpu: Optional[int]) -> None:
+        key = (c.namespace_of(pod), c.name_of(pod))
+        self._job_of[key] = c.labels_of(pod).get(c.JOB_NAME_LABEL, "")
+        now = c.now_precise()
+        self._set_status(pod, c.POD_PENDING, conditions=[
+            {"type": "PodScheduled", "status": "True", "lastTransitionTime": now}], host=True)
+        # init containers, sequentially
+        for ic in pod.get("spec", {}).get("initContainers") or []:
+            env = self.build_env(pod, ic, gpu)
+            argv = self.registry.resolve(ic, env)
+            rc = subprocess.call(argv, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            if rc != 0:
+                raise RuntimeError(f"init container {ic.get('name')} exited with {rc}")
+        containers = pod.get("spec", {}).get("containers") or []
+        if not containers:
+            raise RuntimeError("pod has no containers")
+        # one process per pod: the default (first) container carries the workload
+        ctr = containers[0]
+        env = self.build_env(pod, ctr, gpu)
+        argv = self.registry.resolve(ctr, env)
+        log_path = os.path.join(self.log_dir, f"{key[0]}_{key[1]}.log")
+        lf = open(log_path, "ab")
+        popen = subprocess.Popen(argv, env=env, stdout=lf, stderr=subprocess.STDOUT,
+                                 cwd=ctr.get("workingDir") or None, start_new_session=True)
+        lf.close()
+        proc = _Proc(key, ctr.get("name", ""), popen, gpu, started_at=c.now_precise(), log_path=log_path)
+        with self._lock:
+            self._procs[key] = proc
+        self.launched += 1
+        ready = c.now_precise()
+        self._set_status(pod, c.POD_RUNNING, conditions=[
+            {"type": "PodScheduled", "status": "True", "lastTransitionTime": now},
+            {"type": "Initialized", "status": "True", "lastTransitionTime": ready},
+            {"type": "ContainersReady", "status": "True", "lastTransitionTime": ready},
+            {"type": "Ready", "status": "True", "lastTransitionTime": ready}],
+            container_statuses=[{"name": proc.container, "ready": True, "restartCount": 0,
+                                 "state": {"running": {"startedAt": ready}}}], host=True, start=ready)
+
+    def _set_status(self, pod: dict, phase: str, conditions=None, container_statuses=None, reason: str = "",
+                    exit_code: Optional[int] = None, host: bool = False, start: Optional[str] = None) -> None:
+        try:
+            cur = self.api.get("Pod", c.namespace_of(pod), c.name_of(pod))
+        except NotFound:
+            return
+        status = cur.get("status") or {}
+        status["phase"] = phase
+        if conditions is not None:
+            status["conditions"] = conditions
+        if container_statuses is not None:
+            status["containerStatuses"] = container_statuses
+        if reason:
+            status["reason"] = reason[:200]
+        if host:
+            status["hostIP"] = "127.0.0.1"
+            status["podIP"] = "127.0.0.1"
+            cur.setdefault("spec", {})["nodeName"] = self.node_name
+        if start:
+            status["startTime"] = start
+        if exit_code is not None and container_statuses is None:
+            name = (cur.get("spec", {}).get("containers") or [{}])[0].get("name", "")
+            status["containerStatuses"] = [{"name": name, "ready": False, "restartCount": 0,
+                                            "state": {"terminated": {"exitCode": exit_code, "reason": "Error",
+                                                                     "finishedAt": c.now_precise()}}}]
+        cur["status"] = status
+        cur["metadata"].pop("resourceVersion", None)
+        try:
+            self.api.update(cur)
+        except NotFound:
+            pass
+
+    def _reap(self) -> None:
+        with self._lock:
+            procs = list(self._procs.items())
+        for key, proc in procs:
+            rc = proc.popen.poll()
+            if rc is None:
+                continue
+            if rc < 0:
+                rc = 128 - rc  # killed by signal n -> 128+n, like a container runtime reports
+            try:
+                pod = self.api.get("Pod", key[0], key[1])
+            except NotFound:
+                with self._lock:
+                    self._procs.pop(key, None)
+                continue
+            policy = pod.get("spec", {}).get("restartPolicy") or "Never"
+            if (policy == "Always") or (policy == "OnFailure" and rc != 0):
+                self._restart_in_place(pod, proc)
+                continue
+            with self._lock:
+                self._procs.pop(key, None)
+                gpu = self._gpu_of.pop(key, None)
+                if gpu is not None:
+                    self.free_gpus.append(gpu)
+                    self.free_gpus.sort()
+            done = c.now_precise()
+            conds = [cd for cd in (pod.get("status") or {}).get("conditions") or []]
+            for cd in conds:
+                if cd.get("type") in ("Ready", "ContainersReady"):
+                    cd["status"] = "False"
+                    cd["lastTransitionTime"] = done
+            self._set_status(pod, c.POD_SUCCEEDED if rc == 0 else c.POD_FAILED, conditions=conds,
+                             container_statuses=[{"name": proc.container, "ready": False,
+                                                  "restartCount": proc.restart_count,
+                                                  "state": {"terminated": {"exitCode": rc,
+                                                                           "reason": "Completed" if rc == 0 else "Error",
+                                                                           "startedAt": proc.started_at,
+                                                                           "finishedAt": done}}}])
+
+    def _restart_in_place(self, pod: dict, proc: _Proc) -> None:
+        ctr = (pod.get("spec", {}).get("containers") or [{}])[0]
+        env = self.build_env(pod, ctr, proc.gpu)
+        argv = self.registry.resolve(ctr, env)
+        lf = open(proc.log_path, "ab")
+        proc.popen = subprocess.Popen(argv, env=env, stdout=lf, stderr=subprocess.STDOUT, start_new_session=True)
+        lf.close()
+        proc.restart_count += 1
+        proc.started_at = c.now_precise()
+        conds = (pod.get("status") or {}).get("conditions")
+        self._set_status(pod, c.POD_RUNNING, conditions=conds,
+                         container_statuses=[{"name": proc.container, "ready": True,
+                                              "restartCount": proc.restart_count,
+                                              "state": {"running": {"startedAt": proc.started_at}}}])
+
+    def _kill(self, proc: _Proc, sig: int = signal.SIGKILL) -> None:
+        try:
+            os.killpg(proc.popen.pid, sig)   # the exact process group we started
+        except (ProcessLookupError, PermissionError):
+            pass
+
+    # ------------------------------------------------------------------ fault injection
+    def kill_pod(self, namespace: str, name: str, sig: int = signal.SIGKILL) -> bool:
+        with self._lock:
+            p = self._procs.get((namespace, name))
+        if p is None:
+            return False
+        self._kill(p, sig)
+        return True
+
+    def fail_pod_after(self, namespace: str, name: str, seconds: float, sig: int = signal.SIGTERM) -> None:
+        threading.Timer(seconds, lambda: self.kill_pod(namespace, name, sig)).start()
+
+    def pod_log(self, namespace: str, name: str) -> str:
+        path = os.path.join(self.log_dir, f"{namespace}_{name}.log")
+        try:
+            with open(path, "r", errors="replace") as f:
+                return f.read()
+        except FileNotFoundError:
+            return ""
+
+
+class FakeKubelet:
+    """Process-free kubelet for control-plane tests: flip pod phases by hand, with the same
+    status shape gpulet writes (what reference pkg/test_util/v1/pod.go:57-95 does with
+    hand-built Pod objects)."""
+
+    def __init__(self, api: APIServer):
+        self.api = api
+
+    def set_phase(self, namespace: str, name: str, phase: str, exit_code: Optional[int] = None,
+                  restart_count: int = 0, container: Optional[str] = None, ready_at: Optional[str] = None) -> dict:
+        pod = self.api.get("Pod", namespace, name)
+        cname = container or (pod["spec"]["containers"][0].get("name", "") if pod["spec"].get("containers") else "")
+        status = pod.get("status") or {}
+        status["phase"] = phase
+        now = ready_at or c.now_precise()
+        if phase == c.POD_RUNNING:
+            status["conditions"] = [{"type": "PodScheduled", "status": "True", "lastTransitionTime": now},
+                                    {"type": "Ready", "status": "True", "lastTransitionTime": now}]
+            status["containerStatuses"] = [{"name": cname, "ready": True, "restartCount": restart_count,
+                                            "state": {"running": {"startedAt": now}}}]
+            status.setdefault("startTime", now)
+        elif phase in (c.POD_SUCCEEDED, c.POD_FAILED):
+            code = exit_code if exit_code is not None else (0 if phase == c.POD_SUCCEEDED else 1)
+            status["containerStatuses"] = [{"name": cname, "ready": False, "restartCount": restart_count,
+                                            "state": {"terminated": {"exitCode": code, "finishedAt": now}}}]
+        pod["status"] = status
+        pod["metadata"].pop("resourceVersion", None)
+        return self.api.update(pod)
+
+    def set_all(self, namespace: str, phase: str, selector: Optional[Dict[str, str]] = None, **kw) -> int:
+        n = 0
+        for pod in self.api.list("Pod", namespace, selector):
+            self.set_phase(namespace, c.name_of(pod), phase, **kw)
+            n += 1
+        return n

@@ -141,6 +141,12 @@ class JobMetrics:
         self._restart = fam.restart.labels(lk)
         self._first, self._all = fam.first_pod, fam.all_pods
         self.launch_delays: Dict[str, List[Tuple[str, float]]] = {"first_pod": [], "all_pods": []}
+        # The reference means to observe each delay once per job but its guards leak (first-pod is
+        # re-observed on every pass while Created stays True, job.go:243-245; all-pods again after
+        # a restart because Restarting has already flipped back to Running, job.go:255-259).
+        # Observing once per job UID gives the intended semantics.
+        self._seen_first: set = set()
+        self._seen_all: set = set()
         if reader is not None:
             fam.gauge_sources[lk] = lambda: (job_status_counter(kind, reader, st.is_running),
                                              job_status_counter(kind, reader, _is_pending))
@@ -168,6 +174,9 @@ class JobMetrics:
         created = c.parse_time(job.get("metadata", {}).get("creationTimestamp"))
         if earliest is None or created is None:
             return
+        if c.uid_of(job) in self._seen_first:
+            return
+        self._seen_first.add(c.uid_of(job))
         delay = earliest - created
         self._first.labels(self.kind, c.name_of(job), c.namespace_of(job), c.uid_of(job)).observe(delay)
         self.launch_delays["first_pod"].append((c.key_of(job), delay))
@@ -187,6 +196,9 @@ class JobMetrics:
             t = _pod_ready_time(pod)
             if t is not None and t > final:
                 final = t
+        if c.uid_of(job) in self._seen_all:
+            return
+        self._seen_all.add(c.uid_of(job))
         delay = final - created
         self._all.labels(self.kind, c.name_of(job), c.namespace_of(job), c.uid_of(job)).observe(delay)
         self.launch_delays["all_pods"].append((c.key_of(job), delay))

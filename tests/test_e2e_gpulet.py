@@ -1,0 +1,137 @@
+"""End to end on CPU (BASELINE.json config #1): the reference's PyTorchJob example YAML, unchanged,
+through the controllers and the node agent — real processes, real gloo rendezvous wired only by
+the injected env — until the job reports Succeeded; plus the gpulet helpers."""
+import os
+import time
+
+import pytest
+from prometheus_client import CollectorRegistry
+
+from cp_helpers import load_example, tmpl
+from kubedl_b200.api import common as c
+from kubedl_b200.api import kinds as k
+from kubedl_b200.controllers.registry import setup_with_manager
+from kubedl_b200.engine.job_controller import JobControllerConfiguration
+from kubedl_b200.node.gpulet import Gpulet, ImageRegistry, expand_vars
+from kubedl_b200.plugins import gang_schedule
+from kubedl_b200.runtime.manager import Manager
+
+
+def _wait(fn, timeout=120.0, every=0.05):
+    t0 = time.time()
+    while time.time() - t0 < timeout:
+        v = fn()
+        if v:
+            return v
+        time.sleep(every)
+    raise AssertionError("timed out")
+
+
+def _cluster(num_gpus=0, gang=""):
+    mgr = Manager()
+    gang_schedule.register_gang_schedulers(mgr)
+    cfg = JobControllerConfiguration(enable_gang_scheduling=bool(gang), gang_scheduler_name=gang)
+    recs = setup_with_manager(mgr, cfg, "*", CollectorRegistry())
+    let = Gpulet(mgr.api, num_gpus=num_gpus, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}")
+    mgr.start()
+    let.start()
+    return mgr, recs, let
+
+
+def _terminal(mgr, kind, ns, name):
+    conds = [x["type"] for x in mgr.api.get(kind, ns, name).get("status", {}).get("conditions", [])]
+    return conds if ("Succeeded" in conds or "Failed" in conds) else None
+
+
+def test_expand_vars():
+    env = {"TASK_NAME": "worker", "TASK_INDEX": "1"}
+    assert expand_vars("--task_name $(TASK_NAME) --i $(TASK_INDEX) $(NOPE) $$(TASK_NAME)", env) == \
+        "--task_name worker --i 1 $(NOPE) $(TASK_NAME)"
+
+
+def test_image_registry_resolution():
+    reg = ImageRegistry()
+    argv = reg.resolve({"image": "kubedl/pytorch-dist-example"}, {})
+    assert argv[-2:] == ["-m", "kubedl_b200.worker.mnist_ddp"]
+    argv = reg.resolve({"image": "busybox", "command": ["sh", "-c"], "args": ["echo $(X)"]}, {"X": "hi"})
+    assert argv == ["sh", "-c", "echo hi"]
+    with pytest.raises(RuntimeError):
+        reg.resolve({"image": "unknown/image"}, {})
+
+
+def test_pytorch_example_end_to_end_gloo():
+    mgr, recs, let = _cluster()
+    try:
+        (job,) = load_example("example/pytorch/pytorch_job_mnist_mpi.yaml")
+        for spec in job["spec"]["pytorchReplicaSpecs"].values():          # keep the run short
+            spec["template"]["spec"]["containers"][0]["env"] = [{"name": "KUBEDL_MNIST_STEPS", "value": "5"}]
+        mgr.api.create(job)
+        conds = _wait(lambda: _terminal(mgr, "PyTorchJob", "kubedl", "pytorch-dist-sendrecv-example"))
+        assert conds == ["Created", "Running", "Succeeded"], (conds, let.pod_log("kubedl", "pytorch-dist-sendrecv-example-master-0"))
+        st = mgr.api.get("PyTorchJob", "kubedl", "pytorch-dist-sendrecv-example")["status"]
+        assert st["replicaStatuses"]["Master"]["succeeded"] == 1
+        log = let.pod_log("kubedl", "pytorch-dist-sendrecv-example-worker-1")
+        assert "rank 2/3" in log
+        m = recs["PyTorchJob"].metrics
+        assert len(m.launch_delays["first_pod"]) == 1 and len(m.launch_delays["all_pods"]) == 1
+        assert 0 <= m.launch_delays["first_pod"][0][1] <= m.launch_delays["all_pods"][0][1] < 30
+    finally:
+        let.stop()
+        mgr.stop()
+
+
+def test_exit_code_restart_end_to_end():
+    """Worker exits with the user-retryable code 138 once -> pod recreated with the same rank ->
+    job still succeeds (reference pod.go:282-304, train_util.go:18-53)."""
+    mgr, recs, let = _cluster()
+    try:
+        marker = f"/tmp/kubedl-b200/restarted-{os.getpid()}"
+        if os.path.exists(marker):
+            os.remove(marker)
+        script = (f"import os,sys\n"
+                  f"if os.environ['KUBEDL_REPLICA_TYPE']=='worker' and not os.path.exists('{marker}'):\n"
+                  f"    open('{marker}','w').close(); sys.exit(138)\n"
+                  f"sys.exit(0)\n")
+        t = {"spec": {"containers": [{"name": "pytorch", "image": "python", "command": ["python", "-c", script]}]}}
+        job = k.new_job("PyTorchJob", "flaky", "ns", {"Master": {"restartPolicy": "ExitCode", "template": t},
+                                                       "Worker": {"restartPolicy": "ExitCode", "template": t}})
+        # keep the master alive until the worker has been through its restart
+        job["spec"]["pytorchReplicaSpecs"]["Master"]["template"] = {"spec": {"containers": [{
+            "name": "pytorch", "image": "python",
+            "command": ["python", "-c", f"import os,time\nwhile not os.path.exists('{marker}'): time.sleep(0.05)\ntime.sleep(1.0)"]}]}}
+        mgr.api.create(job)
+        conds = _wait(lambda: _terminal(mgr, "PyTorchJob", "ns", "flaky"))
+        assert conds[-1] == "Succeeded", conds
+        assert "JobRestarting" in recs["PyTorchJob"].recorder.reasons()
+        assert "ExitedWithCode" in recs["PyTorchJob"].recorder.reasons()
+    finally:
+        let.stop()
+        mgr.stop()
+
+
+def test_gpu_gang_admission_is_all_or_nothing():
+    """Two 2-GPU gangs on a 3-GPU node: the second gang must wait for the first to finish."""
+    mgr, recs, let = _cluster(num_gpus=3, gang="gpu-gang")
+    try:
+        def job(name, seconds):
+            t = {"spec": {"containers": [{"name": "pytorch", "image": "python",
+                                          "command": ["python", "-c", f"import time; time.sleep({seconds})"],
+                                          "resources": {"limits": {"nvidia.com/gpu": 1}}}]}}
+            return k.new_job("PyTorchJob", name, "ns", {"Master": {"restartPolicy": "Never", "template": t},
+                                                         "Worker": {"restartPolicy": "Never", "template": t}},
+                             cleanPodPolicy="All")
+        mgr.api.create(job("a", 1.5))
+        _wait(lambda: len([p for p in mgr.api.list("Pod", "ns") if p.get("status", {}).get("phase") == "Running"]) == 2)
+        mgr.api.create(job("b", 0.2))
+        time.sleep(0.5)
+        b_pods = [p for p in mgr.api.list("Pod", "ns", {"job-name": "b"})]
+        assert len(b_pods) == 2 and all(not p.get("status", {}).get("phase") or p["status"]["phase"] == "Pending"
+                                        for p in b_pods)                 # 1 free GPU < 2 needed: nobody starts
+        assert mgr.api.get("PodGroup", "ns", "b")["spec"]["minResources"] == {"nvidia.com/gpu": 2}
+        _wait(lambda: _terminal(mgr, "PyTorchJob", "ns", "a"))
+        assert _wait(lambda: _terminal(mgr, "PyTorchJob", "ns", "b"))[-1] == "Succeeded"
+        gpus = {e for e in let.free_gpus}
+        assert gpus == {0, 1, 2}
+    finally:
+        let.stop()
+        mgr.stop()

@@ -1,0 +1,198 @@
+"""`python -m kubedl_b200.cmd.kubedlctl` — kubectl-style client for a running manager, plus an
+embedded mode (`run`) that brings up control plane + node agent in-process, applies manifests,
+waits for the jobs to finish and prints status and launch-delay metrics.
+
+  kubedlctl apply -f job.yaml            kubedlctl get pytorchjobs -n kubedl
+  kubedlctl describe tfjob mnist -n kubedl     kubedlctl delete xdljob x -n kubedl
+  kubedlctl logs <pod> -n kubedl         kubedlctl run -f example.yaml --gpus 8 --timeout 600
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+import time
+import urllib.error
+import urllib.request
+from typing import List, Optional
+
+import yaml
+
+from ..api import common as c
+from ..api.kinds import SCHEME
+from ..utils import status as st
+
+_ALIASES = {}
+for _info in SCHEME.workload_kinds():
+    for _n in (_info.kind.lower(), _info.plural, _info.singular):
+        _ALIASES[_n] = _info.kind
+_ALIASES.update({"pod": "Pod", "pods": "Pod", "svc": "Service", "service": "Service", "services": "Service",
+                 "event": "Event", "events": "Event", "podgroup": "PodGroup", "podgroups": "PodGroup"})
+
+
+def resolve_kind(word: str) -> str:
+    k = _ALIASES.get(word.lower())
+    if k is None:
+        raise SystemExit(f"error: the server doesn't have a resource type \"{word}\"")
+    return k
+
+
+def _path(kind: str, ns: str, name: Optional[str] = None) -> str:
+    if SCHEME.is_workload(kind):
+        i = SCHEME.info(kind)
+        p = f"/apis/{i.group}/{i.version}/namespaces/{ns}/{i.plural}"
+    elif kind == "PodGroup":
+        p = f"/apis/scheduling.incubator.k8s.io/v1alpha1/namespaces/{ns}/podgroups"
+    else:
+        p = f"/api/v1/namespaces/{ns}/{kind.lower()}s"
+    return p + (f"/{name}" if name else "")
+
+
+def _http(server: str, method: str, path: str, body: Optional[bytes] = None):
+    req = urllib.request.Request(f"http://{server}{path}", data=body, method=method)
+    try:
+        with urllib.request.urlopen(req, timeout=30) as r:
+            data = r.read()
+            ctype = r.headers.get("Content-Type", "")
+    except urllib.error.HTTPError as e:
+        msg = e.read().decode()
+        try:
+            msg = json.loads(msg).get("message", msg)
+        except Exception:
+            pass
+        raise SystemExit(f"Error from server: {msg}")
+    except urllib.error.URLError as e:
+        raise SystemExit(f"cannot reach the manager at {server}: {e.reason} (start it with python -m kubedl_b200.cmd.manager)")
+    return json.loads(data) if "json" in ctype else data.decode()
+
+
+def _age(ts: Optional[str]) -> str:
+    t = c.parse_time(ts)
+    if t is None:
+        return "<unknown>"
+    s = int(time.time() - t)
+    return f"{s}s" if s < 120 else (f"{s // 60}m" if s < 7200 else f"{s // 3600}h")
+
+
+def print_table(kind: str, items: List[dict]) -> None:
+    if SCHEME.is_workload(kind):
+        # printer columns of the CRDs (reference config/crd/bases/kubeflow.org_pytorchjobs.yaml:11-32)
+        rows = [("NAME", "STATE", "AGE", "FINISHED-TTL", "MAX-LIFETIME")]
+        for o in items:
+            sp = o.get("spec", {})
+            rows.append((c.name_of(o), st.last_condition_type(o.get("status", {})) or "", _age(o["metadata"].get("creationTimestamp")),
+                         str(sp.get("ttlSecondsAfterFinished", "")), str(sp.get("activeDeadlineSeconds", ""))))
+    elif kind == "Pod":
+        rows = [("NAME", "STATUS", "RESTARTS", "AGE", "NODE")]
+        for o in items:
+            cs = (o.get("status", {}).get("containerStatuses") or [{}])[0]
+            rows.append((c.name_of(o), o.get("status", {}).get("phase", "Pending"), str(cs.get("restartCount", 0)),
+                         _age(o["metadata"].get("creationTimestamp")), o.get("spec", {}).get("nodeName", "")))
+    else:
+        rows = [("NAME", "AGE")] + [(c.name_of(o), _age(o["metadata"].get("creationTimestamp"))) for o in items]
+    w = [max(len(r[i]) for r in rows) for i in range(len(rows[0]))]
+    for r in rows:
+        print("   ".join(x.ljust(w[i]) for i, x in enumerate(r)).rstrip())
+
+
+def cmd_run(args) -> int:
+    """Embedded cluster: apply, wait for every submitted job to reach a terminal condition."""
+    from prometheus_client import CollectorRegistry
+    from . import manager as M
+    margs = M.build_parser().parse_args(["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0",
+                                         "--workloads", "*"] + (["--gpus", str(args.gpus)] if args.gpus is not None else [])
+                                        + (["--gang-scheduler-name", args.gang] if args.gang else []))
+    reg = CollectorRegistry()
+    op = M.build_operator(margs, metrics_registry=reg)
+    M.start_operator(op, margs, metrics_registry=reg)
+    jobs = []
+    try:
+        for f in args.filename:
+            with open(f) as fh:
+                for d in yaml.safe_load_all(fh):
+                    if not d:
+                        continue
+                    if not op.mgr.api.scheme.knows(d.get("kind", "")):
+                        print(f"skipped {d.get('kind')}/{d.get('metadata', {}).get('name')} (not served on a single box)")
+                        continue
+                    o = op.mgr.api.apply(d)
+                    print(f"{o['kind'].lower()}/{c.name_of(o)} applied")
+                    if SCHEME.is_workload(o["kind"]):
+                        jobs.append((o["kind"], c.namespace_of(o), c.name_of(o)))
+        deadline = time.time() + args.timeout
+        rc = 0
+        for kind, ns, name in jobs:
+            while time.time() < deadline:
+                try:
+                    status = op.mgr.api.get(kind, ns, name).get("status", {})
+                except Exception:
+                    status = {"conditions": [{"type": "Deleted", "status": "True"}]}
+                    break
+                if st.is_succeeded(status) or st.is_failed(status):
+                    break
+                time.sleep(0.05)
+            state = st.last_condition_type(status)
+            print(f"{kind.lower()}/{name}: {state}  replicaStatuses={json.dumps(status.get('replicaStatuses', {}))}")
+            if state != c.JOB_SUCCEEDED:
+                rc = 1
+        for kind, rec in op.reconcilers.items():
+            for which, obs in rec.metrics.launch_delays.items():
+                for key, v in obs:
+                    print(f"launch-delay {which} {kind} {key}: {v * 1000:.1f} ms")
+        return rc
+    finally:
+        op.stop()
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="kubedlctl")
+    ap.add_argument("--server", "-s", default="127.0.0.1:8001")
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    a = sub.add_parser("apply"); a.add_argument("-f", "--filename", required=True, action="append")
+    g = sub.add_parser("get"); g.add_argument("kind"); g.add_argument("name", nargs="?"); g.add_argument("-n", "--namespace", default="default"); g.add_argument("-o", "--output", default="")
+    d = sub.add_parser("describe"); d.add_argument("kind"); d.add_argument("name"); d.add_argument("-n", "--namespace", default="default")
+    r = sub.add_parser("delete"); r.add_argument("kind"); r.add_argument("name"); r.add_argument("-n", "--namespace", default="default")
+    l = sub.add_parser("logs"); l.add_argument("pod"); l.add_argument("-n", "--namespace", default="default")
+    x = sub.add_parser("run"); x.add_argument("-f", "--filename", required=True, action="append")
+    x.add_argument("--gpus", type=int, default=None); x.add_argument("--timeout", type=float, default=600.0); x.add_argument("--gang", default="")
+    args = ap.parse_args(argv)
+    if args.cmd == "run":
+        return cmd_run(args)
+    if args.cmd == "apply":
+        for f in args.filename:
+            with open(f, "rb") as fh:
+                for res in _http(args.server, "POST", "/apply", fh.read()):
+                    print(f"{str(res.get('kind', '')).lower()}/{res.get('name')} {res.get('result')}")
+        return 0
+    if args.cmd == "logs":
+        print(_http(args.server, "GET", f"/logs/{args.namespace}/{args.pod}"), end="")
+        return 0
+    kind = resolve_kind(args.kind)
+    if args.cmd == "get":
+        out = _http(args.server, "GET", _path(kind, args.namespace, args.name))
+        items = [out] if args.name else out["items"]
+        if args.output in ("json", "yaml"):
+            obj = out if args.name else {"items": items}
+            print(json.dumps(obj, indent=2) if args.output == "json" else yaml.safe_dump(obj, sort_keys=False))
+        else:
+            print_table(kind, items)
+        return 0
+    if args.cmd == "describe":
+        obj = _http(args.server, "GET", _path(kind, args.namespace, args.name))
+        print(yaml.safe_dump(obj, sort_keys=False))
+        evs = _http(args.server, "GET", f"/api/v1/namespaces/{args.namespace}/events")["items"]
+        mine = [e for e in evs if e.get("involvedObject", {}).get("uid") == obj["metadata"]["uid"]]
+        if mine:
+            print("Events:")
+            for e in mine:
+                print(f"  {e['type']:8s} {e['reason']:28s} {e['message']}")
+        return 0
+    if args.cmd == "delete":
+        _http(args.server, "DELETE", _path(kind, args.namespace, args.name))
+        print(f"{kind.lower()} \"{args.name}\" deleted")
+        return 0
+    return 2
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,126 @@
+"""`python -m kubedl_b200.cmd.manager` — the operator process (reference main.go:48-115).
+
+Order of wiring is the reference's: manager -> schemes -> gang schedulers -> workload controllers
+(through the workload gate) -> storage backends -> persist controllers -> metrics HTTP -> start.
+Flags are the reference's (main.go:54-60, workload_gate.go:22, persist_controller.go:31-33;
+table in reference docs/startup_flags.md) plus what a single-box deployment needs: the REST
+façade address, the number of GPUs the node agent manages, and `--no-node-agent`.
+"""
+from __future__ import annotations
+
+import argparse
+import signal
+import sys
+import threading
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+from ..apiserver import rest
+from ..apiserver.store import APIServer
+from ..controllers import persist
+from ..controllers import registry as controller_registry
+from ..engine.job_controller import JobControllerConfiguration
+from ..node.gpulet import Gpulet
+from ..plugins import gang_schedule
+from ..plugins import metrics as metrics_mod
+from ..plugins.storage import backends as storage_backends
+from ..runtime.manager import Manager
+from ..utils.logger import logger
+
+log = logger("kubedl.setup")
+
+# package-level option holder read by the controllers (reference cmd/options/options.go:22)
+CTRL_CONFIG = JobControllerConfiguration()
+
+
+def _bool(s: str) -> bool:
+    return str(s).lower() in ("1", "true", "yes", "y", "")
+
+
+def build_parser() -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser(prog="kubedl-manager")
+    ap.add_argument("--controller-metrics-addr", default=":8080", help="The address the controller metric endpoint binds to.")
+    ap.add_argument("--metrics-addr", type=int, default=8443, help="The address the default endpoints binds to.")
+    ap.add_argument("--enable-leader-election", type=_bool, nargs="?", const=True, default=True,
+                    help="Enable leader election for controller manager.")
+    ap.add_argument("--gang-scheduler-name", default="", help="The scheduler to gang-schedule kubedl jobs, "
+                    "gang-scheduling is enabled when it is not empty (kube-batch | gpu-gang).")
+    ap.add_argument("--max-reconciles", type=int, default=1, help="The number of max concurrent reconciles of each controller")
+    ap.add_argument("--workloads", default="auto", help="List of workloads to be enabled, `*` enables all, `-foo` disables foo.")
+    ap.add_argument("--region", default="", help="region tag for persisted rows")
+    ap.add_argument("--event-storage", default="", help="event storage backend plugin name, persist events into backend if specified")
+    ap.add_argument("--object-storage", default="", help="object storage backend plugin name, persist jobs and pods into backend if specified")
+    # single-box additions
+    ap.add_argument("--serve", default="127.0.0.1:8001", help="REST façade address for kubedlctl ('' disables)")
+    ap.add_argument("--gpus", type=int, default=None, help="GPUs managed by the node agent (default: all visible)")
+    ap.add_argument("--no-node-agent", action="store_true", help="control plane only (pods are never started)")
+    ap.add_argument("--leader-lock", default="/tmp/kubedl-b200-leader.lock")
+    return ap
+
+
+@dataclass
+class Operator:
+    mgr: Manager
+    reconcilers: Dict[str, object]
+    persisters: Dict[str, object]
+    gpulet: Optional[Gpulet]
+    servers: List[object] = field(default_factory=list)
+
+    def stop(self) -> None:
+        if self.gpulet:
+            self.gpulet.stop()
+        for s in self.servers:
+            try:
+                s.shutdown()
+            except Exception:
+                pass
+        self.mgr.stop()
+
+
+def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None) -> Operator:
+    if args.max_reconciles <= 0:
+        args.max_reconciles = 1
+    CTRL_CONFIG.max_concurrent_reconciles = args.max_reconciles
+    if args.gang_scheduler_name:
+        CTRL_CONFIG.enable_gang_scheduling = True
+        CTRL_CONFIG.gang_scheduler_name = args.gang_scheduler_name
+    mgr = Manager(api=api, leader_election=bool(args.enable_leader_election), leader_lock_path=args.leader_lock)
+    gang_schedule.register_gang_schedulers(mgr)
+    recs = controller_registry.setup_with_manager(mgr, CTRL_CONFIG, args.workloads, metrics_registry)
+    storage_backends.register_storage_backends()
+    pers = persist.setup_with_manager(mgr, args.object_storage, args.event_storage, args.region, args.workloads)
+    let = None if args.no_node_agent else Gpulet(mgr.api, num_gpus=args.gpus)
+    return Operator(mgr, recs, pers, let)
+
+
+def start_operator(op: Operator, args, metrics_registry=None) -> None:
+    if args.metrics_addr:
+        try:
+            metrics_mod.start_monitoring(int(args.metrics_addr), registry=metrics_registry)
+        except OSError as e:
+            log.warning("metrics endpoint on %s unavailable: %s", args.metrics_addr, e)
+    op.mgr.start(block=False)
+    if op.gpulet:
+        op.gpulet.start()
+    if args.serve:
+        host, _, port = args.serve.rpartition(":")
+        op.servers.append(rest.serve(op.mgr.api, host or "127.0.0.1", int(port),
+                                     log_reader=op.gpulet.pod_log if op.gpulet else None))
+
+
+def main(argv=None) -> int:
+    args = build_parser().parse_args(argv)
+    op = build_operator(args)
+    start_operator(op, args)
+    log.warning("kubedl-b200 manager up: workloads=%s gang=%s rest=%s gpus=%s", list(op.reconcilers),
+                args.gang_scheduler_name or "-", args.serve or "-", op.gpulet.num_gpus if op.gpulet else "-")
+    stop = threading.Event()
+    for sig in (signal.SIGINT, signal.SIGTERM):   # reference pkg/util/signals/signal.go
+        signal.signal(sig, lambda *_: stop.set())
+    stop.wait()
+    op.stop()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,80 @@
+"""Operator entry, flags (reference main.go:54-60, docs/startup_flags.md) and the kubedlctl client
+against the REST façade."""
+import json
+import socket
+import time
+
+import pytest
+from prometheus_client import CollectorRegistry
+
+from cp_helpers import REF
+from kubedl_b200.cmd import kubedlctl, manager
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def test_flag_defaults_match_reference():
+    a = manager.build_parser().parse_args([])
+    assert a.controller_metrics_addr == ":8080" and a.metrics_addr == 8443
+    assert a.enable_leader_election is True and a.gang_scheduler_name == "" and a.max_reconciles == 1
+    assert a.workloads == "auto" and a.region == "" and a.event_storage == "" and a.object_storage == ""
+    a = manager.build_parser().parse_args(["--enable-leader-election=false", "--max-reconciles", "0"])
+    assert a.enable_leader_election is False
+
+
+def test_operator_wiring_and_kubedlctl(capsys, tmp_path):
+    port = _free_port()
+    args = manager.build_parser().parse_args(["--enable-leader-election=false", "--serve", f"127.0.0.1:{port}",
+                                              "--metrics-addr", "0", "--workloads", "*", "--no-node-agent",
+                                              "--max-reconciles", "0", "--gang-scheduler-name", "kube-batch",
+                                              "--object-storage", "mysql", "--region", "box"])
+    reg = CollectorRegistry()
+    op = manager.build_operator(args, metrics_registry=reg)
+    assert manager.CTRL_CONFIG.max_concurrent_reconciles == 1 and manager.CTRL_CONFIG.enable_gang_scheduling
+    assert set(op.reconcilers) == {"PyTorchJob", "TFJob", "XGBoostJob", "XDLJob"} and "pod" in op.persisters
+    manager.start_operator(op, args, metrics_registry=reg)
+    try:
+        srv = f"127.0.0.1:{port}"
+        assert kubedlctl.main(["-s", srv, "apply", "-f", f"{REF}/example/xdl/xdl_job_mnist.yaml"]) == 0
+        out = capsys.readouterr().out
+        # the ZooKeeper Service + Deployment in the same file are stored (nothing runs them here)
+        assert "xdljob/xdl-mnist-example applied" in out and "deployment/zk-0 applied" in out
+        for _ in range(100):
+            kubedlctl.main(["-s", srv, "get", "pods", "-n", "kubedl"])
+            if "xdl-mnist-example-worker-1" in capsys.readouterr().out:
+                break
+            time.sleep(0.05)
+        else:
+            raise AssertionError("pods never appeared")
+        assert kubedlctl.main(["-s", srv, "get", "xdljobs", "-n", "kubedl"]) == 0
+        table = capsys.readouterr().out
+        assert "NAME" in table and "STATE" in table and "FINISHED-TTL" in table and "3600" in table
+        kubedlctl.main(["-s", srv, "get", "xdljob", "xdl-mnist-example", "-n", "kubedl", "-o", "json"])
+        obj = json.loads(capsys.readouterr().out)
+        assert obj["kind"] == "XDLJob" and obj["spec"]["ttlSecondsAfterFinished"] == 3600
+        assert kubedlctl.main(["-s", srv, "describe", "xdljob", "xdl-mnist-example", "-n", "kubedl"]) == 0
+        assert "SuccessfulCreatePod" in capsys.readouterr().out
+        assert kubedlctl.main(["-s", srv, "get", "podgroups", "-n", "kubedl"]) == 0
+        assert "xdl-mnist-example" in capsys.readouterr().out
+        assert kubedlctl.main(["-s", srv, "delete", "xdljob", "xdl-mnist-example", "-n", "kubedl"]) == 0
+        with pytest.raises(SystemExit):
+            kubedlctl.main(["-s", srv, "get", "xdljob", "xdl-mnist-example", "-n", "kubedl"])
+        with pytest.raises(SystemExit):
+            kubedlctl.resolve_kind("nonsense")
+    finally:
+        op.stop()
+        manager.CTRL_CONFIG.enable_gang_scheduling = False
+        manager.CTRL_CONFIG.gang_scheduler_name = ""
+
+
+def test_leader_election_is_exclusive(tmp_path):
+    from kubedl_b200.runtime.manager import LeaderElector
+    lock = str(tmp_path / "leader.lock")
+    a, b = LeaderElector(lock, "a"), LeaderElector(lock, "b")
+    assert a.acquire(blocking=False) is True
+    assert b.acquire(blocking=False) is False
+    a.release()
+    assert b.acquire(blocking=False) is True
+    b.release()

@@ -1,0 +1,196 @@
+"""DMO converters, storage backends and persist controllers.
+Case names follow reference pkg/storage/dmo/converters/{pod,job,event}_test.go."""
+import json
+import os
+
+import pytest
+
+from cp_helpers import Cluster, tmpl
+from kubedl_b200.api import common as c
+from kubedl_b200.api import kinds as k
+from kubedl_b200.controllers import persist
+from kubedl_b200.plugins.storage import backends as B
+from kubedl_b200.plugins.storage import dmo
+
+TS = "2020-03-01T10:00:00Z"
+
+
+def _pod(phase=None, cstate=None, owner=True, rtype=True, containers=None, init=None, uid="pod-uid"):
+    m = {"name": "job-worker-0", "namespace": "ns", "uid": uid, "resourceVersion": "3", "creationTimestamp": TS,
+         "labels": {}}
+    if rtype:
+        m["labels"][c.REPLICA_TYPE_LABEL] = "worker"
+    if owner:
+        m["ownerReferences"] = [{"kind": "TFJob", "name": "job", "uid": "job-uid", "controller": True}]
+    pod = {"kind": "Pod", "metadata": m,
+           "spec": {"containers": containers or [{"name": "tensorflow", "image": "tf:1"}], "initContainers": init or []},
+           "status": {}}
+    if phase:
+        pod["status"] = {"phase": phase, "podIP": "10.0.0.1", "hostIP": "192.168.0.1",
+                         "containerStatuses": [{"name": "tensorflow", "state": cstate or {}}]}
+    return pod
+
+
+def test_pod_owner_reference_error_and_replica_type_error():
+    with pytest.raises(dmo.NoDependentOwner):
+        dmo.convert_pod_to_dmo_pod(_pod(owner=False), "tensorflow")
+    with pytest.raises(dmo.NoReplicaTypeLabel):
+        dmo.convert_pod_to_dmo_pod(_pod(rtype=False), "tensorflow")
+
+
+def test_pod_status_unknown_pending_running():
+    d = dmo.convert_pod_to_dmo_pod(_pod(), "tensorflow", region="cn")
+    assert d.status == "Unknown" and d.job_id == "job-uid" and d.replica_type == "worker"
+    assert d.deploy_region == "cn" and d.deleted == 0 and d.is_in_etcd == 1 and d.image == "tf:1"
+    d = dmo.convert_pod_to_dmo_pod(_pod("Pending"), "tensorflow")
+    assert d.status == "Pending" and d.gmt_started is None and d.pod_ip == "10.0.0.1" and d.host_ip == "192.168.0.1"
+    d = dmo.convert_pod_to_dmo_pod(_pod("Running", {"running": {"startedAt": "2020-03-01T10:00:05Z"}}), "tensorflow")
+    assert d.status == "Running" and d.gmt_started == "2020-03-01T10:00:05Z"
+    d = dmo.convert_pod_to_dmo_pod(_pod("Running", {}), "tensorflow")
+    assert d.gmt_started == TS                                   # falls back to creation time
+
+
+def test_pod_status_succeeded_failed_with_remark():
+    term = {"startedAt": "2020-03-01T10:00:05Z", "finishedAt": "2020-03-01T10:10:05Z", "exitCode": 137,
+            "reason": "OOMKilled", "message": "killed"}
+    d = dmo.convert_pod_to_dmo_pod(_pod("Succeeded", {"terminated": term}), "tensorflow")
+    assert (d.status, d.gmt_started, d.gmt_finished, d.remark) == \
+        ("Succeeded", "2020-03-01T10:00:05Z", "2020-03-01T10:10:05Z", None)
+    d = dmo.convert_pod_to_dmo_pod(_pod("Failed", {"terminated": term}), "tensorflow")
+    assert d.remark == "Reason: OOMKilled\nExitCode: 137\nMessage: killed"
+
+
+def test_pod_single_and_multiple_container_resources():
+    d = dmo.convert_pod_to_dmo_pod(_pod(containers=[{"name": "tensorflow", "image": "i", "resources": {
+        "requests": {"cpu": "1", "memory": "1Gi"}, "limits": {"cpu": "2", "memory": "2Gi"}}}]), "tensorflow")
+    assert json.loads(d.resources) == {"requests": {"cpu": "1", "memory": "1Gi"}, "limits": {"cpu": "2", "memory": "2Gi"}}
+    d = dmo.convert_pod_to_dmo_pod(_pod(
+        containers=[{"name": "a", "image": "a", "resources": {"requests": {"cpu": "1"}}},
+                    {"name": "tensorflow", "image": "main", "resources": {"requests": {"cpu": "500m", "memory": "1Gi"}}}],
+        init=[{"name": "init", "resources": {"requests": {"cpu": "3", "memory": "100Mi"}}}]), "tensorflow")
+    assert json.loads(d.resources) == {"requests": {"cpu": "3", "memory": "1Gi"}}   # max(init, sum containers)
+    assert d.image == "main"                                                          # default container's image
+
+
+def _job(kind="TFJob", conds=(), annotations=None, completion=None):
+    info = k.SCHEME.info(kind)
+    rt = "Worker" if "Worker" in info.replica_types else info.replica_types[-1]
+    job = k.new_job(kind, "j", "ns", {rt: {"replicas": 2, "template": tmpl(
+        info.default_container_name, resources={"requests": {"cpu": "1"}})}})
+    job["metadata"].update({"uid": "job-uid", "resourceVersion": "5", "creationTimestamp": TS})
+    if annotations:
+        job["metadata"]["annotations"] = annotations
+    job["status"] = {"conditions": [{"type": t, "status": "True"} for t in conds], "replicaStatuses": {}}
+    if completion:
+        job["status"]["completionTime"] = completion
+    return job
+
+
+def test_job_created_status_and_resources():
+    job = _job()
+    kind, specs, status = dmo.extract_typed_job_infos(job)
+    d = dmo.convert_job_to_dmo_job(job, kind, specs, status, "")
+    assert (d.status, d.kind, d.job_id, d.version, d.tenant, d.owner, d.deploy_region) == \
+        ("Created", "TFJob", "job-uid", "5", "", "", None)
+    assert json.loads(d.resources) == {"Worker": {"replicas": 2, "resources": {"requests": {"cpu": "1"}}}}
+
+
+def test_job_tenancy_region_annotation_and_succeeded_kinds():
+    ann = {c.ANNOTATION_TENANCY_INFO: json.dumps({"tenant": "t1", "user": "u1", "region": "r1"})}
+    job = _job(annotations=ann)
+    d = dmo.convert_job_to_dmo_job(job, *dmo.extract_typed_job_infos(job)[:2], job["status"], "")
+    assert (d.tenant, d.owner, d.deploy_region) == ("t1", "u1", "r1")
+    d = dmo.convert_job_to_dmo_job(job, "TFJob", {}, job["status"], "explicit")
+    assert d.deploy_region == "explicit"
+    for kind in ("XDLJob", "PyTorchJob", "XGBoostJob"):
+        j = _job(kind, conds=("Created", "Running", "Succeeded"), completion="2020-03-01T11:00:00Z")
+        kk, specs, status = dmo.extract_typed_job_infos(j)
+        d = dmo.convert_job_to_dmo_job(j, kk, specs, status, "")
+        assert (d.kind, d.status, d.gmt_finished) == (kind, "Succeeded", "2020-03-01T11:00:00Z")
+    with pytest.raises(ValueError):
+        dmo.extract_typed_job_infos({"kind": "Deployment", "metadata": {"name": "x"}})
+
+
+def test_event_conversion_keeps_involved_object():
+    ev = {"metadata": {"name": "e1", "namespace": "ns"}, "type": "Normal", "reason": "SuccessfulCreatePod",
+          "message": "Created pod: p", "count": 2, "firstTimestamp": TS, "lastTimestamp": TS,
+          "involvedObject": {"kind": "TFJob", "namespace": "ns", "name": "j", "uid": "job-uid"}}
+    d = dmo.convert_event_to_dmo_event(ev, "cn")
+    assert (d.kind, d.obj_name, d.obj_uid, d.count, d.region, d.reason) == \
+        ("TFJob", "j", "job-uid", 2, "cn", "SuccessfulCreatePod")
+
+
+def test_sql_backend_upsert_stop_delete_and_query(tmp_path):
+    b = B.SqlObjectBackend(str(tmp_path / "kubedl.db"))
+    b.initialize()
+    job = _job(conds=("Created",))
+    b.save_job(job, "TFJob", job["spec"]["tfReplicaSpecs"], job["status"], "cn")
+    assert b.get_job("ns", "j", "job-uid", "cn").status == "Created"
+    job["metadata"]["resourceVersion"] = "9"
+    job["status"]["conditions"].append({"type": "Succeeded"})
+    job["status"]["completionTime"] = "2020-03-01T11:00:00Z"
+    b.save_job(job, "TFJob", job["spec"]["tfReplicaSpecs"], job["status"], "cn")
+    job["metadata"]["resourceVersion"] = "4"                               # stale write is ignored
+    job["status"]["conditions"] = [{"type": "Running"}]
+    b.save_job(job, "TFJob", job["spec"]["tfReplicaSpecs"], job["status"], "cn")
+    got = b.get_job("ns", "j", "job-uid", "cn")
+    assert (got.status, got.version, got.gmt_finished) == ("Succeeded", "9", "2020-03-01T11:00:00Z")
+    pg = B.QueryPagination(page_num=1, page_size=10)
+    assert [j.name for j in b.list_jobs(B.Query(namespace="ns", status="Succeeded", pagination=pg))] == ["j"]
+    assert pg.count == 1 and b.list_jobs(B.Query(status="Failed")) == []
+    pod = _pod("Running", {"running": {"startedAt": TS}})
+    b.save_pod(pod, "tensorflow", "cn")
+    assert [p.name for p in b.list_pods("job-uid", "cn")] == ["job-worker-0"]
+    b.stop_pod("ns", "job-worker-0", "pod-uid")
+    p = b.list_pods("job-uid", "")[0]
+    assert p.status == "Stopped" and p.is_in_etcd == 0 and p.gmt_finished
+    b.stop_job("ns", "j", "job-uid", "cn")                                  # terminal status is sticky
+    b.delete_job("ns", "j", "job-uid", "cn")
+    got = b.get_job("ns", "j", "job-uid", "cn")
+    assert got.status == "Succeeded" and got.deleted == 1 and got.is_in_etcd == 0
+    assert b.list_jobs(B.Query(is_del=0)) == []
+    b.close()
+
+
+def test_registry():
+    B.register_storage_backends()
+    assert B.REGISTRY.get_object_backend("mysql").name() == "mysql"
+    assert B.REGISTRY.get_event_backend("aliyun-sls").name() == "aliyun-sls"
+    assert B.REGISTRY.get_object_backend("nope") is None
+
+
+def test_persist_controllers_full_loop(tmp_path):
+    cl = Cluster()
+    sql = B.SqlObjectBackend(":memory:")
+    ev = B.JsonlEventBackend(str(tmp_path / "events.jsonl"))
+    B.REGISTRY.add_object_backend(sql)
+    B.REGISTRY.add_event_backend(ev)
+    try:
+        ctrls = persist.setup_with_manager(cl.mgr, "mysql", "aliyun-sls", region="b200-box", workloads="*")
+        assert set(ctrls) == {"job/PyTorchJob", "job/TFJob", "job/XGBoostJob", "job/XDLJob", "pod", "event"}
+        job = cl.submit(k.new_job("TFJob", "tf", "ns", {"Worker": {"replicas": 2, "restartPolicy": "Never",
+                                                                    "template": tmpl("tensorflow")}}))
+        uid = job["metadata"]["uid"]
+        cl.kubelet.set_all("ns", "Running")
+        cl.settle()
+        row = sql.get_job("ns", "tf", uid, "b200-box")
+        assert row.status == "Running" and row.kind == "TFJob" and row.is_in_etcd == 1
+        pods = sql.list_pods(uid, "b200-box")
+        assert sorted(p.name for p in pods) == ["tf-worker-0", "tf-worker-1"] and all(p.status == "Running" for p in pods)
+        cl.kubelet.set_phase("ns", "tf-worker-0", "Succeeded")
+        cl.kubelet.set_phase("ns", "tf-worker-1", "Succeeded")
+        cl.settle()
+        assert sql.get_job("ns", "tf", uid, "b200-box").status == "Succeeded"
+        reasons = {e.reason for e in ev.list_event("ns", "tf")}
+        assert {"SuccessfulCreatePod", "SuccessfulCreateService", "JobSucceeded"} <= reasons
+        cl.api.delete("TFJob", "ns", "tf")
+        cl.settle()
+        row = sql.get_job("ns", "tf", uid, "b200-box")
+        assert row.deleted == 1 and row.is_in_etcd == 0 and row.status == "Succeeded"
+        assert all(p.is_in_etcd == 0 for p in sql.list_pods(uid, ""))
+        with pytest.raises(ValueError):
+            persist.setup_with_manager(cl.mgr, object_storage="no-such-backend")
+        assert persist.parse_id_name(persist.gen_id_name("u", "n")) == ("u", "n")
+    finally:
+        B.REGISTRY.remove_object_backend("mysql")
+        B.REGISTRY.remove_event_backend("aliyun-sls")

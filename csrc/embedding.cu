@@ -1,0 +1,205 @@
+// N4 / N5: sharded sparse-embedding exchange fused with the adjacent compute, over NVLink peer
+// memory (BASELINE.json config #5 "XDLJob-shaped sparse CTR model ...
+// embedding all-to-all dispatch/combine over NVSwitch").
+//
+// The table E[V, D] (fp32 master rows) is row-sharded: rank r owns rows [r*rows_per_rank, ...),
+// every shard lives in the symmetric heap, so any rank can address any row directly.
+//
+//   din_gather_attend (N4, forward "dispatch"): one warp per sample PULLS the user row, the
+//       candidate row and L history rows straight from their owners' shards (no id exchange, no
+//       vector all-to-all), computes DIN-style attention a = softmax(<h_i, c>/sqrt(D)), pools
+//       p = sum a_i h_i, and writes the MLP input [u, c, p, p*c] in bf16 — gather, pooling and
+//       concat in one pass.  History rows and weights are kept locally for the backward pass.
+//   din_scatter_update (N5, backward "combine"): one warp per sample back-propagates through the
+//       pooling, then pushes -lr * grad for every touched row to its owner with vectorised
+//       red.global.add.f32 over NVLink — scatter-add, duplicate coalescing (atomics) and the
+//       sparse SGD update in one pass; no gradient all-to-all and no dense gradient table.
+//
+// Stock equivalent: all_to_all_single(ids) + embedding_bag + all_to_all_single(vectors) forward,
+// all_to_all_single(grads) + index_add_ + sparse optimizer backward.  The reference operator only
+// provides TASK_NAME / TASK_INDEX / ZK_ADDR for XDL's own PS exchange (reference
+// controllers/xdl/xdljob_controller.go:191-217).
+#include "common.cuh"
+#include "../include/kubedl_b200.h"
+
+namespace kdl {
+
+constexpr int kD = 64;            // embedding width; lane l owns dims 2l, 2l+1
+constexpr int kWarpsPerBlock = 8;
+
+struct EmbParams {
+  float* shard[KDL_MAX_WORLD];    // peer-mapped shard base pointers
+  int world;
+  int64_t rows_per_rank;
+  const int64_t* user;            // [B]
+  const int64_t* cand;            // [B]
+  const int64_t* hist;            // [B, L], -1 = padding
+  int B, L;
+  bf16* x;                        // [B, 4*D] MLP input (fwd out)
+  bf16* hsave;                    // [B, L, D] gathered history rows (fwd out, bwd in)
+  float* asave;                   // [B, L] attention weights (fwd out, bwd in)
+  const bf16* dx;                 // [B, 4*D] gradient of the MLP input (bwd in)
+  float lr;
+};
+
+__device__ __forceinline__ const float* row_ptr(const EmbParams& p, int64_t id) {
+  const int owner = (int)(id / p.rows_per_rank);
+  return p.shard[owner] + (id - (int64_t)owner * p.rows_per_rank) * kD;
+}
+
+__device__ __forceinline__ float2 ld_row2(const float* row, int lane) {
+  float2 v;
+  asm volatile("ld.global.L1::no_allocate.v2.f32 {%0,%1}, [%2];"
+               : "=f"(v.x), "=f"(v.y)
+               : "l"(row + 2 * lane)
+               : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void red_add2(float* row, int lane, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(row + 2 * lane), "f"(a), "f"(b) : "memory");
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) din_gather_attend_kernel(EmbParams p) {
+  const int lane = threadIdx.x & 31;
+  const int s = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (s >= p.B) return;
+  const float inv_sqrt_d = rsqrtf((float)kD);
+  const float2 u = ld_row2(row_ptr(p, p.user[s]), lane);
+  const float2 c = ld_row2(row_ptr(p, p.cand[s]), lane);
+  const int64_t* hid = p.hist + (size_t)s * p.L;
+  bf16* hs = p.hsave + (size_t)s * p.L * kD;
+  float* as = p.asave + (size_t)s * p.L;
+
+  // pass 1: pull history rows (8 remote rows in flight per warp), scores -> smem-free online softmax
+  float m = -1e30f, denom = 0.f;
+  float2 acc = make_float2(0.f, 0.f);
+  constexpr int U = 8;
+  for (int i0 = 0; i0 < p.L; i0 += U) {
+    float2 h[U];
+    int64_t id[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      id[k] = (i0 + k < p.L) ? hid[i0 + k] : -1;
+      h[k] = id[k] >= 0 ? ld_row2(row_ptr(p, id[k]), lane) : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      if (i0 + k >= p.L) break;
+      *reinterpret_cast<__nv_bfloat162*>(hs + (size_t)(i0 + k) * kD + 2 * lane) = __floats2bfloat162_rn(h[k].x, h[k].y);
+      if (id[k] < 0) {              // padding: weight 0
+        if (lane == 0) as[i0 + k] = -1e30f;
+        continue;
+      }
+      float sc = warp_sum(h[k].x * c.x + h[k].y * c.y) * inv_sqrt_d;
+      if (lane == 0) as[i0 + k] = sc;
+      const float mn = fmaxf(m, sc);
+      const float corr = __expf(m - mn), e = __expf(sc - mn);
+      denom = denom * corr + e;
+      acc.x = acc.x * corr + e * h[k].x;
+      acc.y = acc.y * corr + e * h[k].y;
+      m = mn;
+    }
+  }
+  const float inv = denom > 0.f ? 1.f / denom : 0.f;
+  const float2 pl = make_float2(acc.x * inv, acc.y * inv);
+  __syncwarp();
+  // normalise the saved scores into weights
+  for (int i = lane; i < p.L; i += 32) {
+    float sc = as[i];
+    as[i] = sc > -1e29f ? __expf(sc - m) * inv : 0.f;
+  }
+  bf16* x = p.x + (size_t)s * 4 * kD;
+  *reinterpret_cast<__nv_bfloat162*>(x + 2 * lane) = __floats2bfloat162_rn(u.x, u.y);
+  *reinterpret_cast<__nv_bfloat162*>(x + kD + 2 * lane) = __floats2bfloat162_rn(c.x, c.y);
+  *reinterpret_cast<__nv_bfloat162*>(x + 2 * kD + 2 * lane) = __floats2bfloat162_rn(pl.x, pl.y);
+  *reinterpret_cast<__nv_bfloat162*>(x + 3 * kD + 2 * lane) = __floats2bfloat162_rn(pl.x * c.x, pl.y * c.y);
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) din_scatter_update_kernel(EmbParams p) {
+  const int lane = threadIdx.x & 31;
+  const int s = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (s >= p.B) return;
+  const float inv_sqrt_d = rsqrtf((float)kD);
+  const bf16* dx = p.dx + (size_t)s * 4 * kD;
+  auto ld2 = [&](const bf16* q) { return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(q + 2 * lane)); };
+  const float2 du = ld2(dx), dc0 = ld2(dx + kD), dp0 = ld2(dx + 2 * kD), dpc = ld2(dx + 3 * kD);
+  const int64_t cid = p.cand[s];
+  // the candidate vector exactly as the MLP saw it (the table row may already be receiving
+  // updates from other samples in this very launch)
+  const float2 c = ld2(p.x + (size_t)s * 4 * kD + kD);
+  const bf16* hs = p.hsave + (size_t)s * p.L * kD;
+  const float* as = p.asave + (size_t)s * p.L;
+  const int64_t* hid = p.hist + (size_t)s * p.L;
+  // recompute p = sum a_i h_i and t = sum_j a_j <dp, h_j>
+  float2 pl = make_float2(0.f, 0.f);
+  for (int i = 0; i < p.L; ++i) {
+    const float a = as[i];
+    const float2 h = ld2(hs + (size_t)i * kD);
+    pl.x += a * h.x; pl.y += a * h.y;
+  }
+  const float2 dp = make_float2(dp0.x + dpc.x * c.x, dp0.y + dpc.y * c.y);
+  float2 dc = make_float2(dc0.x + dpc.x * pl.x, dc0.y + dpc.y * pl.y);
+  const float t = warp_sum(dp.x * pl.x + dp.y * pl.y);   // sum_j a_j da_j  (da_j = <dp, h_j>)
+  const float nlr = -p.lr;
+  for (int i = 0; i < p.L; ++i) {
+    const int64_t id = hid[i];
+    if (id < 0) continue;
+    const float a = as[i];
+    const float2 h = ld2(hs + (size_t)i * kD);
+    const float da = warp_sum(dp.x * h.x + dp.y * h.y);
+    const float ds = a * (da - t) * inv_sqrt_d;
+    // dh_i = a_i dp + ds_i c ; dc += ds_i h_i
+    red_add2(const_cast<float*>(row_ptr(p, id)), lane, nlr * (a * dp.x + ds * c.x), nlr * (a * dp.y + ds * c.y));
+    dc.x += ds * h.x; dc.y += ds * h.y;
+  }
+  red_add2(const_cast<float*>(row_ptr(p, cid)), lane, nlr * dc.x, nlr * dc.y);
+  red_add2(const_cast<float*>(row_ptr(p, p.user[s])), lane, nlr * du.x, nlr * du.y);
+}
+
+}  // namespace kdl
+
+using namespace kdl;
+
+static int fill(EmbParams* p, void* const* shard_ptrs, int world, int64_t rows_per_rank, const int64_t* user,
+                const int64_t* cand, const int64_t* hist, int B, int L, int D) {
+  if (D != kD) {
+    kdl_set_error("embedding kernels are specialised for D=%d (got %d)", kD, D);
+    return KDL_ERR_UNSUPPORTED;
+  }
+  if (world < 1 || world > KDL_MAX_WORLD || B < 1 || L < 0 || rows_per_rank < 1) {
+    kdl_set_error("embedding: bad arguments world=%d B=%d L=%d rows_per_rank=%lld", world, B, L, (long long)rows_per_rank);
+    return KDL_ERR_ARG;
+  }
+  for (int r = 0; r < world; ++r) p->shard[r] = (float*)shard_ptrs[r];
+  p->world = world; p->rows_per_rank = rows_per_rank;
+  p->user = user; p->cand = cand; p->hist = hist; p->B = B; p->L = L;
+  return KDL_OK;
+}
+
+extern "C" int kdl_din_gather_attend(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+                                     const int64_t* user, const int64_t* cand, const int64_t* hist, int B,
+                                     int L, int D, void* x_bf16, void* hsave_bf16, float* asave,
+                                     cudaStream_t stream) {
+  EmbParams p = {};
+  int rc = fill(&p, shard_ptrs, world, rows_per_rank, user, cand, hist, B, L, D);
+  if (rc) return rc;
+  p.x = (bf16*)x_bf16; p.hsave = (bf16*)hsave_bf16; p.asave = asave;
+  din_gather_attend_kernel<<<(B + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+                                      const int64_t* user, const int64_t* cand, const int64_t* hist, int B,
+                                      int L, int D, const void* x_bf16, const void* dx_bf16,
+                                      const void* hsave_bf16, const float* asave, float lr,
+                                      cudaStream_t stream) {
+  EmbParams p = {};
+  int rc = fill(&p, shard_ptrs, world, rows_per_rank, user, cand, hist, B, L, D);
+  if (rc) return rc;
+  p.x = (bf16*)x_bf16; p.dx = (const bf16*)dx_bf16; p.hsave = (bf16*)hsave_bf16; p.asave = const_cast<float*>(asave); p.lr = lr;
+  din_scatter_update_kernel<<<(B + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}

@@ -1,0 +1,157 @@
+"""DIN-style sparse CTR model over a row-sharded embedding table (BASELINE.json config #5:
+"XDLJob-shaped sparse CTR model (10M-row embedding, DIN-style) with embedding all-to-all
+dispatch/combine over NVSwitch at 8 GPUs").
+
+Per sample: user id, candidate item id and L history item ids index ONE table E[V, 64] (fp32
+rows, sharded by row range over the ranks, each shard in the symmetric heap).  Forward =
+`kdl_din_gather_attend` (remote pull + attention pooling + concat, kernel N4) -> MLP 256-512-256-1
+on the tcgen05 GEMM -> sigmoid BCE.  Backward = MLP backward on the GEMM (nn / tn variants) ->
+`kdl_din_scatter_update` (pooling backward + remote red.add sparse-SGD, kernel N5) -> fused
+all-reduce of the dense MLP gradients (which is also the cross-rank barrier that orders this
+step's table updates before the next step's reads) -> fused SGD.
+
+The XDLJob controller supplies TASK_NAME/TASK_INDEX (reference
+controllers/xdl/xdljob_controller.go:191-217); XDL's own PS/worker exchange over ZooKeeper is what
+this replaces.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from ..ops import lib as L
+from ..ops import nn as K
+from ..ops.gemm import Gemm
+from .arena import ParamArena
+
+L.register_signatures({
+    "kdl_din_gather_attend": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "kdl_din_scatter_update": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_float, C.c_void_p]),
+})
+
+D = 64
+
+
+class DINModel:
+    def __init__(self, vocab: int = 10_000_000, hist_len: int = 62, hidden=(512, 256), lr: float = 0.05,
+                 emb_lr: Optional[float] = None, heap=None, group=None, seed: int = 0, device=None):
+        import torch.distributed as dist
+        self.lib = L.lib()
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.dev = device or torch.device("cuda", torch.cuda.current_device())
+        self.vocab, self.L, self.lr = vocab, hist_len, lr
+        self.emb_lr = lr if emb_lr is None else emb_lr
+        self.rows_per_rank = (vocab + self.world - 1) // self.world
+        shard_bytes = self.rows_per_rank * D * 4
+        if heap is None:
+            from ..parallel.symm import SymmetricHeap
+            heap = SymmetricHeap(shard_bytes + (64 << 20), group=group)
+        self.heap = heap
+        self.shard_off, self.shard = heap.alloc_tensor((self.rows_per_rank, D), torch.float32)
+        g = torch.Generator(device=self.dev).manual_seed(seed * 1000 + self.rank)
+        self.shard.copy_(torch.randn(self.rows_per_rank, D, device=self.dev, generator=g) * 0.05)
+        self._shard_tab = heap.ptr_table(self.shard_off)
+        # dense part
+        self.arena = ParamArena()
+        h1, h2 = hidden
+        self.dims = (4 * D, h1, h2, 8)     # the scalar output is padded to 8 columns for the GEMM
+        for i, (k_in, k_out) in enumerate(zip(self.dims[:-1], self.dims[1:]), start=1):
+            self.arena.declare(f"w{i}", (k_out, k_in), decay=True, init="kaiming", fan=k_in)
+            self.arena.declare(f"b{i}", (k_out,), decay=False, init="zeros")
+        order = [n for i in (3, 2, 1) for n in (f"w{i}", f"b{i}")]
+        self.arena.finalize(self.dev, order, heap=heap, seed=seed)   # same seed -> same MLP on every rank
+        with torch.no_grad():
+            self.arena.w32("w3")[1:].zero_()
+            self.arena.p16.copy_(self.arena.p32)
+        self.gemm = Gemm(self.dev)
+        self.ar = None
+        if self.world > 1:
+            from ..parallel.collectives import FusedAllReduce
+            self.ar = FusedAllReduce(heap)
+            dist.barrier(group=group)
+        self.saved = None
+
+    # ------------------------------------------------------------------ forward / backward
+    def forward(self, user: torch.Tensor, cand: torch.Tensor, hist: torch.Tensor) -> torch.Tensor:
+        B = user.numel()
+        x = torch.empty(B, 4 * D, dtype=torch.bfloat16, device=self.dev)
+        hs = torch.empty(B, self.L, D, dtype=torch.bfloat16, device=self.dev)
+        aw = torch.empty(B, self.L, dtype=torch.float32, device=self.dev)
+        L.check(self.lib.kdl_din_gather_attend(self._shard_tab, self.world, self.rows_per_rank, user.data_ptr(),
+                                               cand.data_ptr(), hist.data_ptr(), B, self.L, D, x.data_ptr(),
+                                               hs.data_ptr(), aw.data_ptr(), L.stream_ptr()), "kdl_din_gather_attend")
+        L.count(1)
+        a = self.arena
+        h1 = self.gemm.nt(x, a.w16("w1"), bias=a.w16("b1"), relu=True)
+        h2 = self.gemm.nt(h1, a.w16("w2"), bias=a.w16("b2"), relu=True)
+        z = self.gemm.nt(h2, a.w16("w3"), bias=a.w16("b3"))
+        self.saved = (user, cand, hist, x, hs, aw, h1, h2)
+        return z[:, 0].float()
+
+    def backward(self, dlogit: torch.Tensor) -> None:
+        user, cand, hist, x, hs, aw, h1, h2 = self.saved
+        self.saved = None
+        a, B = self.arena, user.numel()
+        dz = torch.zeros(B, 8, dtype=torch.bfloat16, device=self.dev)
+        dz[:, 0] = dlogit.to(torch.bfloat16)
+        self.gemm.tn(dz, h2, out=a.grad("w3"))
+        torch.sum(dz.float(), 0, out=None).to(torch.bfloat16, copy=False)
+        a.grad("b3").copy_(dz.float().sum(0))
+        dh2 = self.gemm.nn(dz, a.w16("w3")) * (h2 > 0)
+        self.gemm.tn(dh2, h1, out=a.grad("w2"))
+        a.grad("b2").copy_(dh2.float().sum(0))
+        dh1 = self.gemm.nn(dh2, a.w16("w2")) * (h1 > 0)
+        self.gemm.tn(dh1, x, out=a.grad("w1"))
+        a.grad("b1").copy_(dh1.float().sum(0))
+        dx = self.gemm.nn(dh1, a.w16("w1"))
+        a.grad("w3")[1:].zero_()            # padded output columns carry no parameters
+        a.grad("b3")[1:].zero_()
+        L.check(self.lib.kdl_din_scatter_update(self._shard_tab, self.world, self.rows_per_rank, user.data_ptr(),
+                                                cand.data_ptr(), hist.data_ptr(), B, self.L, D, x.data_ptr(),
+                                                dx.data_ptr(), hs.data_ptr(), aw.data_ptr(), self.emb_lr,
+                                                L.stream_ptr()), "kdl_din_scatter_update")
+        L.count(1)
+
+    def step(self, user, cand, hist, label) -> torch.Tensor:
+        logit = self.forward(user, cand, hist)
+        loss = torch.nn.functional.binary_cross_entropy_with_logits(logit, label)
+        dlogit = (torch.sigmoid(logit) - label) / label.numel()
+        self.backward(dlogit)
+        a = self.arena
+        if self.ar is not None:
+            # dense-gradient all-reduce; its entry barrier also orders every rank's table updates
+            # of this step before anybody's gathers of the next step
+            self.ar(a.g16_off, a.total, torch.bfloat16)
+        K.sgd_momentum(a.p32, a.mom, a.g16, a.p16, self.lr, 0.0, 0.0, wd_count=a.wd_count)
+        return loss
+
+    # ------------------------------------------------------------------ checkpoint (per-rank shard)
+    def state_dict(self) -> dict:
+        return {"shard": self.shard.detach().cpu(), "arena": self.arena.state_dict(), "rank": self.rank,
+                "rows_per_rank": self.rows_per_rank}
+
+    def load_state_dict(self, sd: dict) -> None:
+        assert sd["rank"] == self.rank and sd["rows_per_rank"] == self.rows_per_rank
+        self.shard.copy_(sd["shard"])
+        self.arena.load_state_dict(sd["arena"])
+
+
+def synthetic_batch(B: int, L: int, vocab: int, device, seed: int = 0, zipf: bool = True):
+    """Skewed ids (hot items), variable-length histories padded with -1, a learnable label."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    def ids(shape):
+        if zipf:
+            u = torch.rand(shape, device=device, generator=g)
+            return (u.pow(3) * vocab).long().clamp_(0, vocab - 1)
+        return torch.randint(0, vocab, shape, device=device, generator=g)
+    user, cand, hist = ids((B,)), ids((B,)), ids((B, L))
+    lens = torch.randint(1, L + 1, (B, 1), device=device, generator=g)
+    hist = torch.where(torch.arange(L, device=device)[None, :] < lens, hist, torch.full_like(hist, -1))
+    label = (cand % 2).float()          # learnable through the candidate's embedding row
+    return user, cand, hist, label

@@ -298,6 +298,43 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const bf16* __restrict
   }
 }
 
+// Stem im2col fused with the input normalisation: uint8 NHWC image -> bf16 patch matrix
+// [N*OH*OW, KP] for the 7x7 stride-2 pad-3 convolution, column k = (kh*7 + kw)*3 + c (the order of
+// the NHWC weight [Cout, 7, 7, 3]), columns 147..KP-1 zero.  The stem then runs as a plain GEMM on
+// the tcgen05 kernel (K = 147 is far too thin for an implicit-GEMM pipeline to pay off, and the
+// patch matrix is written once and reused by wgrad).  One thread = one 16-byte output vector.
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const uint8_t* __restrict__ img,
+                                                          bf16* __restrict__ out, int N, int H, int W,
+                                                          int OH, int OW, int KP, float m0, float m1,
+                                                          float m2, float s0, float s1, float s2) {
+  const int vpr = KP / 8;
+  const int64_t total = (int64_t)N * OH * OW * vpr;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  const float mean[3] = {m0, m1, m2}, istd[3] = {s0, s1, s2};
+  const float k255 = 1.f / 255.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
+    const int v = (int)(i % vpr);
+    int64_t pix = i / vpr;
+    const int ow = (int)(pix % OW); pix /= OW;
+    const int oh = (int)(pix % OH);
+    const int n = (int)(pix / OH);
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = v * 8 + j;
+      float val = 0.f;
+      if (k < 147) {
+        const int kh = k / 21, r = k - kh * 21, kw = r / 3, c = r - kw * 3;
+        const int ih = oh * 2 - 3 + kh, iw = ow * 2 - 3 + kw;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W)
+          val = ((float)img[(((int64_t)n * H + ih) * W + iw) * 3 + c] * k255 - mean[c]) * istd[c];
+      }
+      f[j] = val;
+    }
+    *reinterpret_cast<uint4*>(out + i * 8) = pack8(f);
+  }
+}
+
 static int grid_for(int64_t n, int per_block) {
   int64_t g = (n + per_block - 1) / per_block;
   if (g > 148 * 16) g = 148 * 16;
@@ -416,6 +453,21 @@ extern "C" int kdl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C,
   int64_t total = (int64_t)N * HW * (C / 8);
   avgpool_bwd_kernel<<<grid_for(total, 256), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, N, HW,
                                                                C);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_stem_im2col_u8(const void* img_u8, void* patches_bf16, int N, int H, int W, int KP,
+                                  const float* mean3, const float* std3, cudaStream_t stream) {
+  if (KP < 152 || (KP % 8) != 0) {
+    kdl_set_error("stem_im2col: KP must be a multiple of 8 and >= 152");
+    return KDL_ERR_ARG;
+  }
+  const int OH = (H + 6 - 7) / 2 + 1, OW = (W + 6 - 7) / 2 + 1;
+  const int64_t total = (int64_t)N * OH * OW * (KP / 8);
+  stem_im2col_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
+      (const uint8_t*)img_u8, (bf16*)patches_bf16, N, H, W, OH, OW, KP, mean3[0], mean3[1], mean3[2],
+      1.f / std3[0], 1.f / std3[1], 1.f / std3[2]);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }

@@ -66,6 +66,10 @@ int kdl_bn_fwd_static_scratch(const void* x, const void* res, void* y, int64_t M
 /* ---- N8: other memory-bound fused ops of the DDP worker --------------------------------- */
 int kdl_u8_normalize(const void* in_u8, void* out_bf16, int64_t npix, int cpad,
                      const float* mean3_host, const float* std3_host, cudaStream_t stream);
+/* uint8 NHWC image -> normalised bf16 im2col patches [N*OH*OW, KP] of the 7x7/s2/p3 stem
+ * convolution (column = (kh*7+kw)*3+c, zero padded to KP >= 152), so the stem runs on kdl_gemm_bf16. */
+int kdl_stem_im2col_u8(const void* img_u8, void* patches_bf16, int N, int H, int W, int KP,
+                       const float* mean3_host, const float* std3_host, cudaStream_t stream);
 size_t kdl_softmax_xent_workspace_bytes(int B);
 int kdl_softmax_xent(const void* logits, int logits_is_fp32, const int64_t* labels,
                      void* dlogits_bf16, float* loss_out, int B, int V, int ldv, float grad_scale,
@@ -80,6 +84,51 @@ int kdl_maxpool3x3s2_bwd(const void* dy, const void* idx_u8, void* dx, int N, in
                          cudaStream_t stream);
 int kdl_avgpool_fwd(const void* x, void* y, int N, int HW, int C, cudaStream_t stream);
 int kdl_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t stream);
+
+/* ---- N6: bf16 GEMM on tcgen05 tensor cores (TMEM accumulators, TMA loads/stores) -----------
+ * C[M,N] = op(A) op(B) (+bias[N]) (+addend[M,N]) (ReLU).  a_mn_major=0: A is [M, lda] (K
+ * contiguous); 1: A is [K, lda] (M contiguous).  Same for B with N.  nt = forward of a 1x1
+ * convolution / linear layer, nn = dgrad, tn = wgrad (split over K; `scratch` of
+ * kdl_gemm_scratch_bytes() holds the fp32 partial tiles, reduced in a fixed order).  Replaces the
+ * cuBLAS/cuDNN calls of the stock worker image (reference
+ * example/pytorch/pytorch_job_mnist_mpi.yaml:15). */
+int kdl_gemm_splits(int M, int N, int K, int requested);
+size_t kdl_gemm_scratch_bytes(int M, int N, int K, int split_k);
+int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                  int b_mn_major, int lda, int ldb, int ldc, const void* bias_bf16,
+                  const void* addend_bf16, int relu, int split_k, void* scratch, size_t scratch_bytes,
+                  cudaStream_t stream);
+
+/* ---- N3: histogram GBDT, histogram build fused with the cross-GPU reduction ---------------
+ * Replaces XGBoost gpu_hist + ncclAllReduce of histograms, for which the reference only injects
+ * the tracker address (reference controllers/xgboost/pod.go:106-152).  peer_local / flag_ptrs are
+ * HOST arrays of `world` device pointers into the symmetric heap (NULL when world == 1). */
+int kdl_gbdt_grad_logistic(const float* pred, const float* label, void* gh, int64_t n,
+                           cudaStream_t stream);
+size_t kdl_gbdt_hist_bytes(int nodes, int F);
+int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, const void* gh, const int32_t* ridx,
+                            const int32_t* seg, const int32_t* build, int nbuild, int64_t n_rows_hint,
+                            void* local_hist, void* out_hist, void* node_done, void* const* peer_local,
+                            void* const* flag_ptrs, int world, int rank, int max_nodes, unsigned epoch,
+                            void* status, unsigned long long timeout_ns, cudaStream_t stream);
+int kdl_gbdt_split_eval(const void* hist, int nodes, int F, float lambda, float gamma,
+                        float min_child_weight, float* out8, cudaStream_t stream);
+int kdl_gbdt_apply_split(int32_t* node_of_row, const void* bins, int fstride, const float* splits8,
+                         int64_t n, cudaStream_t stream);
+int kdl_gbdt_update_pred(float* pred, const int32_t* node_of_row, const float* leaf_value, int64_t n,
+                         cudaStream_t stream);
+
+/* ---- N4/N5: sharded embedding gather (+DIN attention pooling) and scatter-add SGD update ----
+ * over NVLink peer memory; replaces all_to_all_single + embedding_bag / index_add_ of a stock
+ * PyTorch worker (XDL's PS exchange; reference controllers/xdl/xdljob_controller.go:191-217).
+ * shard_ptrs: HOST array of `world` device pointers to the fp32 row shards [rows_per_rank, 64]. */
+int kdl_din_gather_attend(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+                          const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L,
+                          int D, void* x_bf16, void* hsave_bf16, float* asave, cudaStream_t stream);
+int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+                           const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L,
+                           int D, const void* x_bf16, const void* dx_bf16, const void* hsave_bf16,
+                           const float* asave, float lr, cudaStream_t stream);
 
 /* ---- N1/N2: fused gradient-bucket all-reduce over NVLink peer memory ---------------------
  * Replaces ncclAllReduce + div_ + cast of torch DDP, for which the reference only injects

@@ -57,19 +57,27 @@ class Conv:
                                        [self.pad] * 2, [1, 1], False, [0, 0], 1)
         return _nhwc(y)
 
-    def bwd(self, dy: torch.Tensor, x: torch.Tensor, need_dx: bool = True) -> Optional[torch.Tensor]:
+    def bwd(self, dy: torch.Tensor, x: torch.Tensor, need_dx: bool = True,
+            addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """Returns dx (+ addend, the gradient arriving over the residual branch — fused into the
+        dgrad GEMM epilogue on the tcgen05 path)."""
         net = self.net
         if self.is_gemm and net.gemm is not None:
             N, H, W, Cin = x.shape
             dy2, x2 = dy.view(-1, self.cout), x.view(-1, Cin)
-            # dW[Cout, Cin] = dy^T x ; dx[M, Cin] = dy W
+            # dW[Cout, Cin] = dy^T x ; dx[M, Cin] = dy W (+ addend)
             net.gemm.tn(dy2, x2, out=net.arena.grad(self.name).view(self.cout, Cin))
-            dx = net.gemm.nn(dy2, self.w.view(self.cout, Cin)).view(N, H, W, Cin) if need_dx else None
+            dx = None
+            if need_dx:
+                dx = net.gemm.nn(dy2, self.w.view(self.cout, Cin),
+                                 addend=None if addend is None else addend.view(-1, Cin)).view(N, H, W, Cin)
         else:
             dxn, dw, _ = _conv_bwd(_nchw(dy), _nchw(x), self.w_nchw, None, [self.stride] * 2,
                                    [self.pad] * 2, [1, 1], False, [0, 0], 1, [need_dx, True, False])
             self.gw.copy_(dw)
             dx = _nhwc(dxn) if need_dx else None
+            if dx is not None and addend is not None:
+                K.add_(dx, addend)
         net.reducer_ready(self.g_end)
         return dx
 
@@ -120,11 +128,13 @@ class Bottleneck:
         return ms
 
     def backward_param_order(self) -> List[str]:
+        # must match the order in which bwd() produces the weight gradients: conv3, conv2,
+        # downsample (if any), conv1 — the reducer treats the arena as a growing ready prefix
         names = [self.c3.name, self.b3.name + ".weight", self.b3.name + ".bias",
-                 self.c2.name, self.b2.name + ".weight", self.b2.name + ".bias",
-                 self.c1.name, self.b1.name + ".weight", self.b1.name + ".bias"]
+                 self.c2.name, self.b2.name + ".weight", self.b2.name + ".bias"]
         if self.cd is not None:
             names += [self.cd.name, self.bd.name + ".weight", self.bd.name + ".bias"]
+        names += [self.c1.name, self.b1.name + ".weight", self.b1.name + ".bias"]
         return names
 
     def fwd(self, x, train=True):
@@ -152,13 +162,12 @@ class Bottleneck:
         dc2 = self.b2.bwd(da2, c2, a2)
         da1 = self.c2.bwd(dc2, a1)
         dc1 = self.b1.bwd(da1, c1, a1)
-        dx = self.c1.bwd(dc1, x)
         if self.cd is not None:
             dcd = self.bd.bwd(dres, cdo, None)
             dx2 = self.cd.bwd(dcd, x)
-            K.add_(dx, dx2)
+            dx = self.c1.bwd(dc1, x, addend=dx2)
         else:
-            K.add_(dx, dres)
+            dx = self.c1.bwd(dc1, x, addend=dres)
         return dx
 
 
@@ -205,8 +214,24 @@ class ResNet50:
             self.reducer.ready_upto(end_elem)
 
     # ------------------------------------------------------------------ forward
-    def forward(self, x_bf16_nhwc: torch.Tensor, train: bool = True) -> torch.Tensor:
-        c = self.stem.fwd(x_bf16_nhwc)
+    def _stem_w_padded(self) -> torch.Tensor:
+        w = torch.zeros(64, K.STEM_KP, dtype=torch.bfloat16, device=self.device)
+        w[:, :147] = self.stem.w.view(64, 147)
+        return w
+
+    def forward(self, x, train: bool = True) -> torch.Tensor:
+        """x: normalised bf16 NHWC image, or (tcgen05 path) the raw uint8 NHWC image — then the stem
+        is im2col (fused with the normalisation) + GEMM instead of cuDNN's 3-channel convolution."""
+        stem_gemm = x.dtype == torch.uint8
+        if stem_gemm:
+            assert self.gemm is not None
+            N, H, W, _ = x.shape
+            patches = K.stem_im2col(x)
+            c = self.gemm.nt(patches, self._stem_w_padded()).view(N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, 64)
+            x_bf16_nhwc = patches
+        else:
+            x_bf16_nhwc = x
+            c = self.stem.fwd(x_bf16_nhwc)
         a = self.stem_bn.fwd(c)
         p, idx = K.maxpool3x3s2_fwd(a)
         h = p
@@ -242,12 +267,17 @@ class ResNet50:
             dh = b.bwd(dh)
         da = K.maxpool3x3s2_bwd(dh, idx, a.shape)
         dc = self.stem_bn.bwd(da, c, a)
-        self.stem.bwd(dc, x, need_dx=False)
+        if x.dim() == 2:   # im2col patches: stem wgrad is one tn GEMM (split over the 3.2 M rows)
+            gw = self.gemm.tn(dc.view(-1, 64), x)
+            self.arena.grad("conv1").view(64, 147).copy_(gw[:, :147])
+            self.reducer_ready(self.stem.g_end)
+        else:
+            self.stem.bwd(dc, x, need_dx=False)
         if self.reducer is not None:
             self.reducer.finish()
 
     def loss_and_grad(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        x = K.u8_normalize(images_u8, cpad=3)
+        x = images_u8 if self.gemm is not None else K.u8_normalize(images_u8, cpad=3)
         logits = self.forward(x, train=True)
         loss, dlogits = K.softmax_xent(logits, labels, V=self.num_classes)
         self.backward(dlogits)

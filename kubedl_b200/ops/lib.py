@@ -32,6 +32,8 @@ _SIGS = {
                            c_void_p]),
     "kdl_u8_normalize": (c_int, [c_void_p, c_void_p, c_int64, c_int, C.POINTER(c_float),
                                  C.POINTER(c_float), c_void_p]),
+    "kdl_stem_im2col_u8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, C.POINTER(c_float),
+                                   C.POINTER(c_float), c_void_p]),
     "kdl_softmax_xent_workspace_bytes": (c_size_t, [c_int]),
     "kdl_softmax_xent": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                  c_int, c_float, c_void_p, c_size_t, c_void_p]),

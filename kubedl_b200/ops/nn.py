@@ -98,6 +98,22 @@ def u8_normalize(img_u8: torch.Tensor, cpad: int = 3, out: Optional[torch.Tensor
     return out
 
 
+STEM_KP = 152   # 7*7*3 = 147 im2col columns padded to a 16-byte multiple
+
+
+def stem_im2col(img_u8: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 NHWC [N,H,W,3] -> normalised bf16 patches [N*OH*OW, 152] of the 7x7/s2/p3 stem conv."""
+    assert img_u8.dtype == torch.uint8 and img_u8.shape[-1] == 3 and img_u8.is_contiguous()
+    N, H, W, _ = img_u8.shape
+    OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    if out is None:
+        out = torch.empty(N * OH * OW, STEM_KP, dtype=torch.bfloat16, device=img_u8.device)
+    L.check(L.lib().kdl_stem_im2col_u8(img_u8.data_ptr(), out.data_ptr(), N, H, W, STEM_KP, _IMAGENET_MEAN,
+                                       _IMAGENET_STD, L.stream_ptr()), "kdl_stem_im2col_u8")
+    L.count(1)
+    return out
+
+
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, V: Optional[int] = None,
                  grad_scale: Optional[float] = None, dlogits: Optional[torch.Tensor] = None,
                  loss: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:

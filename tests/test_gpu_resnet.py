@@ -44,7 +44,8 @@ def test_resnet50_step_matches_torchvision(cuda, use_gemm):
     lab = torch.randint(0, 1000, (B,), device=cuda)
 
     x = K.u8_normalize(img)
-    logits = net.forward(x, train=True)
+    # tcgen05 path: the stem takes the raw uint8 image (fused normalise + im2col + GEMM)
+    logits = net.forward(img if use_gemm else x, train=True)
     loss, dlogits = K.softmax_xent(logits, lab, V=1000)
     net.backward(dlogits)
     torch.cuda.synchronize()
@@ -145,3 +146,28 @@ def test_bottleneck_block_fwd_bwd(cuda, block, shape, use_gemm):
             go = go.permute(0, 3, 1, 2)
         c = _cos(go, p.grad)
         assert c > 0.99, f"{name}: cosine {c}"
+
+
+def test_stem_im2col_gemm_matches_conv2d(cuda):
+    """uint8 image -> fused normalise+im2col -> tcgen05 GEMM  ==  conv2d(normalised image, 7x7/s2/p3);
+    and the wgrad GEMM over the same patches == conv2d weight gradient."""
+    from kubedl_b200.ops import nn as K
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(0)
+    N, S = 4, 64
+    img = torch.randint(0, 256, (N, S, S, 3), dtype=torch.uint8, device=cuda)
+    w = (torch.randn(64, 7, 7, 3, device=cuda) * 0.05).bfloat16()
+    patches = K.stem_im2col(img)
+    assert patches.shape == (N * 32 * 32, 152) and float(patches[:, 147:].abs().max()) == 0.0
+    wp = torch.zeros(64, 152, dtype=torch.bfloat16, device=cuda)
+    wp[:, :147] = w.view(64, 147)
+    y = g.nt(patches, wp).view(N, 32, 32, 64)
+    xn = K.u8_normalize(img).float().permute(0, 3, 1, 2)
+    wr = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xn, wr, stride=2, padding=3)
+    torch.testing.assert_close(y.float(), yr.permute(0, 2, 3, 1), atol=5e-2, rtol=3e-2)
+    dy = torch.randn_like(y)
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    gw = g.tn(dy.view(-1, 64), patches)[:, :147].view(64, 7, 7, 3)
+    assert _cos(gw, wr.grad.permute(0, 2, 3, 1)) > 0.999

@@ -1,0 +1,103 @@
+"""Job launch-delay benchmark (second half of BASELINE.json's metric: "job launch delay p50").
+
+Submits N jobs of a kind sequentially to an embedded operator + node agent and reads the raw
+observations behind `kubedl_jobs_first_pod_launch_delay_seconds` and
+`kubedl_jobs_all_pods_launch_delay_seconds` (definitions: reference pkg/metrics/job_metrics.go:139-194,
+docs/metrics.md:16-17), plus time-to-Succeeded.  Pods are real local processes.
+
+    python -m kubedl_b200.bench.launch_delay --jobs 30 --replicas 8
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import statistics
+import sys
+import time
+
+from prometheus_client import CollectorRegistry
+
+from ..api import kinds as k
+from ..cmd import manager as M
+from ..utils import status as st
+
+
+def _pct(xs, q):
+    xs = sorted(xs)
+    if not xs:
+        return float("nan")
+    i = min(len(xs) - 1, max(0, int(round(q * (len(xs) - 1)))))
+    return xs[i]
+
+
+def _job(kind: str, name: str, replicas: int, seconds: float) -> dict:
+    cmd = [sys.executable, "-c", f"import time; time.sleep({seconds})"]
+    if kind == "PyTorchJob":
+        t = lambda: {"spec": {"containers": [{"name": "pytorch", "image": "python", "command": cmd}]}}
+        return k.new_job(kind, name, "bench", {"Master": {"replicas": 1, "restartPolicy": "Never", "template": t()},
+                                               "Worker": {"replicas": replicas - 1, "restartPolicy": "Never", "template": t()}},
+                         cleanPodPolicy="All")
+    if kind == "TFJob":
+        t = lambda: {"spec": {"containers": [{"name": "tensorflow", "image": "kubedl/tf-mnist-with-summaries:1.0",
+                                              "env": [{"name": "KUBEDL_TF_TRAIN_SECONDS", "value": str(seconds)}]}]}}
+        return k.new_job(kind, name, "bench", {"PS": {"replicas": 1, "restartPolicy": "Never", "template": t()},
+                                               "Worker": {"replicas": replicas - 1, "restartPolicy": "Never", "template": t()}},
+                         cleanPodPolicy="All")
+    if kind == "XGBoostJob":
+        t = lambda: {"spec": {"containers": [{"name": "xgboostjob", "image": "python", "command": cmd}]}}
+        return k.new_job(kind, name, "bench", {"Master": {"replicas": 1, "restartPolicy": "Never", "template": t()},
+                                               "Worker": {"replicas": replicas - 1, "restartPolicy": "Never", "template": t()}},
+                         cleanPodPolicy="All", ttlSecondsAfterFinished=3600)
+    t = lambda: {"spec": {"containers": [{"name": "xdl", "image": "python", "command": cmd}]}}
+    return k.new_job(kind, name, "bench", {"Worker": {"replicas": replicas, "restartPolicy": "Never", "template": t()}},
+                     cleanPodPolicy="All")
+
+
+def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1) -> dict:
+    args = M.build_parser().parse_args(["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0",
+                                        "--workloads", "*", "--gpus", "0", "--max-reconciles", str(max_reconciles)])
+    reg = CollectorRegistry()
+    op = M.build_operator(args, metrics_registry=reg)
+    M.start_operator(op, args, metrics_registry=reg)
+    done_times = []
+    try:
+        for i in range(jobs):
+            name = f"{kind.lower()}-{i}"
+            t0 = time.time()
+            op.mgr.api.create(_job(kind, name, replicas, seconds))
+            while True:
+                s = op.mgr.api.get(kind, "bench", name).get("status", {})
+                if st.is_succeeded(s) or st.is_failed(s):
+                    break
+                if time.time() - t0 > 120:
+                    raise RuntimeError(f"{name} did not finish: {s}")
+                time.sleep(0.002)
+            done_times.append(time.time() - t0)
+            op.mgr.api.delete(kind, "bench", name)
+        m = op.reconcilers[kind].metrics
+        first = [v for _, v in m.launch_delays["first_pod"]]
+        allp = [v for _, v in m.launch_delays["all_pods"]]
+        creates = sum(1 for verb, kd, _ in op.mgr.api.request_log if verb == "create" and kd in ("Pod", "Service"))
+        return {"kind": kind, "jobs": jobs, "replicas": replicas, "worker_seconds": seconds,
+                "first_pod_ms": {"p50": 1e3 * _pct(first, 0.5), "p90": 1e3 * _pct(first, 0.9), "n": len(first)},
+                "all_pods_ms": {"p50": 1e3 * _pct(allp, 0.5), "p90": 1e3 * _pct(allp, 0.9), "n": len(allp)},
+                "time_to_succeeded_ms": {"p50": 1e3 * _pct(done_times, 0.5), "p90": 1e3 * _pct(done_times, 0.9)},
+                "api_creates_per_job": creates / jobs}
+    finally:
+        op.stop()
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--jobs", type=int, default=30)
+    ap.add_argument("--replicas", type=int, default=8)
+    ap.add_argument("--seconds", type=float, default=0.2)
+    ap.add_argument("--kinds", default="PyTorchJob,TFJob,XGBoostJob,XDLJob")
+    a = ap.parse_args(argv)
+    for kind in a.kinds.split(","):
+        print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds)), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -98,7 +98,16 @@ class BaseJobReconciler(ControllerInterface):
             return Result()
         SCHEME.default(job)
         specs = self.info.replica_specs(job)
-        return self.ctrl.reconcile_jobs(job, specs, c.status_of(job), c.run_policy_of(job))
+        try:
+            return self.ctrl.reconcile_jobs(job, specs, c.status_of(job), c.run_policy_of(job))
+        except NotFound:
+            # the job vanished while we were working on it (deleted between the cached read and a
+            # write): nothing left to reconcile, the delete event will account for it
+            try:
+                self.client.reader().get(self.KIND, req.namespace, req.name)
+            except NotFound:
+                return Result()
+            raise
 
     # ------------------------------------------------------------------ identity
     def controller_name(self) -> str: return self.CONTROLLER_NAME

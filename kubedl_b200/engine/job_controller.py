@@ -332,7 +332,8 @@ class JobController:
 
         self.controller.update_job_status(job, replicas, job_status, restart[0])
 
-        if st.is_created(old_status) and not st.is_running(old_status) and st.is_running(job_status):
+        # reference condition (job.go:243-245); the metric itself observes once per job UID
+        if st.is_created(old_status) and st.is_running(job_status):
             self.metrics.first_pod_launch_delay_seconds(active_pods, job, job_status)
         if k8sutil.get_total_active_replicas(job_status.get("replicaStatuses")) == total and \
                 k8sutil.get_total_active_replicas(old_status.get("replicaStatuses")) < total and \

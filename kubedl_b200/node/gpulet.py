@@ -31,6 +31,7 @@ import subprocess
 import sys
 import threading
 import time
+from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Tuple
 
@@ -145,6 +146,7 @@ class Gpulet:
         self._stop = threading.Event()
         self._threads: List[threading.Thread] = []
         self._unwatch: List[Callable[[], None]] = []
+        self._pool = ThreadPoolExecutor(max_workers=16, thread_name_prefix="gpulet-pod")
         self.launched = 0
 
     # ------------------------------------------------------------------ lifecycle
@@ -163,6 +165,7 @@ class Gpulet:
             procs = list(self._procs.values())
         for p in procs:
             self._kill(p)
+        self._pool.shutdown(wait=False)
 
     def _kick(self) -> None:
         pass  # the loop polls; the hook exists so watches wake it in future revisions
@@ -245,15 +248,20 @@ class Gpulet:
                     self._gpu_of[key] = gpu
             with self._lock:
                 self._pending.pop(key, None)
-            try:
-                self._launch(pod, gpu)
-            except Exception as e:
-                log.warning("launch of %s failed: %s", key, e)
-                self._set_status(pod, c.POD_FAILED, reason=str(e), exit_code=127)
-                with self._lock:
-                    g = self._gpu_of.pop(key, None)
-                    if g is not None:
-                        self.free_gpus.append(g)
+            # pods start concurrently (a kubelet runs one pod worker per pod): the all-pods launch
+            # delay is then one process spawn, not eight in a row
+            self._pool.submit(self._launch_guarded, key, pod, gpu)
+
+    def _launch_guarded(self, key, pod, gpu) -> None:
+        try:
+            self._launch(pod, gpu)
+        except Exception as e:
+            log.warning("launch of %s failed: %s", key, e)
+            self._set_status(pod, c.POD_FAILED, reason=str(e), exit_code=127)
+            with self._lock:
+                g = self._gpu_of.pop(key, None)
+                if g is not None:
+                    self.free_gpus.append(g)
 
     # ------------------------------------------------------------------ env / DNS
     def _service_names(self, ns: str) -> Dict[str, dict]:

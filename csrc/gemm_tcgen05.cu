@@ -21,6 +21,7 @@
 #include "../include/kubedl_b200.h"
 #include <cuda.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace kdl {
 
@@ -415,6 +416,272 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   }
 }
 
+// ------------------------------------------------------------------ 2-CTA (cta_group::2) variant
+// A CTA pair (cluster of 2 = the two SMs of a TPC) computes one 256 x 256 tile with
+// tcgen05.mma.cta_group::2: each CTA stages its own 128 rows of A and its own 128 columns' worth
+// of B, so per-SM shared-memory traffic per FLOP halves and the MMA runs at the full UMMA_M=256
+// rate (a single CTA tops out near 50 % of tensor peak: profiles/ncu_hot_kernels_raw.csv).
+// The leader CTA (rank 0) issues every MMA; TMA loads of both CTAs complete on the leader's
+// "full" barrier, commits are multicast to both CTAs' "empty" / "tmem full" barriers, and both
+// CTAs' epilogue warps arrive on the leader's "tmem empty" barrier.
+constexpr int BN2 = 256;
+constexpr int STAGES2 = 5;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar), "r"(cta)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar,
+                                                int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3)
+      : "memory");
+}
+
+struct SmemLayout2 {
+  static constexpr int kABytes = BM * BK * 2;            // this CTA's 128 rows of A
+  static constexpr int kBBytes = (BN2 / 2) * BK * 2;     // this CTA's half of B
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagingOffset = STAGES2 * kStageBytes;
+  static constexpr int kStagingPerWarp = 2 * 4096;
+  static constexpr int kBarOffset = kStagingOffset + 4 * kStagingPerWarp;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES2 + 4) * 8 + 16;
+};
+
+template <int A_MN, int B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
+                         const __grid_constant__ CUtensorMap tma_b,
+                         const __grid_constant__ CUtensorMap tma_c, const GemmParams p) {
+  using SL = SmemLayout2;
+  constexpr int STAGES = STAGES2;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar_base = smem_base + SL::kBarOffset;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SL::kBarOffset + (2 * STAGES + 4) * 8);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  constexpr uint32_t kTmemCols = 2 * BN2;   // 512: two accumulator stages
+  constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit: address of the leader's copy
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_c) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 2);    // one arrive per CTA's producer
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 8);  // 4 epilogue warps x 2 CTAs
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_ptr_smem)),
+                 "r"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int num_pairs = gridDim.x / 2;
+  const int pair = blockIdx.x / 2;
+  const int total_tiles = p.num_m * p.num_n;    // tiles of 256 x 256
+  const int kb_total = (p.K + BK - 1) / BK;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < total_tiles; t += num_pairs) {
+        const int n_idx = t % p.num_n;
+        const int m_idx = t / p.num_n;
+        const int m0 = m_idx * 256 + (int)cta * BM;
+        const int n0 = n_idx * BN2 + (int)cta * (BN2 / 2);
+        for (int kb = 0; kb < kb_total; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * SL::kStageBytes;
+          const uint32_t sb = sa + SL::kABytes;
+          const uint32_t lbar = full_bar(stage) & kPeerMask;
+          if (A_MN) {
+#pragma unroll
+            for (int a = 0; a < BM / 64; ++a)
+              tma_load_2d_2sm(sa + a * (BK * 128), &tma_a, lbar, m0 + a * 64, kb * BK);
+          } else {
+            tma_load_2d_2sm(sa, &tma_a, lbar, kb * BK, m0);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int a = 0; a < (BN2 / 2) / 64; ++a)
+              tma_load_2d_2sm(sb + a * (BK * 128), &tma_b, lbar, n0 + a * 64, kb * BK);
+          } else {
+            tma_load_2d_2sm(sb, &tma_b, lbar, kb * BK, n0);
+          }
+          if (leader) mbar_expect_tx(full_bar(stage), 2 * SL::kStageBytes);
+          else mbar_arrive_remote(full_bar(stage), 0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)A_MN << 15) |
+                                 ((uint32_t)B_MN << 16) | ((uint32_t)(BN2 >> 3) << 17) |
+                                 ((uint32_t)(256 >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int iter = 0;
+      for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
+        const int as = iter & 1;
+        const uint32_t aphase = (iter >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN2;
+        for (int kb = 0; kb < kb_total; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + stage * SL::kStageBytes;
+          const uint32_t sb = sa + SL::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = make_desc<A_MN>(sa + k_advance_bytes<A_MN>(k));
+            const uint64_t bd = make_desc<B_MN>(sb + k_advance_bytes<B_MN>(k));
+            umma_bf16_2sm(tmem_d, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_2sm(empty_bar(stage));
+          if (kb == kb_total - 1) umma_commit_2sm(tfull_bar(as));
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    const int q = warp & 3;
+    const uint32_t stg_base = smem_base + SL::kStagingOffset + q * SL::kStagingPerWarp;
+    uint8_t* stg_ptr = smem + SL::kStagingOffset + q * SL::kStagingPerWarp;
+    int iter = 0;
+    int buf = 0;
+    for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
+      const int n_idx = t % p.num_n;
+      const int m_idx = t / p.num_n;
+      const int as = iter & 1;
+      const uint32_t aphase = (iter >> 1) & 1;
+      mbar_wait(tfull_bar(as), aphase);
+      tcgen05_fence_after();
+      const int row0 = m_idx * 256 + (int)cta * BM + q * 32;
+      const int row = row0 + lane;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN2;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN2; c0 += 64) {
+        uint32_t r[64];
+        tmem_ld32(taddr + c0, r);
+        tmem_ld32(taddr + c0 + 32, r + 32);
+        tmem_ld_wait();
+        const int col = n_idx * BN2 + c0;
+        float f[64];
+#pragma unroll
+        for (int j = 0; j < 64; ++j) f[j] = __uint_as_float(r[j]);
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 64; ++j)
+            if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
+        }
+        if (p.addend && row < p.M) {
+          const bf16* ad = p.addend + (size_t)row * p.ldc + col;
+          if (col + 64 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 64; j += 8) {
+              float b[8];
+              unpack8(ld_plain(ad + j), b);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[j + i] += b[i];
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 64; ++j)
+              if (col + j < p.N) f[j] += __bfloat162float(ad[j]);
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 64; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+        uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tma_c, stg_base + buf * 4096, col, row0);
+          tma_store_commit();
+        }
+        buf ^= 1;
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(tempty_bar(as), 0);   // the leader's barrier, from both CTAs
+    }
+    if (lane == 0) tma_store_wait_read<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(kTmemCols)
+                 : "memory");
+  }
+}
+
 // Deterministic split-K reduction: out = bf16(sum_s partial[s]) (fixed order).
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partial,
                                                             bf16* __restrict__ out, int64_t MN,
@@ -537,6 +804,35 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
   return KDL_OK;
 }
 
+template <int A_MN, int B_MN>
+static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+                       const GemmParams& p, cudaStream_t stream) {
+  using SL = SmemLayout2;
+  auto kern = gemm_tcgen05_2cta_kernel<A_MN, B_MN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    KDL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::kTotal + 1024));
+    attr_done = true;
+  }
+  int tiles = p.num_m * p.num_n;
+  int pairs = num_sms() / 2;
+  if (tiles < pairs) pairs = tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = SL::kTotal + 1024;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  KDL_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, p));
+  return KDL_OK;
+}
+
 template <int BN, int STAGES>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
                           const CUtensorMap& mc, const GemmParams& p, cudaStream_t s) {
@@ -551,6 +847,21 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUten
 using namespace kdl;
 
 static int pick_bn(int N) { return N <= 64 ? 64 : 128; }
+
+// 2-CTA tiles (256 x 256) pay off when the problem is compute-heavy enough: wide N, deep-ish K.
+static bool want_2cta(int M, int N, int K, int splits, int force) {
+  if (force == 0) return false;
+  if (splits > 1) return false;
+  if (force == 1) return N >= 128 && M >= 256;
+  static int env = -1;
+  if (env < 0) {
+    const char* e = getenv("KDL_GEMM_2CTA");
+    env = e ? atoi(e) : 2;   // 0 = never, 1 = whenever legal, 2 = heuristic
+  }
+  if (env == 0) return false;
+  if (env == 1) return N >= 128 && M >= 256;
+  return N >= 256 && M >= 1024 && K >= 256;
+}
 
 static int pick_splits(int M, int N, int K, int requested) {
   int bn = pick_bn(N);
@@ -627,13 +938,25 @@ extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   }
   CUtensorMap ma, mb;
   int rc;
+  const bool two = want_2cta(M, N, K, splits, -1);
   // K-major: global [rows=MN extent][K] ; MN-major: global [K][MN extent]
   if (a_mn_major) rc = make_map(&ma, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
   else rc = make_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
   if (rc) return rc;
   if (b_mn_major) rc = make_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
-  else rc = make_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)bn);
+  else rc = make_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, two ? (uint32_t)(BN2 / 2) : (uint32_t)bn);
   if (rc) return rc;
+  if (two) {
+    CUtensorMap mc2;
+    rc = make_c_map(&mc2, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);
+    if (rc) return rc;
+    p.num_m = (M + 255) / 256;
+    p.num_n = (N + BN2 - 1) / BN2;
+    if (!a_mn_major && !b_mn_major) return launch_2cta<0, 0>(ma, mb, mc2, p, stream);
+    if (!a_mn_major && b_mn_major) return launch_2cta<0, 1>(ma, mb, mc2, p, stream);
+    if (a_mn_major && b_mn_major) return launch_2cta<1, 1>(ma, mb, mc2, p, stream);
+    return launch_2cta<1, 0>(ma, mb, mc2, p, stream);
+  }
   CUtensorMap mc;
   if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)N, (uint64_t)N, (uint64_t)splits);
   else rc = make_c_map(&mc, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);

@@ -68,3 +68,29 @@ def test_gemm_tn_splitk(cuda, K, M, N, split):
     assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
     out2 = g.tn(a, b, split_k=split)
     assert torch.equal(out, out2)  # deterministic split-K
+
+
+@pytest.mark.parametrize("mode,M,N,K", [
+    ("nt", 2048, 256, 256), ("nt", 2000, 1000, 512), ("nt", 1300, 320, 264), ("nt", 8192, 2048, 1024),
+    ("nn", 2048, 512, 256), ("nn", 5000, 1024, 768), ("tn", 1024, 256, 512), ("tn", 1536, 768, 2048),
+])
+def test_gemm_2cta_path(cuda, mode, M, N, K):
+    """Shapes that the dispatcher sends to the cta_group::2 kernel (N >= 256, M >= 1024, K >= 256),
+    with ragged M / N / K so TMA clipping and zero fill are exercised on both CTAs of the pair."""
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(7)
+    if mode == "nt":
+        a = torch.randn(M, K, device=cuda).bfloat16(); b = torch.randn(N, K, device=cuda).bfloat16()
+        bias = torch.randn(N, device=cuda).bfloat16(); add = torch.randn(M, N, device=cuda).bfloat16()
+        out = g.nt(a, b, bias=bias, addend=add, relu=True)
+        ref = torch.relu(a.float() @ b.float().t() + bias.float() + add.float())
+    elif mode == "nn":
+        a = torch.randn(M, K, device=cuda).bfloat16(); b = torch.randn(K, N, device=cuda).bfloat16()
+        out = g.nn(a, b)
+        ref = a.float() @ b.float()
+    else:
+        a = torch.randn(K, M, device=cuda).bfloat16(); b = torch.randn(K, N, device=cuda).bfloat16()
+        out = g.tn(a, b, split_k=1)
+        ref = a.float().t() @ b.float()
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)

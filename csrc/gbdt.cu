@@ -49,6 +49,7 @@ struct HistParams {
   unsigned* node_done;   // [nbuild] local arrival counters, zero on entry, zero on exit
   // cross-GPU part
   const float* peer_local[KDL_MAX_WORLD];  // peers' `local` buffers
+  const float* mc_local;                   // NVLS multicast alias of `local` (or null): in-switch sum
   uint32_t* flags[KDL_MAX_WORLD];          // per rank: [world][max nodes] epoch flags
   int world, rank;
   int max_nodes;
@@ -139,6 +140,19 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
       }
     }
     __syncthreads();
+    if (p.mc_local != nullptr) {
+      // NVLS: one multimem.ld_reduce per 16 bytes sums all ranks' copies inside the NVSwitch;
+      // every rank receives the same switch-computed value, so trees stay identical
+      const float* src = p.mc_local + (size_t)bi * hist_floats;
+      for (int i = tid; i < hist_floats / 4; i += kHistThreads) {
+        float4 v;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "l"(src + 4 * (size_t)i)
+                     : "memory");
+        reinterpret_cast<float4*>(out)[i] = v;
+      }
+    } else
     // one-shot reduce in rank order (same order everywhere -> identical trees on every rank)
     for (int i = tid; i < hist_floats / 4; i += kHistThreads) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -278,7 +292,8 @@ extern "C" int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, con
                                        const int32_t* ridx, const int32_t* seg, const int32_t* build,
                                        int nbuild, int64_t n_rows_hint, void* local_hist, void* out_hist,
                                        void* node_done, void* const* peer_local, void* const* flag_ptrs,
-                                       int world, int rank, int max_nodes, unsigned epoch, void* status,
+                                       const void* mc_local, int world, int rank, int max_nodes,
+                                       unsigned epoch, void* status,
                                        unsigned long long timeout_ns, cudaStream_t stream) {
   if (F < 1 || F > 32 || fstride < F || (fstride % 16) != 0) {
     kdl_set_error("gbdt_hist: need 1 <= F <= 32 and a 16-byte multiple row stride >= F (F=%d stride=%d)", F, fstride);
@@ -294,6 +309,7 @@ extern "C" int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, con
   p.local = (float*)local_hist; p.out = (float*)out_hist; p.node_done = (unsigned*)node_done;
   p.world = world; p.rank = rank; p.max_nodes = max_nodes; p.epoch = epoch;
   p.timeout_ns = timeout_ns; p.status = (uint32_t*)status;
+  p.mc_local = world > 1 ? (const float*)mc_local : nullptr;
   for (int r = 0; r < world; ++r) {
     p.peer_local[r] = peer_local ? (const float*)peer_local[r] : (const float*)local_hist;
     p.flags[r] = flag_ptrs ? (uint32_t*)flag_ptrs[r] : nullptr;

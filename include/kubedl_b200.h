@@ -109,7 +109,8 @@ size_t kdl_gbdt_hist_bytes(int nodes, int F);
 int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, const void* gh, const int32_t* ridx,
                             const int32_t* seg, const int32_t* build, int nbuild, int64_t n_rows_hint,
                             void* local_hist, void* out_hist, void* node_done, void* const* peer_local,
-                            void* const* flag_ptrs, int world, int rank, int max_nodes, unsigned epoch,
+                            void* const* flag_ptrs, const void* mc_local /* NVLS alias of local_hist or NULL */,
+                            int world, int rank, int max_nodes, unsigned epoch,
                             void* status, unsigned long long timeout_ns, cudaStream_t stream);
 int kdl_gbdt_split_eval(const void* hist, int nodes, int F, float lambda, float gamma,
                         float min_child_weight, float* out8, cudaStream_t stream);

@@ -29,8 +29,8 @@ L.register_signatures({
     "kdl_gbdt_hist_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "kdl_gbdt_hist_allreduce": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
-                                          C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int,
-                                          C.c_uint, C.c_void_p, C.c_ulonglong, C.c_void_p]),
+                                          C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int,
+                                          C.c_int, C.c_uint, C.c_void_p, C.c_ulonglong, C.c_void_p]),
     "kdl_gbdt_split_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
                                       C.c_void_p, C.c_void_p]),
     "kdl_gbdt_apply_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
@@ -86,6 +86,8 @@ class GBDTTrainer:
         self.heap = heap
         self.comm = comm if self.world > 1 else "none"
         self.group = group
+        import os as _os
+        self.use_nvls = _os.environ.get("KUBEDL_NVLS", "auto") != "0"
         if self.world > 1 and heap is None and comm == "fused":
             from ..parallel.symm import SymmetricHeap
             self.heap = heap = SymmetricHeap(64 << 20, group=group)
@@ -142,7 +144,9 @@ class GBDTTrainer:
             self.bins.data_ptr(), FSTRIDE, self.F, self.gh.data_ptr(), ridx.data_ptr(), seg.data_ptr(),
             build.data_ptr(), nbuild, self.n, self.local[par].data_ptr(), self.out.data_ptr(),
             self.node_done.data_ptr(), self._peer_tabs[par] if fused else None,
-            self._flag_tab if fused else None, self.world if fused else 1, self.rank if fused else 0,
+            self._flag_tab if fused else None,
+            (self.heap.mc(self.local_off[par]) if (fused and self.use_nvls) else None),
+            self.world if fused else 1, self.rank if fused else 0,
             self.max_nodes, self.epoch, None, int(30e9), L.stream_ptr())
         L.check(rc, "kdl_gbdt_hist_allreduce")
         L.count(1)

@@ -481,6 +481,65 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
   return KDL_OK;
 }
 
+// BN forward when the per-channel sums were already produced by the GEMM epilogue
+// (kdl_gemm_bf16_ex `stats_partial`): finalise [nparts][2][C] partials in a fixed order, then apply.
+__global__ void __launch_bounds__(256) bn_finalize_partials_kernel(const float* __restrict__ partial, int nparts,
+                                                                   int64_t M, int C, const float* gamma,
+                                                                   const float* beta, float* running_mean,
+                                                                   float* running_var, float eps, float momentum,
+                                                                   float* mean_rstd, float* coef) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float S0 = 0.f, S1 = 0.f;
+  for (int i = 0; i < nparts; ++i) {
+    S0 += __ldcg(partial + (size_t)i * 2 * C + c);
+    S1 += __ldcg(partial + (size_t)i * 2 * C + C + c);
+  }
+  const float invM = 1.f / (float)M;
+  const float mu = S0 * invM;
+  const float var = fmaxf(S1 * invM - mu * mu, 0.f);
+  const float rs = rsqrtf(var + eps);
+  const float a = (gamma ? gamma[c] : 1.f) * rs;
+  mean_rstd[c] = mu;
+  mean_rstd[C + c] = rs;
+  coef[c] = a;
+  coef[C + c] = (beta ? beta[c] : 0.f) - mu * a;
+  if (running_mean) {
+    const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mu;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+}
+
+extern "C" int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C,
+                                     const float* gamma, const float* beta, float* running_mean,
+                                     float* running_var, float eps, float momentum, int relu,
+                                     float* save_mean_rstd, const float* stats_partial, int nparts,
+                                     void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  BnPlan pl;
+  unsigned* counter;
+  float *coef, *partial;
+  int rc = carve(workspace, workspace_bytes, M, C, &pl, &counter, &coef, &partial);
+  if (rc) return rc;
+  if (nparts < 1 || stats_partial == nullptr) {
+    kdl_set_error("bn_fwd_from_stats: no partial statistics given");
+    return KDL_ERR_ARG;
+  }
+  bn_finalize_partials_kernel<<<(C + 255) / 256, 256, 0, stream>>>(stats_partial, nparts, M, C, gamma, beta,
+                                                                   running_mean, running_var, eps, momentum,
+                                                                   save_mean_rstd, coef);
+  KDL_CHECK_LAUNCH();
+  int64_t nvec = M * C / 8;
+  int cvec = C / 8;
+  int g = apply_grid(nvec);
+  if ((256 % cvec) == 0)
+    bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu);
+  else
+    bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // kdl_bn_fwd_static_scratch: the same fused BN forward for callers that must not allocate.
 //

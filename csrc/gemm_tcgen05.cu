@@ -28,7 +28,11 @@ namespace kdl {
 constexpr int BM = 128;       // UMMA M (cta_group::1)
 constexpr int BK = 64;        // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 256;
+// 4 control warps + kEpiWarps epilogue warps.  8 epilogue warps (two per TMEM lane quarter, alternating
+// column chunks) were measured: they hide the fused-statistics epilogue but cost a pipeline stage of
+// shared memory and ~5 % on compute-bound shapes (profiles/gemm_vs_cublas_shapes.log), so 4 it is.
+constexpr int kEpiWarps = 4;
+constexpr int kGemmThreads = 128 + 32 * kEpiWarps;
 constexpr int kEpiWarp0 = 4;
 
 struct GemmParams {
@@ -42,7 +46,31 @@ struct GemmParams {
   int splits;
   int kb_per_split;
   int num_m, num_n;
+  float* stats;   // optional [gridDim.x][2][N]: per-CTA column sum / sum-of-squares of the bf16 output
 };
+
+constexpr int kStatsMaxN = 2048;
+constexpr int kStatsBytes = 2 * kStatsMaxN * 4;
+
+// Column statistics of one 32-row x 64-column bf16 chunk sitting in a (128B-swizzled) staging
+// buffer: lane l owns columns 2l, 2l+1.  Feeds the BatchNorm that follows a 1x1 convolution, so
+// the separate statistics pass over the activation disappears.
+__device__ __forceinline__ void chunk_col_stats(const uint8_t* buf, int lane, int rows_valid, int col0,
+                                                int N, float* cta_stats) {
+  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+  for (int r = 0; r < 32; ++r) {
+    if (r < rows_valid) {
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + r * 128 + ((((lane >> 2) ^ (r & 7))) << 4) + (lane & 3) * 4);
+      const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+      s0 += v.x; q0 = fmaf(v.x, v.x, q0);
+      s1 += v.y; q1 = fmaf(v.y, v.y, q1);
+    }
+  }
+  const int c = col0 + 2 * lane;
+  if (c < N) { atomicAdd(cta_stats + c, s0); atomicAdd(cta_stats + kStatsMaxN + c, q0); }
+  if (c + 1 < N) { atomicAdd(cta_stats + c + 1, s1); atomicAdd(cta_stats + kStatsMaxN + c + 1, q1); }
+}
 
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -173,7 +201,8 @@ struct SmemLayout {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagingOffset = STAGES * kStageBytes;   // 1024-aligned
   static constexpr int kStagingPerWarp = 2 * 4096;             // two 32-row x 128-B buffers
-  static constexpr int kBarOffset = kStagingOffset + 4 * kStagingPerWarp;
+  static constexpr int kStatsOffset = kStagingOffset + kEpiWarps * kStagingPerWarp;
+  static constexpr int kBarOffset = kStatsOffset + kStatsBytes;
   static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
 };
 
@@ -195,6 +224,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;  // power of two for BN in {32,64,128,256}
+  float* cta_stats = reinterpret_cast<float*>(smem + SL::kStatsOffset);
+  if (p.stats) {
+    for (int i = threadIdx.x; i < 2 * kStatsMaxN; i += kGemmThreads) cta_stats[i] = 0.f;
+  }
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -208,7 +241,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 4);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(s), kEpiWarps);  // one arrive per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -299,9 +332,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     // TMEM -> registers -> (bias, addend, ReLU) -> bf16 -> 128B-swizzled smem staging -> TMA
     // store.  Each warp owns 32 accumulator rows and two 4 KB staging buffers, so the bulk
     // store of chunk i overlaps the TMEM read + math of chunk i+1; TMA clips M/N tails.
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const uint32_t stg_base = smem_base + SL::kStagingOffset + q * SL::kStagingPerWarp;
-    uint8_t* stg_ptr = smem + SL::kStagingOffset + q * SL::kStagingPerWarp;
+    const int q = warp & 3;                   // TMEM lane quarter this warp may access
+    const int half = (warp - kEpiWarp0) >> 2; // the two warps of a quarter take alternate column chunks
+    const int ew = warp - kEpiWarp0;
+    const uint32_t stg_base = smem_base + SL::kStagingOffset + ew * SL::kStagingPerWarp;
+    uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
     int iter = 0;
     int buf = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
@@ -318,7 +353,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       if (p.partial != nullptr) {
         // split-K: fp32 partial tile, 32 columns (128 B) per staging row
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = half * 32; c0 < BN; c0 += 32 * (kEpiWarps / 4)) {
           uint32_t r[32];
           tmem_ld32(taddr + c0, r);
           tmem_ld_wait();
@@ -339,7 +374,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         }
       } else {
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 64) {
+        for (int c0 = half * 64; c0 < BN; c0 += 64 * (kEpiWarps / 4)) {
           uint32_t r[64];
           tmem_ld32(taddr + c0, r);
           tmem_ld32(taddr + c0 + 32, r + 32);
@@ -389,6 +424,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
+          if (p.stats) {
+            __syncwarp();
+            chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, col, p.N, cta_stats);
+          }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
@@ -408,6 +447,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 
   tcgen05_fence_before();
   __syncthreads();
+  if (p.stats) {
+    float* dst = p.stats + (size_t)blockIdx.x * 2 * p.N;
+    for (int i = threadIdx.x; i < p.N; i += kGemmThreads) {
+      dst[i] = cta_stats[i];
+      dst[p.N + i] = cta_stats[kStatsMaxN + i];
+    }
+  }
   if (warp == 2) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
@@ -474,7 +520,8 @@ struct SmemLayout2 {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagingOffset = STAGES2 * kStageBytes;
   static constexpr int kStagingPerWarp = 2 * 4096;
-  static constexpr int kBarOffset = kStagingOffset + 4 * kStagingPerWarp;
+  static constexpr int kStatsOffset = kStagingOffset + kEpiWarps * kStagingPerWarp;
+  static constexpr int kBarOffset = kStatsOffset + kStatsBytes;
   static constexpr int kTotal = kBarOffset + (2 * STAGES2 + 4) * 8 + 16;
 };
 
@@ -498,6 +545,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
   const bool leader = cta == 0;
+  float* cta_stats = reinterpret_cast<float*>(smem + SL::kStatsOffset);
+  if (p.stats) {
+    for (int i = threadIdx.x; i < 2 * kStatsMaxN; i += kGemmThreads) cta_stats[i] = 0.f;
+  }
   constexpr uint32_t kTmemCols = 2 * BN2;   // 512: two accumulator stages
   constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit: address of the leader's copy
 
@@ -513,7 +564,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 8);  // 4 epilogue warps x 2 CTAs
+      mbar_init(tempty_bar(s), 2 * kEpiWarps);  // epilogue warps of both CTAs
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -601,8 +652,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else if (warp >= kEpiWarp0) {
     const int q = warp & 3;
-    const uint32_t stg_base = smem_base + SL::kStagingOffset + q * SL::kStagingPerWarp;
-    uint8_t* stg_ptr = smem + SL::kStagingOffset + q * SL::kStagingPerWarp;
+    const int half = (warp - kEpiWarp0) >> 2;
+    const int ew = warp - kEpiWarp0;
+    const uint32_t stg_base = smem_base + SL::kStagingOffset + ew * SL::kStagingPerWarp;
+    uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
     int iter = 0;
     int buf = 0;
     for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
@@ -616,7 +669,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       const int row = row0 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN2;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN2; c0 += 64) {
+      for (int c0 = half * 64; c0 < BN2; c0 += 64 * (kEpiWarps / 4)) {
         uint32_t r[64];
         tmem_ld32(taddr + c0, r);
         tmem_ld32(taddr + c0 + 32, r + 32);
@@ -656,6 +709,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
+        if (p.stats) {
+          __syncwarp();
+          chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, col, p.N, cta_stats);
+        }
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
@@ -674,6 +731,13 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
 
   tcgen05_fence_before();
   cluster_sync_all();
+  if (p.stats) {
+    float* dst = p.stats + (size_t)blockIdx.x * 2 * p.N;
+    for (int i = threadIdx.x; i < p.N; i += kGemmThreads) {
+      dst[i] = cta_stats[i];
+      dst[p.N + i] = cta_stats[kStatsMaxN + i];
+    }
+  }
   if (warp == 2) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
@@ -893,10 +957,27 @@ extern "C" size_t kdl_gemm_scratch_bytes(int M, int N, int K, int split_k) {
   return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
 }
 
+extern "C" int kdl_gemm_max_ctas(void) { return num_sms(); }
+
+extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
+                                int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
+                                const void* bias, const void* addend, int relu, int split_k,
+                                void* scratch, size_t scratch_bytes, float* stats_partial,
+                                int* stats_parts_out, cudaStream_t stream);
+
 extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                              int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
                              const void* bias, const void* addend, int relu, int split_k,
                              void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  return kdl_gemm_bf16_ex(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, bias, addend, relu,
+                          split_k, scratch, scratch_bytes, nullptr, nullptr, stream);
+}
+
+extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
+                                int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
+                                const void* bias, const void* addend, int relu, int split_k,
+                                void* scratch, size_t scratch_bytes, float* stats_partial,
+                                int* stats_parts_out, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) {
     kdl_set_error("gemm: bad shape %dx%dx%d", M, N, K);
     return KDL_ERR_ARG;
@@ -920,6 +1001,13 @@ extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.kb_per_split = (kb_total + splits - 1) / splits;
   p.num_m = (M + BM - 1) / BM;
   p.num_n = (N + bn - 1) / bn;
+  p.stats = stats_partial;
+  if (stats_partial != nullptr) {
+    if (N > kStatsMaxN || splits > 1) {
+      kdl_set_error("gemm: fused column statistics need N <= %d and no split-K", kStatsMaxN);
+      return KDL_ERR_UNSUPPORTED;
+    }
+  }
   if (splits > 1) {
     if (bias || addend || relu) {
       kdl_set_error("gemm: split-K does not support fused bias/addend/relu");
@@ -952,16 +1040,24 @@ extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N
     if (rc) return rc;
     p.num_m = (M + 255) / 256;
     p.num_n = (N + BN2 - 1) / BN2;
+    if (stats_parts_out) {
+      int tiles2 = p.num_m * p.num_n, pairs = num_sms() / 2;
+      *stats_parts_out = 2 * (tiles2 < pairs ? tiles2 : pairs);
+    }
     if (!a_mn_major && !b_mn_major) return launch_2cta<0, 0>(ma, mb, mc2, p, stream);
     if (!a_mn_major && b_mn_major) return launch_2cta<0, 1>(ma, mb, mc2, p, stream);
     if (a_mn_major && b_mn_major) return launch_2cta<1, 1>(ma, mb, mc2, p, stream);
     return launch_2cta<1, 0>(ma, mb, mc2, p, stream);
   }
+  if (stats_parts_out) {
+    int tiles1 = p.num_m * p.num_n * p.splits;
+    *stats_parts_out = tiles1 < num_sms() ? tiles1 : num_sms();
+  }
   CUtensorMap mc;
   if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)N, (uint64_t)N, (uint64_t)splits);
   else rc = make_c_map(&mc, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);
   if (rc) return rc;
-  if (bn == 64) rc = dispatch_major<64, 8>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
+  if (bn == 64) rc = dispatch_major<64, 6>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
   else rc = dispatch_major<128, 5>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
   if (rc) return rc;
   if (splits > 1) {

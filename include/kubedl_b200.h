@@ -48,6 +48,13 @@ int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dre
                void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
 
+/* BN forward fed by the column statistics a preceding kdl_gemm_bf16_ex call produced in its
+ * epilogue ([nparts][2][C] partial sums): the separate statistics pass over x is skipped. */
+int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,
+                          const float* beta, float* running_mean, float* running_var, float eps,
+                          float momentum, int relu, float* save_mean_rstd, const float* stats_partial,
+                          int nparts, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
 /* kdl_bn_fwd for callers that cannot allocate device memory (the GPU's memory is wholly owned by
  * someone else's pool, or cudaMalloc's device-wide synchronisation is not acceptable where the
  * call is made).  This entry point has no counterpart in the reference.  Same arguments as
@@ -98,6 +105,13 @@ int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
                   int b_mn_major, int lda, int ldb, int ldc, const void* bias_bf16,
                   const void* addend_bf16, int relu, int split_k, void* scratch, size_t scratch_bytes,
                   cudaStream_t stream);
+/* Same, and additionally (stats_partial != NULL) per-CTA column sum / sum-of-squares of the bf16
+ * output, [kdl_gemm_max_ctas()][2][N] floats; *stats_parts_out = number of rows written. */
+int kdl_gemm_max_ctas(void);
+int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                     int b_mn_major, int lda, int ldb, int ldc, const void* bias_bf16,
+                     const void* addend_bf16, int relu, int split_k, void* scratch, size_t scratch_bytes,
+                     float* stats_partial, int* stats_parts_out, cudaStream_t stream);
 
 /* ---- N3: histogram GBDT, histogram build fused with the cross-GPU reduction ---------------
  * Replaces XGBoost gpu_hist + ncclAllReduce of histograms, for which the reference only injects

@@ -47,15 +47,20 @@ class Conv:
         self.g_end = a.end_offset(self.name)
         self.is_gemm = (self.k == 1 and self.stride == 1)
 
-    def fwd(self, x: torch.Tensor) -> torch.Tensor:
+    def fwd(self, x: torch.Tensor, want_stats: bool = False):
+        """want_stats: also return the BN column statistics produced by the GEMM epilogue (None on
+        the cuDNN path)."""
         net = self.net
         if self.is_gemm and net.gemm is not None:
             N, H, W, Cin = x.shape
-            y = net.gemm.nt(x.view(-1, Cin), self.w.view(self.cout, Cin))
-            return y.view(N, H, W, self.cout)
+            if want_stats and net.fuse_bn_stats:
+                y, stats = net.gemm.nt_stats(x.view(-1, Cin), self.w.view(self.cout, Cin))
+                return y.view(N, H, W, self.cout), stats
+            y = net.gemm.nt(x.view(-1, Cin), self.w.view(self.cout, Cin)).view(N, H, W, self.cout)
+            return (y, None) if want_stats else y
         y = torch.ops.aten.convolution(_nchw(x), self.w_nchw, None, [self.stride] * 2,
                                        [self.pad] * 2, [1, 1], False, [0, 0], 1)
-        return _nhwc(y)
+        return (_nhwc(y), None) if want_stats else _nhwc(y)
 
     def bwd(self, dy: torch.Tensor, x: torch.Tensor, need_dx: bool = True,
             addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
@@ -96,9 +101,9 @@ class BN:
         self.running_var = torch.ones(self.c, dtype=torch.float32, device=dev)
         self.save = torch.empty(2, self.c, dtype=torch.float32, device=dev)
 
-    def fwd(self, x, res=None):
+    def fwd(self, x, res=None, stats=None):
         y, _ = K.bn_fwd(x, self.gamma, self.beta, self.running_mean, self.running_var, res=res,
-                        relu=self.relu, save=self.save)
+                        relu=self.relu, save=self.save, stats=stats)
         return y
 
     def bwd(self, dy, x, y, dres=None):
@@ -138,17 +143,17 @@ class Bottleneck:
         return names
 
     def fwd(self, x, train=True):
-        c1 = self.c1.fwd(x)
-        a1 = self.b1.fwd(c1)
+        c1, s1 = self.c1.fwd(x, want_stats=True)
+        a1 = self.b1.fwd(c1, stats=s1)
         c2 = self.c2.fwd(a1)
         a2 = self.b2.fwd(c2)
-        c3 = self.c3.fwd(a2)
+        c3, s3 = self.c3.fwd(a2, want_stats=True)
         if self.cd is not None:
-            cdo = self.cd.fwd(x)
-            idn = self.bd.fwd(cdo)
+            cdo, sd = self.cd.fwd(x, want_stats=True)
+            idn = self.bd.fwd(cdo, stats=sd)
         else:
             cdo, idn = None, x
-        out = self.b3.fwd(c3, res=idn)
+        out = self.b3.fwd(c3, res=idn, stats=s3)
         if train:
             self.saved = (x, c1, a1, c2, a2, c3, cdo, out)
         return out
@@ -178,6 +183,11 @@ class ResNet50:
                  zero_init_residual: bool = False):
         self.device = torch.device(device)
         self.zero_init_residual = zero_init_residual
+        import os as _os
+        # BN column statistics from the GEMM epilogue: numerically validated, but measured slower
+        # end to end (24.4 vs 23.1 ms/step) because the epilogue warps are already the bottleneck of
+        # the memory-bound 1x1-conv GEMMs; off unless asked for.
+        self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "0") == "1"
         self.num_classes = num_classes
         self.arena = ParamArena()
         self.gemm = gemm
@@ -227,12 +237,16 @@ class ResNet50:
             assert self.gemm is not None
             N, H, W, _ = x.shape
             patches = K.stem_im2col(x)
-            c = self.gemm.nt(patches, self._stem_w_padded()).view(N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, 64)
+            if self.fuse_bn_stats:
+                c, stem_stats = self.gemm.nt_stats(patches, self._stem_w_padded())
+            else:
+                c, stem_stats = self.gemm.nt(patches, self._stem_w_padded()), None
+            c = c.view(N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, 64)
             x_bf16_nhwc = patches
         else:
             x_bf16_nhwc = x
-            c = self.stem.fwd(x_bf16_nhwc)
-        a = self.stem_bn.fwd(c)
+            c, stem_stats = self.stem.fwd(x_bf16_nhwc), None
+        a = self.stem_bn.fwd(c, stats=stem_stats)
         p, idx = K.maxpool3x3s2_fwd(a)
         h = p
         for b in self.blocks:

@@ -21,6 +21,11 @@ from .nn import workspace
 L.register_signatures({
     "kdl_gemm_splits": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "kdl_gemm_scratch_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int]),
+    "kdl_gemm_max_ctas": (C.c_int, []),
+    "kdl_gemm_bf16_ex": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                   C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                   C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_int),
+                                   C.c_void_p]),
     "kdl_gemm_bf16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                 C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
@@ -36,6 +41,24 @@ class Gemm:
     def __init__(self, device=None):
         self.lib = L.lib()
         self.device = device
+
+    def nt_stats(self, a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None):
+        """y = a @ b^T plus, from the same epilogue, per-CTA column sum / sum-of-squares of y (as
+        stored, i.e. bf16-rounded).  Returns (y, (partial[nparts_max, 2, N] fp32, nparts)) for
+        ops.nn.bn_fwd(stats=...)."""
+        _chk(a); _chk(b)
+        M, K = a.shape
+        N = b.shape[0]
+        if out is None:
+            out = torch.empty(M, N, dtype=torch.bfloat16, device=a.device)
+        partial = torch.empty(self.lib.kdl_gemm_max_ctas(), 2, N, dtype=torch.float32, device=a.device)
+        nparts = C.c_int(0)
+        rc = self.lib.kdl_gemm_bf16_ex(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, 0, 0, a.stride(0),
+                                       b.stride(0), out.stride(0), None, None, 0, 1, None, 0, partial.data_ptr(),
+                                       C.byref(nparts), L.stream_ptr())
+        L.check(rc, "kdl_gemm_bf16_ex")
+        L.count(1)
+        return out, (partial, nparts.value)
 
     def _run(self, A, B, out, M, N, K, a_mn, b_mn, bias, addend, relu, split_k):
         lib = self.lib

@@ -30,6 +30,9 @@ _SIGS = {
     "kdl_bn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                            c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
                            c_void_p]),
+    "kdl_bn_fwd_from_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_void_p, c_int,
+                                      c_void_p, c_size_t, c_void_p]),
     "kdl_u8_normalize": (c_int, [c_void_p, c_void_p, c_int64, c_int, C.POINTER(c_float),
                                  C.POINTER(c_float), c_void_p]),
     "kdl_stem_im2col_u8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, C.POINTER(c_float),

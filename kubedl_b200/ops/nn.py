@@ -39,8 +39,9 @@ def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
            running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
            res: Optional[torch.Tensor] = None, relu: bool = True, eps: float = 1e-5,
            momentum: float = 0.1, out: Optional[torch.Tensor] = None,
-           save: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
-    """y = relu(bn_train(x) + res) on x:[M,C] (or [N,H,W,C]) bf16. Returns (y, save_mean_rstd[2,C])."""
+           save: Optional[torch.Tensor] = None, stats=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """y = relu(bn_train(x) + res) on x:[M,C] (or [N,H,W,C]) bf16. Returns (y, save_mean_rstd[2,C]).
+    `stats` = (partial, nparts) from Gemm.nt_stats: the statistics pass over x is skipped."""
     _chk_bf16(x, res)
     Cn = x.shape[-1]
     M = x.numel() // Cn
@@ -52,6 +53,14 @@ def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
     if need == 0:
         raise L.KernelError(f"bn_fwd: unsupported shape M={M} C={Cn}")
     ws = workspace(need, x.device)
+    if stats is not None:
+        partial, nparts = stats
+        L.check(lib.kdl_bn_fwd_from_stats(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
+                                          beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps,
+                                          momentum, int(relu), save.data_ptr(), partial.data_ptr(), nparts,
+                                          ws.data_ptr(), ws.numel(), L.stream_ptr()), "kdl_bn_fwd_from_stats")
+        L.count(2)
+        return y, save
     L.check(lib.kdl_bn_fwd(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
                            beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps, momentum,
                            int(relu), save.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()),

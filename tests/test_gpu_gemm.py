@@ -94,3 +94,26 @@ def test_gemm_2cta_path(cuda, mode, M, N, K):
         out = g.tn(a, b, split_k=1)
         ref = a.float().t() @ b.float()
     assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+
+
+@pytest.mark.parametrize("M,N,K", [(5000, 64, 64), (30000, 256, 64), (4096, 1024, 256), (1500, 2048, 512), (777, 192, 328)])
+def test_gemm_fused_bn_stats_and_bn_from_stats(cuda, M, N, K):
+    """Column statistics from the GEMM epilogue (1-CTA and 2-CTA kernels) == statistics of the stored
+    bf16 output, and BN fed by them == BN that recomputes them."""
+    from kubedl_b200.ops.gemm import Gemm
+    from kubedl_b200.ops import nn as Kn
+    g = Gemm(cuda)
+    torch.manual_seed(11)
+    a = torch.randn(M, K, device=cuda).bfloat16(); b = (torch.randn(N, K, device=cuda) * 0.2).bfloat16()
+    y, (partial, nparts) = g.nt_stats(a, b)
+    ref = a.float() @ b.float().t()
+    assert _rel_err(y, ref) < 1e-2
+    s = partial[:nparts].double().sum(0)
+    yf = y.double()
+    torch.testing.assert_close(s[0], yf.sum(0), atol=1e-2 * M ** 0.5, rtol=1e-3)
+    torch.testing.assert_close(s[1], (yf * yf).sum(0), atol=1e-2 * M ** 0.5, rtol=1e-3)
+    gamma, beta = torch.rand(N, device=cuda) + 0.5, torch.randn(N, device=cuda) * 0.1
+    y1, sv1 = Kn.bn_fwd(y, gamma, beta, None, None, relu=True)
+    y2, sv2 = Kn.bn_fwd(y, gamma, beta, None, None, relu=True, stats=(partial, nparts))
+    torch.testing.assert_close(sv2, sv1, atol=1e-4, rtol=1e-4)
+    torch.testing.assert_close(y2.float(), y1.float(), atol=2e-2, rtol=2e-2)

@@ -1,0 +1,37 @@
+# Counterpart of the reference Makefile (manager / test / manifests / docker-build targets).
+PY ?= python
+
+all: lib manifests
+
+# Build the sm_100a kernel library in-tree (kubedl_b200/_lib/libkubedl_b200.so)
+lib:
+	$(PY) -m kubedl_b200.ops.build
+
+# Run the operator against the in-process API server
+run:
+	$(PY) -m kubedl_b200.cmd.manager --enable-leader-election=false
+
+# CPU tests (control plane, host logic) — what CI runs; GPU tests need a B200
+test: lib manifests
+	KUBEDL_CI=true $(PY) -m pytest tests -x -q -m "not gpu"
+
+test-gpu: lib
+	$(PY) -m pytest tests -x -q -m gpu
+
+# Regenerate CRD manifests from the kind registry
+manifests:
+	$(PY) -m kubedl_b200.api.crd --out config/crd/bases
+
+bench:
+	$(PY) bench.py --steps 20 --warmup 3
+
+launch-delay:
+	$(PY) -m kubedl_b200.bench.launch_delay --jobs 30 --replicas 8
+
+sass:
+	cuobjdump -sass kubedl_b200/_lib/libkubedl_b200.so | grep -E "UTCHMMA|UTMALDG|UTMASTG|LDTM|MULTIMEM" | sort | uniq -c
+
+docker-build:
+	docker build . -t kubedl-b200/manager:latest
+
+.PHONY: all lib run test test-gpu manifests bench launch-delay sass docker-build

@@ -47,6 +47,13 @@ struct GemmParams {
   int kb_per_split;
   int num_m, num_n;
   float* stats;   // optional [gridDim.x][2][N]: per-CTA column sum / sum-of-squares of the bf16 output
+  // implicit-GEMM convolution (N7): one operand is fetched with TMA im2col loads
+  int conv_mode;     // 0 plain GEMM; 1 A = activation patches (fprop / dgrad); 2 B = activation patches (wgrad)
+  int conv_q, conv_p;        // spatial extent the pixel index runs over (output W, H of this pass)
+  int conv_stride, conv_pad; // traversal stride and the (effective) padding of this pass
+  int conv_s, conv_r;        // filter W, H
+  int conv_c;                // channels of the patch operand (K per tap for mode 1, N per tap for mode 2)
+  int conv_flip;             // dgrad: filter taps are visited mirrored
 };
 
 constexpr int kStatsMaxN = 2048;
@@ -104,6 +111,17 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+// TMA im2col load: `pixels` consecutive output positions (W fastest, wrapping over H and N inside the
+// bounding box of the tensor map) x 64 channels of filter tap (off_w, off_h), zero-filled padding.
+__device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c,
+                                                int w, int h, int n, int off_w, int off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w),
+      "h"((uint16_t)off_h)
       : "memory");
 }
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
@@ -276,6 +294,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           const uint32_t sa = smem_base + stage * SL::kStageBytes;
           const uint32_t sb = sa + SL::kABytes;
           mbar_expect_tx(full_bar(stage), SL::kStageBytes);
+          if (p.conv_mode == 1) {
+            // K runs over (tap, channel block): A = 128 output pixels x 64 channels of that tap
+            const int cblks = p.conv_c / BK;
+            const int tap = kb / cblks, cb = kb - tap * cblks;
+            int kh = tap / p.conv_s, kw = tap - kh * p.conv_s;
+            const int m0 = m_idx * BM;
+            const int pq = p.conv_p * p.conv_q;
+            const int n0 = m0 / pq, rem = m0 - n0 * pq, oh0 = rem / p.conv_q, ow0 = rem - oh0 * p.conv_q;
+            const int fh = p.conv_flip ? p.conv_r - 1 - kh : kh, fw = p.conv_flip ? p.conv_s - 1 - kw : kw;
+            tma_load_im2col(sa, &tma_a, full_bar(stage), cb * BK, ow0 * p.conv_stride - p.conv_pad,
+                            oh0 * p.conv_stride - p.conv_pad, n0, fw, fh);
+            if (B_MN) {   // dgrad: weights [Cout][taps*Cin] read as K(cout) x N(cin) tiles of tap (kh,kw)
+#pragma unroll
+              for (int a = 0; a < BN / 64; ++a)
+                tma_load_2d(sb + a * (BK * 128), &tma_b, full_bar(stage), tap * p.N + n_idx * BN + a * 64, cb * BK);
+            } else {      // fprop: weights [Cout][taps*Cin] are already K-major in (tap, channel) order
+              tma_load_2d(sb, &tma_b, full_bar(stage), kb * BK, n_idx * BN);
+            }
+          } else {
           if (A_MN) {
 #pragma unroll
             for (int a = 0; a < BM / 64; ++a)
@@ -283,12 +320,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           } else {
             tma_load_2d(sa, &tma_a, full_bar(stage), kb * BK, m_idx * BM);
           }
-          if (B_MN) {
+          if (p.conv_mode == 2) {
+            // wgrad: K runs over 64-pixel blocks; the N tile lies inside one filter tap
+            const int ncol = n_idx * BN;
+            const int tap = ncol / p.conv_c, c0 = ncol - tap * p.conv_c;
+            const int kh = tap / p.conv_s, kw = tap - kh * p.conv_s;
+            const int m0 = kb * BK;
+            const int pq = p.conv_p * p.conv_q;
+            const int n0 = m0 / pq, rem = m0 - n0 * pq, oh0 = rem / p.conv_q, ow0 = rem - oh0 * p.conv_q;
+#pragma unroll
+            for (int a = 0; a < BN / 64; ++a)
+              tma_load_im2col(sb + a * (BK * 128), &tma_b, full_bar(stage), c0 + a * 64,
+                              ow0 * p.conv_stride - p.conv_pad, oh0 * p.conv_stride - p.conv_pad, n0, kw, kh);
+          } else if (B_MN) {
 #pragma unroll
             for (int a = 0; a < BN / 64; ++a)
               tma_load_2d(sb + a * (BK * 128), &tma_b, full_bar(stage), n_idx * BN + a * 64, kb * BK);
           } else {
             tma_load_2d(sb, &tma_b, full_bar(stage), kb * BK, n_idx * BN);
+          }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -1068,4 +1118,146 @@ extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, in
     KDL_CHECK_LAUNCH();
   }
   return KDL_OK;
+}
+
+
+// ------------------------------------------------------------------ N7: implicit-GEMM convolution
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_encode_im2col() {
+  static EncodeIm2colFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeIm2colFn)ptr;
+    else
+      cudaGetLastError();
+  }
+  return fn;
+}
+
+// NHWC bf16 activation [N,H,W,C] as an im2col tensor map: `pixels` output positions x 64 channels per load.
+static int make_im2col_map(CUtensorMap* map, const void* base, int N, int H, int W, int C, int R, int S,
+                           int stride, int pad, int pixels) {
+  EncodeIm2colFn enc = get_encode_im2col();
+  if (!enc) {
+    kdl_set_error("cuTensorMapEncodeIm2col unavailable (no CUDA driver?)");
+    return KDL_ERR_UNSUPPORTED;
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {-pad, -pad};
+  int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower,
+                   upper, 64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    kdl_set_error("cuTensorMapEncodeIm2col failed (%d): N=%d H=%d W=%d C=%d R=%d S=%d stride=%d pad=%d", (int)r, N,
+                  H, W, C, R, S, stride, pad);
+    return KDL_ERR_CUDA;
+  }
+  return KDL_OK;
+}
+
+extern "C" size_t kdl_conv2d_scratch_bytes(int mode, int N, int H, int W, int Cin, int Cout, int R, int S,
+                                           int stride, int pad) {
+  if (mode != 2) return 0;
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  return kdl_gemm_scratch_bytes(Cout, R * S * Cin, N * OH * OW, 0);
+}
+
+// mode 0 fprop : in0 = x [N,H,W,Cin],   in1 = w [Cout,R,S,Cin] -> out = y  [N,OH,OW,Cout]
+// mode 1 dgrad : in0 = dy [N,OH,OW,Cout], in1 = w              -> out = dx [N,H,W,Cin] (+addend); stride 1, 2*pad = R-1
+// mode 2 wgrad : in0 = dy,               in1 = x               -> out = dw [Cout,R,S,Cin] (split over pixels)
+extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N, int H, int W,
+                               int Cin, int Cout, int R, int S, int stride, int pad, const void* addend,
+                               void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  if (Cin % 64 || Cout % 64) {
+    kdl_set_error("conv2d: Cin and Cout must be multiples of 64 (Cin=%d Cout=%d)", Cin, Cout);
+    return KDL_ERR_UNSUPPORTED;
+  }
+  if (mode == 1 && (stride != 1 || 2 * pad != R - 1 || 2 * pad != S - 1)) {
+    kdl_set_error("conv2d dgrad: only stride 1 'same' convolutions are implemented");
+    return KDL_ERR_UNSUPPORTED;
+  }
+  GemmParams p = {};
+  CUtensorMap ma, mb, mc;
+  int rc;
+  p.conv_s = S; p.conv_r = R; p.conv_stride = stride; p.conv_pad = pad;
+  p.relu = 0; p.splits = 1;
+  if (mode == 0 || mode == 1) {
+    const int Cpatch = mode == 0 ? Cin : Cout;        // channels of the patch operand
+    const int Nout = mode == 0 ? Cout : Cin;
+    const int Hs = mode == 0 ? H : OH, Ws = mode == 0 ? W : OW;   // spatial dims of the patch tensor
+    const int P = mode == 0 ? OH : H, Q = mode == 0 ? OW : W;     // spatial dims the pixel index runs over
+    const int M = N * P * Q, K = R * S * Cpatch;
+    const int bn = Nout <= 64 ? 64 : 128;
+    p.C = (bf16*)out; p.M = M; p.N = Nout; p.K = K; p.ldc = Nout;
+    p.addend = (const bf16*)addend;
+    p.kb_per_split = (K + BK - 1) / BK;
+    p.num_m = (M + BM - 1) / BM; p.num_n = (Nout + bn - 1) / bn;
+    p.conv_mode = 1; p.conv_q = Q; p.conv_p = P; p.conv_c = Cpatch; p.conv_flip = mode == 1;
+    const int eff_pad = mode == 0 ? pad : (R - 1 - pad);
+    p.conv_pad = eff_pad;
+    rc = make_im2col_map(&ma, in0, N, Hs, Ws, Cpatch, R, S, mode == 0 ? stride : 1, eff_pad, BM);
+    if (rc) return rc;
+    if (mode == 0) rc = make_map(&mb, in1, (uint64_t)K, (uint64_t)Cout, (uint64_t)K, BK, (uint32_t)bn);
+    else rc = make_map(&mb, in1, (uint64_t)(R * S * Cin), (uint64_t)Cout, (uint64_t)(R * S * Cin), 64, BK);
+    if (rc) return rc;
+    rc = make_c_map(&mc, out, 0, (uint64_t)M, (uint64_t)Nout, (uint64_t)Nout, 1);
+    if (rc) return rc;
+    if (mode == 0) return bn == 64 ? launch<0, 0, 64, 6>(ma, mb, mc, p, stream) : launch<0, 0, 128, 5>(ma, mb, mc, p, stream);
+    return bn == 64 ? launch<0, 1, 64, 6>(ma, mb, mc, p, stream) : launch<0, 1, 128, 5>(ma, mb, mc, p, stream);
+  }
+  if (mode == 2) {
+    const int M = Cout, Nn = R * S * Cin, K = N * OH * OW;
+    const int bn = Cin <= 64 ? 64 : 128;
+    if (Cin % bn) {
+      kdl_set_error("conv2d wgrad: Cin must be a multiple of %d", bn);
+      return KDL_ERR_UNSUPPORTED;
+    }
+    const int splits = pick_splits(M, Nn, K, 0);
+    const int kb_total = (K + BK - 1) / BK;
+    p.C = (bf16*)out; p.M = M; p.N = Nn; p.K = K; p.ldc = Nn;
+    p.splits = splits; p.kb_per_split = (kb_total + splits - 1) / splits;
+    p.num_m = (M + BM - 1) / BM; p.num_n = Nn / bn;
+    p.conv_mode = 2; p.conv_q = OW; p.conv_p = OH; p.conv_c = Cin; p.conv_flip = 0;
+    if (splits > 1) {
+      size_t need = (size_t)splits * M * Nn * sizeof(float);
+      if (scratch == nullptr || scratch_bytes < need) {
+        kdl_set_error("conv2d wgrad: scratch too small (%zu < %zu)", scratch_bytes, need);
+        return KDL_ERR_WORKSPACE;
+      }
+      p.partial = (float*)scratch;
+    }
+    rc = make_map(&ma, in0, (uint64_t)Cout, (uint64_t)K, (uint64_t)Cout, 64, BK);   // dy^T: MN-major A
+    if (rc) return rc;
+    rc = make_im2col_map(&mb, in1, N, H, W, Cin, R, S, stride, pad, BK);
+    if (rc) return rc;
+    if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)Nn, (uint64_t)Nn, (uint64_t)splits);
+    else rc = make_c_map(&mc, out, 0, (uint64_t)M, (uint64_t)Nn, (uint64_t)Nn, 1);
+    if (rc) return rc;
+    rc = bn == 64 ? launch<1, 1, 64, 6>(ma, mb, mc, p, stream) : launch<1, 1, 128, 5>(ma, mb, mc, p, stream);
+    if (rc) return rc;
+    if (splits > 1) {
+      int64_t MN = (int64_t)M * Nn;
+      int64_t g = (MN + 255) / 256;
+      if (g > 148 * 8) g = 148 * 8;
+      splitk_reduce_kernel<<<(int)g, 256, 0, stream>>>(p.partial, (bf16*)out, MN, Nn, Nn, splits);
+      KDL_CHECK_LAUNCH();
+    }
+    return KDL_OK;
+  }
+  kdl_set_error("conv2d: unknown mode %d", mode);
+  return KDL_ERR_ARG;
 }

@@ -113,6 +113,17 @@ int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
                      const void* addend_bf16, int relu, int split_k, void* scratch, size_t scratch_bytes,
                      float* stats_partial, int* stats_parts_out, cudaStream_t stream);
 
+/* ---- N7: implicit-GEMM convolution on the same tcgen05 kernel (NHWC bf16) ------------------
+ * The activation operand is fetched with TMA im2col loads (no patch matrix in memory).  mode 0 =
+ * fprop (x, w -> y), 1 = dgrad (dy, w -> dx [+addend]; stride-1 "same" convolutions), 2 = wgrad
+ * (dy, x -> dw, split over the pixels, `scratch` of kdl_conv2d_scratch_bytes()).  Cin, Cout
+ * multiples of 64.  Replaces the cuDNN convolutions of the stock worker. */
+size_t kdl_conv2d_scratch_bytes(int mode, int N, int H, int W, int Cin, int Cout, int R, int S, int stride,
+                                int pad);
+int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N, int H, int W, int Cin,
+                    int Cout, int R, int S, int stride, int pad, const void* addend_bf16, void* scratch,
+                    size_t scratch_bytes, cudaStream_t stream);
+
 /* ---- N3: histogram GBDT, histogram build fused with the cross-GPU reduction ---------------
  * Replaces XGBoost gpu_hist + ncclAllReduce of histograms, for which the reference only injects
  * the tracker address (reference controllers/xgboost/pod.go:106-152).  peer_local / flag_ptrs are

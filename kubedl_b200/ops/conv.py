@@ -1,0 +1,60 @@
+"""Implicit-GEMM convolution on the tcgen05 kernel with TMA im2col operand loads (kernel N7).
+NHWC bf16 activations, weights [Cout, R, S, Cin]."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import lib as L
+from .nn import workspace
+
+L.register_signatures({
+    "kdl_conv2d_scratch_bytes": (C.c_size_t, [C.c_int] * 10),
+    "kdl_conv2d_bf16": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 9 +
+                        [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+})
+
+
+def _chk(t):
+    assert t.dtype == torch.bfloat16 and t.is_cuda and t.is_contiguous(), (t.dtype, t.shape)
+
+
+def _run(mode, in0, in1, out, N, H, W, Cin, Cout, R, S, stride, pad, addend=None):
+    lib = L.lib()
+    nb = lib.kdl_conv2d_scratch_bytes(mode, N, H, W, Cin, Cout, R, S, stride, pad)
+    ws = workspace(nb, out.device, key="gemm_splitk") if nb else None
+    L.check(lib.kdl_conv2d_bf16(mode, in0.data_ptr(), in1.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout, R, S,
+                                stride, pad, L.ptr(addend), L.ptr(ws), ws.numel() if ws is not None else 0,
+                                L.stream_ptr()), "kdl_conv2d_bf16")
+    L.count(2 if (mode == 2 and nb) else 1)
+    return out
+
+
+def fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
+    _chk(x); _chk(w)
+    N, H, W, Cin = x.shape
+    Cout, R, S, _ = w.shape
+    OH, OW = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    y = torch.empty(N, OH, OW, Cout, dtype=torch.bfloat16, device=x.device)
+    return _run(0, x, w, y, N, H, W, Cin, Cout, R, S, stride, pad)
+
+
+def dgrad(dy: torch.Tensor, w: torch.Tensor, in_hw, stride: int, pad: int,
+          addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _chk(dy); _chk(w)
+    N, OH, OW, Cout = dy.shape
+    _, R, S, Cin = w.shape
+    H, W = in_hw
+    dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device=dy.device)
+    return _run(1, dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad, addend)
+
+
+def wgrad(dy: torch.Tensor, x: torch.Tensor, R: int, S: int, stride: int, pad: int,
+          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _chk(dy); _chk(x)
+    N, H, W, Cin = x.shape
+    Cout = dy.shape[-1]
+    dw = out if out is not None else torch.empty(Cout, R, S, Cin, dtype=torch.bfloat16, device=x.device)
+    return _run(2, dy, x, dw, N, H, W, Cin, Cout, R, S, stride, pad)

@@ -1,0 +1,42 @@
+"""Implicit-GEMM convolution (TMA im2col + tcgen05, kernel N7) vs torch conv2d in fp32."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cos(a, b):
+    a, b = a.flatten().float(), b.flatten().float()
+    return float((a @ b) / (a.norm() * b.norm() + 1e-12))
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,R,stride,pad", [
+    (8, 56, 64, 64, 3, 1, 1), (4, 28, 128, 128, 3, 1, 1), (3, 14, 256, 256, 3, 1, 1),
+    (4, 56, 128, 128, 3, 2, 1), (2, 14, 512, 512, 3, 1, 1), (5, 20, 64, 192, 3, 1, 1),
+])
+def test_conv_fprop_dgrad_wgrad(cuda, N, H, Cin, Cout, R, stride, pad):
+    from kubedl_b200.ops import conv
+    torch.manual_seed(0)
+    x = torch.randn(N, H, H, Cin, device=cuda).bfloat16()
+    w = (torch.randn(Cout, R, R, Cin, device=cuda) * 0.05).bfloat16()
+    xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    wr = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xr, wr, stride=stride, padding=pad)
+    y = conv.fprop(x, w, stride, pad)
+    assert y.shape == yr.permute(0, 2, 3, 1).shape
+    err = float((y.float() - yr.permute(0, 2, 3, 1)).abs().max() / yr.abs().max())
+    assert err < 1.5e-2, err
+    dy = torch.randn_like(y)
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    dw = conv.wgrad(dy, x, R, R, stride, pad)
+    assert _cos(dw, wr.grad.permute(0, 2, 3, 1)) > 0.999
+    err = float((dw.float() - wr.grad.permute(0, 2, 3, 1)).abs().max() / wr.grad.abs().max())
+    assert err < 2e-2, err
+    if stride == 1:
+        dx = conv.dgrad(dy, w, (H, H), stride, pad)
+        err = float((dx.float() - xr.grad.permute(0, 2, 3, 1)).abs().max() / xr.grad.abs().max())
+        assert err < 1.5e-2, err
+        add = torch.randn_like(dx)
+        dx2 = conv.dgrad(dy, w, (H, H), stride, pad, addend=add)
+        err = float((dx2.float() - (xr.grad.permute(0, 2, 3, 1) + add.float())).abs().max() / xr.grad.abs().max())
+        assert err < 2e-2, err

@@ -520,7 +520,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 // The leader CTA (rank 0) issues every MMA; TMA loads of both CTAs complete on the leader's
 // "full" barrier, commits are multicast to both CTAs' "empty" / "tmem full" barriers, and both
 // CTAs' epilogue warps arrive on the leader's "tmem empty" barrier.
-constexpr int BN2 = 256;
 constexpr int STAGES2 = 5;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -564,6 +563,7 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
       : "memory");
 }
 
+template <int BN2>
 struct SmemLayout2 {
   static constexpr int kABytes = BM * BK * 2;            // this CTA's 128 rows of A
   static constexpr int kBBytes = (BN2 / 2) * BK * 2;     // this CTA's half of B
@@ -575,12 +575,22 @@ struct SmemLayout2 {
   static constexpr int kTotal = kBarOffset + (2 * STAGES2 + 4) * 8 + 16;
 };
 
-template <int A_MN, int B_MN>
+__device__ __forceinline__ void tma_load_im2col_2sm(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar,
+                                                    int c, int w, int h, int n, int off_w, int off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w),
+      "h"((uint16_t)off_h)
+      : "memory");
+}
+
+template <int A_MN, int B_MN, int BN2>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b,
                          const __grid_constant__ CUtensorMap tma_c, const GemmParams p) {
-  using SL = SmemLayout2;
+  using SL = SmemLayout2<BN2>;
   constexpr int STAGES = STAGES2;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t smem_base = smem_u32(smem);
@@ -599,7 +609,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
   if (p.stats) {
     for (int i = threadIdx.x; i < 2 * kStatsMaxN; i += kGemmThreads) cta_stats[i] = 0.f;
   }
-  constexpr uint32_t kTmemCols = 2 * BN2;   // 512: two accumulator stages
+  constexpr uint32_t kTmemCols = 2 * BN2;   // two accumulator stages (256 or 512 columns)
   constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit: address of the leader's copy
 
   if (warp == 0 && lane == 0) {
@@ -632,7 +642,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
 
   const int num_pairs = gridDim.x / 2;
   const int pair = blockIdx.x / 2;
-  const int total_tiles = p.num_m * p.num_n;    // tiles of 256 x 256
+  const int total_tiles = p.num_m * p.num_n * p.splits;    // tiles of 256 x BN2 (x K splits)
   const int kb_total = (p.K + BK - 1) / BK;
 
   if (warp == 0) {
@@ -641,14 +651,34 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       uint32_t phase = 0;
       for (int t = pair; t < total_tiles; t += num_pairs) {
         const int n_idx = t % p.num_n;
-        const int m_idx = t / p.num_n;
+        const int m_idx = (t / p.num_n) % p.num_m;
+        const int split = t / (p.num_n * p.num_m);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
         const int m0 = m_idx * 256 + (int)cta * BM;
         const int n0 = n_idx * BN2 + (int)cta * (BN2 / 2);
-        for (int kb = 0; kb < kb_total; ++kb) {
+        const int pq = p.conv_p * p.conv_q;
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * SL::kStageBytes;
           const uint32_t sb = sa + SL::kABytes;
           const uint32_t lbar = full_bar(stage) & kPeerMask;
+          if (p.conv_mode == 1) {
+            const int cblks = p.conv_c / BK;
+            const int tap = kb / cblks, cb = kb - tap * cblks;
+            const int kh = tap / p.conv_s, kw = tap - kh * p.conv_s;
+            const int in0 = m0 / pq, rem = m0 - in0 * pq, oh0 = rem / p.conv_q, ow0 = rem - oh0 * p.conv_q;
+            const int fh = p.conv_flip ? p.conv_r - 1 - kh : kh, fw = p.conv_flip ? p.conv_s - 1 - kw : kw;
+            tma_load_im2col_2sm(sa, &tma_a, lbar, cb * BK, ow0 * p.conv_stride - p.conv_pad,
+                                oh0 * p.conv_stride - p.conv_pad, in0, fw, fh);
+            if (B_MN) {
+#pragma unroll
+              for (int a = 0; a < (BN2 / 2) / 64; ++a)
+                tma_load_2d_2sm(sb + a * (BK * 128), &tma_b, lbar, tap * p.N + n0 + a * 64, cb * BK);
+            } else {
+              tma_load_2d_2sm(sb, &tma_b, lbar, kb * BK, n0);
+            }
+          } else {
           if (A_MN) {
 #pragma unroll
             for (int a = 0; a < BM / 64; ++a)
@@ -656,12 +686,22 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
           } else {
             tma_load_2d_2sm(sa, &tma_a, lbar, kb * BK, m0);
           }
-          if (B_MN) {
+          if (p.conv_mode == 2) {
+            const int tap = n0 / p.conv_c, c0 = n0 - tap * p.conv_c;
+            const int kh = tap / p.conv_s, kw = tap - kh * p.conv_s;
+            const int px = kb * BK;
+            const int in0 = px / pq, rem = px - in0 * pq, oh0 = rem / p.conv_q, ow0 = rem - oh0 * p.conv_q;
+#pragma unroll
+            for (int a = 0; a < (BN2 / 2) / 64; ++a)
+              tma_load_im2col_2sm(sb + a * (BK * 128), &tma_b, lbar, c0 + a * 64, ow0 * p.conv_stride - p.conv_pad,
+                                  oh0 * p.conv_stride - p.conv_pad, in0, kw, kh);
+          } else if (B_MN) {
 #pragma unroll
             for (int a = 0; a < (BN2 / 2) / 64; ++a)
               tma_load_2d_2sm(sb + a * (BK * 128), &tma_b, lbar, n0 + a * 64, kb * BK);
           } else {
             tma_load_2d_2sm(sb, &tma_b, lbar, kb * BK, n0);
+          }
           }
           if (leader) mbar_expect_tx(full_bar(stage), 2 * SL::kStageBytes);
           else mbar_arrive_remote(full_bar(stage), 0);
@@ -678,12 +718,15 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       uint32_t phase = 0;
       int iter = 0;
       for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
+        const int split = t / (p.num_n * p.num_m);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
         const int as = iter & 1;
         const uint32_t aphase = (iter >> 1) & 1;
         mbar_wait(tempty_bar(as), aphase ^ 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + as * BN2;
-        for (int kb = 0; kb < kb_total; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tcgen05_fence_after();
           const uint32_t sa = smem_base + stage * SL::kStageBytes;
@@ -692,10 +735,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t ad = make_desc<A_MN>(sa + k_advance_bytes<A_MN>(k));
             const uint64_t bd = make_desc<B_MN>(sb + k_advance_bytes<B_MN>(k));
-            umma_bf16_2sm(tmem_d, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_bf16_2sm(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit_2sm(empty_bar(stage));
-          if (kb == kb_total - 1) umma_commit_2sm(tfull_bar(as));
+          if (kb == kb1 - 1) umma_commit_2sm(tfull_bar(as));
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -710,7 +753,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     int buf = 0;
     for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
       const int n_idx = t % p.num_n;
-      const int m_idx = t / p.num_n;
+      const int m_idx = (t / p.num_n) % p.num_m;
+      const int split = t / (p.num_n * p.num_m);
       const int as = iter & 1;
       const uint32_t aphase = (iter >> 1) & 1;
       mbar_wait(tfull_bar(as), aphase);
@@ -718,6 +762,28 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       const int row0 = m_idx * 256 + (int)cta * BM + q * 32;
       const int row = row0 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN2;
+      if (p.partial != nullptr) {
+#pragma unroll 1
+        for (int c0 = half * 32; c0 < BN2; c0 += 32 * (kEpiWarps / 4)) {
+          uint32_t r[32];
+          tmem_ld32(taddr + c0, r);
+          tmem_ld_wait();
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
+                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d(&tma_c, stg_base + buf * 4096, n_idx * BN2 + c0, row0, split);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        }
+      } else
 #pragma unroll 1
       for (int c0 = half * 64; c0 < BN2; c0 += 64 * (kEpiWarps / 4)) {
         uint32_t r[64];
@@ -918,17 +984,17 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
   return KDL_OK;
 }
 
-template <int A_MN, int B_MN>
+template <int A_MN, int B_MN, int BN2 = 256>
 static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
                        const GemmParams& p, cudaStream_t stream) {
-  using SL = SmemLayout2;
-  auto kern = gemm_tcgen05_2cta_kernel<A_MN, B_MN>;
+  using SL = SmemLayout2<BN2>;
+  auto kern = gemm_tcgen05_2cta_kernel<A_MN, B_MN, BN2>;
   static bool attr_done = false;
   if (!attr_done) {
     KDL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::kTotal + 1024));
     attr_done = true;
   }
-  int tiles = p.num_m * p.num_n;
+  int tiles = p.num_m * p.num_n * (p.splits > 0 ? p.splits : 1);
   int pairs = num_sms() / 2;
   if (tiles < pairs) pairs = tiles;
   cudaLaunchConfig_t cfg = {};
@@ -1082,14 +1148,14 @@ extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, in
   else rc = make_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
   if (rc) return rc;
   if (b_mn_major) rc = make_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
-  else rc = make_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, two ? (uint32_t)(BN2 / 2) : (uint32_t)bn);
+  else rc = make_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, two ? (uint32_t)128 : (uint32_t)bn);
   if (rc) return rc;
   if (two) {
     CUtensorMap mc2;
     rc = make_c_map(&mc2, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);
     if (rc) return rc;
     p.num_m = (M + 255) / 256;
-    p.num_n = (N + BN2 - 1) / BN2;
+    p.num_n = (N + 255) / 256;
     if (stats_parts_out) {
       int tiles2 = p.num_m * p.num_n, pairs = num_sms() / 2;
       *stats_parts_out = 2 * (tiles2 < pairs ? tiles2 : pairs);
@@ -1172,7 +1238,10 @@ extern "C" size_t kdl_conv2d_scratch_bytes(int mode, int N, int H, int W, int Ci
                                            int stride, int pad) {
   if (mode != 2) return 0;
   const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
-  return kdl_gemm_scratch_bytes(Cout, R * S * Cin, N * OH * OW, 0);
+  size_t a = kdl_gemm_scratch_bytes(Cout, R * S * Cin, N * OH * OW, 0);
+  size_t b = (size_t)148 * Cout * R * S * Cin * sizeof(float) / 1;   // upper bound for the 2-CTA split choice
+  if (b > ((size_t)64 * Cout * R * S * Cin * sizeof(float))) b = (size_t)64 * Cout * R * S * Cin * sizeof(float);
+  return a > b ? a : b;
 }
 
 // mode 0 fprop : in0 = x [N,H,W,Cin],   in1 = w [Cout,R,S,Cin] -> out = y  [N,OH,OW,Cout]
@@ -1211,11 +1280,32 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
     p.conv_pad = eff_pad;
     rc = make_im2col_map(&ma, in0, N, Hs, Ws, Cpatch, R, S, mode == 0 ? stride : 1, eff_pad, BM);
     if (rc) return rc;
-    if (mode == 0) rc = make_map(&mb, in1, (uint64_t)K, (uint64_t)Cout, (uint64_t)K, BK, (uint32_t)bn);
+    static int conv2 = -1;
+    if (conv2 < 0) {
+      const char* e = getenv("KDL_CONV_2CTA");
+      conv2 = e ? atoi(e) : 1;
+    }
+    const bool two = conv2 && M >= 1024 && Nout >= 128;
+    // N tile of the CTA pair: 256 unless 128 fills the 74 pairs better (wave quantisation)
+    int bn2 = 128;
+    if (Nout >= 256) {
+      const int pairs = kdl_gemm_max_ctas() / 2, nm = (M + 255) / 256;
+      const int c256 = ((nm * ((Nout + 255) / 256) + pairs - 1) / pairs) * 256;
+      const int c128 = ((nm * ((Nout + 127) / 128) + pairs - 1) / pairs) * 128;
+      bn2 = c128 < c256 ? 128 : 256;
+    }
+    const uint32_t brows = two ? (uint32_t)(bn2 / 2) : (uint32_t)bn;
+    if (mode == 0) rc = make_map(&mb, in1, (uint64_t)K, (uint64_t)Cout, (uint64_t)K, BK, brows);
     else rc = make_map(&mb, in1, (uint64_t)(R * S * Cin), (uint64_t)Cout, (uint64_t)(R * S * Cin), 64, BK);
     if (rc) return rc;
     rc = make_c_map(&mc, out, 0, (uint64_t)M, (uint64_t)Nout, (uint64_t)Nout, 1);
     if (rc) return rc;
+    if (two) {
+      p.num_m = (M + 255) / 256;
+      p.num_n = (Nout + bn2 - 1) / bn2;
+      if (mode == 0) return bn2 == 256 ? launch_2cta<0, 0, 256>(ma, mb, mc, p, stream) : launch_2cta<0, 0, 128>(ma, mb, mc, p, stream);
+      return bn2 == 256 ? launch_2cta<0, 1, 256>(ma, mb, mc, p, stream) : launch_2cta<0, 1, 128>(ma, mb, mc, p, stream);
+    }
     if (mode == 0) return bn == 64 ? launch<0, 0, 64, 6>(ma, mb, mc, p, stream) : launch<0, 0, 128, 5>(ma, mb, mc, p, stream);
     return bn == 64 ? launch<0, 1, 64, 6>(ma, mb, mc, p, stream) : launch<0, 1, 128, 5>(ma, mb, mc, p, stream);
   }
@@ -1226,8 +1316,25 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
       kdl_set_error("conv2d wgrad: Cin must be a multiple of %d", bn);
       return KDL_ERR_UNSUPPORTED;
     }
-    const int splits = pick_splits(M, Nn, K, 0);
+    static int conv2w = -1;
+    if (conv2w < 0) {
+      const char* e = getenv("KDL_CONV_2CTA");
+      conv2w = e ? atoi(e) : 1;
+    }
+    const bool two = conv2w && Cout >= 256 && Cin >= 128;
     const int kb_total = (K + BK - 1) / BK;
+    int splits;
+    if (two) {
+      int tiles2 = ((M + 255) / 256) * (Nn / 256 + ((Nn % 256) ? 1 : 0));
+      splits = (148 + tiles2 - 1) / tiles2;
+      if (splits > kb_total / 4) splits = kb_total / 4;
+      if (splits < 1) splits = 1;
+      if (splits > 64) splits = 64;
+      int per = (kb_total + splits - 1) / splits;
+      splits = (kb_total + per - 1) / per;
+    } else {
+      splits = pick_splits(M, Nn, K, 0);
+    }
     p.C = (bf16*)out; p.M = M; p.N = Nn; p.K = K; p.ldc = Nn;
     p.splits = splits; p.kb_per_split = (kb_total + splits - 1) / splits;
     p.num_m = (M + BM - 1) / BM; p.num_n = Nn / bn;
@@ -1247,7 +1354,13 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
     if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)Nn, (uint64_t)Nn, (uint64_t)splits);
     else rc = make_c_map(&mc, out, 0, (uint64_t)M, (uint64_t)Nn, (uint64_t)Nn, 1);
     if (rc) return rc;
-    rc = bn == 64 ? launch<1, 1, 64, 6>(ma, mb, mc, p, stream) : launch<1, 1, 128, 5>(ma, mb, mc, p, stream);
+    if (two) {
+      p.num_m = (M + 255) / 256;
+      p.num_n = (Nn + 255) / 256;
+      rc = launch_2cta<1, 1, 256>(ma, mb, mc, p, stream);
+    } else {
+      rc = bn == 64 ? launch<1, 1, 64, 6>(ma, mb, mc, p, stream) : launch<1, 1, 128, 5>(ma, mb, mc, p, stream);
+    }
     if (rc) return rc;
     if (splits > 1) {
       int64_t MN = (int64_t)M * Nn;

@@ -18,6 +18,7 @@ from typing import List, Optional, Tuple
 
 import torch
 
+from ..ops import conv as conv_ops
 from ..ops import nn as K
 from .arena import ParamArena
 
@@ -46,6 +47,9 @@ class Conv:
         self.gw = a.grad(self.name).permute(0, 3, 1, 2)
         self.g_end = a.end_offset(self.name)
         self.is_gemm = (self.k == 1 and self.stride == 1)
+        # 3x3 convolutions on the TMA-im2col implicit GEMM (kernel N7) instead of cuDNN
+        self.own_conv = (self.k == 3 and self.net.own_conv and self.net.gemm is not None
+                         and self.cin % 64 == 0)
 
     def fwd(self, x: torch.Tensor, want_stats: bool = False):
         """want_stats: also return the BN column statistics produced by the GEMM epilogue (None on
@@ -57,6 +61,9 @@ class Conv:
                 y, stats = net.gemm.nt_stats(x.view(-1, Cin), self.w.view(self.cout, Cin))
                 return y.view(N, H, W, self.cout), stats
             y = net.gemm.nt(x.view(-1, Cin), self.w.view(self.cout, Cin)).view(N, H, W, self.cout)
+            return (y, None) if want_stats else y
+        if self.own_conv:
+            y = conv_ops.fprop(x, self.w, self.stride, self.pad)
             return (y, None) if want_stats else y
         y = torch.ops.aten.convolution(_nchw(x), self.w_nchw, None, [self.stride] * 2,
                                        [self.pad] * 2, [1, 1], False, [0, 0], 1)
@@ -76,6 +83,17 @@ class Conv:
             if need_dx:
                 dx = net.gemm.nn(dy2, self.w.view(self.cout, Cin),
                                  addend=None if addend is None else addend.view(-1, Cin)).view(N, H, W, Cin)
+        elif self.own_conv:
+            conv_ops.wgrad(dy, x, self.k, self.k, self.stride, self.pad, out=net.arena.grad(self.name))
+            dx = None
+            if need_dx and self.stride == 1:
+                dx = conv_ops.dgrad(dy, self.w, x.shape[1:3], 1, self.pad, addend=addend)
+            elif need_dx:     # strided dgrad: cuDNN
+                dxn, _, _ = _conv_bwd(_nchw(dy), _nchw(x), self.w_nchw, None, [self.stride] * 2,
+                                      [self.pad] * 2, [1, 1], False, [0, 0], 1, [True, False, False])
+                dx = _nhwc(dxn)
+                if addend is not None:
+                    K.add_(dx, addend)
         else:
             dxn, dw, _ = _conv_bwd(_nchw(dy), _nchw(x), self.w_nchw, None, [self.stride] * 2,
                                    [self.pad] * 2, [1, 1], False, [0, 0], 1, [need_dx, True, False])
@@ -188,6 +206,9 @@ class ResNet50:
         # end to end (24.4 vs 23.1 ms/step) because the epilogue warps are already the bottleneck of
         # the memory-bound 1x1-conv GEMMs; off unless asked for.
         self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "0") == "1"
+        # 3x3 convolutions through our implicit-GEMM kernel (N7) instead of cuDNN; off by default
+        # until it wins on every ResNet shape (profiles/conv3x3_vs_cudnn_*.log)
+        self.own_conv = _os.environ.get("KUBEDL_OWN_CONV", "0") == "1"
         self.num_classes = num_classes
         self.arena = ParamArena()
         self.gemm = gemm

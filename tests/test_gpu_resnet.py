@@ -111,8 +111,8 @@ def test_trainer_graph_replay_matches_eager(cuda):
 
 @pytest.mark.parametrize("block,shape", [((0, 0), (8, 28, 28, 64)), ((1, 1), (8, 14, 14, 512)),
                                          ((2, 0), (8, 14, 14, 512))])
-@pytest.mark.parametrize("use_gemm", [False, True])
-def test_bottleneck_block_fwd_bwd(cuda, block, shape, use_gemm):
+@pytest.mark.parametrize("use_gemm", [False, True, "own_conv"])
+def test_bottleneck_block_fwd_bwd(cuda, block, shape, use_gemm, monkeypatch):
     """One bottleneck in isolation (errors do not compound): outputs, input gradient and every
     parameter gradient against the fp32 torchvision block with identical weights."""
     import torchvision
@@ -121,7 +121,10 @@ def test_bottleneck_block_fwd_bwd(cuda, block, shape, use_gemm):
     if use_gemm:
         G = pytest.importorskip("kubedl_b200.ops.gemm")
         gemm = G.Gemm(cuda)
+    if use_gemm == "own_conv":      # 3x3 convolutions on the implicit-GEMM kernel (N7) too
+        monkeypatch.setenv("KUBEDL_OWN_CONV", "1")
     net = ResNet50(cuda, gemm=gemm, seed=11)
+    assert net.own_conv == (use_gemm == "own_conv")
     tv = torchvision.models.resnet50().to(cuda).float().train()
     _load_into_torchvision(net, tv)
     li, bi = block

@@ -18,6 +18,7 @@
 // and FC layer and for the DIN MLP; the reference operator itself has no math at all
 // (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15 just names a worker image).
 #include "common.cuh"
+#include "tcgen05.cuh"
 #include "../include/kubedl_b200.h"
 #include <cuda.h>
 #include <string.h>
@@ -26,8 +27,6 @@
 namespace kdl {
 
 constexpr int BM = 128;       // UMMA M (cta_group::1)
-constexpr int BK = 64;        // 64 bf16 = 128 B = one swizzle row
-constexpr int UMMA_K = 16;
 // 4 control warps + kEpiWarps epilogue warps.  8 epilogue warps (two per TMEM lane quarter, alternating
 // column chunks) were measured: they hide the fused-statistics epilogue but cost a pipeline stage of
 // shared memory and ~5 % on compute-bound shapes (profiles/gemm_vs_cublas_shapes.log), so 4 it is.
@@ -77,130 +76,6 @@ __device__ __forceinline__ void chunk_col_stats(const uint8_t* buf, int lane, in
   const int c = col0 + 2 * lane;
   if (c < N) { atomicAdd(cta_stats + c, s0); atomicAdd(cta_stats + kStatsMaxN + c, q0); }
   if (c + 1 < N) { atomicAdd(cta_stats + c + 1, s1); atomicAdd(cta_stats + kStatsMaxN + c + 1, q1); }
-}
-
-// ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  } while (!ok);
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
-                                            int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-// TMA im2col load: `pixels` consecutive output positions (W fastest, wrapping over H and N inside the
-// bounding box of the tensor map) x 64 channels of filter tap (off_w, off_h), zero-filled padding.
-__device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c,
-                                                int w, int h, int n, int off_w, int off_h) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w),
-      "h"((uint16_t)off_h)
-      : "memory");
-}
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-               ::"l"(map), "r"(src), "r"(c0), "r"(c1)
-               : "memory");
-}
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1,
-                                             int c2) {
-  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2)
-               : "memory");
-}
-__device__ __forceinline__ void tma_store_commit() {
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-template <int N>
-__device__ __forceinline__ void tma_store_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async_smem() {
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() {
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_after() {
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
-                                          uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
-               ::"r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
-        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
-        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
-        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
-        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() {
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// Shared-memory matrix descriptor (sm_100 "version 1", 128-byte swizzle).
-//   K-major : rows of 128 B (64 bf16 along K); 8-row atoms 1024 B apart (SBO); LBO unused.
-//   MN-major: rows of 128 B (64 bf16 along M/N) for consecutive K; atoms of 8 K-rows 1024 B
-//             apart (SBO), 64-wide M/N atoms BK*128 B apart (LBO).
-template <int MN_MAJOR>
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
-  const uint32_t lbo = MN_MAJOR ? (BK * 128) : 0;
-  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((1024 >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;  // descriptor version (sm_100)
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
-  return d;
-}
-// byte advance of the start address for the k-th UMMA_K slice inside a BK block
-template <int MN_MAJOR>
-__device__ __forceinline__ uint32_t k_advance_bytes(int k) {
-  return MN_MAJOR ? (uint32_t)k * UMMA_K * 128u : (uint32_t)k * UMMA_K * 2u;
 }
 
 template <int A_MN, int B_MN, int BN>
@@ -346,7 +221,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else if (warp == 1) {
     // ============================== MMA issuer ==============================
-    if (lane == 0) {
+    // The whole warp walks the loop and one elected lane issues (predicate inside the asm): with no
+    // divergent branch around it ptxas keeps descriptors in uniform registers, instead of an
+    // ELECT / R2UR broadcast loop in front of every UTCHMMA (which made the issue path, not the
+    // tensor pipe, the limit for N <= 128 tiles).
+    {
+      const uint32_t el = elect_one();
       constexpr uint32_t idesc = make_idesc<A_MN, B_MN, BN>();
       int stage = 0;
       uint32_t phase = 0;
@@ -364,15 +244,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           mbar_wait(full_bar(stage), phase);
           tcgen05_fence_after();
           const uint32_t sa = smem_base + stage * SL::kStageBytes;
-          const uint32_t sb = sa + SL::kABytes;
+          const uint64_t ad0 = make_desc<A_MN>(sa);
+          const uint64_t bd0 = make_desc<B_MN>(sa + SL::kABytes);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = make_desc<A_MN>(sa + k_advance_bytes<A_MN>(k));
-            const uint64_t bd = make_desc<B_MN>(sb + k_advance_bytes<B_MN>(k));
-            umma_bf16(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_bf16_pred(tmem_d, ad0 + (uint64_t)(k_advance_bytes<A_MN>(k) >> 4),
+                           bd0 + (uint64_t)(k_advance_bytes<B_MN>(k) >> 4), idesc,
+                           (kb > kb0 || k > 0) ? 1u : 0u, el);
           }
-          umma_commit(empty_bar(stage));  // frees the smem stage once these MMAs retire
-          if (kb == kb1 - 1) umma_commit(tfull_bar(as));
+          umma_commit_pred(empty_bar(stage), el);  // frees the smem stage once these MMAs retire
+          if (kb == kb1 - 1) umma_commit_pred(tfull_bar(as), el);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -563,6 +444,25 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
       : "memory");
 }
 
+__device__ __forceinline__ void umma_bf16_2sm_pred(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                                   uint32_t idesc, uint32_t accumulate, uint32_t el) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(el)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm_pred(uint32_t bar, uint32_t el) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "setp.ne.b32 q, %2, 0;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+      ::"r"(bar), "h"((uint16_t)3), "r"(el)
+      : "memory");
+}
+
 template <int BN2>
 struct SmemLayout2 {
   static constexpr int kABytes = BM * BK * 2;            // this CTA's 128 rows of A
@@ -710,7 +610,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       }
     }
   } else if (warp == 1) {
-    if (leader && lane == 0) {
+    if (leader) {
+      const uint32_t el = elect_one();   // whole warp walks the loop, one lane issues (see 1-CTA kernel)
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)A_MN << 15) |
                                  ((uint32_t)B_MN << 16) | ((uint32_t)(BN2 >> 3) << 17) |
                                  ((uint32_t)(256 >> 4) << 24);
@@ -730,15 +631,16 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
           mbar_wait(full_bar(stage), phase);
           tcgen05_fence_after();
           const uint32_t sa = smem_base + stage * SL::kStageBytes;
-          const uint32_t sb = sa + SL::kABytes;
+          const uint64_t ad0 = make_desc<A_MN>(sa);
+          const uint64_t bd0 = make_desc<B_MN>(sa + SL::kABytes);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = make_desc<A_MN>(sa + k_advance_bytes<A_MN>(k));
-            const uint64_t bd = make_desc<B_MN>(sb + k_advance_bytes<B_MN>(k));
-            umma_bf16_2sm(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_bf16_2sm_pred(tmem_d, ad0 + (uint64_t)(k_advance_bytes<A_MN>(k) >> 4),
+                               bd0 + (uint64_t)(k_advance_bytes<B_MN>(k) >> 4), idesc,
+                               (kb > kb0 || k > 0) ? 1u : 0u, el);
           }
-          umma_commit_2sm(empty_bar(stage));
-          if (kb == kb1 - 1) umma_commit_2sm(tfull_bar(as));
+          umma_commit_2sm_pred(empty_bar(stage), el);
+          if (kb == kb1 - 1) umma_commit_2sm_pred(tfull_bar(as), el);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -1286,14 +1188,10 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
       conv2 = e ? atoi(e) : 1;
     }
     const bool two = conv2 && M >= 1024 && Nout >= 128;
-    // N tile of the CTA pair: 256 unless 128 fills the 74 pairs better (wave quantisation)
-    int bn2 = 128;
-    if (Nout >= 256) {
-      const int pairs = kdl_gemm_max_ctas() / 2, nm = (M + 255) / 256;
-      const int c256 = ((nm * ((Nout + 255) / 256) + pairs - 1) / pairs) * 256;
-      const int c128 = ((nm * ((Nout + 127) / 128) + pairs - 1) / pairs) * 128;
-      bn2 = c128 < c256 ? 128 : 256;
-    }
+    // N tile of the CTA pair.  (A 128-wide tile would fill the 74 pairs better for Cout = 512 at 7x7,
+    // but the loop is bound by the im2col TMA rate per 128-pixel load, not by the MMA, so the wider
+    // tile that amortises each load over more columns wins: measured 0.070 vs 0.098 ms.)
+    const int bn2 = Nout >= 256 ? 256 : 128;
     const uint32_t brows = two ? (uint32_t)(bn2 / 2) : (uint32_t)bn;
     if (mode == 0) rc = make_map(&mb, in1, (uint64_t)K, (uint64_t)Cout, (uint64_t)K, BK, brows);
     else rc = make_map(&mb, in1, (uint64_t)(R * S * Cin), (uint64_t)Cout, (uint64_t)(R * S * Cin), 64, BK);

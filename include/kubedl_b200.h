@@ -124,6 +124,24 @@ int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N
                     int Cout, int R, int S, int stride, int pad, const void* addend_bf16, void* scratch,
                     size_t scratch_bytes, cudaStream_t stream);
 
+/* ---- N7b: 3x3 / stride-1 / pad-1 convolution with the input halo resident in shared memory ----
+ * One tiled TMA box per 64 channels brings a (rows+2) x (W+2) input halo into shared memory; the nine
+ * filter taps are row-shifted UMMA descriptor windows over that one buffer, the CTA's weights stay
+ * resident.  mode 0 = fprop, 1 = dgrad (optionally + addend, ReLU).  Supported when Cin, Cout are
+ * multiples of 64, the weights of 64 output channels fit next to two halo buffers (C <= 128) and
+ * some divisor TR of H has TR*(W+2) <= 128 — ask kdl_conv3x3_halo_supported().  No reference
+ * counterpart (the operator launches pods; cuDNN would run this in the stock worker). */
+int kdl_conv3x3_halo_supported(int mode, int N, int H, int W, int Cin, int Cout);
+int kdl_conv3x3_halo_bf16(int mode, const void* in0, const void* w, void* out, int N, int H, int W, int Cin,
+                          int Cout, const void* addend_bf16, int relu, cudaStream_t stream);
+/* wgrad of the same convolution (Cin, Cout <= 128): the pixel index is the MMA K dimension, every CTA
+ * owns one filter row and keeps its 3 x Cin accumulator columns in TMEM across all of its pixel tiles;
+ * fp32 partials in `scratch` (kdl_conv3x3_halo_wgrad_scratch_bytes(), 0 = shape unsupported) are reduced
+ * in a fixed order by a second kernel. */
+size_t kdl_conv3x3_halo_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout);
+int kdl_conv3x3_halo_wgrad_bf16(const void* dy, const void* x, void* dw, int N, int H, int W, int Cin, int Cout,
+                                void* scratch, size_t scratch_bytes, cudaStream_t stream);
+
 /* ---- N3: histogram GBDT, histogram build fused with the cross-GPU reduction ---------------
  * Replaces XGBoost gpu_hist + ncclAllReduce of histograms, for which the reference only injects
  * the tracker address (reference controllers/xgboost/pod.go:106-152).  peer_local / flag_ptrs are

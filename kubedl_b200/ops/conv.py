@@ -14,7 +14,30 @@ L.register_signatures({
     "kdl_conv2d_scratch_bytes": (C.c_size_t, [C.c_int] * 10),
     "kdl_conv2d_bf16": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 9 +
                         [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kdl_conv3x3_halo_supported": (C.c_int, [C.c_int] * 6),
+    "kdl_conv3x3_halo_wgrad_scratch_bytes": (C.c_size_t, [C.c_int] * 5),
+    "kdl_conv3x3_halo_wgrad_bf16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 +
+                                    [C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kdl_conv3x3_halo_bf16": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 +
+                              [C.c_void_p, C.c_int, C.c_void_p]),
 })
+
+import os as _os
+
+# 3x3 / stride-1 / pad-1 shapes with C <= 128 go to the halo-resident kernel (csrc/conv3x3_halo.cu);
+# KDL_CONV_HALO=0 keeps everything on the TMA-im2col kernel
+_HALO = _os.environ.get("KDL_CONV_HALO", "1") != "0"
+
+
+def halo_supported(mode, N, H, W, Cin, Cout) -> bool:
+    return bool(L.lib().kdl_conv3x3_halo_supported(mode, N, H, W, Cin, Cout))
+
+
+def _run_halo(mode, in0, w, out, N, H, W, Cin, Cout, addend=None, relu=False):
+    L.check(L.lib().kdl_conv3x3_halo_bf16(mode, in0.data_ptr(), w.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout,
+                                          L.ptr(addend), int(relu), L.stream_ptr()), "kdl_conv3x3_halo_bf16")
+    L.count(1)
+    return out
 
 
 def _chk(t):
@@ -32,29 +55,43 @@ def _run(mode, in0, in1, out, N, H, W, Cin, Cout, R, S, stride, pad, addend=None
     return out
 
 
-def fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
+def fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int, halo: bool = True) -> torch.Tensor:
     _chk(x); _chk(w)
     N, H, W, Cin = x.shape
     Cout, R, S, _ = w.shape
     OH, OW = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
     y = torch.empty(N, OH, OW, Cout, dtype=torch.bfloat16, device=x.device)
+    if _HALO and halo and R == 3 and S == 3 and stride == 1 and pad == 1 and halo_supported(0, N, H, W, Cin, Cout):
+        return _run_halo(0, x, w, y, N, H, W, Cin, Cout)
     return _run(0, x, w, y, N, H, W, Cin, Cout, R, S, stride, pad)
 
 
 def dgrad(dy: torch.Tensor, w: torch.Tensor, in_hw, stride: int, pad: int,
-          addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+          addend: Optional[torch.Tensor] = None, halo: bool = True) -> torch.Tensor:
     _chk(dy); _chk(w)
     N, OH, OW, Cout = dy.shape
     _, R, S, Cin = w.shape
     H, W = in_hw
     dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device=dy.device)
+    if _HALO and halo and R == 3 and S == 3 and stride == 1 and pad == 1 and halo_supported(1, N, H, W, Cin, Cout):
+        return _run_halo(1, dy, w, dx, N, H, W, Cin, Cout, addend=addend)
     return _run(1, dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad, addend)
 
 
 def wgrad(dy: torch.Tensor, x: torch.Tensor, R: int, S: int, stride: int, pad: int,
-          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+          out: Optional[torch.Tensor] = None, halo: bool = True) -> torch.Tensor:
     _chk(dy); _chk(x)
     N, H, W, Cin = x.shape
     Cout = dy.shape[-1]
     dw = out if out is not None else torch.empty(Cout, R, S, Cin, dtype=torch.bfloat16, device=x.device)
+    if _HALO and halo and R == 3 and S == 3 and stride == 1 and pad == 1:
+        lib = L.lib()
+        nb = lib.kdl_conv3x3_halo_wgrad_scratch_bytes(N, H, W, Cin, Cout)
+        if nb:
+            ws = workspace(nb, dw.device, key="gemm_splitk")
+            L.check(lib.kdl_conv3x3_halo_wgrad_bf16(dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N, H, W, Cin, Cout,
+                                                    ws.data_ptr(), ws.numel(), L.stream_ptr()),
+                    "kdl_conv3x3_halo_wgrad_bf16")
+            L.count(2)
+            return dw
     return _run(2, dy, x, dw, N, H, W, Cin, Cout, R, S, stride, pad)

@@ -14,7 +14,10 @@ def _cos(a, b):
     (8, 56, 64, 64, 3, 1, 1), (4, 28, 128, 128, 3, 1, 1), (3, 14, 256, 256, 3, 1, 1),
     (4, 56, 128, 128, 3, 2, 1), (2, 14, 512, 512, 3, 1, 1), (5, 20, 64, 192, 3, 1, 1),
 ])
-def test_conv_fprop_dgrad_wgrad(cuda, N, H, Cin, Cout, R, stride, pad):
+@pytest.mark.parametrize("halo", [True, False])
+def test_conv_fprop_dgrad_wgrad(cuda, N, H, Cin, Cout, R, stride, pad, halo):
+    """halo=True lets the 3x3/s1 shapes that fit take the halo-resident kernel (conv3x3_halo.cu);
+    halo=False pins everything on the TMA-im2col kernel."""
     from kubedl_b200.ops import conv
     torch.manual_seed(0)
     x = torch.randn(N, H, H, Cin, device=cuda).bfloat16()
@@ -22,21 +25,27 @@ def test_conv_fprop_dgrad_wgrad(cuda, N, H, Cin, Cout, R, stride, pad):
     xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
     wr = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
     yr = torch.nn.functional.conv2d(xr, wr, stride=stride, padding=pad)
-    y = conv.fprop(x, w, stride, pad)
+    y = conv.fprop(x, w, stride, pad, halo=halo)
     assert y.shape == yr.permute(0, 2, 3, 1).shape
     err = float((y.float() - yr.permute(0, 2, 3, 1)).abs().max() / yr.abs().max())
     assert err < 1.5e-2, err
     dy = torch.randn_like(y)
     yr.backward(dy.float().permute(0, 3, 1, 2))
-    dw = conv.wgrad(dy, x, R, R, stride, pad)
+    dw = conv.wgrad(dy, x, R, R, stride, pad, halo=halo)
     assert _cos(dw, wr.grad.permute(0, 2, 3, 1)) > 0.999
     err = float((dw.float() - wr.grad.permute(0, 2, 3, 1)).abs().max() / wr.grad.abs().max())
     assert err < 2e-2, err
     if stride == 1:
-        dx = conv.dgrad(dy, w, (H, H), stride, pad)
+        dx = conv.dgrad(dy, w, (H, H), stride, pad, halo=halo)
         err = float((dx.float() - xr.grad.permute(0, 2, 3, 1)).abs().max() / xr.grad.abs().max())
         assert err < 1.5e-2, err
         add = torch.randn_like(dx)
-        dx2 = conv.dgrad(dy, w, (H, H), stride, pad, addend=add)
+        dx2 = conv.dgrad(dy, w, (H, H), stride, pad, addend=add, halo=halo)
         err = float((dx2.float() - (xr.grad.permute(0, 2, 3, 1) + add.float())).abs().max() / xr.grad.abs().max())
         assert err < 2e-2, err
+
+
+def test_halo_dispatch(cuda):
+    from kubedl_b200.ops import conv
+    assert conv.halo_supported(0, 256, 56, 56, 64, 64) and conv.halo_supported(1, 256, 28, 28, 128, 128)
+    assert not conv.halo_supported(0, 256, 14, 14, 256, 256)     # weights do not fit: im2col kernel

@@ -129,11 +129,15 @@ int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N
  * filter taps are row-shifted UMMA descriptor windows over that one buffer, the CTA's weights stay
  * resident.  mode 0 = fprop, 1 = dgrad (optionally + addend, ReLU).  Supported when Cin, Cout are
  * multiples of 64, the weights of 64 output channels fit next to two halo buffers (C <= 128) and
- * some divisor TR of H has TR*(W+2) <= 128 — ask kdl_conv3x3_halo_supported().  No reference
+ * some divisor TR of H has TR*(W+2) <= 128 — ask kdl_conv3x3_halo_supported().  With Cout (fprop) /
+ * Cin (dgrad) of 64 or 128 a CTA pair runs one cta_group::2 MMA over two pixel tiles and all output
+ * channels; dgrad then needs kdl_conv3x3_halo_scratch_bytes() of scratch for a flipped filter copy.  No reference
  * counterpart (the operator launches pods; cuDNN would run this in the stock worker). */
 int kdl_conv3x3_halo_supported(int mode, int N, int H, int W, int Cin, int Cout);
+size_t kdl_conv3x3_halo_scratch_bytes(int mode, int N, int H, int W, int Cin, int Cout);
 int kdl_conv3x3_halo_bf16(int mode, const void* in0, const void* w, void* out, int N, int H, int W, int Cin,
-                          int Cout, const void* addend_bf16, int relu, cudaStream_t stream);
+                          int Cout, const void* addend_bf16, int relu, void* scratch, size_t scratch_bytes,
+                          cudaStream_t stream);
 /* wgrad of the same convolution (Cin, Cout <= 128): the pixel index is the MMA K dimension, every CTA
  * owns one filter row and keeps its 3 x Cin accumulator columns in TMEM across all of its pixel tiles;
  * fp32 partials in `scratch` (kdl_conv3x3_halo_wgrad_scratch_bytes(), 0 = shape unsupported) are reduced

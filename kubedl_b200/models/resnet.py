@@ -8,9 +8,11 @@ backward, bucket all-reduces on a side stream, fused SGD) is a static launch seq
 can be captured once into a CUDA graph.
 
 Convolutions: 1x1 stride-1 convolutions and the FC layer are GEMMs on the [N*H*W, C] view and
-go to the tcgen05 GEMM kernel when it is enabled (ops.gemm); 7x7/3x3/strided convolutions go to
-cuDNN through ATen (library code, like the stock worker).  This is config #2 of
-BASELINE.json ("PyTorchJob ResNet-50 DDP bf16 ... synthetic 224² images").
+go to the tcgen05 GEMM kernel (ops.gemm); the 7x7 stem is fused normalise+im2col + the same GEMM;
+3x3 convolutions go to the halo-resident / TMA-im2col tcgen05 kernels (ops.conv).  What is left
+on cuDNN (through ATen) are the six stride-2 dgrads and the three 1x1/stride-2 downsample
+convolutions.  With gemm=None everything falls back to cuDNN/cuBLAS (the A/B arm of the tests).
+This is config #2 of BASELINE.json ("PyTorchJob ResNet-50 DDP bf16 ... synthetic 224² images").
 """
 from __future__ import annotations
 
@@ -206,9 +208,10 @@ class ResNet50:
         # end to end (24.4 vs 23.1 ms/step) because the epilogue warps are already the bottleneck of
         # the memory-bound 1x1-conv GEMMs; off unless asked for.
         self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "0") == "1"
-        # 3x3 convolutions through our implicit-GEMM kernel (N7) instead of cuDNN; off by default
-        # until it wins on every ResNet shape (profiles/conv3x3_vs_cudnn_*.log)
-        self.own_conv = _os.environ.get("KUBEDL_OWN_CONV", "0") == "1"
+        # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
+        # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
+        # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.
+        self.own_conv = _os.environ.get("KUBEDL_OWN_CONV", "1") == "1"
         self.num_classes = num_classes
         self.arena = ParamArena()
         self.gemm = gemm

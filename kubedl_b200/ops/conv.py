@@ -18,8 +18,9 @@ L.register_signatures({
     "kdl_conv3x3_halo_wgrad_scratch_bytes": (C.c_size_t, [C.c_int] * 5),
     "kdl_conv3x3_halo_wgrad_bf16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 +
                                     [C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kdl_conv3x3_halo_scratch_bytes": (C.c_size_t, [C.c_int] * 6),
     "kdl_conv3x3_halo_bf16": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 +
-                              [C.c_void_p, C.c_int, C.c_void_p]),
+                              [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
 })
 
 import os as _os
@@ -34,9 +35,14 @@ def halo_supported(mode, N, H, W, Cin, Cout) -> bool:
 
 
 def _run_halo(mode, in0, w, out, N, H, W, Cin, Cout, addend=None, relu=False):
-    L.check(L.lib().kdl_conv3x3_halo_bf16(mode, in0.data_ptr(), w.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout,
-                                          L.ptr(addend), int(relu), L.stream_ptr()), "kdl_conv3x3_halo_bf16")
-    L.count(1)
+    lib = L.lib()
+    nb = lib.kdl_conv3x3_halo_scratch_bytes(mode, N, H, W, Cin, Cout)
+    # the flipped filter copy is consumed by the very next launch on the same stream: one buffer serves all layers
+    ws = workspace(nb, out.device, key="conv_wt") if nb else None
+    L.check(lib.kdl_conv3x3_halo_bf16(mode, in0.data_ptr(), w.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout,
+                                      L.ptr(addend), int(relu), L.ptr(ws), ws.numel() if ws is not None else 0,
+                                      L.stream_ptr()), "kdl_conv3x3_halo_bf16")
+    L.count(2 if nb else 1)
     return out
 
 

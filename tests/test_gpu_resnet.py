@@ -121,8 +121,8 @@ def test_bottleneck_block_fwd_bwd(cuda, block, shape, use_gemm, monkeypatch):
     if use_gemm:
         G = pytest.importorskip("kubedl_b200.ops.gemm")
         gemm = G.Gemm(cuda)
-    if use_gemm == "own_conv":      # 3x3 convolutions on the implicit-GEMM kernel (N7) too
-        monkeypatch.setenv("KUBEDL_OWN_CONV", "1")
+    # 3x3 convolutions on our kernels (N7) or on cuDNN
+    monkeypatch.setenv("KUBEDL_OWN_CONV", "1" if use_gemm == "own_conv" else "0")
     net = ResNet50(cuda, gemm=gemm, seed=11)
     assert net.own_conv == (use_gemm == "own_conv")
     tv = torchvision.models.resnet50().to(cuda).float().train()

@@ -21,6 +21,7 @@ namespace kdl {
 
 constexpr int kBins = 256;
 constexpr int kHistThreads = 256;
+constexpr int kFlushRows = 8192;     // rows a block accumulates in int32 fixed point between flushes
 
 __global__ void __launch_bounds__(256) grad_logistic_kernel(const float* __restrict__ pred,
                                                             const float* __restrict__ label,
@@ -56,11 +57,19 @@ struct HistParams {
   uint32_t epoch;        // value that marks "this level's histogram of node k is complete"
   uint64_t timeout_ns;
   uint32_t* status;
+  float qscale, inv_qscale;   // fixed-point scale of the shared-memory accumulators
 };
 
-// Dynamic shared memory: float hist[F][256][2]
+// Dynamic shared memory: int hist[F][256][2] (fixed point)
 __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams p) {
-  extern __shared__ float hist[];
+  // Shared-memory accumulators are 32-bit fixed point: fp32 atomicAdd on shared memory compiles to a
+  // compare-and-swap loop (ATOMS.CAST.SPIN, 64 of them per row here) that collapses under same-bin
+  // collisions, integer ATOMS.ADD is native.  |g|, |h| <= gh_abs_max are scaled to 17 bits, a block
+  // flushes (-> fp32 global atomics) every kFlushRows = 8192 rows, so the int32 sums cannot overflow;
+  // the rounding error per row is 2^-18 of the bound.
+  // (Packing g and h into one 64-bit shared atomic does not help: ATOMS has no native 64-bit add, it
+  // compiles to ATOMS.CAST.SPIN.64.)
+  extern __shared__ int hist[];
   __shared__ int s_last;
   const int hist_floats = p.F * kBins * 2;
   const int tid = threadIdx.x;
@@ -74,14 +83,17 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
   float* local = p.local + (size_t)bi * hist_floats;
 
   if (my_first < ntiles) {
-    for (int i = tid; i < hist_floats; i += kHistThreads) hist[i] = 0.f;
+    for (int i = tid; i < hist_floats; i += kHistThreads) hist[i] = 0;
     __syncthreads();
+    int tiles_since_flush = 0;
     for (int t = my_first; t < ntiles; t += gridDim.x) {
       const int r0 = beg + t * p.rows_per_tile;
       const int r1 = min(r0 + p.rows_per_tile, end);
       for (int r = r0 + tid; r < r1; r += kHistThreads) {
         const int row = p.ridx[r];
         const float2 gh = p.gh[row];
+        const int gq = __float2int_rn(fminf(fmaxf(gh.x * p.qscale, -131072.f), 131072.f));
+        const int hq = __float2int_rn(fminf(fmaxf(gh.y * p.qscale, -131072.f), 131072.f));
         const uint8_t* b = p.bins + (size_t)row * p.fstride;
         // 32-byte rows: two 128-bit loads cover up to 32 features
         uint4 v0 = *reinterpret_cast<const uint4*>(b);
@@ -91,18 +103,26 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
         for (int f = 0; f < 32; ++f) {
           if (f < p.F) {
             const uint32_t bin = (w[f >> 2] >> ((f & 3) * 8)) & 0xffu;
-            float* h = hist + ((size_t)f * kBins + bin) * 2;
-            atomicAdd(h, gh.x);
-            atomicAdd(h + 1, gh.y);
+            int* h = hist + ((size_t)f * kBins + bin) * 2;
+            atomicAdd(h, gq);
+            atomicAdd(h + 1, hq);
           }
         }
       }
-    }
-    __syncthreads();
-    // flush: one red.global per non-zero entry
-    for (int i = tid; i < hist_floats; i += kHistThreads) {
-      float v = hist[i];
-      if (v != 0.f) atomicAdd(local + i, v);
+      const bool last_tile = t + (int)gridDim.x >= ntiles;
+      if (++tiles_since_flush == kFlushRows / 4096 || last_tile) {
+        tiles_since_flush = 0;
+        __syncthreads();
+        // flush: one red.global per non-zero entry
+        for (int i = tid; i < hist_floats; i += kHistThreads) {
+          const int v = hist[i];
+          if (v != 0) {
+            atomicAdd(local + i, (float)v * p.inv_qscale);
+            hist[i] = 0;
+          }
+        }
+        __syncthreads();
+      }
     }
   }
   // ---- node completion: the last block of this node performs the cross-GPU reduction
@@ -269,6 +289,103 @@ __global__ void __launch_bounds__(256) update_pred_kernel(float* __restrict__ pr
     pred[i] += leaf_value[node_of_row[i]];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Row partition: rows grouped by tree node with ONE counting-sort pass per level (node ids at
+// level d take 2^d <= 256 values).  Replaces torch.sort + scatter_add (4-5 ms per level on 11 M
+// rows — most of a boosting round) with three launches that read the node array twice and write the
+// row order once (~130 MB per level).  Order inside a node is block-major, arbitrary inside a
+// block's chunk: rows of a node stay in ascending-chunk order (good locality for the histogram
+// gather) and the histogram sums do not depend on the order beyond fp32 rounding.
+constexpr int kPartThreads = 256;
+constexpr int kPartMaxNodes = 256;
+
+__device__ __forceinline__ int warp_rank_in_group(unsigned mask, int lane) {
+  return __popc(mask & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(kPartThreads) part_count_kernel(const int32_t* __restrict__ node_of_row,
+                                                                 int64_t n, int nodes, int64_t chunk,
+                                                                 int32_t* __restrict__ block_counts) {
+  __shared__ int cnt[kPartMaxNodes];
+  for (int i = threadIdx.x; i < nodes; i += kPartThreads) cnt[i] = 0;
+  __syncthreads();
+  const int64_t lo = (int64_t)blockIdx.x * chunk;
+  const int64_t hi = min(lo + chunk, n);
+  const int lane = threadIdx.x & 31;
+  for (int64_t i0 = lo; i0 < hi; i0 += kPartThreads) {
+    const int64_t i = i0 + threadIdx.x;
+    const bool ok = i < hi;
+    const unsigned act = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const int v = node_of_row[i];
+      const unsigned m = __match_any_sync(act, v);
+      if (warp_rank_in_group(m, lane) == 0) atomicAdd(&cnt[v], __popc(m));
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nodes; i += kPartThreads) block_counts[(size_t)i * gridDim.x + blockIdx.x] = cnt[i];
+}
+
+// exclusive scan of block_counts (node-major: [nodes][B]) in place; seg[v] = first slot of node v
+__global__ void __launch_bounds__(1024) part_scan_kernel(int32_t* __restrict__ block_counts, int total, int B,
+                                                         int nodes, int32_t* __restrict__ seg,
+                                                         int32_t* __restrict__ counts) {
+  __shared__ int partial[1024];
+  const int per = (total + 1023) / 1024;
+  const int lo = min((int)threadIdx.x * per, total), hi = min(lo + per, total);
+  int sum = 0;
+  for (int i = lo; i < hi; ++i) sum += block_counts[i];
+  partial[threadIdx.x] = sum;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {      // Hillis-Steele inclusive scan
+    int v = threadIdx.x >= off ? partial[threadIdx.x - off] : 0;
+    __syncthreads();
+    partial[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = partial[threadIdx.x] - sum;
+  for (int i = lo; i < hi; ++i) {
+    const int c = block_counts[i];
+    block_counts[i] = run;
+    run += c;
+  }
+  __syncthreads();
+  const int n_all = partial[1023];
+  for (int v = threadIdx.x; v <= nodes; v += 1024) seg[v] = v < nodes ? block_counts[(size_t)v * B] : n_all;
+  __syncthreads();
+  for (int v = threadIdx.x; v < nodes; v += 1024) {
+    const int a = block_counts[(size_t)v * B];
+    const int b = v + 1 < nodes ? block_counts[(size_t)(v + 1) * B] : n_all;
+    counts[v] = b - a;
+  }
+}
+
+__global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const int32_t* __restrict__ node_of_row,
+                                                                   int64_t n, int nodes, int64_t chunk,
+                                                                   const int32_t* __restrict__ block_offsets,
+                                                                   int32_t* __restrict__ ridx) {
+  __shared__ int offs[kPartMaxNodes];
+  for (int i = threadIdx.x; i < nodes; i += kPartThreads) offs[i] = block_offsets[(size_t)i * gridDim.x + blockIdx.x];
+  __syncthreads();
+  const int64_t lo = (int64_t)blockIdx.x * chunk;
+  const int64_t hi = min(lo + chunk, n);
+  const int lane = threadIdx.x & 31;
+  for (int64_t i0 = lo; i0 < hi; i0 += kPartThreads) {
+    const int64_t i = i0 + threadIdx.x;
+    const bool ok = i < hi;
+    const unsigned act = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const int v = node_of_row[i];
+      const unsigned m = __match_any_sync(act, v);
+      const int leader = __ffs(m) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(&offs[v], __popc(m));
+      base = __shfl_sync(m, base, leader);
+      ridx[base + warp_rank_in_group(m, lane)] = (int32_t)i;
+    }
+  }
+}
+
 static int ew_grid(int64_t n) {
   int64_t g = (n + 255) / 256;
   if (g > 148 * 16) g = 148 * 16;
@@ -294,7 +411,7 @@ extern "C" int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, con
                                        void* node_done, void* const* peer_local, void* const* flag_ptrs,
                                        const void* mc_local, int world, int rank, int max_nodes,
                                        unsigned epoch, void* status,
-                                       unsigned long long timeout_ns, cudaStream_t stream) {
+                                       unsigned long long timeout_ns, float gh_abs_max, cudaStream_t stream) {
   if (F < 1 || F > 32 || fstride < F || (fstride % 16) != 0) {
     kdl_set_error("gbdt_hist: need 1 <= F <= 32 and a 16-byte multiple row stride >= F (F=%d stride=%d)", F, fstride);
     return KDL_ERR_ARG;
@@ -309,6 +426,8 @@ extern "C" int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, con
   p.local = (float*)local_hist; p.out = (float*)out_hist; p.node_done = (unsigned*)node_done;
   p.world = world; p.rank = rank; p.max_nodes = max_nodes; p.epoch = epoch;
   p.timeout_ns = timeout_ns; p.status = (uint32_t*)status;
+  if (!(gh_abs_max > 0.f)) gh_abs_max = 1.f;
+  p.qscale = 131072.f / gh_abs_max; p.inv_qscale = gh_abs_max / 131072.f;
   p.mc_local = world > 1 ? (const float*)mc_local : nullptr;
   for (int r = 0; r < world; ++r) {
     p.peer_local[r] = peer_local ? (const float*)peer_local[r] : (const float*)local_hist;
@@ -350,6 +469,36 @@ extern "C" int kdl_gbdt_apply_split(int32_t* node_of_row, const void* bins, int 
 extern "C" int kdl_gbdt_update_pred(float* pred, const int32_t* node_of_row, const float* leaf_value,
                                     int64_t n, cudaStream_t stream) {
   update_pred_kernel<<<ew_grid(n), 256, 0, stream>>>(pred, node_of_row, leaf_value, n);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+// Rows grouped by node: ridx[n] (row ids, node-major), seg[nodes+1] (first slot of every node),
+// counts[nodes].  workspace: kdl_gbdt_partition_workspace_bytes(nodes) bytes.
+static int part_blocks() { return 148 * 8; }
+extern "C" size_t kdl_gbdt_partition_workspace_bytes(int nodes) { return (size_t)nodes * part_blocks() * sizeof(int32_t); }
+extern "C" int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nodes, int32_t* ridx, int32_t* seg,
+                                  int32_t* counts, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  if (nodes < 1 || nodes > kPartMaxNodes) {
+    kdl_set_error("gbdt partition: %d nodes per level unsupported (max %d)", nodes, kPartMaxNodes);
+    return KDL_ERR_UNSUPPORTED;
+  }
+  if (n >= ((int64_t)1 << 31)) {
+    kdl_set_error("gbdt partition: %lld rows per rank exceed int32 row ids", (long long)n);
+    return KDL_ERR_UNSUPPORTED;
+  }
+  const int B = part_blocks();
+  if (workspace == nullptr || workspace_bytes < (size_t)nodes * B * sizeof(int32_t)) {
+    kdl_set_error("gbdt partition: workspace too small");
+    return KDL_ERR_WORKSPACE;
+  }
+  const int64_t chunk = ((n + B - 1) / B + kPartThreads - 1) / kPartThreads * kPartThreads;
+  int32_t* bc = (int32_t*)workspace;
+  part_count_kernel<<<B, kPartThreads, 0, stream>>>(node_of_row, n, nodes, chunk, bc);
+  KDL_CHECK_LAUNCH();
+  part_scan_kernel<<<1, 1024, 0, stream>>>(bc, nodes * B, B, nodes, seg, counts);
+  KDL_CHECK_LAUNCH();
+  part_scatter_kernel<<<B, kPartThreads, 0, stream>>>(node_of_row, n, nodes, chunk, bc, ridx);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }

@@ -149,7 +149,8 @@ int kdl_conv3x3_halo_wgrad_bf16(const void* dy, const void* x, void* dw, int N, 
 /* ---- N3: histogram GBDT, histogram build fused with the cross-GPU reduction ---------------
  * Replaces XGBoost gpu_hist + ncclAllReduce of histograms, for which the reference only injects
  * the tracker address (reference controllers/xgboost/pod.go:106-152).  peer_local / flag_ptrs are
- * HOST arrays of `world` device pointers into the symmetric heap (NULL when world == 1). */
+ * HOST arrays of `world` device pointers into the symmetric heap (NULL when world == 1).   Shared-memory accumulators are 17-bit fixed point relative to gh_abs_max (bound on |g|, |h|;
+ * 1 for logistic loss): integer shared-memory atomics are native, fp32 ones are CAS loops. */
 int kdl_gbdt_grad_logistic(const float* pred, const float* label, void* gh, int64_t n,
                            cudaStream_t stream);
 size_t kdl_gbdt_hist_bytes(int nodes, int F);
@@ -158,7 +159,13 @@ int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, const void* gh
                             void* local_hist, void* out_hist, void* node_done, void* const* peer_local,
                             void* const* flag_ptrs, const void* mc_local /* NVLS alias of local_hist or NULL */,
                             int world, int rank, int max_nodes, unsigned epoch,
-                            void* status, unsigned long long timeout_ns, cudaStream_t stream);
+                            void* status, unsigned long long timeout_ns, float gh_abs_max,
+                            cudaStream_t stream);
+/* Rows grouped by tree node with one counting-sort pass (node ids of a level take <= 256 values):
+ * ridx[n] row ids node-major, seg[nodes+1] first slot per node, counts[nodes]. */
+size_t kdl_gbdt_partition_workspace_bytes(int nodes);
+int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nodes, int32_t* ridx, int32_t* seg,
+                       int32_t* counts, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 int kdl_gbdt_split_eval(const void* hist, int nodes, int F, float lambda, float gamma,
                         float min_child_weight, float* out8, cudaStream_t stream);
 int kdl_gbdt_apply_split(int32_t* node_of_row, const void* bins, int fstride, const float* splits8,

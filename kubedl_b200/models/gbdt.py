@@ -30,11 +30,14 @@ L.register_signatures({
     "kdl_gbdt_hist_allreduce": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int,
-                                          C.c_int, C.c_uint, C.c_void_p, C.c_ulonglong, C.c_void_p]),
+                                          C.c_int, C.c_uint, C.c_void_p, C.c_ulonglong, C.c_float, C.c_void_p]),
     "kdl_gbdt_split_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
                                       C.c_void_p, C.c_void_p]),
     "kdl_gbdt_apply_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
     "kdl_gbdt_update_pred": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "kdl_gbdt_partition_workspace_bytes": (C.c_size_t, [C.c_int]),
+    "kdl_gbdt_partition": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_size_t, C.c_void_p]),
 })
 
 FSTRIDE = 32
@@ -117,6 +120,7 @@ class GBDTTrainer:
         self.epoch = 0
         self.level_parity = 0
         self.trees: List[Tree] = []
+        self.gh_abs_max = 1.0    # logistic loss: |g| <= 1, h <= 1/4 (bound of the fixed-point histogram scale)
 
     # ------------------------------------------------------------------ one tree
     def _global_counts(self, counts: torch.Tensor) -> torch.Tensor:
@@ -133,6 +137,21 @@ class GBDTTrainer:
         self.ar(self.cnt_off, n, torch.float32, scale=1.0, channel=7)
         return self.cnt[:counts.numel()].clone()
 
+    def _partition(self, nodes: int):
+        """Rows grouped by node (one counting-sort pass, csrc/gbdt.cu) -> (ridx, seg, counts)."""
+        lib = self.lib
+        if not hasattr(self, "_ridx"):
+            self._ridx = torch.empty(self.n, dtype=torch.int32, device=self.dev)
+            nb = lib.kdl_gbdt_partition_workspace_bytes(1 << max(self.depth - 1, 0))
+            self._part_ws = torch.empty(nb, dtype=torch.uint8, device=self.dev)
+        seg = torch.empty(nodes + 1, dtype=torch.int32, device=self.dev)
+        counts = torch.empty(nodes, dtype=torch.int32, device=self.dev)
+        L.check(lib.kdl_gbdt_partition(self.node.data_ptr(), self.n, nodes, self._ridx.data_ptr(), seg.data_ptr(),
+                                       counts.data_ptr(), self._part_ws.data_ptr(), self._part_ws.numel(),
+                                       L.stream_ptr()), "kdl_gbdt_partition")
+        L.count(3)
+        return self._ridx, seg, counts.long()
+
     def _build_hist(self, ridx, seg, build, nbuild) -> torch.Tensor:
         par = self.level_parity
         self.level_parity ^= 1
@@ -147,7 +166,7 @@ class GBDTTrainer:
             self._flag_tab if fused else None,
             (self.heap.mc(self.local_off[par]) if (fused and self.use_nvls) else None),
             self.world if fused else 1, self.rank if fused else 0,
-            self.max_nodes, self.epoch, None, int(30e9), L.stream_ptr())
+            self.max_nodes, self.epoch, None, int(30e9), self.gh_abs_max, L.stream_ptr())
         L.check(rc, "kdl_gbdt_hist_allreduce")
         L.count(1)
         out = self.out[:hist_floats]
@@ -166,12 +185,7 @@ class GBDTTrainer:
         parent_hist = None
         for d in range(self.depth):
             nodes = 1 << d
-            order = torch.sort(self.node, stable=True)
-            ridx = order.indices.to(torch.int32)
-            counts = torch.zeros(nodes, dtype=torch.int64, device=self.dev).scatter_add_(
-                0, self.node.long(), torch.ones(self.n, dtype=torch.int64, device=self.dev))
-            seg = torch.zeros(nodes + 1, dtype=torch.int32, device=self.dev)
-            seg[1:] = counts.cumsum(0).to(torch.int32)
+            ridx, seg, counts = self._partition(nodes)
             if d == 0:
                 build = torch.zeros(1, dtype=torch.int32, device=self.dev)
                 hist = self._build_hist(ridx, seg, build, 1).clone()

@@ -69,3 +69,27 @@ def test_tree_matches_oracle_and_loss_decreases(cuda):
     assert losses[0] < l0 and all(b < a for a, b in zip(losses, losses[1:])), (l0, losses)
     # the stored trees reproduce the running prediction
     torch.testing.assert_close(tr.predict_bins(tr.bins), tr.pred, atol=1e-4, rtol=1e-4)
+
+
+@pytest.mark.parametrize("n,nodes", [(1000, 1), (100_003, 8), (1_000_000, 128), (257, 256)])
+def test_partition_groups_rows_by_node(cuda, n, nodes):
+    """Counting-sort row partition: a permutation of the rows, node-major, with matching segments."""
+    import ctypes as C
+    from kubedl_b200.models import gbdt  # noqa: F401  (registers the signatures)
+    from kubedl_b200.ops import lib as L
+    lib = L.lib()
+    torch.manual_seed(n)
+    node = torch.randint(0, nodes, (n,), device=cuda, dtype=torch.int32)
+    ridx = torch.empty(n, dtype=torch.int32, device=cuda)
+    seg = torch.empty(nodes + 1, dtype=torch.int32, device=cuda)
+    counts = torch.empty(nodes, dtype=torch.int32, device=cuda)
+    ws = torch.empty(lib.kdl_gbdt_partition_workspace_bytes(nodes), dtype=torch.uint8, device=cuda)
+    L.check(lib.kdl_gbdt_partition(node.data_ptr(), n, nodes, ridx.data_ptr(), seg.data_ptr(), counts.data_ptr(),
+                                   ws.data_ptr(), ws.numel(), L.stream_ptr()), "kdl_gbdt_partition")
+    torch.cuda.synchronize()
+    ref_counts = torch.bincount(node.long(), minlength=nodes)
+    assert torch.equal(counts.long(), ref_counts)
+    assert torch.equal(seg.long(), torch.cat([torch.zeros(1, dtype=torch.long, device=cuda), ref_counts.cumsum(0)]))
+    assert torch.equal(torch.sort(ridx.long()).values, torch.arange(n, device=cuda))       # a permutation
+    grouped = node[ridx.long()]
+    assert bool((grouped[1:] >= grouped[:-1]).all())                                          # node-major

@@ -58,6 +58,7 @@ struct HistParams {
   uint64_t timeout_ns;
   uint32_t* status;
   float qscale, inv_qscale;   // fixed-point scale of the shared-memory accumulators
+  uint32_t* epoch_state;      // optional device-resident {epoch, finished nodes}: makes the launch CUDA-graph replayable
 };
 
 // Dynamic shared memory: int hist[F][256][2] (fixed point)
@@ -135,6 +136,9 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  // the epoch either comes by value (a fresh one per launch from the host) or lives on the device and
+  // is advanced by the last finishing node of this launch, so a captured launch can be replayed
+  const uint32_t epoch = p.epoch_state ? *((volatile uint32_t*)p.epoch_state) + 1u : p.epoch;
   float* out = p.out + (size_t)bi * hist_floats;
   if (p.world == 1) {
     for (int i = tid; i < hist_floats / 4; i += kHistThreads)
@@ -143,11 +147,11 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
     // tell every peer "my histogram of build-slot bi is complete", wait for theirs
     if (tid < p.world) {
       __threadfence_system();
-      st_release_sys(p.flags[tid] + (size_t)p.rank * p.max_nodes + bi, p.epoch);
+      st_release_sys(p.flags[tid] + (size_t)p.rank * p.max_nodes + bi, epoch);
       const uint32_t* mine = p.flags[p.rank] + (size_t)tid * p.max_nodes + bi;
       uint64_t t0 = 0;
       uint32_t spins = 0;
-      while ((int32_t)(ld_acquire_sys(mine) - p.epoch) < 0) {
+      while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
         if (p.timeout_ns && (++spins & 1023u) == 0) {
           uint64_t now = globaltimer_ns();
           if (t0 == 0) t0 = now;
@@ -191,7 +195,17 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
       reinterpret_cast<float4*>(out)[i] = acc;
     }
   }
-  if (tid == 0) p.node_done[bi] = 0u;
+  if (tid == 0) {
+    p.node_done[bi] = 0u;
+    if (p.epoch_state) {
+      __threadfence();
+      const unsigned prev = atomicAdd(p.epoch_state + 1, 1u);
+      if (prev == gridDim.y - 1) {          // every node of this launch has read the epoch
+        p.epoch_state[1] = 0u;
+        *((volatile uint32_t*)p.epoch_state) = epoch;
+      }
+    }
+  }
 }
 
 // One block per node: gain scan over bins for every feature, arg-max.
@@ -411,7 +425,8 @@ extern "C" int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, con
                                        void* node_done, void* const* peer_local, void* const* flag_ptrs,
                                        const void* mc_local, int world, int rank, int max_nodes,
                                        unsigned epoch, void* status,
-                                       unsigned long long timeout_ns, float gh_abs_max, cudaStream_t stream) {
+                                       unsigned long long timeout_ns, float gh_abs_max, void* epoch_state,
+                                       cudaStream_t stream) {
   if (F < 1 || F > 32 || fstride < F || (fstride % 16) != 0) {
     kdl_set_error("gbdt_hist: need 1 <= F <= 32 and a 16-byte multiple row stride >= F (F=%d stride=%d)", F, fstride);
     return KDL_ERR_ARG;
@@ -426,6 +441,7 @@ extern "C" int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, con
   p.local = (float*)local_hist; p.out = (float*)out_hist; p.node_done = (unsigned*)node_done;
   p.world = world; p.rank = rank; p.max_nodes = max_nodes; p.epoch = epoch;
   p.timeout_ns = timeout_ns; p.status = (uint32_t*)status;
+  p.epoch_state = (uint32_t*)epoch_state;
   if (!(gh_abs_max > 0.f)) gh_abs_max = 1.f;
   p.qscale = 131072.f / gh_abs_max; p.inv_qscale = gh_abs_max / 131072.f;
   p.mc_local = world > 1 ? (const float*)mc_local : nullptr;

@@ -160,6 +160,8 @@ int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, const void* gh
                             void* const* flag_ptrs, const void* mc_local /* NVLS alias of local_hist or NULL */,
                             int world, int rank, int max_nodes, unsigned epoch,
                             void* status, unsigned long long timeout_ns, float gh_abs_max,
+                            void* epoch_state /* optional 2 x uint32 on the device, zeroed once: the epoch then lives
+                            there (the `epoch` argument is ignored) and the launch can be replayed from a CUDA graph */,
                             cudaStream_t stream);
 /* Rows grouped by tree node with one counting-sort pass (node ids of a level take <= 256 values):
  * ridx[n] row ids node-major, seg[nodes+1] first slot per node, counts[nodes]. */

@@ -30,7 +30,8 @@ L.register_signatures({
     "kdl_gbdt_hist_allreduce": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int,
-                                          C.c_int, C.c_uint, C.c_void_p, C.c_ulonglong, C.c_float, C.c_void_p]),
+                                          C.c_int, C.c_uint, C.c_void_p, C.c_ulonglong, C.c_float, C.c_void_p,
+                                          C.c_void_p]),
     "kdl_gbdt_split_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
                                       C.c_void_p, C.c_void_p]),
     "kdl_gbdt_apply_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
@@ -77,7 +78,7 @@ def quantize(X: torch.Tensor, cuts: torch.Tensor) -> torch.Tensor:
 class GBDTTrainer:
     def __init__(self, X: torch.Tensor, y: torch.Tensor, max_depth: int = 6, learning_rate: float = 0.1,
                  reg_lambda: float = 1.0, gamma: float = 0.0, min_child_weight: float = 1.0, heap=None,
-                 cuts: Optional[torch.Tensor] = None, group=None, comm: str = "fused"):
+                 cuts: Optional[torch.Tensor] = None, group=None, comm: str = "fused", use_graph: bool = True):
         import torch.distributed as dist
         self.lib = L.lib()
         self.dev = X.device
@@ -120,6 +121,11 @@ class GBDTTrainer:
         self.epoch = 0
         self.level_parity = 0
         self.trees: List[Tree] = []
+        # {epoch, finished nodes} of the in-kernel cross-GPU barrier live on the device, so a whole
+        # boosting round can be captured into a CUDA graph and replayed
+        self.epoch_state = torch.zeros(2, dtype=torch.int32, device=self.dev)
+        self.use_graph = use_graph and self.comm != "nccl"
+        self._graph = None
         self.gh_abs_max = 1.0    # logistic loss: |g| <= 1, h <= 1/4 (bound of the fixed-point histogram scale)
 
     # ------------------------------------------------------------------ one tree
@@ -166,7 +172,8 @@ class GBDTTrainer:
             self._flag_tab if fused else None,
             (self.heap.mc(self.local_off[par]) if (fused and self.use_nvls) else None),
             self.world if fused else 1, self.rank if fused else 0,
-            self.max_nodes, self.epoch, None, int(30e9), self.gh_abs_max, L.stream_ptr())
+            self.max_nodes, self.epoch, None, int(30e9), self.gh_abs_max,
+            self.epoch_state.data_ptr() if fused else None, L.stream_ptr())
         L.check(rc, "kdl_gbdt_hist_allreduce")
         L.count(1)
         out = self.out[:hist_floats]
@@ -176,6 +183,36 @@ class GBDTTrainer:
         return out.view(nbuild, self.F, NBINS, 2)
 
     def grow_tree(self) -> Tree:
+        """One boosting round.  The launch sequence of a round is static (≈150 launches, no host
+        synchronisation), so after one eager round it is captured into a CUDA graph and replayed:
+        at 8 GPUs a round is otherwise bound by launch latency, not by the kernels."""
+        if not self.use_graph:
+            tree = self._grow_tree_eager()
+        elif self._graph is None and not getattr(self, "_warm", False):
+            self._warm = True
+            tree = self._grow_tree_eager()
+        else:
+            if self._graph is None:
+                L.lib()                      # everything is loaded before capture
+                torch.cuda.synchronize()
+                self._graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._graph):
+                    self._graph_tree = self._grow_tree_eager()
+                self.trees.pop()             # capture does not execute: that tree never existed
+            self._graph.replay()
+            L.count(self._graph_launches)
+            src = self._graph_tree
+            tree = Tree(src.depth, [t.clone() for t in src.splits], src.leaf_value.clone())
+            self.trees.append(tree)
+        return tree
+
+    def _grow_tree_eager(self) -> Tree:
+        n0 = L.launch_count()
+        tree = self._grow_tree_impl()
+        self._graph_launches = L.launch_count() - n0
+        return tree
+
+    def _grow_tree_impl(self) -> Tree:
         lib = self.lib
         L.check(lib.kdl_gbdt_grad_logistic(self.pred.data_ptr(), self.y.data_ptr(), self.gh.data_ptr(), self.n,
                                            L.stream_ptr()), "kdl_gbdt_grad_logistic")
@@ -183,6 +220,11 @@ class GBDTTrainer:
         self.node.zero_()
         tree = Tree(self.depth)
         parent_hist = None
+        if self.world > 1 and self.comm == "fused":
+            # cross-rank barrier: nobody zeroes a histogram buffer a peer may still be reading from the
+            # previous round's last level (inside a round the row-count all-reduce of every level does it)
+            self._global_counts(torch.zeros(1, dtype=torch.int64, device=self.dev))
+        self.level_parity = 0
         for d in range(self.depth):
             nodes = 1 << d
             ridx, seg, counts = self._partition(nodes)

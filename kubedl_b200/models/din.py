@@ -119,6 +119,36 @@ class DINModel:
         L.count(1)
 
     def step(self, user, cand, hist, label) -> torch.Tensor:
+        """One training step.  With a batch of a few thousand samples every kernel is tiny and the step is
+        launch-bound (≈ 40 launches), so after one eager step the sequence is captured into a CUDA graph
+        that reads the batch from static buffers; KUBEDL_DIN_GRAPH=0 keeps it eager."""
+        import os as _os
+        if _os.environ.get("KUBEDL_DIN_GRAPH", "1") == "0":
+            return self._step_eager(user, cand, hist, label)
+        key = (user.numel(), tuple(hist.shape), self.lr, self.emb_lr)    # kernel arguments baked into the graph
+        g = getattr(self, "_graphs", None)
+        if g is None:
+            g = self._graphs = {}
+        ent = g.get(key)
+        if ent is None:
+            g[key] = "warm"
+            return self._step_eager(user, cand, hist, label)      # loads kernels, sizes workspaces
+        if ent == "warm":
+            bufs = (user.clone(), cand.clone(), hist.clone(), label.clone())
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            n0 = L.launch_count()
+            with torch.cuda.graph(graph):
+                loss = self._step_eager(*bufs)
+            ent = g[key] = (graph, bufs, loss, L.launch_count() - n0)
+        graph, bufs, loss, launches = ent
+        for b, t in zip(bufs, (user, cand, hist, label)):
+            b.copy_(t)
+        graph.replay()
+        L.count(launches)
+        return loss.clone()
+
+    def _step_eager(self, user, cand, hist, label) -> torch.Tensor:
         logit = self.forward(user, cand, hist)
         loss = torch.nn.functional.binary_cross_entropy_with_logits(logit, label)
         dlogit = (torch.sigmoid(logit) - label) / label.numel()

@@ -36,11 +36,11 @@ struct BnReduceParams {
   float eps;
   float momentum;
   float* mean_rstd;  // [2][C] saved for backward (fwd: out, bwd: in)
-  float* coef;       // fwd: [2][C] (a,b); bwd: [3][C] (A,B,D)
+  float* coef;       // fwd: [2][C] (a,b); bwd: [4][C] (A,B,D, forward shift b)
   // bwd finalisation
   bf16* dgamma;
   bf16* dbeta;
-  int relu;
+  int relu;          // bwd: 1 = mask from y (b), 2 = mask recomputed from x with the forward affine (no y read)
 };
 
 template <int MODE>
@@ -59,12 +59,16 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
 
-  float mean[8], rstd[8];
+  float mean[8], rstd[8], fwa[8], fwb[8];
   if (MODE == 1) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       mean[j] = p.mean_rstd[ch0 + j];
       rstd[j] = p.mean_rstd[p.C + ch0 + j];
+      // the forward pass computed y = relu(fma(a, x, b)), a = gamma*rstd, b = beta - mean*a: the same
+      // expression gives the ReLU mask back without reading y (layers without a residual input)
+      fwa[j] = (p.gamma ? p.gamma[ch0 + j] : 1.f) * rstd[j];
+      fwb[j] = (p.beta ? p.beta[ch0 + j] : 0.f) - mean[j] * fwa[j];
     }
   }
 
@@ -79,7 +83,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
         va[u] = ld_stream(p.a + off);
         if (MODE == 1) {
           vc[u] = ld_stream(p.c + off);
-          if (p.relu) vb[u] = ld_stream(p.b + off);
+          if (p.relu == 1) vb[u] = ld_stream(p.b + off);
         }
       }
     }
@@ -98,11 +102,14 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
         } else {
           float fx[8];
           unpack8(vc[u], fx);
-          if (p.relu) {
+          if (p.relu == 1) {
             float fy[8];
             unpack8(vb[u], fy);
 #pragma unroll
             for (int j = 0; j < 8; ++j) fa[j] = fy[j] > 0.f ? fa[j] : 0.f;
+          } else if (p.relu == 2) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) fa[j] = fmaf(fwa[j], fx[j], fwb[j]) > 0.f ? fa[j] : 0.f;
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -207,6 +214,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
       p.coef[c] = a;
       p.coef[p.C + c] = -a * c2 * rs;
       p.coef[2 * p.C + c] = a * (c2 * rs * mu - c1);
+      p.coef[3 * p.C + c] = (p.beta ? p.beta[c] : 0.f) - mu * a;
     }
   }
   if (tid == 0) p.counter[slice] = 0u;
@@ -283,7 +291,7 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
                                                     const float* __restrict__ coef, int relu) {
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  float A[8], B[8], D[8];
+  float A[8], B[8], D[8], Fb[8];
   if (FIXED_CG) {
     int cg = (int)(i % cvec);
 #pragma unroll
@@ -291,6 +299,7 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
       A[j] = coef[cg * 8 + j];
       B[j] = coef[C + cg * 8 + j];
       D[j] = coef[2 * C + cg * 8 + j];
+      Fb[j] = coef[3 * C + cg * 8 + j];
     }
   }
   constexpr int U = 2;
@@ -302,7 +311,7 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
       if (k < nvec) {
         vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
         vx[u] = ld_stream(x + k * 8);
-        if (relu) vy[u] = ld_stream(y + k * 8);
+        if (relu == 1) vy[u] = ld_stream(y + k * 8);
       }
     }
 #pragma unroll
@@ -316,16 +325,20 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
             A[j] = coef[cg * 8 + j];
             B[j] = coef[C + cg * 8 + j];
             D[j] = coef[2 * C + cg * 8 + j];
+            Fb[j] = coef[3 * C + cg * 8 + j];
           }
         }
         float fd[8], fx[8];
         unpack8(vd[u], fd);
         unpack8(vx[u], fx);
-        if (relu) {
+        if (relu == 1) {
           float fy[8];
           unpack8(vy[u], fy);
 #pragma unroll
           for (int j = 0; j < 8; ++j) fd[j] = fy[j] > 0.f ? fd[j] : 0.f;
+        } else if (relu == 2) {      // A = gamma*rstd is also the forward scale
+#pragma unroll
+          for (int j = 0; j < 8; ++j) fd[j] = fmaf(A[j], fx[j], Fb[j]) > 0.f ? fd[j] : 0.f;
         }
         if (dres) *reinterpret_cast<uint4*>(dres + k * 8) = pack8(fd);
         float o[8];
@@ -374,8 +387,8 @@ using namespace kdl;
 extern "C" size_t kdl_bn_workspace_bytes(int64_t M, int C) {
   BnPlan pl;
   if (!make_plan(M, C, &pl)) return 0;
-  // counters | coef[3][C] | partials
-  return kCounterBytes + (size_t)3 * C * sizeof(float) + pl.partial_floats * sizeof(float);
+  // counters | coef[4][C] | partials
+  return kCounterBytes + (size_t)4 * C * sizeof(float) + pl.partial_floats * sizeof(float);
 }
 
 static int carve(void* ws, size_t ws_bytes, int64_t M, int C, BnPlan* pl, unsigned** counter,
@@ -396,7 +409,7 @@ static int carve(void* ws, size_t ws_bytes, int64_t M, int C, BnPlan* pl, unsign
   char* b = (char*)ws;
   *counter = (unsigned*)b;
   *coef = (float*)(b + kCounterBytes);
-  *partial = *coef + (size_t)3 * C;
+  *partial = *coef + (size_t)4 * C;
   return KDL_OK;
 }
 
@@ -442,7 +455,7 @@ extern "C" int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, in
 }
 
 extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dres,
-                          int64_t M, int C, const float* gamma, const float* save_mean_rstd,
+                          int64_t M, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
                           int relu, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
                           size_t workspace_bytes, cudaStream_t stream) {
   BnPlan pl;
@@ -451,14 +464,19 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
   int rc = carve(workspace, workspace_bytes, M, C, &pl, &counter, &coef, &partial);
   if (rc) return rc;
   if (relu && y == nullptr) {
-    kdl_set_error("bn_bwd: relu mask needs y");
-    return KDL_ERR_ARG;
+    if (beta == nullptr) {
+      kdl_set_error("bn_bwd: the relu mask needs y, or beta to recompute it from x");
+      return KDL_ERR_ARG;
+    }
+    relu = 2;
+  } else if (relu) {
+    relu = 1;
   }
   BnReduceParams p = {};
   p.a = (const bf16*)dy; p.b = (const bf16*)y; p.c = (const bf16*)x;
   p.M = M; p.C = C; p.CS = pl.CS; p.tpr = pl.tpr; p.rpb = pl.rpb;
   p.partial = partial; p.counter = counter;
-  p.gamma = gamma;
+  p.gamma = gamma; p.beta = beta;
   p.mean_rstd = const_cast<float*>(save_mean_rstd);
   p.coef = coef;
   p.dgamma = (bf16*)dgamma_bf16; p.dbeta = (bf16*)dbeta_bf16;

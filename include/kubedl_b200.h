@@ -43,8 +43,10 @@ int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, int C, const 
                const float* beta, float* running_mean, float* running_var, float eps,
                float momentum, int relu, float* save_mean_rstd, void* workspace,
                size_t workspace_bytes, cudaStream_t stream);
+/* relu != 0: the ReLU mask comes from y, or — y == NULL and beta given, layers without a residual input —
+ * is recomputed from x with the forward affine, which saves reading y in both backward passes. */
 int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dres, int64_t M,
-               int C, const float* gamma, const float* save_mean_rstd, int relu,
+               int C, const float* gamma, const float* beta, const float* save_mean_rstd, int relu,
                void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
 
@@ -74,7 +76,8 @@ int kdl_bn_fwd_static_scratch(const void* x, const void* res, void* y, int64_t M
 int kdl_u8_normalize(const void* in_u8, void* out_bf16, int64_t npix, int cpad,
                      const float* mean3_host, const float* std3_host, cudaStream_t stream);
 /* uint8 NHWC image -> normalised bf16 im2col patches [N*OH*OW, KP] of the 7x7/s2/p3 stem
- * convolution (column = (kh*7+kw)*3+c, zero padded to KP >= 152), so the stem runs on kdl_gemm_bf16. */
+ * convolution (KP = 168: column = kh*24 + kw*3 + c, columns 21..23 of every filter row zero), so the
+ * stem runs on kdl_gemm_bf16.  W % 4 == 0, W <= 256. */
 int kdl_stem_im2col_u8(const void* img_u8, void* patches_bf16, int N, int H, int W, int KP,
                        const float* mean3_host, const float* std3_host, cudaStream_t stream);
 size_t kdl_softmax_xent_workspace_bytes(int B);

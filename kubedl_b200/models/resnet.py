@@ -126,9 +126,11 @@ class BN:
                         relu=self.relu, save=self.save, stats=stats)
         return y
 
-    def bwd(self, dy, x, y, dres=None):
-        return K.bn_bwd(dy, x, y if self.relu else None, self.gamma, self.save, self.relu,
-                        self.dgamma, self.dbeta, dres=dres)
+    def bwd(self, dy, x, y, dres=None, had_residual=False):
+        """y is read for the ReLU mask only when the forward pass added a residual; otherwise the mask
+        is recomputed from x (one tensor less to stream in both backward passes)."""
+        return K.bn_bwd(dy, x, y if (self.relu and had_residual) else None, self.gamma, self.save, self.relu,
+                        self.dgamma, self.dbeta, dres=dres, beta=self.beta)
 
 
 class Bottleneck:
@@ -181,7 +183,7 @@ class Bottleneck:
     def bwd(self, dout, need_dx=True):
         x, c1, a1, c2, a2, c3, cdo, out = self.saved
         self.saved = None
-        dc3 = self.b3.bwd(dout, c3, out, dres=dout)  # dout now holds dz (grad of the residual)
+        dc3 = self.b3.bwd(dout, c3, out, dres=dout, had_residual=True)  # dout now holds dz (grad of the residual)
         dres = dout
         da2 = self.c3.bwd(dc3, a2)
         dc2 = self.b2.bwd(da2, c2, a2)
@@ -249,9 +251,7 @@ class ResNet50:
 
     # ------------------------------------------------------------------ forward
     def _stem_w_padded(self) -> torch.Tensor:
-        w = torch.zeros(64, K.STEM_KP, dtype=torch.bfloat16, device=self.device)
-        w[:, :147] = self.stem.w.view(64, 147)
-        return w
+        return K.stem_weight_padded(self.stem.w)
 
     def forward(self, x, train: bool = True) -> torch.Tensor:
         """x: normalised bf16 NHWC image, or (tcgen05 path) the raw uint8 NHWC image — then the stem
@@ -307,7 +307,7 @@ class ResNet50:
         dc = self.stem_bn.bwd(da, c, a)
         if x.dim() == 2:   # im2col patches: stem wgrad is one tn GEMM (split over the 3.2 M rows)
             gw = self.gemm.tn(dc.view(-1, 64), x)
-            self.arena.grad("conv1").view(64, 147).copy_(gw[:, :147])
+            self.arena.grad("conv1").view(64, 147).copy_(K.stem_weight_unpad(gw))
             self.reducer_ready(self.stem.g_end)
         else:
             self.stem.bwd(dc, x, need_dx=False)

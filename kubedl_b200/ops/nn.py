@@ -71,10 +71,12 @@ def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
 
 def bn_bwd(dy: torch.Tensor, x: torch.Tensor, y: Optional[torch.Tensor], gamma: torch.Tensor,
            save: torch.Tensor, relu: bool, dgamma: torch.Tensor, dbeta: torch.Tensor,
-           dx: Optional[torch.Tensor] = None, dres: Optional[torch.Tensor] = None) -> torch.Tensor:
+           dx: Optional[torch.Tensor] = None, dres: Optional[torch.Tensor] = None,
+           beta: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Backward of bn_fwd.  dgamma/dbeta: bf16 [C] (views into the gradient arena).  If `dres`
     is given it receives dz = dy * relu_mask (the gradient of the residual input); it may alias
-    dy."""
+    dy.  With relu and y=None (layers without a residual input) the mask is recomputed from x with
+    the forward affine (`beta` required) and y is never read."""
     _chk_bf16(dy, x, y, dx, dres, dgamma, dbeta)
     Cn = x.shape[-1]
     M = x.numel() // Cn
@@ -84,7 +86,7 @@ def bn_bwd(dy: torch.Tensor, x: torch.Tensor, y: Optional[torch.Tensor], gamma: 
     need = lib.kdl_bn_workspace_bytes(M, Cn)
     ws = workspace(need, x.device)
     L.check(lib.kdl_bn_bwd(dy.data_ptr(), x.data_ptr(), L.ptr(y), dx.data_ptr(), L.ptr(dres), M, Cn,
-                           gamma.data_ptr(), save.data_ptr(), int(relu), dgamma.data_ptr(),
+                           gamma.data_ptr(), L.ptr(beta), save.data_ptr(), int(relu), dgamma.data_ptr(),
                            dbeta.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()),
             "kdl_bn_bwd")
     L.count(2)
@@ -107,11 +109,25 @@ def u8_normalize(img_u8: torch.Tensor, cpad: int = 3, out: Optional[torch.Tensor
     return out
 
 
-STEM_KP = 152   # 7*7*3 = 147 im2col columns padded to a 16-byte multiple
+STEM_KW = 24            # a filter row (7 pixels x 3 channels = 21 values) padded to 24
+STEM_KP = 7 * STEM_KW   # 168 patch columns
+
+
+def stem_weight_padded(w: torch.Tensor) -> torch.Tensor:
+    """[64, 7, 7, 3] stem filter -> [64, 168] in the patch-column layout of stem_im2col."""
+    wp = torch.zeros(w.shape[0], 7, STEM_KW, dtype=w.dtype, device=w.device)
+    wp[:, :, :21] = w.reshape(w.shape[0], 7, 21)
+    return wp.view(w.shape[0], STEM_KP)
+
+
+def stem_weight_unpad(gw: torch.Tensor) -> torch.Tensor:
+    """[64, 168] gradient in patch-column layout -> [64, 147]."""
+    return gw.view(gw.shape[0], 7, STEM_KW)[:, :, :21].reshape(gw.shape[0], 147)
 
 
 def stem_im2col(img_u8: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """uint8 NHWC [N,H,W,3] -> normalised bf16 patches [N*OH*OW, 152] of the 7x7/s2/p3 stem conv."""
+    """uint8 NHWC [N,H,W,3] -> normalised bf16 patches [N*OH*OW, 168] of the 7x7/s2/p3 stem conv
+    (7 filter rows x 24 columns, 21 used)."""
     assert img_u8.dtype == torch.uint8 and img_u8.shape[-1] == 3 and img_u8.is_contiguous()
     N, H, W, _ = img_u8.shape
     OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1

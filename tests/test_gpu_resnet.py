@@ -162,9 +162,9 @@ def test_stem_im2col_gemm_matches_conv2d(cuda):
     img = torch.randint(0, 256, (N, S, S, 3), dtype=torch.uint8, device=cuda)
     w = (torch.randn(64, 7, 7, 3, device=cuda) * 0.05).bfloat16()
     patches = K.stem_im2col(img)
-    assert patches.shape == (N * 32 * 32, 152) and float(patches[:, 147:].abs().max()) == 0.0
-    wp = torch.zeros(64, 152, dtype=torch.bfloat16, device=cuda)
-    wp[:, :147] = w.view(64, 147)
+    assert patches.shape == (N * 32 * 32, K.STEM_KP)
+    assert float(patches.view(-1, 7, K.STEM_KW)[:, :, 21:].abs().max()) == 0.0
+    wp = K.stem_weight_padded(w)
     y = g.nt(patches, wp).view(N, 32, 32, 64)
     xn = K.u8_normalize(img).float().permute(0, 3, 1, 2)
     wr = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
@@ -172,5 +172,5 @@ def test_stem_im2col_gemm_matches_conv2d(cuda):
     torch.testing.assert_close(y.float(), yr.permute(0, 2, 3, 1), atol=5e-2, rtol=3e-2)
     dy = torch.randn_like(y)
     yr.backward(dy.float().permute(0, 3, 1, 2))
-    gw = g.tn(dy.view(-1, 64), patches)[:, :147].view(64, 7, 7, 3)
+    gw = K.stem_weight_unpad(g.tn(dy.view(-1, 64), patches)).view(64, 7, 7, 3)
     assert _cos(gw, wr.grad.permute(0, 2, 3, 1)) > 0.999

@@ -39,6 +39,8 @@ struct GemmParams {
   float* partial;       // fp32 split-K partials [splits][M][N] (mode 1)
   const bf16* bias;     // [N] or null
   const bf16* addend;   // [M, ldc] or null
+  int add_h, add_w;     // > 0: rows are pixels (n, h, w) of an add_h x add_w map and `addend` is the compact
+                        // [n, add_h/2, add_w/2] tensor of a stride-2 branch: added at even (h, w) only
   int M, N, K;
   int ldc;
   int relu;
@@ -329,8 +331,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                 if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
             }
           }
-          if (p.addend && row < p.M) {
-            const bf16* ad = p.addend + (size_t)row * p.ldc + col;
+          bool add_row = p.addend && row < p.M;
+          size_t add_idx = (size_t)row;
+          if (add_row && p.add_h > 0) {      // gradient of a 1x1 / stride-2 branch, kept compact (never up-sampled)
+            const int hw = p.add_h * p.add_w;
+            const int ni = row / hw, rem = row - ni * hw, hh = rem / p.add_w, ww = rem - hh * p.add_w;
+            add_row = ((hh | ww) & 1) == 0;
+            add_idx = ((size_t)ni * (p.add_h >> 1) + (hh >> 1)) * (p.add_w >> 1) + (ww >> 1);
+          }
+          if (add_row) {
+            const bf16* ad = p.addend + add_idx * p.ldc + col;
             if (col + 64 <= p.N) {
 #pragma unroll
               for (int j = 0; j < 64; j += 8) {
@@ -641,8 +651,16 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int j = 0; j < 64; ++j)
             if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
         }
-        if (p.addend && row < p.M) {
-          const bf16* ad = p.addend + (size_t)row * p.ldc + col;
+        bool add_row = p.addend && row < p.M;
+        size_t add_idx = (size_t)row;
+        if (add_row && p.add_h > 0) {
+          const int hw = p.add_h * p.add_w;
+          const int ni = row / hw, rem = row - ni * hw, hh = rem / p.add_w, ww = rem - hh * p.add_w;
+          add_row = ((hh | ww) & 1) == 0;
+          add_idx = ((size_t)ni * (p.add_h >> 1) + (hh >> 1)) * (p.add_w >> 1) + (ww >> 1);
+        }
+        if (add_row) {
+          const bf16* ad = p.addend + add_idx * p.ldc + col;
           if (col + 64 <= p.N) {
 #pragma unroll
             for (int j = 0; j < 64; j += 8) {
@@ -917,11 +935,32 @@ extern "C" size_t kdl_gemm_scratch_bytes(int M, int N, int K, int split_k) {
 
 extern "C" int kdl_gemm_max_ctas(void) { return num_sms(); }
 
+static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major, int b_mn_major,
+                     int lda, int ldb, int ldc, const void* bias, const void* addend, int add_h, int add_w,
+                     int relu, int split_k, void* scratch, size_t scratch_bytes, float* stats_partial,
+                     int* stats_parts_out, cudaStream_t stream);
+
 extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
                                 int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
                                 const void* bias, const void* addend, int relu, int split_k,
                                 void* scratch, size_t scratch_bytes, float* stats_partial,
-                                int* stats_parts_out, cudaStream_t stream);
+                                int* stats_parts_out, cudaStream_t stream) {
+  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, bias, addend, 0, 0, relu, split_k,
+                   scratch, scratch_bytes, stats_partial, stats_parts_out, stream);
+}
+
+// C[M, N] = A B (+ addend): rows of C are the pixels of an [n, H, W] map and `addend_compact` is the
+// [n, H/2, W/2, N] gradient of a 1x1 / stride-2 branch reading the same input, added at even (h, w).
+extern "C" int kdl_gemm_bf16_subadd(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                                    int b_mn_major, int lda, int ldb, int ldc, const void* addend_compact, int H,
+                                    int W, cudaStream_t stream) {
+  if (H <= 0 || W <= 0 || (H & 1) || (W & 1) || M % (H * W) != 0) {
+    kdl_set_error("gemm_subadd: need even H, W and M a multiple of H*W (M=%d H=%d W=%d)", M, H, W);
+    return KDL_ERR_ARG;
+  }
+  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, nullptr, addend_compact, H, W, 0, 1,
+                   nullptr, 0, nullptr, nullptr, stream);
+}
 
 extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                              int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
@@ -931,11 +970,10 @@ extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N
                           split_k, scratch, scratch_bytes, nullptr, nullptr, stream);
 }
 
-extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
-                                int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
-                                const void* bias, const void* addend, int relu, int split_k,
-                                void* scratch, size_t scratch_bytes, float* stats_partial,
-                                int* stats_parts_out, cudaStream_t stream) {
+static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major, int b_mn_major,
+                     int lda, int ldb, int ldc, const void* bias, const void* addend, int add_h, int add_w,
+                     int relu, int split_k, void* scratch, size_t scratch_bytes, float* stats_partial,
+                     int* stats_parts_out, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) {
     kdl_set_error("gemm: bad shape %dx%dx%d", M, N, K);
     return KDL_ERR_ARG;
@@ -953,6 +991,7 @@ extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, in
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.bias = (const bf16*)bias;
   p.addend = (const bf16*)addend;
+  p.add_h = add_h; p.add_w = add_w;
   p.relu = relu;
   p.splits = splits;
   const int kb_total = (K + BK - 1) / BK;

@@ -116,6 +116,14 @@ int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
                      const void* addend_bf16, int relu, int split_k, void* scratch, size_t scratch_bytes,
                      float* stats_partial, int* stats_parts_out, cudaStream_t stream);
 
+/* C[M, N] = A B + up-sampled addend: the rows of C are the pixels of an [n, H, W] map and `addend_compact`
+ * is [n, H/2, W/2, N] (row stride ldc), added at even (h, w) only.  Used for the input gradient of a
+ * bottleneck whose 1x1 / stride-2 downsample branch reads the same input: that branch's dgrad stays a
+ * compact GEMM result and is never scattered into a mostly-zero full-size tensor. */
+int kdl_gemm_bf16_subadd(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                         int b_mn_major, int lda, int ldb, int ldc, const void* addend_compact, int H, int W,
+                         cudaStream_t stream);
+
 /* ---- N7: implicit-GEMM convolution on the same tcgen05 kernel (NHWC bf16) ------------------
  * The activation operand is fetched with TMA im2col loads (no patch matrix in memory).  mode 0 =
  * fprop (x, w -> y), 1 = dgrad (dy, w -> dx [+addend]; stride-1 "same" convolutions), 2 = wgrad

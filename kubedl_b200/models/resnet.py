@@ -52,6 +52,10 @@ class Conv:
         # 3x3 convolutions on the TMA-im2col implicit GEMM (kernel N7) instead of cuDNN
         self.own_conv = (self.k == 3 and self.net.own_conv and self.net.gemm is not None
                          and self.cin % 64 == 0)
+        # 1x1 / stride-2 downsample convolution: fprop and wgrad on the TMA-im2col kernel, dgrad as a
+        # plain GEMM whose COMPACT result the sibling conv1 dgrad adds at even pixels in its epilogue
+        self.own_strided = (self.k == 1 and self.stride == 2 and self.net.own_conv and self.net.gemm is not None
+                            and self.cin % 64 == 0)
 
     def fwd(self, x: torch.Tensor, want_stats: bool = False):
         """want_stats: also return the BN column statistics produced by the GEMM epilogue (None on
@@ -64,7 +68,7 @@ class Conv:
                 return y.view(N, H, W, self.cout), stats
             y = net.gemm.nt(x.view(-1, Cin), self.w.view(self.cout, Cin)).view(N, H, W, self.cout)
             return (y, None) if want_stats else y
-        if self.own_conv:
+        if self.own_conv or self.own_strided:
             y = conv_ops.fprop(x, self.w, self.stride, self.pad)
             return (y, None) if want_stats else y
         y = torch.ops.aten.convolution(_nchw(x), self.w_nchw, None, [self.stride] * 2,
@@ -72,9 +76,10 @@ class Conv:
         return (_nhwc(y), None) if want_stats else _nhwc(y)
 
     def bwd(self, dy: torch.Tensor, x: torch.Tensor, need_dx: bool = True,
-            addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+            addend: Optional[torch.Tensor] = None, addend_compact: bool = False) -> Optional[torch.Tensor]:
         """Returns dx (+ addend, the gradient arriving over the residual branch — fused into the
-        dgrad GEMM epilogue on the tcgen05 path)."""
+        dgrad GEMM epilogue on the tcgen05 path; addend_compact: it is the [N, H/2, W/2, Cin] result
+        of a stride-2 sibling's bwd_compact)."""
         net = self.net
         if self.is_gemm and net.gemm is not None:
             N, H, W, Cin = x.shape
@@ -84,7 +89,8 @@ class Conv:
             dx = None
             if need_dx:
                 dx = net.gemm.nn(dy2, self.w.view(self.cout, Cin),
-                                 addend=None if addend is None else addend.view(-1, Cin)).view(N, H, W, Cin)
+                                 addend=None if addend is None else addend.view(-1, Cin),
+                                 addend_hw=(H, W) if addend_compact else None).view(N, H, W, Cin)
         elif self.own_conv:
             conv_ops.wgrad(dy, x, self.k, self.k, self.stride, self.pad, out=net.arena.grad(self.name))
             dx = None
@@ -105,6 +111,15 @@ class Conv:
                 K.add_(dx, addend)
         net.reducer_ready(self.g_end)
         return dx
+
+    def bwd_compact(self, dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+        """1x1 / stride-2: weight gradient into the arena, and the input gradient at the sampled (even)
+        pixels only, [N, H/2, W/2, Cin]."""
+        net = self.net
+        conv_ops.wgrad(dy, x, 1, 1, self.stride, 0, out=net.arena.grad(self.name))
+        dxc = net.gemm.nn(dy.view(-1, self.cout), self.w.view(self.cout, self.cin))
+        net.reducer_ready(self.g_end)
+        return dxc.view(dy.shape[0], dy.shape[1], dy.shape[2], self.cin)
 
 
 class BN:
@@ -191,8 +206,10 @@ class Bottleneck:
         dc1 = self.b1.bwd(da1, c1, a1)
         if self.cd is not None:
             dcd = self.bd.bwd(dres, cdo, None)
-            dx2 = self.cd.bwd(dcd, x)
-            dx = self.c1.bwd(dc1, x, addend=dx2)
+            if self.cd.own_strided and self.c1.is_gemm:
+                dx = self.c1.bwd(dc1, x, addend=self.cd.bwd_compact(dcd, x), addend_compact=True)
+            else:
+                dx = self.c1.bwd(dc1, x, addend=self.cd.bwd(dcd, x))
         else:
             dx = self.c1.bwd(dc1, x, addend=dres)
         return dx

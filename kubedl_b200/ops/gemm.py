@@ -26,6 +26,8 @@ L.register_signatures({
                                    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                    C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_int),
                                    C.c_void_p]),
+    "kdl_gemm_bf16_subadd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "kdl_gemm_bf16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                 C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
@@ -88,13 +90,25 @@ class Gemm:
         return self._run(a, b, out, M, N, K, 0, 0, bias, addend, relu, 1)
 
     def nn(self, a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
-           addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+           addend: Optional[torch.Tensor] = None, addend_hw=None) -> torch.Tensor:
+        """out = a @ b (+ addend).  addend_hw=(H, W): the rows of `out` are the pixels of an [n, H, W] map
+        and `addend` is the compact [n*H/2*W/2, N] gradient of a 1x1 / stride-2 branch, added at even
+        (h, w) only — the up-sampled (three quarters zero) tensor is never materialised."""
         _chk(a); _chk(b)
         M, K = a.shape
         K2, N = b.shape
         assert K == K2
         if out is None:
             out = torch.empty(M, N, dtype=torch.bfloat16, device=a.device)
+        if addend_hw is not None:
+            H, W = addend_hw
+            _chk(addend)
+            assert addend.shape == (M // 4, N) and addend.stride(0) == out.stride(0)
+            L.check(self.lib.kdl_gemm_bf16_subadd(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, 0, 1, a.stride(0),
+                                                  b.stride(0), out.stride(0), addend.data_ptr(), H, W, L.stream_ptr()),
+                    "kdl_gemm_bf16_subadd")
+            L.count(1)
+            return out
         return self._run(a, b, out, M, N, K, 0, 1, None, addend, False, 1)
 
     def tn(self, a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,

@@ -13,6 +13,7 @@ def _cos(a, b):
 @pytest.mark.parametrize("N,H,Cin,Cout,R,stride,pad", [
     (8, 56, 64, 64, 3, 1, 1), (4, 28, 128, 128, 3, 1, 1), (3, 14, 256, 256, 3, 1, 1),
     (4, 56, 128, 128, 3, 2, 1), (2, 14, 512, 512, 3, 1, 1), (5, 20, 64, 192, 3, 1, 1),
+    (4, 56, 256, 512, 1, 2, 0), (3, 14, 1024, 2048, 1, 2, 0),       # the 1x1 / stride-2 downsample convolutions
 ])
 @pytest.mark.parametrize("halo", [True, False])
 def test_conv_fprop_dgrad_wgrad(cuda, N, H, Cin, Cout, R, stride, pad, halo):

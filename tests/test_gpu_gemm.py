@@ -117,3 +117,20 @@ def test_gemm_fused_bn_stats_and_bn_from_stats(cuda, M, N, K):
     y2, sv2 = Kn.bn_fwd(y, gamma, beta, None, None, relu=True, stats=(partial, nparts))
     torch.testing.assert_close(sv2, sv1, atol=1e-4, rtol=1e-4)
     torch.testing.assert_close(y2.float(), y1.float(), atol=2e-2, rtol=2e-2)
+
+
+def test_nn_compact_stride2_addend(cuda):
+    """dgrad GEMM + the compact gradient of a 1x1/stride-2 sibling branch added at even pixels."""
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(3)
+    for (n, H, W, K, N) in [(2, 8, 8, 64, 256), (3, 28, 28, 128, 512), (2, 56, 56, 64, 256)]:
+        M = n * H * W
+        a = torch.randn(M, K, device=cuda).bfloat16()
+        b = (torch.randn(K, N, device=cuda) * 0.1).bfloat16()
+        addc = torch.randn(n, H // 2, W // 2, N, device=cuda).bfloat16()
+        out = g.nn(a, b, addend=addc.view(-1, N), addend_hw=(H, W))
+        ref = (a.float() @ b.float()).view(n, H, W, N)
+        ref[:, ::2, ::2, :] += addc.float()
+        err = float((out.view(n, H, W, N).float() - ref).abs().max() / ref.abs().max())
+        assert err < 1.5e-2, (n, H, W, K, N, err)

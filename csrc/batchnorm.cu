@@ -501,18 +501,30 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
 
 // BN forward when the per-channel sums were already produced by the GEMM epilogue
 // (kdl_gemm_bf16_ex `stats_partial`): finalise [nparts][2][C] partials in a fixed order, then apply.
-__global__ void __launch_bounds__(256) bn_finalize_partials_kernel(const float* __restrict__ partial, int nparts,
-                                                                   int64_t M, int C, const float* gamma,
-                                                                   const float* beta, float* running_mean,
-                                                                   float* running_var, float eps, float momentum,
-                                                                   float* mean_rstd, float* coef) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float S0 = 0.f, S1 = 0.f;
-  for (int i = 0; i < nparts; ++i) {
-    S0 += __ldcg(partial + (size_t)i * 2 * C + c);
-    S1 += __ldcg(partial + (size_t)i * 2 * C + C + c);
+// 32 channels x 32 part-lanes per block: the partials of a channel are summed by 32 threads in a fixed
+// interleaving and then in a fixed order (deterministic); a single thread walking several hundred
+// partial rows took tens of microseconds per BatchNorm layer.
+__global__ void __launch_bounds__(1024) bn_finalize_partials_kernel(const float* __restrict__ partial, int nparts,
+                                                                    int64_t M, int C, const float* gamma,
+                                                                    const float* beta, float* running_mean,
+                                                                    float* running_var, float eps, float momentum,
+                                                                    float* mean_rstd, float* coef) {
+  __shared__ float r0[32][33], r1[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  float a0 = 0.f, a1 = 0.f;
+  if (c < C) {
+    for (int i = ty; i < nparts; i += 32) {
+      a0 += __ldcg(partial + (size_t)i * 2 * C + c);
+      a1 += __ldcg(partial + (size_t)i * 2 * C + C + c);
+    }
   }
+  r0[ty][tx] = a0; r1[ty][tx] = a1;
+  __syncthreads();
+  if (ty != 0 || c >= C) return;
+  float S0 = 0.f, S1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) { S0 += r0[i][tx]; S1 += r1[i][tx]; }
   const float invM = 1.f / (float)M;
   const float mu = S0 * invM;
   const float var = fmaxf(S1 * invM - mu * mu, 0.f);
@@ -543,7 +555,7 @@ extern "C" int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, in
     kdl_set_error("bn_fwd_from_stats: no partial statistics given");
     return KDL_ERR_ARG;
   }
-  bn_finalize_partials_kernel<<<(C + 255) / 256, 256, 0, stream>>>(stats_partial, nparts, M, C, gamma, beta,
+  bn_finalize_partials_kernel<<<(C + 31) / 32, 1024, 0, stream>>>(stats_partial, nparts, M, C, gamma, beta,
                                                                    running_mean, running_var, eps, momentum,
                                                                    save_mean_rstd, coef);
   KDL_CHECK_LAUNCH();

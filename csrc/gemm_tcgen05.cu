@@ -47,7 +47,7 @@ struct GemmParams {
   int splits;
   int kb_per_split;
   int num_m, num_n;
-  float* stats;   // optional [gridDim.x][2][N]: per-CTA column sum / sum-of-squares of the bf16 output
+  float* stats;   // optional [parts][2][N]: per epilogue-warp column sum / sum-of-squares of the bf16 output
   // implicit-GEMM convolution (N7): one operand is fetched with TMA im2col loads
   int conv_mode;     // 0 plain GEMM; 1 A = activation patches (fprop / dgrad); 2 B = activation patches (wgrad)
   int conv_q, conv_p;        // spatial extent the pixel index runs over (output W, H of this pass)
@@ -61,23 +61,39 @@ constexpr int kStatsMaxN = 2048;
 constexpr int kStatsBytes = 2 * kStatsMaxN * 4;
 
 // Column statistics of one 32-row x 64-column bf16 chunk sitting in a (128B-swizzled) staging
-// buffer: lane l owns columns 2l, 2l+1.  Feeds the BatchNorm that follows a 1x1 convolution, so
-// the separate statistics pass over the activation disappears.
-__device__ __forceinline__ void chunk_col_stats(const uint8_t* buf, int lane, int rows_valid, int col0,
-                                                int N, float* cta_stats) {
+// buffer: lane l owns columns 2l, 2l+1 and keeps their running sum / sum of squares in REGISTERS for
+// the whole persistent loop (acc[0..1] sums, acc[2..3] squares).  That works because the grid is
+// sized as a multiple of the number of column tiles when statistics are requested, so a CTA sees the
+// same columns in every tile it processes.  (A first version accumulated with shared-memory
+// atomicAdd(float) — a compare-and-swap loop in SASS — and lost more time than the saved pass.)
+// Feeds the BatchNorm that follows a 1x1 convolution: the separate statistics pass over the
+// activation disappears.
+__device__ __forceinline__ void chunk_col_stats(const uint8_t* buf, int lane, int rows_valid, float* acc) {
   float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-#pragma unroll 8
-  for (int r = 0; r < 32; ++r) {
-    if (r < rows_valid) {
+  if (rows_valid >= 32) {
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + r * 128 + ((((lane >> 2) ^ (r & 7))) << 4) + (lane & 3) * 4);
+      const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+      s0 += v.x; q0 = fmaf(v.x, v.x, q0);
+      s1 += v.y; q1 = fmaf(v.y, v.y, q1);
+    }
+  } else {
+    for (int r = 0; r < rows_valid; ++r) {
       const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + r * 128 + ((((lane >> 2) ^ (r & 7))) << 4) + (lane & 3) * 4);
       const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
       s0 += v.x; q0 = fmaf(v.x, v.x, q0);
       s1 += v.y; q1 = fmaf(v.y, v.y, q1);
     }
   }
-  const int c = col0 + 2 * lane;
-  if (c < N) { atomicAdd(cta_stats + c, s0); atomicAdd(cta_stats + kStatsMaxN + c, q0); }
-  if (c + 1 < N) { atomicAdd(cta_stats + c + 1, s1); atomicAdd(cta_stats + kStatsMaxN + c + 1, q1); }
+  acc[0] += s0; acc[1] += s1; acc[2] += q0; acc[3] += q1;
+}
+
+// part row layout of the statistics buffer: [nparts][2][N]
+__device__ __forceinline__ void store_col_stats(float* stats, int part, int N, int col, const float* acc) {
+  float* dst = stats + (size_t)part * 2 * N;
+  if (col < N) { dst[col] = acc[0]; dst[N + col] = acc[2]; }
+  if (col + 1 < N) { dst[col + 1] = acc[1]; dst[N + col + 1] = acc[3]; }
 }
 
 template <int A_MN, int B_MN, int BN>
@@ -119,10 +135,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;  // power of two for BN in {32,64,128,256}
-  float* cta_stats = reinterpret_cast<float*>(smem + SL::kStatsOffset);
-  if (p.stats) {
-    for (int i = threadIdx.x; i < 2 * kStatsMaxN; i += kGemmThreads) cta_stats[i] = 0.f;
-  }
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -272,6 +284,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
     int iter = 0;
     int buf = 0;
+    float st_acc[BN / 64][4];
+#pragma unroll
+    for (int c = 0; c < BN / 64; ++c) st_acc[c][0] = st_acc[c][1] = st_acc[c][2] = st_acc[c][3] = 0.f;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
       const int n_idx = t % p.num_n;
       const int m_idx = (t / p.num_n) % p.num_m;
@@ -367,7 +382,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
           if (p.stats) {
             __syncwarp();
-            chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, col, p.N, cta_stats);
+            float t4[4] = {0.f, 0.f, 0.f, 0.f};
+            chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, t4);
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c)      // compile-time indices keep st_acc in registers
+              if (c == (c0 >> 6)) { st_acc[c][0] += t4[0]; st_acc[c][1] += t4[1]; st_acc[c][2] += t4[2]; st_acc[c][3] += t4[3]; }
           }
           fence_proxy_async_smem();
           __syncwarp();
@@ -384,17 +403,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
+    if (p.stats) {   // this CTA's column tile is blockIdx.x % num_n for every tile it processed
+      const int part = (blockIdx.x / p.num_n) * kEpiWarps + ew;
+#pragma unroll
+      for (int c = 0; c < BN / 64; ++c)
+        store_col_stats(p.stats, part, p.N, (int)(blockIdx.x % p.num_n) * BN + c * 64 + 2 * lane, st_acc[c]);
+    }
   }
 
   tcgen05_fence_before();
   __syncthreads();
-  if (p.stats) {
-    float* dst = p.stats + (size_t)blockIdx.x * 2 * p.N;
-    for (int i = threadIdx.x; i < p.N; i += kGemmThreads) {
-      dst[i] = cta_stats[i];
-      dst[p.N + i] = cta_stats[kStatsMaxN + i];
-    }
-  }
   if (warp == 2) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
@@ -455,10 +473,6 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
   const bool leader = cta == 0;
-  float* cta_stats = reinterpret_cast<float*>(smem + SL::kStatsOffset);
-  if (p.stats) {
-    for (int i = threadIdx.x; i < 2 * kStatsMaxN; i += kGemmThreads) cta_stats[i] = 0.f;
-  }
   constexpr uint32_t kTmemCols = 2 * BN2;   // two accumulator stages (256 or 512 columns)
   constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit: address of the leader's copy
 
@@ -603,6 +617,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
     int iter = 0;
     int buf = 0;
+    float st_acc[BN2 / 64][4];
+#pragma unroll
+    for (int c = 0; c < BN2 / 64; ++c) st_acc[c][0] = st_acc[c][1] = st_acc[c][2] = st_acc[c][3] = 0.f;
     for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
       const int n_idx = t % p.num_n;
       const int m_idx = (t / p.num_n) % p.num_m;
@@ -687,7 +704,11 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
           *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
         if (p.stats) {
           __syncwarp();
-          chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, col, p.N, cta_stats);
+          float t4[4] = {0.f, 0.f, 0.f, 0.f};
+          chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, t4);
+#pragma unroll
+          for (int c = 0; c < BN2 / 64; ++c)
+            if (c == (c0 >> 6)) { st_acc[c][0] += t4[0]; st_acc[c][1] += t4[1]; st_acc[c][2] += t4[2]; st_acc[c][3] += t4[3]; }
         }
         fence_proxy_async_smem();
         __syncwarp();
@@ -703,17 +724,16 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
+    if (p.stats) {   // the pair's column tile is pair % num_n for every tile it processed
+      const int part = ((pair / p.num_n) * 2 + (int)cta) * kEpiWarps + ew;
+#pragma unroll
+      for (int c = 0; c < BN2 / 64; ++c)
+        store_col_stats(p.stats, part, p.N, (pair % p.num_n) * BN2 + c * 64 + 2 * lane, st_acc[c]);
+    }
   }
 
   tcgen05_fence_before();
   cluster_sync_all();
-  if (p.stats) {
-    float* dst = p.stats + (size_t)blockIdx.x * 2 * p.N;
-    for (int i = threadIdx.x; i < p.N; i += kGemmThreads) {
-      dst[i] = cta_stats[i];
-      dst[p.N + i] = cta_stats[kStatsMaxN + i];
-    }
-  }
   if (warp == 2) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
@@ -827,6 +847,12 @@ static int make_c_map(CUtensorMap* map, void* base, int fp32_partial, uint64_t M
   return KDL_OK;
 }
 
+// CTAs (or CTA pairs) when column statistics are fused: a multiple of the number of column tiles
+static int stats_grid(int want, int num_n) {
+  int g = want - want % num_n;
+  return g < num_n ? num_n : g;
+}
+
 template <int A_MN, int B_MN, int BN, int STAGES>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
                   const GemmParams& p, cudaStream_t stream) {
@@ -839,6 +865,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
   }
   int tiles = p.num_m * p.num_n * p.splits;
   int grid = tiles < num_sms() ? tiles : num_sms();
+  if (p.stats) grid = stats_grid(grid, p.num_n);   // every CTA keeps one column tile (register-held statistics)
   kern<<<grid, kGemmThreads, SL::kTotal + 1024, stream>>>(ma, mb, mc, p);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
@@ -857,6 +884,7 @@ static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
   int tiles = p.num_m * p.num_n * (p.splits > 0 ? p.splits : 1);
   int pairs = num_sms() / 2;
   if (tiles < pairs) pairs = tiles;
+  if (p.stats) pairs = stats_grid(pairs, p.num_n);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(kGemmThreads);
@@ -933,7 +961,8 @@ extern "C" size_t kdl_gemm_scratch_bytes(int M, int N, int K, int split_k) {
   return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
 }
 
-extern "C" int kdl_gemm_max_ctas(void) { return num_sms(); }
+// rows a statistics buffer needs: one per epilogue warp of every CTA
+extern "C" int kdl_gemm_max_ctas(void) { return num_sms() * kEpiWarps; }
 
 static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major, int b_mn_major,
                      int lda, int ldb, int ldc, const void* bias, const void* addend, int add_h, int add_w,
@@ -1039,7 +1068,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
     p.num_n = (N + 255) / 256;
     if (stats_parts_out) {
       int tiles2 = p.num_m * p.num_n, pairs = num_sms() / 2;
-      *stats_parts_out = 2 * (tiles2 < pairs ? tiles2 : pairs);
+      *stats_parts_out = (stats_grid(tiles2 < pairs ? tiles2 : pairs, p.num_n) / p.num_n) * 2 * kEpiWarps;
     }
     if (!a_mn_major && !b_mn_major) return launch_2cta<0, 0>(ma, mb, mc2, p, stream);
     if (!a_mn_major && b_mn_major) return launch_2cta<0, 1>(ma, mb, mc2, p, stream);
@@ -1048,7 +1077,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   }
   if (stats_parts_out) {
     int tiles1 = p.num_m * p.num_n * p.splits;
-    *stats_parts_out = tiles1 < num_sms() ? tiles1 : num_sms();
+    *stats_parts_out = (stats_grid(tiles1 < num_sms() ? tiles1 : num_sms(), p.num_n) / p.num_n) * kEpiWarps;
   }
   CUtensorMap mc;
   if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)N, (uint64_t)N, (uint64_t)splits);

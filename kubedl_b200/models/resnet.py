@@ -223,10 +223,12 @@ class ResNet50:
         self.device = torch.device(device)
         self.zero_init_residual = zero_init_residual
         import os as _os
-        # BN column statistics from the GEMM epilogue: numerically validated, but measured slower
-        # end to end (24.4 vs 23.1 ms/step) because the epilogue warps are already the bottleneck of
-        # the memory-bound 1x1-conv GEMMs; off unless asked for.
-        self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "0") == "1"
+        # BN column statistics from the GEMM epilogue (1x1 convolutions, stem): every epilogue warp keeps
+        # the sums of its columns in registers across the persistent loop, a small kernel reduces the
+        # per-warp rows, and the statistics pass over the activation disappears: 22.0 vs 22.5 ms/step
+        # (profiles/bench_1gpu_bnstats_ab.log).  The first version used shared-memory float atomics
+        # (CAS loops) and a serial finalizer and was slower than the separate pass.
+        self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "1") == "1"
         # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
         # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
         # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.

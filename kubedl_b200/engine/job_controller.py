@@ -342,6 +342,14 @@ class JobController:
 
         if old_status != job_status:
             self.controller.update_job_status_in_api_server(job, job_status)
+        # The reference has no timer for activeDeadlineSeconds: the deadline is noticed only when some
+        # other event triggers a reconcile (job.go:151-156; the only RequeueAfter is the TTL one).
+        # Fixed here: come back when the deadline expires.
+        ads = run_policy.get("activeDeadlineSeconds")
+        start = c.parse_time(job_status.get("startTime"))
+        if ads is not None and start is not None and result.requeue_after <= 0:
+            # requeue=False: a timer wake-up is not a retry and must not count towards backoffLimit
+            result = Result(requeue=False, requeue_after=max(start + float(ads) - time.time(), 0.0) + 0.05)
         return result
 
     def needs_service(self, rtype: str) -> bool:

@@ -91,6 +91,11 @@ class GpuGangScheduler(KubeBatchScheduler):
                 per_pod += int(lim.get("nvidia.com/gpu", 0) or 0)
             gpus += per_pod * c.replicas_of(spec)
         pg["spec"]["minResources"] = {"nvidia.com/gpu": gpus}
+        # RunPolicy.schedulingPolicy.minAvailable is declared but unused by the reference
+        # (SURVEY.md §2.6 item 18); here it lowers the gang size when present
+        min_avail = ((c.run_policy_of(job).get("schedulingPolicy") or {}).get("minAvailable"))
+        if min_avail is not None and 0 < int(min_avail) <= pg["spec"]["minMember"]:
+            pg["spec"]["minMember"] = int(min_avail)
         return pg
 
     def bind_pod_to_gang(self, pod_template, gang):

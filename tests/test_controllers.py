@@ -336,6 +336,19 @@ def test_gang_scheduling_kube_batch():
     assert "JobTerminated" in reasons and "SuccessfulDeletePodGroup" in reasons
 
 
+def test_gpu_gang_honours_min_available():
+    """schedulingPolicy.minAvailable is declared but unused by the reference; the gpu-gang scheduler uses
+    it as the gang size (capped by the replica count)."""
+    cl = Cluster(gang="gpu-gang")
+    job = _pt(workers=3)
+    job["spec"]["schedulingPolicy"] = {"minAvailable": 2}
+    cl.submit(job)
+    pg = cl.api.get("PodGroup", "ns", "pt")
+    assert pg["spec"]["minMember"] == 2
+    assert all(p["spec"]["schedulerName"] == "gpu-gang" for p in cl.pods("ns"))
+    assert all(p["metadata"]["annotations"]["kubedl.io/gang-name"] == "pt" for p in cl.pods("ns"))
+
+
 def test_gang_scheduler_registry_and_unknown_name():
     from kubedl_b200.plugins import gang_schedule
     cl = Cluster()

@@ -220,6 +220,22 @@ def test_active_deadline_marks_failed_and_cleans_up():
     assert cl.pods("ns") == []
 
 
+def test_active_deadline_fires_without_any_other_event():
+    """The reference only notices an expired deadline when something else triggers a reconcile
+    (SURVEY.md §2.6 item 15); here the reconcile asks to be woken up when the deadline passes."""
+    import time
+    cl = Cluster()
+    cl.submit(_tfjob(workers=1, activeDeadlineSeconds=2, cleanPodPolicy="All"))   # startTime has 1 s resolution
+    cl.kubelet.set_all("ns", "Running")
+    cl.settle()
+    assert cl.conditions("TFJob", "ns", "tf")[-1] == ("Running", "True")
+    assert cl.recs["TFJob"].controller.queue.pending_delayed() >= 1
+    time.sleep(2.2)
+    cl.settle()                                   # no pod / job event in between
+    assert cl.conditions("TFJob", "ns", "tf")[-1] == ("Failed", "True")
+    assert cl.pods("ns") == []
+
+
 def test_backoff_limit_exceeded_by_restart_counts():
     cl = Cluster()
     job = k.new_job("TFJob", "tf", "ns", {"Worker": {"replicas": 1, "restartPolicy": "OnFailure",

@@ -25,6 +25,8 @@ class FusedAllReduce:
         self.heap = heap
         self.lib = L.lib()
         self.timeout_ns = int(timeout_s * 1e9)
+        if max_blocks == 0:
+            max_blocks = int(os.environ.get("KUBEDL_AR_BLOCKS", "0"))
         self.max_blocks = max_blocks
         if use_nvls is None:
             # measured on 8xB200 (profiles/allreduce_*gpu.log): in-switch reduction wins from

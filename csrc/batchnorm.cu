@@ -40,7 +40,9 @@ struct BnReduceParams {
   // bwd finalisation
   bf16* dgamma;
   bf16* dbeta;
-  int relu;          // bwd: 1 = mask from y (b), 2 = mask recomputed from x with the forward affine (no y read)
+  int relu;          // bwd: 1 = mask from y (b), 2 = mask recomputed from x with the forward affine (no y read),
+                     //      3 = 1 bit per element saved by the forward pass (layers with a residual input)
+  const uint8_t* mask;   // [M*C/8], bit j of byte v = element 8v+j was positive
 };
 
 template <int MODE>
@@ -84,6 +86,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
         if (MODE == 1) {
           vc[u] = ld_stream(p.c + off);
           if (p.relu == 1) vb[u] = ld_stream(p.b + off);
+          else if (p.relu == 3) vb[u].x = p.mask[off >> 3];
         }
       }
     }
@@ -110,6 +113,9 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
           } else if (p.relu == 2) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) fa[j] = fmaf(fwa[j], fx[j], fwb[j]) > 0.f ? fa[j] : 0.f;
+          } else if (p.relu == 3) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) fa[j] = ((vb[u].x >> j) & 1u) ? fa[j] : 0.f;
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -227,7 +233,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
                                                        const bf16* __restrict__ res,
                                                        bf16* __restrict__ y, int64_t nvec, int cvec,
                                                        int C, const float* __restrict__ coef,
-                                                       int relu) {
+                                                       int relu, uint8_t* __restrict__ mask = nullptr) {
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float a[8], b[8];
@@ -273,6 +279,12 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
           for (int j = 0; j < 8; ++j) f[j] += r[j];
         }
         if (relu) {
+          if (mask) {      // 1 bit per element for the backward pass: 1/16 of the bytes of y
+            unsigned bits = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bits |= (f[j] > 0.f ? 1u : 0u) << j;
+            mask[k] = (uint8_t)bits;
+          }
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
         }
@@ -288,7 +300,8 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
                                                     const bf16* __restrict__ x,
                                                     const bf16* __restrict__ y, bf16* dx, bf16* dres,
                                                     int64_t nvec, int cvec, int C,
-                                                    const float* __restrict__ coef, int relu) {
+                                                    const float* __restrict__ coef, int relu,
+                                                    const uint8_t* __restrict__ mask = nullptr) {
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float A[8], B[8], D[8], Fb[8];
@@ -312,6 +325,7 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
         vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
         vx[u] = ld_stream(x + k * 8);
         if (relu == 1) vy[u] = ld_stream(y + k * 8);
+        else if (relu == 3) vy[u].x = mask[k];
       }
     }
 #pragma unroll
@@ -339,6 +353,9 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
         } else if (relu == 2) {      // A = gamma*rstd is also the forward scale
 #pragma unroll
           for (int j = 0; j < 8; ++j) fd[j] = fmaf(A[j], fx[j], Fb[j]) > 0.f ? fd[j] : 0.f;
+        } else if (relu == 3) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) fd[j] = ((vy[u].x >> j) & 1u) ? fd[j] : 0.f;
         }
         if (dres) *reinterpret_cast<uint4*>(dres + k * 8) = pack8(fd);
         float o[8];
@@ -420,11 +437,10 @@ static int apply_grid(int64_t nvec) {
   return (int)g;
 }
 
-extern "C" int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, int C,
-                          const float* gamma, const float* beta, float* running_mean,
-                          float* running_var, float eps, float momentum, int relu,
-                          float* save_mean_rstd, void* workspace, size_t workspace_bytes,
-                          cudaStream_t stream) {
+static int bn_fwd_impl(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,
+                       const float* beta, float* running_mean, float* running_var, float eps, float momentum,
+                       int relu, float* save_mean_rstd, uint8_t* relu_mask, void* workspace,
+                       size_t workspace_bytes, cudaStream_t stream) {
   BnPlan pl;
   unsigned* counter;
   float *coef, *partial;
@@ -446,24 +462,47 @@ extern "C" int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, in
   bool fixed = (256 % cvec) == 0;
   if (fixed)
     bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec,
-                                                 cvec, C, coef, relu);
+                                                 cvec, C, coef, relu, relu_mask);
   else
     bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec,
-                                                  cvec, C, coef, relu);
+                                                  cvec, C, coef, relu, relu_mask);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }
 
-extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dres,
-                          int64_t M, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
-                          int relu, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
-                          size_t workspace_bytes, cudaStream_t stream) {
+extern "C" int kdl_bn_fwd(const void* x, const void* res, void* y, int64_t M, int C,
+                          const float* gamma, const float* beta, float* running_mean,
+                          float* running_var, float eps, float momentum, int relu,
+                          float* save_mean_rstd, void* workspace, size_t workspace_bytes,
+                          cudaStream_t stream) {
+  return bn_fwd_impl(x, res, y, M, C, gamma, beta, running_mean, running_var, eps, momentum, relu, save_mean_rstd,
+                     nullptr, workspace, workspace_bytes, stream);
+}
+
+// Same, and additionally one bit per element (relu_mask, M*C/8 bytes): "was positive before the ReLU".
+// kdl_bn_bwd_mask reads that instead of the 16x larger y — for layers whose ReLU follows a residual add,
+// where the mask cannot be recomputed from x alone.
+extern "C" int kdl_bn_fwd_mask(const void* x, const void* res, void* y, int64_t M, int C,
+                               const float* gamma, const float* beta, float* running_mean,
+                               float* running_var, float eps, float momentum, int relu,
+                               float* save_mean_rstd, void* relu_mask, void* workspace, size_t workspace_bytes,
+                               cudaStream_t stream) {
+  return bn_fwd_impl(x, res, y, M, C, gamma, beta, running_mean, running_var, eps, momentum, relu, save_mean_rstd,
+                     (uint8_t*)relu_mask, workspace, workspace_bytes, stream);
+}
+
+static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, void* dres,
+                       int64_t M, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
+                       int relu, const uint8_t* relu_mask, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
+                       size_t workspace_bytes, cudaStream_t stream) {
   BnPlan pl;
   unsigned* counter;
   float *coef, *partial;
   int rc = carve(workspace, workspace_bytes, M, C, &pl, &counter, &coef, &partial);
   if (rc) return rc;
-  if (relu && y == nullptr) {
+  if (relu && relu_mask != nullptr) {
+    relu = 3;
+  } else if (relu && y == nullptr) {
     if (beta == nullptr) {
       kdl_set_error("bn_bwd: the relu mask needs y, or beta to recompute it from x");
       return KDL_ERR_ARG;
@@ -480,7 +519,7 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
   p.mean_rstd = const_cast<float*>(save_mean_rstd);
   p.coef = coef;
   p.dgamma = (bf16*)dgamma_bf16; p.dbeta = (bf16*)dbeta_bf16;
-  p.relu = relu;
+  p.relu = relu; p.mask = relu_mask;
   bn_reduce_kernel<1><<<dim3(pl.gx, pl.nslices), pl.threads, 0, stream>>>(p);
   KDL_CHECK_LAUNCH();
   int64_t nvec = M * C / 8;
@@ -491,12 +530,33 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
   bool fixed = (256 % cvec) == 0;
   if (fixed)
     bn_dx_kernel<true><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
-                                              (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu);
+                                              (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask);
   else
     bn_dx_kernel<false><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
-                                               (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu);
+                                               (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
+}
+
+extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dres,
+                          int64_t M, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
+                          int relu, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
+                          size_t workspace_bytes, cudaStream_t stream) {
+  return bn_bwd_impl(dy, x, y, dx, dres, M, C, gamma, beta, save_mean_rstd, relu, nullptr, dgamma_bf16, dbeta_bf16,
+                     workspace, workspace_bytes, stream);
+}
+
+// Backward with the ReLU mask taken from the bit mask kdl_bn_fwd_mask / kdl_bn_fwd_from_stats_mask saved.
+extern "C" int kdl_bn_bwd_mask(const void* dy, const void* x, const void* relu_mask, void* dx, void* dres,
+                               int64_t M, int C, const float* gamma, const float* save_mean_rstd,
+                               void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
+                               cudaStream_t stream) {
+  if (relu_mask == nullptr) {
+    kdl_set_error("bn_bwd_mask: relu_mask is null");
+    return KDL_ERR_ARG;
+  }
+  return bn_bwd_impl(dy, x, nullptr, dx, dres, M, C, gamma, nullptr, save_mean_rstd, 1, (const uint8_t*)relu_mask,
+                     dgamma_bf16, dbeta_bf16, workspace, workspace_bytes, stream);
 }
 
 // BN forward when the per-channel sums were already produced by the GEMM epilogue
@@ -541,11 +601,11 @@ __global__ void __launch_bounds__(1024) bn_finalize_partials_kernel(const float*
   }
 }
 
-extern "C" int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C,
-                                     const float* gamma, const float* beta, float* running_mean,
-                                     float* running_var, float eps, float momentum, int relu,
-                                     float* save_mean_rstd, const float* stats_partial, int nparts,
-                                     void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+static int bn_fwd_from_stats_impl(const void* x, const void* res, void* y, int64_t M, int C,
+                                  const float* gamma, const float* beta, float* running_mean,
+                                  float* running_var, float eps, float momentum, int relu,
+                                  float* save_mean_rstd, const float* stats_partial, int nparts, uint8_t* relu_mask,
+                                  void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   BnPlan pl;
   unsigned* counter;
   float *coef, *partial;
@@ -563,11 +623,31 @@ extern "C" int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, in
   int cvec = C / 8;
   int g = apply_grid(nvec);
   if ((256 % cvec) == 0)
-    bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu);
+    bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu, relu_mask);
   else
-    bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu);
+    bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu, relu_mask);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
+}
+
+extern "C" int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C,
+                                     const float* gamma, const float* beta, float* running_mean,
+                                     float* running_var, float eps, float momentum, int relu,
+                                     float* save_mean_rstd, const float* stats_partial, int nparts,
+                                     void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  return bn_fwd_from_stats_impl(x, res, y, M, C, gamma, beta, running_mean, running_var, eps, momentum, relu,
+                                save_mean_rstd, stats_partial, nparts, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int kdl_bn_fwd_from_stats_mask(const void* x, const void* res, void* y, int64_t M, int C,
+                                          const float* gamma, const float* beta, float* running_mean,
+                                          float* running_var, float eps, float momentum, int relu,
+                                          float* save_mean_rstd, const float* stats_partial, int nparts,
+                                          void* relu_mask, void* workspace, size_t workspace_bytes,
+                                          cudaStream_t stream) {
+  return bn_fwd_from_stats_impl(x, res, y, M, C, gamma, beta, running_mean, running_var, eps, momentum, relu,
+                                save_mean_rstd, stats_partial, nparts, (uint8_t*)relu_mask, workspace, workspace_bytes,
+                                stream);
 }
 
 // ---------------------------------------------------------------------------------------------

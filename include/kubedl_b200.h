@@ -50,6 +50,23 @@ int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx, void* dre
                void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
 
+/* ReLU bit mask: kdl_bn_fwd_mask / kdl_bn_fwd_from_stats_mask additionally write one bit per element
+ * ("positive before the ReLU", M*C/8 bytes, bit j of byte v = element 8v+j; may be NULL), and
+ * kdl_bn_bwd_mask reads those bits instead of y.  For a ReLU that follows a residual add the mask cannot
+ * be recomputed from x, and y is 16x the size of the bit mask. */
+int kdl_bn_fwd_mask(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,
+                    const float* beta, float* running_mean, float* running_var, float eps, float momentum,
+                    int relu, float* save_mean_rstd, void* relu_mask, void* workspace, size_t workspace_bytes,
+                    cudaStream_t stream);
+int kdl_bn_bwd_mask(const void* dy, const void* x, const void* relu_mask, void* dx, void* dres, int64_t M, int C,
+                    const float* gamma, const float* save_mean_rstd, void* dgamma_bf16, void* dbeta_bf16,
+                    void* workspace, size_t workspace_bytes, cudaStream_t stream);
+int kdl_bn_fwd_from_stats_mask(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,
+                               const float* beta, float* running_mean, float* running_var, float eps,
+                               float momentum, int relu, float* save_mean_rstd, const float* stats_partial,
+                               int nparts, void* relu_mask, void* workspace, size_t workspace_bytes,
+                               cudaStream_t stream);
+
 /* BN forward fed by the column statistics a preceding kdl_gemm_bf16_ex call produced in its
  * epilogue ([nparts][2][C] partial sums): the separate statistics pass over x is skipped. */
 int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,

@@ -136,16 +136,23 @@ class BN:
         self.running_var = torch.ones(self.c, dtype=torch.float32, device=dev)
         self.save = torch.empty(2, self.c, dtype=torch.float32, device=dev)
 
-    def fwd(self, x, res=None, stats=None):
+    def fwd(self, x, res=None, stats=None, train=True):
+        # ReLU after a residual add: the mask cannot be recomputed from x alone, so the forward pass
+        # leaves one bit per element for the backward pass (instead of the backward reading y twice)
+        self.mask = None
+        if res is not None and self.relu and train and self.net.bn_relu_bitmask:
+            self.mask = torch.empty(x.numel() // 8, dtype=torch.uint8, device=x.device)
         y, _ = K.bn_fwd(x, self.gamma, self.beta, self.running_mean, self.running_var, res=res,
-                        relu=self.relu, save=self.save, stats=stats)
+                        relu=self.relu, save=self.save, stats=stats, relu_mask=self.mask)
         return y
 
     def bwd(self, dy, x, y, dres=None, had_residual=False):
         """y is read for the ReLU mask only when the forward pass added a residual; otherwise the mask
         is recomputed from x (one tensor less to stream in both backward passes)."""
-        return K.bn_bwd(dy, x, y if (self.relu and had_residual) else None, self.gamma, self.save, self.relu,
-                        self.dgamma, self.dbeta, dres=dres, beta=self.beta)
+        mask = getattr(self, "mask", None) if had_residual else None
+        self.mask = None
+        return K.bn_bwd(dy, x, y if (self.relu and had_residual and mask is None) else None, self.gamma, self.save,
+                        self.relu, self.dgamma, self.dbeta, dres=dres, beta=self.beta, relu_mask=mask)
 
 
 class Bottleneck:
@@ -190,7 +197,7 @@ class Bottleneck:
             idn = self.bd.fwd(cdo, stats=sd)
         else:
             cdo, idn = None, x
-        out = self.b3.fwd(c3, res=idn, stats=s3)
+        out = self.b3.fwd(c3, res=idn, stats=s3, train=train)
         if train:
             self.saved = (x, c1, a1, c2, a2, c3, cdo, out)
         return out
@@ -229,6 +236,8 @@ class ResNet50:
         # (profiles/bench_1gpu_bnstats_ab.log).  The first version used shared-memory float atomics
         # (CAS loops) and a serial finalizer and was slower than the separate pass.
         self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "1") == "1"
+        # ReLU masks of the residual BatchNorms as 1 bit per element (0: the backward pass reads y)
+        self.bn_relu_bitmask = _os.environ.get("KUBEDL_BN_BITMASK", "1") == "1"
         # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
         # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
         # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.

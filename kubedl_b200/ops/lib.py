@@ -30,6 +30,14 @@ _SIGS = {
     "kdl_bn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                            c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
                            c_void_p]),
+    "kdl_bn_fwd_mask": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
+                                c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p,
+                                c_size_t, c_void_p]),
+    "kdl_bn_bwd_mask": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "kdl_bn_fwd_from_stats_mask": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_void_p, c_int,
+                                           c_void_p, c_void_p, c_size_t, c_void_p]),
     "kdl_bn_fwd_from_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
                                       c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_void_p, c_int,
                                       c_void_p, c_size_t, c_void_p]),

@@ -39,9 +39,12 @@ def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
            running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
            res: Optional[torch.Tensor] = None, relu: bool = True, eps: float = 1e-5,
            momentum: float = 0.1, out: Optional[torch.Tensor] = None,
-           save: Optional[torch.Tensor] = None, stats=None) -> Tuple[torch.Tensor, torch.Tensor]:
+           save: Optional[torch.Tensor] = None, stats=None,
+           relu_mask: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """y = relu(bn_train(x) + res) on x:[M,C] (or [N,H,W,C]) bf16. Returns (y, save_mean_rstd[2,C]).
-    `stats` = (partial, nparts) from Gemm.nt_stats: the statistics pass over x is skipped."""
+    `stats` = (partial, nparts) from Gemm.nt_stats: the statistics pass over x is skipped.
+    `relu_mask` (uint8 [M*C/8]) receives one bit per element, "positive before the ReLU", for
+    bn_bwd(relu_mask=...) — 1/16 of the bytes of y."""
     _chk_bf16(x, res)
     Cn = x.shape[-1]
     M = x.numel() // Cn
@@ -53,18 +56,21 @@ def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
     if need == 0:
         raise L.KernelError(f"bn_fwd: unsupported shape M={M} C={Cn}")
     ws = workspace(need, x.device)
+    if relu_mask is not None:
+        assert relu_mask.dtype == torch.uint8 and relu_mask.numel() * 8 == x.numel() and relu_mask.is_contiguous()
     if stats is not None:
         partial, nparts = stats
-        L.check(lib.kdl_bn_fwd_from_stats(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
-                                          beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps,
-                                          momentum, int(relu), save.data_ptr(), partial.data_ptr(), nparts,
-                                          ws.data_ptr(), ws.numel(), L.stream_ptr()), "kdl_bn_fwd_from_stats")
+        L.check(lib.kdl_bn_fwd_from_stats_mask(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
+                                               beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps,
+                                               momentum, int(relu), save.data_ptr(), partial.data_ptr(), nparts,
+                                               L.ptr(relu_mask), ws.data_ptr(), ws.numel(), L.stream_ptr()),
+                "kdl_bn_fwd_from_stats_mask")
         L.count(2)
         return y, save
-    L.check(lib.kdl_bn_fwd(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
-                           beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps, momentum,
-                           int(relu), save.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()),
-            "kdl_bn_fwd")
+    L.check(lib.kdl_bn_fwd_mask(x.data_ptr(), L.ptr(res), y.data_ptr(), M, Cn, gamma.data_ptr(),
+                                beta.data_ptr(), L.ptr(running_mean), L.ptr(running_var), eps, momentum,
+                                int(relu), save.data_ptr(), L.ptr(relu_mask), ws.data_ptr(), ws.numel(),
+                                L.stream_ptr()), "kdl_bn_fwd_mask")
     L.count(2)
     return y, save
 
@@ -72,11 +78,12 @@ def bn_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
 def bn_bwd(dy: torch.Tensor, x: torch.Tensor, y: Optional[torch.Tensor], gamma: torch.Tensor,
            save: torch.Tensor, relu: bool, dgamma: torch.Tensor, dbeta: torch.Tensor,
            dx: Optional[torch.Tensor] = None, dres: Optional[torch.Tensor] = None,
-           beta: Optional[torch.Tensor] = None) -> torch.Tensor:
+           beta: Optional[torch.Tensor] = None, relu_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Backward of bn_fwd.  dgamma/dbeta: bf16 [C] (views into the gradient arena).  If `dres`
     is given it receives dz = dy * relu_mask (the gradient of the residual input); it may alias
     dy.  With relu and y=None (layers without a residual input) the mask is recomputed from x with
-    the forward affine (`beta` required) and y is never read."""
+    the forward affine (`beta` required) and y is never read; with `relu_mask` (the bit mask bn_fwd
+    saved) the mask bits are read instead of y."""
     _chk_bf16(dy, x, y, dx, dres, dgamma, dbeta)
     Cn = x.shape[-1]
     M = x.numel() // Cn
@@ -85,6 +92,12 @@ def bn_bwd(dy: torch.Tensor, x: torch.Tensor, y: Optional[torch.Tensor], gamma: 
     lib = L.lib()
     need = lib.kdl_bn_workspace_bytes(M, Cn)
     ws = workspace(need, x.device)
+    if relu and relu_mask is not None:
+        L.check(lib.kdl_bn_bwd_mask(dy.data_ptr(), x.data_ptr(), relu_mask.data_ptr(), dx.data_ptr(), L.ptr(dres), M, Cn,
+                                    gamma.data_ptr(), save.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), L.stream_ptr()), "kdl_bn_bwd_mask")
+        L.count(2)
+        return dx
     L.check(lib.kdl_bn_bwd(dy.data_ptr(), x.data_ptr(), L.ptr(y), dx.data_ptr(), L.ptr(dres), M, Cn,
                            gamma.data_ptr(), L.ptr(beta), save.data_ptr(), int(relu), dgamma.data_ptr(),
                            dbeta.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()),

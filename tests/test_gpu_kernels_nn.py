@@ -66,6 +66,16 @@ def test_bn_fwd_bwd(cuda, M, C, relu, use_res):
         dy2 = dy.clone()
         dx2 = K.bn_bwd(dy2, x, y, gamma, save, relu, dgamma, dbeta, dres=dy2)
         assert torch.equal(dx2, dx) and torch.equal(dy2, dres)
+        if relu:
+            # the forward pass can leave a 1-bit-per-element mask; backward from it == backward from y
+            mask = torch.empty(M * C // 8, dtype=torch.uint8, device=cuda)
+            y3, _ = K.bn_fwd(x, gamma, beta, None, None, res=res, relu=relu, relu_mask=mask)
+            assert torch.equal(y3, y)
+            dg4, db4 = torch.empty_like(dgamma), torch.empty_like(dbeta)
+            dres4 = torch.empty_like(dy)
+            dx4 = K.bn_bwd(dy, x, None, gamma, save, relu, dg4, db4, dres=dres4, relu_mask=mask)
+            assert torch.equal(dx4, dx) and torch.equal(dres4, dres)
+            assert torch.equal(dg4, dgamma) and torch.equal(db4, dbeta)
     elif relu:
         # without a residual the ReLU mask can be recomputed from x: same result, y never read
         dg3, db3 = torch.empty_like(dgamma), torch.empty_like(dbeta)

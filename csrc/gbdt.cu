@@ -73,6 +73,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
   extern __shared__ int hist[];
   __shared__ int s_last;
   const int hist_floats = p.F * kBins * 2;
+  const int plane = p.F * kBins;
   const int tid = threadIdx.x;
 
   // blockIdx.y = index into the build list; blockIdx.x = tile of that node's rows (strided)
@@ -104,9 +105,10 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
         for (int f = 0; f < 32; ++f) {
           if (f < p.F) {
             const uint32_t bin = (w[f >> 2] >> ((f & 3) * 8)) & 0xffu;
-            int* h = hist + ((size_t)f * kBins + bin) * 2;
-            atomicAdd(h, gq);
-            atomicAdd(h + 1, hq);
+            // g and h live in separate planes: lane addresses are bin-strided by ONE word, so a warp's
+            // atomics spread over all 32 banks (interleaved (g,h) pairs only ever hit the even ones)
+            atomicAdd(hist + f * kBins + bin, gq);
+            atomicAdd(hist + plane + f * kBins + bin, hq);
           }
         }
       }
@@ -118,7 +120,9 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(HistParams
         for (int i = tid; i < hist_floats; i += kHistThreads) {
           const int v = hist[i];
           if (v != 0) {
-            atomicAdd(local + i, (float)v * p.inv_qscale);
+            // plane layout [2][F][256] in shared memory -> interleaved [F][256][2] in global memory
+            const int o = i < plane ? 2 * i : 2 * (i - plane) + 1;
+            atomicAdd(local + o, (float)v * p.inv_qscale);
             hist[i] = 0;
           }
         }

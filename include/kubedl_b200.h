@@ -142,6 +142,21 @@ int kdl_gemm_bf16_subadd(const void* A, const void* B, void* C, int M, int N, in
                          int b_mn_major, int lda, int ldb, int ldc, const void* addend_compact, int H, int W,
                          cudaStream_t stream);
 
+/* ---- N7c: the 7x7 / stride-2 stem convolution straight from the uint8 image (224x224) -----------------
+ * Builder warps normalise the image rows and write the patch tile of one output row directly in the
+ * swizzled shared-memory layout tcgen05.mma reads; no patch matrix exists in global memory.  w / gw are
+ * [64][168] in the kh*24 + kw*3 + c column layout.  fwd optionally emits BatchNorm column statistics
+ * ([kdl_stem_conv_max_parts()][2][64]); wgrad keeps D[64,192] in TMEM across all rows of a CTA and needs
+ * kdl_stem_conv_wgrad_scratch_bytes() of scratch.  No reference counterpart. */
+int kdl_stem_conv_supported(int H, int W);
+int kdl_stem_conv_max_parts(void);
+size_t kdl_stem_conv_wgrad_scratch_bytes(void);
+int kdl_stem_conv_fwd(const void* img_u8, const void* w_padded, void* y, int N, int H, int W, const float* mean3,
+                      const float* std3, float* stats_partial, int* stats_parts_out, cudaStream_t stream);
+int kdl_stem_conv_wgrad(const void* img_u8, const void* dy, void* gw_padded, int N, int H, int W,
+                        const float* mean3, const float* std3, void* scratch, size_t scratch_bytes,
+                        cudaStream_t stream);
+
 /* ---- N7: implicit-GEMM convolution on the same tcgen05 kernel (NHWC bf16) ------------------
  * The activation operand is fetched with TMA im2col loads (no patch matrix in memory).  mode 0 =
  * fprop (x, w -> y), 1 = dgrad (dy, w -> dx [+addend]; stride-1 "same" convolutions), 2 = wgrad

@@ -238,6 +238,8 @@ class ResNet50:
         self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "1") == "1"
         # ReLU masks of the residual BatchNorms as 1 bit per element (0: the backward pass reads y)
         self.bn_relu_bitmask = _os.environ.get("KUBEDL_BN_BITMASK", "1") == "1"
+        # stem convolution straight from the uint8 image (224x224 inputs); 0: im2col patch matrix + GEMM
+        self.stem_direct = _os.environ.get("KUBEDL_STEM_DIRECT", "1") == "1"
         # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
         # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
         # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.
@@ -288,13 +290,18 @@ class ResNet50:
         if stem_gemm:
             assert self.gemm is not None
             N, H, W, _ = x.shape
-            patches = K.stem_im2col(x)
-            if self.fuse_bn_stats:
-                c, stem_stats = self.gemm.nt_stats(patches, self._stem_w_padded())
+            if self.stem_direct and K.stem_conv_supported(H, W):
+                # straight from the uint8 image: patch tiles are built in shared memory (csrc/stem_conv.cu)
+                c, stem_stats = K.stem_conv_fwd(x, self._stem_w_padded(), want_stats=self.fuse_bn_stats)
+                x_bf16_nhwc = x
             else:
-                c, stem_stats = self.gemm.nt(patches, self._stem_w_padded()), None
-            c = c.view(N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, 64)
-            x_bf16_nhwc = patches
+                patches = K.stem_im2col(x)
+                if self.fuse_bn_stats:
+                    c, stem_stats = self.gemm.nt_stats(patches, self._stem_w_padded())
+                else:
+                    c, stem_stats = self.gemm.nt(patches, self._stem_w_padded()), None
+                c = c.view(N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, 64)
+                x_bf16_nhwc = patches
         else:
             x_bf16_nhwc = x
             c, stem_stats = self.stem.fwd(x_bf16_nhwc), None
@@ -333,7 +340,11 @@ class ResNet50:
             dh = b.bwd(dh)
         da = K.maxpool3x3s2_bwd(dh, idx, a.shape)
         dc = self.stem_bn.bwd(da, c, a)
-        if x.dim() == 2:   # im2col patches: stem wgrad is one tn GEMM (split over the 3.2 M rows)
+        if x.dtype == torch.uint8:    # direct stem kernels: patch tiles rebuilt in shared memory
+            gw = K.stem_conv_wgrad(x, dc)
+            self.arena.grad("conv1").view(64, 147).copy_(K.stem_weight_unpad(gw))
+            self.reducer_ready(self.stem.g_end)
+        elif x.dim() == 2:   # im2col patches: stem wgrad is one tn GEMM (split over the 3.2 M rows)
             gw = self.gemm.tn(dc.view(-1, 64), x)
             self.arena.grad("conv1").view(64, 147).copy_(K.stem_weight_unpad(gw))
             self.reducer_ready(self.stem.g_end)

@@ -152,6 +152,41 @@ def stem_im2col(img_u8: torch.Tensor, out: Optional[torch.Tensor] = None) -> tor
     return out
 
 
+def stem_conv_supported(H: int, W: int) -> bool:
+    return bool(L.lib().kdl_stem_conv_supported(H, W))
+
+
+def stem_conv_fwd(img_u8: torch.Tensor, w_padded: torch.Tensor, want_stats: bool = False):
+    """7x7/s2/p3 stem convolution straight from the uint8 NHWC image (csrc/stem_conv.cu): no patch matrix
+    in memory.  w_padded: [64, 168] (stem_weight_padded).  Returns (y [N,112,112,64], stats or None) with
+    stats = (partial, nparts) for bn_fwd(stats=...)."""
+    assert img_u8.dtype == torch.uint8 and img_u8.shape[-1] == 3 and img_u8.is_contiguous()
+    assert w_padded.shape == (64, STEM_KP) and w_padded.is_contiguous()
+    N, H, W, _ = img_u8.shape
+    lib = L.lib()
+    y = torch.empty(N, H // 2, W // 2, 64, dtype=torch.bfloat16, device=img_u8.device)
+    partial, nparts = None, C.c_int(0)
+    if want_stats:
+        partial = torch.empty(lib.kdl_stem_conv_max_parts(), 2, 64, dtype=torch.float32, device=img_u8.device)
+    L.check(lib.kdl_stem_conv_fwd(img_u8.data_ptr(), w_padded.data_ptr(), y.data_ptr(), N, H, W, _IMAGENET_MEAN,
+                                  _IMAGENET_STD, L.ptr(partial), C.byref(nparts), L.stream_ptr()), "kdl_stem_conv_fwd")
+    L.count(1)
+    return y, ((partial, nparts.value) if want_stats else None)
+
+
+def stem_conv_wgrad(img_u8: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
+    """Weight gradient of the stem, [64, 168] in the padded column layout (stem_weight_unpad)."""
+    N, H, W, _ = img_u8.shape
+    assert dy.dtype == torch.bfloat16 and dy.is_contiguous() and dy.numel() == N * (H // 2) * (W // 2) * 64
+    lib = L.lib()
+    ws = workspace(lib.kdl_stem_conv_wgrad_scratch_bytes(), img_u8.device, key="stem_wgrad")
+    gw = torch.empty(64, STEM_KP, dtype=torch.bfloat16, device=img_u8.device)
+    L.check(lib.kdl_stem_conv_wgrad(img_u8.data_ptr(), dy.data_ptr(), gw.data_ptr(), N, H, W, _IMAGENET_MEAN,
+                                    _IMAGENET_STD, ws.data_ptr(), ws.numel(), L.stream_ptr()), "kdl_stem_conv_wgrad")
+    L.count(2)
+    return gw
+
+
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, V: Optional[int] = None,
                  grad_scale: Optional[float] = None, dlogits: Optional[torch.Tensor] = None,
                  loss: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:

@@ -174,3 +174,34 @@ def test_stem_im2col_gemm_matches_conv2d(cuda):
     yr.backward(dy.float().permute(0, 3, 1, 2))
     gw = K.stem_weight_unpad(g.tn(dy.view(-1, 64), patches)).view(64, 7, 7, 3)
     assert _cos(gw, wr.grad.permute(0, 2, 3, 1)) > 0.999
+
+
+def test_stem_direct_conv_matches_patch_gemm(cuda):
+    """Stem convolution straight from the uint8 image (no patch matrix): forward, BN statistics and weight
+    gradient against the im2col + GEMM path and conv2d."""
+    from kubedl_b200.ops import nn as K
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(0)
+    N, S = 3, 224
+    img = torch.randint(0, 256, (N, S, S, 3), dtype=torch.uint8, device=cuda)
+    w = (torch.randn(64, 7, 7, 3, device=cuda) * 0.05).bfloat16()
+    wp = K.stem_weight_padded(w)
+    y, (partial, nparts) = K.stem_conv_fwd(img, wp, want_stats=True)
+    xn = K.u8_normalize(img).float().permute(0, 3, 1, 2)
+    wr = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xn, wr, stride=2, padding=3)
+    torch.testing.assert_close(y.float(), yr.permute(0, 2, 3, 1), atol=5e-2, rtol=3e-2)
+    y2 = g.nt(K.stem_im2col(img), wp).view(N, 112, 112, 64)
+    assert float((y.float() - y2.float()).abs().max()) < 2e-2
+    # statistics of the stored bf16 values
+    s = partial[:nparts].sum(0)
+    yf = y.float().view(-1, 64)
+    torch.testing.assert_close(s[0], yf.sum(0), atol=0.5, rtol=1e-3)
+    torch.testing.assert_close(s[1], (yf * yf).sum(0), atol=0.5, rtol=1e-3)
+    dy = torch.randn_like(y)
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    gw = K.stem_weight_unpad(K.stem_conv_wgrad(img, dy)).view(64, 7, 7, 3)
+    assert _cos(gw, wr.grad.permute(0, 2, 3, 1)) > 0.999
+    err = float((gw.float() - wr.grad.permute(0, 2, 3, 1)).abs().max() / wr.grad.abs().max())
+    assert err < 2e-2, err

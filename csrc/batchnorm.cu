@@ -630,6 +630,24 @@ static int bn_fwd_from_stats_impl(const void* x, const void* res, void* y, int64
   return KDL_OK;
 }
 
+// Only the finalisation: mean / rstd (save_mean_rstd), running statistics and the forward coefficients
+// coef_out = [2][C] (a = gamma*rstd, b = beta - mean*a) from epilogue partials — for consumers that apply
+// the affine themselves (kdl_maxpool3x3s2_affine_relu_fwd).
+extern "C" int kdl_bn_finalize_from_stats(int64_t M, int C, const float* gamma, const float* beta,
+                                          float* running_mean, float* running_var, float eps, float momentum,
+                                          float* save_mean_rstd, const float* stats_partial, int nparts,
+                                          float* coef_out, cudaStream_t stream) {
+  if (nparts < 1 || stats_partial == nullptr || coef_out == nullptr || save_mean_rstd == nullptr) {
+    kdl_set_error("bn_finalize_from_stats: missing partial statistics or outputs");
+    return KDL_ERR_ARG;
+  }
+  bn_finalize_partials_kernel<<<(C + 31) / 32, 1024, 0, stream>>>(stats_partial, nparts, M, C, gamma, beta,
+                                                                   running_mean, running_var, eps, momentum,
+                                                                   save_mean_rstd, coef_out);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
 extern "C" int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C,
                                      const float* gamma, const float* beta, float* running_mean,
                                      float* running_var, float eps, float momentum, int relu,

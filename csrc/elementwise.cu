@@ -170,10 +170,15 @@ __global__ void __launch_bounds__(256) add_bf16_kernel(const bf16* a, const bf16
 
 // 3x3 stride-2 pad-1 max-pool on NHWC bf16; saves the argmax (0..8) per output vector lane so
 // the backward pass is a gather (each input pixel looks at the <=4 windows that cover it).
+// AFFINE: the input is a raw convolution output and y = maxpool(relu(a*x + b)) with per-channel (a, b) —
+// BatchNorm apply + ReLU + max-pool of the ResNet stem in one pass; the normalised activation (411 MB at
+// batch 256) is never written or re-read.
+template <bool AFFINE>
 __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __restrict__ x,
                                                                bf16* __restrict__ y,
                                                                uint8_t* __restrict__ idx, int N,
-                                                               int H, int W, int C, int OH, int OW) {
+                                                               int H, int W, int C, int OH, int OW,
+                                                               const float* __restrict__ coef) {
   const int cvec = C / 8;
   const int64_t total = (int64_t)N * OH * OW * cvec;
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
@@ -185,6 +190,11 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __res
     int n = (int)(t / OH);
     float best[8];
     int bi[8];
+    float ca[8], cb[8];
+    if (AFFINE) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { ca[j] = coef[cg * 8 + j]; cb[j] = coef[C + cg * 8 + j]; }
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) { best[j] = -FLT_MAX; bi[j] = 4; }
 #pragma unroll
@@ -198,6 +208,11 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __res
         uint4 v = ld_plain(x + (((int64_t)n * H + ih) * W + iw) * C + cg * 8);
         float f[8];
         unpack8(v, f);
+        if (AFFINE) {     // same rounding as the separate BatchNorm pass: bf16 before the comparison
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            f[j] = __bfloat162float(__float2bfloat16(fmaxf(fmaf(ca[j], f[j], cb[j]), 0.f)));
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           if (f[j] > best[j]) { best[j] = f[j]; bi[j] = kh * 3 + kw; }
@@ -434,8 +449,23 @@ extern "C" int kdl_maxpool3x3s2_fwd(const void* x, void* y, void* idx_u8, int N,
   }
   int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
   int64_t total = (int64_t)N * OH * OW * (C / 8);
-  maxpool3x3s2_fwd_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
-      (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, OH, OW);
+  maxpool3x3s2_fwd_kernel<false><<<grid_for(total, 256), 256, 0, stream>>>(
+      (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, OH, OW, nullptr);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+// y = maxpool3x3s2(relu(a*x + b)), coef = [2][C] (a, b) as kdl_bn_finalize_from_stats writes them
+extern "C" int kdl_maxpool3x3s2_affine_relu_fwd(const void* x, const float* coef, void* y, void* idx_u8, int N,
+                                                int H, int W, int C, cudaStream_t stream) {
+  if (C % 8 || coef == nullptr) {
+    kdl_set_error("maxpool_affine: C must be a multiple of 8 and coef non-null");
+    return KDL_ERR_ARG;
+  }
+  int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+  int64_t total = (int64_t)N * OH * OW * (C / 8);
+  maxpool3x3s2_fwd_kernel<true><<<grid_for(total, 256), 256, 0, stream>>>(
+      (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, OH, OW, coef);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }

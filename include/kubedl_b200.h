@@ -67,6 +67,15 @@ int kdl_bn_fwd_from_stats_mask(const void* x, const void* res, void* y, int64_t 
                                int nparts, void* relu_mask, void* workspace, size_t workspace_bytes,
                                cudaStream_t stream);
 
+/* Finalisation only (mean / rstd, running statistics, forward coefficients coef_out = [2][C]) from epilogue
+ * partials, and a 3x3/s2 max-pool that applies relu(a*x + b) on load: BatchNorm apply + ReLU + max-pool of
+ * the ResNet stem in one pass, the normalised activation is never materialised. */
+int kdl_bn_finalize_from_stats(int64_t M, int C, const float* gamma, const float* beta, float* running_mean,
+                               float* running_var, float eps, float momentum, float* save_mean_rstd,
+                               const float* stats_partial, int nparts, float* coef_out, cudaStream_t stream);
+int kdl_maxpool3x3s2_affine_relu_fwd(const void* x, const float* coef, void* y, void* idx_u8, int N, int H, int W,
+                                     int C, cudaStream_t stream);
+
 /* BN forward fed by the column statistics a preceding kdl_gemm_bf16_ex call produced in its
  * epilogue ([nparts][2][C] partial sums): the separate statistics pass over x is skipped. */
 int kdl_bn_fwd_from_stats(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,

@@ -240,6 +240,7 @@ class ResNet50:
         self.bn_relu_bitmask = _os.environ.get("KUBEDL_BN_BITMASK", "1") == "1"
         # stem convolution straight from the uint8 image (224x224 inputs); 0: im2col patch matrix + GEMM
         self.stem_direct = _os.environ.get("KUBEDL_STEM_DIRECT", "1") == "1"
+        self.fuse_stem_pool = _os.environ.get("KUBEDL_FUSE_STEM_POOL", "1") == "1"
         # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
         # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
         # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.
@@ -305,8 +306,15 @@ class ResNet50:
         else:
             x_bf16_nhwc = x
             c, stem_stats = self.stem.fwd(x_bf16_nhwc), None
-        a = self.stem_bn.fwd(c, stats=stem_stats)
-        p, idx = K.maxpool3x3s2_fwd(a)
+        if stem_stats is not None and self.fuse_stem_pool:
+            # BN apply + ReLU + max-pool in one pass over the convolution output; the normalised
+            # activation is not needed by the backward pass either (its ReLU mask is recomputed from c)
+            sb = self.stem_bn
+            p, idx = K.bn_relu_maxpool_fwd(c, sb.gamma, sb.beta, sb.running_mean, sb.running_var, sb.save, stem_stats)
+            a = None
+        else:
+            a = self.stem_bn.fwd(c, stats=stem_stats)
+            p, idx = K.maxpool3x3s2_fwd(a)
         h = p
         for b in self.blocks:
             h = b.fwd(h, train)
@@ -338,7 +346,7 @@ class ResNet50:
         dh = K.avgpool_bwd(dpooled, hshape)
         for b in reversed(self.blocks):
             dh = b.bwd(dh)
-        da = K.maxpool3x3s2_bwd(dh, idx, a.shape)
+        da = K.maxpool3x3s2_bwd(dh, idx, c.shape)
         dc = self.stem_bn.bwd(da, c, a)
         if x.dtype == torch.uint8:    # direct stem kernels: patch tiles rebuilt in shared memory
             gw = K.stem_conv_wgrad(x, dc)

@@ -45,6 +45,10 @@ _SIGS = {
                                  C.POINTER(c_float), c_void_p]),
     "kdl_stem_im2col_u8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, C.POINTER(c_float),
                                    C.POINTER(c_float), c_void_p]),
+    "kdl_bn_finalize_from_stats": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float,
+                                           c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "kdl_maxpool3x3s2_affine_relu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                                 c_void_p]),
     "kdl_stem_conv_supported": (c_int, [c_int, c_int]),
     "kdl_stem_conv_max_parts": (c_int, []),
     "kdl_stem_conv_wgrad_scratch_bytes": (c_size_t, []),

@@ -245,6 +245,28 @@ def maxpool3x3s2_fwd(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     return y, idx
 
 
+def bn_relu_maxpool_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, running_mean, running_var,
+                        save: torch.Tensor, stats, eps: float = 1e-5, momentum: float = 0.1):
+    """maxpool3x3s2(relu(bn_train(x))) in one pass over x [N,H,W,C] (a raw convolution output whose column
+    statistics `stats` = (partial, nparts) came from the producing kernel's epilogue).  The normalised
+    activation is never materialised.  Returns (pooled, idx); `save` receives mean / rstd."""
+    _chk_bf16(x)
+    N, H, W, Cn = x.shape
+    partial, nparts = stats
+    lib = L.lib()
+    coef = torch.empty(2, Cn, dtype=torch.float32, device=x.device)
+    L.check(lib.kdl_bn_finalize_from_stats(N * H * W, Cn, gamma.data_ptr(), beta.data_ptr(), L.ptr(running_mean),
+                                           L.ptr(running_var), eps, momentum, save.data_ptr(), partial.data_ptr(),
+                                           nparts, coef.data_ptr(), L.stream_ptr()), "kdl_bn_finalize_from_stats")
+    OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    y = torch.empty(N, OH, OW, Cn, dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty(N, OH, OW, Cn, dtype=torch.uint8, device=x.device)
+    L.check(lib.kdl_maxpool3x3s2_affine_relu_fwd(x.data_ptr(), coef.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W,
+                                                 Cn, L.stream_ptr()), "kdl_maxpool3x3s2_affine_relu_fwd")
+    L.count(2)
+    return y, idx
+
+
 def maxpool3x3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, in_shape) -> torch.Tensor:
     _chk_bf16(dy)
     N, H, W, Cn = in_shape

@@ -191,3 +191,30 @@ def test_allreduce_protocol_emulated(cuda, W, n, dt_in, dt_out):
         for o in outs:
             torch.testing.assert_close(o.float(), ref * (it + 2), atol=tol * (it + 2), rtol=tol)
     assert int(run.state["status"][0].item()) == 0
+
+
+def test_bn_relu_maxpool_fused_matches_separate_passes(cuda):
+    """BN apply + ReLU + 3x3/s2 max-pool in one pass (statistics from the producer's epilogue) == bn_fwd then
+    maxpool; argmax indices may differ only on exact ties."""
+    from kubedl_b200.ops import nn as K
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(4)
+    N, H, C, Kd = 3, 16, 64, 64
+    a = torch.randn(N * H * H, Kd, device=cuda).bfloat16()
+    w = torch.randn(C, Kd, device=cuda).bfloat16()
+    x2, stats = g.nt_stats(a, w)
+    x = x2.view(N, H, H, C)
+    gamma = torch.rand(C, device=cuda) + 0.5
+    beta = torch.randn(C, device=cuda) * 0.1
+    save1 = torch.empty(2, C, device=cuda)
+    y, _ = K.bn_fwd(x, gamma, beta, None, None, relu=True, save=save1, stats=stats)
+    p_ref, _ = K.maxpool3x3s2_fwd(y)
+    save2 = torch.empty(2, C, device=cuda)
+    p, idx = K.bn_relu_maxpool_fwd(x, gamma, beta, None, None, save2, stats)
+    assert torch.equal(save1, save2)
+    assert torch.equal(p, p_ref)
+    # the saved argmax really points at the maximum
+    dy = torch.ones_like(p)
+    dx = K.maxpool3x3s2_bwd(dy, idx, x.shape)
+    assert float(dx.float().sum()) == float(p.numel())

@@ -43,7 +43,47 @@ struct BnReduceParams {
   int relu;          // bwd: 1 = mask from y (b), 2 = mask recomputed from x with the forward affine (no y read),
                      //      3 = 1 bit per element saved by the forward pass (layers with a residual input)
   const uint8_t* mask;   // [M*C/8], bit j of byte v = element 8v+j was positive
+  // bwd: dy is not in memory but the gradient of a 3x3/s2 max-pool output (pool_dp, pool_idx): it is
+  // gathered on the fly from the <= 4 windows covering each pixel (rows of this BN = pixels of an H x W map)
+  const bf16* pool_dp;
+  const uint8_t* pool_idx;
+  int pool_H, pool_W;
 };
+
+// gradient of the max-pool INPUT at pixel `row` (= (n*H + ih)*W + iw), channels [ch0, ch0+8), rounded to bf16
+// exactly like the separate kdl_maxpool3x3s2_bwd pass would store it
+__device__ __forceinline__ uint4 pool_grad_gather(const bf16* __restrict__ dp, const uint8_t* __restrict__ idx,
+                                                  int64_t row, int ch0, int H, int W, int C) {
+  const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+  const int iw = (int)(row % W);
+  const int64_t t = row / W;
+  const int ih = (int)(t % H);
+  const int n = (int)(t / H);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int oh = (ih + 1) / 2 - 1; oh <= (ih + 1) / 2; ++oh) {
+    if (oh < 0 || oh >= OH) continue;
+    const int kh = ih - (oh * 2 - 1);
+    if (kh < 0 || kh > 2) continue;
+    for (int ow = (iw + 1) / 2 - 1; ow <= (iw + 1) / 2; ++ow) {
+      if (ow < 0 || ow >= OW) continue;
+      const int kw = iw - (ow * 2 - 1);
+      if (kw < 0 || kw > 2) continue;
+      const int64_t o = (((int64_t)n * OH + oh) * OW + ow) * C + ch0;
+      const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+      float f[8];
+      unpack8(ld_plain(dp + o), f);
+      const int code = kh * 3 + kw;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int b = (j < 4 ? (pk.x >> (8 * j)) : (pk.y >> (8 * (j - 4)))) & 0xff;
+        if (b == code) acc[j] += f[j];
+      }
+    }
+  }
+  return pack8(acc);
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
@@ -82,7 +122,8 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
       int64_t r = row + u * step;
       if (r < p.M) {
         int64_t off = r * p.C + ch0;
-        va[u] = ld_stream(p.a + off);
+        if (MODE == 1 && p.pool_dp) va[u] = pool_grad_gather(p.pool_dp, p.pool_idx, r, ch0, p.pool_H, p.pool_W, p.C);
+        else va[u] = ld_stream(p.a + off);
         if (MODE == 1) {
           vc[u] = ld_stream(p.c + off);
           if (p.relu == 1) vb[u] = ld_stream(p.b + off);
@@ -301,7 +342,10 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
                                                     const bf16* __restrict__ y, bf16* dx, bf16* dres,
                                                     int64_t nvec, int cvec, int C,
                                                     const float* __restrict__ coef, int relu,
-                                                    const uint8_t* __restrict__ mask = nullptr) {
+                                                    const uint8_t* __restrict__ mask = nullptr,
+                                                    const bf16* __restrict__ pool_dp = nullptr,
+                                                    const uint8_t* __restrict__ pool_idx = nullptr,
+                                                    int pool_H = 0, int pool_W = 0) {
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float A[8], B[8], D[8], Fb[8];
@@ -322,7 +366,8 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
     for (int u = 0; u < U; ++u) {
       int64_t k = i + u * T;
       if (k < nvec) {
-        vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
+        if (pool_dp) vd[u] = pool_grad_gather(pool_dp, pool_idx, k / cvec, (int)(k % cvec) * 8, pool_H, pool_W, C);
+        else vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
         vx[u] = ld_stream(x + k * 8);
         if (relu == 1) vy[u] = ld_stream(y + k * 8);
         else if (relu == 3) vy[u].x = mask[k];
@@ -494,7 +539,8 @@ extern "C" int kdl_bn_fwd_mask(const void* x, const void* res, void* y, int64_t 
 static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, void* dres,
                        int64_t M, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
                        int relu, const uint8_t* relu_mask, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
-                       size_t workspace_bytes, cudaStream_t stream) {
+                       size_t workspace_bytes, cudaStream_t stream, const bf16* pool_dp = nullptr,
+                       const uint8_t* pool_idx = nullptr, int pool_H = 0, int pool_W = 0) {
   BnPlan pl;
   unsigned* counter;
   float *coef, *partial;
@@ -520,6 +566,7 @@ static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, v
   p.coef = coef;
   p.dgamma = (bf16*)dgamma_bf16; p.dbeta = (bf16*)dbeta_bf16;
   p.relu = relu; p.mask = relu_mask;
+  p.pool_dp = pool_dp; p.pool_idx = pool_idx; p.pool_H = pool_H; p.pool_W = pool_W;
   bn_reduce_kernel<1><<<dim3(pl.gx, pl.nslices), pl.threads, 0, stream>>>(p);
   KDL_CHECK_LAUNCH();
   int64_t nvec = M * C / 8;
@@ -530,10 +577,12 @@ static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, v
   bool fixed = (256 % cvec) == 0;
   if (fixed)
     bn_dx_kernel<true><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
-                                              (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask);
+                                              (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask,
+                                              pool_dp, pool_idx, pool_H, pool_W);
   else
     bn_dx_kernel<false><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
-                                               (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask);
+                                               (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask,
+                                               pool_dp, pool_idx, pool_H, pool_W);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }
@@ -544,6 +593,23 @@ extern "C" int kdl_bn_bwd(const void* dy, const void* x, const void* y, void* dx
                           size_t workspace_bytes, cudaStream_t stream) {
   return bn_bwd_impl(dy, x, y, dx, dres, M, C, gamma, beta, save_mean_rstd, relu, nullptr, dgamma_bf16, dbeta_bf16,
                      workspace, workspace_bytes, stream);
+}
+
+// Backward of relu(bn(x)) followed by a 3x3/s2 max-pool, given the gradient of the POOLED output (dp,
+// [N, (H+1)/2, (W+1)/2, C]) and the pool's argmax indices: the gradient of the pool input is gathered on
+// the fly inside both BatchNorm passes instead of being written (and read twice) as a full-size tensor.
+// The ReLU mask is recomputed from x (no residual input).
+extern "C" int kdl_bn_bwd_pooled(const void* dp, const void* pool_idx_u8, const void* x, void* dx, int N, int H,
+                                 int W, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
+                                 void* dgamma_bf16, void* dbeta_bf16, void* workspace, size_t workspace_bytes,
+                                 cudaStream_t stream) {
+  if (dp == nullptr || pool_idx_u8 == nullptr || beta == nullptr) {
+    kdl_set_error("bn_bwd_pooled: dp, pool_idx and beta are required");
+    return KDL_ERR_ARG;
+  }
+  return bn_bwd_impl(nullptr, x, nullptr, dx, nullptr, (int64_t)N * H * W, C, gamma, beta, save_mean_rstd, 1, nullptr,
+                     dgamma_bf16, dbeta_bf16, workspace, workspace_bytes, stream, (const bf16*)dp,
+                     (const uint8_t*)pool_idx_u8, H, W);
 }
 
 // Backward with the ReLU mask taken from the bit mask kdl_bn_fwd_mask / kdl_bn_fwd_from_stats_mask saved.

@@ -241,6 +241,7 @@ class ResNet50:
         # stem convolution straight from the uint8 image (224x224 inputs); 0: im2col patch matrix + GEMM
         self.stem_direct = _os.environ.get("KUBEDL_STEM_DIRECT", "1") == "1"
         self.fuse_stem_pool = _os.environ.get("KUBEDL_FUSE_STEM_POOL", "1") == "1"
+        self.fuse_stem_pool_bwd = _os.environ.get("KUBEDL_FUSE_STEM_POOL_BWD", "0") == "1"
         # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
         # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
         # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.
@@ -346,8 +347,15 @@ class ResNet50:
         dh = K.avgpool_bwd(dpooled, hshape)
         for b in reversed(self.blocks):
             dh = b.bwd(dh)
-        da = K.maxpool3x3s2_bwd(dh, idx, c.shape)
-        dc = self.stem_bn.bwd(da, c, a)
+        if self.fuse_stem_pool_bwd:
+            # max-pool backward gathered inside the two BatchNorm backward passes: the 411 MB pool-input
+            # gradient is never written or re-read.  Bit-identical, but measured SLOWER (+0.8 ms/step: the
+            # gather costs more than the traffic it saves, profiles/stem_pool_ab.log), so off by default.
+            sb = self.stem_bn
+            dc = K.bn_bwd_pooled(dh, idx, c, sb.gamma, sb.beta, sb.save, sb.dgamma, sb.dbeta)
+        else:
+            da = K.maxpool3x3s2_bwd(dh, idx, c.shape)
+            dc = self.stem_bn.bwd(da, c, a)
         if x.dtype == torch.uint8:    # direct stem kernels: patch tiles rebuilt in shared memory
             gw = K.stem_conv_wgrad(x, dc)
             self.arena.grad("conv1").view(64, 147).copy_(K.stem_weight_unpad(gw))

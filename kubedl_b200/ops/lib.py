@@ -45,6 +45,8 @@ _SIGS = {
                                  C.POINTER(c_float), c_void_p]),
     "kdl_stem_im2col_u8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, C.POINTER(c_float),
                                    C.POINTER(c_float), c_void_p]),
+    "kdl_bn_bwd_pooled": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "kdl_bn_finalize_from_stats": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float,
                                            c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "kdl_maxpool3x3s2_affine_relu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,

@@ -267,6 +267,22 @@ def bn_relu_maxpool_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor
     return y, idx
 
 
+def bn_bwd_pooled(dp: torch.Tensor, idx: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+                  save: torch.Tensor, dgamma: torch.Tensor, dbeta: torch.Tensor) -> torch.Tensor:
+    """Backward of maxpool3x3s2(relu(bn(x))) given dp = gradient of the pooled output: the pool-input gradient is
+    gathered on the fly inside the two BatchNorm backward passes (never written as a tensor).  Returns dx."""
+    _chk_bf16(dp, x, dgamma, dbeta)
+    N, H, W, Cn = x.shape
+    dx = torch.empty_like(x)
+    lib = L.lib()
+    ws = workspace(lib.kdl_bn_workspace_bytes(N * H * W, Cn), x.device)
+    L.check(lib.kdl_bn_bwd_pooled(dp.data_ptr(), idx.data_ptr(), x.data_ptr(), dx.data_ptr(), N, H, W, Cn,
+                                  gamma.data_ptr(), beta.data_ptr(), save.data_ptr(), dgamma.data_ptr(),
+                                  dbeta.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()), "kdl_bn_bwd_pooled")
+    L.count(2)
+    return dx
+
+
 def maxpool3x3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, in_shape) -> torch.Tensor:
     _chk_bf16(dy)
     N, H, W, Cn = in_shape

@@ -218,3 +218,22 @@ def test_bn_relu_maxpool_fused_matches_separate_passes(cuda):
     dy = torch.ones_like(p)
     dx = K.maxpool3x3s2_bwd(dy, idx, x.shape)
     assert float(dx.float().sum()) == float(p.numel())
+
+
+def test_bn_bwd_pooled_matches_separate_passes(cuda):
+    """max-pool backward gathered inside the BatchNorm backward == maxpool_bwd followed by bn_bwd."""
+    from kubedl_b200.ops import nn as K
+    torch.manual_seed(5)
+    N, H, C = 3, 16, 64
+    x = torch.randn(N, H, H, C, device=cuda).bfloat16()
+    gamma = torch.rand(C, device=cuda) + 0.5
+    beta = torch.randn(C, device=cuda) * 0.1
+    y, save = K.bn_fwd(x, gamma, beta, None, None, relu=True)
+    p, idx = K.maxpool3x3s2_fwd(y)
+    dp = torch.randn_like(p)
+    da = K.maxpool3x3s2_bwd(dp, idx, x.shape)
+    dg1, db1 = torch.empty(C, device=cuda, dtype=torch.bfloat16), torch.empty(C, device=cuda, dtype=torch.bfloat16)
+    dx1 = K.bn_bwd(da, x, None, gamma, save, True, dg1, db1, beta=beta)
+    dg2, db2 = torch.empty_like(dg1), torch.empty_like(db1)
+    dx2 = K.bn_bwd_pooled(dp, idx, x, gamma, beta, save, dg2, db2)
+    assert torch.equal(dx1, dx2) and torch.equal(dg1, dg2) and torch.equal(db1, db2)

@@ -27,7 +27,6 @@ constexpr int kStemBuilders = 512;  // building a patch tile is the critical pat
 constexpr int kStemThreads = 256 + kStemBuilders;   // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-7 epilogue, warps 8.. builders
 constexpr int kStemW = 224;         // input width / height this kernel is specialised for
 constexpr int kStemOW = 112;
-constexpr int kStemRowElems = (kStemW + 6) * 3 + 8;   // staged image row: 3 zero pixels either side + slack
 constexpr int kStemABytes = 3 * 128 * 128;            // patch tile: 3 column blocks of 128 rows x 128 B
 constexpr int kStemWBytes = 3 * 64 * 128;             // filter: 3 column blocks of 64 rows x 128 B
 constexpr int kStemStgBytes = 112 * 128;              // output staging tile (112 pixels x 64 channels bf16)
@@ -43,29 +42,67 @@ struct StemParams {
 __device__ __forceinline__ void builders_sync() { asm volatile("bar.sync 2, %0;" ::"n"(kStemBuilders) : "memory"); }
 __device__ __forceinline__ void stem_epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-// Stage the 7 image rows of output row (n, oh) as normalised bf16 and emit the patch tile into `tile`
-// (swizzled K-major, rows = output pixels).  Executed by the kStemBuilders builder threads.
-__device__ __forceinline__ void build_patch_tile(const StemParams& p, int row, bf16 (*srow)[kStemRowElems],
-                                                 uint8_t* tile, int bt) {
+// Raw image rows: the producer warp prefetches the 7 rows (672 B each) an output row needs with 1-D bulk
+// async copies, one output row ahead, into slots of kRawSlot bytes (data at byte 16, zero guards either side);
+// the builders convert straight from those bytes.  (The first version had the builders load the image with
+// ordinary loads and stage bf16 rows: every tile then paid a global-load round trip, ~5k clocks per tile.)
+constexpr int kRawSlot = 16 + kStemW * 3 + 16;     // 704
+constexpr int kRawBytes = 7 * kRawSlot;            // one output row's worth
+
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+// Issued by one thread: the rows of output row `row` that exist (out-of-image rows are skipped; the builders
+// never read them).
+__device__ __forceinline__ void prefetch_raw_rows(const StemParams& p, int row, uint32_t raw_smem, uint32_t bar) {
   const int n = row / kStemOW, oh = row - n * kStemOW;
+  int valid = 0;
+  for (int kh = 0; kh < 7; ++kh) {
+    const int ih = oh * 2 - 3 + kh;
+    valid += (ih >= 0 && ih < kStemW);
+  }
+  mbar_expect_tx(bar, (uint32_t)(valid * kStemW * 3));
+  for (int kh = 0; kh < 7; ++kh) {
+    const int ih = oh * 2 - 3 + kh;
+    if (ih < 0 || ih >= kStemW) continue;
+    bulk_load_1d(raw_smem + kh * kRawSlot + 16, p.img + ((size_t)n * kStemW + ih) * kStemW * 3, kStemW * 3, bar);
+  }
+}
+
+constexpr int kStemRowElems = (kStemW + 6) * 3 + 8;   // normalised image row: 3 zero pixels either side + slack
+
+// Emit the patch tile of output row `row` into `tile` (swizzled K-major, rows = output pixels).  Two phases by
+// the kStemBuilders builder threads: (1) the prefetched raw uint8 rows -> normalised bf16 rows `srow` (every
+// image element converted once; converting per patch vector instead was measured 4x more work and slower),
+// (2) 112 x 24 sixteen-byte vectors copied out of `srow` with four aligned 32-bit shared loads each.
+__device__ __forceinline__ void build_patch_tile(const StemParams& p, int row, const uint8_t* raw,
+                                                 bf16 (*srow)[kStemRowElems], uint8_t* tile, int bt) {
+  const int oh = row % kStemOW;
   const float k255 = 1.f / 255.f;
-  const float mean[3] = {p.m0, p.m1, p.m2}, istd[3] = {p.s0, p.s1, p.s2};
+  const float sc[3] = {k255 * p.s0, k255 * p.s1, k255 * p.s2};
+  const float bi[3] = {-p.m0 * p.s0, -p.m1 * p.s1, -p.m2 * p.s2};
   constexpr int words = kStemW * 3 / 4;   // 168 four-byte words per image row
   for (int i = bt; i < 7 * words; i += kStemBuilders) {
     const int kh = i / words, w4 = i - kh * words;
     const int ih = oh * 2 - 3 + kh;
-    uchar4 v = make_uchar4(0, 0, 0, 0);
     const bool in = ih >= 0 && ih < kStemW;
-    if (in) v = *reinterpret_cast<const uchar4*>(p.img + ((size_t)n * kStemW + ih) * kStemW * 3 + 4 * w4);
-    const unsigned char b[4] = {v.x, v.y, v.z, v.w};
+    const uint32_t v = in ? *reinterpret_cast<const uint32_t*>(raw + kh * kRawSlot + 16 + 4 * w4) : 0u;
+    const int c0 = (4 * w4) % 3;
+    float f[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int e = 4 * w4 + j, c = e % 3;
-      srow[kh][9 + e] = in ? __float2bfloat16(((float)b[j] * k255 - mean[c]) * istd[c]) : __float2bfloat16(0.f);
+      const int c = (c0 + j) % 3;
+      f[j] = in ? fmaf((float)((v >> (8 * j)) & 0xffu), sc[c], bi[c]) : 0.f;
     }
+    // srow element 9 + 4*w4: odd element index -> 2-byte stores
+    bf16* dst = &srow[kh][9 + 4 * w4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dst[j] = __float2bfloat16(f[j]);
   }
   builders_sync();
-  // 112 pixels x 24 sixteen-byte vectors (21 real + 3 zero ones that pad K from 168 to 192)
   for (int q = bt; q < kStemOW * 24; q += kStemBuilders) {
     const int ow = q / 24, v = q - ow * 24;
     uint4 o = make_uint4(0, 0, 0, 0);
@@ -87,7 +124,8 @@ constexpr int kOffW = 0;
 constexpr int kOffA = kOffW + kStemWBytes;              // two patch tiles
 constexpr int kOffStg = kOffA + 2 * kStemABytes;        // fprop: two output staging tiles; wgrad: two dy tiles
 constexpr int kOffSrow = kOffStg + 2 * 16384;
-constexpr int kOffBar = kOffSrow + ((7 * kStemRowElems * 2 + 1023) / 1024) * 1024;
+constexpr int kOffNorm = kOffSrow + ((2 * kRawBytes + 1023) / 1024) * 1024;    // after the two raw-row buffers
+constexpr int kOffBar = kOffNorm + ((7 * kStemRowElems * 2 + 1023) / 1024) * 1024;
 constexpr int kStemSmem = kOffBar + 256 + 1024;
 
 __global__ void __launch_bounds__(kStemThreads, 1)
@@ -103,8 +141,9 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
   auto aempty = [&](int b) { return bar + 8u * (3 + b); };
   auto tfull = [&](int b) { return bar + 8u * (5 + b); };
   auto tempty = [&](int b) { return bar + 8u * (7 + b); };
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + kOffBar + 8 * 9);
-  bf16 (*srow)[kStemRowElems] = reinterpret_cast<bf16 (*)[kStemRowElems]>(smem + kOffSrow);
+  auto rawfull = [&](int b) { return bar + 8u * (9 + b); };
+  auto rawempty = [&](int b) { return bar + 8u * (11 + b); };
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + kOffBar + 8 * 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 128;     // two 64-column accumulators
@@ -125,6 +164,8 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
       mbar_init(aempty(b), 1);
       mbar_init(tfull(b), 1);
       mbar_init(tempty(b), 1);
+      mbar_init(rawfull(b), 1);
+      mbar_init(rawempty(b), 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -143,6 +184,12 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
     if (lane == 0) {
       mbar_expect_tx(wfull(), kStemWBytes);
       for (int kb = 0; kb < 3; ++kb) tma_load_2d(sbase + kOffW + kb * 8192, &tma_w, wfull(), kb * 64, 0);
+      int iter = 0;
+      for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {     // raw image rows, one tile ahead
+        const int b = iter & 1;
+        mbar_wait(rawempty(b), ((iter >> 1) & 1) ^ 1);
+        prefetch_raw_rows(p, row, sbase + kOffSrow + b * kRawBytes, rawfull(b));
+      }
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer: 3 column blocks x 4 K-slices per output row
@@ -234,8 +281,13 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
       const int b = iter & 1;
       const uint32_t ph = (iter >> 1) & 1;
       mbar_wait(aempty(b), ph ^ 1);
-      build_patch_tile(p, row, srow, smem + kOffA + b * kStemABytes, bt);
-      if (bt == 0) mbar_arrive(afull(b));
+      mbar_wait(rawfull(b), ph);
+      build_patch_tile(p, row, smem + kOffSrow + b * kRawBytes,
+                       reinterpret_cast<bf16 (*)[kStemRowElems]>(smem + kOffNorm), smem + kOffA + b * kStemABytes, bt);
+      if (bt == 0) {
+        mbar_arrive(afull(b));
+        mbar_arrive(rawempty(b));
+      }
     }
   }
 
@@ -269,8 +321,9 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
   auto afull = [&](int b) { return bar + 8u * (2 + b); };
   auto empty = [&](int b) { return bar + 8u * (4 + b); };
   auto done = [&]() { return bar + 8u * 6; };
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + kOffBar + 8 * 7);
-  bf16 (*srow)[kStemRowElems] = reinterpret_cast<bf16 (*)[kStemRowElems]>(smem + kOffSrow);
+  auto rawfull = [&](int b) { return bar + 8u * (7 + b); };
+  auto rawempty = [&](int b) { return bar + 8u * (9 + b); };
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + kOffBar + 8 * 11);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 256;     // D[64, 192]
@@ -285,6 +338,8 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
       mbar_init(dyfull(b), 1);
       mbar_init(afull(b), 1);
       mbar_init(empty(b), 1);
+      mbar_init(rawfull(b), 1);
+      mbar_init(rawempty(b), 1);
     }
     mbar_init(done(), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -305,6 +360,8 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
       int iter = 0;
       for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
         const int b = iter & 1;
+        mbar_wait(rawempty(b), ((iter >> 1) & 1) ^ 1);
+        prefetch_raw_rows(p, row, sbase + kOffSrow + b * kRawBytes, rawfull(b));
         mbar_wait(empty(b), ((iter >> 1) & 1) ^ 1);
         mbar_expect_tx(dyfull(b), kStemStgBytes);
         tma_load_2d(sbase + kOffStg + b * 16384, &tma_dy, dyfull(b), 0, row * kStemOW);
@@ -354,8 +411,13 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
     for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
       const int b = iter & 1;
       mbar_wait(empty(b), ((iter >> 1) & 1) ^ 1);
-      build_patch_tile(p, row, srow, smem + kOffA + b * kStemABytes, bt);
-      if (bt == 0) mbar_arrive(afull(b));
+      mbar_wait(rawfull(b), (iter >> 1) & 1);
+      build_patch_tile(p, row, smem + kOffSrow + b * kRawBytes,
+                       reinterpret_cast<bf16 (*)[kStemRowElems]>(smem + kOffNorm), smem + kOffA + b * kStemABytes, bt);
+      if (bt == 0) {
+        mbar_arrive(afull(b));
+        mbar_arrive(rawempty(b));
+      }
     }
   }
 

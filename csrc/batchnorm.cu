@@ -72,13 +72,15 @@ __device__ __forceinline__ uint4 pool_grad_gather(const bf16* __restrict__ dp, c
       if (kw < 0 || kw > 2) continue;
       const int64_t o = (((int64_t)n * OH + oh) * OW + ow) * C + ch0;
       const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+      const uint32_t c4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
+      const uint32_t m0 = __vcmpeq4(pk.x, c4), m1 = __vcmpeq4(pk.y, c4);
+      if ((m0 | m1) == 0u) continue;
       float f[8];
       unpack8(ld_plain(dp + o), f);
-      const int code = kh * 3 + kw;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const int b = (j < 4 ? (pk.x >> (8 * j)) : (pk.y >> (8 * (j - 4)))) & 0xff;
-        if (b == code) acc[j] += f[j];
+        const uint32_t hit = (j < 4 ? (m0 >> (8 * j)) : (m1 >> (8 * (j - 4)))) & 1u;
+        if (hit) acc[j] += f[j];
       }
     }
   }

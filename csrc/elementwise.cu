@@ -208,15 +208,18 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __res
         uint4 v = ld_plain(x + (((int64_t)n * H + ih) * W + iw) * C + cg * 8);
         float f[8];
         unpack8(v, f);
-        if (AFFINE) {     // same rounding as the separate BatchNorm pass: bf16 before the comparison
+        if (AFFINE) {     // relu(a*x + b) is monotonic in x: compare sign(a)*x now, apply the affine once at the end
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            f[j] = __bfloat162float(__float2bfloat16(fmaxf(fmaf(ca[j], f[j], cb[j]), 0.f)));
+          for (int j = 0; j < 8; ++j) f[j] = ca[j] >= 0.f ? f[j] : -f[j];
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           if (f[j] > best[j]) { best[j] = f[j]; bi[j] = kh * 3 + kw; }
       }
+    }
+    if (AFFINE) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) best[j] = fmaxf(fmaf(ca[j], ca[j] >= 0.f ? best[j] : -best[j], cb[j]), 0.f);
     }
     *reinterpret_cast<uint4*>(y + i * 8) = pack8(best);
     uint2 pk;
@@ -253,14 +256,18 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const bf16* __res
         if (kw < 0 || kw > 2) continue;
         int64_t o = (((int64_t)n * OH + oh) * OW + ow) * cvec + cg;
         uint2 pk = *reinterpret_cast<const uint2*>(idx + o * 8);
+        // byte-wise SIMD compare of the eight argmax codes; most windows select another position for
+        // all eight channels, then the gradient vector is not even loaded
+        const uint32_t c4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
+        const uint32_t m0 = __vcmpeq4(pk.x, c4), m1 = __vcmpeq4(pk.y, c4);
+        if ((m0 | m1) == 0u) continue;
         uint4 v = ld_plain(dy + o * 8);
         float f[8];
         unpack8(v, f);
-        const int code = kh * 3 + kw;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          int b = (j < 4 ? (pk.x >> (8 * j)) : (pk.y >> (8 * (j - 4)))) & 0xff;
-          if (b == code) acc[j] += f[j];
+          const uint32_t hit = (j < 4 ? (m0 >> (8 * j)) : (m1 >> (8 * (j - 4)))) & 1u;
+          if (hit) acc[j] += f[j];
         }
       }
     }

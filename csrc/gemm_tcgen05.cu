@@ -105,6 +105,27 @@ __host__ __device__ constexpr uint32_t make_idesc() {
          ((uint32_t)(BM >> 4) << 24);
 }
 
+// The four epilogue warps of a CTA hold statistics of the same columns over different rows: add them in
+// shared memory (fixed order) and write ONE partial row per CTA, so the finalizer walks a quarter of the rows.
+template <int BNT>
+__device__ __forceinline__ void reduce_store_col_stats(float* sm, float* stats, int part, int N, int col0, int ew,
+                                                       int lane, float (*acc)[4]) {
+#pragma unroll
+  for (int c = 0; c < BNT / 64; ++c) {
+    const int col = c * 64 + 2 * lane;
+    sm[(ew * 2 + 0) * BNT + col] = acc[c][0]; sm[(ew * 2 + 0) * BNT + col + 1] = acc[c][1];
+    sm[(ew * 2 + 1) * BNT + col] = acc[c][2]; sm[(ew * 2 + 1) * BNT + col + 1] = acc[c][3];
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+  float* dst = stats + (size_t)part * 2 * N;
+  for (int col = ew * 32 + lane; col < BNT; col += kEpiWarps * 32) {
+    float s0 = 0.f, q0 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kEpiWarps; ++w) { s0 += sm[(w * 2 + 0) * BNT + col]; q0 += sm[(w * 2 + 1) * BNT + col]; }
+    if (col0 + col < N) { dst[col0 + col] = s0; dst[N + col0 + col] = q0; }
+  }
+}
+
 template <int BN, int STAGES>
 struct SmemLayout {
   static constexpr int kABytes = BM * BK * 2;
@@ -403,12 +424,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
-    if (p.stats) {   // this CTA's column tile is blockIdx.x % num_n for every tile it processed
-      const int part = (blockIdx.x / p.num_n) * kEpiWarps + ew;
-#pragma unroll
-      for (int c = 0; c < BN / 64; ++c)
-        store_col_stats(p.stats, part, p.N, (int)(blockIdx.x % p.num_n) * BN + c * 64 + 2 * lane, st_acc[c]);
-    }
+    if (p.stats)     // this CTA's column tile is blockIdx.x % num_n for every tile it processed
+      reduce_store_col_stats<BN>(reinterpret_cast<float*>(smem + SL::kStatsOffset), p.stats, blockIdx.x / p.num_n, p.N,
+                                 (int)(blockIdx.x % p.num_n) * BN, ew, lane, st_acc);
   }
 
   tcgen05_fence_before();
@@ -724,12 +742,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
-    if (p.stats) {   // the pair's column tile is pair % num_n for every tile it processed
-      const int part = ((pair / p.num_n) * 2 + (int)cta) * kEpiWarps + ew;
-#pragma unroll
-      for (int c = 0; c < BN2 / 64; ++c)
-        store_col_stats(p.stats, part, p.N, (pair % p.num_n) * BN2 + c * 64 + 2 * lane, st_acc[c]);
-    }
+    if (p.stats)     // the pair's column tile is pair % num_n for every tile it processed
+      reduce_store_col_stats<BN2>(reinterpret_cast<float*>(smem + SL::kStatsOffset), p.stats,
+                                  (pair / p.num_n) * 2 + (int)cta, p.N, (pair % p.num_n) * BN2, ew, lane, st_acc);
   }
 
   tcgen05_fence_before();
@@ -961,8 +976,8 @@ extern "C" size_t kdl_gemm_scratch_bytes(int M, int N, int K, int split_k) {
   return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
 }
 
-// rows a statistics buffer needs: one per epilogue warp of every CTA
-extern "C" int kdl_gemm_max_ctas(void) { return num_sms() * kEpiWarps; }
+// rows a statistics buffer needs: one per CTA
+extern "C" int kdl_gemm_max_ctas(void) { return num_sms(); }
 
 static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major, int b_mn_major,
                      int lda, int ldb, int ldc, const void* bias, const void* addend, int add_h, int add_w,
@@ -1068,7 +1083,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
     p.num_n = (N + 255) / 256;
     if (stats_parts_out) {
       int tiles2 = p.num_m * p.num_n, pairs = num_sms() / 2;
-      *stats_parts_out = (stats_grid(tiles2 < pairs ? tiles2 : pairs, p.num_n) / p.num_n) * 2 * kEpiWarps;
+      *stats_parts_out = (stats_grid(tiles2 < pairs ? tiles2 : pairs, p.num_n) / p.num_n) * 2;
     }
     if (!a_mn_major && !b_mn_major) return launch_2cta<0, 0>(ma, mb, mc2, p, stream);
     if (!a_mn_major && b_mn_major) return launch_2cta<0, 1>(ma, mb, mc2, p, stream);
@@ -1077,7 +1092,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   }
   if (stats_parts_out) {
     int tiles1 = p.num_m * p.num_n * p.splits;
-    *stats_parts_out = (stats_grid(tiles1 < num_sms() ? tiles1 : num_sms(), p.num_n) / p.num_n) * kEpiWarps;
+    *stats_parts_out = stats_grid(tiles1 < num_sms() ? tiles1 : num_sms(), p.num_n) / p.num_n;
   }
   CUtensorMap mc;
   if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)N, (uint64_t)N, (uint64_t)splits);

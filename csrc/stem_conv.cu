@@ -35,7 +35,7 @@ struct StemParams {
   const uint8_t* img;    // [N, 224, 224, 3]
   int rows;              // N * 112 output rows
   float m0, m1, m2, s0, s1, s2;   // mean, 1/std per channel
-  float* stats;          // fprop: [gridDim.x * 4][2][64] column sum / sum of squares (or null)
+  float* stats;          // fprop: [gridDim.x][2][64] column sum / sum of squares (or null)
   float* partial;        // wgrad: [gridDim.x][64][192]
 };
 
@@ -268,10 +268,18 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
     }
     if (leader) tma_store_wait_read<0>();
     __syncwarp();
-    if (p.stats) {
-      float* dst = p.stats + (size_t)(blockIdx.x * 4 + q) * 2 * 64;
-      dst[2 * lane] = st[0]; dst[2 * lane + 1] = st[1];
-      dst[64 + 2 * lane] = st[2]; dst[64 + 2 * lane + 1] = st[3];
+    if (p.stats) {     // add the four warps' partials in shared memory: one partial row per CTA
+      stem_epi_sync();                                   // every TMA store has read the staging tiles
+      float* sm = reinterpret_cast<float*>(smem + kOffStg);
+      sm[(q * 2 + 0) * 64 + 2 * lane] = st[0]; sm[(q * 2 + 0) * 64 + 2 * lane + 1] = st[1];
+      sm[(q * 2 + 1) * 64 + 2 * lane] = st[2]; sm[(q * 2 + 1) * 64 + 2 * lane + 1] = st[3];
+      stem_epi_sync();
+      const int t = q * 32 + lane;                       // 128 threads: 64 sums + 64 sums of squares
+      const int k = t >> 6, col = t & 63;
+      float acc = 0.f;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) acc += sm[(w * 2 + k) * 64 + col];
+      p.stats[(size_t)blockIdx.x * 128 + k * 64 + col] = acc;
     }
   } else if (warp >= 8) {
     // ---------------- builders
@@ -510,7 +518,7 @@ static int stem_fill(StemParams* p, const void* img, int N, int H, int W, const 
 using namespace kdl;
 
 extern "C" int kdl_stem_conv_supported(int H, int W) { return H == kStemW && W == kStemW; }
-extern "C" int kdl_stem_conv_max_parts(void) { return stem_sms() * 4; }
+extern "C" int kdl_stem_conv_max_parts(void) { return stem_sms(); }
 extern "C" size_t kdl_stem_conv_wgrad_scratch_bytes(void) { return (size_t)stem_sms() * 64 * 192 * sizeof(float); }
 
 // y [N,112,112,64] = conv7x7/s2/p3(normalise(img_u8 [N,224,224,3]), w); w_padded is [64][168] in the
@@ -532,7 +540,7 @@ extern "C" int kdl_stem_conv_fwd(const void* img_u8, const void* w_padded, void*
     attr = true;
   }
   const int grid = p.rows < stem_sms() ? p.rows : stem_sms();
-  if (stats_parts_out) *stats_parts_out = grid * 4;
+  if (stats_parts_out) *stats_parts_out = grid;
   stem_fprop_kernel<<<grid, kStemThreads, kStemSmem, stream>>>(mw, my, p);
   KDL_CHECK_LAUNCH();
   return KDL_OK;

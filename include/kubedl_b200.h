@@ -135,7 +135,7 @@ int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
                   const void* addend_bf16, int relu, int split_k, void* scratch, size_t scratch_bytes,
                   cudaStream_t stream);
 /* Same, and additionally (stats_partial != NULL) column sum / sum-of-squares of the bf16 output, one
- * partial row per epilogue warp: [kdl_gemm_max_ctas()][2][N] floats (kdl_gemm_max_ctas() = the most rows
+ * partial row per CTA: [kdl_gemm_max_ctas()][2][N] floats (kdl_gemm_max_ctas() = the most rows
  * any launch writes); *stats_parts_out = number of rows written. */
 int kdl_gemm_max_ctas(void);
 int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,

@@ -642,7 +642,18 @@ __global__ void __launch_bounds__(1024) bn_finalize_partials_kernel(const float*
   const int c = blockIdx.x * 32 + tx;
   float a0 = 0.f, a1 = 0.f;
   if (c < C) {
-    for (int i = ty; i < nparts; i += 32) {
+    int i = ty;
+    for (; i + 96 < nparts; i += 128) {     // four independent pairs of loads in flight
+      float u0[4], u1[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        u0[u] = __ldcg(partial + (size_t)(i + 32 * u) * 2 * C + c);
+        u1[u] = __ldcg(partial + (size_t)(i + 32 * u) * 2 * C + C + c);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { a0 += u0[u]; a1 += u1[u]; }
+    }
+    for (; i < nparts; i += 32) {
       a0 += __ldcg(partial + (size_t)i * 2 * C + c);
       a1 += __ldcg(partial + (size_t)i * 2 * C + C + c);
     }

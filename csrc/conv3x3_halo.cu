@@ -730,7 +730,15 @@ __global__ void halo_wgrad_reduce_kernel(const float* __restrict__ partial, bf16
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= n) return;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int gI = 0; gI < G; ++gI) {
+  int gI = 0;
+  for (; gI + 4 <= G; gI += 4) {      // four independent 16-byte loads in flight, fixed summation order
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const float4*>(partial + (size_t)(gI + u) * n + i);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+  }
+  for (; gI < G; ++gI) {
     const float4 v = *reinterpret_cast<const float4*>(partial + (size_t)gI * n + i);
     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
   }

@@ -763,8 +763,18 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
                                                             int N, int ldc, int splits) {
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < MN; i += T) {
+    // eight independent loads in flight per thread (the loop is latency-bound: a few thousand threads walk
+    // up to 128 partial planes); the summation order stays fixed, so the result is deterministic
     float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += __ldcg(partial + (size_t)s * MN + i);
+    int s = 0;
+    for (; s + 8 <= splits; s += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(partial + (size_t)(s + u) * MN + i);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += v[u];
+    }
+    for (; s < splits; ++s) acc += __ldcg(partial + (size_t)s * MN + i);
     const int64_t r = i / N, c = i % N;
     out[r * ldc + c] = __float2bfloat16(acc);
   }

@@ -1,0 +1,14 @@
+"""One launch of the direct stem kernels + the stem BN / pool kernels at batch 256 (ncu target)."""
+import sys
+sys.path.insert(0, ".")
+import torch
+from kubedl_b200.ops import nn as K
+dev = torch.device("cuda", 0)
+img = torch.randint(0, 256, (256, 224, 224, 3), dtype=torch.uint8, device=dev)
+w = (torch.randn(64, 7, 7, 3, device=dev) * 0.05).bfloat16()
+wp = K.stem_weight_padded(w)
+for _ in range(2):
+    y, stats = K.stem_conv_fwd(img, wp, want_stats=True)
+    gw = K.stem_conv_wgrad(img, y)
+torch.cuda.synchronize()
+print("ok")

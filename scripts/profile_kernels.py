@@ -16,10 +16,18 @@ for _ in range(2):
     dy = torch.randn_like(y)
     dg, db = torch.empty(C, device=dev, dtype=torch.bfloat16), torch.empty(C, device=dev, dtype=torch.bfloat16)
     dx = K.bn_bwd(dy, x, y, g, save, True, dg, db, dres=dy)
+# the variants the model actually uses: statistics from the GEMM epilogue, 1-bit ReLU mask, mask recomputed from x
+mask = torch.empty(M * C // 8, dtype=torch.uint8, device=dev)
+for _ in range(2):
+    y2, _ = K.bn_fwd(x, g, b, None, None, res=res, relu=True, relu_mask=mask)
+    dy2 = torch.randn_like(y2)
+    dx2 = K.bn_bwd(dy2, x, None, g, save, True, dg, db, dres=dy2, relu_mask=mask)
+    dx3 = K.bn_bwd(dy2, x, None, g, save, True, dg, db, beta=b)
 gm = Gemm(dev)
 a = torch.randn(M, 64, device=dev).bfloat16(); w = torch.randn(256, 64, device=dev).bfloat16()
 for _ in range(2):
     o = gm.nt(a, w)            # layer1 conv3 forward: memory-bound
+    o2, st = gm.nt_stats(a, w)  # the same with BatchNorm column statistics from the epilogue
     dw = gm.tn(o, a)           # its wgrad (split-K)
 A = torch.randn(8192, 8192, device=dev).bfloat16(); B = torch.randn(8192, 8192, device=dev).bfloat16()
 for _ in range(2):

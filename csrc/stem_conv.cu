@@ -34,6 +34,8 @@ constexpr int kStemStgBytes = 112 * 128;              // output staging tile (11
 struct StemParams {
   const uint8_t* img;    // [N, 224, 224, 3]
   int rows;              // N * 112 output rows
+  int rows_per_cta;      // consecutive output rows per CTA (host: ceil(rows / SMs); grid = ceil(rows / rows_per_cta),
+                         // so every CTA has at least one row — the wgrad accumulator of an idle CTA would be garbage)
   float m0, m1, m2, s0, s1, s2;   // mean, 1/std per channel
   float* stats;          // fprop: [gridDim.x][2][64] column sum / sum of squares (or null)
   float* partial;        // wgrad: [gridDim.x][64][192]
@@ -55,17 +57,29 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint
                : "memory");
 }
 
-// Issued by one thread: the rows of output row `row` that exist (out-of-image rows are skipped; the builders
-// never read them).
-__device__ __forceinline__ void prefetch_raw_rows(const StemParams& p, int row, uint32_t raw_smem, uint32_t bar) {
+// First image row (as filter-row index kh) that tile `row` has to bring in: all seven for the first tile of a
+// CTA and for the first output row of an image, otherwise the two rows the previous tile did not have.
+__device__ __forceinline__ int stem_first_new_kh(int row, int row_lo) {
+  return (row == row_lo || row % kStemOW == 0) ? 0 : 5;
+}
+
+// Issued by one thread: the NEW image rows of output row `row` that exist (out-of-image rows are skipped;
+// the builders write zeros for them).
+__device__ __forceinline__ void prefetch_raw_rows(const StemParams& p, int row, int row_lo, uint32_t raw_smem,
+                                                  uint32_t bar) {
   const int n = row / kStemOW, oh = row - n * kStemOW;
+  const int kh0 = stem_first_new_kh(row, row_lo);
   int valid = 0;
-  for (int kh = 0; kh < 7; ++kh) {
+  for (int kh = kh0; kh < 7; ++kh) {
     const int ih = oh * 2 - 3 + kh;
     valid += (ih >= 0 && ih < kStemW);
   }
+  if (valid == 0) {            // nothing to fetch: complete the phase without a transfer
+    mbar_arrive(bar);
+    return;
+  }
   mbar_expect_tx(bar, (uint32_t)(valid * kStemW * 3));
-  for (int kh = 0; kh < 7; ++kh) {
+  for (int kh = kh0; kh < 7; ++kh) {
     const int ih = oh * 2 - 3 + kh;
     if (ih < 0 || ih >= kStemW) continue;
     bulk_load_1d(raw_smem + kh * kRawSlot + 16, p.img + ((size_t)n * kStemW + ih) * kStemW * 3, kStemW * 3, bar);
@@ -78,15 +92,17 @@ constexpr int kStemRowElems = (kStemW + 6) * 3 + 8;   // normalised image row: 3
 // the kStemBuilders builder threads: (1) the prefetched raw uint8 rows -> normalised bf16 rows `srow` (every
 // image element converted once; converting per patch vector instead was measured 4x more work and slower),
 // (2) 112 x 24 sixteen-byte vectors copied out of `srow` with four aligned 32-bit shared loads each.
-__device__ __forceinline__ void build_patch_tile(const StemParams& p, int row, const uint8_t* raw,
+__device__ __forceinline__ void build_patch_tile(const StemParams& p, int row, int row_lo, const uint8_t* raw,
                                                  bf16 (*srow)[kStemRowElems], uint8_t* tile, int bt) {
   const int oh = row % kStemOW;
+  const int kh0 = stem_first_new_kh(row, row_lo);
+  const int nnew = 7 - kh0;
   const float k255 = 1.f / 255.f;
   const float sc[3] = {k255 * p.s0, k255 * p.s1, k255 * p.s2};
   const float bi[3] = {-p.m0 * p.s0, -p.m1 * p.s1, -p.m2 * p.s2};
   constexpr int words = kStemW * 3 / 4;   // 168 four-byte words per image row
-  for (int i = bt; i < 7 * words; i += kStemBuilders) {
-    const int kh = i / words, w4 = i - kh * words;
+  for (int i = bt; i < nnew * words; i += kStemBuilders) {
+    const int kh = kh0 + i / words, w4 = i % words;
     const int ih = oh * 2 - 3 + kh;
     const bool in = ih >= 0 && ih < kStemW;
     const uint32_t v = in ? *reinterpret_cast<const uint32_t*>(raw + kh * kRawSlot + 16 + 4 * w4) : 0u;
@@ -98,7 +114,7 @@ __device__ __forceinline__ void build_patch_tile(const StemParams& p, int row, c
       f[j] = in ? fmaf((float)((v >> (8 * j)) & 0xffu), sc[c], bi[c]) : 0.f;
     }
     // srow element 9 + 4*w4: odd element index -> 2-byte stores
-    bf16* dst = &srow[kh][9 + 4 * w4];
+    bf16* dst = &srow[(ih + 8) & 7][9 + 4 * w4];      // ring slot of image row ih
 #pragma unroll
     for (int j = 0; j < 4; ++j) dst[j] = __float2bfloat16(f[j]);
   }
@@ -108,7 +124,7 @@ __device__ __forceinline__ void build_patch_tile(const StemParams& p, int row, c
     uint4 o = make_uint4(0, 0, 0, 0);
     if (v < 21) {
       const int kh = v / 3, j0 = (v - kh * 3) * 8;
-      const uint32_t* src = reinterpret_cast<const uint32_t*>(&srow[kh][ow * 6 + j0]);
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&srow[(oh * 2 - 3 + kh + 8) & 7][ow * 6 + j0]);
       o = make_uint4(src[0], src[1], src[2], src[3]);
       if (j0 == 16) { o.z &= 0x0000ffffu; o.w = 0u; }    // columns 21..23 of a filter row are padding
     }
@@ -125,7 +141,7 @@ constexpr int kOffA = kOffW + kStemWBytes;              // two patch tiles
 constexpr int kOffStg = kOffA + 2 * kStemABytes;        // fprop: two output staging tiles; wgrad: two dy tiles
 constexpr int kOffSrow = kOffStg + 2 * 16384;
 constexpr int kOffNorm = kOffSrow + ((2 * kRawBytes + 1023) / 1024) * 1024;    // after the two raw-row buffers
-constexpr int kOffBar = kOffNorm + ((7 * kStemRowElems * 2 + 1023) / 1024) * 1024;
+constexpr int kOffBar = kOffNorm + ((8 * kStemRowElems * 2 + 1023) / 1024) * 1024;     // ring of 8 normalised rows
 constexpr int kStemSmem = kOffBar + 256 + 1024;
 
 __global__ void __launch_bounds__(kStemThreads, 1)
@@ -179,16 +195,19 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // a CTA walks CONSECUTIVE output rows: row oh+1 shares five of its seven image rows with row oh, so only
+  // two new rows are fetched and normalised per tile (a ring of eight normalised rows)
+  const int row_lo = min((int)blockIdx.x * p.rows_per_cta, p.rows), row_hi = min(row_lo + p.rows_per_cta, p.rows);
 
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(wfull(), kStemWBytes);
       for (int kb = 0; kb < 3; ++kb) tma_load_2d(sbase + kOffW + kb * 8192, &tma_w, wfull(), kb * 64, 0);
       int iter = 0;
-      for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {     // raw image rows, one tile ahead
+      for (int row = row_lo; row < row_hi; ++row, ++iter) {     // raw image rows, one tile ahead
         const int b = iter & 1;
         mbar_wait(rawempty(b), ((iter >> 1) & 1) ^ 1);
-        prefetch_raw_rows(p, row, sbase + kOffSrow + b * kRawBytes, rawfull(b));
+        prefetch_raw_rows(p, row, row_lo, sbase + kOffSrow + b * kRawBytes, rawfull(b));
       }
     }
   } else if (warp == 1) {
@@ -198,7 +217,7 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
     mbar_wait(wfull(), 0);
     tcgen05_fence_after();
     int iter = 0;
-    for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
+    for (int row = row_lo; row < row_hi; ++row, ++iter) {
       const int b = iter & 1;
       const uint32_t ph = (iter >> 1) & 1;
       mbar_wait(tempty(b), ph ^ 1);
@@ -223,7 +242,7 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
     const bool leader = warp == 4 && lane == 0;
     float st[4] = {0.f, 0.f, 0.f, 0.f};
     int iter = 0;
-    for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
+    for (int row = row_lo; row < row_hi; ++row, ++iter) {
       const int b = iter & 1;
       const uint32_t ph = (iter >> 1) & 1;
       mbar_wait(tfull(b), ph);
@@ -285,12 +304,12 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tma_w,   // filter [64][16
     // ---------------- builders
     const int bt = threadIdx.x - 256;
     int iter = 0;
-    for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
+    for (int row = row_lo; row < row_hi; ++row, ++iter) {
       const int b = iter & 1;
       const uint32_t ph = (iter >> 1) & 1;
       mbar_wait(aempty(b), ph ^ 1);
       mbar_wait(rawfull(b), ph);
-      build_patch_tile(p, row, smem + kOffSrow + b * kRawBytes,
+      build_patch_tile(p, row, row_lo, smem + kOffSrow + b * kRawBytes,
                        reinterpret_cast<bf16 (*)[kStemRowElems]>(smem + kOffNorm), smem + kOffA + b * kStemABytes, bt);
       if (bt == 0) {
         mbar_arrive(afull(b));
@@ -362,14 +381,17 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // a CTA walks CONSECUTIVE output rows: row oh+1 shares five of its seven image rows with row oh, so only
+  // two new rows are fetched and normalised per tile (a ring of eight normalised rows)
+  const int row_lo = min((int)blockIdx.x * p.rows_per_cta, p.rows), row_hi = min(row_lo + p.rows_per_cta, p.rows);
 
   if (warp == 0) {
     if (lane == 0) {
       int iter = 0;
-      for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
+      for (int row = row_lo; row < row_hi; ++row, ++iter) {
         const int b = iter & 1;
         mbar_wait(rawempty(b), ((iter >> 1) & 1) ^ 1);
-        prefetch_raw_rows(p, row, sbase + kOffSrow + b * kRawBytes, rawfull(b));
+        prefetch_raw_rows(p, row, row_lo, sbase + kOffSrow + b * kRawBytes, rawfull(b));
         mbar_wait(empty(b), ((iter >> 1) & 1) ^ 1);
         mbar_expect_tx(dyfull(b), kStemStgBytes);
         tma_load_2d(sbase + kOffStg + b * 16384, &tma_dy, dyfull(b), 0, row * kStemOW);
@@ -382,7 +404,7 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
     constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                                ((uint32_t)(192 >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
     int iter = 0;
-    for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
+    for (int row = row_lo; row < row_hi; ++row, ++iter) {
       const int b = iter & 1;
       const uint32_t ph = (iter >> 1) & 1;
       mbar_wait(dyfull(b), ph);
@@ -416,11 +438,11 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112]
   } else if (warp >= 8) {
     const int bt = threadIdx.x - 256;
     int iter = 0;
-    for (int row = blockIdx.x; row < p.rows; row += gridDim.x, ++iter) {
+    for (int row = row_lo; row < row_hi; ++row, ++iter) {
       const int b = iter & 1;
       mbar_wait(empty(b), ((iter >> 1) & 1) ^ 1);
       mbar_wait(rawfull(b), (iter >> 1) & 1);
-      build_patch_tile(p, row, smem + kOffSrow + b * kRawBytes,
+      build_patch_tile(p, row, row_lo, smem + kOffSrow + b * kRawBytes,
                        reinterpret_cast<bf16 (*)[kStemRowElems]>(smem + kOffNorm), smem + kOffA + b * kStemABytes, bt);
       if (bt == 0) {
         mbar_arrive(afull(b));
@@ -508,6 +530,7 @@ static int stem_fill(StemParams* p, const void* img, int N, int H, int W, const 
   }
   p->img = (const uint8_t*)img;
   p->rows = N * kStemOW;
+  p->rows_per_cta = (p->rows + stem_sms() - 1) / stem_sms();
   p->m0 = mean3[0]; p->m1 = mean3[1]; p->m2 = mean3[2];
   p->s0 = 1.f / std3[0]; p->s1 = 1.f / std3[1]; p->s2 = 1.f / std3[2];
   return KDL_OK;
@@ -539,7 +562,7 @@ extern "C" int kdl_stem_conv_fwd(const void* img_u8, const void* w_padded, void*
     KDL_CUDA(cudaFuncSetAttribute(stem_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
     attr = true;
   }
-  const int grid = p.rows < stem_sms() ? p.rows : stem_sms();
+  const int grid = (p.rows + p.rows_per_cta - 1) / p.rows_per_cta;
   if (stats_parts_out) *stats_parts_out = grid;
   stem_fprop_kernel<<<grid, kStemThreads, kStemSmem, stream>>>(mw, my, p);
   KDL_CHECK_LAUNCH();
@@ -553,7 +576,7 @@ extern "C" int kdl_stem_conv_wgrad(const void* img_u8, const void* dy, void* gw_
   StemParams p = {};
   int rc = stem_fill(&p, img_u8, N, H, W, mean3, std3);
   if (rc) return rc;
-  const int grid = p.rows < stem_sms() ? p.rows : stem_sms();
+  const int grid = (p.rows + p.rows_per_cta - 1) / p.rows_per_cta;
   const size_t need = (size_t)grid * 64 * 192 * sizeof(float);
   if (scratch == nullptr || scratch_bytes < need) {
     kdl_set_error("stem wgrad: scratch too small (%zu < %zu)", scratch_bytes, need);

@@ -248,7 +248,27 @@ def emit(args, world, ms, clocks, e2e, launches, impl, extra):
     }
     if e2e is not None:
         rec["e2e"] = e2e
+    ld = launch_delay_probe() if impl == "ours" else None
+    if ld is not None:
+        rec["launch_delay"] = ld
     print(json.dumps(rec), flush=True)
+
+
+def launch_delay_probe():
+    """Second half of the headline metric ("job launch delay p50"): a few 8-replica PyTorchJobs through the
+    embedded operator + node agent (pods = local sleep processes), outside the timed region, rank 0 only.
+    KUBEDL_BENCH_LAUNCH_DELAY=0 skips it."""
+    if os.environ.get("KUBEDL_BENCH_LAUNCH_DELAY", "1") == "0":
+        return None
+    try:
+        from kubedl_b200.bench import launch_delay as LD
+        r = LD.run("PyTorchJob", jobs=int(os.environ.get("KUBEDL_BENCH_LAUNCH_JOBS", "8")), replicas=8, seconds=0.1)
+        return {"kind": "PyTorchJob", "replicas": 8, "jobs": r["jobs"], "unit": "ms",
+                "first_pod_p50": r["first_pod_ms"]["p50"], "all_pods_p50": r["all_pods_ms"]["p50"],
+                "time_to_succeeded_p50": r["time_to_succeeded_ms"]["p50"],
+                "note": "pods are local processes started by the node agent; no published reference number"}
+    except Exception as e:      # the probe must never take the training number down with it
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 def finish(world):

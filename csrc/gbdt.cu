@@ -522,3 +522,78 @@ extern "C" int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nod
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Small per-level glue kernels.  A boosting round is ~150 launches and, at 8 GPUs, bound by launch latency
+// rather than by any kernel; these three replace about ten tiny tensor-library launches per level.
+namespace kdl {
+
+// build[i] = the smaller child of parent i (ties -> left): 2i + (count[2i+1] < count[2i])
+__global__ void choose_build_kernel(const void* counts, int is_float, int pairs, int32_t* build) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= pairs) return;
+  bool right;
+  if (is_float) right = ((const float*)counts)[2 * i + 1] < ((const float*)counts)[2 * i];
+  else right = ((const int32_t*)counts)[2 * i + 1] < ((const int32_t*)counts)[2 * i];
+  build[i] = 2 * i + (right ? 1 : 0);
+}
+
+// level histograms from the built (smaller) children and the parents: sibling = parent - built
+__global__ void assemble_hist_kernel(const float4* __restrict__ parent, const float4* __restrict__ built,
+                                     const int32_t* __restrict__ build, int nodes, int per_node4,
+                                     float4* __restrict__ out) {
+  const int64_t total = (int64_t)nodes * per_node4;
+  const int64_t T = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
+    const int node = (int)(i / per_node4), e = (int)(i - (int64_t)node * per_node4);
+    const int pr = node >> 1;
+    const float4 b = built[(size_t)pr * per_node4 + e];
+    if (build[pr] == node) {
+      out[i] = b;
+    } else {
+      const float4 p = parent[(size_t)pr * per_node4 + e];
+      out[i] = make_float4(p.x - b.x, p.y - b.y, p.z - b.z, p.w - b.w);
+    }
+  }
+}
+
+// leaf values of the deepest level from its split statistics (feat, thr, gain, GL, HL, G, H, valid)
+__global__ void leaf_values_kernel(const float* __restrict__ splits8, int nodes, float lambda, float lr,
+                                   float* __restrict__ leaf) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nodes) return;
+  const float* s = splits8 + (size_t)i * 8;
+  const float GL = s[3], HL = s[4], G = s[5], H = s[6];
+  leaf[2 * i] = -GL / (HL + lambda) * lr;
+  leaf[2 * i + 1] = -(G - GL) / ((H - HL) + lambda) * lr;
+}
+
+}  // namespace kdl
+
+extern "C" int kdl_gbdt_choose_build(const void* counts, int counts_are_float, int nodes, int32_t* build,
+                                     cudaStream_t stream) {
+  const int pairs = nodes / 2;
+  if (pairs < 1) return KDL_OK;
+  kdl::choose_build_kernel<<<(pairs + 127) / 128, 128, 0, stream>>>(counts, counts_are_float, pairs, build);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_gbdt_assemble_hist(const void* parent_hist, const void* built_hist, const int32_t* build, int nodes,
+                                      int F, void* out_hist, cudaStream_t stream) {
+  const int per_node4 = F * kdl::kBins * 2 / 4;
+  const int64_t total = (int64_t)nodes * per_node4;
+  int64_t g = (total + 255) / 256;
+  if (g > 148 * 8) g = 148 * 8;
+  kdl::assemble_hist_kernel<<<(int)g, 256, 0, stream>>>((const float4*)parent_hist, (const float4*)built_hist, build,
+                                                        nodes, per_node4, (float4*)out_hist);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_gbdt_leaf_values(const float* splits8, int nodes, float lambda, float lr, float* leaf,
+                                    cudaStream_t stream) {
+  kdl::leaf_values_kernel<<<(nodes + 127) / 128, 128, 0, stream>>>(splits8, nodes, lambda, lr, leaf);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}

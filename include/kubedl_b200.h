@@ -221,6 +221,13 @@ int kdl_gbdt_hist_allreduce(const void* bins, int fstride, int F, const void* gh
 size_t kdl_gbdt_partition_workspace_bytes(int nodes);
 int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nodes, int32_t* ridx, int32_t* seg,
                        int32_t* counts, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+/* Per-level glue (a round is launch-latency bound at 8 GPUs): the smaller child of every parent from the
+ * (global) row counts; both children's histograms from the built one and the parent (subtraction trick);
+ * leaf values of the deepest level. */
+int kdl_gbdt_choose_build(const void* counts, int counts_are_float, int nodes, int32_t* build, cudaStream_t stream);
+int kdl_gbdt_assemble_hist(const void* parent_hist, const void* built_hist, const int32_t* build, int nodes, int F,
+                           void* out_hist, cudaStream_t stream);
+int kdl_gbdt_leaf_values(const float* splits8, int nodes, float lambda, float lr, float* leaf, cudaStream_t stream);
 int kdl_gbdt_split_eval(const void* hist, int nodes, int F, float lambda, float gamma,
                         float min_child_weight, float* out8, cudaStream_t stream);
 int kdl_gbdt_apply_split(int32_t* node_of_row, const void* bins, int fstride, const float* splits8,

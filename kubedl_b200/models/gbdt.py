@@ -36,6 +36,9 @@ L.register_signatures({
                                       C.c_void_p, C.c_void_p]),
     "kdl_gbdt_apply_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
     "kdl_gbdt_update_pred": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "kdl_gbdt_choose_build": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "kdl_gbdt_assemble_hist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "kdl_gbdt_leaf_values": (C.c_int, [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "kdl_gbdt_partition_workspace_bytes": (C.c_size_t, [C.c_int]),
     "kdl_gbdt_partition": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
@@ -141,7 +144,7 @@ class GBDTTrainer:
         self.cnt.zero_()
         self.cnt[:counts.numel()] = counts.float()
         self.ar(self.cnt_off, n, torch.float32, scale=1.0, channel=7)
-        return self.cnt[:counts.numel()].clone()
+        return self.cnt[:counts.numel()]      # consumed (stream-ordered) before the next level zeroes it
 
     def _partition(self, nodes: int):
         """Rows grouped by node (one counting-sort pass, csrc/gbdt.cu) -> (ridx, seg, counts)."""
@@ -156,7 +159,7 @@ class GBDTTrainer:
                                        counts.data_ptr(), self._part_ws.data_ptr(), self._part_ws.numel(),
                                        L.stream_ptr()), "kdl_gbdt_partition")
         L.count(3)
-        return self._ridx, seg, counts.long()
+        return self._ridx, seg, counts
 
     def _build_hist(self, ridx, seg, build, nbuild) -> torch.Tensor:
         par = self.level_parity
@@ -232,15 +235,16 @@ class GBDTTrainer:
                 build = torch.zeros(1, dtype=torch.int32, device=self.dev)
                 hist = self._build_hist(ridx, seg, build, 1).clone()
             else:
-                gc = self._global_counts(counts).view(-1, 2)
-                right_smaller = (gc[:, 1] < gc[:, 0]).to(torch.int32)
-                build = (torch.arange(nodes // 2, device=self.dev, dtype=torch.int32) * 2 + right_smaller).contiguous()
+                gc = self._global_counts(counts).contiguous()
+                build = torch.empty(nodes // 2, dtype=torch.int32, device=self.dev)
+                L.check(lib.kdl_gbdt_choose_build(gc.data_ptr(), int(gc.dtype == torch.float32), nodes,
+                                                  build.data_ptr(), L.stream_ptr()), "kdl_gbdt_choose_build")
                 built = self._build_hist(ridx, seg, build, nodes // 2)
-                other = parent_hist - built                     # subtraction trick
+                # subtraction trick: sibling = parent - built, both children written in one pass
                 hist = torch.empty(nodes, self.F, NBINS, 2, dtype=torch.float32, device=self.dev)
-                bl = build.long()
-                hist[bl] = built
-                hist[bl ^ 1] = other
+                L.check(lib.kdl_gbdt_assemble_hist(parent_hist.data_ptr(), built.data_ptr(), build.data_ptr(), nodes,
+                                                   self.F, hist.data_ptr(), L.stream_ptr()), "kdl_gbdt_assemble_hist")
+                L.count(2)
             splits = torch.empty(nodes, 8, dtype=torch.float32, device=self.dev)
             L.check(lib.kdl_gbdt_split_eval(hist.data_ptr(), nodes, self.F, self.lam, self.gamma, self.mcw,
                                             splits.data_ptr(), L.stream_ptr()), "kdl_gbdt_split_eval")
@@ -251,10 +255,10 @@ class GBDTTrainer:
             parent_hist = hist
         # leaf values from the last level's split statistics
         last = tree.splits[-1]
-        GL, HL, G, H = last[:, 3], last[:, 4], last[:, 5], last[:, 6]
         leaf = torch.empty(1 << self.depth, dtype=torch.float32, device=self.dev)
-        leaf[0::2] = -GL / (HL + self.lam) * self.lr
-        leaf[1::2] = -(G - GL) / ((H - HL) + self.lam) * self.lr
+        L.check(lib.kdl_gbdt_leaf_values(last.data_ptr(), last.shape[0], self.lam, self.lr, leaf.data_ptr(),
+                                         L.stream_ptr()), "kdl_gbdt_leaf_values")
+        L.count(1)
         tree.leaf_value = leaf
         L.check(lib.kdl_gbdt_update_pred(self.pred.data_ptr(), self.node.data_ptr(), leaf.data_ptr(), self.n,
                                          L.stream_ptr()), "kdl_gbdt_update_pred")

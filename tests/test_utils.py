@@ -110,3 +110,16 @@ def test_tenancy_annotation():
     assert tenancy.get_tenancy({"metadata": {}}) is None
     with pytest.raises(ValueError):
         tenancy.get_tenancy({"metadata": {"annotations": {c.ANNOTATION_TENANCY_INFO: "{bad"}}})
+
+
+def test_stem_weight_pad_unpad_roundtrip():
+    """The stem filter's patch-column layout (7 filter rows x 24 columns, 21 used) is a pure re-indexing."""
+    import torch
+    from kubedl_b200.ops import nn as K
+    w = torch.randn(64, 7, 7, 3)
+    wp = K.stem_weight_padded(w)
+    assert wp.shape == (64, K.STEM_KP) and K.STEM_KP == 168
+    assert float(wp.view(64, 7, K.STEM_KW)[:, :, 21:].abs().max()) == 0.0
+    assert torch.equal(K.stem_weight_unpad(wp).view(64, 7, 7, 3), w)
+    # column of (kh, kw, c) is kh*24 + kw*3 + c
+    assert float(wp[5, 2 * 24 + 4 * 3 + 1]) == float(w[5, 2, 4, 1])

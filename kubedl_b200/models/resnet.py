@@ -8,10 +8,12 @@ backward, bucket all-reduces on a side stream, fused SGD) is a static launch seq
 can be captured once into a CUDA graph.
 
 Convolutions: 1x1 stride-1 convolutions and the FC layer are GEMMs on the [N*H*W, C] view and
-go to the tcgen05 GEMM kernel (ops.gemm); the 7x7 stem is fused normalise+im2col + the same GEMM;
-3x3 convolutions go to the halo-resident / TMA-im2col tcgen05 kernels (ops.conv).  What is left
-on cuDNN (through ATen) are the six stride-2 dgrads and the three 1x1/stride-2 downsample
-convolutions.  With gemm=None everything falls back to cuDNN/cuBLAS (the A/B arm of the tests).
+go to the tcgen05 GEMM kernel (ops.gemm, BatchNorm statistics from its epilogue); the 7x7 stem runs
+straight from the uint8 image (csrc/stem_conv.cu; im2col + GEMM for sizes other than 224x224);
+3x3 convolutions go to the halo-resident / TMA-im2col tcgen05 kernels (ops.conv); the 1x1/stride-2
+downsample convolutions use the im2col kernel, their dgrad stays a compact GEMM result that the
+sibling conv1 dgrad adds in its epilogue.  What is left on cuDNN (through ATen) are the three
+stride-2 3x3 dgrads.  With gemm=None everything falls back to cuDNN/cuBLAS (the A/B arm of the tests).
 This is config #2 of BASELINE.json ("PyTorchJob ResNet-50 DDP bf16 ... synthetic 224² images").
 """
 from __future__ import annotations

@@ -139,6 +139,17 @@ def test_pools_and_add(cuda):
     dx = K.maxpool3x3s2_bwd(dy, idx, x.shape)
     torch.testing.assert_close(dx.float(), xr.grad.permute(0, 2, 3, 1), atol=2e-2, rtol=2e-2)
 
+    # odd sizes take the generic backward kernel, even sizes the 2x2-block one: both against autograd
+    x2 = torch.randn(2, 13, 15, 64, device=cuda).bfloat16()
+    y2, idx2 = K.maxpool3x3s2_fwd(x2)
+    xr2 = x2.float().permute(0, 3, 1, 2).requires_grad_(True)
+    yr2 = torch.nn.functional.max_pool2d(xr2, 3, 2, 1)
+    torch.testing.assert_close(y2.float(), yr2.permute(0, 2, 3, 1), atol=0, rtol=0)
+    dy2 = torch.randn_like(y2)
+    yr2.backward(dy2.float().permute(0, 3, 1, 2))
+    dx2 = K.maxpool3x3s2_bwd(dy2, idx2, x2.shape)
+    torch.testing.assert_close(dx2.float(), xr2.grad.permute(0, 2, 3, 1), atol=2e-2, rtol=2e-2)
+
     h = torch.randn(8, 7, 7, 2048, device=cuda).bfloat16()
     p = K.avgpool_fwd(h)
     torch.testing.assert_close(p.float(), h.float().mean((1, 2)), atol=1e-2, rtol=1e-2)

@@ -206,16 +206,16 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
     const int part = tid / nf4;
     const int c4 = tid % nf4;
     if (part < parts) {
-      // four independent loads in flight (with several hundred partial rows and few channels this loop was a
+      // eight independent loads in flight (with several hundred partial rows and few channels this loop was a
       // serial tail of ~20 us: one L2 round trip per row); the order of the additions is unchanged
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
       int bx = part;
-      for (; bx + 3 * parts < gx; bx += 4 * parts) {
-        float4 v[4];
+      for (; bx + 7 * parts < gx; bx += 8 * parts) {
+        float4 v[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = __ldcg(reinterpret_cast<const float4*>(base + (size_t)(bx + u * parts) * W2) + c4);
+        for (int u = 0; u < 8; ++u) v[u] = __ldcg(reinterpret_cast<const float4*>(base + (size_t)(bx + u * parts) * W2) + c4);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+        for (int u = 0; u < 8; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
       }
       for (; bx < gx; bx += parts) {
         float4 v = __ldcg(reinterpret_cast<const float4*>(base + (size_t)bx * W2) + c4);

@@ -91,6 +91,8 @@ template <int MODE>
 __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
   __shared__ float red[256 * 16];
   __shared__ int is_last;
+  pdl_wait();      // programmatic dependent launch: nothing global is touched before the predecessor has finished
+  pdl_launch();
   const int tid = threadIdx.x;
   const int nthreads = blockDim.x;
   const int cg = tid % p.tpr;
@@ -295,6 +297,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
                                                        bf16* __restrict__ y, int64_t nvec, int cvec,
                                                        int C, const float* __restrict__ coef,
                                                        int relu, uint8_t* __restrict__ mask = nullptr) {
+  pdl_wait();
+  pdl_launch();
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float a[8], b[8];
@@ -366,6 +370,8 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
                                                     const bf16* __restrict__ pool_dp = nullptr,
                                                     const uint8_t* __restrict__ pool_idx = nullptr,
                                                     int pool_H = 0, int pool_W = 0) {
+  pdl_wait();
+  pdl_launch();
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float A[8], B[8], D[8], Fb[8];
@@ -519,19 +525,17 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int64_t M, int C
   p.running_mean = running_mean; p.running_var = running_var;
   p.eps = eps; p.momentum = momentum;
   p.mean_rstd = save_mean_rstd; p.coef = coef;
-  bn_reduce_kernel<0><<<dim3(pl.gx, pl.nslices), pl.threads, 0, stream>>>(p);
-  KDL_CHECK_LAUNCH();
+  KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<0>, dim3(pl.gx, pl.nslices), dim3(pl.threads), 0, stream, p));
   int64_t nvec = M * C / 8;
   int cvec = C / 8;
   int g = apply_grid(nvec);
   bool fixed = (256 % cvec) == 0;
   if (fixed)
-    bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec,
-                                                 cvec, C, coef, relu, relu_mask);
+    KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<true>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
   else
-    bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec,
-                                                  cvec, C, coef, relu, relu_mask);
-  KDL_CHECK_LAUNCH();
+    KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<false>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
   return KDL_OK;
 }
 
@@ -587,8 +591,7 @@ static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, v
   p.dgamma = (bf16*)dgamma_bf16; p.dbeta = (bf16*)dbeta_bf16;
   p.relu = relu; p.mask = relu_mask;
   p.pool_dp = pool_dp; p.pool_idx = pool_idx; p.pool_H = pool_H; p.pool_W = pool_W;
-  bn_reduce_kernel<1><<<dim3(pl.gx, pl.nslices), pl.threads, 0, stream>>>(p);
-  KDL_CHECK_LAUNCH();
+  KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1>, dim3(pl.gx, pl.nslices), dim3(pl.threads), 0, stream, p));
   int64_t nvec = M * C / 8;
   int cvec = C / 8;
   int64_t g64 = (nvec + 256 * 2 - 1) / (256 * 2);
@@ -596,14 +599,13 @@ static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, v
   int g = (int)(g64 < 1 ? 1 : g64);
   bool fixed = (256 % cvec) == 0;
   if (fixed)
-    bn_dx_kernel<true><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
-                                              (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask,
-                                              pool_dp, pool_idx, pool_H, pool_W);
+    KDL_CUDA(kdl_launch_pdl(bn_dx_kernel<true>, dim3(g), dim3(256), 0, stream, (const bf16*)dy, (const bf16*)x,
+                            (const bf16*)y, (bf16*)dx, (bf16*)dres, nvec, cvec, C, (const float*)coef, relu, relu_mask,
+                            pool_dp, pool_idx, pool_H, pool_W));
   else
-    bn_dx_kernel<false><<<g, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y,
-                                               (bf16*)dx, (bf16*)dres, nvec, cvec, C, coef, relu, relu_mask,
-                                               pool_dp, pool_idx, pool_H, pool_W);
-  KDL_CHECK_LAUNCH();
+    KDL_CUDA(kdl_launch_pdl(bn_dx_kernel<false>, dim3(g), dim3(256), 0, stream, (const bf16*)dy, (const bf16*)x,
+                            (const bf16*)y, (bf16*)dx, (bf16*)dres, nvec, cvec, C, (const float*)coef, relu, relu_mask,
+                            pool_dp, pool_idx, pool_H, pool_W));
   return KDL_OK;
 }
 
@@ -656,6 +658,8 @@ __global__ void __launch_bounds__(1024) bn_finalize_partials_kernel(const float*
                                                                     float* running_var, float eps, float momentum,
                                                                     float* mean_rstd, float* coef) {
   __shared__ float r0[32][33], r1[32][33];
+  pdl_wait();
+  pdl_launch();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
   float a0 = 0.f, a1 = 0.f;
@@ -712,18 +716,17 @@ static int bn_fwd_from_stats_impl(const void* x, const void* res, void* y, int64
     kdl_set_error("bn_fwd_from_stats: no partial statistics given");
     return KDL_ERR_ARG;
   }
-  bn_finalize_partials_kernel<<<(C + 31) / 32, 1024, 0, stream>>>(stats_partial, nparts, M, C, gamma, beta,
-                                                                   running_mean, running_var, eps, momentum,
-                                                                   save_mean_rstd, coef);
-  KDL_CHECK_LAUNCH();
+  KDL_CUDA(kdl_launch_pdl(bn_finalize_partials_kernel, dim3((C + 31) / 32), dim3(1024), 0, stream, stats_partial, nparts,
+                          M, C, gamma, beta, running_mean, running_var, eps, momentum, save_mean_rstd, coef));
   int64_t nvec = M * C / 8;
   int cvec = C / 8;
   int g = apply_grid(nvec);
   if ((256 % cvec) == 0)
-    bn_apply_kernel<true><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu, relu_mask);
+    KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<true>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
   else
-    bn_apply_kernel<false><<<g, 256, 0, stream>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nvec, cvec, C, coef, relu, relu_mask);
-  KDL_CHECK_LAUNCH();
+    KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<false>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
   return KDL_OK;
 }
 
@@ -738,10 +741,8 @@ extern "C" int kdl_bn_finalize_from_stats(int64_t M, int C, const float* gamma, 
     kdl_set_error("bn_finalize_from_stats: missing partial statistics or outputs");
     return KDL_ERR_ARG;
   }
-  bn_finalize_partials_kernel<<<(C + 31) / 32, 1024, 0, stream>>>(stats_partial, nparts, M, C, gamma, beta,
-                                                                   running_mean, running_var, eps, momentum,
-                                                                   save_mean_rstd, coef_out);
-  KDL_CHECK_LAUNCH();
+  KDL_CUDA(kdl_launch_pdl(bn_finalize_partials_kernel, dim3((C + 31) / 32), dim3(1024), 0, stream, stats_partial, nparts,
+                          M, C, gamma, beta, running_mean, running_var, eps, momentum, save_mean_rstd, coef_out));
   return KDL_OK;
 }
 

@@ -10,6 +10,7 @@ step of reference Makefile:47-48).
 from __future__ import annotations
 
 import argparse
+import copy
 import os
 from typing import Dict
 
@@ -78,6 +79,34 @@ def crd_for(info: KindInfo) -> dict:
     }
 
 
+def crd_for_v1(info: KindInfo) -> dict:
+    """The same CRD as `apiextensions.k8s.io/v1` (clusters from 1.22 on no longer serve the
+    v1beta1 form the reference ships).  v1 wants a structural schema per version: every object
+    node is typed, and free-form parts (pod templates, metadata of embedded objects) say so."""
+    beta = crd_for(info)
+    schema = copy.deepcopy(beta["spec"]["validation"]["openAPIV3Schema"])
+
+    def structural(node: dict) -> None:
+        if node.get("type") == "object" and "properties" not in node and "additionalProperties" not in node:
+            node["x-kubernetes-preserve-unknown-fields"] = True
+        for child in (node.get("properties") or {}).values():
+            structural(child)
+        if isinstance(node.get("additionalProperties"), dict):
+            structural(node["additionalProperties"])
+        if isinstance(node.get("items"), dict):
+            structural(node["items"])
+    structural(schema)
+    cols = [{"jsonPath": col["JSONPath"], "name": col["name"], "type": col["type"]} for col in PRINTER_COLUMNS]
+    return {
+        "apiVersion": "apiextensions.k8s.io/v1", "kind": "CustomResourceDefinition",
+        "metadata": copy.deepcopy(beta["metadata"]),
+        "spec": {"group": info.group, "scope": "Namespaced", "names": copy.deepcopy(beta["spec"]["names"]),
+                 "versions": [{"name": info.version, "served": True, "storage": True,
+                               "additionalPrinterColumns": cols, "subresources": {"status": {}},
+                               "schema": {"openAPIV3Schema": schema}}]},
+    }
+
+
 def filename_for(info: KindInfo) -> str:
     return f"{info.group}_{info.plural}.yaml"
 
@@ -90,6 +119,18 @@ def write_all(out_dir: str) -> list:
         with open(p, "w") as f:
             f.write("# generated by `python -m kubedl_b200.api.crd`; do not edit\n---\n")
             yaml.safe_dump(crd_for(info), f, sort_keys=False)
+        paths.append(p)
+    return paths
+
+
+def write_all_v1(out_dir: str) -> list:
+    os.makedirs(out_dir, exist_ok=True)
+    paths = []
+    for info in SCHEME.workload_kinds():
+        p = os.path.join(out_dir, filename_for(info))
+        with open(p, "w") as f:
+            f.write("# generated by `python -m kubedl_b200.api.crd`; do not edit\n---\n")
+            yaml.safe_dump(crd_for_v1(info), f, sort_keys=False)
         paths.append(p)
     return paths
 
@@ -107,5 +148,7 @@ def validate(obj: dict) -> None:
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="config/crd/bases")
-    for p in write_all(ap.parse_args().out):
+    ap.add_argument("--out-v1", default="config/crd/v1")
+    a = ap.parse_args()
+    for p in write_all(a.out) + write_all_v1(a.out_v1):
         print(p)

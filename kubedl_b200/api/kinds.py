@@ -191,6 +191,7 @@ class Scheme:
                          "Event": ("", "v1", "events"), "ConfigMap": ("", "v1", "configmaps"),
                          "Namespace": ("", "v1", "namespaces"),
                          "Deployment": ("apps", "v1", "deployments"),
+                         "Lease": ("coordination.k8s.io", "v1", "leases"),
                          "PodGroup": ("scheduling.incubator.k8s.io", "v1alpha1", "podgroups")}
 
     def register(self, info: KindInfo) -> None:
@@ -216,6 +217,16 @@ class Scheme:
         if info is not None:
             info.defaulter(obj)
         return obj
+
+    def resource(self, kind: str) -> Tuple[str, str, str]:
+        """(group, version, plural) of any known kind — what a REST path is built from."""
+        if kind in self._by_kind:
+            i = self._by_kind[kind]
+            return (i.group, i.version, i.plural)
+        return self._builtin[kind]
+
+    def all_kinds(self) -> List[str]:
+        return list(self._by_kind) + list(self._builtin)
 
     def api_version(self, kind: str) -> str:
         if kind in self._by_kind:

@@ -46,6 +46,11 @@ class Timeout(ApiError):
     reason, code = "Timeout", 504
 
 
+class Gone(ApiError):
+    """watch from a resourceVersion that has fallen out of the event history (HTTP 410)."""
+    reason, code = "Expired", 410
+
+
 def is_not_found(e: Exception) -> bool: return isinstance(e, NotFound)
 def is_already_exists(e: Exception) -> bool: return isinstance(e, AlreadyExists)
 def is_conflict(e: Exception) -> bool: return isinstance(e, Conflict)
@@ -56,7 +61,7 @@ WatchHandler = Callable[[str, dict, Optional[dict]], None]  # (event_type, obj, 
 
 
 class APIServer:
-    def __init__(self, scheme=SCHEME, install_all_crds: bool = True):
+    def __init__(self, scheme=SCHEME, install_all_crds: bool = True, history: int = 8192):
         self.scheme = scheme
         self._lock = threading.RLock()
         self._objs: Dict[str, Dict[Tuple[str, str], dict]] = collections.defaultdict(dict)
@@ -66,6 +71,9 @@ class APIServer:
         self._dispatch_lock = threading.RLock()
         self._dispatching = threading.local()
         self._crds: Dict[str, dict] = {}
+        # bounded event history so remote watchers can resume from a resourceVersion
+        self._history: Deque[Tuple[int, str, str, dict]] = collections.deque(maxlen=history)
+        self._history_floor = 0    # events with rv <= floor have been dropped
         self.fail_next: Dict[Tuple[str, str], Exception] = {}  # fault injection: (verb, kind) -> error
         self.request_log: List[Tuple[str, str, str]] = []      # (verb, kind, ns/name) for launch-delay analysis
         if install_all_crds:
@@ -91,6 +99,25 @@ class APIServer:
     def _next_rv(self) -> str:
         self._rv += 1
         return str(self._rv)
+
+    def current_rv(self) -> str:
+        with self._lock:
+            return str(self._rv)
+
+    def _record(self, kind: str, ev: str, obj: dict) -> None:
+        """Append to the watch history (caller holds the lock; obj is already a private copy)."""
+        if self._history.maxlen is not None and len(self._history) == self._history.maxlen:
+            self._history_floor = self._history[0][0]
+        self._history.append((int(obj["metadata"]["resourceVersion"]), kind, ev, obj))
+
+    def events_since(self, kind: str, rv: str) -> List[Tuple[str, dict]]:
+        """Events of `kind` newer than resourceVersion `rv`, oldest first; `Gone` when the
+        history no longer reaches back that far (the client must list again)."""
+        since = int(rv or 0)
+        with self._lock:
+            if since < self._history_floor:
+                raise Gone(f"too old resource version: {since} ({self._history_floor})")
+            return [(ev, copy.deepcopy(o)) for r, k, ev, o in self._history if k == kind and r > since]
 
     def _maybe_fail(self, verb: str, kind: str) -> None:
         err = self.fail_next.pop((verb, kind), None)
@@ -127,6 +154,7 @@ class APIServer:
             m.setdefault("generation", 1)
             self._objs[kind][key] = o
             out = copy.deepcopy(o)
+            self._record(kind, ADDED, out)
             self._pending.append((kind, ADDED, out, None))
         self._dispatch()
         return copy.deepcopy(out)
@@ -152,6 +180,12 @@ class APIServer:
                 out.append(copy.deepcopy(o))
             out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
             return out
+
+    def list_with_rv(self, kind: str, namespace: Optional[str] = None,
+                     label_selector: Optional[Dict[str, str]] = None) -> Tuple[List[dict], str]:
+        """LIST plus the resourceVersion it is consistent with (what a reflector watches from)."""
+        with self._lock:
+            return self.list(kind, namespace, label_selector), str(self._rv)
 
     def _update(self, obj: dict, status_only: bool, spec_only: bool) -> dict:
         kind = obj.get("kind")
@@ -187,6 +221,7 @@ class APIServer:
             new["metadata"]["resourceVersion"] = self._next_rv()
             self._objs[kind][key] = new
             out = copy.deepcopy(new)
+            self._record(kind, MODIFIED, out)
             self._pending.append((kind, MODIFIED, out, old))
         self._dispatch()
         return copy.deepcopy(out)
@@ -220,6 +255,8 @@ class APIServer:
                 raise NotFound(f'{kind.lower()} "{name}" not found')
             gone = copy.deepcopy(cur)
             gone.setdefault("metadata", {})["deletionTimestamp"] = c.now_rfc3339()
+            gone["metadata"]["resourceVersion"] = self._next_rv()   # a deletion is a write too
+            self._record(kind, DELETED, gone)
             self._pending.append((kind, DELETED, gone, None))
             dependents = []
             if cascade:

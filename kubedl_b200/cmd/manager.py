@@ -5,6 +5,13 @@ Order of wiring is the reference's: manager -> schemes -> gang schedulers -> wor
 Flags are the reference's (main.go:54-60, workload_gate.go:22, persist_controller.go:31-33;
 table in reference docs/startup_flags.md) plus what a single-box deployment needs: the REST
 façade address, the number of GPUs the node agent manages, and `--no-node-agent`.
+
+Two deployment shapes:
+  * all-in-one (default): API server, controllers and node agent in this process;
+  * against a cluster: `--master URL`, `--kubeconfig PATH`, `$KUBECONFIG` or the pod's service
+    account (reference pkg/util/k8sutil/k8sutil.go:44-69) select a remote Kubernetes API server
+    (a real kube-apiserver, or `python -m kubedl_b200.cmd.apiserver`); pods are then run by that
+    cluster's kubelets (or by `python -m kubedl_b200.cmd.gpulet`), leader election uses a Lease.
 """
 from __future__ import annotations
 
@@ -16,6 +23,7 @@ from dataclasses import dataclass, field
 from typing import Dict, List, Optional
 
 from ..apiserver import rest
+from ..apiserver.kube import KubeAPIServer, KubeConfig
 from ..apiserver.store import APIServer
 from ..controllers import persist
 from ..controllers import registry as controller_registry
@@ -55,7 +63,23 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--gpus", type=int, default=None, help="GPUs managed by the node agent (default: all visible)")
     ap.add_argument("--no-node-agent", action="store_true", help="control plane only (pods are never started)")
     ap.add_argument("--leader-lock", default="/tmp/kubedl-b200-leader.lock")
+    # against a cluster
+    ap.add_argument("--master", default="", help="URL of a Kubernetes API server to reconcile against "
+                    "(overrides the server of the kubeconfig)")
+    ap.add_argument("--kubeconfig", default="", help="path to a kubeconfig; $KUBECONFIG and the in-cluster "
+                    "service account are tried when --in-cluster is given")
+    ap.add_argument("--context", default=None, help="kubeconfig context (default: current-context)")
+    ap.add_argument("--in-cluster", action="store_true", help="use $KUBECONFIG or the pod's service account")
+    ap.add_argument("--leader-election-namespace", default="kubedl-system")
+    ap.add_argument("--install-crds", action="store_true", help="create missing CRDs on the remote API server at start")
     return ap
+
+
+def remote_api_from_args(args) -> Optional[KubeAPIServer]:
+    """A `KubeAPIServer` when any of the cluster flags is given, else None (all-in-one)."""
+    if not (args.master or args.kubeconfig or args.in_cluster):
+        return None
+    return KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context))
 
 
 @dataclass
@@ -84,12 +108,21 @@ def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None)
     if args.gang_scheduler_name:
         CTRL_CONFIG.enable_gang_scheduling = True
         CTRL_CONFIG.gang_scheduler_name = args.gang_scheduler_name
-    mgr = Manager(api=api, leader_election=bool(args.enable_leader_election), leader_lock_path=args.leader_lock)
+    if api is None:
+        api = remote_api_from_args(args)
+    remote = bool(getattr(api, "remote", False))
+    if remote and getattr(args, "install_crds", False):
+        from ..api.kinds import SCHEME
+        for info in SCHEME.workload_kinds():
+            api.install_crd(info.kind)
+    mgr = Manager(api=api, leader_election=bool(args.enable_leader_election), leader_lock_path=args.leader_lock,
+                  leader_election_namespace=getattr(args, "leader_election_namespace", "kubedl-system"))
     gang_schedule.register_gang_schedulers(mgr)
     recs = controller_registry.setup_with_manager(mgr, CTRL_CONFIG, args.workloads, metrics_registry)
     storage_backends.register_storage_backends()
     pers = persist.setup_with_manager(mgr, args.object_storage, args.event_storage, args.region, args.workloads)
-    let = None if args.no_node_agent else Gpulet(mgr.api, num_gpus=args.gpus)
+    # against a cluster the pods belong to its kubelets (or to a separate gpulet process)
+    let = None if (args.no_node_agent or remote) else Gpulet(mgr.api, num_gpus=args.gpus)
     return Operator(mgr, recs, pers, let)
 
 
@@ -102,7 +135,7 @@ def start_operator(op: Operator, args, metrics_registry=None) -> None:
     op.mgr.start(block=False)
     if op.gpulet:
         op.gpulet.start()
-    if args.serve:
+    if args.serve and not getattr(op.mgr.api, "remote", False):
         host, _, port = args.serve.rpartition(":")
         op.servers.append(rest.serve(op.mgr.api, host or "127.0.0.1", int(port),
                                      log_reader=op.gpulet.pod_log if op.gpulet else None))

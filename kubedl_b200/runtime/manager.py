@@ -46,6 +46,17 @@ class Result:
     requeue_after: float = 0.0
 
 
+def _older(a: Optional[dict], b: Optional[dict], unknown: bool = False) -> bool:
+    """Is `a` an older version of the object than `b`?  resourceVersions are compared as the
+    integers every real API server uses; if they are not integers the answer is `unknown`."""
+    if a is None or b is None:
+        return False
+    try:
+        return int(a["metadata"]["resourceVersion"]) < int(b["metadata"]["resourceVersion"])
+    except (KeyError, TypeError, ValueError):
+        return unknown
+
+
 class Client:
     """Reads come from an informer cache kept current by watches; writes go to the API server.
     `reader()` gives uncached reads (reference pkg/util/runtime.go:29-48)."""
@@ -67,9 +78,24 @@ class Client:
             with self._lock:
                 if ev == DELETED:
                     self._cache[kind].pop(key, None)
-                else:
+                elif not _older(obj, self._cache[kind].get(key)):
                     self._cache[kind][key] = obj
         self._stops.append(self.api.watch(kind, on_event, replay=True))
+
+    def _remember(self, obj: dict) -> dict:
+        """Read-your-writes: what a write returned goes into the cache at once if it is newer than
+        what the watch has delivered so far.  Against a remote API server the watch event for our
+        own write arrives later; a reconcile in between would otherwise compute the next status
+        from a copy that lacks the previous one (and, writing it, drop a condition)."""
+        kind = obj.get("kind", "")
+        with self._lock:
+            cache = self._cache.get(kind)
+            if cache is not None:
+                key = (c.namespace_of(obj), c.name_of(obj))
+                cur = cache.get(key)
+                if cur is not None and _older(cur, obj):   # never resurrect what a DELETED event removed
+                    cache[key] = copy.deepcopy(obj)
+        return obj
 
     def get(self, kind: str, namespace: str, name: str) -> dict:
         self.ensure_informer(kind)
@@ -100,8 +126,8 @@ class Client:
 
     # writes
     def create(self, obj: dict) -> dict: return self.api.create(obj)
-    def update(self, obj: dict) -> dict: return self.api.update(obj)
-    def update_status(self, obj: dict) -> dict: return self.api.update_status(obj)
+    def update(self, obj: dict) -> dict: return self._remember(self.api.update(obj))
+    def update_status(self, obj: dict) -> dict: return self._remember(self.api.update_status(obj))
     def delete(self, kind: str, namespace: str, name: str) -> None: self.api.delete(kind, namespace, name)
 
     def stop(self) -> None:
@@ -285,9 +311,113 @@ class LeaderElector:
             self._fd = None
 
 
+class LeaseLeaderElector:
+    """Leader election on a `coordination.k8s.io/v1` Lease — what controller-runtime does for the
+    reference when `--enable-leader-election` is set (reference main.go:56-57,73) — used when the
+    API server is remote, where an flock on one machine means nothing.
+
+    A candidate owns the lease if it created it, if the holder field is empty, or if the holder
+    has not renewed within `leaseDurationSeconds`.  Every write carries the resourceVersion that
+    was read, so two candidates racing for an expired lease cannot both win.  The holder renews
+    every `retry_period`; if it cannot renew for `renew_deadline` it calls `on_lost` (the manager
+    stops: two active operators would fight over the same pods)."""
+
+    def __init__(self, api, namespace: str = "kubedl-system", name: str = "kubedl-election",
+                 identity: Optional[str] = None, lease_duration: float = 15.0, renew_deadline: float = 10.0,
+                 retry_period: float = 2.0, on_lost: Optional[Callable[[], None]] = None):
+        self.api, self.namespace, self.name = api, namespace, name
+        self.identity = identity or f"{os.uname().nodename}_{os.getpid()}_{os.urandom(3).hex()}"
+        self.lease_duration, self.renew_deadline, self.retry_period = lease_duration, renew_deadline, retry_period
+        self.on_lost = on_lost
+        self.is_leader = False
+        self._stop = threading.Event()
+        self._thread: Optional[threading.Thread] = None
+
+    def _spec(self, prev: Optional[dict]) -> dict:
+        now = c.now_precise()
+        prev = prev or {}
+        mine = prev.get("holderIdentity") == self.identity
+        return {"holderIdentity": self.identity, "leaseDurationSeconds": int(round(self.lease_duration)),
+                "acquireTime": prev.get("acquireTime") if mine else now, "renewTime": now,
+                "leaseTransitions": int(prev.get("leaseTransitions", 0)) + (0 if mine or not prev else 1)}
+
+    def try_acquire_or_renew(self) -> bool:
+        from ..apiserver.store import AlreadyExists, Conflict
+        try:
+            lease = self.api.get("Lease", self.namespace, self.name)
+        except NotFound:
+            try:
+                self.api.create({"apiVersion": "coordination.k8s.io/v1", "kind": "Lease",
+                                 "metadata": {"name": self.name, "namespace": self.namespace},
+                                 "spec": self._spec(None)})
+                return True
+            except AlreadyExists:
+                return False
+        spec = lease.get("spec") or {}
+        holder = spec.get("holderIdentity") or ""
+        if holder and holder != self.identity:
+            renewed = c.parse_time(spec.get("renewTime")) or 0.0
+            if time.time() < renewed + float(spec.get("leaseDurationSeconds") or self.lease_duration):
+                return False                     # somebody else holds a live lease
+        lease["spec"] = self._spec(spec)
+        try:
+            self.api.update(lease)               # carries the resourceVersion we read
+            return True
+        except (Conflict, NotFound):
+            return False
+
+    def acquire(self, blocking: bool = True) -> bool:
+        while not self._stop.is_set():
+            try:
+                if self.try_acquire_or_renew():
+                    self.is_leader = True
+                    self._thread = threading.Thread(target=self._renew_loop, name="leader-renew", daemon=True)
+                    self._thread.start()
+                    return True
+            except Exception as e:
+                log.warning("leader election: %r", e)
+            if not blocking:
+                return False
+            self._stop.wait(self.retry_period)
+        return False
+
+    def _renew_loop(self) -> None:
+        last_ok = time.monotonic()
+        while not self._stop.wait(self.retry_period):
+            ok = False
+            try:
+                ok = self.try_acquire_or_renew()
+            except Exception as e:
+                log.warning("leader election renew: %r", e)
+            if ok:
+                last_ok = time.monotonic()
+            elif time.monotonic() - last_ok > self.renew_deadline:
+                self.is_leader = False
+                log.error("leader election lost (%s)", self.identity)
+                if self.on_lost:
+                    self.on_lost()
+                return
+
+    def release(self) -> None:
+        self._stop.set()
+        if self._thread is not None and self._thread is not threading.current_thread():
+            self._thread.join(timeout=2)
+        if not self.is_leader:
+            return
+        self.is_leader = False
+        try:                                     # hand over at once instead of after leaseDuration
+            lease = self.api.get("Lease", self.namespace, self.name)
+            if (lease.get("spec") or {}).get("holderIdentity") == self.identity:
+                lease["spec"]["holderIdentity"] = ""
+                self.api.update(lease)
+        except Exception:
+            pass
+
+
 class Manager:
     def __init__(self, api: Optional[APIServer] = None, scheme=SCHEME, leader_election: bool = False,
-                 leader_lock_path: str = "/tmp/kubedl-b200-leader.lock"):
+                 leader_lock_path: str = "/tmp/kubedl-b200-leader.lock",
+                 leader_election_namespace: str = "kubedl-system"):
         self.api = api or APIServer(scheme)
         self.scheme = scheme
         self.client = Client(self.api)
@@ -295,7 +425,12 @@ class Manager:
         self.stopping = threading.Event()
         self._recorders: Dict[str, EventRecorder] = {}
         self.leader_election = leader_election
-        self.elector = LeaderElector(leader_lock_path) if leader_election else None
+        if not leader_election:
+            self.elector = None
+        elif getattr(self.api, "remote", False):
+            self.elector = LeaseLeaderElector(self.api, leader_election_namespace, on_lost=self.stop)
+        else:
+            self.elector = LeaderElector(leader_lock_path)
         self.runnables: List[Callable[["Manager"], None]] = []   # started with the manager (gpulet, metrics...)
         self._started = False
 
@@ -341,6 +476,8 @@ class Manager:
         self.client.stop()
         if self.elector is not None:
             self.elector.release()
+        if getattr(self.api, "remote", False):
+            self.api.close()                     # ends the reflector threads
 
     # ---- deterministic mode (tests, single-threaded drivers)
     def start_watches(self) -> None:

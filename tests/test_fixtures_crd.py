@@ -72,6 +72,31 @@ def test_crd_manifests_match_registry(tmp_path):
     assert "minFinishWorkRate" in xdl["spec"]["validation"]["openAPIV3Schema"]["properties"]["spec"]["properties"]
 
 
+def test_crd_v1_manifests_match_registry(tmp_path):
+    """The apiextensions.k8s.io/v1 form (for clusters that dropped v1beta1) stays in step too."""
+    for p in crd.write_all_v1(str(tmp_path)):
+        doc = list(yaml.safe_load_all(open(p)))[-1]
+        committed = list(yaml.safe_load_all(open(os.path.join("config/crd/v1", os.path.basename(p)))))[-1]
+        assert doc == committed, f"{p}: run python -m kubedl_b200.api.crd"
+        assert doc["apiVersion"] == "apiextensions.k8s.io/v1" and "validation" not in doc["spec"]
+        (v,) = doc["spec"]["versions"]
+        assert v["served"] and v["storage"] and v["subresources"] == {"status": {}}
+        assert [col["name"] for col in v["additionalPrinterColumns"]] == ["State", "Age", "Finished-TTL", "Max-Lifetime"]
+        assert all("jsonPath" in col for col in v["additionalPrinterColumns"])
+
+        def check(node, path="root"):      # structural: every object node has a shape or says it is free-form
+            if node.get("type") == "object":
+                assert "properties" in node or "additionalProperties" in node or \
+                    node.get("x-kubernetes-preserve-unknown-fields"), path
+            for k, child in (node.get("properties") or {}).items():
+                check(child, f"{path}.{k}")
+            if isinstance(node.get("additionalProperties"), dict):
+                check(node["additionalProperties"], path + "[*]")
+            if isinstance(node.get("items"), dict):
+                check(node["items"], path + "[]")
+        check(v["schema"]["openAPIV3Schema"])
+
+
 def test_crd_validation_of_examples():
     import jsonschema
     for path in ("example/pytorch/pytorch_job_mnist_mpi.yaml", "example/tf/tf_job_mnist.yaml",

@@ -74,7 +74,8 @@ class ImageRegistry:
         py = sys.executable
         self.images: Dict[str, List[str]] = {
             "kubedl/pytorch-dist-example": [py, "-m", "kubedl_b200.worker.mnist_ddp"],
-            "kubedl/tf-mnist-with-summaries:1.0": [py, "-m", "kubedl_b200.worker.tf_stub"],
+            "kubedl/tf-mnist-with-summaries:1.0": [py, "-m", "kubedl_b200.worker.tf_ps_train"],
+            "kubedl-b200/tf-lifecycle-stub": [py, "-m", "kubedl_b200.worker.tf_stub"],
             "docker.io/merlintang/xgboost-dist-iris:1.1": [py, "-m", "kubedl_b200.worker.xgb_train"],
             "kubedl/xdl-mnist-example": [py, "-m", "kubedl_b200.worker.xdl_train"],
             "kubedl/git-sync:v1": [py, "-m", "kubedl_b200.node.git_sync"],
@@ -283,7 +284,9 @@ class Gpulet:
                 return m.group(0)
             out = "127.0.0.1"
             if port:
-                out += ":" + str(self._host_port(ns, job, int(port)))
+                # one host port per (replica, declared port): every entry of a TF_CONFIG cluster map
+                # declares the same port on a different DNS name and must stay distinguishable
+                out += ":" + str(self._host_port(ns, short, int(port)))
             return out
         pat = re.compile(r"\b(" + re.escape(job) + r"-[a-z0-9]+-\d+(\.[A-Za-z0-9.\-]+)?)(?::(\d+))?")
         return pat.sub(repl, value)

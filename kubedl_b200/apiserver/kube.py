@@ -26,6 +26,7 @@ import copy
 import http.client
 import json
 import os
+import socket
 import ssl
 import tempfile
 import threading
@@ -196,8 +197,12 @@ class KubeConfig:
     def connect(self, timeout: Optional[float]) -> http.client.HTTPConnection:
         u = urllib.parse.urlsplit(self.server)
         if u.scheme == "https":
-            return http.client.HTTPSConnection(u.hostname, u.port or 443, timeout=timeout, context=self.ssl_context())
-        return http.client.HTTPConnection(u.hostname, u.port or 80, timeout=timeout)
+            conn = http.client.HTTPSConnection(u.hostname, u.port or 443, timeout=timeout, context=self.ssl_context())
+        else:
+            conn = http.client.HTTPConnection(u.hostname, u.port or 80, timeout=timeout)
+        conn.connect()
+        conn.sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)   # small requests, latency matters
+        return conn
 
     @property
     def base_path(self) -> str:

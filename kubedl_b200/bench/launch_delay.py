@@ -53,20 +53,37 @@ def _job(kind: str, name: str, replicas: int, seconds: float) -> dict:
                      cleanPodPolicy="All")
 
 
-def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1) -> dict:
-    args = M.build_parser().parse_args(["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0",
-                                        "--workloads", "*", "--gpus", "0", "--max-reconciles", str(max_reconciles)])
+def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1, remote: bool = False) -> dict:
+    """remote=True puts the API server behind HTTP (`apiserver/rest.py`) with the node agent next to
+    it, and makes the operator a client of it (`apiserver/kube.py`) — the reference's deployment
+    shape, where every pod / service create and every status write is a round trip."""
+    flags = ["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0", "--workloads", "*",
+             "--gpus", "0", "--max-reconciles", str(max_reconciles)]
     reg = CollectorRegistry()
+    extra = []
+    if remote:
+        from ..apiserver import rest
+        from ..apiserver.store import APIServer
+        from ..node.gpulet import Gpulet
+        backing = APIServer()
+        srv = rest.serve(backing, "127.0.0.1", 0)
+        let = Gpulet(backing, num_gpus=0)
+        let.start()
+        extra = [let.stop, srv.shutdown]
+        flags += ["--master", srv.url]
+    args = M.build_parser().parse_args(flags)
     op = M.build_operator(args, metrics_registry=reg)
     M.start_operator(op, args, metrics_registry=reg)
     done_times = []
+    # the bench's own polling must not load the wire it is measuring: watch the state where it lives
+    state = backing if remote else op.mgr.api
     try:
         for i in range(jobs):
             name = f"{kind.lower()}-{i}"
             t0 = time.time()
             op.mgr.api.create(_job(kind, name, replicas, seconds))
             while True:
-                s = op.mgr.api.get(kind, "bench", name).get("status", {})
+                s = state.get(kind, "bench", name).get("status", {})
                 if st.is_succeeded(s) or st.is_failed(s):
                     break
                 if time.time() - t0 > 120:
@@ -82,9 +99,11 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
                 "first_pod_ms": {"p50": 1e3 * _pct(first, 0.5), "p90": 1e3 * _pct(first, 0.9), "n": len(first)},
                 "all_pods_ms": {"p50": 1e3 * _pct(allp, 0.5), "p90": 1e3 * _pct(allp, 0.9), "n": len(allp)},
                 "time_to_succeeded_ms": {"p50": 1e3 * _pct(done_times, 0.5), "p90": 1e3 * _pct(done_times, 0.9)},
-                "api_creates_per_job": creates / jobs}
+                "api_creates_per_job": creates / jobs, "api": "http" if remote else "in-process"}
     finally:
         op.stop()
+        for fn in extra:
+            fn()
 
 
 def main(argv=None) -> int:
@@ -93,9 +112,11 @@ def main(argv=None) -> int:
     ap.add_argument("--replicas", type=int, default=8)
     ap.add_argument("--seconds", type=float, default=0.2)
     ap.add_argument("--kinds", default="PyTorchJob,TFJob,XGBoostJob,XDLJob")
+    ap.add_argument("--remote", action="store_true", help="operator talks to the API server over HTTP")
+    ap.add_argument("--max-reconciles", type=int, default=1)
     a = ap.parse_args(argv)
     for kind in a.kinds.split(","):
-        print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds)), flush=True)
+        print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds, a.max_reconciles, a.remote)), flush=True)
     return 0
 
 

@@ -55,6 +55,8 @@ def main(argv=None) -> int:
     ap.add_argument("--state", default="", help="snapshot file to load at start and save at exit")
     ap.add_argument("--snapshot-interval", type=float, default=0.0)
     args = ap.parse_args(argv)
+    from .manager import low_latency_threads
+    low_latency_threads()
     api = APIServer(install_all_crds=False)
     wanted = [k.strip().lower() for k in args.crds.split(",") if k.strip()]
     for info in SCHEME.workload_kinds():

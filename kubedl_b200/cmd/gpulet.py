@@ -28,6 +28,8 @@ def main(argv=None) -> int:
     ap.add_argument("--node-name", default="b200-node-0")
     ap.add_argument("--log-dir", default="/tmp/kubedl-b200/pods")
     args = ap.parse_args(argv)
+    from .manager import low_latency_threads
+    low_latency_threads()
     api = KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context))
     let = Gpulet(api, num_gpus=args.gpus, node_name=args.node_name, log_dir=args.log_dir)
     let.start()

@@ -405,8 +405,8 @@ class JobController:
                     if is_already_exists(e):
                         # the cache missed an earlier create: observe it ourselves so the queue
                         # does not stall on the expectation (reference pod.go:265-278)
+                        # (create_new_pod has taken the failed create out of the pod count already)
                         key = c.key_of(job)
-                        self.expectations.creation_observed(gen_expectation_pods_key(key, rt))
                         self.expectations.creation_observed(gen_expectation_services_key(key, rt))
                     raise
             else:
@@ -429,28 +429,33 @@ class JobController:
     def create_new_pod(self, job: dict, rt: str, index: str, spec: dict, master_role: bool,
                        replicas: Dict[str, dict]) -> None:
         job_key = c.key_of(job)
-        self.expectations.expect_creations(gen_expectation_pods_key(job_key, rt), 1)
-        labels = self.gen_labels(c.name_of(job))
-        labels[c.REPLICA_TYPE_LABEL] = rt
-        labels[c.REPLICA_INDEX_LABEL] = index
-        if master_role:
-            labels[c.JOB_ROLE_LABEL] = "master"
-        template = c.deepcopy(spec.get("template") or {})
-        tm = template.setdefault("metadata", {})
-        tm["name"] = gen_general_name(c.name_of(job), rt, index)
-        tm.setdefault("labels", {})
-        if tm["labels"] is None:
-            tm["labels"] = {}
-        tm["labels"].update(labels)
-        template.setdefault("spec", {})
-        self.controller.set_cluster_spec(job, template, rt, index)
-        if template["spec"].get("restartPolicy"):
-            msg = "Restart policy in pod template will be overwritten by restart policy in replica spec"
-            self.recorder.event(job, EVENT_WARNING, POD_TEMPLATE_RESTART_POLICY_REASON, msg)
-        set_restart_policy(template, spec)
-        if self.config.enable_gang_scheduling and self.gang_scheduler is not None:
-            gang = self.gang_scheduler.get_gang(c.namespace_of(job), c.name_of(job))
-            self.gang_scheduler.bind_pod_to_gang(template, gang)
+        exp_key = gen_expectation_pods_key(job_key, rt)
+        self.expectations.expect_one_more_creation(exp_key)
+        try:
+            labels = self.gen_labels(c.name_of(job))
+            labels[c.REPLICA_TYPE_LABEL] = rt
+            labels[c.REPLICA_INDEX_LABEL] = index
+            if master_role:
+                labels[c.JOB_ROLE_LABEL] = "master"
+            template = c.deepcopy(spec.get("template") or {})
+            tm = template.setdefault("metadata", {})
+            tm["name"] = gen_general_name(c.name_of(job), rt, index)
+            tm.setdefault("labels", {})
+            if tm["labels"] is None:
+                tm["labels"] = {}
+            tm["labels"].update(labels)
+            template.setdefault("spec", {})
+            self.controller.set_cluster_spec(job, template, rt, index)
+            if template["spec"].get("restartPolicy"):
+                msg = "Restart policy in pod template will be overwritten by restart policy in replica spec"
+                self.recorder.event(job, EVENT_WARNING, POD_TEMPLATE_RESTART_POLICY_REASON, msg)
+            set_restart_policy(template, spec)
+            if self.config.enable_gang_scheduling and self.gang_scheduler is not None:
+                gang = self.gang_scheduler.get_gang(c.namespace_of(job), c.name_of(job))
+                self.gang_scheduler.bind_pod_to_gang(template, gang)
+        except Exception:
+            self.expectations.creation_observed(exp_key)   # nothing was sent: nothing to wait for
+            raise
         ref = self.gen_owner_reference(job)
         try:
             pod = self.pod_control_template_to_pod(template, job, ref)
@@ -458,6 +463,9 @@ class JobController:
         except Exception as e:
             if is_timeout(e):
                 return  # the create may still land; the expectation/TTL path resolves it
+            # no ADDED event will come for this one (AlreadyExists included: that pod's event was
+            # either seen already or belongs to an earlier expectation)
+            self.expectations.creation_observed(exp_key)
             self.recorder.eventf(job, EVENT_WARNING, "FailedCreatePod", "Error creating: %s", e)
             raise
         self.recorder.eventf(job, EVENT_NORMAL, "SuccessfulCreatePod", "Created pod: %s", tm["name"])
@@ -494,11 +502,16 @@ class JobController:
 
     def create_new_service(self, job: dict, rtype: str, spec: dict, index: str) -> None:
         rt = rtype.lower()
-        self.expectations.expect_creations(gen_expectation_services_key(c.key_of(job), rt), 1)
+        exp_key = gen_expectation_services_key(c.key_of(job), rt)
+        self.expectations.expect_one_more_creation(exp_key)
         labels = self.gen_labels(c.name_of(job))
         labels[c.REPLICA_TYPE_LABEL] = rt
         labels[c.REPLICA_INDEX_LABEL] = index
-        port = self.get_port_from_spec(spec)
+        try:
+            port = self.get_port_from_spec(spec)
+        except LookupError:
+            self.expectations.creation_observed(exp_key)
+            raise
         name = gen_general_name(c.name_of(job), rt, index)
         svc = {"apiVersion": "v1", "kind": "Service",
                "metadata": {"name": name, "namespace": c.namespace_of(job), "labels": dict(labels),
@@ -510,6 +523,7 @@ class JobController:
         except Exception as e:
             if is_timeout(e):
                 return
+            self.expectations.creation_observed(exp_key)
             self.recorder.eventf(job, EVENT_WARNING, "FailedCreateService", "Error creating: %s", e)
             raise RuntimeError(f"unable to create services: {e}") from e
         self.recorder.eventf(job, EVENT_NORMAL, "SuccessfulCreateService", "Created service: %s", name)

@@ -5,7 +5,12 @@ does not re-diff until they are observed or the expectation expires (5 min upstr
 The reference keys them `<jobKey>/<rtype>/pods` and `<jobKey>/<rtype>/services`
 (pkg/job_controller/util.go:51-57) and ANDs them in SatisfyExpectations
 (pkg/job_controller/expectations.go:11-27).  Note `expect_creations(key, n)` OVERWRITES the
-record (SetExpectations), which the reference calls with n=1 per pod (pod.go:329-333).
+record (SetExpectations), which the reference calls with n=1 per pod (pod.go:329-333): after
+eight creates it expects one event, so the first ADDED that arrives lets a reconcile through
+while seven pods are still unknown to the cache, and that reconcile creates them again
+(AlreadyExists, error, rate-limited requeue).  Against an in-process store that never shows;
+against a remote API server it showed on every other job.  The engine therefore counts with
+`expect_one_more_creation`, which accumulates.
 """
 from __future__ import annotations
 
@@ -42,6 +47,18 @@ class ControllerExpectations:
 
     def expect_deletions(self, key: str, dels: int) -> None:
         self.set_expectations(key, 0, dels)
+
+    def expect_one_more_creation(self, key: str) -> None:
+        """Count one more create in flight.  A live record with creates still unobserved grows;
+        anything else (no record, satisfied, expired) starts again at one."""
+        with self._lock:
+            r = self._store.get(key)
+            now = self.clock()
+            if r is not None and r.add > 0 and now - r.ts <= self.ttl:
+                r.add += 1
+                r.ts = now
+            else:
+                self._store[key] = _Record(1, 0, now)
 
     def raise_expectations(self, key: str, add: int, dele: int) -> None:
         with self._lock:

@@ -15,6 +15,7 @@ from __future__ import annotations
 import copy
 import fcntl
 import os
+import queue
 import threading
 import time
 import traceback
@@ -143,10 +144,43 @@ class EventRecorder:
         self.api, self.component = api, component
         self.events: List[Tuple[str, str, str, str]] = []  # (object key, type, reason, message)
         self._lock = threading.Lock()
+        # Against a remote API server an Event is a round trip; client-go's recorder hands events
+        # to a broadcaster goroutine so that reconciles never wait for them, and so do we.
+        self._async = bool(getattr(api, "remote", False))
+        self._q: "queue.Queue" = queue.Queue(maxsize=1000)
+        self._thread: Optional[threading.Thread] = None
+
+    def _drain(self) -> None:
+        while True:
+            item = self._q.get()
+            if item is None:
+                return
+            try:
+                self.api.record_event(*item, source=self.component)
+            except Exception:  # events are best effort
+                pass
+            finally:
+                self._q.task_done()
+
+    def flush(self, timeout: float = 5.0) -> None:
+        """Wait until queued events have been written (tests, shutdown)."""
+        deadline = time.monotonic() + timeout
+        while self._q.unfinished_tasks and time.monotonic() < deadline:
+            time.sleep(0.005)
 
     def event(self, obj: dict, etype: str, reason: str, message: str) -> None:
         with self._lock:
             self.events.append((c.key_of(obj), etype, reason, message))
+            if self._async and self._thread is None:
+                self._thread = threading.Thread(target=self._drain, name=f"events-{self.component}", daemon=True)
+                self._thread.start()
+        if self._async:
+            try:
+                self._q.put_nowait((copy.deepcopy({k: obj.get(k) for k in ("kind", "apiVersion", "metadata")}),
+                                    etype, reason, message))
+            except queue.Full:       # dropping beats blocking a reconcile (client-go does the same)
+                pass
+            return
         try:
             self.api.record_event(obj, etype, reason, message, source=self.component)
         except Exception:  # events are best effort

@@ -34,6 +34,11 @@ import threading
 import time
 from typing import Dict, List, Optional, Tuple
 
+if __name__ == "__main__" and os.environ.get("KUBEDL_TF_TRAIN_SECONDS"):
+    # lifecycle-only mode (launch-delay bench): answer before paying for `import torch`
+    from kubedl_b200.worker import tf_stub
+    sys.exit(tf_stub.main())
+
 import torch
 
 from .rendezvous import replica_identity, tf_config

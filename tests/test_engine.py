@@ -263,6 +263,38 @@ def test_already_exists_recovery_does_not_stall_expectations():
     assert [c.name_of(p) for p in cl.pods("ns")] == ["tf-worker-0"]
 
 
+def test_expectations_count_every_create_in_flight():
+    """Eight creates mean eight ADDED events to wait for, not one (the reference's
+    `ExpectCreations(key, 1)` per pod overwrites, pod.go:329-333; see docs/parity_notes.md #5)."""
+    from kubedl_b200.runtime.expectations import ControllerExpectations
+    now = [0.0]
+    e = ControllerExpectations(clock=lambda: now[0], ttl=300)
+    for _ in range(3):
+        e.expect_one_more_creation("k")
+    e.creation_observed("k")
+    assert not e.satisfied_expectations("k")          # two still unseen
+    e.creation_observed("k")
+    e.creation_observed("k")
+    assert e.satisfied_expectations("k")
+    e.expect_one_more_creation("k")                   # a satisfied record starts again at one
+    assert e.get("k").add == 1
+    now[0] = 301.0
+    assert e.satisfied_expectations("k")              # expired: resync
+    e.expect_one_more_creation("k")                   # an expired record is not grown
+    assert e.get("k").add == 1 and not e.satisfied_expectations("k")
+
+
+def test_failed_create_does_not_leave_an_expectation_behind():
+    cl = Cluster()
+    cl.api.create(_tfjob(workers=2))
+    cl.api.fail_next[("create", "Pod")] = RuntimeError("admission webhook said no")
+    cl.settle()
+    r = cl.recs["TFJob"]
+    assert r.ctrl.expectations.satisfied_expectations(gen_expectation_pods_key("ns/tf", "worker"))
+    cl.mgr.run_until_idle(advance_delayed=True)
+    assert [c.name_of(p) for p in cl.pods("ns")] == ["tf-worker-0", "tf-worker-1"]
+
+
 def test_timeout_on_create_is_not_an_error():
     cl = Cluster()
     cl.api.create(_tfjob(workers=1))

@@ -135,6 +135,24 @@ def write_all_v1(out_dir: str) -> list:
     return paths
 
 
+def all_in_one(config_dir: str = "config") -> str:
+    """One file to `kubectl apply`: namespaces, v1 CRDs, RBAC, operator Deployment — what the
+    reference ships as config/manager/all_in_one.yaml (namespaces `kubedl` and `kubedl-system`,
+    ClusterRole + binding, Deployment; reference all_in_one.yaml:1-328)."""
+    parts = ["# generated by `python -m kubedl_b200.api.crd`; do not edit\n"
+             "# kubectl apply -f config/manager/all_in_one.yaml\n"]
+    docs = [{"apiVersion": "v1", "kind": "Namespace", "metadata": {"name": "kubedl"}}]
+    docs += [crd_for_v1(info) for info in SCHEME.workload_kinds()]
+    for rel in ("manager/in_cluster.yaml", "rbac/role.yaml", "rbac/role_binding.yaml",
+                "rbac/leader_election_role.yaml", "rbac/leader_election_role_binding.yaml"):
+        with open(os.path.join(config_dir, rel)) as f:
+            docs += [d for d in yaml.safe_load_all(f) if d]
+    order = {"Namespace": 0, "CustomResourceDefinition": 1, "ServiceAccount": 2, "ClusterRole": 3, "Role": 3,
+             "ClusterRoleBinding": 4, "RoleBinding": 4, "Deployment": 5}
+    docs.sort(key=lambda d: order.get(d["kind"], 9))
+    return parts[0] + "---\n".join(yaml.safe_dump(d, sort_keys=False) for d in docs)
+
+
 def validate(obj: dict) -> None:
     """Minimal structural validation of a job against the CRD schema (what the API server's
     OpenAPI validation would reject)."""
@@ -152,3 +170,6 @@ if __name__ == "__main__":
     a = ap.parse_args()
     for p in write_all(a.out) + write_all_v1(a.out_v1):
         print(p)
+    with open("config/manager/all_in_one.yaml", "w") as f:
+        f.write(all_in_one())
+    print("config/manager/all_in_one.yaml")

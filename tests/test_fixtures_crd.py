@@ -146,3 +146,41 @@ def test_custom_workload_recipe():
     finally:
         registry.SETUP_WITH_MANAGER_MAP.pop(T.TEST_JOB_KIND, None)
         SCHEME._by_kind.pop(T.TEST_JOB_KIND, None)
+
+
+def test_deploy_manifests_are_consistent():
+    """config/: the all-in-one file is what the generator emits, every kustomization points at files
+    that exist, and the RBAC rules cover every resource the operator reads or writes."""
+    import glob
+    assert open("config/manager/all_in_one.yaml").read() == crd.all_in_one(), "run python -m kubedl_b200.api.crd"
+    for path in glob.glob("config/**/*.yaml", recursive=True):
+        docs = [d for d in yaml.safe_load_all(open(path)) if d]
+        assert docs, path
+        if os.path.basename(path) == "kustomization.yaml":
+            base = os.path.dirname(path)
+            for rel in (docs[0].get("resources") or []) + (docs[0].get("bases") or []) + \
+                    (docs[0].get("patchesStrategicMerge") or []):
+                assert os.path.exists(os.path.join(base, rel)), f"{path}: {rel} missing"
+    docs = [d for d in yaml.safe_load_all(open("config/manager/all_in_one.yaml")) if d]
+    allowed = set()
+    for d in docs:
+        if d["kind"] in ("ClusterRole", "Role"):
+            for rule in d["rules"]:
+                for g in rule["apiGroups"]:
+                    for r in rule["resources"]:
+                        allowed.add((g, r))
+    needed = {("", "pods"), ("", "services"), ("", "events"), ("coordination.k8s.io", "leases"),
+              ("scheduling.incubator.k8s.io", "podgroups")}
+    for info in SCHEME.workload_kinds():
+        needed |= {(info.group, info.plural), (info.group, info.plural + "/status")}
+    assert needed <= allowed, needed - allowed
+    (dep,) = [d for d in docs if d["kind"] == "Deployment"]
+    pod = dep["spec"]["template"]["spec"]
+    sa = [d for d in docs if d["kind"] == "ServiceAccount"][0]["metadata"]
+    assert pod["serviceAccountName"] == sa["name"] and dep["metadata"]["namespace"] == sa["namespace"]
+    args = pod["containers"][0]["args"]
+    from kubedl_b200.cmd.manager import build_parser
+    parsed = build_parser().parse_args(args)              # the Deployment's flags are flags we have
+    assert parsed.in_cluster and parsed.enable_leader_election and parsed.leader_election_namespace == sa["namespace"]
+    for b in [d for d in docs if d["kind"].endswith("Binding")]:
+        assert b["subjects"][0]["name"] == sa["name"]

@@ -48,4 +48,5 @@ def main(argv=None) -> int:
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    from kubedl_b200.worker.exitcodes import run
+    sys.exit(run(main))

@@ -415,4 +415,5 @@ def _device() -> torch.device:
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    from kubedl_b200.worker.exitcodes import run
+    sys.exit(run(main))

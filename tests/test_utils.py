@@ -123,3 +123,26 @@ def test_stem_weight_pad_unpad_roundtrip():
     assert torch.equal(K.stem_weight_unpad(wp).view(64, 7, 7, 3), w)
     # column of (kh, kw, c) is kh*24 + kw*3 + c
     assert float(wp[5, 2 * 24 + 4 * 3 + 1]) == float(w[5, 2, 4, 1])
+
+
+def test_worker_exit_code_classification():
+    """What a worker dies of decides whether restartPolicy ExitCode brings it back
+    (reference pkg/util/train/train_util.go:18-53)."""
+    from kubedl_b200.utils.train import is_retryable_exit_code
+    from kubedl_b200.worker.exitcodes import classify, run
+    retry = [RuntimeError("CUDA error: unspecified launch failure"), RuntimeError("NCCL error in: ... unhandled system error"),
+             ConnectionResetError("peer"), TimeoutError(), RuntimeError("Socket Timeout"),
+             RuntimeError("[c10d] the client socket has timed out after 600s while trying to connect to the store"),
+             RuntimeError("all-reduce watchdog: peer did not arrive"), KeyboardInterrupt(), MemoryError()]
+    for e in retry:
+        assert is_retryable_exit_code(classify(e)), e
+    perm = [ValueError("batch must be a multiple of 8"), ImportError("no module"), AssertionError("shape"),
+            RuntimeError("CUDA out of memory. Tried to allocate 2.00 GiB"), KeyError("RANK")]
+    for e in perm:
+        assert not is_retryable_exit_code(classify(e)), e
+    assert classify(SystemExit(0)) == 0 and classify(SystemExit(3)) == 3 and classify(SystemExit(None)) == 0
+    assert run(lambda: None) == 0 and run(lambda: 7) == 7
+
+    def boom():
+        raise RuntimeError("CUDA error: an illegal memory access was encountered")
+    assert run(boom) == 138

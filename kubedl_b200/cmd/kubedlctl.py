@@ -95,6 +95,28 @@ def print_table(kind: str, items: List[dict]) -> None:
         print("   ".join(x.ljust(w[i]) for i, x in enumerate(r)).rstrip())
 
 
+def _scale_to(job: dict, total: int) -> None:
+    """Shrink / grow a manifest to `total` pods: singleton types (Master, Chief, Scheduler...) keep
+    their one replica, the type with the most replicas absorbs the difference."""
+    specs = SCHEME.info(job["kind"]).replica_specs(job)
+    if not specs:
+        return
+    big = max(specs, key=lambda k: int(specs[k].get("replicas") or 1))
+    others = sum(int(v.get("replicas") or 1) for k, v in specs.items() if k != big)
+    specs[big]["replicas"] = max(total - others, 0 if others else 1)
+    if specs[big]["replicas"] == 0:
+        del specs[big]
+
+
+def _add_env(job: dict, kv: str) -> None:
+    name, _, value = kv.partition("=")
+    for spec in SCHEME.info(job["kind"]).replica_specs(job).values() if SCHEME.is_workload(job.get("kind", "")) else []:
+        for ctr in spec.get("template", {}).get("spec", {}).get("containers", []):
+            env = [e for e in ctr.get("env") or [] if e.get("name") != name]
+            env.append({"name": name, "value": value})
+            ctr["env"] = env
+
+
 def cmd_run(args) -> int:
     """Embedded cluster: apply, wait for every submitted job to reach a terminal condition."""
     from prometheus_client import CollectorRegistry
@@ -115,6 +137,10 @@ def cmd_run(args) -> int:
                     if not op.mgr.api.scheme.knows(d.get("kind", "")):
                         print(f"skipped {d.get('kind')}/{d.get('metadata', {}).get('name')} (not served on a single box)")
                         continue
+                    if args.replicas and SCHEME.is_workload(d.get("kind", "")):
+                        _scale_to(d, args.replicas)
+                    for kv in args.env or []:
+                        _add_env(d, kv)
                     o = op.mgr.api.apply(d)
                     print(f"{o['kind'].lower()}/{c.name_of(o)} applied")
                     if SCHEME.is_workload(o["kind"]):
@@ -135,6 +161,17 @@ def cmd_run(args) -> int:
             print(f"{kind.lower()}/{name}: {state}  replicaStatuses={json.dumps(status.get('replicaStatuses', {}))}")
             if state != c.JOB_SUCCEEDED:
                 rc = 1
+        if args.logs and op.gpulet is not None:
+            import glob
+            import os
+            for path in sorted(glob.glob(os.path.join(op.gpulet.log_dir, "*.log"))):
+                base = os.path.basename(path)[:-4]
+                if not any(base.startswith(f"{ns}_{name}-") for _, ns, name in jobs):
+                    continue
+                with open(path, errors="replace") as fh:
+                    tail = fh.read().splitlines()[-args.logs:]
+                for line in tail:
+                    print(f"[{base}] {line}")
         for kind, rec in op.reconcilers.items():
             for which, obs in rec.metrics.launch_delays.items():
                 for key, v in obs:
@@ -155,6 +192,9 @@ def main(argv=None) -> int:
     l = sub.add_parser("logs"); l.add_argument("pod"); l.add_argument("-n", "--namespace", default="default")
     x = sub.add_parser("run"); x.add_argument("-f", "--filename", required=True, action="append")
     x.add_argument("--gpus", type=int, default=None); x.add_argument("--timeout", type=float, default=600.0); x.add_argument("--gang", default="")
+    x.add_argument("--replicas", type=int, default=0, help="scale every job in the manifests to this many pods")
+    x.add_argument("--env", action="append", help="NAME=VALUE added to every container of every job")
+    x.add_argument("--logs", type=int, default=0, help="print the last N log lines of every pod at the end")
     args = ap.parse_args(argv)
     if args.cmd == "run":
         return cmd_run(args)

@@ -47,7 +47,7 @@ def main(argv=None) -> int:
             os._exit(args.fail_with)
         if args.checkpoint and rank == 0 and step % 5 == 4:
             torch.save({"model": model.state_dict(), "step": step + 1}, args.checkpoint)
-    print(f"rank {rank}/{world}: {args.steps - start_step} steps, loss {float(loss) if loss is not None else float('nan'):.4f}, "
+    print(f"rank {rank}/{world}: {args.steps - start_step} steps, loss {float(loss.detach()) if loss is not None else float('nan'):.4f}, "
           f"time-to-done {time.time() - t0:.2f}s", flush=True)
     if world > 1:
         dist.barrier()

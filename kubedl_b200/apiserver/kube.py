@@ -385,6 +385,25 @@ class _Reflector:
                 pass
 
 
+def _url_template(path: str) -> str:
+    """`/api/v1/namespaces/kubedl/pods/x-worker-0?y` -> `/api/v1/namespaces/{namespace}/pods/{name}`
+    (client-go labels request latency by URL template, not by object)."""
+    parts = path.split("?")[0].strip("/").split("/")
+    out, i = [], 0
+    head = 2 if parts and parts[0] == "api" else 3
+    out += parts[:head]
+    rest_ = parts[head:]
+    if len(rest_) >= 2 and rest_[0] == "namespaces" and len(rest_) > 2:
+        out += ["namespaces", "{namespace}"]
+        rest_ = rest_[2:]
+    if rest_:
+        out.append(rest_[0])
+        if len(rest_) > 1:
+            out.append("{name}")
+        out += rest_[2:]
+    return "/" + "/".join(out)
+
+
 class KubeAPIServer:
     """Drop-in for `store.APIServer` backed by a remote Kubernetes API server."""
 
@@ -399,6 +418,8 @@ class KubeAPIServer:
         self.discovery_ttl = 10.0
         self.request_log: List[Tuple[str, str, str]] = []
         self.remote = True
+        self.metrics = None      # plugins/controller_metrics.ControllerMetrics (rest_client_* series)
+        self._host = urllib.parse.urlsplit(config.server).netloc
 
     # ------------------------------------------------------------------ paths
     def _prefix(self, kind: str) -> Tuple[str, str]:
@@ -429,6 +450,7 @@ class KubeAPIServer:
             conn = getattr(self._local, "conn", None)
             if conn is None:
                 conn = self._local.conn = self.config.connect(self.request_timeout)
+            t0 = time.perf_counter()
             try:
                 conn.request(method, self.config.base_path + path, body=data, headers=headers)
                 resp = conn.getresponse()
@@ -440,6 +462,8 @@ class KubeAPIServer:
                 finally:
                     self._local.conn = None
                 continue
+            if self.metrics is not None:
+                self.metrics.observe_request(method, self._host, _url_template(path), resp.status, time.perf_counter() - t0)
             if resp.status >= 400:
                 raise error_from_status(resp.status, raw)
             if not raw:

@@ -57,7 +57,7 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
     """remote=True puts the API server behind HTTP (`apiserver/rest.py`) with the node agent next to
     it, and makes the operator a client of it (`apiserver/kube.py`) — the reference's deployment
     shape, where every pod / service create and every status write is a round trip."""
-    flags = ["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0", "--workloads", "*",
+    flags = ["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0", "--controller-metrics-addr", "0", "--workloads", "*",
              "--gpus", "0", "--max-reconciles", str(max_reconciles)]
     reg = CollectorRegistry()
     extra = []

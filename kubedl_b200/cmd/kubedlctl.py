@@ -122,7 +122,7 @@ def cmd_run(args) -> int:
     from prometheus_client import CollectorRegistry
     from . import manager as M
     margs = M.build_parser().parse_args(["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0",
-                                         "--workloads", "*"] + (["--gpus", str(args.gpus)] if args.gpus is not None else [])
+                                         "--controller-metrics-addr", "0", "--workloads", "*"] + (["--gpus", str(args.gpus)] if args.gpus is not None else [])
                                         + (["--gang-scheduler-name", args.gang] if args.gang else []))
     reg = CollectorRegistry()
     op = M.build_operator(margs, metrics_registry=reg)

@@ -29,7 +29,7 @@ from ..controllers import persist
 from ..controllers import registry as controller_registry
 from ..engine.job_controller import JobControllerConfiguration
 from ..node.gpulet import Gpulet
-from ..plugins import gang_schedule
+from ..plugins import controller_metrics, gang_schedule
 from ..plugins import metrics as metrics_mod
 from ..plugins.storage import backends as storage_backends
 from ..runtime.manager import Manager
@@ -117,6 +117,7 @@ def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None)
             api.install_crd(info.kind)
     mgr = Manager(api=api, leader_election=bool(args.enable_leader_election), leader_lock_path=args.leader_lock,
                   leader_election_namespace=getattr(args, "leader_election_namespace", "kubedl-system"))
+    mgr.set_controller_metrics(controller_metrics.ControllerMetrics())
     gang_schedule.register_gang_schedulers(mgr)
     recs = controller_registry.setup_with_manager(mgr, CTRL_CONFIG, args.workloads, metrics_registry)
     storage_backends.register_storage_backends()
@@ -144,6 +145,13 @@ def start_operator(op: Operator, args, metrics_registry=None) -> None:
             metrics_mod.start_monitoring(int(args.metrics_addr), registry=metrics_registry)
         except OSError as e:
             log.warning("metrics endpoint on %s unavailable: %s", args.metrics_addr, e)
+    if op.mgr.controller_metrics is not None:
+        try:
+            srv = controller_metrics.serve(op.mgr.controller_metrics, args.controller_metrics_addr)
+            if srv is not None:
+                op.servers.append(srv)
+        except OSError as e:
+            log.warning("controller metrics endpoint on %s unavailable: %s", args.controller_metrics_addr, e)
     op.mgr.start(block=False)
     if op.gpulet:
         op.gpulet.start()

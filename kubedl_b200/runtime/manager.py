@@ -288,6 +288,11 @@ class Controller:
                                "error": repr(err) if err else None})
             if len(self.trace) > 4096:
                 del self.trace[:2048]
+        cm = self.manager.controller_metrics
+        if cm is not None:
+            result = "error" if err is not None else "requeue_after" if res.requeue_after > 0 else \
+                "requeue" if res.requeue else "success"
+            cm.observe_reconcile(self.name, result, time.perf_counter() - t0)
         if err is not None:
             self.queue.add_rate_limited(req)
         elif res.requeue_after > 0:
@@ -466,7 +471,16 @@ class Manager:
         else:
             self.elector = LeaderElector(leader_lock_path)
         self.runnables: List[Callable[["Manager"], None]] = []   # started with the manager (gpulet, metrics...)
+        self.controller_metrics = None       # plugins/controller_metrics.ControllerMetrics (set_controller_metrics)
         self._started = False
+
+    def set_controller_metrics(self, cm) -> None:
+        """controller-runtime's registry: reconcile + workqueue + REST client instruments."""
+        self.controller_metrics = cm
+        for ctl in self.controllers:
+            ctl.queue.metrics = cm.for_queue(ctl.name)
+        if getattr(self.api, "remote", False):
+            self.api.metrics = cm
 
     def get_event_recorder_for(self, name: str) -> EventRecorder:
         if name not in self._recorders:
@@ -476,6 +490,8 @@ class Manager:
     def new_controller(self, name: str, reconciler: Callable[[Request], Result],
                        max_concurrent_reconciles: int = 1) -> Controller:
         ctl = Controller(name, reconciler, self, max_concurrent_reconciles)
+        if self.controller_metrics is not None:
+            ctl.queue.metrics = self.controller_metrics.for_queue(name)
         self.controllers.append(ctl)
         if self._started:
             ctl.start_watches()

@@ -50,6 +50,7 @@ class RateLimitingQueue:
         self._seq = 0
         self._shutdown = False
         self.adds = 0
+        self.metrics = None      # plugins/controller_metrics.QueueMetrics, attached by the manager
 
     # ---- plain queue
     def add(self, item) -> None:
@@ -58,6 +59,8 @@ class RateLimitingQueue:
                 return
             self.adds += 1
             self._dirty.add(item)
+            if self.metrics is not None:
+                self.metrics.add(item)
             if item in self._processing:
                 return  # re-queued when done() is called
             self._queue.append(item)
@@ -70,6 +73,8 @@ class RateLimitingQueue:
             _, _, item = heapq.heappop(self._waiting)
             if item not in self._dirty:
                 self._dirty.add(item)
+                if self.metrics is not None:
+                    self.metrics.add(item)
                 if item not in self._processing:
                     self._queue.append(item)
         return (self._waiting[0][0] - now) if self._waiting else None
@@ -84,6 +89,8 @@ class RateLimitingQueue:
                     item = self._queue.pop(0)
                     self._processing.add(item)
                     self._dirty.discard(item)
+                    if self.metrics is not None:
+                        self.metrics.get(item)
                     return item, False
                 if self._shutdown:
                     return None, True
@@ -99,6 +106,8 @@ class RateLimitingQueue:
     def done(self, item) -> None:
         with self._cv:
             self._processing.discard(item)
+            if self.metrics is not None:
+                self.metrics.done(item)
             if item in self._dirty:
                 self._queue.append(item)
                 self._cv.notify()
@@ -133,6 +142,8 @@ class RateLimitingQueue:
             self._cv.notify()
 
     def add_rate_limited(self, item) -> None:
+        if self.metrics is not None:
+            self.metrics.retry()
         self.add_after(item, self.limiter.when(item))
 
     def forget(self, item) -> None:

@@ -27,8 +27,8 @@ def test_flag_defaults_match_reference():
 def test_operator_wiring_and_kubedlctl(capsys, tmp_path):
     port = _free_port()
     args = manager.build_parser().parse_args(["--enable-leader-election=false", "--serve", f"127.0.0.1:{port}",
-                                              "--metrics-addr", "0", "--workloads", "*", "--no-node-agent",
-                                              "--max-reconciles", "0", "--gang-scheduler-name", "kube-batch",
+                                              "--metrics-addr", "0", "--controller-metrics-addr", "0",
+                                              "--workloads", "*", "--no-node-agent", "--max-reconciles", "0", "--gang-scheduler-name", "kube-batch",
                                               "--object-storage", "mysql", "--region", "box"])
     reg = CollectorRegistry()
     op = manager.build_operator(args, metrics_registry=reg)
@@ -78,3 +78,71 @@ def test_leader_election_is_exclusive(tmp_path):
     a.release()
     assert b.acquire(blocking=False) is True
     b.release()
+
+
+def test_controller_runtime_metrics_endpoint():
+    """`--controller-metrics-addr` serves what controller-runtime serves for the reference
+    (main.go:70-72): reconcile and work-queue series per controller, by the upstream names."""
+    import urllib.request
+    from kubedl_b200.api.kinds import new_job
+    from kubedl_b200.node.gpulet import FakeKubelet
+    from cp_helpers import tmpl
+    args = manager.build_parser().parse_args(["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0",
+                                              "--controller-metrics-addr", "127.0.0.1:0", "--workloads", "*", "--no-node-agent"])
+    op = manager.build_operator(args, metrics_registry=CollectorRegistry())
+    manager.start_operator(op, args)
+    try:
+        (srv,) = op.servers
+        url = "http://%s:%d/metrics" % srv.server_address[:2]
+        api = op.mgr.api
+        api.create(new_job("TFJob", "m", "ns", replica_specs={"Worker": {"replicas": 2, "template": tmpl("tensorflow")}}))
+        kubelet = FakeKubelet(api)
+        for _ in range(200):
+            if len(api.list("Pod", "ns")) == 2:
+                break
+            time.sleep(0.01)
+        kubelet.set_all("ns", "Running")
+        kubelet.set_all("ns", "Succeeded", exit_code=0)
+        for _ in range(300):
+            conds = [x["type"] for x in api.get("TFJob", "ns", "m").get("status", {}).get("conditions", [])]
+            if conds and conds[-1] == "Succeeded":
+                break
+            time.sleep(0.01)
+        assert conds[-1] == "Succeeded"
+        text = urllib.request.urlopen(url, timeout=5).read().decode()
+        samples = {}
+        for line in text.splitlines():
+            if line and not line.startswith("#"):
+                name, _, value = line.rpartition(" ")
+                samples[name] = float(value)
+        ok = samples['controller_runtime_reconcile_total{controller="TFJobController",result="success"}']
+        assert ok >= 3
+        assert samples['controller_runtime_reconcile_time_seconds_count{controller="TFJobController"}'] >= ok
+        assert samples['workqueue_adds_total{name="TFJobController"}'] >= ok
+        assert samples['workqueue_depth{name="TFJobController"}'] == 0
+        assert samples['workqueue_work_duration_seconds_count{name="TFJobController"}'] >= ok
+        assert samples['workqueue_queue_duration_seconds_count{name="TFJobController"}'] >= ok
+        assert 'workqueue_longest_running_processor_seconds{name="TFJobController"}' in samples
+        assert 'workqueue_depth{name="PytorchJobController"}' in samples       # every controller has its queue
+        # an error is counted as such and as a retry
+        from kubedl_b200.apiserver.store import Invalid
+        api.create(new_job("TFJob", "bad", "ns", replica_specs={"Worker": {"replicas": 1, "template": tmpl("tensorflow")}}))
+        time.sleep(0.1)
+        api.fail_next[("create", "Pod")] = Invalid("nope")
+        api.delete("Pod", "ns", "bad-worker-0")
+        for _ in range(300):
+            text = urllib.request.urlopen(url, timeout=5).read().decode()
+            if 'controller_runtime_reconcile_errors_total{controller="TFJobController"} 1.0' in text:
+                break
+            time.sleep(0.01)
+        assert 'controller_runtime_reconcile_errors_total{controller="TFJobController"} 1.0' in text
+        assert 'workqueue_retries_total{name="TFJobController"} 1.0' in text
+    finally:
+        op.stop()
+
+
+def test_bind_address_parsing():
+    from kubedl_b200.plugins.controller_metrics import parse_bind_address
+    assert parse_bind_address(":8080") == ("0.0.0.0", 8080)
+    assert parse_bind_address("127.0.0.1:9090") == ("127.0.0.1", 9090)
+    assert parse_bind_address("0") is None and parse_bind_address("") is None

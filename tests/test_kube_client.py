@@ -286,7 +286,7 @@ def test_operator_reconciles_through_the_wire():
     api = store.APIServer()
     srv = rest.serve(api, "127.0.0.1", 0)
     args = cmd.build_parser().parse_args(["--master", srv.url, "--workloads", "*", "--enable-leader-election=false",
-                                          "--metrics-addr", "0", "--serve", ""])
+                                          "--metrics-addr", "0", "--controller-metrics-addr", "0", "--serve", ""])
     reg = CollectorRegistry()
     op = cmd.build_operator(args, metrics_registry=reg)
     assert getattr(op.mgr.api, "remote", False) and op.gpulet is None
@@ -326,6 +326,12 @@ def test_operator_reconciles_through_the_wire():
         assert job["status"]["completionTime"]
         reasons = {e["reason"] for e in user.events_for(job)}
         assert {"SuccessfulCreatePod", "SuccessfulCreateService"} <= reasons
+        # client-go's rest_client_* series, by URL template rather than by object
+        reg_cm = op.mgr.controller_metrics.registry
+        assert reg_cm.get_sample_value("rest_client_requests_total", {
+            "code": "201", "method": "POST", "host": srv.url.split("//")[1]}) >= 4     # 3 pods + 1 service (+ events)
+        assert reg_cm.get_sample_value("rest_client_request_latency_seconds_count", {
+            "verb": "PUT", "url": "/apis/kubeflow.org/v1/namespaces/{namespace}/pytorchjobs/{name}/status"}) >= 3
         # deleting the job through the wire collects its pods and services on the server
         user.delete("PyTorchJob", "kubedl", "wire")
         wait_for(lambda: not api.list("Pod", "kubedl") and not api.list("Service", "kubedl"), what="garbage collection")
@@ -406,7 +412,8 @@ def test_three_processes_run_the_reference_example(tmp_path):
         spawn("apiserver", "--serve", url)
         cli = KubeAPIServer(KubeConfig.from_url(url))
         wait_for(cli.healthy, timeout=60, what="apiserver up")
-        spawn("manager", "--master", url, "--workloads", "*", "--metrics-addr", "0", "--leader-election-namespace", "kubedl")
+        spawn("manager", "--master", url, "--workloads", "*", "--metrics-addr", "0", "--controller-metrics-addr", "0",
+              "--leader-election-namespace", "kubedl")
         spawn("gpulet", "--master", url, "--gpus", "0", "--log-dir", str(tmp_path / "pods"))
         wait_for(lambda: cli.list("Lease", "kubedl"), timeout=60, what="operator elected")
         out = subprocess.run([sys.executable, "-m", "kubedl_b200.cmd.kubedlctl", "--server", url, "apply", "-f",

@@ -60,7 +60,7 @@ def main(argv=None) -> int:
             ids = torch.randint(0, 1000, (256,))
             loss = torch.nn.functional.binary_cross_entropy_with_logits(lin(emb(ids))[:, 0], (ids % 2).float())
             opt.zero_grad(); loss.backward(); opt.step()
-        loss = float(loss)
+        loss = float(loss.detach())
     print(json.dumps({"task": task, "index": index, "world": world, "steps": args.steps, "loss": loss,
                       "seconds": time.time() - t0, "zk_addr": zk}), flush=True)
     if world > 1:

@@ -448,17 +448,18 @@ class KubeAPIServer:
         last: Optional[Exception] = None
         for attempt in range(2):                 # a kept-alive connection may have been closed under us
             conn = getattr(self._local, "conn", None)
-            if conn is None:
-                conn = self._local.conn = self.config.connect(self.request_timeout)
             t0 = time.perf_counter()
             try:
+                if conn is None:
+                    conn = self._local.conn = self.config.connect(self.request_timeout)
                 conn.request(method, self.config.base_path + path, body=data, headers=headers)
                 resp = conn.getresponse()
                 raw = resp.read()
             except (http.client.HTTPException, ConnectionError, BrokenPipeError, TimeoutError, OSError) as e:
                 last = e
                 try:
-                    conn.close()
+                    if conn is not None:
+                        conn.close()
                 finally:
                     self._local.conn = None
                 continue
@@ -472,8 +473,7 @@ class KubeAPIServer:
                 return json.loads(raw)
             except ValueError:
                 return {"raw": raw.decode(errors="replace")}
-        err = st.Timeout(f"{method} {path}: {last!r}")
-        raise err
+        raise st.Timeout(f"{method} {path}: {last!r}")
 
     def _prepare(self, obj: dict) -> dict:
         kind = obj.get("kind")

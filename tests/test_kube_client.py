@@ -471,3 +471,42 @@ def test_install_crds_on_a_bare_server():
     finally:
         cli.close()
         srv.shutdown()
+
+
+def test_unreachable_server_is_an_api_timeout_not_a_crash():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()                                           # nothing listens here
+    cli = KubeAPIServer(KubeConfig.from_url(f"127.0.0.1:{port}"), request_timeout=1)
+    with pytest.raises(store.Timeout):
+        cli.get("Pod", "default", "x")
+    assert store.is_timeout(pytest.raises(store.Timeout, cli.list, "Pod").value)
+    assert not cli.healthy()
+    cli.close()
+
+
+def test_apiserver_snapshot_survives_a_restart(tmp_path):
+    """`cmd.apiserver --state`: uids, creation timestamps, status and owner links come back, so a
+    restarted operator picks its jobs up where they were and garbage collection still works."""
+    from kubedl_b200.cmd import apiserver as A
+    api = store.APIServer()
+    job = api.create(new_job("TFJob", "t", "ns", replica_specs={"Worker": {"replicas": 1, "template": tmpl("tensorflow")}}))
+    job["status"] = {"conditions": [{"type": "Created", "status": "True"}], "replicaStatuses": {}}
+    api.update_status(job)
+    p = pod("t-worker-0", ns="ns")
+    p["metadata"]["ownerReferences"] = [{"apiVersion": "kubeflow.org/v1", "kind": "TFJob", "name": "t",
+                                         "uid": job["metadata"]["uid"], "controller": True}]
+    api.create(p)
+    api.record_event(job, "Normal", "SuccessfulCreatePod", "x")
+    path = str(tmp_path / "state.json")
+    assert A.save_state(api, path) == 2                     # events are not part of the snapshot
+    fresh = store.APIServer()
+    assert A.load_state(fresh, path) == 2
+    j2 = fresh.get("TFJob", "ns", "t")
+    assert j2["metadata"]["uid"] == job["metadata"]["uid"]
+    assert j2["metadata"]["creationTimestamp"] == job["metadata"]["creationTimestamp"]
+    assert j2["status"]["conditions"][0]["type"] == "Created"
+    fresh.delete("TFJob", "ns", "t")
+    assert fresh.list("Pod", "ns") == []                    # the owner link still resolves

@@ -88,7 +88,9 @@ class Route:
 
 
 def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]] = None,
-                 stopping: Optional[threading.Event] = None):
+                 stopping: Optional[threading.Event] = None, latency: float = 0.0):
+    """latency: seconds added to every non-watch request — a stand-in for the network round trip
+    and etcd commit of a real API server when measuring what the operator's request pattern costs."""
     resources = _resource_map(api.scheme)
     stopping = stopping or threading.Event()
 
@@ -166,6 +168,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
 
         # ------------------------------------------------------------ plumbing
         def _send(self, code: int, body) -> None:
+            if latency > 0:
+                time.sleep(latency)
             data = body if isinstance(body, bytes) else json.dumps(body).encode()
             self.send_response(code)
             self.send_header("Content-Type", "application/json" if not isinstance(body, bytes) else "text/plain")
@@ -406,9 +410,9 @@ class RestServer(ThreadingHTTPServer):
     daemon_threads = True
     allow_reuse_address = True
 
-    def __init__(self, addr, api: APIServer, log_reader=None):
+    def __init__(self, addr, api: APIServer, log_reader=None, latency: float = 0.0):
         self.stopping = threading.Event()
-        super().__init__(addr, make_handler(api, log_reader, self.stopping))
+        super().__init__(addr, make_handler(api, log_reader, self.stopping, latency))
 
     @property
     def url(self) -> str:
@@ -421,7 +425,7 @@ class RestServer(ThreadingHTTPServer):
         self.server_close()
 
 
-def serve(api: APIServer, host: str = "127.0.0.1", port: int = 8001, log_reader=None) -> RestServer:
-    srv = RestServer((host, port), api, log_reader)
+def serve(api: APIServer, host: str = "127.0.0.1", port: int = 8001, log_reader=None, latency: float = 0.0) -> RestServer:
+    srv = RestServer((host, port), api, log_reader, latency)
     threading.Thread(target=srv.serve_forever, name="kubedl-rest", daemon=True).start()
     return srv

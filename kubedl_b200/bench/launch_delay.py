@@ -53,12 +53,13 @@ def _job(kind: str, name: str, replicas: int, seconds: float) -> dict:
                      cleanPodPolicy="All")
 
 
-def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1, remote: bool = False) -> dict:
+def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1, remote: bool = False,
+        create_parallelism: int = 1, api_latency: float = 0.0) -> dict:
     """remote=True puts the API server behind HTTP (`apiserver/rest.py`) with the node agent next to
     it, and makes the operator a client of it (`apiserver/kube.py`) — the reference's deployment
     shape, where every pod / service create and every status write is a round trip."""
     flags = ["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0", "--controller-metrics-addr", "0", "--workloads", "*",
-             "--gpus", "0", "--max-reconciles", str(max_reconciles)]
+             "--gpus", "0", "--max-reconciles", str(max_reconciles), "--pod-create-parallelism", str(create_parallelism)]
     reg = CollectorRegistry()
     extra = []
     if remote:
@@ -66,7 +67,7 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
         from ..apiserver.store import APIServer
         from ..node.gpulet import Gpulet
         backing = APIServer()
-        srv = rest.serve(backing, "127.0.0.1", 0)
+        srv = rest.serve(backing, "127.0.0.1", 0, latency=api_latency)
         let = Gpulet(backing, num_gpus=0)
         let.start()
         extra = [let.stop, srv.shutdown]
@@ -99,7 +100,8 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
                 "first_pod_ms": {"p50": 1e3 * _pct(first, 0.5), "p90": 1e3 * _pct(first, 0.9), "n": len(first)},
                 "all_pods_ms": {"p50": 1e3 * _pct(allp, 0.5), "p90": 1e3 * _pct(allp, 0.9), "n": len(allp)},
                 "time_to_succeeded_ms": {"p50": 1e3 * _pct(done_times, 0.5), "p90": 1e3 * _pct(done_times, 0.9)},
-                "api_creates_per_job": creates / jobs, "api": "http" if remote else "in-process"}
+                "api_creates_per_job": creates / jobs, "api": "http" if remote else "in-process",
+                "pod_create_parallelism": create_parallelism, "api_latency_ms": 1e3 * api_latency}
     finally:
         op.stop()
         for fn in extra:
@@ -114,9 +116,12 @@ def main(argv=None) -> int:
     ap.add_argument("--kinds", default="PyTorchJob,TFJob,XGBoostJob,XDLJob")
     ap.add_argument("--remote", action="store_true", help="operator talks to the API server over HTTP")
     ap.add_argument("--max-reconciles", type=int, default=1)
+    ap.add_argument("--create-parallelism", type=int, default=1)
+    ap.add_argument("--api-latency-ms", type=float, default=0.0, help="with --remote: added to every API request")
     a = ap.parse_args(argv)
     for kind in a.kinds.split(","):
-        print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds, a.max_reconciles, a.remote)), flush=True)
+        print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds, a.max_reconciles, a.remote, a.create_parallelism,
+                             a.api_latency_ms / 1e3)), flush=True)
     return 0
 
 

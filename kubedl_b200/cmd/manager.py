@@ -72,6 +72,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--in-cluster", action="store_true", help="use $KUBECONFIG or the pod's service account")
     ap.add_argument("--leader-election-namespace", default="kubedl-system")
     ap.add_argument("--install-crds", action="store_true", help="create missing CRDs on the remote API server at start")
+    ap.add_argument("--pod-create-parallelism", type=int, default=1,
+                    help="pods of one replica type created concurrently in slow-start batches (1 = serial, as the reference)")
     return ap
 
 
@@ -105,6 +107,7 @@ def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None)
     if args.max_reconciles <= 0:
         args.max_reconciles = 1
     CTRL_CONFIG.max_concurrent_reconciles = args.max_reconciles
+    CTRL_CONFIG.pod_create_parallelism = max(1, int(getattr(args, "pod_create_parallelism", 1) or 1))
     if args.gang_scheduler_name:
         CTRL_CONFIG.enable_gang_scheduling = True
         CTRL_CONFIG.gang_scheduler_name = args.gang_scheduler_name

@@ -41,6 +41,10 @@ class JobControllerConfiguration:
     max_concurrent_reconciles: int = 1
     reconciler_sync_loop_period: float = 15.0   # declared but unused upstream too
     gang_scheduler_name: str = ""
+    # pods of one replica type created concurrently, in slow-start batches (1, 2, 4, ...) as the
+    # Kubernetes Job controller does; 1 = one at a time in index order like the reference
+    # (pod.go:235-281), which costs one API round trip per replica before the last pod exists
+    pod_create_parallelism: int = 1
 
 
 def gen_general_name(job_name: str, rtype: str, index: str) -> str:
@@ -394,21 +398,32 @@ class JobController:
         pods = self.filter_pods_for_replica_type(pods, rt)
         num = c.replicas_of(spec)
         initialize_replica_statuses(job_status, rtype)
-        for index, pod_slice in enumerate(self.get_pod_slices(pods, num, log)):
+        slices = self.get_pod_slices(pods, num, log)
+
+        def create(index: int) -> None:
+            master = self.controller.is_master_role(replicas, rtype, index)
+            try:
+                self.create_new_pod(job, rt, str(index), spec, master, replicas)
+            except Exception as e:
+                if is_already_exists(e):
+                    # the cache missed an earlier create: observe it ourselves so the queue
+                    # does not stall on the expectation (reference pod.go:265-278)
+                    # (create_new_pod has taken the failed create out of the pod count already)
+                    key = c.key_of(job)
+                    self.expectations.creation_observed(gen_expectation_services_key(key, rt))
+                raise
+
+        missing = [i for i, sl in enumerate(slices) if len(sl) == 0]
+        parallel = max(1, int(getattr(self.config, "pod_create_parallelism", 1) or 1))
+        batched = parallel > 1 and len(missing) > 1
+        if batched:
+            self._create_in_batches(missing, create, parallel)
+        for index, pod_slice in enumerate(slices):
             if len(pod_slice) > 1:
                 log.warning("We have too many pods for %s %d", rt, index)
             elif len(pod_slice) == 0:
-                master = self.controller.is_master_role(replicas, rtype, index)
-                try:
-                    self.create_new_pod(job, rt, str(index), spec, master, replicas)
-                except Exception as e:
-                    if is_already_exists(e):
-                        # the cache missed an earlier create: observe it ourselves so the queue
-                        # does not stall on the expectation (reference pod.go:265-278)
-                        # (create_new_pod has taken the failed create out of the pod count already)
-                        key = c.key_of(job)
-                        self.expectations.creation_observed(gen_expectation_services_key(key, rt))
-                    raise
+                if not batched:
+                    create(index)
             else:
                 pod = pod_slice[0]
                 exit_code = 0xBEEF
@@ -425,6 +440,23 @@ class JobController:
                         self.controller.delete_pod(job, pod)
                         restart[0] = True
                 update_job_replica_statuses(job_status, rtype, pod)
+
+    @staticmethod
+    def _create_in_batches(indices: List[int], create, parallel: int) -> None:
+        """Slow start: 1, 2, 4, ... creates at a time (capped at `parallel`); a failing batch stops
+        the ramp — when the API server rejects pods, the rest would be rejected too — and the
+        first error is raised once the batch has finished."""
+        from concurrent.futures import ThreadPoolExecutor
+        todo = list(indices)
+        size = 1
+        with ThreadPoolExecutor(max_workers=parallel, thread_name_prefix="pod-create") as pool:
+            while todo:
+                batch, todo = todo[:size], todo[size:]
+                errors = [f.exception() for f in [pool.submit(create, i) for i in batch]]
+                errors = [e for e in errors if e is not None]
+                if errors:
+                    raise errors[0]
+                size = min(size * 2, parallel)
 
     def create_new_pod(self, job: dict, rt: str, index: str, spec: dict, master_role: bool,
                        replicas: Dict[str, dict]) -> None:

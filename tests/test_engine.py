@@ -348,3 +348,38 @@ def test_template_restart_policy_warning():
     cl.submit(k.new_job("TFJob", "tf", "ns", {"Worker": {"replicas": 1, "restartPolicy": "Never", "template": t}}))
     assert "SettedPodTemplateRestartPolicy" in cl.recs["TFJob"].recorder.reasons()
     assert cl.pods("ns")[0]["spec"]["restartPolicy"] == "Never"
+
+
+def test_parallel_pod_creation_slow_start():
+    """`--pod-create-parallelism`: same pods, same expectations, created in batches 1, 2, 4, 4...;
+    a rejected create stops the ramp and surfaces as the reconcile error."""
+    cl = Cluster()
+    r = cl.recs["TFJob"]
+    r.ctrl.config.pod_create_parallelism = 4
+    try:
+        batches, lock = [], __import__("threading").Lock()
+        real = r.ctrl.create_new_pod
+
+        def spy(job, rt, index, *a, **kw):
+            with lock:
+                batches.append(int(index))
+            return real(job, rt, index, *a, **kw)
+        r.ctrl.create_new_pod = spy
+        cl.submit(_tfjob(workers=11))
+        assert sorted(c.name_of(p) for p in cl.pods("ns")) == sorted(f"tf-worker-{i}" for i in range(11))
+        assert sorted(batches) == list(range(11))
+        assert batches[0] == 0 and set(batches[1:3]) == {1, 2} and set(batches[3:7]) == {3, 4, 5, 6}   # 1, 2, 4, 4
+        assert r.ctrl.expectations.satisfied_expectations(gen_expectation_pods_key("ns/tf", "worker"))
+        cl.kubelet.set_all("ns", "Running")
+        cl.settle()
+        assert cl.job("TFJob", "ns", "tf")["status"]["replicaStatuses"]["Worker"]["active"] == 11
+        # failure in the second batch: nothing beyond that batch is attempted in this pass
+        del batches[:]
+        cl.api.create(_tfjob(name="tf2", workers=8))
+        cl.api.fail_next[("create", "Pod")] = RuntimeError("quota exceeded")
+        cl.settle()
+        assert r.controller.error_count == 1
+        cl.mgr.run_until_idle(advance_delayed=True)
+        assert len([p for p in cl.pods("ns") if c.name_of(p).startswith("tf2-")]) == 8
+    finally:
+        r.ctrl.config.pod_create_parallelism = 1

@@ -27,11 +27,13 @@ def main(argv=None) -> int:
     ap.add_argument("--gpus", type=int, default=None, help="GPUs to hand out (default: all visible)")
     ap.add_argument("--node-name", default="b200-node-0")
     ap.add_argument("--log-dir", default="/tmp/kubedl-b200/pods")
+    ap.add_argument("--prefork-workers", action="store_true", help="fork pods from a launcher that has torch imported")
     args = ap.parse_args(argv)
     from .manager import low_latency_threads
     low_latency_threads()
     api = KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context))
-    let = Gpulet(api, num_gpus=args.gpus, node_name=args.node_name, log_dir=args.log_dir)
+    let = Gpulet(api, num_gpus=args.gpus, node_name=args.node_name, log_dir=args.log_dir,
+                 prefork=True if args.prefork_workers else None)
     let.start()
     print(f"kubedl-b200 gpulet {args.node_name}: {let.num_gpus} GPUs, API {api.config.server}", flush=True)
     stop = threading.Event()

@@ -62,6 +62,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--serve", default="127.0.0.1:8001", help="REST façade address for kubedlctl ('' disables)")
     ap.add_argument("--gpus", type=int, default=None, help="GPUs managed by the node agent (default: all visible)")
     ap.add_argument("--no-node-agent", action="store_true", help="control plane only (pods are never started)")
+    ap.add_argument("--prefork-workers", action="store_true",
+                    help="node agent forks `python -m module` pods from a launcher that has torch imported")
     ap.add_argument("--leader-lock", default="/tmp/kubedl-b200-leader.lock")
     # against a cluster
     ap.add_argument("--master", default="", help="URL of a Kubernetes API server to reconcile against "
@@ -126,7 +128,8 @@ def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None)
     storage_backends.register_storage_backends()
     pers = persist.setup_with_manager(mgr, args.object_storage, args.event_storage, args.region, args.workloads)
     # against a cluster the pods belong to its kubelets (or to a separate gpulet process)
-    let = None if (args.no_node_agent or remote) else Gpulet(mgr.api, num_gpus=args.gpus)
+    let = None if (args.no_node_agent or remote) else Gpulet(mgr.api, num_gpus=args.gpus,
+                                                                  prefork=True if getattr(args, "prefork_workers", False) else None)
     return Operator(mgr, recs, pers, let)
 
 

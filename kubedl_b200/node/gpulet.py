@@ -124,7 +124,7 @@ class _Proc:
 class Gpulet:
     def __init__(self, api: APIServer, num_gpus: Optional[int] = None, registry: Optional[ImageRegistry] = None,
                  log_dir: str = "/tmp/kubedl-b200/pods", node_name: str = "b200-node-0",
-                 default_gpu_per_pod: bool = False):
+                 default_gpu_per_pod: bool = False, prefork: Optional[bool] = None):
         self.api = api
         self.registry = registry or ImageRegistry()
         if num_gpus is None:
@@ -149,9 +149,30 @@ class Gpulet:
         self._unwatch: List[Callable[[], None]] = []
         self._pool = ThreadPoolExecutor(max_workers=16, thread_name_prefix="gpulet-pod")
         self.launched = 0
+        # pre-forked workers (node/zygote.py): pods fork from a process that has imported torch
+        if prefork is None:
+            prefork = os.environ.get("KUBEDL_GPULET_PREFORK", "0") == "1"
+        self.zygote = None
+        if prefork:
+            from .zygote import ZygoteClient
+            self.zygote = ZygoteClient()
 
     # ------------------------------------------------------------------ lifecycle
+    def _spawn(self, argv: List[str], env: Dict[str, str], log_path: str, cwd: Optional[str]):
+        """Fork from the zygote when it is ready and the command is `python -m module`, else exec."""
+        if self.zygote is not None:
+            child = self.zygote.spawn(argv, env, log_path, cwd)
+            if child is not None:
+                return child
+        lf = open(log_path, "ab")
+        try:
+            return subprocess.Popen(argv, env=env, stdout=lf, stderr=subprocess.STDOUT, cwd=cwd, start_new_session=True)
+        finally:
+            lf.close()
+
     def start(self) -> None:
+        if self.zygote is not None:
+            self.zygote.start()
         self._unwatch.append(self.api.watch("Pod", self._on_pod, replay=True))
         self._unwatch.append(self.api.watch("PodGroup", lambda *a: self._kick(), replay=False))
         t = threading.Thread(target=self._loop, name="gpulet", daemon=True)
@@ -167,6 +188,8 @@ class Gpulet:
         for p in procs:
             self._kill(p)
         self._pool.shutdown(wait=False)
+        if self.zygote is not None:
+            self.zygote.stop()
 
     def _kick(self) -> None:
         pass  # the loop polls; the hook exists so watches wake it in future revisions
@@ -341,10 +364,7 @@ class Gpulet:
         env = self.build_env(pod, ctr, gpu)
         argv = self.registry.resolve(ctr, env)
         log_path = os.path.join(self.log_dir, f"{key[0]}_{key[1]}.log")
-        lf = open(log_path, "ab")
-        popen = subprocess.Popen(argv, env=env, stdout=lf, stderr=subprocess.STDOUT,
-                                 cwd=ctr.get("workingDir") or None, start_new_session=True)
-        lf.close()
+        popen = self._spawn(argv, env, log_path, ctr.get("workingDir") or None)
         proc = _Proc(key, ctr.get("name", ""), popen, gpu, started_at=c.now_precise(), log_path=log_path)
         with self._lock:
             self._procs[key] = proc
@@ -433,9 +453,7 @@ class Gpulet:
         ctr = (pod.get("spec", {}).get("containers") or [{}])[0]
         env = self.build_env(pod, ctr, proc.gpu)
         argv = self.registry.resolve(ctr, env)
-        lf = open(proc.log_path, "ab")
-        proc.popen = subprocess.Popen(argv, env=env, stdout=lf, stderr=subprocess.STDOUT, start_new_session=True)
-        lf.close()
+        proc.popen = self._spawn(argv, env, proc.log_path, ctr.get("workingDir") or None)
         proc.restart_count += 1
         proc.started_at = c.now_precise()
         conds = (pod.get("status") or {}).get("conditions")

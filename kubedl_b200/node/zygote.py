@@ -1,0 +1,366 @@
+"""Pre-forked worker launcher for the node agent.
+
+A pod on this node agent is a Python worker process, and most of what separates "pod Running"
+from "first training step" is `import torch` (4–5 s warm, tens of seconds when eight ranks page
+the libraries in at once on a fresh box; `profiles/examples_through_operator_8gpu.log`: 23 s to the
+first step).  The zygote is one long-lived process that has already paid for those imports and
+has NOT touched CUDA; every pod whose command is `python -m <module> ...` is then an `os.fork()`
+of it — copy-on-write pages, no interpreter start, no import — with the pod's own environment
+(`CUDA_VISIBLE_DEVICES`, rendezvous variables) installed before the module runs, so CUDA
+initialises in the child exactly as in a fresh process.  The same trick as Android's zygote and
+as torch's own fork-based DataLoader workers.
+
+Protocol, JSON lines over a UNIX stream socket (one persistent connection from the node agent):
+    -> {"op": "spawn", "id": 7, "argv": ["-m", "pkg.mod", "--flag"], "env": {...}, "log": "/path", "cwd": null}
+    <- {"id": 7, "pid": 4242}
+    <- {"exit": 4242, "status": 0}            (later, unsolicited; negative = killed by that signal)
+    -> {"op": "ping"}   <- {"pong": true, "preloaded": ["torch", ...]}
+Children are session leaders (`os.setsid`), so the agent can signal their whole process group.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import runpy
+import selectors
+import signal
+import socket
+import subprocess
+import sys
+import threading
+import time
+import traceback
+from typing import Dict, List, Optional
+
+DEFAULT_PRELOAD = ("torch", "torch.distributed", "numpy", "kubedl_b200.worker.rendezvous")
+
+
+# ------------------------------------------------------------------------------ server side
+def _run_child(req: dict, close_fds: List[int]) -> None:
+    """In the forked child: become the pod's process.  Never returns."""
+    code = 1
+    try:
+        for fd in close_fds:
+            try:
+                os.close(fd)
+            except OSError:
+                pass
+        for sig in (signal.SIGINT, signal.SIGTERM, signal.SIGCHLD, signal.SIGPIPE):
+            signal.signal(sig, signal.SIG_DFL)
+        os.setsid()
+        # fork happened with INT / TERM blocked: one that arrived meanwhile is delivered now, to the
+        # default action, instead of to the launcher's handler inherited for a few microseconds
+        signal.pthread_sigmask(signal.SIG_UNBLOCK, {signal.SIGINT, signal.SIGTERM})
+        log_fd = os.open(req["log"], os.O_WRONLY | os.O_CREAT | os.O_APPEND, 0o644)
+        null_fd = os.open(os.devnull, os.O_RDONLY)
+        os.dup2(null_fd, 0)
+        os.dup2(log_fd, 1)
+        os.dup2(log_fd, 2)
+        os.close(log_fd)
+        os.close(null_fd)
+        sys.stdin = open(0, "r", closefd=False)
+        sys.stdout = open(1, "w", buffering=1, closefd=False)       # line-buffered, like PYTHONUNBUFFERED logs
+        sys.stderr = open(2, "w", buffering=1, closefd=False)
+        os.environ.clear()
+        os.environ.update(req.get("env") or {})
+        for p in reversed([q for q in os.environ.get("PYTHONPATH", "").split(os.pathsep) if q]):
+            if p not in sys.path:
+                sys.path.insert(0, p)
+        if req.get("cwd"):
+            os.chdir(req["cwd"])
+        argv = list(req["argv"])
+        assert argv[0] == "-m" and len(argv) >= 2, argv
+        module, args = argv[1], argv[2:]
+        sys.argv = [module] + args
+        try:
+            runpy.run_module(module, run_name="__main__", alter_sys=True)
+            code = 0
+        except SystemExit as e:
+            code = e.code if isinstance(e.code, int) else (0 if e.code is None else 1)
+        except BaseException:
+            traceback.print_exc()
+            code = 1
+    except BaseException:
+        try:
+            traceback.print_exc()
+        except Exception:
+            pass
+        code = 1
+    finally:
+        try:
+            sys.stdout.flush()
+            sys.stderr.flush()
+        except Exception:
+            pass
+        os._exit(code & 0xFF)
+
+
+def serve(sock_path: str, preload=DEFAULT_PRELOAD) -> int:
+    loaded = []
+    for name in preload:
+        try:
+            importlib.import_module(name)
+            loaded.append(name)
+        except Exception as e:      # a missing optional module must not take the launcher down
+            print(f"zygote: preload of {name} failed: {e}", file=sys.stderr, flush=True)
+    if "torch" in sys.modules and sys.modules["torch"].cuda.is_initialized():
+        print("zygote: CUDA got initialised during preload; forked workers would not be able to use it",
+              file=sys.stderr, flush=True)
+        return 3
+    try:
+        os.unlink(sock_path)
+    except FileNotFoundError:
+        pass
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(sock_path)
+    os.chmod(sock_path, 0o600)
+    srv.listen(4)
+    sel = selectors.DefaultSelector()
+    sel.register(srv, selectors.EVENT_READ)
+    conns: Dict[socket.socket, bytearray] = {}
+    owner: Dict[int, socket.socket] = {}           # child pid -> connection that asked for it
+    stopping = []
+    signal.signal(signal.SIGTERM, lambda *_: stopping.append(1))
+    signal.signal(signal.SIGINT, lambda *_: stopping.append(1))
+    print(f"zygote ready on {sock_path} (preloaded: {', '.join(loaded)})", flush=True)
+
+    def send(conn: socket.socket, msg: dict) -> None:
+        try:
+            conn.sendall(json.dumps(msg).encode() + b"\n")
+        except OSError:
+            pass
+
+    def handle(conn: socket.socket, req: dict) -> None:
+        if req.get("op") == "ping":
+            return send(conn, {"pong": True, "preloaded": loaded, "pid": os.getpid()})
+        if req.get("op") == "spawn":
+            fds = [srv.fileno(), sel.fileno()] + [c.fileno() for c in conns]
+            signal.pthread_sigmask(signal.SIG_BLOCK, {signal.SIGINT, signal.SIGTERM})
+            try:
+                pid = os.fork()
+                if pid == 0:
+                    _run_child(req, fds)           # never returns
+            finally:
+                signal.pthread_sigmask(signal.SIG_UNBLOCK, {signal.SIGINT, signal.SIGTERM})
+            owner[pid] = conn
+            return send(conn, {"id": req.get("id"), "pid": pid})
+        send(conn, {"id": req.get("id"), "error": f"unknown op {req.get('op')!r}"})
+
+    while not stopping:
+        for key, _ in sel.select(timeout=0.05):
+            if key.fileobj is srv:
+                conn, _ = srv.accept()
+                conns[conn] = bytearray()
+                sel.register(conn, selectors.EVENT_READ)
+                continue
+            conn = key.fileobj
+            try:
+                data = conn.recv(65536)
+            except OSError:
+                data = b""
+            if not data:
+                sel.unregister(conn)
+                conns.pop(conn, None)
+                conn.close()
+                continue
+            buf = conns[conn]
+            buf += data
+            while b"\n" in buf:
+                line, _, rest = bytes(buf).partition(b"\n")
+                buf[:] = rest
+                if line.strip():
+                    try:
+                        handle(conn, json.loads(line))
+                    except Exception as e:
+                        send(conn, {"error": repr(e)})
+        while True:                                   # reap
+            try:
+                pid, status = os.waitpid(-1, os.WNOHANG)
+            except ChildProcessError:
+                break
+            if pid == 0:
+                break
+            rc = -os.WTERMSIG(status) if os.WIFSIGNALED(status) else os.WEXITSTATUS(status)
+            conn = owner.pop(pid, None)
+            if conn is not None and conn in conns:
+                send(conn, {"exit": pid, "status": rc})
+    for pid in list(owner):                           # going down: take the pods along
+        try:
+            os.killpg(pid, signal.SIGTERM)
+        except OSError:
+            pass
+    srv.close()
+    try:
+        os.unlink(sock_path)
+    except OSError:
+        pass
+    return 0
+
+
+# ------------------------------------------------------------------------------ client side
+class ZygoteProc:
+    """What the node agent needs of a `subprocess.Popen`: pid, poll(), returncode, wait()."""
+
+    def __init__(self, pid: int):
+        self.pid = pid
+        self.returncode: Optional[int] = None
+        self._done = threading.Event()
+
+    def _finish(self, status: int) -> None:
+        self.returncode = status
+        self._done.set()
+
+    def poll(self) -> Optional[int]:
+        return self.returncode
+
+    def wait(self, timeout: Optional[float] = None) -> Optional[int]:
+        self._done.wait(timeout)
+        return self.returncode
+
+
+class ZygoteClient:
+    """Starts the zygote in the background and forks workers from it once it is ready; until then
+    (and for commands that are not `python -m module`) the caller falls back to a plain exec."""
+
+    def __init__(self, sock_path: Optional[str] = None, preload=DEFAULT_PRELOAD, env: Optional[dict] = None):
+        self.sock_path = sock_path or f"/tmp/kubedl-b200-zygote-{os.getpid()}-{id(self) & 0xFFFF:x}.sock"
+        self.preload = tuple(preload)
+        self.ready = threading.Event()
+        self.failed = threading.Event()
+        self._env = env
+        self._proc: Optional[subprocess.Popen] = None
+        self._sock: Optional[socket.socket] = None
+        self._lock = threading.Lock()
+        self._next_id = 0
+        self._pending: Dict[int, dict] = {}
+        self._replies: Dict[int, threading.Event] = {}
+        self._children: Dict[int, ZygoteProc] = {}
+        self._early_exits: Dict[int, int] = {}
+        self.spawned = 0
+
+    def start(self) -> None:
+        env = dict(self._env if self._env is not None else os.environ)
+        env["PYTHONPATH"] = os.pathsep.join(filter(None, [os.getcwd(), env.get("PYTHONPATH", "")]))
+        env.pop("CUDA_VISIBLE_DEVICES", None)
+        self._proc = subprocess.Popen([sys.executable, "-m", "kubedl_b200.node.zygote", "--socket", self.sock_path,
+                                       "--preload", ",".join(self.preload)],
+                                      env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, start_new_session=True)
+        threading.Thread(target=self._connect, name="zygote-connect", daemon=True).start()
+
+    def _connect(self) -> None:
+        deadline = time.monotonic() + 300
+        while time.monotonic() < deadline:
+            if self._proc is None or self._proc.poll() is not None:
+                break
+            try:
+                s = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                s.connect(self.sock_path)
+                self._sock = s
+                threading.Thread(target=self._reader, name="zygote-reader", daemon=True).start()
+                self.ready.set()
+                return
+            except OSError:
+                time.sleep(0.05)
+        self.failed.set()
+
+    def _reader(self) -> None:
+        buf = bytearray()
+        sock = self._sock
+        try:
+            while True:
+                data = sock.recv(65536)
+                if not data:
+                    break
+                buf += data
+                while b"\n" in buf:
+                    line, _, rest = bytes(buf).partition(b"\n")
+                    buf[:] = rest
+                    msg = json.loads(line)
+                    if "exit" in msg:
+                        with self._lock:
+                            child = self._children.pop(msg["exit"], None)
+                            if child is None:
+                                self._early_exits[msg["exit"]] = msg["status"]
+                        if child is not None:
+                            child._finish(msg["status"])
+                    elif "id" in msg:
+                        with self._lock:
+                            self._pending[msg["id"]] = msg
+                            ev = self._replies.get(msg["id"])
+                        if ev is not None:
+                            ev.set()
+        except (OSError, ValueError):
+            pass
+        # the zygote is gone: whatever it was parenting is gone or orphaned — report it as killed
+        self.ready.clear()
+        self.failed.set()
+        with self._lock:
+            children, self._children = list(self._children.values()), {}
+        for ch in children:
+            ch._finish(-signal.SIGKILL)
+
+    @staticmethod
+    def eligible(argv: List[str]) -> bool:
+        return len(argv) >= 3 and argv[0] == sys.executable and argv[1] == "-m"
+
+    def spawn(self, argv: List[str], env: Dict[str, str], log_path: str, cwd: Optional[str] = None,
+              timeout: float = 10.0) -> Optional[ZygoteProc]:
+        """Fork a worker; None when the zygote is not (yet) usable or the command is not a module run."""
+        if not self.ready.is_set() or not self.eligible(argv):
+            return None
+        with self._lock:
+            self._next_id += 1
+            rid = self._next_id
+            ev = self._replies[rid] = threading.Event()
+            try:
+                self._sock.sendall(json.dumps({"op": "spawn", "id": rid, "argv": argv[1:], "env": env,
+                                               "log": log_path, "cwd": cwd}).encode() + b"\n")
+            except OSError:
+                self._replies.pop(rid, None)
+                return None
+        if not ev.wait(timeout):
+            return None
+        with self._lock:
+            msg = self._pending.pop(rid, {})
+            self._replies.pop(rid, None)
+            pid = msg.get("pid")
+            if pid is None:
+                return None
+            child = ZygoteProc(pid)
+            if pid in self._early_exits:
+                child._finish(self._early_exits.pop(pid))
+            else:
+                self._children[pid] = child
+            self.spawned += 1
+        return child
+
+    def stop(self) -> None:
+        if self._sock is not None:
+            try:
+                self._sock.close()
+            except OSError:
+                pass
+        if self._proc is not None and self._proc.poll() is None:
+            self._proc.terminate()        # the exact process we started
+            try:
+                self._proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self._proc.kill()
+        try:
+            os.unlink(self.sock_path)
+        except OSError:
+            pass
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="kubedl-zygote")
+    ap.add_argument("--socket", required=True)
+    ap.add_argument("--preload", default=",".join(DEFAULT_PRELOAD))
+    a = ap.parse_args(argv)
+    return serve(a.socket, tuple(p for p in a.preload.split(",") if p))
+
+
+if __name__ == "__main__":
+    sys.exit(main())

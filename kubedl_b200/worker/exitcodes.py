@@ -22,7 +22,8 @@ _RETRYABLE_MARKERS = (
     "cuda error", "unspecified launch failure", "device-side assert", "an illegal memory access",
     "cudaerrorlaunchfailure", "cudaerrorecc", "watchdog",
     "nccl", "communicator was aborted", "collective operation timeout",
-    "connection reset", "connection refused", "broken pipe", "socket timeout", "timed out",
+    "connection reset", "connection refused", "connection closed", "closed by peer", "broken pipe",
+    "socket timeout", "timed out",
     "tcpstore", "the store", "rendezvous", "peer closed", "unreachable",
     "kdl_err_peer", "peer did not arrive",
 )

@@ -31,18 +31,45 @@ def main(argv=None) -> int:
         sd = torch.load(args.checkpoint, weights_only=False)
         model.load_state_dict(sd["model"])
         start_step = sd["step"]
-    ddp = torch.nn.parallel.DistributedDataParallel(model) if world > 1 else model
-    opt = torch.optim.SGD(ddp.parameters(), lr=0.05)
+    # Data parallelism by hand: one flat gradient all-reduce per step.  torch's DistributedDataParallel
+    # would do the same for this model, but constructing it imports torch._dynamo (5 s on this
+    # image), which is most of the job's wall time.
+    params = list(model.parameters())
+    if world > 1:
+        flat = torch.cat([p.detach().reshape(-1) for p in params])
+        dist.broadcast(flat, src=0)                    # identical start, whatever the seeds did
+        o = 0
+        with torch.no_grad():
+            for p in params:
+                p.copy_(flat[o:o + p.numel()].view_as(p))
+                o += p.numel()
+    ddp = model
+    lr = 0.05        # plain SGD by hand: torch.optim pulls in torch._dynamo as well
     g = torch.Generator().manual_seed(100 + rank)
     loss = None
     for step in range(start_step, args.steps):
         x = torch.randn(args.batch, 1, 28, 28, generator=g)
         y = (x.flatten(1)[:, :10]).argmax(1)  # learnable synthetic labels
         loss = torch.nn.functional.cross_entropy(ddp(x), y)
-        opt.zero_grad()
+        for p in params:
+            p.grad = None
         loss.backward()
-        opt.step()
-        if args.fail_with and step == 2 and rank == world - 1 and not os.environ.get("KUBEDL_RESTARTED"):
+        if world > 1:
+            g_flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(g_flat)
+            g_flat /= world
+            o = 0
+            for p in params:
+                p.grad.copy_(g_flat[o:o + p.numel()].view_as(p))
+                o += p.numel()
+        with torch.no_grad():
+            for p in params:
+                p.add_(p.grad, alpha=-lr)
+        once = os.environ.get("KUBEDL_FAIL_ONCE", "")      # marker file: only the first incarnation fails
+        if args.fail_with and step == 2 and rank == world - 1 and not os.environ.get("KUBEDL_RESTARTED") \
+                and not (once and os.path.exists(once)):
+            if once:
+                open(once, "w").close()
             print(f"rank {rank}: injected failure with exit code {args.fail_with}", flush=True)
             os._exit(args.fail_with)
         if args.checkpoint and rank == 0 and step % 5 == 4:

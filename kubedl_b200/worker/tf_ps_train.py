@@ -187,10 +187,10 @@ def serve_shard(shard: ParameterShard, host: str, port: int) -> socketserver.Thr
                         send_msg(sock, b"OK  ", shard.version,
                                  json.dumps({"version": shard.version, "done": shard.done, "pushes": shard.pushes}).encode())
                     elif op == b"STOP":
-                        send_msg(sock, b"OK  ", shard.version)
                         shard.stop.set()
                         with shard.cv:
                             shard.cv.notify_all()
+                        send_msg(sock, b"OK  ", shard.version)
                     else:
                         send_msg(sock, b"ERR ", 0, b"unknown op")
             except (ConnectionError, OSError):

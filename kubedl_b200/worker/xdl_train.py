@@ -55,11 +55,16 @@ def main(argv=None) -> int:
     else:
         emb = torch.nn.Embedding(1000, 16)
         lin = torch.nn.Linear(16, 1)
-        opt = torch.optim.SGD(list(emb.parameters()) + list(lin.parameters()), lr=0.5)
+        params = list(emb.parameters()) + list(lin.parameters())
         for it in range(args.steps):
             ids = torch.randint(0, 1000, (256,))
             loss = torch.nn.functional.binary_cross_entropy_with_logits(lin(emb(ids))[:, 0], (ids % 2).float())
-            opt.zero_grad(); loss.backward(); opt.step()
+            for p in params:
+                p.grad = None
+            loss.backward()
+            with torch.no_grad():          # SGD by hand: torch.optim imports torch._dynamo (5 s)
+                for p in params:
+                    p.add_(p.grad, alpha=-0.5)
         loss = float(loss.detach())
     print(json.dumps({"task": task, "index": index, "world": world, "steps": args.steps, "loss": loss,
                       "seconds": time.time() - t0, "zk_addr": zk}), flush=True)

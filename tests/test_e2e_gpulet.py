@@ -135,3 +135,31 @@ def test_gpu_gang_admission_is_all_or_nothing():
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_rank_failure_recovers_through_exit_codes(tmp_path):
+    """A rank dies mid-run with the retryable 138.  Its peers' collectives fail, `worker/exitcodes.py`
+    turns those failures into 138 as well, the ExitCode policy recreates every pod that left that
+    way (same names, same ranks), the job rendezvouses again and finishes."""
+    mgr, recs, let = _cluster()
+    try:
+        (job,) = load_example("example/pytorch/pytorch_job_mnist_mpi.yaml")
+        job["metadata"]["name"] = "recover"
+        for spec in job["spec"]["pytorchReplicaSpecs"].values():
+            spec["template"]["spec"]["containers"][0]["env"] = [
+                {"name": "KUBEDL_MNIST_STEPS", "value": "6"}, {"name": "KUBEDL_FAIL_WITH", "value": "138"},
+                {"name": "KUBEDL_FAIL_ONCE", "value": str(tmp_path / "failed-once")}]
+        seen = []
+        mgr.api.watch("PyTorchJob", lambda ev, obj, old: seen.append(
+            [x["type"] for x in obj.get("status", {}).get("conditions", [])][-1:]))
+        mgr.api.create(job)
+        conds = _wait(lambda: _terminal(mgr, "PyTorchJob", "kubedl", "recover"), timeout=180)
+        logs = {p: let.pod_log("kubedl", f"recover-{p}") for p in ("master-0", "worker-0", "worker-1")}
+        assert conds[-1] == "Succeeded", (conds, logs)
+        assert ["Restarting"] in seen
+        assert "injected failure with exit code 138" in logs["worker-1"]
+        assert "exiting with 138 (retryable" in logs["master-0"] + logs["worker-0"]     # a survivor left retryably
+        assert logs["worker-1"].count("rank 2/3: 6 steps") == 1                           # second incarnation finished
+    finally:
+        let.stop()
+        mgr.stop()

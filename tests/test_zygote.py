@@ -1,0 +1,122 @@
+"""Pre-forked worker launcher (`node/zygote.py`): pods fork from a process that already paid for
+the imports.  No counterpart in the reference (kubelet + container runtime start its pods)."""
+import os
+import signal
+import sys
+import time
+
+from prometheus_client import CollectorRegistry
+
+from cp_helpers import load_example
+from kubedl_b200.controllers.registry import setup_with_manager
+from kubedl_b200.engine.job_controller import JobControllerConfiguration
+from kubedl_b200.node.gpulet import Gpulet
+from kubedl_b200.node.zygote import ZygoteClient
+from kubedl_b200.plugins import gang_schedule
+from kubedl_b200.runtime.manager import Manager
+
+
+def _wait(fn, timeout=60.0):
+    t0 = time.time()
+    while time.time() - t0 < timeout:
+        v = fn()
+        if v:
+            return v
+        time.sleep(0.02)
+    raise AssertionError("timed out")
+
+
+def _env(**extra):
+    env = dict(os.environ, PYTHONPATH=os.getcwd())
+    env.update(extra)
+    return env
+
+
+def test_spawn_exit_codes_logs_and_signals(tmp_path):
+    z = ZygoteClient(preload=("json", "kubedl_b200.worker.rendezvous"))
+    z.start()
+    try:
+        assert z.ready.wait(30)
+        py = sys.executable
+        # not a module run -> the caller has to exec
+        assert z.spawn(["/bin/echo", "hi"], _env(), str(tmp_path / "x.log")) is None
+        assert not z.eligible([py, "script.py"])
+        # a module run: environment and arguments are the pod's, output lands in the pod log
+        log = str(tmp_path / "ok.log")
+        tfc = '{"cluster": {"worker": ["a:1", "b:2"]}, "task": {"type": "worker", "index": 1}, "environment": "cloud"}'
+        p = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(TF_CONFIG=tfc, KUBEDL_TF_TRAIN_SECONDS="0.05"), log)
+        assert p is not None and p.pid > 0 and p.pid != os.getpid()
+        assert p.wait(20) == 0 and p.poll() == 0
+        assert "TF_CONFIG ok: task worker:1 rank 1/2" in open(log).read()
+        # exit codes pass through
+        p = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_FAIL_WITH="3", KUBEDL_TF_TRAIN_SECONDS="0.01"),
+                    str(tmp_path / "fail.log"))
+        assert p.wait(20) == 3
+        # an import error inside the worker is a failure of that pod only
+        p = z.spawn([py, "-m", "kubedl_b200.worker.no_such_module"], _env(), str(tmp_path / "bad.log"))
+        assert p.wait(20) == 1 and "No module named" in open(tmp_path / "bad.log").read()
+        # children lead their own process group: signalling the group reports -signal, like Popen
+        p = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="30"), str(tmp_path / "kill.log"))
+        _wait(lambda: os.getpgid(p.pid) == p.pid)
+        os.killpg(p.pid, signal.SIGTERM)
+        assert p.wait(20) == -signal.SIGTERM
+        assert z.spawned == 4
+        # the environment of one pod does not leak into the next
+        p = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="0.01"), str(tmp_path / "clean.log"))
+        assert p.wait(20) == 0 and "TF_CONFIG absent" in open(tmp_path / "clean.log").read()
+    finally:
+        z.stop()
+    assert not os.path.exists(z.sock_path)
+
+
+def test_zygote_death_fails_its_pods(tmp_path):
+    z = ZygoteClient(preload=("json",))
+    z.start()
+    try:
+        assert z.ready.wait(30)
+        p = z.spawn([sys.executable, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="30"), str(tmp_path / "a.log"))
+        z._proc.kill()                                   # the exact launcher process we started
+        assert p.wait(20) == -signal.SIGKILL             # reported as killed; the operator's policy takes over
+        assert z.failed.is_set() and not z.ready.is_set()
+        assert z.spawn([sys.executable, "-m", "kubedl_b200.worker.tf_stub"], _env(), str(tmp_path / "b.log")) is None
+        try:
+            os.killpg(p.pid, signal.SIGKILL)             # orphaned by the launcher's death: clean it up
+        except ProcessLookupError:
+            pass
+    finally:
+        z.stop()
+
+
+def test_pytorch_example_through_preforked_workers(tmp_path):
+    mgr = Manager()
+    gang_schedule.register_gang_schedulers(mgr)
+    setup_with_manager(mgr, JobControllerConfiguration(), "*", CollectorRegistry())
+    let = Gpulet(mgr.api, num_gpus=0, log_dir=str(tmp_path / "pods"), prefork=True)
+    mgr.start()
+    let.start()
+    try:
+        assert let.zygote.ready.wait(120)
+        (job,) = load_example("example/pytorch/pytorch_job_mnist_mpi.yaml")
+        for spec in job["spec"]["pytorchReplicaSpecs"].values():
+            spec["template"]["spec"]["containers"][0]["env"] = [{"name": "KUBEDL_MNIST_STEPS", "value": "5"},
+                                                               {"name": "KUBEDL_FAIL_WITH", "value": "138"},
+                                                               {"name": "KUBEDL_FAIL_ONCE", "value": str(tmp_path / "failed-once")}]
+        t0 = time.time()
+        mgr.api.create(job)
+
+        def terminal():
+            conds = [x["type"] for x in mgr.api.get("PyTorchJob", "kubedl", "pytorch-dist-sendrecv-example")
+                     .get("status", {}).get("conditions", [])]
+            return conds if conds and conds[-1] in ("Succeeded", "Failed") else None
+        conds = _wait(terminal, timeout=120)
+        wall = time.time() - t0
+        log = let.pod_log("kubedl", "pytorch-dist-sendrecv-example-worker-1")
+        # the last rank kills itself once with the retryable 138; ExitCode policy recreates it, and
+        # the recreated pod is again a fork of the launcher
+        assert conds[0] == "Created" and conds[-1] == "Succeeded", (conds, log)
+        assert "injected failure with exit code 138" in log
+        assert let.zygote.spawned >= 4, let.zygote.spawned
+        assert wall < 60
+    finally:
+        let.stop()
+        mgr.stop()

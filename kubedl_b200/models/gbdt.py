@@ -284,9 +284,54 @@ class GBDTTrainer:
         return out
 
 
+# ---------------------------------------------------------------------- model files
+def export_model(cuts: torch.Tensor, trees: List[Tree], **meta) -> dict:
+    """What a Predict job needs: the cut points that define the bins and, per tree, (feature,
+    threshold bin) of every internal node level by level plus the leaf values."""
+    return {"format": "kubedl-b200-gbdt-v1", "cuts": cuts.detach().float().cpu(),
+            "trees": [{"feat": [s[:, 0].detach().long().cpu() for s in t.splits],
+                       "thr": [s[:, 1].detach().long().cpu() for s in t.splits],
+                       "leaf": t.leaf_value.detach().float().cpu()} for t in trees],
+            "meta": dict(meta)}
+
+
+def save_model(path: str, model: dict) -> None:
+    import os as _os
+    _os.makedirs(_os.path.dirname(_os.path.abspath(path)), exist_ok=True)
+    tmp = path + ".tmp"
+    torch.save(model, tmp)
+    _os.replace(tmp, path)
+
+
+def load_model(path: str) -> dict:
+    m = torch.load(path, map_location="cpu", weights_only=False)
+    if m.get("format") != "kubedl-b200-gbdt-v1":
+        raise ValueError(f"{path} is not a kubedl-b200 GBDT model")
+    return m
+
+
+def predict_margin(model: dict, X: torch.Tensor) -> torch.Tensor:
+    """Sum of leaf values over the trees for raw (un-binned) rows, on X's device."""
+    dev = X.device
+    bins = quantize(X, model["cuts"].to(dev))
+    n = X.shape[0]
+    rows = torch.arange(n, device=dev)
+    out = torch.zeros(n, dtype=torch.float32, device=dev)
+    for t in model["trees"]:
+        node = torch.zeros(n, dtype=torch.int64, device=dev)
+        for feat, thr in zip(t["feat"], t["thr"]):
+            f, th = feat.to(dev)[node], thr.to(dev)[node]
+            node = 2 * node + (bins[rows, f].long() > th).long()
+        out += t["leaf"].to(dev)[node]
+    return out
+
+
 def reference_tree_torch(bins: torch.Tensor, gh: torch.Tensor, F: int, depth: int, lam: float, lr: float,
-                         gamma: float = 0.0, mcw: float = 1.0):
-    """Plain PyTorch fp64 oracle of one tree (histogram via index_add, exhaustive gain scan)."""
+                         gamma: float = 0.0, mcw: float = 1.0, allreduce=None):
+    """Plain PyTorch fp64 oracle of one tree (histogram via index_add, exhaustive gain scan).
+    `allreduce(tensor)` (in place, SUM over ranks) makes it the distributed algorithm: every rank
+    histograms its own rows, the histograms and leaf sums are summed, and all ranks pick the
+    same splits — what XGBoost's `hist` does over Rabit, and what the CUDA trainer fuses."""
     n = bins.shape[0]
     node = torch.zeros(n, dtype=torch.int64, device=bins.device)
     g, h = gh[:, 0].double(), gh[:, 1].double()
@@ -297,6 +342,8 @@ def reference_tree_torch(bins: torch.Tensor, gh: torch.Tensor, F: int, depth: in
         for f in range(F):
             idx = (node * F + f) * NBINS + bins[:, f].long()
             hist.index_add_(0, idx, torch.stack([g, h], 1))
+        if allreduce is not None:
+            allreduce(hist)
         hist = hist.view(nodes, F, NBINS, 2)
         cs = hist.cumsum(2)
         tot = cs[:, :, -1:, :]
@@ -317,4 +364,18 @@ def reference_tree_torch(bins: torch.Tensor, gh: torch.Tensor, F: int, depth: in
     leaves = 1 << depth
     G = torch.zeros(leaves, dtype=torch.float64, device=bins.device).index_add_(0, node, g)
     H = torch.zeros(leaves, dtype=torch.float64, device=bins.device).index_add_(0, node, h)
+    if allreduce is not None:
+        allreduce(G)
+        allreduce(H)
     return splits, (-G / (H + lam) * lr), node
+
+
+def tree_from_reference(splits, leaf: torch.Tensor) -> Tree:
+    """The oracle's output in the trainer's `Tree` layout (columns 0 / 1 = feature / threshold)."""
+    t = Tree(depth=len(splits))
+    for feat, thr, gain, valid in splits:
+        row = torch.zeros(feat.shape[0], 8, dtype=torch.float32)
+        row[:, 0], row[:, 1], row[:, 2], row[:, 7] = feat.float(), thr.float(), gain.float(), valid.float()
+        t.splits.append(row)
+    t.leaf_value = leaf.float()
+    return t

@@ -163,3 +163,49 @@ def test_rank_failure_recovers_through_exit_codes(tmp_path):
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_xgboost_train_then_predict_jobs(tmp_path, monkeypatch):
+    """The reference's XGBoost example has two job types, Train and Predict, linked by --model_path
+    (example/xgboost/xgboostjob_v1alpha1_iris_train.yaml:21-28).  Train over 3 ranks (histograms
+    summed with gloo, every rank grows identical trees), rank 0 writes the model; a second
+    XGBoostJob loads it and scores the same shards: same loss."""
+    import json as _json
+    monkeypatch.setenv("KUBEDL_MODEL_DIR", str(tmp_path / "models"))
+    mgr, recs, let = _cluster()
+    try:
+        (job,) = load_example("example/xgboost/xgboostjob_v1alpha1_iris_train.yaml")
+        ns, name = job["metadata"].get("namespace", "default"), job["metadata"]["name"]
+        for spec in job["spec"]["xgbReplicaSpecs"].values():
+            ctr = spec["template"]["spec"]["containers"][0]
+            ctr["env"] = [{"name": "KUBEDL_XGB_ROWS", "value": "4000"}]
+            ctr["args"] = [a for a in ctr["args"] if not a.startswith("--model_path")] + ["--model_path=autoAI/xgb-opt/2"]
+        mgr.api.create(job)
+        conds = _wait(lambda: _terminal(mgr, "XGBoostJob", ns, name), timeout=180)
+        logs = [let.pod_log(ns, f"{name}-{p}") for p in ("master-0", "worker-0", "worker-1")]
+        assert conds[-1] == "Succeeded", logs
+        res = [_json.loads([l for l in lg.splitlines() if l.startswith("{")][-1]) for lg in logs]
+        assert [r["rank"] for r in res] == [0, 1, 2] and all(r["world"] == 3 and r["trees"] == 3 for r in res)
+        assert "written to" in logs[0] and "kept on local disk" in logs[0]          # oss -> local, and says so
+        model = tmp_path / "models" / "autoAI" / "xgb-opt" / "2" / "model.pt"
+        assert model.exists()
+        train_loss = sum(r["logloss"] for r in res) / 3
+        assert train_loss < 0.69                                                        # below ln 2: it learned
+        # Predict job on the same shards
+        import copy
+        pj = copy.deepcopy(job)
+        pj["metadata"] = {"name": "xgb-predict", "namespace": ns}
+        pj.pop("status", None)
+        for spec in pj["spec"]["xgbReplicaSpecs"].values():
+            ctr = spec["template"]["spec"]["containers"][0]
+            ctr["args"] = ["--job_type=Predict" if a.startswith("--job_type") else a for a in ctr["args"]]
+        mgr.api.create(pj)
+        conds = _wait(lambda: _terminal(mgr, "XGBoostJob", ns, "xgb-predict"), timeout=180)
+        plog = let.pod_log(ns, "xgb-predict-master-0")
+        assert conds[-1] == "Succeeded", plog
+        pr = _json.loads([l for l in plog.splitlines() if l.startswith("{")][-1])
+        assert pr["job_type"] == "Predict" and pr["trees"] == 3 and pr["rows"] == 12000
+        assert abs(pr["logloss"] - train_loss) < 1e-4 and pr["accuracy"] > 0.55
+    finally:
+        let.stop()
+        mgr.stop()

@@ -69,6 +69,16 @@ def test_tree_matches_oracle_and_loss_decreases(cuda):
     assert losses[0] < l0 and all(b < a for a, b in zip(losses, losses[1:])), (l0, losses)
     # the stored trees reproduce the running prediction
     torch.testing.assert_close(tr.predict_bins(tr.bins), tr.pred, atol=1e-4, rtol=1e-4)
+    # and so does the exported model file, from raw rows, on either device (what a Predict job does)
+    import os
+    import tempfile
+    from kubedl_b200.models import gbdt as G
+    with tempfile.TemporaryDirectory() as d:
+        G.save_model(os.path.join(d, "m", "model.pt"), G.export_model(tr.cuts, tr.trees, learning_rate=tr.lr))
+        model = G.load_model(os.path.join(d, "m", "model.pt"))
+    assert len(model["trees"]) == len(tr.trees)
+    torch.testing.assert_close(G.predict_margin(model, X), tr.pred, atol=1e-4, rtol=1e-4)
+    torch.testing.assert_close(G.predict_margin(model, X[:4096].cpu()), tr.pred[:4096].cpu(), atol=1e-4, rtol=1e-4)
 
 
 @pytest.mark.parametrize("n,nodes", [(1000, 1), (100_003, 8), (1_000_000, 128), (257, 256)])

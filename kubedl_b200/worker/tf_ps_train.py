@@ -158,6 +158,29 @@ class ParameterShard:
             self.cv.wait_for(lambda: self.version >= min_version or self.stop.is_set(), timeout)
             return self.version, self.w.numpy().tobytes()
 
+    # ---- checkpoint / resume: a PS pod recreated by the operator (same name, same index) picks up
+    # its shard where the previous incarnation left it
+    def save(self, path: str) -> None:
+        with self.cv:
+            state = {"w": self.w.clone(), "m": self.m.clone(), "version": self.version, "pushes": self.pushes}
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        tmp = f"{path}.tmp{os.getpid()}"
+        torch.save(state, tmp)
+        os.replace(tmp, path)
+
+    def load(self, path: str) -> bool:
+        if not os.path.exists(path):
+            return False
+        state = torch.load(path, map_location="cpu", weights_only=False)
+        if state["w"].shape != self.w.shape:
+            raise ValueError(f"checkpoint {path} holds {tuple(state['w'].shape)} parameters, this shard has {tuple(self.w.shape)}")
+        with self.cv:
+            self.w.copy_(state["w"])
+            self.m.copy_(state["m"])
+            self.version, self.pushes = int(state["version"]), int(state.get("pushes", 0))
+            self.cv.notify_all()
+        return True
+
     def worker_done(self) -> int:
         with self.cv:
             self.done += 1
@@ -348,6 +371,9 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--momentum", type=float, default=0.9)
     ap.add_argument("--sync_replicas", action="store_true", default=os.environ.get("KUBEDL_TF_SYNC", "0") == "1")
     ap.add_argument("--summary_every", type=int, default=10)
+    ap.add_argument("--checkpoint_dir", default=os.environ.get("KUBEDL_TF_CHECKPOINT_DIR", ""),
+                    help="ps tasks keep their shard here (ps-<index>.pt) and resume from it")
+    ap.add_argument("--checkpoint_every", type=float, default=5.0, help="seconds between shard checkpoints")
     ap.add_argument("--original-command", default="", help="command line of the image this entrypoint stands in for")
     return ap
 
@@ -380,10 +406,20 @@ def main(argv=None) -> int:
         shard = ParameterShard(flat_params(build_model())[lo:hi], args.learning_rate, args.momentum,
                                n_workers, args.sync_replicas)
         port = int(ps_addrs[tindex].rpartition(":")[2])
+        ckpt = os.path.join(args.checkpoint_dir, f"ps-{tindex}.pt") if args.checkpoint_dir else ""
+        if ckpt and shard.load(ckpt):
+            print(f"ps:{tindex} resumed from {ckpt} at version {shard.version}", flush=True)
         srv = serve_shard(shard, os.environ.get("KUBEDL_BIND_ADDR", "0.0.0.0"), port)
         print(f"ps:{tindex} serving parameters [{lo}, {hi}) of {total} on port {port} "
               f"({'sync' if args.sync_replicas else 'async'}, {n_workers} workers)", flush=True)
-        shard.stop.wait(float(os.environ.get("KUBEDL_TF_PS_SECONDS", "86400")))
+        deadline = time.monotonic() + float(os.environ.get("KUBEDL_TF_PS_SECONDS", "86400"))
+        saved = shard.version
+        while not shard.stop.wait(args.checkpoint_every if ckpt else 3600.0) and time.monotonic() < deadline:
+            if ckpt and shard.version != saved:
+                shard.save(ckpt)
+                saved = shard.version
+        if ckpt and shard.version != saved:
+            shard.save(ckpt)
         srv.shutdown()
         print(f"ps:{tindex} stopping at version {shard.version} after {shard.pushes} pushes", flush=True)
         return 0

@@ -179,3 +179,20 @@ def test_reference_tf_example_runs_single_replica(tmp_path):
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_ps_shard_checkpoint_resume(tmp_path):
+    a = ps.ParameterShard(torch.arange(5, dtype=torch.float32), lr=0.1, momentum=0.9, n_workers=1, sync=False)
+    a.push(torch.ones(5))
+    a.push(torch.ones(5))
+    path = str(tmp_path / "ckpt" / "ps-0.pt")
+    a.save(path)
+    b = ps.ParameterShard(torch.zeros(5), lr=0.1, momentum=0.9, n_workers=1, sync=False)
+    assert b.load(path) and b.version == 2 and b.pushes == 2
+    a.push(torch.ones(5))
+    b.push(torch.ones(5))
+    assert torch.equal(a.w, b.w) and torch.equal(a.m, b.m)          # momentum came along
+    assert not ps.ParameterShard(torch.zeros(5), 0.1, 0.9, 1, False).load(str(tmp_path / "none.pt"))
+    import pytest
+    with pytest.raises(ValueError):
+        ps.ParameterShard(torch.zeros(7), 0.1, 0.9, 1, False).load(path)

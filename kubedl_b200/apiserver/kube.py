@@ -22,6 +22,7 @@ Only the standard library is used (http.client + ssl), so the operator image nee
 from __future__ import annotations
 
 import base64
+import collections
 import copy
 import http.client
 import json
@@ -416,7 +417,7 @@ class KubeAPIServer:
         self._lock = threading.RLock()
         self._discovery: Dict[str, Tuple[float, List[str]]] = {}
         self.discovery_ttl = 10.0
-        self.request_log: List[Tuple[str, str, str]] = []
+        self.request_log = collections.deque(maxlen=65536)
         self.remote = True
         self.metrics = None      # plugins/controller_metrics.ControllerMetrics (rest_client_* series)
         self._host = urllib.parse.urlsplit(config.server).netloc

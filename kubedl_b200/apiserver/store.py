@@ -75,7 +75,9 @@ class APIServer:
         self._history: Deque[Tuple[int, str, str, dict]] = collections.deque(maxlen=history)
         self._history_floor = 0    # events with rv <= floor have been dropped
         self.fail_next: Dict[Tuple[str, str], Exception] = {}  # fault injection: (verb, kind) -> error
-        self.request_log: List[Tuple[str, str, str]] = []      # (verb, kind, ns/name) for launch-delay analysis
+        self.request_log: Deque[Tuple[str, str, str]] = collections.deque(maxlen=65536)   # (verb, kind, ns/name), recent
+        self.event_ttl = 3600.0          # Events are dropped after an hour, as kube-apiserver does
+        self._events_since_prune = 0
         if install_all_crds:
             for info in scheme.workload_kinds():
                 self.install_crd(info.kind)
@@ -317,7 +319,26 @@ class APIServer:
                                  "uid": c.uid_of(involved), "apiVersion": involved.get("apiVersion", "")},
               "type": etype, "reason": reason, "message": message, "count": 1,
               "firstTimestamp": now, "lastTimestamp": now, "source": {"component": source}}
-        return self.create(ev)
+        out = self.create(ev)
+        self._events_since_prune += 1
+        if self._events_since_prune >= 256:
+            self._events_since_prune = 0
+            self.prune_events()
+        return out
+
+    def prune_events(self, now: Optional[float] = None) -> int:
+        """Delete Events older than `event_ttl` (kube-apiserver's --event-ttl, 1 h by default)."""
+        import time as _time
+        cutoff = (now if now is not None else _time.time()) - self.event_ttl
+        with self._lock:
+            old = [(ns, n) for (ns, n), e in self._objs["Event"].items()
+                   if (c.parse_time(e.get("lastTimestamp")) or 0.0) < cutoff]
+        for ns, n in old:
+            try:
+                self.delete("Event", ns, n, cascade=False)
+            except NotFound:
+                pass
+        return len(old)
 
     def events_for(self, involved: dict) -> List[dict]:
         uid = c.uid_of(involved)

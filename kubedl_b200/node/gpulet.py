@@ -204,6 +204,12 @@ class Gpulet:
                 if gpu is not None:
                     self.free_gpus.append(gpu)
                     self.free_gpus.sort()
+                # last pod of a job gone: forget the job's host-port assignments
+                job = self._job_of.pop(key, None)
+                if job and not any(k[0] == key[0] and j == job for k, j in self._job_of.items()):
+                    for pk in [pk for pk in self._ports
+                               if pk[0] == key[0] and (pk[1] == job or str(pk[1]).startswith(job + "-"))]:
+                        del self._ports[pk]
             elif ev == ADDED and not (pod.get("status") or {}).get("phase"):
                 self._pending[key] = pod
                 p = None

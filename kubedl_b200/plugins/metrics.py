@@ -13,6 +13,8 @@ launch-delay benchmark can report p50/p90 (default buckets stop at 10 s).
 """
 from __future__ import annotations
 
+import collections
+
 import threading
 from typing import Callable, Dict, List, Optional, Tuple
 
@@ -130,6 +132,25 @@ def _pod_ready_time(pod: dict) -> Optional[float]:
     return None
 
 
+class _BoundedSet:
+    """Insertion-ordered set that forgets its oldest members beyond `limit` (job UIDs seen)."""
+
+    def __init__(self, limit: int):
+        self.limit = limit
+        self._d: "collections.OrderedDict" = collections.OrderedDict()
+
+    def add(self, x) -> None:
+        self._d[x] = None
+        while len(self._d) > self.limit:
+            self._d.popitem(last=False)
+
+    def __contains__(self, x) -> bool:
+        return x in self._d
+
+    def __len__(self) -> int:
+        return len(self._d)
+
+
 class JobMetrics:
     def __init__(self, kind: str, reader, registry: Optional[CollectorRegistry] = None):
         self.kind = kind
@@ -140,13 +161,15 @@ class JobMetrics:
         self._success, self._failure = fam.success.labels(lk), fam.failure.labels(lk)
         self._restart = fam.restart.labels(lk)
         self._first, self._all = fam.first_pod, fam.all_pods
-        self.launch_delays: Dict[str, List[Tuple[str, float]]] = {"first_pod": [], "all_pods": []}
+        # bounded: an operator runs for months
+        self.launch_delays: Dict[str, collections.deque] = {"first_pod": collections.deque(maxlen=100_000),
+                                                            "all_pods": collections.deque(maxlen=100_000)}
         # The reference means to observe each delay once per job but its guards leak (first-pod is
         # re-observed on every pass while Created stays True, job.go:243-245; all-pods again after
         # a restart because Restarting has already flipped back to Running, job.go:255-259).
         # Observing once per job UID gives the intended semantics.
-        self._seen_first: set = set()
-        self._seen_all: set = set()
+        self._seen_first = _BoundedSet(200_000)
+        self._seen_all = _BoundedSet(200_000)
         if reader is not None:
             fam.gauge_sources[lk] = lambda: (job_status_counter(kind, reader, st.is_running),
                                              job_status_counter(kind, reader, _is_pending))

@@ -12,6 +12,7 @@ drains every queue on the calling thread (deterministic tests — the stronger h
 """
 from __future__ import annotations
 
+import collections
 import copy
 import fcntl
 import os
@@ -142,7 +143,7 @@ class EventRecorder:
 
     def __init__(self, api: APIServer, component: str):
         self.api, self.component = api, component
-        self.events: List[Tuple[str, str, str, str]] = []  # (object key, type, reason, message)
+        self.events: "collections.deque" = collections.deque(maxlen=4096)  # (object key, type, reason, message), most recent
         self._lock = threading.Lock()
         # Against a remote API server an Event is a round trip; client-go's recorder hands events
         # to a broadcaster goroutine so that reconciles never wait for them, and so do we.

@@ -11,6 +11,7 @@ rank is the cure for all of those, so they leave with 138.
 """
 from __future__ import annotations
 
+import os
 import sys
 import traceback
 from typing import Callable, Optional
@@ -23,8 +24,9 @@ _RETRYABLE_MARKERS = (
     "cudaerrorlaunchfailure", "cudaerrorecc", "watchdog",
     "nccl", "communicator was aborted", "collective operation timeout",
     "connection reset", "connection refused", "connection closed", "closed by peer", "broken pipe",
-    "socket timeout", "timed out",
-    "tcpstore", "the store", "rendezvous", "peer closed", "unreachable",
+    "timeout", "timed out", "gloo/", "processgroup",
+    "tcpstore", "the store", "diststoreerror", "distnetworkerror", "distbackenderror", "wait timeout",
+    "rendezvous", "peer closed", "unreachable",
     "kdl_err_peer", "peer did not arrive",
 )
 _PERMANENT_TYPES = (SyntaxError, ImportError, AttributeError, TypeError, KeyError, AssertionError, NotImplementedError)
@@ -51,8 +53,12 @@ def classify(exc: BaseException) -> int:
     return 1
 
 
-def run(main: Callable[[], Optional[int]]) -> int:
-    """`sys.exit(run(main))`: main's return value, or the classified code of what it raised."""
+def run(main: Callable[[], Optional[int]], hard_exit: Optional[bool] = None) -> int:
+    """`sys.exit(run(main))`: main's return value, or the classified code of what it raised.
+    hard_exit (default: only when running as a worker process, i.e. called from `__main__`):
+    on failure, exit the process immediately with that code."""
+    if hard_exit is None:
+        hard_exit = sys._getframe(1).f_globals.get("__name__") == "__main__"
     try:
         rc = main()
         return int(rc or 0)
@@ -63,4 +69,13 @@ def run(main: Callable[[], Optional[int]]) -> int:
             kind = "retryable" if code in (USER_RETRYABLE_EXIT_CODE, 130, 137, 143) else "permanent"
             print(f"worker failed ({type(e).__name__}); exiting with {code} ({kind} under restartPolicy ExitCode)",
                   file=sys.stderr, flush=True)
+            if hard_exit:
+                # Leave now.  Normal interpreter shutdown would tear down a process group whose
+                # transport threads are mid-failure; gloo then calls std::terminate and the pod
+                # reports SIGABRT (134, permanent) instead of the code chosen above.
+                try:
+                    sys.stdout.flush()
+                    sys.stderr.flush()
+                finally:
+                    os._exit(code)
         return code

@@ -66,5 +66,11 @@ def init_process_group(backend: str = "gloo", kind: str = "pytorch", env: Mappin
         if addr == "localhost":
             addr = "127.0.0.1"
         port = env.get("MASTER_PORT", "23456")
-        dist.init_process_group(backend, init_method=f"tcp://{addr}:{port}", rank=rank, world_size=world)
+        # A rank recreated by the ExitCode policy can reach the previous incarnation's store just
+        # before its peers die too; it must give up on that rendezvous (and leave with a retryable
+        # code) rather than wait the default half hour.  KUBEDL_RENDEZVOUS_TIMEOUT, seconds.
+        import datetime
+        timeout = datetime.timedelta(seconds=float(env.get("KUBEDL_RENDEZVOUS_TIMEOUT", "1800")))
+        dist.init_process_group(backend, init_method=f"tcp://{addr}:{port}", rank=rank, world_size=world,
+                                timeout=timeout)
     return rank, world

@@ -148,7 +148,9 @@ def test_rank_failure_recovers_through_exit_codes(tmp_path):
         for spec in job["spec"]["pytorchReplicaSpecs"].values():
             spec["template"]["spec"]["containers"][0]["env"] = [
                 {"name": "KUBEDL_MNIST_STEPS", "value": "6"}, {"name": "KUBEDL_FAIL_WITH", "value": "138"},
-                {"name": "KUBEDL_FAIL_ONCE", "value": str(tmp_path / "failed-once")}]
+                {"name": "KUBEDL_FAIL_ONCE", "value": str(tmp_path / "failed-once")},
+                # a recreated rank that met the dying incarnation's store gives up quickly and retries
+                {"name": "KUBEDL_RENDEZVOUS_TIMEOUT", "value": "8"}]
         seen = []
         mgr.api.watch("PyTorchJob", lambda ev, obj, old: seen.append(
             [x["type"] for x in obj.get("status", {}).get("conditions", [])][-1:]))
@@ -159,7 +161,7 @@ def test_rank_failure_recovers_through_exit_codes(tmp_path):
         assert ["Restarting"] in seen
         assert "injected failure with exit code 138" in logs["worker-1"]
         assert "exiting with 138 (retryable" in logs["master-0"] + logs["worker-0"]     # a survivor left retryably
-        assert logs["worker-1"].count("rank 2/3: 6 steps") == 1                           # second incarnation finished
+        assert logs["worker-1"].count("rank 2/3: 6 steps") == 1                           # a later incarnation finished
     finally:
         let.stop()
         mgr.stop()

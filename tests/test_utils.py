@@ -133,7 +133,10 @@ def test_worker_exit_code_classification():
     retry = [RuntimeError("CUDA error: unspecified launch failure"), RuntimeError("NCCL error in: ... unhandled system error"),
              ConnectionResetError("peer"), TimeoutError(), RuntimeError("Socket Timeout"),
              RuntimeError("[c10d] the client socket has timed out after 600s while trying to connect to the store"),
-             RuntimeError("all-reduce watchdog: peer did not arrive"), KeyboardInterrupt(), MemoryError()]
+             RuntimeError("all-reduce watchdog: peer did not arrive"), KeyboardInterrupt(), MemoryError(),
+             type("DistStoreError", (RuntimeError,), {})("wait timeout after 15000ms, keys: /default_pg/0//cpu//0/0"),
+             RuntimeError("[gloo/transport/tcp/pair.cc:547] Connection closed by peer [127.0.0.1]:59032"),
+             RuntimeError("[/pytorch/third_party/gloo/gloo/transport/tcp/pair.cc:311] Connect timeout [none]")]
     for e in retry:
         assert is_retryable_exit_code(classify(e)), e
     perm = [ValueError("batch must be a multiple of 8"), ImportError("no module"), AssertionError("shape"),

@@ -201,3 +201,17 @@ def test_crd_discovery_gates_kinds():
     api.install_crd("TFJob")
     assert api.server_resources_for_group_version("kubeflow.org/v1") == ["TFJob"]
     api.create(k.new_job("TFJob", "j"))
+
+
+def test_events_expire_like_kube_apiserver():
+    """--event-ttl: Events older than an hour are dropped so a long-running manager does not grow."""
+    import time
+    from kubedl_b200.apiserver.store import APIServer
+    api = APIServer()
+    job = api.create(k.new_job("TFJob", "e", "ns", replica_specs={}))
+    for i in range(3):
+        api.record_event(job, "Normal", "SuccessfulCreatePod", f"pod {i}")
+    assert len(api.events_for(job)) == 3
+    assert api.prune_events(now=time.time() + 10) == 0
+    assert api.prune_events(now=time.time() + 3700) == 3 and api.events_for(job) == []
+    assert api.request_log.maxlen == 65536

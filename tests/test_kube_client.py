@@ -510,3 +510,24 @@ def test_apiserver_snapshot_survives_a_restart(tmp_path):
     assert j2["status"]["conditions"][0]["type"] == "Created"
     fresh.delete("TFJob", "ns", "t")
     assert fresh.list("Pod", "ns") == []                    # the owner link still resolves
+
+
+def test_wire_helpers():
+    from kubedl_b200.apiserver.kube import _url_template, error_from_status
+    from kubedl_b200.apiserver.rest import merge_patch, parse_label_selector
+    assert _url_template("/api/v1/namespaces/kubedl/pods/x-worker-0?a=b") == "/api/v1/namespaces/{namespace}/pods/{name}"
+    assert _url_template("/apis/kubeflow.org/v1/namespaces/ns/tfjobs/t/status") == \
+        "/apis/kubeflow.org/v1/namespaces/{namespace}/tfjobs/{name}/status"
+    assert _url_template("/apis/kubeflow.org/v1/tfjobs") == "/apis/kubeflow.org/v1/tfjobs"
+    assert _url_template("/api/v1/namespaces/ns/pods") == "/api/v1/namespaces/{namespace}/pods"
+    assert parse_label_selector("a=b, c==d,") == {"a": "b", "c": "d"} and parse_label_selector("") is None
+    with pytest.raises(ValueError):
+        parse_label_selector("a!=b")
+    assert merge_patch({"a": {"b": 1, "c": 2}, "d": 3}, {"a": {"b": None, "e": 4}, "d": [1]}) == {"a": {"c": 2, "e": 4}, "d": [1]}
+    # Status bodies -> exception classes, by reason first, by code when the body is not a Status
+    assert isinstance(error_from_status(409, b'{"kind":"Status","reason":"AlreadyExists","message":"x","code":409}'), store.AlreadyExists)
+    assert isinstance(error_from_status(409, b'{"kind":"Status","reason":"Conflict","message":"x","code":409}'), store.Conflict)
+    assert isinstance(error_from_status(404, b"404 page not found"), store.NotFound)
+    assert isinstance(error_from_status(403, b'{"reason":"Forbidden","message":"no"}'), kube.Forbidden)
+    e = error_from_status(500, b"boom")
+    assert isinstance(e, store.ApiError) and e.code == 500 and "boom" in str(e)

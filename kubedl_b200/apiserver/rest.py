@@ -71,6 +71,10 @@ def merge_patch(target, patch):
     return out
 
 
+def url_tail(path: str) -> str:
+    return path.split("?")[0].rstrip("/").rsplit("/", 1)[-1]
+
+
 def status_body(code: int, reason: str, message: str) -> dict:
     return {"kind": "Status", "apiVersion": "v1", "metadata": {}, "status": "Failure" if code >= 400 else "Success",
             "message": message, "reason": reason, "code": code}
@@ -316,6 +320,10 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
                     return self._not_found()
                 if (r.q("watch") or "").lower() in ("1", "true"):
                     return self._watch(r)
+                if r.name and r.kind == "Pod" and url_tail(self.path) == "log":
+                    api.get("Pod", r.namespace or "default", r.name)          # 404 for unknown pods
+                    text = log_reader(r.namespace or "default", r.name) if log_reader else ""
+                    return self._send(200, text.encode())
                 if r.name:
                     return self._send(200, api.get(r.kind, r.namespace or "default", r.name))
                 items, rv = api.list_with_rv(r.kind, r.namespace, parse_label_selector(r.q("labelSelector")))

@@ -184,9 +184,69 @@ def cmd_run(args) -> int:
         op.stop()
 
 
+def cmd_cluster(args) -> int:
+    """The same verbs against a real Kubernetes API server (or the façade) through the client the
+    operator uses — for boxes where kubectl is not installed; kubectl works just as well."""
+    from ..apiserver.kube import KubeAPIServer, KubeConfig
+    from ..apiserver.store import ApiError
+    cfg = KubeConfig.load(kubeconfig=args.kubeconfig, context=args.context)
+    cli = KubeAPIServer(cfg)
+    ns = getattr(args, "namespace", None)
+    if ns == "default" and cfg.namespace:
+        ns = cfg.namespace                       # the context's namespace is the default, as with kubectl
+    try:
+        if args.cmd == "apply":
+            for f in args.filename:
+                with open(f) as fh:
+                    for d in yaml.safe_load_all(fh):
+                        if not d:
+                            continue
+                        if not cli.scheme.knows(d.get("kind", "")):
+                            print(f"{str(d.get('kind', '')).lower()}/{d.get('metadata', {}).get('name')} skipped (apply it with kubectl)")
+                            continue
+                        d.setdefault("metadata", {}).setdefault("namespace", cfg.namespace or "default")
+                        o = cli.apply(d)
+                        print(f"{o['kind'].lower()}/{c.name_of(o)} applied")
+            return 0
+        if args.cmd == "logs":
+            out = cli._request("GET", cli._object_path("Pod", ns, args.pod, "log"))
+            print(out.get("raw", "") if isinstance(out, dict) else out, end="")
+            return 0
+        kind = resolve_kind(args.kind)
+        if args.cmd == "get":
+            items = [cli.get(kind, ns, args.name)] if args.name else cli.list(kind, ns)
+            if args.output in ("json", "yaml"):
+                obj = items[0] if args.name else {"items": items}
+                print(json.dumps(obj, indent=2) if args.output == "json" else yaml.safe_dump(obj, sort_keys=False))
+            else:
+                print_table(kind, items)
+            return 0
+        if args.cmd == "describe":
+            obj = cli.get(kind, ns, args.name)
+            print(yaml.safe_dump(obj, sort_keys=False))
+            mine = cli.events_for(obj)
+            if mine:
+                print("Events:")
+                for e in mine:
+                    print(f"  {e['type']:8s} {e['reason']:28s} {e['message']}")
+            return 0
+        if args.cmd == "delete":
+            cli.delete(kind, ns, args.name)
+            print(f"{kind.lower()} \"{args.name}\" deleted")
+            return 0
+        return 2
+    except ApiError as e:
+        raise SystemExit(f"Error from server ({e.reason}): {e}")
+    finally:
+        cli.close()
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="kubedlctl")
     ap.add_argument("--server", "-s", default="127.0.0.1:8001")
+    ap.add_argument("--kubeconfig", default="", help="talk to the Kubernetes cluster of this kubeconfig instead of a local manager")
+    ap.add_argument("--context", default=None)
+    ap.add_argument("--in-cluster", action="store_true", help="use $KUBECONFIG or the pod's service account")
     sub = ap.add_subparsers(dest="cmd", required=True)
     a = sub.add_parser("apply"); a.add_argument("-f", "--filename", required=True, action="append")
     g = sub.add_parser("get"); g.add_argument("kind"); g.add_argument("name", nargs="?"); g.add_argument("-n", "--namespace", default="default"); g.add_argument("-o", "--output", default="")
@@ -202,6 +262,8 @@ def main(argv=None) -> int:
     args = ap.parse_args(argv)
     if args.cmd == "run":
         return cmd_run(args)
+    if args.kubeconfig or args.in_cluster:
+        return cmd_cluster(args)
     if args.cmd == "apply":
         for f in args.filename:
             with open(f, "rb") as fh:

@@ -146,3 +146,35 @@ def test_bind_address_parsing():
     assert parse_bind_address(":8080") == ("0.0.0.0", 8080)
     assert parse_bind_address("127.0.0.1:9090") == ("127.0.0.1", 9090)
     assert parse_bind_address("0") is None and parse_bind_address("") is None
+
+
+def test_kubedlctl_with_a_kubeconfig(capsys, tmp_path):
+    """`kubedlctl --kubeconfig`: the same verbs through the Kubernetes client (here against the façade,
+    which speaks the same protocol as kube-apiserver)."""
+    import yaml
+    from kubedl_b200.apiserver import rest, store
+    api = store.APIServer()
+    srv = rest.serve(api, "127.0.0.1", 0, log_reader=lambda ns, name: f"log of {ns}/{name}\n")
+    kc = tmp_path / "config"
+    kc.write_text(yaml.safe_dump({"current-context": "box", "clusters": [{"name": "b", "cluster": {"server": srv.url}}],
+                                  "contexts": [{"name": "box", "context": {"cluster": "b", "namespace": "kubedl"}}]}))
+    base = ["--kubeconfig", str(kc)]
+    try:
+        assert kubedlctl.main(base + ["apply", "-f", f"{REF}/example/pytorch/pytorch_job_mnist_mpi.yaml"]) == 0
+        assert "pytorchjob/pytorch-dist-sendrecv-example applied" in capsys.readouterr().out
+        assert api.get("PyTorchJob", "kubedl", "pytorch-dist-sendrecv-example")
+        assert kubedlctl.main(base + ["get", "pytorchjobs"]) == 0                 # namespace from the context
+        assert "pytorch-dist-sendrecv-example" in capsys.readouterr().out
+        kubedlctl.main(base + ["get", "pytorchjob", "pytorch-dist-sendrecv-example", "-o", "json"])
+        assert json.loads(capsys.readouterr().out)["kind"] == "PyTorchJob"
+        api.create({"kind": "Pod", "metadata": {"name": "p0", "namespace": "kubedl"}, "spec": {"containers": []}})
+        assert kubedlctl.main(base + ["logs", "p0"]) == 0
+        assert capsys.readouterr().out == "log of kubedl/p0\n"
+        assert kubedlctl.main(base + ["describe", "pytorchjob", "pytorch-dist-sendrecv-example"]) == 0
+        capsys.readouterr()
+        assert kubedlctl.main(base + ["delete", "pytorchjob", "pytorch-dist-sendrecv-example"]) == 0
+        with pytest.raises(SystemExit) as e:
+            kubedlctl.main(base + ["get", "pytorchjob", "pytorch-dist-sendrecv-example"])
+        assert "NotFound" in str(e.value)
+    finally:
+        srv.shutdown()

@@ -531,3 +531,55 @@ def test_wire_helpers():
     assert isinstance(error_from_status(403, b'{"reason":"Forbidden","message":"no"}'), kube.Forbidden)
     e = error_from_status(500, b"boom")
     assert isinstance(e, store.ApiError) and e.code == 500 and "boom" in str(e)
+
+
+def test_operator_restart_resumes_from_api_state():
+    """Kill the operator mid-job, start a new one against the same API server: it re-lists, adopts
+    the pods that carry its owner reference, creates nothing twice, and drives the job to the end
+    (all state lives in the API server)."""
+    from prometheus_client import CollectorRegistry
+    from kubedl_b200.cmd import manager as cmd
+    from kubedl_b200.node.gpulet import FakeKubelet
+    api = store.APIServer()
+    srv = rest.serve(api, "127.0.0.1", 0)
+    kubelet = FakeKubelet(api)
+    flags = ["--master", srv.url, "--workloads", "*", "--enable-leader-election=false", "--metrics-addr", "0",
+             "--controller-metrics-addr", "0", "--serve", ""]
+
+    def operator():
+        args = cmd.build_parser().parse_args(flags)
+        reg = CollectorRegistry()
+        op = cmd.build_operator(args, metrics_registry=reg)
+        cmd.start_operator(op, args, metrics_registry=reg)
+        return op, reg
+
+    conds = lambda: [x["type"] for x in api.get("TFJob", "ns", "r").get("status", {}).get("conditions", [])]
+    op1, _ = operator()
+    try:
+        api.create(new_job("TFJob", "r", "ns", replica_specs={
+            "PS": {"replicas": 1, "template": tmpl("tensorflow")}, "Worker": {"replicas": 3, "template": tmpl("tensorflow")}}))
+        wait_for(lambda: len(api.list("Pod", "ns")) == 4 and conds() == ["Created"], what="pods created")
+        uids = {c.name_of(p): p["metadata"]["uid"] for p in api.list("Pod", "ns")}
+    finally:
+        op1.stop()
+    # while nobody is reconciling: pods start, one worker pod disappears
+    kubelet.set_all("ns", "Running")
+    api.delete("Pod", "ns", "r-worker-2")
+    time.sleep(0.2)
+    assert conds() == ["Created"]
+    creates_before = sum(1 for verb, kind, _ in api.request_log if verb == "create" and kind == "Pod")
+    op2, reg2 = operator()
+    try:
+        wait_for(lambda: len(api.list("Pod", "ns")) == 4 and conds() == ["Created", "Running"], what="resumed")
+        now = {c.name_of(p): p["metadata"]["uid"] for p in api.list("Pod", "ns")}
+        assert {n: u for n, u in now.items() if n != "r-worker-2"} == {n: u for n, u in uids.items() if n != "r-worker-2"}
+        assert now["r-worker-2"] != uids["r-worker-2"]                               # only the missing index was created
+        assert sum(1 for verb, kind, _ in api.request_log if verb == "create" and kind == "Pod") == creates_before + 1
+        assert reg2.get_sample_value("kubedl_jobs_created", {"kind": "tfjob"}) in (None, 0.0)   # Created was already recorded
+        kubelet.set_all("ns", "Running")
+        for i in range(3):
+            kubelet.set_phase("ns", f"r-worker-{i}", "Succeeded", exit_code=0)
+        wait_for(lambda: conds()[-1] == "Succeeded", what="Succeeded after restart")
+    finally:
+        op2.stop()
+        srv.shutdown()

@@ -189,7 +189,7 @@ class Scheme:
         self._by_kind: Dict[str, KindInfo] = {}
         self._builtin = {"Pod": ("", "v1", "pods"), "Service": ("", "v1", "services"),
                          "Event": ("", "v1", "events"), "ConfigMap": ("", "v1", "configmaps"),
-                         "Namespace": ("", "v1", "namespaces"),
+                         "Namespace": ("", "v1", "namespaces"), "Node": ("", "v1", "nodes"),
                          "Deployment": ("apps", "v1", "deployments"),
                          "Lease": ("coordination.k8s.io", "v1", "leases"),
                          "PodGroup": ("scheduling.incubator.k8s.io", "v1alpha1", "podgroups")}

@@ -432,7 +432,7 @@ class KubeAPIServer:
 
     def _collection_path(self, kind: str, namespace: Optional[str]) -> str:
         prefix, plural = self._prefix(kind)
-        if namespace and kind != "Namespace":
+        if namespace and kind not in ("Namespace", "Node"):      # cluster-scoped kinds have no namespace segment
             return f"{prefix}/namespaces/{urllib.parse.quote(namespace)}/{plural}"
         return f"{prefix}/{plural}"
 

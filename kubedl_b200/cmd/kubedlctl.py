@@ -27,7 +27,8 @@ for _info in SCHEME.workload_kinds():
     for _n in (_info.kind.lower(), _info.plural, _info.singular):
         _ALIASES[_n] = _info.kind
 _ALIASES.update({"pod": "Pod", "pods": "Pod", "svc": "Service", "service": "Service", "services": "Service",
-                 "event": "Event", "events": "Event", "podgroup": "PodGroup", "podgroups": "PodGroup"})
+                 "event": "Event", "events": "Event", "podgroup": "PodGroup", "podgroups": "PodGroup",
+                 "node": "Node", "nodes": "Node", "no": "Node", "lease": "Lease", "leases": "Lease"})
 
 
 def resolve_kind(word: str) -> str:
@@ -37,14 +38,13 @@ def resolve_kind(word: str) -> str:
     return k
 
 
+CLUSTER_SCOPED = ("Node", "Namespace")
+
+
 def _path(kind: str, ns: str, name: Optional[str] = None) -> str:
-    if SCHEME.is_workload(kind):
-        i = SCHEME.info(kind)
-        p = f"/apis/{i.group}/{i.version}/namespaces/{ns}/{i.plural}"
-    elif kind == "PodGroup":
-        p = f"/apis/scheduling.incubator.k8s.io/v1alpha1/namespaces/{ns}/podgroups"
-    else:
-        p = f"/api/v1/namespaces/{ns}/{kind.lower()}s"
+    g, v, plural = SCHEME.resource(kind)
+    prefix = f"/apis/{g}/{v}" if g else f"/api/{v}"
+    p = f"{prefix}/{plural}" if kind in CLUSTER_SCOPED else f"{prefix}/namespaces/{ns}/{plural}"
     return p + (f"/{name}" if name else "")
 
 
@@ -88,6 +88,14 @@ def print_table(kind: str, items: List[dict]) -> None:
             cs = (o.get("status", {}).get("containerStatuses") or [{}])[0]
             rows.append((c.name_of(o), o.get("status", {}).get("phase", "Pending"), str(cs.get("restartCount", 0)),
                          _age(o["metadata"].get("creationTimestamp")), o.get("spec", {}).get("nodeName", "")))
+    elif kind == "Node":
+        rows = [("NAME", "STATUS", "GPUS FREE/TOTAL", "HEARTBEAT", "AGE")]
+        for o in items:
+            stt = o.get("status", {})
+            ready = next((cd for cd in stt.get("conditions") or [] if cd.get("type") == "Ready"), {})
+            rows.append((c.name_of(o), "Ready" if ready.get("status") == "True" else "NotReady",
+                         f"{stt.get('allocatable', {}).get('nvidia.com/gpu', '?')}/{stt.get('capacity', {}).get('nvidia.com/gpu', '?')}",
+                         _age(ready.get("lastHeartbeatTime")) + " ago", _age(o["metadata"].get("creationTimestamp"))))
     else:
         rows = [("NAME", "AGE")] + [(c.name_of(o), _age(o["metadata"].get("creationTimestamp"))) for o in items]
     w = [max(len(r[i]) for r in rows) for i in range(len(rows[0]))]

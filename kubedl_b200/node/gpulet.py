@@ -22,6 +22,7 @@ kube-dns do the rest (SURVEY.md §1 boundaries).  On a single box gpulet plays t
 """
 from __future__ import annotations
 
+import json
 import os
 import re
 import shlex
@@ -149,6 +150,8 @@ class Gpulet:
         self._unwatch: List[Callable[[], None]] = []
         self._pool = ThreadPoolExecutor(max_workers=16, thread_name_prefix="gpulet-pod")
         self.launched = 0
+        self._ready_since = c.now_rfc3339()
+        self._node_sig, self._node_at = None, 0.0
         # pre-forked workers (node/zygote.py): pods fork from a process that has imported torch
         if prefork is None:
             prefork = os.environ.get("KUBEDL_GPULET_PREFORK", "0") == "1"
@@ -259,9 +262,53 @@ class Gpulet:
             try:
                 self._admit()
                 self._reap()
+                self._heartbeat()
             except Exception as e:  # keep the node alive
                 log.error("gpulet loop error: %s", e)
             time.sleep(0.01)
+
+    # ------------------------------------------------------------------ Node object
+    def node_object(self) -> dict:
+        """What a kubelet registers: capacity, what is still allocatable, and a Ready condition whose
+        heartbeat shows the agent is alive (`kubedlctl get nodes`)."""
+        now = c.now_rfc3339()
+        with self._lock:
+            free, used = len(self.free_gpus), dict(self._gpu_of)
+        return {"apiVersion": "v1", "kind": "Node",
+                "metadata": {"name": self.node_name, "namespace": "default",
+                             "labels": {"kubernetes.io/hostname": self.node_name, "kubedl-b200/accelerator": "nvidia-b200"},
+                             "annotations": {"kubedl-b200/gpu-assignments": json.dumps(
+                                 {f"{ns}/{name}": g for (ns, name), g in sorted(used.items())})}},
+                "status": {"capacity": {"nvidia.com/gpu": str(self.num_gpus), "cpu": str(os.cpu_count() or 1), "pods": "110"},
+                           "allocatable": {"nvidia.com/gpu": str(free), "cpu": str(os.cpu_count() or 1), "pods": "110"},
+                           "addresses": [{"type": "InternalIP", "address": "127.0.0.1"},
+                                         {"type": "Hostname", "address": self.node_name}],
+                           "nodeInfo": {"kubeletVersion": "kubedl-b200-gpulet", "operatingSystem": "linux"},
+                           "conditions": [{"type": "Ready", "status": "True", "reason": "GpuletReady",
+                                           "message": "node agent is posting ready status",
+                                           "lastHeartbeatTime": now, "lastTransitionTime": self._ready_since}]}}
+
+    def _heartbeat(self, force: bool = False) -> None:
+        """Register / refresh the Node: every 10 s, and at once when the GPU assignment changed."""
+        with self._lock:
+            sig = (len(self.free_gpus), tuple(sorted(self._gpu_of.items())))
+        now = time.monotonic()
+        if not force and sig == self._node_sig and now - self._node_at < 10.0:
+            return
+        self._node_sig, self._node_at = sig, now
+        node = self.node_object()
+        try:
+            cur = self.api.get("Node", "default", self.node_name)
+            node["metadata"]["resourceVersion"] = cur["metadata"].get("resourceVersion")
+            self.api.update(node)
+        except NotFound:
+            try:
+                self.api.create(node)
+            except Exception as e:
+                log.debug("node registration: %s", e)
+        except Exception as e:      # a conflict or an API hiccup: the next beat repairs it
+            log.debug("node heartbeat: %s", e)
+            self._node_at = 0.0
 
     def _admit(self) -> None:
         with self._lock:

@@ -2,6 +2,7 @@
 through the controllers and the node agent — real processes, real gloo rendezvous wired only by
 the injected env — until the job reports Succeeded; plus the gpulet helpers."""
 import os
+import sys
 import time
 
 import pytest
@@ -209,5 +210,38 @@ def test_xgboost_train_then_predict_jobs(tmp_path, monkeypatch):
         assert pr["job_type"] == "Predict" and pr["trees"] == 3 and pr["rows"] == 12000
         assert abs(pr["logloss"] - train_loss) < 1e-4 and pr["accuracy"] > 0.55
     finally:
+        let.stop()
+        mgr.stop()
+
+
+def test_node_agent_registers_a_node(capsys):
+    """The agent shows up as a Node with its GPU capacity, what is still free, and a heartbeat —
+    what `kubectl get nodes` shows for a kubelet."""
+    from kubedl_b200.apiserver import rest
+    from kubedl_b200.cmd import kubedlctl
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=4, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}", node_name="box-7")
+    let.start()
+    srv = rest.serve(mgr.api, "127.0.0.1", 0)
+    try:
+        node = _wait(lambda: mgr.api.list("Node"), timeout=10)[0]
+        assert node["metadata"]["name"] == "box-7"
+        assert node["status"]["capacity"]["nvidia.com/gpu"] == "4" and node["status"]["allocatable"]["nvidia.com/gpu"] == "4"
+        assert node["status"]["conditions"][0]["type"] == "Ready" and node["status"]["conditions"][0]["status"] == "True"
+        # a pod that asks for a GPU shows up in the node's books at once
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "g", "namespace": "d"},
+                        "spec": {"restartPolicy": "Never", "containers": [{
+                            "name": "c", "image": "x", "command": [sys.executable, "-c", "import time; time.sleep(2)"],
+                            "resources": {"limits": {"nvidia.com/gpu": 1}}}]}})
+        _wait(lambda: mgr.api.get("Node", "default", "box-7")["status"]["allocatable"]["nvidia.com/gpu"] == "3", timeout=10)
+        import json as _json
+        assign = _json.loads(mgr.api.get("Node", "default", "box-7")["metadata"]["annotations"]["kubedl-b200/gpu-assignments"])
+        assert assign == {"d/g": 0}
+        assert kubedlctl.main(["-s", srv.url.split("//")[1], "get", "nodes"]) == 0
+        out = capsys.readouterr().out
+        assert "box-7" in out and "Ready" in out and "3/4" in out
+        _wait(lambda: mgr.api.get("Node", "default", "box-7")["status"]["allocatable"]["nvidia.com/gpu"] == "4", timeout=15)
+    finally:
+        srv.shutdown()
         let.stop()
         mgr.stop()

@@ -125,7 +125,7 @@ class _Proc:
 class Gpulet:
     def __init__(self, api: APIServer, num_gpus: Optional[int] = None, registry: Optional[ImageRegistry] = None,
                  log_dir: str = "/tmp/kubedl-b200/pods", node_name: str = "b200-node-0",
-                 default_gpu_per_pod: bool = False, prefork: Optional[bool] = None):
+                 default_gpu_per_pod: bool = False, prefork: Optional[bool] = None, multi_node: bool = False):
         self.api = api
         self.registry = registry or ImageRegistry()
         if num_gpus is None:
@@ -150,6 +150,9 @@ class Gpulet:
         self._unwatch: List[Callable[[], None]] = []
         self._pool = ThreadPoolExecutor(max_workers=16, thread_name_prefix="gpulet-pod")
         self.launched = 0
+        # several node agents on one API server: a job runs where its binding Lease was won
+        self.multi_node = multi_node
+        self._bindings: Dict[Tuple[str, str], bool] = {}
         self._ready_since = c.now_rfc3339()
         self._node_sig, self._node_at = None, 0.0
         # pre-forked workers (node/zygote.py): pods fork from a process that has imported torch
@@ -310,12 +313,60 @@ class Gpulet:
             log.debug("node heartbeat: %s", e)
             self._node_at = 0.0
 
+    def _binds_here(self, pod: dict) -> bool:
+        """Multi-node: which agent runs a job is decided once per job by creating a Lease
+        `node-binding-<job>` (create is atomic: exactly one agent succeeds).  All pods of a job land
+        on one box on purpose — the fused collectives need the ranks in one NVSwitch domain, and the
+        loopback rendezvous addresses stay valid.  The Lease is owned by the job and goes with it.
+        An agent only bids when it could start the pod now (gang complete, GPU free)."""
+        if not self.multi_node:
+            return True
+        ns = c.namespace_of(pod)
+        bound = pod.get("spec", {}).get("nodeName")
+        if bound:
+            return bound == self.node_name
+        unit = c.labels_of(pod).get(c.JOB_NAME_LABEL) or f"pod-{c.name_of(pod)}"
+        with self._lock:
+            if (ns, unit) in self._bindings:
+                return self._bindings[(ns, unit)]
+        name = f"node-binding-{unit}"
+        owner = c.controller_ref(pod)
+        lease = {"apiVersion": "coordination.k8s.io/v1", "kind": "Lease",
+                 "metadata": {"name": name, "namespace": ns, "labels": {"kubedl-b200/node": self.node_name},
+                              "ownerReferences": [owner] if owner else []},
+                 "spec": {"holderIdentity": self.node_name, "acquireTime": c.now_precise()}}
+        try:
+            self.api.create(lease)
+            mine = True
+        except Exception as e:
+            from ..apiserver.store import is_already_exists
+            if not is_already_exists(e):
+                log.warning("binding %s/%s: %s", ns, unit, e)
+                return False            # not cached: try again on the next pass
+            try:
+                mine = (self.api.get("Lease", ns, name).get("spec") or {}).get("holderIdentity") == self.node_name
+            except NotFound:
+                return False
+        with self._lock:
+            self._bindings[(ns, unit)] = mine
+            if len(self._bindings) > 20000:
+                for k in list(self._bindings)[:10000]:
+                    del self._bindings[k]
+        return mine
+
     def _admit(self) -> None:
         with self._lock:
             pending = dict(self._pending)
         for key, pod in sorted(pending.items()):
             if not self._gang_ready(pod, pending):
                 continue
+            if self.multi_node:
+                if self._wants_gpu(pod) and not self.free_gpus:
+                    continue          # do not bid for what cannot start here now
+                if not self._binds_here(pod):
+                    with self._lock:
+                        self._pending.pop(key, None)      # another box runs this job
+                    continue
             gpu = None
             if self._wants_gpu(pod):
                 with self._lock:

@@ -245,3 +245,46 @@ def test_node_agent_registers_a_node(capsys):
         srv.shutdown()
         let.stop()
         mgr.stop()
+
+
+def test_two_node_agents_share_one_api_server(tmp_path):
+    """--multi-node: two agents bid for every job with a Lease; each job runs exactly once, with all
+    its pods on the box that won it."""
+    mgr = Manager()
+    gang_schedule.register_gang_schedulers(mgr)
+    setup_with_manager(mgr, JobControllerConfiguration(), "*", CollectorRegistry())
+    a = Gpulet(mgr.api, num_gpus=0, log_dir=str(tmp_path / "a"), node_name="box-a", multi_node=True)
+    b = Gpulet(mgr.api, num_gpus=0, log_dir=str(tmp_path / "b"), node_name="box-b", multi_node=True)
+    mgr.start()
+    a.start()
+    b.start()
+    try:
+        t = lambda: tmpl("tensorflow", image="kubedl-b200/tf-lifecycle-stub",
+                         env=[{"name": "KUBEDL_TF_TRAIN_SECONDS", "value": "0.3"}])
+        names = [f"mn{i}" for i in range(6)]
+        for n in names:
+            mgr.api.create(k.new_job("TFJob", n, "mn", {"Worker": {"replicas": 3, "restartPolicy": "Never", "template": t()}},
+                                     cleanPodPolicy="None"))
+        for n in names:
+            conds = _wait(lambda n=n: _terminal(mgr, "TFJob", "mn", n), timeout=120)
+            assert conds[-1] == "Succeeded", (n, conds)
+        assert a.launched + b.launched == 18                       # every pod started exactly once
+        holders = {}
+        for n in names:
+            nodes = {p["spec"].get("nodeName") for p in mgr.api.list("Pod", "mn", {c.JOB_NAME_LABEL: n})}
+            assert len(nodes) == 1 and nodes <= {"box-a", "box-b"}, (n, nodes)     # a job stays on one box
+            lease = mgr.api.get("Lease", "mn", f"node-binding-{n}")
+            assert lease["spec"]["holderIdentity"] == next(iter(nodes))
+            holders[n] = lease["spec"]["holderIdentity"]
+        # pods of a box have their logs on that box only
+        for n, node in holders.items():
+            mine, other = (a, b) if node == "box-a" else (b, a)
+            assert "TF_CONFIG ok" in mine.pod_log("mn", f"{n}-worker-0") and other.pod_log("mn", f"{n}-worker-0") == ""
+        # the binding goes away with the job
+        mgr.api.delete("TFJob", "mn", names[0])
+        _wait(lambda: not [l for l in mgr.api.list("Lease", "mn") if c.name_of(l) == f"node-binding-{names[0]}"], timeout=10)
+        assert {c.name_of(nd) for nd in mgr.api.list("Node")} == {"box-a", "box-b"}
+    finally:
+        a.stop()
+        b.stop()
+        mgr.stop()

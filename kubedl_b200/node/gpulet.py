@@ -103,6 +103,18 @@ class ImageRegistry:
         raise RuntimeError(f"image {image!r} is not in the local image registry and the container has no command")
 
 
+def _cpu_threads(container: dict) -> int:
+    """Threads for a container: its CPU limit rounded up (`2`, `1500m`), else 1."""
+    lim = ((container.get("resources") or {}).get("limits") or {}).get("cpu")
+    if lim in (None, ""):
+        return 1
+    try:
+        v = float(str(lim)[:-1]) / 1000.0 if str(lim).endswith("m") else float(lim)
+    except ValueError:
+        return 1
+    return max(1, int(-(-v // 1)))
+
+
 def free_port() -> int:
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -436,6 +448,10 @@ class Gpulet:
         if "MASTER_PORT" in declared and job:
             declared["MASTER_PORT"] = str(self._host_port(ns, job, int(declared["MASTER_PORT"])))
         env.update(declared)
+        if "OMP_NUM_THREADS" not in env:
+            # what torchrun does, for the same reason: N pods with one intra-op thread pool per core each
+            # oversubscribe the box N-fold.  A CPU limit on the container is honoured instead.
+            env["OMP_NUM_THREADS"] = str(_cpu_threads(container))
         env["KUBEDL_POD_NAME"] = c.name_of(pod)
         env["KUBEDL_POD_NAMESPACE"] = ns
         env["KUBEDL_JOB_NAME"] = job

@@ -383,6 +383,9 @@ def main(argv=None) -> int:
         from . import tf_stub
         return tf_stub.main(argv)
     args, _ = build_parser().parse_known_args(argv)
+    # several replicas share a box: with torch's default of one intra-op thread per core each, six pods
+    # on eight cores spend their time fighting (0.3 s/step); this model needs one thread
+    torch.set_num_threads(max(1, int(os.environ.get("KUBEDL_TF_THREADS", "1"))))
     cfg = tf_config()
     total = flat_params(build_model()).numel()
     if cfg is None:

@@ -288,3 +288,23 @@ def test_two_node_agents_share_one_api_server(tmp_path):
         a.stop()
         b.stop()
         mgr.stop()
+
+
+def test_pod_thread_budget():
+    """One intra-op thread per pod unless the container has a CPU limit (what torchrun does)."""
+    from kubedl_b200.node.gpulet import _cpu_threads
+    assert _cpu_threads({}) == 1
+    assert _cpu_threads({"resources": {"limits": {"cpu": "1500m"}}}) == 2
+    assert _cpu_threads({"resources": {"limits": {"cpu": 4}}}) == 4
+    assert _cpu_threads({"resources": {"limits": {"cpu": "garbage"}}}) == 1
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=0, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}")
+    pod = {"kind": "Pod", "metadata": {"name": "p", "namespace": "d", "labels": {}}, "spec": {}}
+    saved = os.environ.pop("OMP_NUM_THREADS", None)
+    try:
+        assert let.build_env(pod, {"name": "c"}, None)["OMP_NUM_THREADS"] == "1"
+        assert let.build_env(pod, {"name": "c", "resources": {"limits": {"cpu": "3"}}}, None)["OMP_NUM_THREADS"] == "3"
+        assert let.build_env(pod, {"name": "c", "env": [{"name": "OMP_NUM_THREADS", "value": "7"}]}, None)["OMP_NUM_THREADS"] == "7"
+    finally:
+        if saved is not None:
+            os.environ["OMP_NUM_THREADS"] = saved

@@ -31,7 +31,28 @@ launch-delay:
 sass:
 	cuobjdump -sass kubedl_b200/_lib/libkubedl_b200.so | grep -E "UTCHMMA|UTMALDG|UTMASTG|LDTM|MULTIMEM" | sort | uniq -c
 
-docker-build:
-	docker build . -t kubedl-b200/manager:latest
+IMG ?= kubedl-b200/manager:latest
+KUBECTL ?= kubectl
 
-.PHONY: all lib run test test-gpu manifests bench launch-delay sass docker-build
+docker-build:
+	docker build . -t $(IMG)
+
+docker-push:
+	docker push $(IMG)
+
+# Against a Kubernetes cluster (reference Makefile:29-36): CRDs only, or CRDs + RBAC + operator Deployment
+install: manifests
+	$(KUBECTL) apply -f config/crd/v1
+
+deploy: manifests
+	$(KUBECTL) apply -f config/manager/all_in_one.yaml
+
+# Operator on this machine against the cluster of the current kubeconfig (reference `make run`)
+run-cluster:
+	$(PY) -m kubedl_b200.cmd.manager --in-cluster --enable-leader-election=false
+
+# Static checks the reference runs before every build (go fmt / go vet): byte-compile everything
+vet:
+	$(PY) -m compileall -q kubedl_b200 tests bench.py __graft_entry__.py
+
+.PHONY: all lib run test test-gpu manifests bench launch-delay sass docker-build docker-push install deploy run-cluster vet

@@ -38,6 +38,10 @@ def init_distributed(backend: str = "nccl"):
         kw = {}
         if backend == "nccl" and torch.cuda.is_available():
             kw["device_id"] = torch.device("cuda", torch.cuda.current_device())
+        if os.environ.get("KUBEDL_RENDEZVOUS_TIMEOUT"):
+            # bound the wait for peers that never come (docs/fault_tolerance.md); unset = torch's default
+            import datetime
+            kw["timeout"] = datetime.timedelta(seconds=float(os.environ["KUBEDL_RENDEZVOUS_TIMEOUT"]))
         dist.init_process_group(backend=backend, init_method="env://", rank=rank, world_size=world, **kw)
     return rank, world, local_rank
 

@@ -234,7 +234,7 @@ class Gpulet:
             else:
                 p = None
         if ev == DELETED and p is not None:
-            self._kill(p)
+            self._terminate(p, pod)
 
     # ------------------------------------------------------------------ scheduling
     def _wants_gpu(self, pod: dict) -> bool:
@@ -581,6 +581,24 @@ class Gpulet:
                          container_statuses=[{"name": proc.container, "ready": True,
                                               "restartCount": proc.restart_count,
                                               "state": {"running": {"startedAt": proc.started_at}}}])
+
+    def _terminate(self, proc: _Proc, pod: dict) -> None:
+        """Pod deleted: SIGTERM to its process group, SIGKILL after the grace period if it is still
+        there — the kubelet's sequence, so a worker can write its checkpoint on the way out.
+        `terminationGracePeriodSeconds` of the pod is honoured (default here 5 s, not 30: a deleted
+        pod's GPU is wanted back quickly on a single box)."""
+        grace = (pod.get("spec") or {}).get("terminationGracePeriodSeconds")
+        grace = float(grace) if grace is not None else float(os.environ.get("KUBEDL_GPULET_GRACE_SECONDS", "5"))
+        if grace <= 0:
+            return self._kill(proc)
+        self._kill(proc, signal.SIGTERM)
+
+        def reap():
+            if proc.popen.poll() is None:
+                self._kill(proc, signal.SIGKILL)
+        t = threading.Timer(grace, reap)
+        t.daemon = True
+        t.start()
 
     def _kill(self, proc: _Proc, sig: int = signal.SIGKILL) -> None:
         try:

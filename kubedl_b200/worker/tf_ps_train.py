@@ -415,6 +415,9 @@ def main(argv=None) -> int:
         srv = serve_shard(shard, os.environ.get("KUBEDL_BIND_ADDR", "0.0.0.0"), port)
         print(f"ps:{tindex} serving parameters [{lo}, {hi}) of {total} on port {port} "
               f"({'sync' if args.sync_replicas else 'async'}, {n_workers} workers)", flush=True)
+        # a deleted pod gets SIGTERM first (node agent and kubelet alike): stop serving, save, leave
+        import signal as _signal
+        _signal.signal(_signal.SIGTERM, lambda *_: shard.stop.set())
         deadline = time.monotonic() + float(os.environ.get("KUBEDL_TF_PS_SECONDS", "86400"))
         saved = shard.version
         while not shard.stop.wait(args.checkpoint_every if ckpt else 3600.0) and time.monotonic() < deadline:

@@ -152,6 +152,32 @@ def test_tfjob_ps_worker_training_async(tmp_path):
     _wait(lambda: not [p for p in mgr.api.list("Pod", "kubedl") if "-ps-" in p["metadata"]["name"]], timeout=20)
 
 
+def test_ps_saves_its_shard_when_the_pod_is_deleted(tmp_path):
+    """cleanPodPolicy removes the PS pods when the job ends; they get SIGTERM, write a last checkpoint
+    and leave, so nothing after the periodic save is lost."""
+    mgr, let = _cluster(tmp_path)
+    try:
+        ck = tmp_path / "ckpt"
+        env = [{"name": "KUBEDL_TF_STEPS", "value": "25"}, {"name": "KUBEDL_TF_DEVICE", "value": "cpu"},
+               {"name": "KUBEDL_TF_CHECKPOINT_DIR", "value": str(ck)}]
+        t = lambda: tmpl("tensorflow", image="kubedl/tf-mnist-with-summaries:1.0", env=list(env),
+                         args=["--learning_rate=0.02", "--momentum=0.5", "--checkpoint_every=3600"])
+        mgr.api.create(new_job("TFJob", "ck", "kubedl", replica_specs={
+            "PS": {"replicas": 1, "template": t()}, "Worker": {"replicas": 1, "template": t()}}))
+
+        def terminal():
+            conds = [x["type"] for x in mgr.api.get("TFJob", "kubedl", "ck").get("status", {}).get("conditions", [])]
+            return conds if conds and conds[-1] in ("Succeeded", "Failed") else None
+        assert _wait(terminal)[-1] == "Succeeded"
+        _wait(lambda: (ck / "ps-0.pt").exists(), timeout=20)             # periodic saving was off: this is the SIGTERM save
+        state = torch.load(ck / "ps-0.pt", weights_only=False)
+        assert state["version"] == 25 and state["pushes"] == 25
+        _wait(lambda: "stopping at version 25" in let.pod_log("kubedl", "ck-ps-0"), timeout=10)
+    finally:
+        let.stop()
+        mgr.stop()
+
+
 def test_tfjob_ps_worker_training_sync(tmp_path):
     _, logs = _run_tfjob(tmp_path, "psync", sync=True)
     assert "(sync, 2 workers)" in logs["ps-0"]

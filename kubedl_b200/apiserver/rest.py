@@ -1,6 +1,6 @@
 """REST front of the in-process API server, speaking the Kubernetes wire protocol.
 
-`kubedlctl`, curl, `kubectl --server` and — most importantly — the operator itself (through
+`kubedlctl`, curl and — most importantly — the operator itself (through
 `apiserver/kube.py::KubeAPIServer`, the client it also uses against a real kube-apiserver) talk
 to it.  The reference reaches its API server through client-go / controller-runtime
 (reference main.go:70-75, pkg/util/k8sutil/k8sutil.go:44-69); this is the server side of that

@@ -4,8 +4,9 @@ The all-in-one manager keeps cluster state in its own process.  For the referenc
 shape — state in an API server, the operator as one client of it, node agents as others
 (reference config/manager/all_in_one.yaml) — run this, then point
 `python -m kubedl_b200.cmd.manager --master URL` and `python -m kubedl_b200.cmd.gpulet --master URL`
-at it.  It serves the Kubernetes wire protocol (`apiserver/rest.py`), so `kubectl --server URL`
-and `kubedlctl --server` work against it too.
+at it.  It serves the Kubernetes wire protocol (`apiserver/rest.py`): `kubedlctl --server URL` and
+`kubedlctl --kubeconfig` work against it (kubectl's discovery / list / watch calls are the same ones, but
+kubectl is not in this image and has not been tried).
 
 State is in memory; `--state FILE` loads a snapshot at start and writes one at exit (and every
 `--snapshot-interval` seconds), which is enough for an operator restart test, not a database.

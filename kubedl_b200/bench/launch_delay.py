@@ -54,7 +54,7 @@ def _job(kind: str, name: str, replicas: int, seconds: float) -> dict:
 
 
 def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1, remote: bool = False,
-        create_parallelism: int = 1, api_latency: float = 0.0) -> dict:
+        create_parallelism: int = 1, api_latency: float = 0.0, prefork: bool = False) -> dict:
     """remote=True puts the API server behind HTTP (`apiserver/rest.py`) with the node agent next to
     it, and makes the operator a client of it (`apiserver/kube.py`) — the reference's deployment
     shape, where every pod / service create and every status write is a round trip."""
@@ -68,13 +68,18 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
         from ..node.gpulet import Gpulet
         backing = APIServer()
         srv = rest.serve(backing, "127.0.0.1", 0, latency=api_latency)
-        let = Gpulet(backing, num_gpus=0)
+        let = Gpulet(backing, num_gpus=0, prefork=prefork)
         let.start()
         extra = [let.stop, srv.shutdown]
         flags += ["--master", srv.url]
+    if prefork and not remote:
+        flags.append("--prefork-workers")
     args = M.build_parser().parse_args(flags)
     op = M.build_operator(args, metrics_registry=reg)
     M.start_operator(op, args, metrics_registry=reg)
+    if prefork:
+        z = (let if remote else op.gpulet).zygote
+        z.ready.wait(300)
     done_times = []
     # the bench's own polling must not load the wire it is measuring: watch the state where it lives
     state = backing if remote else op.mgr.api
@@ -101,7 +106,7 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
                 "all_pods_ms": {"p50": 1e3 * _pct(allp, 0.5), "p90": 1e3 * _pct(allp, 0.9), "n": len(allp)},
                 "time_to_succeeded_ms": {"p50": 1e3 * _pct(done_times, 0.5), "p90": 1e3 * _pct(done_times, 0.9)},
                 "api_creates_per_job": creates / jobs, "api": "http" if remote else "in-process",
-                "pod_create_parallelism": create_parallelism, "api_latency_ms": 1e3 * api_latency}
+                "pod_create_parallelism": create_parallelism, "api_latency_ms": 1e3 * api_latency, "prefork": prefork}
     finally:
         op.stop()
         for fn in extra:
@@ -118,10 +123,11 @@ def main(argv=None) -> int:
     ap.add_argument("--max-reconciles", type=int, default=1)
     ap.add_argument("--create-parallelism", type=int, default=1)
     ap.add_argument("--api-latency-ms", type=float, default=0.0, help="with --remote: added to every API request")
+    ap.add_argument("--prefork", action="store_true", help="node agent forks `python -m` pods from its launcher")
     a = ap.parse_args(argv)
     for kind in a.kinds.split(","):
         print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds, a.max_reconciles, a.remote, a.create_parallelism,
-                             a.api_latency_ms / 1e3)), flush=True)
+                             a.api_latency_ms / 1e3, a.prefork)), flush=True)
     return 0
 
 

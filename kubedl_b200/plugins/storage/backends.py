@@ -5,9 +5,11 @@ EventStorageBackend), query.go:25-41; registry: backends/registry/registry.go:26
 
   "mysql"        object backend.  Same tables/columns as the reference's gorm models
                  (job_info, replica_info; reference backends/objects/mysql/mysql.go:46-443,
-                 env MYSQL_HOST/PORT/DB_NAME/USER/PASSWORD, config.go:41-62).  No MySQL server or
-                 driver exists on this box, so the SQL runs on sqlite3 (file or :memory:,
-                 `MYSQL_DB_NAME` = path); the statements are plain ANSI SQL.  The reference's
+                 env MYSQL_HOST/PORT/DB_NAME/USER/PASSWORD, config.go:41-62).  With MYSQL_HOST set and
+                 a DB-API driver installed (pymysql / MySQLdb / mysql.connector) it connects to that
+                 server; neither exists on this box, where the same statements (plain ANSI SQL, `?`
+                 placeholders rewritten for the driver) run on sqlite3 (file or :memory:,
+                 `MYSQL_DB_NAME` = path).  The reference's
                  queries against non-existent columns (gmt_create / gmt_submit / is_del,
                  mysql.go:113,192-195,212) are written against the real ones.
   "aliyun-sls"   event backend.  The reference ships events to an Aliyun SLS logstore with
@@ -92,13 +94,59 @@ def _cols(cls) -> List[str]:
     return [f.name for f in fields(cls)]
 
 
+class _Db:
+    """The little of DB-API the backend needs, over sqlite3 or a MySQL driver: `execute` with `?`
+    placeholders (rewritten to the driver's `%s`), `commit`, `close`."""
+
+    def __init__(self, conn, paramstyle: str = "qmark", dialect: str = "sqlite"):
+        self.conn, self.paramstyle, self.dialect = conn, paramstyle, dialect
+
+    def execute(self, sql: str, args=()):
+        if self.paramstyle in ("format", "pyformat"):
+            sql = sql.replace("%", "%%").replace("?", "%s")
+        cur = self.conn.cursor()
+        cur.execute(sql, tuple(args))
+        return cur
+
+    def commit(self) -> None:
+        self.conn.commit()
+
+    def close(self) -> None:
+        self.conn.close()
+
+
+def mysql_driver():
+    """The first importable MySQL DB-API module (none ships in this image), else None."""
+    import importlib
+    for name in ("pymysql", "MySQLdb", "mysql.connector"):
+        try:
+            return importlib.import_module(name)
+        except ImportError:
+            continue
+    return None
+
+
+def open_object_db(path: Optional[str] = None, env=os.environ, driver=None) -> _Db:
+    """MYSQL_HOST set and a driver present -> that MySQL server (MYSQL_HOST / MYSQL_PORT / MYSQL_DB_NAME /
+    MYSQL_USER / MYSQL_PASSWORD, reference backends/objects/mysql/config.go:41-62); otherwise sqlite3
+    on `path` / MYSQL_DB_NAME / memory."""
+    host = env.get("MYSQL_HOST", "")
+    driver = driver if driver is not None else (mysql_driver() if host else None)
+    if host and driver is not None and not path:
+        kw = dict(host=host, port=int(env.get("MYSQL_PORT", "3306") or 3306), user=env.get("MYSQL_USER", "root"),
+                  password=env.get("MYSQL_PASSWORD", ""), database=env.get("MYSQL_DB_NAME", "kubedl"))
+        return _Db(driver.connect(**kw), getattr(driver, "paramstyle", "format"), "mysql")
+    return _Db(sqlite3.connect(path or env.get("MYSQL_DB_NAME") or ":memory:", check_same_thread=False), "qmark", "sqlite")
+
+
 class SqlObjectBackend(ObjectStorageBackend):
     """job_info / replica_info with upsert guarded by resourceVersion (newer wins) and terminal
     status stickiness, like reference mysql.go:291-414."""
 
-    def __init__(self, path: Optional[str] = None):
-        self.path = path or os.environ.get("MYSQL_DB_NAME") or ":memory:"
-        self._db: Optional[sqlite3.Connection] = None
+    def __init__(self, path: Optional[str] = None, driver=None):
+        self.path = path
+        self._driver = driver
+        self._db: Optional[_Db] = None
         self._lock = threading.RLock()
         self._initialized = False
 
@@ -109,12 +157,24 @@ class SqlObjectBackend(ObjectStorageBackend):
         with self._lock:
             if self._initialized:
                 return
-            self._db = sqlite3.connect(self.path, check_same_thread=False)
+            self._db = open_object_db(self.path, driver=self._driver)
+            mysql = self._db.dialect == "mysql"
+            keyed = ("namespace", "name", "job_id", "pod_id")            # indexed: bounded type on MySQL
             for cls in (dmo.Job, dmo.Pod):
-                cols = ", ".join(f"{n} TEXT" if n not in ("deleted", "is_in_etcd") else f"{n} INTEGER" for n in _cols(cls))
-                self._db.execute(f"CREATE TABLE IF NOT EXISTS {cls.TABLE} (id INTEGER PRIMARY KEY AUTOINCREMENT, {cols})")
-            self._db.execute("CREATE INDEX IF NOT EXISTS idx_job ON job_info (namespace, name, job_id)")
-            self._db.execute("CREATE INDEX IF NOT EXISTS idx_pod ON replica_info (namespace, name, pod_id)")
+                def coltype(n):
+                    if n in ("deleted", "is_in_etcd"):
+                        return "INTEGER"
+                    return "VARCHAR(255)" if mysql and n in keyed else "TEXT"
+                cols = ", ".join(f"{n} {coltype(n)}" for n in _cols(cls))
+                pk = "id BIGINT PRIMARY KEY AUTO_INCREMENT" if mysql else "id INTEGER PRIMARY KEY AUTOINCREMENT"
+                self._db.execute(f"CREATE TABLE IF NOT EXISTS {cls.TABLE} ({pk}, {cols})")
+            for ddl in ("CREATE INDEX {ine}idx_job ON job_info (namespace, name, job_id)",
+                        "CREATE INDEX {ine}idx_pod ON replica_info (namespace, name, pod_id)"):
+                try:
+                    self._db.execute(ddl.format(ine="" if mysql else "IF NOT EXISTS "))
+                except Exception:          # MySQL has no IF NOT EXISTS for indexes: "duplicate key name" on restart
+                    if not mysql:
+                        raise
             self._db.commit()
             self._initialized = True
 

@@ -194,3 +194,74 @@ def test_persist_controllers_full_loop(tmp_path):
     finally:
         B.REGISTRY.remove_object_backend("mysql")
         B.REGISTRY.remove_event_backend("aliyun-sls")
+
+
+def test_mysql_driver_path_with_a_fake_driver(monkeypatch):
+    """MYSQL_HOST + a DB-API driver -> the backend talks to that server.  No MySQL here, so the
+    "driver" is a shim with MySQL's `%s` parameter style and DDL dialect over sqlite: it checks the
+    placeholder rewriting, the DDL branch and the connection parameters."""
+    import re
+    import sqlite3
+    from kubedl_b200.plugins.storage import backends as B
+    seen = {}
+
+    class Cursor:
+        def __init__(self, cur):
+            self.cur = cur
+
+        def execute(self, sql, args=()):
+            assert "?" not in sql, sql                                   # placeholders were rewritten
+            seen.setdefault("sql", []).append(sql)
+            sql = sql.replace("%s", "?").replace("%%", "%")
+            sql = sql.replace("BIGINT PRIMARY KEY AUTO_INCREMENT", "INTEGER PRIMARY KEY AUTOINCREMENT")
+            sql = re.sub(r"VARCHAR\\(\\d+\\)", "TEXT", sql)
+            return self.cur.execute(sql, args)
+
+        def fetchone(self):
+            return self.cur.fetchone()
+
+        def fetchall(self):
+            return self.cur.fetchall()
+
+    class Conn:
+        def __init__(self):
+            self.db = sqlite3.connect(":memory:", check_same_thread=False)
+
+        def cursor(self):
+            return Cursor(self.db.cursor())
+
+        def commit(self):
+            self.db.commit()
+
+        def close(self):
+            self.db.close()
+
+    class Driver:
+        paramstyle = "format"
+
+        @staticmethod
+        def connect(**kw):
+            seen["connect"] = kw
+            return Conn()
+
+    monkeypatch.setenv("MYSQL_HOST", "db.internal")
+    monkeypatch.setenv("MYSQL_PORT", "3307")
+    monkeypatch.setenv("MYSQL_USER", "kubedl")
+    monkeypatch.setenv("MYSQL_PASSWORD", "pw")
+    monkeypatch.setenv("MYSQL_DB_NAME", "kubedl_prod")
+    be = B.SqlObjectBackend(driver=Driver)
+    be.initialize()
+    assert seen["connect"] == {"host": "db.internal", "port": 3307, "user": "kubedl", "password": "pw", "database": "kubedl_prod"}
+    assert any("AUTO_INCREMENT" in q and "VARCHAR(255)" in q for q in seen["sql"])
+    be.initialize()                                                       # idempotent
+    be.save_pod(_pod(phase="Running"), "tensorflow", "cn")
+    be.save_pod(_pod(phase="Succeeded"), "tensorflow", "cn")
+    (row,) = be.list_pods("job-uid", "cn")
+    assert row.status == "Succeeded"
+    be.stop_pod(row.namespace, row.name, row.pod_id)
+    assert be.list_pods("job-uid", "cn")[0].is_in_etcd == 0
+    be.close()
+    # no driver, or no MYSQL_HOST: sqlite, as before
+    monkeypatch.delenv("MYSQL_HOST")
+    monkeypatch.setenv("MYSQL_DB_NAME", ":memory:")
+    assert B.open_object_db().dialect == "sqlite"

@@ -129,7 +129,8 @@ def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None)
     pers = persist.setup_with_manager(mgr, args.object_storage, args.event_storage, args.region, args.workloads)
     # against a cluster the pods belong to its kubelets (or to a separate gpulet process)
     let = None if (args.no_node_agent or remote) else Gpulet(mgr.api, num_gpus=args.gpus,
-                                                                  prefork=True if getattr(args, "prefork_workers", False) else None)
+                                                                  prefork=True if getattr(args, "prefork_workers", False) else None,
+                                                                  metrics_registry=metrics_registry or metrics_mod.DEFAULT_REGISTRY)
     return Operator(mgr, recs, pers, let)
 
 

@@ -137,7 +137,8 @@ class _Proc:
 class Gpulet:
     def __init__(self, api: APIServer, num_gpus: Optional[int] = None, registry: Optional[ImageRegistry] = None,
                  log_dir: str = "/tmp/kubedl-b200/pods", node_name: str = "b200-node-0",
-                 default_gpu_per_pod: bool = False, prefork: Optional[bool] = None, multi_node: bool = False):
+                 default_gpu_per_pod: bool = False, prefork: Optional[bool] = None, multi_node: bool = False,
+                 metrics_registry=None):
         self.api = api
         self.registry = registry or ImageRegistry()
         if num_gpus is None:
@@ -167,6 +168,13 @@ class Gpulet:
         self._bindings: Dict[Tuple[str, str], bool] = {}
         self._ready_since = c.now_rfc3339()
         self._node_sig, self._node_at = None, 0.0
+        self._start_hist = None
+        if metrics_registry is not None:
+            try:
+                self._register_metrics(metrics_registry)
+            except ValueError as e:      # a second agent on the same registry in one process: first one keeps the series
+                log.debug("node agent metrics not registered: %s", e)
+                self._start_hist = None
         # pre-forked workers (node/zygote.py): pods fork from a process that has imported torch
         if prefork is None:
             prefork = os.environ.get("KUBEDL_GPULET_PREFORK", "0") == "1"
@@ -281,6 +289,22 @@ class Gpulet:
             except Exception as e:  # keep the node alive
                 log.error("gpulet loop error: %s", e)
             time.sleep(0.01)
+
+    # ------------------------------------------------------------------ metrics
+    def _register_metrics(self, registry) -> None:
+        """What a kubelet's /metrics would tell about this box, next to the operator's kubedl_* series."""
+        from prometheus_client import Counter, Gauge, Histogram
+        lab = {"node": self.node_name}
+        g = Gauge("kubedl_gpulet_gpus", "GPUs managed by the node agent", ["node", "state"], registry=registry)
+        g.labels(self.node_name, "total").set_function(lambda: self.num_gpus)
+        g.labels(self.node_name, "free").set_function(lambda: len(self.free_gpus))
+        pods = Gauge("kubedl_gpulet_pods", "Pods on the node agent", ["node", "state"], registry=registry)
+        pods.labels(self.node_name, "running").set_function(lambda: len(self._procs))
+        pods.labels(self.node_name, "pending").set_function(lambda: len(self._pending))
+        self._launched_total = Counter("kubedl_gpulet_pods_launched_total", "Pods started", ["node", "how"], registry=registry)
+        self._start_hist = Histogram("kubedl_gpulet_pod_start_seconds", "Admission to process running, per pod", ["node"],
+                                     buckets=(0.002, 0.005, 0.01, 0.025, 0.05, 0.1, 0.25, 0.5, 1, 2.5, 5, 10),
+                                     registry=registry).labels(**lab)
 
     # ------------------------------------------------------------------ Node object
     def node_object(self) -> dict:
@@ -464,6 +488,7 @@ class Gpulet:
 
     # ------------------------------------------------------------------ launch / status
     def _launch(self, pod: dict, gpu: Optional[int]) -> None:
+        t_launch = time.perf_counter()
         key = (c.namespace_of(pod), c.name_of(pod))
         self._job_of[key] = c.labels_of(pod).get(c.JOB_NAME_LABEL, "")
         now = c.now_precise()
@@ -489,6 +514,9 @@ class Gpulet:
         with self._lock:
             self._procs[key] = proc
         self.launched += 1
+        if self._start_hist is not None:
+            self._start_hist.observe(time.perf_counter() - t_launch)
+            self._launched_total.labels(self.node_name, "fork" if not isinstance(popen, subprocess.Popen) else "exec").inc()
         ready = c.now_precise()
         self._set_status(pod, c.POD_RUNNING, conditions=[
             {"type": "PodScheduled", "status": "True", "lastTransitionTime": now},

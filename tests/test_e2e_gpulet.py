@@ -308,3 +308,26 @@ def test_pod_thread_budget():
     finally:
         if saved is not None:
             os.environ["OMP_NUM_THREADS"] = saved
+
+
+def test_node_agent_metrics():
+    reg = CollectorRegistry()
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=2, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}", node_name="m0", metrics_registry=reg)
+    let.start()
+    try:
+        assert reg.get_sample_value("kubedl_gpulet_gpus", {"node": "m0", "state": "total"}) == 2
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "g", "namespace": "d"},
+                        "spec": {"restartPolicy": "Never", "containers": [{
+                            "name": "c", "image": "x", "command": [sys.executable, "-c", "import time; time.sleep(1.5)"],
+                            "resources": {"limits": {"nvidia.com/gpu": 1}}}]}})
+        _wait(lambda: reg.get_sample_value("kubedl_gpulet_pods", {"node": "m0", "state": "running"}) == 1, timeout=10)
+        assert reg.get_sample_value("kubedl_gpulet_gpus", {"node": "m0", "state": "free"}) == 1
+        assert reg.get_sample_value("kubedl_gpulet_pods_launched_total", {"node": "m0", "how": "exec"}) == 1
+        assert reg.get_sample_value("kubedl_gpulet_pod_start_seconds_count", {"node": "m0"}) == 1
+        _wait(lambda: reg.get_sample_value("kubedl_gpulet_gpus", {"node": "m0", "state": "free"}) == 2, timeout=15)
+        # a second agent on the same registry must not take the process down
+        Gpulet(mgr.api, num_gpus=0, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}", node_name="m1", metrics_registry=reg)
+    finally:
+        let.stop()
+        mgr.stop()

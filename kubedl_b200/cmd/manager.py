@@ -154,7 +154,7 @@ def start_operator(op: Operator, args, metrics_registry=None) -> None:
             log.warning("metrics endpoint on %s unavailable: %s", args.metrics_addr, e)
     if op.mgr.controller_metrics is not None:
         try:
-            srv = controller_metrics.serve(op.mgr.controller_metrics, args.controller_metrics_addr)
+            srv = controller_metrics.serve(op.mgr.controller_metrics, args.controller_metrics_addr, manager=op.mgr)
             if srv is not None:
                 op.servers.append(srv)
         except OSError as e:

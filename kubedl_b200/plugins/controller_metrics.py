@@ -138,14 +138,35 @@ def parse_bind_address(addr: str) -> Optional[Tuple[str, int]]:
     return (host or "0.0.0.0", int(port))
 
 
-def serve(metrics: ControllerMetrics, addr: str) -> Optional[ThreadingHTTPServer]:
+def serve(metrics: ControllerMetrics, addr: str, manager=None) -> Optional[ThreadingHTTPServer]:
+    """`/metrics`, plus — the reference has no tracing at all — `/debug/trace`: the last
+    reconcile spans per controller (key, seconds, error) and `/debug/queues`: depth / delayed / busy per queue."""
     bind = parse_bind_address(addr)
     if bind is None:
         return None
+    import json
 
     class Quiet(MetricsHandler.factory(metrics.registry)):
         def log_message(self, *a):
             pass
+
+        def _json(self, obj) -> None:
+            data = json.dumps(obj).encode()
+            self.send_response(200)
+            self.send_header("Content-Type", "application/json")
+            self.send_header("Content-Length", str(len(data)))
+            self.end_headers()
+            self.wfile.write(data)
+
+        def do_GET(self):
+            path = self.path.split("?")[0]
+            if manager is not None and path == "/debug/trace":
+                return self._json({ctl.name: list(ctl.trace[-200:]) for ctl in manager.controllers})
+            if manager is not None and path == "/debug/queues":
+                return self._json({ctl.name: {"depth": len(ctl.queue), "delayed": ctl.queue.pending_delayed(),
+                                              "idle": ctl.queue.idle(), "reconciles": ctl.reconcile_count,
+                                              "errors": ctl.error_count} for ctl in manager.controllers})
+            return super().do_GET()
 
     class Server(ThreadingHTTPServer):
         daemon_threads = True

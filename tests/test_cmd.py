@@ -124,6 +124,12 @@ def test_controller_runtime_metrics_endpoint():
         assert samples['workqueue_queue_duration_seconds_count{name="TFJobController"}'] >= ok
         assert 'workqueue_longest_running_processor_seconds{name="TFJobController"}' in samples
         assert 'workqueue_depth{name="PytorchJobController"}' in samples       # every controller has its queue
+        base = url.rsplit("/", 1)[0]
+        trace = json.loads(urllib.request.urlopen(base + "/debug/trace", timeout=5).read())
+        assert trace["TFJobController"] and trace["TFJobController"][-1]["key"] == "ns/m"
+        assert all(sp["error"] is None and sp["seconds"] >= 0 for sp in trace["TFJobController"])
+        queues = json.loads(urllib.request.urlopen(base + "/debug/queues", timeout=5).read())
+        assert queues["TFJobController"]["depth"] == 0 and queues["TFJobController"]["reconciles"] >= ok
         # an error is counted as such and as a retry
         from kubedl_b200.apiserver.store import Invalid
         api.create(new_job("TFJob", "bad", "ns", replica_specs={"Worker": {"replicas": 1, "template": tmpl("tensorflow")}}))

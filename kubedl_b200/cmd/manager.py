@@ -175,10 +175,21 @@ def main(argv=None) -> int:
     log.warning("kubedl-b200 manager up: workloads=%s gang=%s rest=%s gpus=%s", list(op.reconcilers),
                 args.gang_scheduler_name or "-", args.serve or "-", op.gpulet.num_gpus if op.gpulet else "-")
     stop = threading.Event()
+    lost = threading.Event()
+    if op.mgr.elector is not None and hasattr(op.mgr.elector, "on_lost"):
+        # controller-runtime exits when the lease is lost, and so do we: the Deployment restarts the
+        # pod, which queues up behind the new leader instead of lingering as a second writer
+        def on_lost():
+            lost.set()
+            stop.set()
+        op.mgr.elector.on_lost = on_lost
     for sig in (signal.SIGINT, signal.SIGTERM):   # reference pkg/util/signals/signal.go
         signal.signal(sig, lambda *_: stop.set())
     stop.wait()
     op.stop()
+    if lost.is_set():
+        log.error("leader election lost: exiting")
+        return 1
     return 0
 
 

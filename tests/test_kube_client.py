@@ -583,3 +583,41 @@ def test_operator_restart_resumes_from_api_state():
     finally:
         op2.stop()
         srv.shutdown()
+
+
+def test_standby_operator_takes_over(remote):
+    """Two operator replicas against one API server (config/manager/in_cluster.yaml runs two): the
+    standby blocks in start() until the leader goes, then reconciles what is there."""
+    from prometheus_client import CollectorRegistry
+    from kubedl_b200.controllers.registry import setup_with_manager
+    from kubedl_b200.engine.job_controller import JobControllerConfiguration
+    from kubedl_b200.runtime.manager import Manager
+    api, srv, _ = remote
+
+    def replica(identity):
+        cli = KubeAPIServer(KubeConfig.from_url(srv.url), watch_timeout=2)
+        mgr = Manager(api=cli, leader_election=True, leader_election_namespace="kubedl-system")
+        mgr.elector.identity = identity
+        mgr.elector.retry_period = 0.1
+        setup_with_manager(mgr, JobControllerConfiguration(), "*", CollectorRegistry())
+        return mgr
+
+    a, b = replica("op-a"), replica("op-b")
+    a.start()
+    started_b = threading.Event()
+    t = threading.Thread(target=lambda: (b.start(), started_b.set()), daemon=True)
+    t.start()
+    try:
+        api.create(new_job("TFJob", "one", "ns", replica_specs={"Worker": {"replicas": 1, "template": tmpl("tensorflow")}}))
+        wait_for(lambda: len(api.list("Pod", "ns")) == 1, what="leader reconciles")
+        time.sleep(0.5)
+        assert not started_b.is_set()                                     # the standby is waiting for the lease
+        assert api.get("Lease", "kubedl-system", "kubedl-election")["spec"]["holderIdentity"] == "op-a"
+        a.stop()                                                          # releases the lease
+        wait_for(started_b.is_set, what="standby started")
+        assert api.get("Lease", "kubedl-system", "kubedl-election")["spec"]["holderIdentity"] == "op-b"
+        api.create(new_job("TFJob", "two", "ns", replica_specs={"Worker": {"replicas": 2, "template": tmpl("tensorflow")}}))
+        wait_for(lambda: len(api.list("Pod", "ns")) == 3, what="new leader reconciles")
+    finally:
+        b.stop()
+        a.stop()

@@ -76,6 +76,7 @@ class APIServer:
         self._history_floor = 0    # events with rv <= floor have been dropped
         self.fail_next: Dict[Tuple[str, str], Exception] = {}  # fault injection: (verb, kind) -> error
         self.request_log: Deque[Tuple[str, str, str]] = collections.deque(maxlen=65536)   # (verb, kind, ns/name), recent
+        self.validate_schema = True      # OpenAPI validation of workload kinds on create / update
         self.event_ttl = 3600.0          # Events are dropped after an hour, as kube-apiserver does
         self._events_since_prune = 0
         if install_all_crds:
@@ -135,11 +136,27 @@ class APIServer:
         return (c.namespace_of(obj), c.name_of(obj))
 
     # ------------------------------------------------------------------ verbs
+    def _validate(self, obj: dict) -> None:
+        """What kube-apiserver does with the CRD's OpenAPI schema: reject a workload object whose
+        shape is wrong (422 Invalid) instead of letting it reach a controller."""
+        if not self.validate_schema or not self.scheme.is_workload(obj.get("kind", "")):
+            return
+        try:
+            from ..api import crd as crd_mod
+            crd_mod.validate(obj)
+        except ImportError:          # jsonschema not installed: accept, as a server without a schema would
+            return
+        except Exception as e:
+            msg = getattr(e, "message", None) or str(e)
+            where = ".".join(str(p) for p in getattr(e, "absolute_path", []) or [])
+            raise Invalid(f'{obj.get("kind")} "{c.name_of(obj)}" is invalid: {where + ": " if where else ""}{msg}')
+
     def create(self, obj: dict) -> dict:
         kind = obj.get("kind")
         if not kind or not c.name_of(obj):
             raise Invalid("object needs kind and metadata.name")
         self._check_kind(kind)
+        self._validate(obj)
         with self._lock:
             self._maybe_fail("create", kind)
             key = self._key(obj)
@@ -230,6 +247,7 @@ class APIServer:
 
     def update(self, obj: dict) -> dict:
         """PUT of the main resource; for workload kinds .status is ignored (status subresource)."""
+        self._validate({k: v for k, v in obj.items() if k != "status"})
         return self._update(obj, status_only=False, spec_only=self.scheme.is_workload(obj.get("kind", "")))
 
     def update_status(self, obj: dict) -> dict:

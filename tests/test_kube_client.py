@@ -621,3 +621,22 @@ def test_standby_operator_takes_over(remote):
     finally:
         b.stop()
         a.stop()
+
+
+def test_invalid_jobs_are_rejected_at_the_door(remote):
+    """The CRD's OpenAPI schema is enforced on create and update, as kube-apiserver does: a job with a
+    malformed spec is a 422 for the client, not an exception in a controller."""
+    api, srv, cli = remote
+    bad = new_job("TFJob", "bad", "ns", replica_specs={"Worker": {"replicas": "two", "template": tmpl("tensorflow")}})
+    with pytest.raises(store.Invalid) as e:
+        cli.create(bad)
+    assert "replicas" in str(e.value) and "bad" in str(e.value)
+    with pytest.raises(store.Invalid):
+        api.create({"kind": "PyTorchJob", "metadata": {"name": "nospec", "namespace": "ns"}, "spec": {}})
+    good = cli.create(new_job("TFJob", "good", "ns", replica_specs={"Worker": {"replicas": 2, "template": tmpl("tensorflow")}}))
+    good["spec"]["cleanPodPolicy"] = "Sometimes"
+    with pytest.raises(store.Invalid):
+        cli.update(good)
+    assert api.get("TFJob", "ns", "good")["spec"].get("cleanPodPolicy") != "Sometimes"
+    api.validate_schema = False                          # a server without the schema takes anything
+    api.create(bad)

@@ -152,8 +152,12 @@ class KubeConfig:
 
     @classmethod
     def load(cls, master: str = "", kubeconfig: str = "", context: Optional[str] = None,
-             env=os.environ) -> "KubeConfig":
+             env=os.environ, token_file: str = "") -> "KubeConfig":
         """Explicit flags first; then $KUBECONFIG; then the pod's service account."""
+        if master and token_file and not kubeconfig:
+            cfg = cls.from_url(master)
+            cfg.token_file = token_file
+            return cfg
         if kubeconfig:
             cfg = cls.from_kubeconfig(kubeconfig, context)
             if master:

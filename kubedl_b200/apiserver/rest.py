@@ -92,7 +92,7 @@ class Route:
 
 
 def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]] = None,
-                 stopping: Optional[threading.Event] = None, latency: float = 0.0):
+                 stopping: Optional[threading.Event] = None, latency: float = 0.0, token: str = ""):
     """latency: seconds added to every non-watch request — a stand-in for the network round trip
     and etcd commit of a real API server when measuring what the operator's request pattern costs."""
     resources = _resource_map(api.scheme)
@@ -188,6 +188,19 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
 
         def _not_found(self) -> None:
             self._send(404, status_body(404, "NotFound", f"the server could not find the requested resource ({self.path})"))
+
+        def _authorized(self) -> bool:
+            """Static bearer token (`--token-file`): enough to keep strangers out when the server has to
+            listen beyond loopback for node agents on other boxes; TLS is the deployment's job (tunnel / proxy)."""
+            if not token or self.path.split("?")[0] in ("/healthz", "/readyz", "/livez"):
+                return True
+            import hmac
+            got = self.headers.get("Authorization", "")
+            if hmac.compare_digest(got.encode(), f"Bearer {token}".encode()):
+                return True
+            self._body()
+            self._send(401, status_body(401, "Unauthorized", "Unauthorized"))
+            return False
 
         def _body(self) -> bytes:
             n = int(self.headers.get("Content-Length", "0") or 0)
@@ -292,6 +305,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
 
         # ------------------------------------------------------------ verbs
         def do_GET(self):
+            if not self._authorized():
+                return
             try:
                 path = self.path.split("?")[0].rstrip("/")
                 if path in ("/healthz", "/readyz", "/livez"):
@@ -333,6 +348,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
                 self._fail(e)
 
         def do_POST(self):
+            if not self._authorized():
+                return
             try:
                 raw = self._body()
                 if self.path.split("?")[0] == "/apply":
@@ -361,6 +378,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
                 self._fail(e)
 
         def do_PUT(self):
+            if not self._authorized():
+                return
             try:
                 r = self._route()
                 if r is None or not r.name:
@@ -374,6 +393,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
                 self._fail(e)
 
         def do_PATCH(self):
+            if not self._authorized():
+                return
             try:
                 r = self._route()
                 if r is None or not r.name:
@@ -390,6 +411,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
                 self._fail(e)
 
         def do_DELETE(self):
+            if not self._authorized():
+                return
             try:
                 hit = crd_request("DELETE", self.path.split("?")[0], b"")
                 if hit:
@@ -418,9 +441,9 @@ class RestServer(ThreadingHTTPServer):
     daemon_threads = True
     allow_reuse_address = True
 
-    def __init__(self, addr, api: APIServer, log_reader=None, latency: float = 0.0):
+    def __init__(self, addr, api: APIServer, log_reader=None, latency: float = 0.0, token: str = ""):
         self.stopping = threading.Event()
-        super().__init__(addr, make_handler(api, log_reader, self.stopping, latency))
+        super().__init__(addr, make_handler(api, log_reader, self.stopping, latency, token))
 
     @property
     def url(self) -> str:
@@ -433,7 +456,8 @@ class RestServer(ThreadingHTTPServer):
         self.server_close()
 
 
-def serve(api: APIServer, host: str = "127.0.0.1", port: int = 8001, log_reader=None, latency: float = 0.0) -> RestServer:
-    srv = RestServer((host, port), api, log_reader, latency)
+def serve(api: APIServer, host: str = "127.0.0.1", port: int = 8001, log_reader=None, latency: float = 0.0,
+          token: str = "") -> RestServer:
+    srv = RestServer((host, port), api, log_reader, latency, token)
     threading.Thread(target=srv.serve_forever, name="kubedl-rest", daemon=True).start()
     return srv

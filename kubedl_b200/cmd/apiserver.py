@@ -54,6 +54,8 @@ def main(argv=None) -> int:
     ap.add_argument("--serve", default="127.0.0.1:8001", help="listen address")
     ap.add_argument("--crds", default="*", help="comma list of workload kinds to serve (`*` = all)")
     ap.add_argument("--state", default="", help="snapshot file to load at start and save at exit")
+    ap.add_argument("--token-file", default="", help="require `Authorization: Bearer <contents>`; the file is created "
+                    "with a random token (mode 0600) if it does not exist.  Use it whenever --serve is not loopback")
     ap.add_argument("--snapshot-interval", type=float, default=0.0)
     args = ap.parse_args(argv)
     from .manager import low_latency_threads
@@ -66,7 +68,18 @@ def main(argv=None) -> int:
     if args.state and os.path.exists(args.state):
         log.warning("loaded %d objects from %s", load_state(api, args.state), args.state)
     host, _, port = args.serve.rpartition(":")
-    srv = rest.serve(api, host or "127.0.0.1", int(port))
+    token = ""
+    if args.token_file:
+        if not os.path.exists(args.token_file):
+            import secrets
+            fd = os.open(args.token_file, os.O_WRONLY | os.O_CREAT | os.O_EXCL, 0o600)
+            with os.fdopen(fd, "w") as f:
+                f.write(secrets.token_urlsafe(32))
+        with open(args.token_file) as f:
+            token = f.read().strip()
+    elif (host or "127.0.0.1") not in ("127.0.0.1", "localhost", "::1"):
+        log.warning("listening on %s without --token-file: anyone who can reach the port owns the cluster", host)
+    srv = rest.serve(api, host or "127.0.0.1", int(port), token=token)
     print(f"kubedl-b200 apiserver listening on {srv.url}", flush=True)
     stop = threading.Event()
     for sig in (signal.SIGINT, signal.SIGTERM):

@@ -24,6 +24,7 @@ def main(argv=None) -> int:
     ap.add_argument("--master", default="", help="URL of the API server")
     ap.add_argument("--kubeconfig", default="")
     ap.add_argument("--context", default=None)
+    ap.add_argument("--token-file", default="", help="bearer token for --master")
     ap.add_argument("--gpus", type=int, default=None, help="GPUs to hand out (default: all visible)")
     ap.add_argument("--node-name", default="b200-node-0")
     ap.add_argument("--log-dir", default="/tmp/kubedl-b200/pods")
@@ -33,7 +34,8 @@ def main(argv=None) -> int:
     args = ap.parse_args(argv)
     from .manager import low_latency_threads
     low_latency_threads()
-    api = KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context))
+    api = KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context,
+                                        token_file=args.token_file))
     let = Gpulet(api, num_gpus=args.gpus, node_name=args.node_name, log_dir=args.log_dir,
                  prefork=True if args.prefork_workers else None, multi_node=args.multi_node)
     let.start()

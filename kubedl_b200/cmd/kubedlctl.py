@@ -197,7 +197,8 @@ def cmd_cluster(args) -> int:
     operator uses — for boxes where kubectl is not installed; kubectl works just as well."""
     from ..apiserver.kube import KubeAPIServer, KubeConfig
     from ..apiserver.store import ApiError
-    cfg = KubeConfig.load(kubeconfig=args.kubeconfig, context=args.context)
+    cfg = KubeConfig.load(master=args.server if args.token_file and not args.kubeconfig else "",
+                          kubeconfig=args.kubeconfig, context=args.context, token_file=args.token_file)
     cli = KubeAPIServer(cfg)
     ns = getattr(args, "namespace", None)
     if ns == "default" and cfg.namespace:
@@ -255,6 +256,7 @@ def main(argv=None) -> int:
     ap.add_argument("--kubeconfig", default="", help="talk to the Kubernetes cluster of this kubeconfig instead of a local manager")
     ap.add_argument("--context", default=None)
     ap.add_argument("--in-cluster", action="store_true", help="use $KUBECONFIG or the pod's service account")
+    ap.add_argument("--token-file", default="", help="bearer token of a --server started with --token-file")
     sub = ap.add_subparsers(dest="cmd", required=True)
     a = sub.add_parser("apply"); a.add_argument("-f", "--filename", required=True, action="append")
     g = sub.add_parser("get"); g.add_argument("kind"); g.add_argument("name", nargs="?"); g.add_argument("-n", "--namespace", default="default"); g.add_argument("-o", "--output", default="")
@@ -270,7 +272,7 @@ def main(argv=None) -> int:
     args = ap.parse_args(argv)
     if args.cmd == "run":
         return cmd_run(args)
-    if args.kubeconfig or args.in_cluster:
+    if args.kubeconfig or args.in_cluster or args.token_file:
         return cmd_cluster(args)
     if args.cmd == "apply":
         for f in args.filename:

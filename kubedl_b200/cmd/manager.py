@@ -71,6 +71,7 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--kubeconfig", default="", help="path to a kubeconfig; $KUBECONFIG and the in-cluster "
                     "service account are tried when --in-cluster is given")
     ap.add_argument("--context", default=None, help="kubeconfig context (default: current-context)")
+    ap.add_argument("--token-file", default="", help="bearer token for --master (python -m kubedl_b200.cmd.apiserver --token-file)")
     ap.add_argument("--in-cluster", action="store_true", help="use $KUBECONFIG or the pod's service account")
     ap.add_argument("--leader-election-namespace", default="kubedl-system")
     ap.add_argument("--install-crds", action="store_true", help="create missing CRDs on the remote API server at start")
@@ -83,7 +84,8 @@ def remote_api_from_args(args) -> Optional[KubeAPIServer]:
     """A `KubeAPIServer` when any of the cluster flags is given, else None (all-in-one)."""
     if not (args.master or args.kubeconfig or args.in_cluster):
         return None
-    return KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context))
+    return KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context,
+                                         token_file=getattr(args, "token_file", "")))
 
 
 @dataclass

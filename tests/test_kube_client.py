@@ -640,3 +640,33 @@ def test_invalid_jobs_are_rejected_at_the_door(remote):
     assert api.get("TFJob", "ns", "good")["spec"].get("cleanPodPolicy") != "Sometimes"
     api.validate_schema = False                          # a server without the schema takes anything
     api.create(bad)
+
+
+def test_bearer_token_guards_the_api(tmp_path, capsys):
+    from kubedl_b200.cmd import kubedlctl
+    api = store.APIServer()
+    srv = rest.serve(api, "127.0.0.1", 0, token="s3cret")
+    tf = tmp_path / "token"
+    tf.write_text("s3cret\n")
+    anon = KubeAPIServer(KubeConfig.from_url(srv.url))
+    bad = KubeAPIServer(KubeConfig.from_url(srv.url, token="nope"))
+    good = KubeAPIServer(KubeConfig.load(master=srv.url, token_file=str(tf)))
+    try:
+        for cli in (anon, bad):
+            with pytest.raises(kube.Unauthorized):
+                cli.list("Pod")
+            with pytest.raises(kube.Unauthorized):
+                cli.create(pod("x"))
+        assert anon.healthy()                                    # probes need no credentials
+        good.create(pod("x"))
+        assert [c.name_of(p) for p in good.list("Pod")] == ["x"] and len(api.list("Pod")) == 1
+        seen = []
+        good.watch("Pod", lambda ev, obj, old: seen.append(ev))   # the watch stream carries the token too
+        assert seen == ["ADDED"]
+        host = srv.url.split("//")[1]
+        assert kubedlctl.main(["-s", host, "--token-file", str(tf), "get", "pods"]) == 0
+        assert "x" in capsys.readouterr().out
+    finally:
+        for cli in (anon, bad, good):
+            cli.close()
+        srv.shutdown()

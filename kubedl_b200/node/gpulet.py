@@ -492,10 +492,14 @@ class Gpulet:
         key = (c.namespace_of(pod), c.name_of(pod))
         self._job_of[key] = c.labels_of(pod).get(c.JOB_NAME_LABEL, "")
         now = c.now_precise()
-        self._set_status(pod, c.POD_PENDING, conditions=[
-            {"type": "PodScheduled", "status": "True", "lastTransitionTime": now}], host=True)
+        inits = pod.get("spec", {}).get("initContainers") or []
+        if inits:
+            # only worth a write of its own when something slow follows; otherwise the Running status
+            # below carries the same PodScheduled time and the operator sees one pod event, not two
+            self._set_status(pod, c.POD_PENDING, conditions=[
+                {"type": "PodScheduled", "status": "True", "lastTransitionTime": now}], host=True)
         # init containers, sequentially
-        for ic in pod.get("spec", {}).get("initContainers") or []:
+        for ic in inits:
             env = self.build_env(pod, ic, gpu)
             argv = self.registry.resolve(ic, env)
             rc = subprocess.call(argv, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)

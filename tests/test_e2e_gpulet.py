@@ -331,3 +331,25 @@ def test_node_agent_metrics():
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_one_status_write_per_pod_start():
+    """A pod without init containers goes ADDED -> Running -> Succeeded: no intermediate Pending write
+    (each extra pod event is an extra reconcile while the operator is still creating the job's pods)."""
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=0, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}")
+    phases = []
+    mgr.api.watch("Pod", lambda ev, obj, old: phases.append((ev, (obj.get("status") or {}).get("phase"))))
+    let.start()
+    try:
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "quick", "namespace": "d"},
+                        "spec": {"restartPolicy": "Never", "containers": [{
+                            "name": "c", "image": "x", "command": [sys.executable, "-c", "pass"]}]}})
+        _wait(lambda: phases and phases[-1][1] == "Succeeded", timeout=20)
+        assert phases == [("ADDED", None), ("MODIFIED", "Running"), ("MODIFIED", "Succeeded")]
+        pod = mgr.api.get("Pod", "d", "quick")
+        kinds = {cd["type"] for cd in pod["status"]["conditions"]}
+        assert {"PodScheduled", "Initialized", "Ready"} <= kinds and pod["spec"]["nodeName"] == let.node_name
+    finally:
+        let.stop()
+        mgr.stop()

@@ -15,7 +15,10 @@ kube-dns do the rest (SURVEY.md §1 boundaries).  On a single box gpulet plays t
     several jobs with the same default port can coexist.
   * status: phase, PodScheduled/Initialized/Ready conditions with precise transition times (the
     launch-delay metrics read PodReady), containerStatuses with state/exitCode/restartCount;
-    OnFailure/Always restart in place, Never/ExitCode end the pod.
+    OnFailure/Always restart in place with the kubelet's CrashLoopBackOff (first restart at once,
+    then 10 s doubling to 5 min, `state.waiting` in between), Never/ExitCode end the pod.
+  * deletion: a pod deleted while its launch is still in flight (init containers) is cancelled by the
+    launching thread itself; a running pod's GPU returns to the pool only once its process is gone.
   * fault injection: `kill_pod`, `fail_pod_after` (reference has none).
 
 `FakeKubelet` is the process-free variant for control-plane tests: phases are flipped by hand.
@@ -132,6 +135,16 @@ class _Proc:
     restart_count: int = 0
     started_at: str = ""
     log_path: str = ""
+    uid: str = ""
+    # CrashLoopBackOff bookkeeping (restartPolicy Always / OnFailure)
+    started_mono: float = 0.0
+    crashes: int = 0                 # consecutive crashes, forgotten after a long clean run
+    restart_at: Optional[float] = None   # monotonic time of the pending in-place restart
+    exit_code: Optional[int] = None
+
+
+class _LaunchCancelled(Exception):
+    """The pod was deleted while its launch was still in flight."""
 
 
 class Gpulet:
@@ -158,6 +171,15 @@ class Gpulet:
         self._gpu_of: Dict[Tuple[str, str], int] = {}
         self._ports: Dict[Tuple[str, str, int], int] = {}     # (ns, job, declared port) -> host port
         self._pending: Dict[Tuple[str, str], dict] = {}
+        # launches in flight: pod key -> pod uid; a DELETED event for such a pod cannot find a process
+        # yet, so it leaves a cancellation mark and the launching thread cleans up after itself
+        self._launching: Dict[Tuple[str, str], str] = {}
+        self._cancelled: set = set()                           # {(key, uid)}
+        # deleted pods whose process has been signalled but not yet seen to exit: (proc, gpu)
+        self._terminating: List[Tuple["_Proc", Optional[int]]] = []
+        # restart back-off for Always / OnFailure, the kubelet's numbers: first restart at once, then
+        # 10 s doubling to 5 min, forgotten after 10 min of clean running
+        self.restart_backoff = (float(os.environ.get("KUBEDL_GPULET_RESTART_BACKOFF_SECONDS", "10")), 300.0, 600.0)
         self._stop = threading.Event()
         self._threads: List[threading.Thread] = []
         self._unwatch: List[Callable[[], None]] = []
@@ -210,7 +232,7 @@ class Gpulet:
         for u in self._unwatch:
             u()
         with self._lock:
-            procs = list(self._procs.values())
+            procs = list(self._procs.values()) + [p for p, _ in self._terminating]
         for p in procs:
             self._kill(p)
         self._pool.shutdown(wait=False)
@@ -222,27 +244,47 @@ class Gpulet:
 
     def _on_pod(self, ev: str, pod: dict, old: Optional[dict]) -> None:
         key = (c.namespace_of(pod), c.name_of(pod))
+        p = None
         with self._lock:
             if ev == DELETED:
                 self._pending.pop(key, None)
-                p = self._procs.pop(key, None)
-                gpu = self._gpu_of.pop(key, None)
-                if gpu is not None:
-                    self.free_gpus.append(gpu)
-                    self.free_gpus.sort()
-                # last pod of a job gone: forget the job's host-port assignments
-                job = self._job_of.pop(key, None)
-                if job and not any(k[0] == key[0] and j == job for k, j in self._job_of.items()):
-                    for pk in [pk for pk in self._ports
-                               if pk[0] == key[0] and (pk[1] == job or str(pk[1]).startswith(job + "-"))]:
-                        del self._ports[pk]
+                uid = self._launching.get(key)
+                if uid is not None and uid == c.uid_of(pod):
+                    # launch in flight (init containers can take seconds): nothing to signal yet, and the
+                    # GPU is not ours to hand back — the launching thread sees the mark, kills whatever
+                    # it started and releases the GPU itself
+                    self._cancelled.add((key, uid))
+                    return
+                p = self._procs.get(key)
+                if p is not None and p.uid and c.uid_of(pod) and p.uid != c.uid_of(pod):
+                    p = None        # a late event for an older incarnation of this name
+                else:
+                    self._procs.pop(key, None)
+                    gpu = self._gpu_of.pop(key, None)
+                    if p is not None:
+                        # the GPU goes back only when the process is seen gone (_reap): until then the
+                        # old worker may still hold its memory
+                        self._terminating.append((p, gpu))
+                    elif gpu is not None:
+                        self._release_gpu(gpu)
+                    self._forget_job(key)
             elif ev == ADDED and not (pod.get("status") or {}).get("phase"):
                 self._pending[key] = pod
-                p = None
-            else:
-                p = None
         if ev == DELETED and p is not None:
             self._terminate(p, pod)
+
+    def _release_gpu(self, gpu: Optional[int]) -> None:
+        if gpu is not None and gpu not in self.free_gpus:
+            self.free_gpus.append(gpu)
+            self.free_gpus.sort()
+
+    def _forget_job(self, key: Tuple[str, str]) -> None:
+        """Last pod of a job gone: forget the job's host-port assignments.  Caller holds the lock."""
+        job = self._job_of.pop(key, None)
+        if job and not any(k[0] == key[0] and j == job for k, j in self._job_of.items()):
+            for pk in [pk for pk in self._ports
+                       if pk[0] == key[0] and (pk[1] == job or str(pk[1]).startswith(job + "-"))]:
+                del self._ports[pk]
 
     # ------------------------------------------------------------------ scheduling
     def _wants_gpu(self, pod: dict) -> bool:
@@ -412,20 +454,38 @@ class Gpulet:
                     self._gpu_of[key] = gpu
             with self._lock:
                 self._pending.pop(key, None)
+                self._launching[key] = c.uid_of(pod)
             # pods start concurrently (a kubelet runs one pod worker per pod): the all-pods launch
             # delay is then one process spawn, not eight in a row
             self._pool.submit(self._launch_guarded, key, pod, gpu)
 
     def _launch_guarded(self, key, pod, gpu) -> None:
+        mark = (key, c.uid_of(pod))
         try:
             self._launch(pod, gpu)
+        except _LaunchCancelled:
+            log.info("pod %s/%s deleted during launch; launch abandoned", *key)
+            with self._lock:
+                if self._gpu_of.get(key) == gpu:
+                    self._gpu_of.pop(key, None)
+                self._release_gpu(gpu)
+                self._forget_job(key)
         except Exception as e:
             log.warning("launch of %s failed: %s", key, e)
             self._set_status(pod, c.POD_FAILED, reason=str(e), exit_code=127)
             with self._lock:
-                g = self._gpu_of.pop(key, None)
-                if g is not None:
-                    self.free_gpus.append(g)
+                if self._gpu_of.get(key) == gpu:
+                    self._gpu_of.pop(key, None)
+                self._release_gpu(gpu)
+        finally:
+            with self._lock:
+                if self._launching.get(key) == mark[1]:
+                    del self._launching[key]
+                self._cancelled.discard(mark)
+
+    def _launch_cancelled(self, pod: dict) -> bool:
+        with self._lock:
+            return ((c.namespace_of(pod), c.name_of(pod)), c.uid_of(pod)) in self._cancelled
 
     # ------------------------------------------------------------------ env / DNS
     def _service_names(self, ns: str) -> Dict[str, dict]:
@@ -502,9 +562,24 @@ class Gpulet:
         for ic in inits:
             env = self.build_env(pod, ic, gpu)
             argv = self.registry.resolve(ic, env)
-            rc = subprocess.call(argv, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            ip = subprocess.Popen(argv, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL,
+                                  start_new_session=True)
+            while True:
+                try:
+                    rc = ip.wait(timeout=0.05)
+                    break
+                except subprocess.TimeoutExpired:
+                    if self._launch_cancelled(pod) or self._stop.is_set():
+                        try:
+                            os.killpg(ip.pid, signal.SIGKILL)      # the exact group started above
+                        except (ProcessLookupError, PermissionError):
+                            pass
+                        ip.wait()
+                        raise _LaunchCancelled()
             if rc != 0:
                 raise RuntimeError(f"init container {ic.get('name')} exited with {rc}")
+        if self._launch_cancelled(pod):
+            raise _LaunchCancelled()
         containers = pod.get("spec", {}).get("containers") or []
         if not containers:
             raise RuntimeError("pod has no containers")
@@ -514,9 +589,21 @@ class Gpulet:
         argv = self.registry.resolve(ctr, env)
         log_path = os.path.join(self.log_dir, f"{key[0]}_{key[1]}.log")
         popen = self._spawn(argv, env, log_path, ctr.get("workingDir") or None)
-        proc = _Proc(key, ctr.get("name", ""), popen, gpu, started_at=c.now_precise(), log_path=log_path)
+        proc = _Proc(key, ctr.get("name", ""), popen, gpu, started_at=c.now_precise(), log_path=log_path,
+                     uid=c.uid_of(pod), started_mono=time.monotonic())
         with self._lock:
-            self._procs[key] = proc
+            # the pod may have been deleted between the check above and the spawn: only a process whose
+            # pod is still wanted is registered; the other one is killed here, before its GPU is freed
+            cancelled = ((key, proc.uid) in self._cancelled)
+            if not cancelled:
+                self._procs[key] = proc
+        if cancelled:
+            self._kill(proc)
+            try:
+                popen.wait(timeout=10)
+            except Exception:
+                pass
+            raise _LaunchCancelled()
         self.launched += 1
         if self._start_hist is not None:
             self._start_hist.observe(time.perf_counter() - t_launch)
@@ -565,7 +652,25 @@ class Gpulet:
     def _reap(self) -> None:
         with self._lock:
             procs = list(self._procs.items())
+            terminating = list(self._terminating)
+        # deleted pods: the GPU goes back to the pool once the signalled process is really gone
+        for item in terminating:
+            if item[0].popen.poll() is not None:
+                with self._lock:
+                    if item in self._terminating:
+                        self._terminating.remove(item)
+                        self._release_gpu(item[1])
         for key, proc in procs:
+            if proc.restart_at is not None:         # in CrashLoopBackOff: waiting for its restart time
+                if time.monotonic() >= proc.restart_at:
+                    try:
+                        pod = self.api.get("Pod", key[0], key[1])
+                    except NotFound:
+                        with self._lock:
+                            self._procs.pop(key, None)
+                        continue
+                    self._restart_in_place(pod, proc)
+                continue
             rc = proc.popen.poll()
             if rc is None:
                 continue
@@ -579,14 +684,12 @@ class Gpulet:
                 continue
             policy = pod.get("spec", {}).get("restartPolicy") or "Never"
             if (policy == "Always") or (policy == "OnFailure" and rc != 0):
-                self._restart_in_place(pod, proc)
+                self._schedule_restart(pod, proc, rc)
                 continue
             with self._lock:
                 self._procs.pop(key, None)
                 gpu = self._gpu_of.pop(key, None)
-                if gpu is not None:
-                    self.free_gpus.append(gpu)
-                    self.free_gpus.sort()
+                self._release_gpu(gpu)
             done = c.now_precise()
             conds = [cd for cd in (pod.get("status") or {}).get("conditions") or []]
             for cd in conds:
@@ -601,18 +704,56 @@ class Gpulet:
                                                                            "startedAt": proc.started_at,
                                                                            "finishedAt": done}}}])
 
+    def _schedule_restart(self, pod: dict, proc: _Proc, rc: int) -> None:
+        """Restart in place (Always / OnFailure) with the kubelet's CrashLoopBackOff: the first restart is
+        immediate, later ones wait base * 2^(n-1) seconds up to the cap, and a container that then runs
+        cleanly for `reset_after` starts from zero again.  While waiting the pod stays Running with the
+        container in `state.waiting` (reason CrashLoopBackOff) — a worker that dies at import no longer
+        respawns on every loop pass and floods the API server with status writes."""
+        base, cap, reset_after = self.restart_backoff
+        now = time.monotonic()
+        if proc.started_mono and now - proc.started_mono >= reset_after:
+            proc.crashes = 0
+        delay = 0.0 if proc.crashes == 0 else min(cap, base * (2.0 ** (proc.crashes - 1)))
+        proc.crashes += 1
+        proc.exit_code = rc
+        if delay <= 0:
+            self._restart_in_place(pod, proc)
+            return
+        proc.restart_at = now + delay
+        done = c.now_precise()
+        conds = [dict(cd) for cd in (pod.get("status") or {}).get("conditions") or []]
+        for cd in conds:
+            if cd.get("type") in ("Ready", "ContainersReady"):
+                cd["status"] = "False"
+                cd["lastTransitionTime"] = done
+        self._set_status(pod, c.POD_RUNNING, conditions=conds, container_statuses=[{
+            "name": proc.container, "ready": False, "restartCount": proc.restart_count,
+            "state": {"waiting": {"reason": "CrashLoopBackOff",
+                                  "message": f"back-off {delay:.0f}s restarting failed container"}},
+            "lastState": {"terminated": {"exitCode": rc, "reason": "Completed" if rc == 0 else "Error",
+                                         "startedAt": proc.started_at, "finishedAt": done}}}])
+
     def _restart_in_place(self, pod: dict, proc: _Proc) -> None:
         ctr = (pod.get("spec", {}).get("containers") or [{}])[0]
         env = self.build_env(pod, ctr, proc.gpu)
         argv = self.registry.resolve(ctr, env)
         proc.popen = self._spawn(argv, env, proc.log_path, ctr.get("workingDir") or None)
         proc.restart_count += 1
+        proc.restart_at = None
         proc.started_at = c.now_precise()
-        conds = (pod.get("status") or {}).get("conditions")
-        self._set_status(pod, c.POD_RUNNING, conditions=conds,
-                         container_statuses=[{"name": proc.container, "ready": True,
-                                              "restartCount": proc.restart_count,
-                                              "state": {"running": {"startedAt": proc.started_at}}}])
+        proc.started_mono = time.monotonic()
+        conds = [dict(cd) for cd in (pod.get("status") or {}).get("conditions") or []]
+        for cd in conds:
+            if cd.get("type") in ("Ready", "ContainersReady") and cd.get("status") != "True":
+                cd["status"] = "True"
+                cd["lastTransitionTime"] = proc.started_at
+        cs = {"name": proc.container, "ready": True, "restartCount": proc.restart_count,
+              "state": {"running": {"startedAt": proc.started_at}}}
+        if proc.exit_code is not None:
+            cs["lastState"] = {"terminated": {"exitCode": proc.exit_code,
+                                              "reason": "Completed" if proc.exit_code == 0 else "Error"}}
+        self._set_status(pod, c.POD_RUNNING, conditions=conds or None, container_statuses=[cs])
 
     def _terminate(self, proc: _Proc, pod: dict) -> None:
         """Pod deleted: SIGTERM to its process group, SIGKILL after the grace period if it is still

@@ -353,3 +353,111 @@ def test_one_status_write_per_pod_start():
     finally:
         let.stop()
         mgr.stop()
+
+
+def _pid_alive(pid: int) -> bool:
+    try:
+        os.kill(pid, 0)
+    except ProcessLookupError:
+        return False
+    try:      # a zombie still answers kill(0)
+        with open(f"/proc/{pid}/stat") as f:
+            return f.read().split(")")[-1].split()[0] != "Z"
+    except FileNotFoundError:
+        return False
+
+
+def test_pod_deleted_during_slow_init_container_leaves_no_orphan(tmp_path):
+    """A pod deleted while its launch is in flight (init container still running) must not end up as a
+    worker process on a GPU that was already handed to the next pod: the launch is abandoned, whatever it
+    started is killed, the GPU returns to the pool and the job's bookkeeping is dropped."""
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=1, default_gpu_per_pod=True, log_dir=str(tmp_path / "pods"))
+    let.start()
+    started, main_ran = tmp_path / "init-started", tmp_path / "main-ran"
+    init_cmd = [sys.executable, "-c",
+                f"import time,os\nopen(r'{started}','w').write(str(os.getpid()))\ntime.sleep(30)"]
+    main_cmd = [sys.executable, "-c", f"open(r'{main_ran}','w').close()\nimport time\ntime.sleep(30)"]
+    try:
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "slow", "namespace": "d",
+                                                    "labels": {c.JOB_NAME_LABEL: "j1"}},
+                        "spec": {"restartPolicy": "Never",
+                                 "initContainers": [{"name": "init", "image": "x", "command": init_cmd}],
+                                 "containers": [{"name": "c", "image": "x", "command": main_cmd}]}})
+        _wait(lambda: started.exists() and started.read_text(), timeout=20)
+        init_pid = int(started.read_text())
+        assert let.free_gpus == [] and ("d", "slow") in let._launching
+        mgr.api.delete("Pod", "d", "slow")
+        _wait(lambda: ("d", "slow") not in let._launching, timeout=20)
+        _wait(lambda: not _pid_alive(init_pid), timeout=10)
+        assert not main_ran.exists(), "the worker was started for a pod that no longer exists"
+        assert let.free_gpus == [0] and not let._procs and not let._gpu_of
+        assert ("d", "slow") not in let._job_of and not let._cancelled
+        # the freed GPU serves the next pod, and nothing of the old one is left on it
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "next", "namespace": "d"},
+                        "spec": {"restartPolicy": "Never", "containers": [{
+                            "name": "c", "image": "x", "command": [sys.executable, "-c", "pass"]}]}})
+        _wait(lambda: (mgr.api.get("Pod", "d", "next").get("status") or {}).get("phase") == "Succeeded", timeout=20)
+        time.sleep(0.2)
+        assert not main_ran.exists()
+    finally:
+        let.stop()
+        mgr.stop()
+
+
+def test_deleted_pod_gpu_returns_only_after_its_process_is_gone(tmp_path):
+    """Deleting a running pod signals its process; the GPU goes back to the pool when the process has
+    really exited (a worker that takes its grace period still holds device memory)."""
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=1, default_gpu_per_pod=True, log_dir=str(tmp_path / "pods"))
+    let.start()
+    stubborn = [sys.executable, "-c",
+                "import signal,time\nsignal.signal(signal.SIGTERM, lambda *a: None)\ntime.sleep(30)"]
+    try:
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "stubborn", "namespace": "d"},
+                        "spec": {"restartPolicy": "Never", "terminationGracePeriodSeconds": 1,
+                                 "containers": [{"name": "c", "image": "x", "command": stubborn}]}})
+        _wait(lambda: ("d", "stubborn") in let._procs, timeout=20)
+        time.sleep(0.3)     # let the interpreter install its SIGTERM handler
+        pid = let._procs[("d", "stubborn")].popen.pid
+        mgr.api.delete("Pod", "d", "stubborn")
+        time.sleep(0.3)
+        assert _pid_alive(pid) and let.free_gpus == [], "GPU handed back while the old worker is still alive"
+        _wait(lambda: let.free_gpus == [0], timeout=10)      # SIGKILL after the 1 s grace period
+        assert not _pid_alive(pid) and not let._terminating
+    finally:
+        let.stop()
+        mgr.stop()
+
+
+def test_crash_loop_backoff_paces_in_place_restarts(tmp_path):
+    """restartPolicy Always/OnFailure: first restart at once, then exponentially spaced, with the
+    container reported `waiting: CrashLoopBackOff` in between (the kubelet's behaviour; without it a
+    worker dying at import respawned on every 10 ms loop pass)."""
+    mgr = Manager()
+    let = Gpulet(mgr.api, num_gpus=0, log_dir=str(tmp_path / "pods"))
+    let.restart_backoff = (0.4, 5.0, 600.0)
+    writes = []
+    mgr.api.watch("Pod", lambda ev, obj, old: writes.append(
+        ((obj.get("status") or {}).get("containerStatuses") or [{}])[0]))
+    let.start()
+    try:
+        mgr.api.create({"kind": "Pod", "metadata": {"name": "crashy", "namespace": "d"},
+                        "spec": {"restartPolicy": "OnFailure", "containers": [{
+                            "name": "c", "image": "x", "command": [sys.executable, "-c", "import sys; sys.exit(3)"]}]}})
+        t0 = time.time()
+        _wait(lambda: any((w.get("state") or {}).get("waiting", {}).get("reason") == "CrashLoopBackOff"
+                          for w in writes), timeout=20)
+        pod = mgr.api.get("Pod", "d", "crashy")
+        assert pod["status"]["phase"] == "Running"
+        cs = pod["status"]["containerStatuses"][0]
+        assert cs["lastState"]["terminated"]["exitCode"] == 3 and cs["ready"] is False
+        time.sleep(2.0)
+        restarts = let._procs[("d", "crashy")].restart_count
+        # 0 s, +0.4, +0.8, +1.6 ...: a handful of restarts in ~2.5 s, not hundreds
+        assert 2 <= restarts <= 5, restarts
+        assert len(writes) < 30, len(writes)
+        assert time.time() - t0 < 30
+    finally:
+        let.stop()
+        mgr.stop()

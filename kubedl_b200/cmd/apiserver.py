@@ -77,6 +77,11 @@ def main(argv=None) -> int:
                 f.write(secrets.token_urlsafe(32))
         with open(args.token_file) as f:
             token = f.read().strip()
+        if not token:
+            # an empty token means "authentication off" further down: never fall into that silently
+            print(f"kubedl-b200 apiserver: --token-file {args.token_file} exists but holds no token; "
+                  "delete it (a random one is generated) or write a token into it", file=sys.stderr, flush=True)
+            return 2
     elif (host or "127.0.0.1") not in ("127.0.0.1", "localhost", "::1"):
         log.warning("listening on %s without --token-file: anyone who can reach the port owns the cluster", host)
     srv = rest.serve(api, host or "127.0.0.1", int(port), token=token)

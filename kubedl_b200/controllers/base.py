@@ -14,7 +14,7 @@ from typing import Dict, List, Optional
 
 from ..api import common as c
 from ..api.kinds import SCHEME, KindInfo
-from ..apiserver.store import NotFound
+from ..apiserver.store import Conflict, NotFound
 from ..engine.control import EVENT_NORMAL, ControllerRefManager
 from ..engine.interface import ControllerInterface
 from ..engine.job_controller import (FAILED_DELETE_JOB_REASON, SUCCESSFUL_DELETE_JOB_REASON,
@@ -74,15 +74,23 @@ class BaseJobReconciler(ControllerInterface):
         if not st.has_condition(status, c.JOB_CREATED):
             msg = f"{self.KIND} {c.name_of(job)} is created."
             st.update_job_conditions(status, c.JOB_CREATED, st.JOB_CREATED_REASON, msg)
-            try:
-                fresh = self.client.reader().get(self.KIND, c.namespace_of(job), c.name_of(job))
-                if not st.has_condition(c.status_of(fresh), c.JOB_CREATED) and \
-                        not fresh["metadata"].get("deletionTimestamp"):
-                    fresh["status"] = status
-                    fresh["metadata"].pop("resourceVersion", None)
+            # runs on the watch thread, possibly next to the first reconcile: compare-and-swap against
+            # what the API server holds now, and add the condition to THAT status instead of replacing it
+            for _ in range(4):
+                try:
+                    fresh = self.client.reader().get(self.KIND, c.namespace_of(job), c.name_of(job))
+                except NotFound:
+                    return False
+                if st.has_condition(c.status_of(fresh), c.JOB_CREATED) or fresh["metadata"].get("deletionTimestamp"):
+                    break
+                st.update_job_conditions(c.status_of(fresh), c.JOB_CREATED, st.JOB_CREATED_REASON, msg)
+                try:
                     self.client.update_status(fresh)
-            except NotFound:
-                return False
+                    break
+                except Conflict:
+                    continue
+                except NotFound:
+                    return False
             self.metrics.created_inc()
         return True
 
@@ -136,10 +144,17 @@ class BaseJobReconciler(ControllerInterface):
         self.recorder.eventf(job, EVENT_NORMAL, SUCCESSFUL_DELETE_JOB_REASON, "Deleted job: %s", c.name_of(job))
 
     def update_job_status_in_api_server(self, job: dict, job_status: dict) -> None:
-        latest = self.client.reader().get(self.KIND, c.namespace_of(job), c.name_of(job))
-        latest["status"] = c.deepcopy(job_status)
-        latest["metadata"].pop("resourceVersion", None)
-        self.client.update_status(latest)
+        """Status().Update with optimistic concurrency (reference controllers/pytorch/job.go:95-105): the
+        write carries the resourceVersion of the object the status was COMPUTED from.  If the job has moved
+        on since (a second reconcile worker, another manager, the Created stamp of the watch thread), the
+        API server answers Conflict, the reconcile ends there and the request is requeued — a status derived
+        from a stale read never overwrites a newer one."""
+        obj = c.deepcopy(job)
+        obj["status"] = c.deepcopy(job_status)
+        written = self.client.update_status(obj)
+        rv = (written or {}).get("metadata", {}).get("resourceVersion")
+        if rv:      # a later write in the same pass continues from what was just written
+            job["metadata"]["resourceVersion"] = rv
 
     # ------------------------------------------------------------------ children
     def _selector(self, job: dict) -> Dict[str, str]:

@@ -280,9 +280,16 @@ class Controller:
             res = self.reconciler(req) or Result()
         except Exception as e:  # reconcile error -> rate-limited requeue
             err = e
-            self.error_count += 1
-            log.warning("reconcile %s %s failed: %s", self.name, req.key, e)
-            log.debug(traceback.format_exc())
+            from ..apiserver.store import Conflict
+            if isinstance(e, Conflict):
+                # optimistic concurrency doing its job (a write computed from a stale read was refused):
+                # routine, requeued like any error but not reported as one
+                self.conflict_count = getattr(self, "conflict_count", 0) + 1
+                log.debug("reconcile %s %s: %s; requeued", self.name, req.key, e)
+            else:
+                self.error_count += 1
+                log.warning("reconcile %s %s failed: %s", self.name, req.key, e)
+                log.debug(traceback.format_exc())
         finally:
             self.reconcile_count += 1
             self.trace.append({"controller": self.name, "key": req.key, "seconds": time.perf_counter() - t0,

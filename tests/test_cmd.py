@@ -184,3 +184,12 @@ def test_kubedlctl_with_a_kubeconfig(capsys, tmp_path):
         assert "NotFound" in str(e.value)
     finally:
         srv.shutdown()
+
+
+def test_apiserver_refuses_an_empty_token_file(tmp_path, capsys):
+    """`--token-file` naming a file with no token in it must not start an unauthenticated server."""
+    from kubedl_b200.cmd import apiserver
+    tf = tmp_path / "token"
+    tf.write_text("  \n")
+    assert apiserver.main(["--serve", "127.0.0.1:0", "--token-file", str(tf)]) == 2
+    assert "holds no token" in capsys.readouterr().err

@@ -396,3 +396,53 @@ def test_status_schema_matches_crd_requirements():
     assert isinstance(st["conditions"], list) and isinstance(st["replicaStatuses"], dict)
     cond = st["conditions"][0]
     assert set(cond) == {"type", "status", "reason", "message", "lastUpdateTime", "lastTransitionTime"}
+
+
+# ---------------------------------------------------------------- status writes are compare-and-swap
+def test_status_write_from_a_stale_job_is_refused_and_requeued():
+    """Status().Update carries the resourceVersion of the object the status was computed from (reference
+    controllers/pytorch/job.go:95-105): a write derived from a stale read gets Conflict instead of
+    overwriting what is newer, and the reconcile is simply run again."""
+    from kubedl_b200.apiserver.store import Conflict
+    cl = Cluster()
+    cl.submit(_pt(workers=1))
+    rec = cl.recs["PyTorchJob"]
+    stale = cl.job("PyTorchJob", "ns", "pt")
+    # somebody else (a second manager) moves the job on
+    newer = cl.job("PyTorchJob", "ns", "pt")
+    newer["status"]["startTime"] = "2026-01-01T00:00:00Z"
+    cl.api.update_status(newer)
+    lost = c.deepcopy(stale["status"])
+    with pytest.raises(Conflict):
+        rec.update_job_status_in_api_server(stale, lost)
+    assert cl.job("PyTorchJob", "ns", "pt")["status"]["startTime"] == "2026-01-01T00:00:00Z"
+    # through the controller: the conflict is a quiet requeue, and the next pass converges
+    ctl = rec.controller
+    errors0 = ctl.error_count
+    real, calls = cl.mgr.client.update_status, []
+
+    def flaky(obj):
+        calls.append(obj["metadata"].get("resourceVersion"))
+        if len(calls) == 1:
+            raise Conflict("the object has been modified")
+        return real(obj)
+    cl.mgr.client.update_status = flaky
+    try:
+        cl.kubelet.set_all("ns", "Running")
+        cl.mgr.run_until_idle(advance_delayed=True)
+    finally:
+        cl.mgr.client.update_status = real
+    assert len(calls) >= 2 and all(calls), calls          # every status write named a resourceVersion
+    assert ("Running", "True") in cl.conditions("PyTorchJob", "ns", "pt")
+    assert ctl.error_count == errors0 and ctl.conflict_count >= 1
+
+
+def test_created_condition_is_added_not_overwritten():
+    """The Created stamp of the watch thread goes on top of whatever status the API server holds."""
+    cl = Cluster()
+    job = _pt(workers=1)
+    job["status"] = {"conditions": [], "replicaStatuses": {}, "startTime": "2026-01-01T00:00:00Z"}
+    cl.api.create(c.deepcopy(job))
+    cl.settle()
+    st_ = cl.job("PyTorchJob", "ns", "pt")["status"]
+    assert st_["conditions"][0]["type"] == "Created" and st_.get("startTime") == "2026-01-01T00:00:00Z"

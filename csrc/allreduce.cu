@@ -238,9 +238,53 @@ __global__ void __launch_bounds__(kThreads) scale_cast_kernel(const void* in, vo
   }
 }
 
+// Flag-only barrier across the ranks (no payload): block 0 of every rank announces epoch+1 to every peer
+// and waits for all of them.  Used where two kernels of one step must be ordered ACROSS GPUs and no
+// collective sits between them (DIN: every rank's forward gather before anybody's remote sparse update).
+// emulate=1: gridDim.y ranks inside one cooperative launch (single-GPU protocol test).
+__global__ void __launch_bounds__(kThreads) symm_barrier_kernel(ArParams p) {
+  const int rank = p.emulate ? (int)blockIdx.y : p.rank;
+  uint32_t* ep = epoch_slot(p, rank);
+  const uint32_t epoch = *ep;
+  block_barrier(p, rank, epoch + 1);
+  if (threadIdx.x == 0) *ep = epoch + 1;
+}
+
 }  // namespace kdl
 
 using namespace kdl;
+
+extern "C" int kdl_symm_barrier(void* const* flag_ptrs, int world, int rank, void* epoch_state, int channels,
+                                int channel, int emulate, void* status, unsigned long long timeout_ns,
+                                cudaStream_t stream) {
+  if (world < 1 || world > kMaxWorld || epoch_state == nullptr || channel < 0 || channel >= channels) {
+    kdl_set_error("symm_barrier: need 1 <= world <= %d, epoch_state and 0 <= channel < channels", kMaxWorld);
+    return KDL_ERR_ARG;
+  }
+  if (world == 1) return KDL_OK;
+  ArParams p = {};
+  for (int r = 0; r < world; ++r) p.flags[r] = (uint32_t*)flag_ptrs[r];
+  p.world = world;
+  p.rank = rank;
+  p.channel = channel;
+  p.emulate = emulate;
+  p.epoch_state = (uint32_t*)epoch_state;
+  p.channels = channels;
+  p.status = (uint32_t*)status;
+  p.timeout_ns = timeout_ns;
+  if (emulate) {
+    void* args[] = {&p};
+    cudaError_t e = cudaLaunchCooperativeKernel((void*)symm_barrier_kernel, dim3(1, world), dim3(kThreads), args, 0, stream);
+    if (e != cudaSuccess) {
+      kdl_set_error("symm_barrier(emulate) cooperative launch failed: %s", cudaGetErrorString(e));
+      return KDL_ERR_CUDA;
+    }
+    return KDL_OK;
+  }
+  symm_barrier_kernel<<<1, kThreads, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
 
 extern "C" size_t kdl_allreduce_flags_bytes(int channels) {
   return (size_t)channels * kMaxWorld * kMaxBlocks * sizeof(uint32_t);

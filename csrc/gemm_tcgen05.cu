@@ -27,12 +27,15 @@
 namespace kdl {
 
 constexpr int BM = 128;       // UMMA M (cta_group::1)
-// 4 control warps + kEpiWarps epilogue warps.  8 epilogue warps (two per TMEM lane quarter, alternating
-// column chunks) were measured: they hide the fused-statistics epilogue but cost a pipeline stage of
-// shared memory and ~5 % on compute-bound shapes (profiles/gemm_vs_cublas_shapes.log), so 4 it is.
-constexpr int kEpiWarps = 4;
-constexpr int kGemmThreads = 128 + 32 * kEpiWarps;
+// 4 control warps + EPI epilogue warps (template parameter, 4 or 8).  With 8, two warps share a TMEM lane
+// quarter and take alternate 64-column chunks.  One epilogue warp per SM sub-partition runs a long serial
+// chain per chunk (TMEM load, addend / statistics, 64 conversions, pack, store) with nobody to hide its
+// latencies behind, so tiles with little K per output element (K <= 256..512: the memory-bound 1x1
+// convolutions, and everything with a fused addend or fused statistics) are EPILOGUE-bound with 4 warps;
+// 8 warps cost 32 KB of staging, i.e. one pipeline stage, which only the deep-K compute-bound shapes miss
+// (profiles/gemm_vs_cublas_shapes.log, profiles/r2_epilogue_warps.md).  The host picks per launch.
 constexpr int kEpiWarp0 = 4;
+constexpr int gemm_threads(int epi) { return 128 + 32 * epi; }
 
 struct GemmParams {
   bf16* C;              // bf16 output (mode 0)
@@ -41,6 +44,9 @@ struct GemmParams {
   const bf16* addend;   // [M, ldc] or null
   int add_h, add_w;     // > 0: rows are pixels (n, h, w) of an add_h x add_w map and `addend` is the compact
                         // [n, add_h/2, add_w/2] tensor of a stride-2 branch: added at even (h, w) only
+  int add_tma;              // the (full-size) addend is fetched by TMA into the output staging buffers (tensor map tma_d)
+  const uint8_t* add_mask;  // optional [M*N/8] bit mask (bit j of byte v <-> element 8v+j): the addend counts only
+                            // where the bit is set (gradient through a ReLU whose mask BatchNorm saved)
   int M, N, K;
   int ldc;
   int relu;
@@ -96,6 +102,124 @@ __device__ __forceinline__ void store_col_stats(float* stats, int part, int N, i
   if (col + 1 < N) { dst[col + 1] = acc[1]; dst[N + col + 1] = acc[3]; }
 }
 
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
+
+// The residual-branch gradient ("addend") of a dgrad GEMM, one accumulator row per lane, 64 columns per chunk.
+// Per-lane loads of "my row" are the wrong shape for the memory system: 16 bytes per lane at a row pitch of
+// 512+ bytes makes every LDG.128 touch 32 different lines (256 L1 wavefronts per 4 KB chunk, four warps
+// deep), and the memory-bound dgrads ran at half of copy bandwidth even with the loads issued a chunk
+// ahead (profiles/r2_addend_epilogue.md).  So a full-size addend comes in by TMA instead (see the
+// epilogue); this register pipeline remains for the compact stride-2 addend, whose rows are not a box.
+struct AddendPipe {
+  uint4 v[8];
+  uint2 m;
+  const bf16* slow;   // partial N tile: element-wise path at apply time
+  int state;          // 0 nothing to add, 1 registers loaded, 2 slow path
+
+  static __device__ __forceinline__ const bf16* row_ptr(const GemmParams& p, int row) {
+    if (p.addend == nullptr || row >= p.M) return nullptr;
+    size_t idx = (size_t)row;
+    if (p.add_h > 0) {      // gradient of a 1x1 / stride-2 branch, kept compact (never up-sampled)
+      const int hw = p.add_h * p.add_w;
+      const int ni = row / hw, rem = row - ni * hw, hh = rem / p.add_w, ww = rem - hh * p.add_w;
+      if (((hh | ww) & 1) != 0) return nullptr;
+      idx = ((size_t)ni * (p.add_h >> 1) + (hh >> 1)) * (p.add_w >> 1) + (ww >> 1);
+    }
+    return p.addend + idx * p.ldc;
+  }
+  // L2 prefetch of `ncols` columns of this lane's row (128-byte lines)
+  static __device__ __forceinline__ void prefetch_l2(const GemmParams& p, int row, int col, int ncols) {
+    const bf16* r = row_ptr(p, row);
+    if (r == nullptr) return;
+    const int end = min(col + ncols, p.N);
+    for (int c = col; c < end; c += 64) asm volatile("prefetch.global.L2 [%0];" ::"l"(r + c));
+    if (p.add_mask) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.add_mask + (((size_t)row * p.N + col) >> 3)));
+  }
+  __device__ __forceinline__ void issue(const GemmParams& p, int row, int col) {
+    state = 0;
+    const bf16* r = row_ptr(p, row);
+    if (r == nullptr || col >= p.N) return;
+    if (col + 64 <= p.N) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = ld_plain(r + col + 8 * j);
+      if (p.add_mask) m = *reinterpret_cast<const uint2*>(p.add_mask + (((size_t)row * p.N + col) >> 3));
+      state = 1;
+    } else {
+      slow = r + col;
+      state = 2;
+    }
+  }
+  __device__ __forceinline__ void apply(const GemmParams& p, int col, float* f) const {
+    if (state == 1) {
+      if (p.add_mask) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float b[8];
+          unpack8(v[j], b);
+          const uint32_t bits = (j < 4 ? m.x : m.y) >> ((j & 3) * 8);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[8 * j + i] += ((bits >> i) & 1u) ? b[i] : 0.f;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float b[8];
+          unpack8(v[j], b);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[8 * j + i] += b[i];
+        }
+      }
+    } else if (state == 2) {
+#pragma unroll
+      for (int j = 0; j < 64; ++j)
+        if (col + j < p.N) f[j] += __bfloat162float(slow[j]);
+    }
+  }
+};
+
+// Full-size addend by TMA.  The 32-row x 64-column addend chunk lands (128B-swizzled, by the same box shape
+// the output store uses) in the very staging buffer the output chunk is about to be written into: lane l
+// reads ITS row with eight conflict-free LDS.128, adds it to its accumulator row and later overwrites the
+// same 128 bytes with the result, so the addend needs no shared memory of its own.  The load for chunk i+1
+// is issued into the other staging buffer while chunk i is converted and stored (after the store that last
+// used that buffer has finished reading it), and a whole tile is prefetched into L2 one tile ahead.
+struct AddendTma {
+  uint32_t phases;     // bit b: parity of the next completion of barrier b
+  uint2 mnext;         // ReLU-mask bits of the chunk whose load is in flight
+
+  static __device__ __forceinline__ uint2 load_mask(const GemmParams& p, int row, int col) {
+    if (p.add_mask == nullptr || row >= p.M || col >= p.N) return make_uint2(0u, 0u);
+    return *reinterpret_cast<const uint2*>(p.add_mask + (((size_t)row * p.N + col) >> 3));
+  }
+  // lane 0 issues; every lane fetches its own mask word
+  __device__ __forceinline__ void issue(const GemmParams& p, const CUtensorMap* map, uint32_t bar, uint32_t dst,
+                                        int row0, int col, int lane) {
+    if (lane == 0) {
+      mbar_expect_tx(bar, 4096);
+      tma_load_2d(dst, map, bar, col, row0);
+    }
+    mnext = load_mask(p, row0 + lane, col);
+  }
+  // wait for buffer `b`'s chunk and add this lane's row (src = its 128 bytes in the staging buffer)
+  __device__ __forceinline__ void consume(const GemmParams& p, uint32_t bar, int b, const uint8_t* src, int lane,
+                                          float* f) {
+    mbar_wait(bar, (phases >> b) & 1u);
+    phases ^= 1u << b;
+    const uint2 m = mnext;
+    const bool masked = p.add_mask != nullptr;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v[8];
+      unpack8(*reinterpret_cast<const uint4*>(src + ((j ^ (lane & 7)) << 4)), v);
+      const uint32_t bits = masked ? ((j < 4 ? m.x : m.y) >> ((j & 3) * 8)) : 0xFFu;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[8 * j + i] += ((bits >> i) & 1u) ? v[i] : 0.f;
+    }
+  }
+};
+
 template <int A_MN, int B_MN, int BN>
 __host__ __device__ constexpr uint32_t make_idesc() {
   return (1u << 4)            // D format f32
@@ -107,7 +231,7 @@ __host__ __device__ constexpr uint32_t make_idesc() {
 
 // The four epilogue warps of a CTA hold statistics of the same columns over different rows: add them in
 // shared memory (fixed order) and write ONE partial row per CTA, so the finalizer walks a quarter of the rows.
-template <int BNT>
+template <int BNT, int EPI>
 __device__ __forceinline__ void reduce_store_col_stats(float* sm, float* stats, int part, int N, int col0, int ew,
                                                        int lane, float (*acc)[4]) {
 #pragma unroll
@@ -116,34 +240,200 @@ __device__ __forceinline__ void reduce_store_col_stats(float* sm, float* stats, 
     sm[(ew * 2 + 0) * BNT + col] = acc[c][0]; sm[(ew * 2 + 0) * BNT + col + 1] = acc[c][1];
     sm[(ew * 2 + 1) * BNT + col] = acc[c][2]; sm[(ew * 2 + 1) * BNT + col + 1] = acc[c][3];
   }
-  asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+  asm volatile("bar.sync 1, %0;" ::"n"(EPI * 32) : "memory");
   float* dst = stats + (size_t)part * 2 * N;
-  for (int col = ew * 32 + lane; col < BNT; col += kEpiWarps * 32) {
+  for (int col = ew * 32 + lane; col < BNT; col += EPI * 32) {
     float s0 = 0.f, q0 = 0.f;
 #pragma unroll
-    for (int w = 0; w < kEpiWarps; ++w) { s0 += sm[(w * 2 + 0) * BNT + col]; q0 += sm[(w * 2 + 1) * BNT + col]; }
+    for (int w = 0; w < EPI; ++w) { s0 += sm[(w * 2 + 0) * BNT + col]; q0 += sm[(w * 2 + 1) * BNT + col]; }
     if (col0 + col < N) { dst[col0 + col] = s0; dst[N + col0 + col] = q0; }
   }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int EPI>
 struct SmemLayout {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagingOffset = STAGES * kStageBytes;   // 1024-aligned
   static constexpr int kStagingPerWarp = 2 * 4096;             // two 32-row x 128-B buffers
-  static constexpr int kStatsOffset = kStagingOffset + kEpiWarps * kStagingPerWarp;
+  static constexpr int kStatsOffset = kStagingOffset + EPI * kStagingPerWarp;
   static constexpr int kBarOffset = kStatsOffset + kStatsBytes;
-  static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+  static constexpr int kAddBarOffset = kBarOffset + (2 * STAGES + 4) * 8 + 16;   // 2 per epilogue warp (addend loads)
+  static constexpr int kTotal = kAddBarOffset + EPI * 2 * 8;
+  static_assert(kTotal + 1024 <= 232448, "shared memory budget");
 };
 
-template <int A_MN, int B_MN, int BN, int STAGES>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// ============================== epilogue (shared by the 1-CTA and the CTA-pair kernel) ==============================
+// TMEM -> registers -> (bias, addend, ReLU) -> bf16 -> 128B-swizzled smem staging -> TMA store.  Each warp
+// owns 32 accumulator rows and two 4 KB staging buffers, so the bulk store of chunk i overlaps the TMEM read
+// + math of chunk i+1; TMA clips M/N tails.  TWO: the CTA is one half of a cta_group::2 pair (tile rows
+// m_idx*256 + cta*128, "accumulator drained" is reported to the leader CTA's barrier).
+template <int BNT, int EPI, bool TWO, class SL>
+__device__ __forceinline__ void gemm_epilogue(const GemmParams& p, const CUtensorMap* tma_c, const CUtensorMap* tma_d,
+                                              uint8_t* smem, uint32_t smem_base, uint32_t tmem_base, uint32_t tfull0,
+                                              uint32_t tempty0, int warp, int lane, int cta, int first_tile,
+                                              int tile_stride, int total_tiles) {
+  constexpr int kRowsPerTile = TWO ? 256 : BM;
+  const int q = warp & 3;                   // TMEM lane quarter this warp may access
+  const int ew = warp - kEpiWarp0;
+  const int half = ew >> 2;                 // the two warps of a quarter take alternate column chunks (EPI == 8)
+  const uint32_t stg_base = smem_base + SL::kStagingOffset + ew * SL::kStagingPerWarp;
+  uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
+  int iter = 0;
+  int buf = 0;
+  float st_acc[BNT / 64][4];
+#pragma unroll
+  for (int c = 0; c < BNT / 64; ++c) st_acc[c][0] = st_acc[c][1] = st_acc[c][2] = st_acc[c][3] = 0.f;
+  constexpr int kChunkStep = 64 * (EPI / 4);
+  auto tile_row0 = [&](int tt) { return ((tt / p.num_n) % p.num_m) * kRowsPerTile + cta * BM + q * 32; };
+  auto tile_col = [&](int tt) { return (tt % p.num_n) * BNT; };
+  const bool add_tma = p.addend != nullptr && p.add_tma != 0;
+  const bool add_reg = p.addend != nullptr && p.add_tma == 0;
+  const uint32_t abar0 = smem_base + SL::kAddBarOffset + 16u * ew;     // this warp's two addend barriers
+  AddendPipe ap;
+  ap.state = 0;
+  AddendTma at;
+  at.phases = 0u;
+  at.mnext = make_uint2(0u, 0u);
+  if (first_tile < total_tiles) {
+    if (add_reg) ap.issue(p, tile_row0(first_tile) + lane, tile_col(first_tile) + half * 64);
+    if (add_tma) at.issue(p, tma_d, abar0, stg_base, tile_row0(first_tile), tile_col(first_tile) + half * 64, lane);
+  }
+  for (int t = first_tile; t < total_tiles; t += tile_stride, ++iter) {
+    const int n_idx = t % p.num_n;
+    const int split = t / (p.num_n * p.num_m);
+    const int as = iter & 1;
+    const uint32_t aphase = (iter >> 1) & 1;
+    const int t_next = t + tile_stride;
+    if (t_next < total_tiles) {      // next tile's addend -> L2 while this tile is worked on
+      if (add_reg) AddendPipe::prefetch_l2(p, tile_row0(t_next) + lane, tile_col(t_next), BNT);
+      if (add_tma && lane == 0) {
+#pragma unroll
+        for (int c = half * 64; c < BNT; c += kChunkStep) tma_prefetch_l2_2d(tma_d, tile_col(t_next) + c, tile_row0(t_next));
+      }
+    }
+    mbar_wait(tfull0 + 8u * as, aphase);
+    tcgen05_fence_after();
+    const int row0 = tile_row0(t);
+    const int row = row0 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BNT;
+    if (p.partial != nullptr) {
+      // split-K: fp32 partial tile, 32 columns (128 B) per staging row
+#pragma unroll 1
+      for (int c0 = half * 32; c0 < BNT; c0 += 32 * (EPI / 4)) {
+        uint32_t r[32];
+        tmem_ld32(taddr + c0, r);
+        tmem_ld_wait();
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+        uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
+              make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(tma_c, stg_base + buf * 4096, n_idx * BNT + c0, row0, split);
+          tma_store_commit();
+        }
+        buf ^= 1;
+      }
+    } else {
+#pragma unroll 1
+      for (int c0 = half * 64; c0 < BNT; c0 += kChunkStep) {
+        uint32_t r[64];
+        tmem_ld32(taddr + c0, r);
+        tmem_ld32(taddr + c0 + 32, r + 32);
+        tmem_ld_wait();
+        const int col = n_idx * BNT + c0;
+        float f[64];
+#pragma unroll
+        for (int j = 0; j < 64; ++j) f[j] = __uint_as_float(r[j]);
+        if (p.bias) {
+          if (col + 64 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 64; j += 8) {
+              float b[8];
+              unpack8(*reinterpret_cast<const uint4*>(p.bias + col + j), b);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[j + i] += b[i];
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 64; ++j)
+              if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
+          }
+        }
+        if (add_reg) {
+          ap.apply(p, col, f);
+          // registers for the next chunk (of this tile, else the first chunk of the next tile) go out now
+          if (c0 + kChunkStep < BNT) ap.issue(p, row, col + kChunkStep);
+          else if (t_next < total_tiles) ap.issue(p, tile_row0(t_next) + lane, tile_col(t_next) + half * 64);
+        }
+        if (add_tma) {
+          at.consume(p, abar0 + 8u * buf, buf, stg_ptr + buf * 4096 + lane * 128, lane, f);
+          // the next chunk's addend goes into the other buffer once the store that last used it has read it
+          const bool in_tile = c0 + kChunkStep < BNT;
+          if (in_tile || t_next < total_tiles) {
+            if (lane == 0) tma_store_wait_read<0>();
+            at.issue(p, tma_d, abar0 + 8u * (buf ^ 1), stg_base + (buf ^ 1) * 4096,
+                     in_tile ? row0 : tile_row0(t_next), in_tile ? col + kChunkStep : tile_col(t_next) + half * 64, lane);
+          }
+          __syncwarp();
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 64; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (lane == 0) tma_store_wait_read<1>();  // the buffer written two chunks ago is free
+        __syncwarp();
+        uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
+        if (p.stats) {
+          __syncwarp();
+          float t4[4] = {0.f, 0.f, 0.f, 0.f};
+          chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, t4);
+#pragma unroll
+          for (int c = 0; c < BNT / 64; ++c)      // compile-time indices keep st_acc in registers
+            if (c == (c0 >> 6)) { st_acc[c][0] += t4[0]; st_acc[c][1] += t4[1]; st_acc[c][2] += t4[2]; st_acc[c][3] += t4[3]; }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(tma_c, stg_base + buf * 4096, col, row0);
+          tma_store_commit();
+        }
+        buf ^= 1;
+      }
+    }
+    tcgen05_fence_before();
+    __syncwarp();
+    if (lane == 0) {
+      if (TWO) mbar_arrive_remote(tempty0 + 8u * as, 0);   // the leader's barrier, from both CTAs
+      else mbar_arrive(tempty0 + 8u * as);
+    }
+  }
+  if (lane == 0) tma_store_wait_read<0>();
+  __syncwarp();
+  if (p.stats) {
+    // the column tile of this CTA (pair) is first_tile % num_n for every tile it processed; one partial row per CTA
+    const int part = TWO ? (first_tile / p.num_n) * 2 + cta : first_tile / p.num_n;
+    reduce_store_col_stats<BNT, EPI>(reinterpret_cast<float*>(smem + SL::kStatsOffset), p.stats, part, p.N,
+                                     (first_tile % p.num_n) * BNT, ew, lane, st_acc);
+  }
+}
+
+template <int A_MN, int B_MN, int BN, int STAGES, int EPI>
+__global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                     const __grid_constant__ CUtensorMap tma_b,
-                    const __grid_constant__ CUtensorMap tma_c, const GemmParams p) {
-  using SL = SmemLayout<BN, STAGES>;
+                    const __grid_constant__ CUtensorMap tma_c,
+                    const __grid_constant__ CUtensorMap tma_d, const GemmParams p) {
+  using SL = SmemLayout<BN, STAGES, EPI>;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t smem_base = smem_u32(smem);
   const uint32_t bar_base = smem_base + SL::kBarOffset;
@@ -169,8 +459,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), kEpiWarps);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(s), EPI);  // one arrive per epilogue warp
     }
+    for (int s = 0; s < 2 * EPI; ++s) mbar_init(smem_base + SL::kAddBarOffset + 8u * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -294,139 +585,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       }
     }
   } else if (warp >= kEpiWarp0) {
-    // ============================== epilogue ==============================
-    // TMEM -> registers -> (bias, addend, ReLU) -> bf16 -> 128B-swizzled smem staging -> TMA
-    // store.  Each warp owns 32 accumulator rows and two 4 KB staging buffers, so the bulk
-    // store of chunk i overlaps the TMEM read + math of chunk i+1; TMA clips M/N tails.
-    const int q = warp & 3;                   // TMEM lane quarter this warp may access
-    const int half = (warp - kEpiWarp0) >> 2; // the two warps of a quarter take alternate column chunks
-    const int ew = warp - kEpiWarp0;
-    const uint32_t stg_base = smem_base + SL::kStagingOffset + ew * SL::kStagingPerWarp;
-    uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
-    int iter = 0;
-    int buf = 0;
-    float st_acc[BN / 64][4];
-#pragma unroll
-    for (int c = 0; c < BN / 64; ++c) st_acc[c][0] = st_acc[c][1] = st_acc[c][2] = st_acc[c][3] = 0.f;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
-      const int n_idx = t % p.num_n;
-      const int m_idx = (t / p.num_n) % p.num_m;
-      const int split = t / (p.num_n * p.num_m);
-      const int as = iter & 1;
-      const uint32_t aphase = (iter >> 1) & 1;
-      mbar_wait(tfull_bar(as), aphase);
-      tcgen05_fence_after();
-      const int row0 = m_idx * BM + q * 32;
-      const int row = row0 + lane;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-      if (p.partial != nullptr) {
-        // split-K: fp32 partial tile, 32 columns (128 B) per staging row
-#pragma unroll 1
-        for (int c0 = half * 32; c0 < BN; c0 += 32 * (kEpiWarps / 4)) {
-          uint32_t r[32];
-          tmem_ld32(taddr + c0, r);
-          tmem_ld_wait();
-          if (lane == 0) tma_store_wait_read<1>();
-          __syncwarp();
-          uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
-                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_3d(&tma_c, stg_base + buf * 4096, n_idx * BN + c0, row0, split);
-            tma_store_commit();
-          }
-          buf ^= 1;
-        }
-      } else {
-#pragma unroll 1
-        for (int c0 = half * 64; c0 < BN; c0 += 64 * (kEpiWarps / 4)) {
-          uint32_t r[64];
-          tmem_ld32(taddr + c0, r);
-          tmem_ld32(taddr + c0 + 32, r + 32);
-          tmem_ld_wait();
-          const int col = n_idx * BN + c0;
-          float f[64];
-#pragma unroll
-          for (int j = 0; j < 64; ++j) f[j] = __uint_as_float(r[j]);
-          if (p.bias) {
-            if (col + 64 <= p.N) {
-#pragma unroll
-              for (int j = 0; j < 64; j += 8) {
-                float b[8];
-                unpack8(*reinterpret_cast<const uint4*>(p.bias + col + j), b);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) f[j + i] += b[i];
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 64; ++j)
-                if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
-            }
-          }
-          bool add_row = p.addend && row < p.M;
-          size_t add_idx = (size_t)row;
-          if (add_row && p.add_h > 0) {      // gradient of a 1x1 / stride-2 branch, kept compact (never up-sampled)
-            const int hw = p.add_h * p.add_w;
-            const int ni = row / hw, rem = row - ni * hw, hh = rem / p.add_w, ww = rem - hh * p.add_w;
-            add_row = ((hh | ww) & 1) == 0;
-            add_idx = ((size_t)ni * (p.add_h >> 1) + (hh >> 1)) * (p.add_w >> 1) + (ww >> 1);
-          }
-          if (add_row) {
-            const bf16* ad = p.addend + add_idx * p.ldc + col;
-            if (col + 64 <= p.N) {
-#pragma unroll
-              for (int j = 0; j < 64; j += 8) {
-                float b[8];
-                unpack8(ld_plain(ad + j), b);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) f[j + i] += b[i];
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 64; ++j)
-                if (col + j < p.N) f[j] += __bfloat162float(ad[j]);
-            }
-          }
-          if (p.relu) {
-#pragma unroll
-            for (int j = 0; j < 64; ++j) f[j] = fmaxf(f[j], 0.f);
-          }
-          if (lane == 0) tma_store_wait_read<1>();  // the buffer written two chunks ago is free
-          __syncwarp();
-          uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
-          if (p.stats) {
-            __syncwarp();
-            float t4[4] = {0.f, 0.f, 0.f, 0.f};
-            chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, t4);
-#pragma unroll
-            for (int c = 0; c < BN / 64; ++c)      // compile-time indices keep st_acc in registers
-              if (c == (c0 >> 6)) { st_acc[c][0] += t4[0]; st_acc[c][1] += t4[1]; st_acc[c][2] += t4[2]; st_acc[c][3] += t4[3]; }
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tma_c, stg_base + buf * 4096, col, row0);
-            tma_store_commit();
-          }
-          buf ^= 1;
-        }
-      }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(as));
-    }
-    if (lane == 0) tma_store_wait_read<0>();
-    __syncwarp();
-    if (p.stats)     // this CTA's column tile is blockIdx.x % num_n for every tile it processed
-      reduce_store_col_stats<BN>(reinterpret_cast<float*>(smem + SL::kStatsOffset), p.stats, blockIdx.x / p.num_n, p.N,
-                                 (int)(blockIdx.x % p.num_n) * BN, ew, lane, st_acc);
+    gemm_epilogue<BN, EPI, false, SL>(p, &tma_c, &tma_d, smem, smem_base, tmem_base, tfull_bar(0), tempty_bar(0), warp, lane,
+                                      0, (int)blockIdx.x, (int)gridDim.x, total_tiles);
   }
 
   tcgen05_fence_before();
@@ -447,18 +607,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 // The leader CTA (rank 0) issues every MMA; TMA loads of both CTAs complete on the leader's
 // "full" barrier, commits are multicast to both CTAs' "empty" / "tmem full" barriers, and both
 // CTAs' epilogue warps arrive on the leader's "tmem empty" barrier.
-constexpr int STAGES2 = 5;
+// 5 pipeline stages with 4 epilogue warps, 4 with 8 (their staging buffers take the fifth stage's 32 KB)
+constexpr int stages2(int epi) { return epi == 8 ? 4 : 5; }
 
-template <int BN2>
+template <int BN2, int EPI>
 struct SmemLayout2 {
+  static constexpr int kStages = stages2(EPI);
   static constexpr int kABytes = BM * BK * 2;            // this CTA's 128 rows of A
   static constexpr int kBBytes = (BN2 / 2) * BK * 2;     // this CTA's half of B
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagingOffset = STAGES2 * kStageBytes;
+  static constexpr int kStagingOffset = kStages * kStageBytes;
   static constexpr int kStagingPerWarp = 2 * 4096;
-  static constexpr int kStatsOffset = kStagingOffset + kEpiWarps * kStagingPerWarp;
+  static constexpr int kStatsOffset = kStagingOffset + EPI * kStagingPerWarp;
   static constexpr int kBarOffset = kStatsOffset + kStatsBytes;
-  static constexpr int kTotal = kBarOffset + (2 * STAGES2 + 4) * 8 + 16;
+  static constexpr int kAddBarOffset = kBarOffset + (2 * kStages + 4) * 8 + 16;
+  static constexpr int kTotal = kAddBarOffset + EPI * 2 * 8;
+  static_assert(kTotal + 1024 <= 232448, "shared memory budget");
 };
 
 __device__ __forceinline__ void tma_load_im2col_2sm(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar,
@@ -471,13 +635,14 @@ __device__ __forceinline__ void tma_load_im2col_2sm(uint32_t dst, const CUtensor
       : "memory");
 }
 
-template <int A_MN, int B_MN, int BN2>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+template <int A_MN, int B_MN, int BN2, int EPI>
+__global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b,
-                         const __grid_constant__ CUtensorMap tma_c, const GemmParams p) {
-  using SL = SmemLayout2<BN2>;
-  constexpr int STAGES = STAGES2;
+                         const __grid_constant__ CUtensorMap tma_c,
+                         const __grid_constant__ CUtensorMap tma_d, const GemmParams p) {
+  using SL = SmemLayout2<BN2, EPI>;
+  constexpr int STAGES = SL::kStages;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t smem_base = smem_u32(smem);
   const uint32_t bar_base = smem_base + SL::kBarOffset;
@@ -506,8 +671,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 2 * kEpiWarps);  // epilogue warps of both CTAs
+      mbar_init(tempty_bar(s), 2 * EPI);  // epilogue warps of both CTAs
     }
+    for (int s = 0; s < 2 * EPI; ++s) mbar_init(smem_base + SL::kAddBarOffset + 8u * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -628,123 +794,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       }
     }
   } else if (warp >= kEpiWarp0) {
-    const int q = warp & 3;
-    const int half = (warp - kEpiWarp0) >> 2;
-    const int ew = warp - kEpiWarp0;
-    const uint32_t stg_base = smem_base + SL::kStagingOffset + ew * SL::kStagingPerWarp;
-    uint8_t* stg_ptr = smem + SL::kStagingOffset + ew * SL::kStagingPerWarp;
-    int iter = 0;
-    int buf = 0;
-    float st_acc[BN2 / 64][4];
-#pragma unroll
-    for (int c = 0; c < BN2 / 64; ++c) st_acc[c][0] = st_acc[c][1] = st_acc[c][2] = st_acc[c][3] = 0.f;
-    for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
-      const int n_idx = t % p.num_n;
-      const int m_idx = (t / p.num_n) % p.num_m;
-      const int split = t / (p.num_n * p.num_m);
-      const int as = iter & 1;
-      const uint32_t aphase = (iter >> 1) & 1;
-      mbar_wait(tfull_bar(as), aphase);
-      tcgen05_fence_after();
-      const int row0 = m_idx * 256 + (int)cta * BM + q * 32;
-      const int row = row0 + lane;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN2;
-      if (p.partial != nullptr) {
-#pragma unroll 1
-        for (int c0 = half * 32; c0 < BN2; c0 += 32 * (kEpiWarps / 4)) {
-          uint32_t r[32];
-          tmem_ld32(taddr + c0, r);
-          tmem_ld_wait();
-          if (lane == 0) tma_store_wait_read<1>();
-          __syncwarp();
-          uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
-                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_3d(&tma_c, stg_base + buf * 4096, n_idx * BN2 + c0, row0, split);
-            tma_store_commit();
-          }
-          buf ^= 1;
-        }
-      } else
-#pragma unroll 1
-      for (int c0 = half * 64; c0 < BN2; c0 += 64 * (kEpiWarps / 4)) {
-        uint32_t r[64];
-        tmem_ld32(taddr + c0, r);
-        tmem_ld32(taddr + c0 + 32, r + 32);
-        tmem_ld_wait();
-        const int col = n_idx * BN2 + c0;
-        float f[64];
-#pragma unroll
-        for (int j = 0; j < 64; ++j) f[j] = __uint_as_float(r[j]);
-        if (p.bias) {
-#pragma unroll
-          for (int j = 0; j < 64; ++j)
-            if (col + j < p.N) f[j] += __bfloat162float(p.bias[col + j]);
-        }
-        bool add_row = p.addend && row < p.M;
-        size_t add_idx = (size_t)row;
-        if (add_row && p.add_h > 0) {
-          const int hw = p.add_h * p.add_w;
-          const int ni = row / hw, rem = row - ni * hw, hh = rem / p.add_w, ww = rem - hh * p.add_w;
-          add_row = ((hh | ww) & 1) == 0;
-          add_idx = ((size_t)ni * (p.add_h >> 1) + (hh >> 1)) * (p.add_w >> 1) + (ww >> 1);
-        }
-        if (add_row) {
-          const bf16* ad = p.addend + add_idx * p.ldc + col;
-          if (col + 64 <= p.N) {
-#pragma unroll
-            for (int j = 0; j < 64; j += 8) {
-              float b[8];
-              unpack8(ld_plain(ad + j), b);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[j + i] += b[i];
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 64; ++j)
-              if (col + j < p.N) f[j] += __bfloat162float(ad[j]);
-          }
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 64; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        if (lane == 0) tma_store_wait_read<1>();
-        __syncwarp();
-        uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = pack8(f + 8 * j);
-        if (p.stats) {
-          __syncwarp();
-          float t4[4] = {0.f, 0.f, 0.f, 0.f};
-          chunk_col_stats(stg_ptr + buf * 4096, lane, p.M - row0, t4);
-#pragma unroll
-          for (int c = 0; c < BN2 / 64; ++c)
-            if (c == (c0 >> 6)) { st_acc[c][0] += t4[0]; st_acc[c][1] += t4[1]; st_acc[c][2] += t4[2]; st_acc[c][3] += t4[3]; }
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_2d(&tma_c, stg_base + buf * 4096, col, row0);
-          tma_store_commit();
-        }
-        buf ^= 1;
-      }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_remote(tempty_bar(as), 0);   // the leader's barrier, from both CTAs
-    }
-    if (lane == 0) tma_store_wait_read<0>();
-    __syncwarp();
-    if (p.stats)     // the pair's column tile is pair % num_n for every tile it processed
-      reduce_store_col_stats<BN2>(reinterpret_cast<float*>(smem + SL::kStatsOffset), p.stats,
-                                  (pair / p.num_n) * 2 + (int)cta, p.N, (pair % p.num_n) * BN2, ew, lane, st_acc);
+    gemm_epilogue<BN2, EPI, true, SL>(p, &tma_c, &tma_d, smem, smem_base, tmem_base, tfull_bar(0), tempty_bar(0), warp, lane,
+                                      (int)cta, pair, num_pairs, total_tiles);
   }
 
   tcgen05_fence_before();
@@ -878,11 +929,23 @@ static int stats_grid(int want, int num_n) {
   return g < num_n ? num_n : g;
 }
 
-template <int A_MN, int B_MN, int BN, int STAGES>
-static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
-                  const GemmParams& p, cudaStream_t stream) {
-  using SL = SmemLayout<BN, STAGES>;
-  auto kern = gemm_tcgen05_kernel<A_MN, B_MN, BN, STAGES>;
+// Epilogue warps for a launch: 8 when a tile carries little K (epilogue-bound, see the top of the file),
+// 4 for deep K.  KDL_GEMM_EPI=4|8 forces one (A/B runs).
+static int pick_epi(int k_per_tile, bool two_cta) {
+  static int env = -1;
+  if (env < 0) {
+    const char* e = getenv("KDL_GEMM_EPI");
+    env = e ? atoi(e) : 0;
+  }
+  if (env == 4 || env == 8) return env;
+  return k_per_tile <= (two_cta ? 512 : 256) ? 8 : 4;
+}
+
+template <int A_MN, int B_MN, int BN, int STAGES, int EPI>
+static int launch_e(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md,
+                    const GemmParams& p, cudaStream_t stream) {
+  using SL = SmemLayout<BN, STAGES, EPI>;
+  auto kern = gemm_tcgen05_kernel<A_MN, B_MN, BN, STAGES, EPI>;
   static bool attr_done = false;
   if (!attr_done) {
     KDL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::kTotal + 1024));
@@ -891,16 +954,25 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
   int tiles = p.num_m * p.num_n * p.splits;
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (p.stats) grid = stats_grid(grid, p.num_n);   // every CTA keeps one column tile (register-held statistics)
-  kern<<<grid, kGemmThreads, SL::kTotal + 1024, stream>>>(ma, mb, mc, p);
+  kern<<<grid, gemm_threads(EPI), SL::kTotal + 1024, stream>>>(ma, mb, mc, md, p);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }
 
-template <int A_MN, int B_MN, int BN2 = 256>
-static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
-                       const GemmParams& p, cudaStream_t stream) {
-  using SL = SmemLayout2<BN2>;
-  auto kern = gemm_tcgen05_2cta_kernel<A_MN, B_MN, BN2>;
+// BN = 128: 5 stages with 4 epilogue warps, 4 with 8;  BN = 64: 6 / 5.
+template <int A_MN, int B_MN, int BN, int STAGES>
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md,
+                  const GemmParams& p, cudaStream_t stream) {
+  const int k_per_tile = (p.kb_per_split > 0 ? p.kb_per_split : (p.K + BK - 1) / BK) * BK;
+  if (pick_epi(k_per_tile, false) == 8) return launch_e<A_MN, B_MN, BN, STAGES - 1, 8>(ma, mb, mc, md, p, stream);
+  return launch_e<A_MN, B_MN, BN, STAGES, 4>(ma, mb, mc, md, p, stream);
+}
+
+template <int A_MN, int B_MN, int BN2, int EPI>
+static int launch_2cta_e(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md,
+                         const GemmParams& p, cudaStream_t stream) {
+  using SL = SmemLayout2<BN2, EPI>;
+  auto kern = gemm_tcgen05_2cta_kernel<A_MN, B_MN, BN2, EPI>;
   static bool attr_done = false;
   if (!attr_done) {
     KDL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::kTotal + 1024));
@@ -912,7 +984,7 @@ static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
   if (p.stats) pairs = stats_grid(pairs, p.num_n);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
-  cfg.blockDim = dim3(kGemmThreads);
+  cfg.blockDim = dim3(gemm_threads(EPI));
   cfg.dynamicSmemBytes = SL::kTotal + 1024;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -922,17 +994,28 @@ static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  KDL_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, p));
+  KDL_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, md, p));
   return KDL_OK;
+}
+
+template <int A_MN, int B_MN, int BN2 = 256>
+static int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md,
+                       const GemmParams& p, cudaStream_t stream) {
+  const int k_per_tile = (p.kb_per_split > 0 ? p.kb_per_split : (p.K + BK - 1) / BK) * BK;
+  // the 8-warp epilogue exists for plain / im2col fprop and dgrad tiles; split-K partial tiles (wgrad) are
+  // deep-K by construction
+  if (p.partial == nullptr && pick_epi(k_per_tile, true) == 8)
+    return launch_2cta_e<A_MN, B_MN, BN2, 8>(ma, mb, mc, md, p, stream);
+  return launch_2cta_e<A_MN, B_MN, BN2, 4>(ma, mb, mc, md, p, stream);
 }
 
 template <int BN, int STAGES>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
-                          const CUtensorMap& mc, const GemmParams& p, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch<0, 0, BN, STAGES>(ma, mb, mc, p, s);
-  if (!a_mn && b_mn) return launch<0, 1, BN, STAGES>(ma, mb, mc, p, s);
-  if (a_mn && b_mn) return launch<1, 1, BN, STAGES>(ma, mb, mc, p, s);
-  return launch<1, 0, BN, STAGES>(ma, mb, mc, p, s);
+                          const CUtensorMap& mc, const CUtensorMap& md, const GemmParams& p, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch<0, 0, BN, STAGES>(ma, mb, mc, md, p, s);
+  if (!a_mn && b_mn) return launch<0, 1, BN, STAGES>(ma, mb, mc, md, p, s);
+  if (a_mn && b_mn) return launch<1, 1, BN, STAGES>(ma, mb, mc, md, p, s);
+  return launch<1, 0, BN, STAGES>(ma, mb, mc, md, p, s);
 }
 
 }  // namespace kdl
@@ -991,16 +1074,30 @@ extern "C" int kdl_gemm_max_ctas(void) { return num_sms(); }
 
 static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major, int b_mn_major,
                      int lda, int ldb, int ldc, const void* bias, const void* addend, int add_h, int add_w,
-                     int relu, int split_k, void* scratch, size_t scratch_bytes, float* stats_partial,
-                     int* stats_parts_out, cudaStream_t stream);
+                     const void* add_mask, int relu, int split_k, void* scratch, size_t scratch_bytes,
+                     float* stats_partial, int* stats_parts_out, cudaStream_t stream);
 
 extern "C" int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
                                 int a_mn_major, int b_mn_major, int lda, int ldb, int ldc,
                                 const void* bias, const void* addend, int relu, int split_k,
                                 void* scratch, size_t scratch_bytes, float* stats_partial,
                                 int* stats_parts_out, cudaStream_t stream) {
-  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, bias, addend, 0, 0, relu, split_k,
-                   scratch, scratch_bytes, stats_partial, stats_parts_out, stream);
+  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, bias, addend, 0, 0, nullptr, relu,
+                   split_k, scratch, scratch_bytes, stats_partial, stats_parts_out, stream);
+}
+
+// C[M, N] = A B + (mask ? addend : 0): `relu_mask` is the [M*N/8] bit mask a BatchNorm forward saved
+// (kdl_bn_fwd_mask), i.e. the addend is a gradient that still has to pass that ReLU.  Lets the residual
+// branch of a bottleneck read dOut and the mask instead of a separately written dOut * mask tensor.
+extern "C" int kdl_gemm_bf16_maskadd(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                                     int b_mn_major, int lda, int ldb, int ldc, const void* addend,
+                                     const void* relu_mask, cudaStream_t stream) {
+  if (addend == nullptr || relu_mask == nullptr || (N & 63) || ldc != N || ((uintptr_t)relu_mask & 7)) {
+    kdl_set_error("gemm_maskadd: need addend, an 8-byte aligned mask, N %% 64 == 0 and ldc == N (N=%d ldc=%d)", N, ldc);
+    return KDL_ERR_ARG;
+  }
+  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, nullptr, addend, 0, 0, relu_mask, 0, 1,
+                   nullptr, 0, nullptr, nullptr, stream);
 }
 
 // C[M, N] = A B (+ addend): rows of C are the pixels of an [n, H, W] map and `addend_compact` is the
@@ -1012,8 +1109,8 @@ extern "C" int kdl_gemm_bf16_subadd(const void* A, const void* B, void* C, int M
     kdl_set_error("gemm_subadd: need even H, W and M a multiple of H*W (M=%d H=%d W=%d)", M, H, W);
     return KDL_ERR_ARG;
   }
-  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, nullptr, addend_compact, H, W, 0, 1,
-                   nullptr, 0, nullptr, nullptr, stream);
+  return gemm_impl(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, nullptr, addend_compact, H, W, nullptr,
+                   0, 1, nullptr, 0, nullptr, nullptr, stream);
 }
 
 extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
@@ -1026,8 +1123,8 @@ extern "C" int kdl_gemm_bf16(const void* A, const void* B, void* C, int M, int N
 
 static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major, int b_mn_major,
                      int lda, int ldb, int ldc, const void* bias, const void* addend, int add_h, int add_w,
-                     int relu, int split_k, void* scratch, size_t scratch_bytes, float* stats_partial,
-                     int* stats_parts_out, cudaStream_t stream) {
+                     const void* add_mask, int relu, int split_k, void* scratch, size_t scratch_bytes,
+                     float* stats_partial, int* stats_parts_out, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) {
     kdl_set_error("gemm: bad shape %dx%dx%d", M, N, K);
     return KDL_ERR_ARG;
@@ -1046,6 +1143,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   p.bias = (const bf16*)bias;
   p.addend = (const bf16*)addend;
   p.add_h = add_h; p.add_w = add_w;
+  p.add_mask = (const uint8_t*)add_mask;
   p.relu = relu;
   p.splits = splits;
   const int kb_total = (K + BK - 1) / BK;
@@ -1085,6 +1183,13 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   if (b_mn_major) rc = make_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
   else rc = make_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, two ? (uint32_t)128 : (uint32_t)bn);
   if (rc) return rc;
+  // full-size addend: its own map with the output's box shape, so a chunk lands in a staging buffer
+  // exactly as the result chunk will be laid out there (the compact stride-2 addend stays on loads)
+  CUtensorMap md;
+  rc = make_c_map(&md, addend != nullptr && add_h == 0 ? const_cast<void*>(addend) : C, 0, (uint64_t)M, (uint64_t)N,
+                  (uint64_t)ldc, 1);
+  if (rc) return rc;
+  p.add_tma = (addend != nullptr && add_h == 0 && ((uintptr_t)addend & 15) == 0) ? 1 : 0;
   if (two) {
     CUtensorMap mc2;
     rc = make_c_map(&mc2, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);
@@ -1095,10 +1200,10 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       int tiles2 = p.num_m * p.num_n, pairs = num_sms() / 2;
       *stats_parts_out = (stats_grid(tiles2 < pairs ? tiles2 : pairs, p.num_n) / p.num_n) * 2;
     }
-    if (!a_mn_major && !b_mn_major) return launch_2cta<0, 0>(ma, mb, mc2, p, stream);
-    if (!a_mn_major && b_mn_major) return launch_2cta<0, 1>(ma, mb, mc2, p, stream);
-    if (a_mn_major && b_mn_major) return launch_2cta<1, 1>(ma, mb, mc2, p, stream);
-    return launch_2cta<1, 0>(ma, mb, mc2, p, stream);
+    if (!a_mn_major && !b_mn_major) return launch_2cta<0, 0>(ma, mb, mc2, md, p, stream);
+    if (!a_mn_major && b_mn_major) return launch_2cta<0, 1>(ma, mb, mc2, md, p, stream);
+    if (a_mn_major && b_mn_major) return launch_2cta<1, 1>(ma, mb, mc2, md, p, stream);
+    return launch_2cta<1, 0>(ma, mb, mc2, md, p, stream);
   }
   if (stats_parts_out) {
     int tiles1 = p.num_m * p.num_n * p.splits;
@@ -1108,8 +1213,8 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)N, (uint64_t)N, (uint64_t)splits);
   else rc = make_c_map(&mc, C, 0, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 1);
   if (rc) return rc;
-  if (bn == 64) rc = dispatch_major<64, 6>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
-  else rc = dispatch_major<128, 5>(a_mn_major, b_mn_major, ma, mb, mc, p, stream);
+  if (bn == 64) rc = dispatch_major<64, 6>(a_mn_major, b_mn_major, ma, mb, mc, md, p, stream);
+  else rc = dispatch_major<128, 5>(a_mn_major, b_mn_major, ma, mb, mc, md, p, stream);
   if (rc) return rc;
   if (splits > 1) {
     int64_t MN = (int64_t)M * N;
@@ -1231,14 +1336,20 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
     if (rc) return rc;
     rc = make_c_map(&mc, out, 0, (uint64_t)M, (uint64_t)Nout, (uint64_t)Nout, 1);
     if (rc) return rc;
+    CUtensorMap md = mc;
+    if (addend != nullptr && ((uintptr_t)addend & 15) == 0) {
+      rc = make_c_map(&md, const_cast<void*>(addend), 0, (uint64_t)M, (uint64_t)Nout, (uint64_t)Nout, 1);
+      if (rc) return rc;
+      p.add_tma = 1;
+    }
     if (two) {
       p.num_m = (M + 255) / 256;
       p.num_n = (Nout + bn2 - 1) / bn2;
-      if (mode == 0) return bn2 == 256 ? launch_2cta<0, 0, 256>(ma, mb, mc, p, stream) : launch_2cta<0, 0, 128>(ma, mb, mc, p, stream);
-      return bn2 == 256 ? launch_2cta<0, 1, 256>(ma, mb, mc, p, stream) : launch_2cta<0, 1, 128>(ma, mb, mc, p, stream);
+      if (mode == 0) return bn2 == 256 ? launch_2cta<0, 0, 256>(ma, mb, mc, md, p, stream) : launch_2cta<0, 0, 128>(ma, mb, mc, md, p, stream);
+      return bn2 == 256 ? launch_2cta<0, 1, 256>(ma, mb, mc, md, p, stream) : launch_2cta<0, 1, 128>(ma, mb, mc, md, p, stream);
     }
-    if (mode == 0) return bn == 64 ? launch<0, 0, 64, 6>(ma, mb, mc, p, stream) : launch<0, 0, 128, 5>(ma, mb, mc, p, stream);
-    return bn == 64 ? launch<0, 1, 64, 6>(ma, mb, mc, p, stream) : launch<0, 1, 128, 5>(ma, mb, mc, p, stream);
+    if (mode == 0) return bn == 64 ? launch<0, 0, 64, 6>(ma, mb, mc, md, p, stream) : launch<0, 0, 128, 5>(ma, mb, mc, md, p, stream);
+    return bn == 64 ? launch<0, 1, 64, 6>(ma, mb, mc, md, p, stream) : launch<0, 1, 128, 5>(ma, mb, mc, md, p, stream);
   }
   if (mode == 2) {
     const int M = Cout, Nn = R * S * Cin, K = N * OH * OW;
@@ -1285,12 +1396,13 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
     if (splits > 1) rc = make_c_map(&mc, p.partial, 1, (uint64_t)M, (uint64_t)Nn, (uint64_t)Nn, (uint64_t)splits);
     else rc = make_c_map(&mc, out, 0, (uint64_t)M, (uint64_t)Nn, (uint64_t)Nn, 1);
     if (rc) return rc;
+    const CUtensorMap md = mc;
     if (two) {
       p.num_m = (M + 255) / 256;
       p.num_n = (Nn + 255) / 256;
-      rc = launch_2cta<1, 1, 256>(ma, mb, mc, p, stream);
+      rc = launch_2cta<1, 1, 256>(ma, mb, mc, md, p, stream);
     } else {
-      rc = bn == 64 ? launch<1, 1, 64, 6>(ma, mb, mc, p, stream) : launch<1, 1, 128, 5>(ma, mb, mc, p, stream);
+      rc = bn == 64 ? launch<1, 1, 64, 6>(ma, mb, mc, md, p, stream) : launch<1, 1, 128, 5>(ma, mb, mc, md, p, stream);
     }
     if (rc) return rc;
     if (splits > 1) {

@@ -150,6 +150,13 @@ int kdl_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K,
 int kdl_gemm_bf16_subadd(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
                          int b_mn_major, int lda, int ldb, int ldc, const void* addend_compact, int H, int W,
                          cudaStream_t stream);
+/* C = A B + (mask ? addend : 0): relu_mask is the [M*N/8] bit mask of kdl_bn_fwd_mask (bit j of byte v <->
+ * element 8v+j).  N % 64 == 0, ldc == N.  The stock worker materialises dOut * mask in a separate
+ * elementwise kernel (ATen threshold_backward); the reference operator has no math (reference
+ * example/pytorch/pytorch_job_mnist_mpi.yaml:15 names an image). */
+int kdl_gemm_bf16_maskadd(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                          int b_mn_major, int lda, int ldb, int ldc, const void* addend,
+                          const void* relu_mask, cudaStream_t stream);
 
 /* ---- N7c: the 7x7 / stride-2 stem convolution straight from the uint8 image (224x224) -----------------
  * Builder warps normalise the image rows and write the patch tile of one output row directly in the
@@ -264,6 +271,13 @@ int kdl_allreduce_fused(const void* const* in_ptrs, void* const* out_ptrs, void*
                         int in_dtype, int out_dtype, float scale, void* epoch_state, int channels,
                         int channel, int max_blocks, int emulate, void* status, unsigned long long timeout_ns,
                         cudaStream_t stream);
+/* Flag-only barrier over the same flag / epoch arrays (own `channel`, same call order on all ranks):
+ * everything the ranks enqueued on `stream` before it has completed on EVERY rank before anything
+ * enqueued after it starts on any rank.  Graph-replayable like the all-reduce.  No counterpart in
+ * the reference (it has no communication backend; reference pkg/job_controller/service.go:237-295). */
+int kdl_symm_barrier(void* const* flag_ptrs, int world, int rank, void* epoch_state, int channels,
+                     int channel, int emulate, void* status, unsigned long long timeout_ns,
+                     cudaStream_t stream);
 
 /* ---- symmetric memory plumbing ------------------------------------------
  * Legacy CUDA IPC path (cudaMalloc + cudaIpc handles) and VMM path (cuMemCreate + POSIX fd

@@ -6,9 +6,15 @@ Per sample: user id, candidate item id and L history item ids index ONE table E[
 rows, sharded by row range over the ranks, each shard in the symmetric heap).  Forward =
 `kdl_din_gather_attend` (remote pull + attention pooling + concat, kernel N4) -> MLP 256-512-256-1
 on the tcgen05 GEMM -> sigmoid BCE.  Backward = MLP backward on the GEMM (nn / tn variants) ->
-`kdl_din_scatter_update` (pooling backward + remote red.add sparse-SGD, kernel N5) -> fused
-all-reduce of the dense MLP gradients (which is also the cross-rank barrier that orders this
-step's table updates before the next step's reads) -> fused SGD.
+device barrier -> `kdl_din_scatter_update` (pooling backward + remote red.add sparse-SGD, kernel N5)
+-> fused all-reduce of the dense MLP gradients -> fused SGD.
+
+Ordering of table reads and writes across ranks (synchronous SGD, same result as one GPU holding the
+whole table): the flag barrier in front of the scatter makes sure EVERY rank's forward gather of step
+N is complete before ANY rank applies step-N updates to the shards (a slow rank would otherwise read
+rows its peers are already adding to, 16 bytes at a time); the entry barrier of the dense-gradient
+all-reduce orders every rank's step-N updates before anybody's step-N+1 gather.  Both barriers keep
+their epoch on the device, so the step stays one replayable CUDA graph.
 
 The XDLJob controller supplies TASK_NAME/TASK_INDEX (reference
 controllers/xdl/xdljob_controller.go:191-217); XDL's own PS/worker exchange over ZooKeeper is what
@@ -70,10 +76,11 @@ class DINModel:
             self.arena.w32("w3")[1:].zero_()
             self.arena.p16.copy_(self.arena.p32)
         self.gemm = Gemm(self.dev)
-        self.ar = None
+        self.ar = self.gather_done = None
         if self.world > 1:
-            from ..parallel.collectives import FusedAllReduce
+            from ..parallel.collectives import FusedAllReduce, SymmBarrier
             self.ar = FusedAllReduce(heap)
+            self.gather_done = SymmBarrier(heap)      # its own flag channel
             dist.barrier(group=group)
         self.saved = None
 
@@ -112,6 +119,9 @@ class DINModel:
         dx = self.gemm.nn(dh1, a.w16("w1"))
         a.grad("w3")[1:].zero_()            # padded output columns carry no parameters
         a.grad("b3")[1:].zero_()
+        if self.gather_done is not None:
+            # nobody updates a shard while a slower peer may still be gathering this step's rows from it
+            self.gather_done()
         L.check(self.lib.kdl_din_scatter_update(self._shard_tab, self.world, self.rows_per_rank, user.data_ptr(),
                                                 cand.data_ptr(), hist.data_ptr(), B, self.L, D, x.data_ptr(),
                                                 dx.data_ptr(), hs.data_ptr(), aw.data_ptr(), self.emb_lr,
@@ -156,7 +166,8 @@ class DINModel:
         a = self.arena
         if self.ar is not None:
             # dense-gradient all-reduce; its entry barrier also orders every rank's table updates
-            # of this step before anybody's gathers of the next step
+            # of this step before anybody's gathers of the next step (the gather -> update order inside
+            # a step is the SymmBarrier in backward())
             self.ar(a.g16_off, a.total, torch.bfloat16)
         K.sgd_momentum(a.p32, a.mom, a.g16, a.p16, self.lr, 0.0, 0.0, wd_count=a.wd_count)
         return loss

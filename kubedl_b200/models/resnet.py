@@ -78,10 +78,12 @@ class Conv:
         return (_nhwc(y), None) if want_stats else _nhwc(y)
 
     def bwd(self, dy: torch.Tensor, x: torch.Tensor, need_dx: bool = True,
-            addend: Optional[torch.Tensor] = None, addend_compact: bool = False) -> Optional[torch.Tensor]:
+            addend: Optional[torch.Tensor] = None, addend_compact: bool = False,
+            addend_mask: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         """Returns dx (+ addend, the gradient arriving over the residual branch — fused into the
         dgrad GEMM epilogue on the tcgen05 path; addend_compact: it is the [N, H/2, W/2, Cin] result
-        of a stride-2 sibling's bwd_compact)."""
+        of a stride-2 sibling's bwd_compact; addend_mask: the addend still has to pass the block's output
+        ReLU, whose 1-bit mask the epilogue applies — GEMM path only)."""
         net = self.net
         if self.is_gemm and net.gemm is not None:
             N, H, W, Cin = x.shape
@@ -92,7 +94,8 @@ class Conv:
             if need_dx:
                 dx = net.gemm.nn(dy2, self.w.view(self.cout, Cin),
                                  addend=None if addend is None else addend.view(-1, Cin),
-                                 addend_hw=(H, W) if addend_compact else None).view(N, H, W, Cin)
+                                 addend_hw=(H, W) if addend_compact else None,
+                                 addend_mask=addend_mask).view(N, H, W, Cin)
         elif self.own_conv:
             conv_ops.wgrad(dy, x, self.k, self.k, self.stride, self.pad, out=net.arena.grad(self.name))
             dx = None
@@ -207,8 +210,15 @@ class Bottleneck:
     def bwd(self, dout, need_dx=True):
         x, c1, a1, c2, a2, c3, cdo, out = self.saved
         self.saved = None
-        dc3 = self.b3.bwd(dout, c3, out, dres=dout, had_residual=True)  # dout now holds dz (grad of the residual)
-        dres = dout
+        # Identity blocks: dz = dout * relu'(out) is needed once more, as the residual term of this block's
+        # input gradient.  Instead of having the BatchNorm backward write it (one more activation-sized
+        # store), conv1's dgrad epilogue reads dout and the 1-bit mask itself.
+        net = self.c1.net
+        mask_addend = (self.cd is None and net.mask_addend and self.b3.mask is not None
+                       and self.c1.is_gemm and net.gemm is not None)
+        amask = self.b3.mask if mask_addend else None
+        dc3 = self.b3.bwd(dout, c3, out, dres=None if mask_addend else dout, had_residual=True)
+        dres = dout       # dz unless mask_addend (then still the unmasked dout, masked by the consumer)
         da2 = self.c3.bwd(dc3, a2)
         dc2 = self.b2.bwd(da2, c2, a2)
         da1 = self.c2.bwd(dc2, a1)
@@ -220,7 +230,7 @@ class Bottleneck:
             else:
                 dx = self.c1.bwd(dc1, x, addend=self.cd.bwd(dcd, x))
         else:
-            dx = self.c1.bwd(dc1, x, addend=dres)
+            dx = self.c1.bwd(dc1, x, addend=dres, addend_mask=amask)
         return dx
 
 
@@ -240,6 +250,8 @@ class ResNet50:
         self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "1") == "1"
         # ReLU masks of the residual BatchNorms as 1 bit per element (0: the backward pass reads y)
         self.bn_relu_bitmask = _os.environ.get("KUBEDL_BN_BITMASK", "1") == "1"
+        # identity blocks: the residual gradient is masked inside conv1's dgrad epilogue (no dz tensor)
+        self.mask_addend = _os.environ.get("KUBEDL_MASK_ADDEND", "1") == "1"
         # stem convolution straight from the uint8 image (224x224 inputs); 0: im2col patch matrix + GEMM
         self.stem_direct = _os.environ.get("KUBEDL_STEM_DIRECT", "1") == "1"
         self.fuse_stem_pool = _os.environ.get("KUBEDL_FUSE_STEM_POOL", "1") == "1"

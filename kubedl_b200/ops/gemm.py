@@ -31,6 +31,8 @@ L.register_signatures({
     "kdl_gemm_bf16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                 C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kdl_gemm_bf16_maskadd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                        C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
 })
 
 
@@ -90,16 +92,28 @@ class Gemm:
         return self._run(a, b, out, M, N, K, 0, 0, bias, addend, relu, 1)
 
     def nn(self, a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
-           addend: Optional[torch.Tensor] = None, addend_hw=None) -> torch.Tensor:
+           addend: Optional[torch.Tensor] = None, addend_hw=None,
+           addend_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         """out = a @ b (+ addend).  addend_hw=(H, W): the rows of `out` are the pixels of an [n, H, W] map
         and `addend` is the compact [n*H/2*W/2, N] gradient of a 1x1 / stride-2 branch, added at even
-        (h, w) only — the up-sampled (three quarters zero) tensor is never materialised."""
+        (h, w) only — the up-sampled (three quarters zero) tensor is never materialised.
+        addend_mask: uint8 [M*N/8] ReLU bit mask (ops.nn.bn_fwd(relu_mask=...)); the addend is added only
+        where its bit is set, i.e. out = a @ b + relu'(.) * addend without a masked copy of the addend."""
         _chk(a); _chk(b)
         M, K = a.shape
         K2, N = b.shape
         assert K == K2
         if out is None:
             out = torch.empty(M, N, dtype=torch.bfloat16, device=a.device)
+        if addend_mask is not None:
+            _chk(addend)
+            assert addend_hw is None and addend.shape == (M, N) and addend.stride(0) == N and out.stride(0) == N
+            assert addend_mask.dtype == torch.uint8 and addend_mask.numel() * 8 == M * N
+            L.check(self.lib.kdl_gemm_bf16_maskadd(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, 0, 1, a.stride(0),
+                                                   b.stride(0), N, addend.data_ptr(), addend_mask.data_ptr(),
+                                                   L.stream_ptr()), "kdl_gemm_bf16_maskadd")
+            L.count(1)
+            return out
         if addend_hw is not None:
             H, W = addend_hw
             _chk(addend)

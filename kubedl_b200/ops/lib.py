@@ -75,6 +75,8 @@ _SIGS = {
                                     c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_int,
                                     c_float, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                     c_ull, c_void_p]),
+    "kdl_symm_barrier": (c_int, [C.POINTER(c_void_p), c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
+                                 c_ull, c_void_p]),
     "kdl_symm_malloc": (c_int, [c_size_t, C.POINTER(c_void_p)]),
     "kdl_symm_free": (c_int, [c_void_p]),
     "kdl_ipc_get_handle": (c_int, [c_void_p, c_void_p]),

@@ -66,6 +66,51 @@ class FusedAllReduce:
             L.count(1)
 
 
+class SymmBarrier:
+    """Device-side barrier over the symmetric heap's flag words (`kdl_symm_barrier`): what this rank
+    enqueued before it has finished on every rank before anything enqueued after it starts anywhere.
+    One tiny launch, no host round trip, replayable from a CUDA graph (the epoch lives on the device).
+    Every user takes its own flag `channel` (the gradient all-reduce uses the low ones)."""
+
+    def __init__(self, heap: SymmetricHeap, channel: int = FLAG_CHANNELS - 1, timeout_s: float = 30.0):
+        assert 0 <= channel < FLAG_CHANNELS
+        self.heap, self.channel = heap, channel
+        self.lib = L.lib()
+        self.timeout_ns = int(timeout_s * 1e9)
+        self._flag_tab = heap.ptr_table(heap.flags_off)
+        self._status_ptr = heap.peer_ptrs[heap.rank] + heap.status_off
+
+    def __call__(self) -> None:
+        h = self.heap
+        if h.world == 1:
+            return
+        rc = self.lib.kdl_symm_barrier(self._flag_tab, h.world, h.rank, h.epoch_state.data_ptr(), FLAG_CHANNELS,
+                                       self.channel, 0, self._status_ptr, self.timeout_ns, L.stream_ptr())
+        L.check(rc, "kdl_symm_barrier")
+        L.count(1)
+
+
+def emulated_barrier(world: int, device, channel: int = FLAG_CHANNELS - 1):
+    """Single-GPU protocol test of `kdl_symm_barrier`: all ranks inside one cooperative launch."""
+    lib = L.lib()
+    fb = lib.kdl_allreduce_flags_bytes(FLAG_CHANNELS)
+    flags = [torch.zeros(fb // 4, dtype=torch.int32, device=device) for _ in range(world)]
+    epochs = torch.zeros(world * fb // 4, dtype=torch.int32, device=device)
+    status = torch.zeros(64, dtype=torch.int32, device=device)
+    ft = (C.c_void_p * 8)()
+    for r in range(world):
+        ft[r] = flags[r].data_ptr()
+
+    def run():
+        rc = lib.kdl_symm_barrier(ft, world, 0, epochs.data_ptr(), FLAG_CHANNELS, channel, 1, status.data_ptr(),
+                                  int(10e9), L.stream_ptr())
+        L.check(rc, "kdl_symm_barrier(emulate)")
+        L.count(1)
+
+    run.state = dict(flags=flags, epochs=epochs, status=status)
+    return run
+
+
 class NcclAllReduce:
     """Baseline: torch.distributed all_reduce (NCCL) followed by the separate scale kernel."""
 

@@ -77,6 +77,21 @@ chk = [torch.empty_like(m.arena.p32) for _ in range(world)]
 dist.all_gather(chk, m.arena.p32)
 res["din"]["dense_identical_on_all_ranks"] = all(torch.equal(chk[0], c_) for c_ in chk)
 assert res["din"]["dense_identical_on_all_ranks"]
+# several more steps through the CUDA-graph path: gather -> device barrier -> remote updates -> all-reduce,
+# replayed; ranks are deliberately skewed on the host so a missing gather/update order would show
+import time
+losses = []
+for it in range(6):
+    if rank == (it % world):
+        time.sleep(0.02)
+    losses.append(float(m.step(user, cand, hist, label)))
+torch.cuda.synchronize(); dist.barrier()
+res["din"]["graph_steps_losses"] = [round(x, 5) for x in losses]
+res["din"]["status_word"] = int(m.heap.status_word())
+assert all(x == x for x in losses) and losses[-1] < losses[0] and res["din"]["status_word"] == 0, res["din"]
+chk = [torch.empty_like(m.arena.p32) for _ in range(world)]
+dist.all_gather(chk, m.arena.p32)
+assert all(torch.equal(chk[0], c_) for c_ in chk)
 if rank == 0:
     print(json.dumps(res), flush=True)
 dist.barrier(); dist.destroy_process_group()

@@ -134,3 +134,47 @@ def test_nn_compact_stride2_addend(cuda):
         ref[:, ::2, ::2, :] += addc.float()
         err = float((out.view(n, H, W, N).float() - ref).abs().max() / ref.abs().max())
         assert err < 1.5e-2, (n, H, W, K, N, err)
+
+
+@pytest.mark.parametrize("M,N,K", [
+    (256, 128, 64),        # one tile, one chunk pair
+    (50000, 256, 64),      # 1-CTA kernel, many tiles per CTA (register + L2 prefetch across tiles), M tail
+    (4099, 320, 128),      # partial N tile: the element-wise tail path
+    (6000, 1024, 256),     # 2-CTA kernel, 4 chunks per warp and tile, M tail
+    (40000, 512, 128),     # 1-CTA kernel, 4 column tiles
+])
+def test_nn_addend_prefetch_pipeline(cuda, M, N, K):
+    """The addend registers are loaded one chunk (and one tile) ahead of where they are added: every
+    chunk must still receive ITS rows and columns, on both kernels, including tails."""
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(21)
+    a = torch.randn(M, K, device=cuda).bfloat16()
+    b = (torch.randn(K, N, device=cuda) * 0.05).bfloat16()
+    add = torch.randn(M, N, device=cuda).bfloat16()
+    out = g.nn(a, b, addend=add)
+    ref = a.float() @ b.float() + add.float()
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+    # the addend dominates the product here, so a chunk that got another chunk's addend shows up element-wise
+    assert float((out.float() - ref).abs().max()) < 0.1
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 64, 64), (50000, 256, 64), (6000, 1024, 256), (12544, 2048, 512)])
+def test_nn_masked_addend_matches_masked_copy(cuda, M, N, K):
+    """out = a @ b + mask * addend with the 1-bit ReLU mask BatchNorm saves (bit j of byte v <-> element 8v+j)
+    == the same GEMM fed a separately masked copy of the addend."""
+    from kubedl_b200.ops.gemm import Gemm
+    g = Gemm(cuda)
+    torch.manual_seed(22)
+    a = torch.randn(M, K, device=cuda).bfloat16()
+    b = (torch.randn(K, N, device=cuda) * 0.05).bfloat16()
+    add = torch.randn(M, N, device=cuda).bfloat16()
+    keep = torch.rand(M, N, device=cuda) < 0.6
+    weights = (1 << torch.arange(8, device=cuda, dtype=torch.int32))
+    mask = (keep.view(-1, 8).int() * weights).sum(1).to(torch.uint8)
+    out = g.nn(a, b, addend=add, addend_mask=mask)
+    ref = a.float() @ b.float() + add.float() * keep
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+    assert float((out.float() - ref).abs().max()) < 0.1
+    want = g.nn(a, b, addend=(add.float() * keep).bfloat16())
+    assert torch.equal(out, want)

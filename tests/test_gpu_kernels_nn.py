@@ -204,6 +204,33 @@ def test_allreduce_protocol_emulated(cuda, W, n, dt_in, dt_out):
     assert int(run.state["status"][0].item()) == 0
 
 
+@pytest.mark.parametrize("W", [2, 4, 8])
+def test_symm_barrier_protocol_emulated(cuda, W):
+    """`kdl_symm_barrier` with all W ranks inside one cooperative launch: returns (no rank is left waiting),
+    advances every rank's device-side epoch by one per call, and replays from a CUDA graph."""
+    from kubedl_b200.parallel.collectives import FLAG_CHANNELS, emulated_barrier
+    from kubedl_b200.ops import lib as L
+    run = emulated_barrier(W, cuda)
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    # epoch words: [rank][channel][block] with KDL_AR_MAX_BLOCKS blocks per channel (csrc/allreduce.cu epoch_slot)
+    fb = L.lib().kdl_allreduce_flags_bytes(FLAG_CHANNELS) // 4
+    max_blocks = fb // FLAG_CHANNELS // 8                # flags are [channel][KDL_MAX_WORLD = 8][block]
+    ep_all = run.state["epochs"]
+    ep = ep_all[: W * FLAG_CHANNELS * max_blocks].view(W, FLAG_CHANNELS, max_blocks)
+    assert ep[:, FLAG_CHANNELS - 1, 0].tolist() == [3] * W
+    assert int(ep_all.sum().item()) == 3 * W             # nothing else was touched
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        run()
+    for _ in range(4):
+        g.replay()
+    torch.cuda.synchronize()
+    assert ep[:, FLAG_CHANNELS - 1, 0].tolist() == [8] * W
+    assert int(run.state["status"][0].item()) == 0
+
+
 def test_bn_relu_maxpool_fused_matches_separate_passes(cuda):
     """BN apply + ReLU + 3x3/s2 max-pool in one pass (statistics from the producer's epilogue) == bn_fwd then
     maxpool; argmax indices may differ only on exact ties."""

@@ -87,8 +87,14 @@ __device__ __forceinline__ uint4 pool_grad_gather(const bf16* __restrict__ dp, c
   return pack8(acc);
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
+// RELU (backward only) is the compile-time copy of p.relu and POOL of (p.pool_dp != nullptr): each variant keeps
+// only the per-channel vectors and loads it needs.  The generic version held mean / rstd / forward scale /
+// forward shift for every thread (128 registers, 2 blocks per SM, 25 % occupancy) and spent 136 warp
+// instructions per 8-element vector: ncu showed DRAM at 53 % with the issue slots 53 % busy
+// (profiles/r2_bn_backward.md).  The second sum is accumulated as sum(dz * x) and centred once, in the
+// finaliser: sum(dz * xhat) = rstd * (sum(dz * x) - mean * sum(dz)).
+template <int MODE, int RELU, bool POOL>
+__global__ void __launch_bounds__(256, MODE == 1 ? 3 : 4) bn_reduce_kernel(BnReduceParams p) {
   __shared__ float red[256 * 16];
   __shared__ int is_last;
   pdl_wait();      // programmatic dependent launch: nothing global is touched before the predecessor has finished
@@ -105,16 +111,15 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
 
-  float mean[8], rstd[8], fwa[8], fwb[8];
-  if (MODE == 1) {
+  float fwa[8], fwb[8];
+  if (MODE == 1 && RELU == 2) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      mean[j] = p.mean_rstd[ch0 + j];
-      rstd[j] = p.mean_rstd[p.C + ch0 + j];
       // the forward pass computed y = relu(fma(a, x, b)), a = gamma*rstd, b = beta - mean*a: the same
       // expression gives the ReLU mask back without reading y (layers without a residual input)
-      fwa[j] = (p.gamma ? p.gamma[ch0 + j] : 1.f) * rstd[j];
-      fwb[j] = (p.beta ? p.beta[ch0 + j] : 0.f) - mean[j] * fwa[j];
+      const float mu = p.mean_rstd[ch0 + j], rs = p.mean_rstd[p.C + ch0 + j];
+      fwa[j] = (p.gamma ? p.gamma[ch0 + j] : 1.f) * rs;
+      fwb[j] = (p.beta ? p.beta[ch0 + j] : 0.f) - mu * fwa[j];
     }
   }
 
@@ -126,12 +131,12 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
       int64_t r = row + u * step;
       if (r < p.M) {
         int64_t off = r * p.C + ch0;
-        if (MODE == 1 && p.pool_dp) va[u] = pool_grad_gather(p.pool_dp, p.pool_idx, r, ch0, p.pool_H, p.pool_W, p.C);
+        if (MODE == 1 && POOL) va[u] = pool_grad_gather(p.pool_dp, p.pool_idx, r, ch0, p.pool_H, p.pool_W, p.C);
         else va[u] = ld_stream(p.a + off);
         if (MODE == 1) {
           vc[u] = ld_stream(p.c + off);
-          if (p.relu == 1) vb[u] = ld_stream(p.b + off);
-          else if (p.relu == 3) vb[u].x = p.mask[off >> 3];
+          if (RELU == 1) vb[u] = ld_stream(p.b + off);
+          else if (RELU == 3) vb[u].x = p.mask[off >> 3];
         }
       }
     }
@@ -150,22 +155,22 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
         } else {
           float fx[8];
           unpack8(vc[u], fx);
-          if (p.relu == 1) {
+          if (RELU == 1) {
             float fy[8];
             unpack8(vb[u], fy);
 #pragma unroll
             for (int j = 0; j < 8; ++j) fa[j] = fy[j] > 0.f ? fa[j] : 0.f;
-          } else if (p.relu == 2) {
+          } else if (RELU == 2) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) fa[j] = fmaf(fwa[j], fx[j], fwb[j]) > 0.f ? fa[j] : 0.f;
-          } else if (p.relu == 3) {
+          } else if (RELU == 3) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) fa[j] = ((vb[u].x >> j) & 1u) ? fa[j] : 0.f;
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             s0[j] += fa[j];
-            s1[j] = fmaf(fa[j], (fx[j] - mean[j]) * rstd[j], s1[j]);
+            s1[j] = fmaf(fa[j], fx[j], s1[j]);
           }
         }
       }
@@ -276,9 +281,10 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(BnReduceParams p) {
       float mu = p.mean_rstd[c], rs = p.mean_rstd[p.C + c];
       float g = p.gamma ? p.gamma[c] : 1.f;
       float a = g * rs;
-      float c1 = S0 * invM, c2 = S1 * invM;
+      const float S1c = rs * (S1 - mu * S0);      // sum(dz * xhat) from sum(dz * x) and sum(dz)
+      float c1 = S0 * invM, c2 = S1c * invM;
       if (p.dbeta) p.dbeta[c] = __float2bfloat16(S0);
-      if (p.dgamma) p.dgamma[c] = __float2bfloat16(S1);
+      if (p.dgamma) p.dgamma[c] = __float2bfloat16(S1c);
       // dx = a*(dz - c1 - xhat*c2) = A*dz + B*x + D
       p.coef[c] = a;
       p.coef[p.C + c] = -a * c2 * rs;
@@ -359,17 +365,18 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
   }
 }
 
-// dx = A*dz + B*x + D with dz = dy * (y > 0); optionally dres = dz.
-template <bool FIXED_CG>
-__global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
-                                                    const bf16* __restrict__ x,
-                                                    const bf16* __restrict__ y, bf16* dx, bf16* dres,
-                                                    int64_t nvec, int cvec, int C,
-                                                    const float* __restrict__ coef, int relu,
-                                                    const uint8_t* __restrict__ mask = nullptr,
-                                                    const bf16* __restrict__ pool_dp = nullptr,
-                                                    const uint8_t* __restrict__ pool_idx = nullptr,
-                                                    int pool_H = 0, int pool_W = 0) {
+// dx = A*dz + B*x + D with dz = dy * relu'(y); optionally dres = dz.  RELU / POOL: compile-time copies of the
+// mask mode and of (pool_dp != nullptr), as in bn_reduce_kernel.
+template <bool FIXED_CG, int RELU, bool POOL>
+__global__ void __launch_bounds__(256, 3) bn_dx_kernel(const bf16* dy,
+                                                       const bf16* __restrict__ x,
+                                                       const bf16* __restrict__ y, bf16* dx, bf16* dres,
+                                                       int64_t nvec, int cvec, int C,
+                                                       const float* __restrict__ coef,
+                                                       const uint8_t* __restrict__ mask,
+                                                       const bf16* __restrict__ pool_dp,
+                                                       const uint8_t* __restrict__ pool_idx,
+                                                       int pool_H, int pool_W) {
   pdl_wait();
   pdl_launch();
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
@@ -382,7 +389,7 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
       A[j] = coef[cg * 8 + j];
       B[j] = coef[C + cg * 8 + j];
       D[j] = coef[2 * C + cg * 8 + j];
-      Fb[j] = coef[3 * C + cg * 8 + j];
+      if (RELU == 2) Fb[j] = coef[3 * C + cg * 8 + j];
     }
   }
   constexpr int U = 2;
@@ -392,11 +399,11 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
     for (int u = 0; u < U; ++u) {
       int64_t k = i + u * T;
       if (k < nvec) {
-        if (pool_dp) vd[u] = pool_grad_gather(pool_dp, pool_idx, k / cvec, (int)(k % cvec) * 8, pool_H, pool_W, C);
+        if (POOL) vd[u] = pool_grad_gather(pool_dp, pool_idx, k / cvec, (int)(k % cvec) * 8, pool_H, pool_W, C);
         else vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
         vx[u] = ld_stream(x + k * 8);
-        if (relu == 1) vy[u] = ld_stream(y + k * 8);
-        else if (relu == 3) vy[u].x = mask[k];
+        if (RELU == 1) vy[u] = ld_stream(y + k * 8);
+        else if (RELU == 3) vy[u].x = mask[k];
       }
     }
 #pragma unroll
@@ -410,21 +417,21 @@ __global__ void __launch_bounds__(256) bn_dx_kernel(const bf16* dy,
             A[j] = coef[cg * 8 + j];
             B[j] = coef[C + cg * 8 + j];
             D[j] = coef[2 * C + cg * 8 + j];
-            Fb[j] = coef[3 * C + cg * 8 + j];
+            if (RELU == 2) Fb[j] = coef[3 * C + cg * 8 + j];
           }
         }
         float fd[8], fx[8];
         unpack8(vd[u], fd);
         unpack8(vx[u], fx);
-        if (relu == 1) {
+        if (RELU == 1) {
           float fy[8];
           unpack8(vy[u], fy);
 #pragma unroll
           for (int j = 0; j < 8; ++j) fd[j] = fy[j] > 0.f ? fd[j] : 0.f;
-        } else if (relu == 2) {      // A = gamma*rstd is also the forward scale
+        } else if (RELU == 2) {      // A = gamma*rstd is also the forward scale
 #pragma unroll
           for (int j = 0; j < 8; ++j) fd[j] = fmaf(A[j], fx[j], Fb[j]) > 0.f ? fd[j] : 0.f;
-        } else if (relu == 3) {
+        } else if (RELU == 3) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) fd[j] = ((vy[u].x >> j) & 1u) ? fd[j] : 0.f;
         }
@@ -525,7 +532,7 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int64_t M, int C
   p.running_mean = running_mean; p.running_var = running_var;
   p.eps = eps; p.momentum = momentum;
   p.mean_rstd = save_mean_rstd; p.coef = coef;
-  KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<0>, dim3(pl.gx, pl.nslices), dim3(pl.threads), 0, stream, p));
+  KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<0, 0, false>, dim3(pl.gx, pl.nslices), dim3(pl.threads), 0, stream, p));
   int64_t nvec = M * C / 8;
   int cvec = C / 8;
   int g = apply_grid(nvec);
@@ -560,6 +567,22 @@ extern "C" int kdl_bn_fwd_mask(const void* x, const void* res, void* y, int64_t 
                      (uint8_t*)relu_mask, workspace, workspace_bytes, stream);
 }
 
+template <bool FIXED_CG>
+static cudaError_t launch_bn_dx(int relu, bool pool, dim3 g, cudaStream_t stream, const bf16* dy, const bf16* x,
+                                const bf16* y, bf16* dx, bf16* dres, int64_t nvec, int cvec, int C, const float* coef,
+                                const uint8_t* mask, const bf16* pool_dp, const uint8_t* pool_idx, int pool_H,
+                                int pool_W) {
+#define KDL_BN_DX(R, P)                                                                                              \
+  return kdl_launch_pdl(bn_dx_kernel<FIXED_CG, R, P>, g, dim3(256), 0, stream, dy, x, y, dx, dres, nvec, cvec, C, coef, \
+                        mask, pool_dp, pool_idx, pool_H, pool_W)
+  if (pool) { KDL_BN_DX(2, true); }
+  if (relu == 0) { KDL_BN_DX(0, false); }
+  if (relu == 1) { KDL_BN_DX(1, false); }
+  if (relu == 2) { KDL_BN_DX(2, false); }
+  KDL_BN_DX(3, false);
+#undef KDL_BN_DX
+}
+
 static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, void* dres,
                        int64_t M, int C, const float* gamma, const float* beta, const float* save_mean_rstd,
                        int relu, const uint8_t* relu_mask, void* dgamma_bf16, void* dbeta_bf16, void* workspace,
@@ -591,7 +614,19 @@ static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, v
   p.dgamma = (bf16*)dgamma_bf16; p.dbeta = (bf16*)dbeta_bf16;
   p.relu = relu; p.mask = relu_mask;
   p.pool_dp = pool_dp; p.pool_idx = pool_idx; p.pool_H = pool_H; p.pool_W = pool_W;
-  KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1>, dim3(pl.gx, pl.nslices), dim3(pl.threads), 0, stream, p));
+  {
+    const dim3 rg(pl.gx, pl.nslices), rb(pl.threads);
+    if (pool_dp != nullptr) {
+      if (relu != 2) {
+        kdl_set_error("bn_bwd: the pooled variant recomputes the ReLU mask from x (relu mode 2), got %d", relu);
+        return KDL_ERR_ARG;
+      }
+      KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1, 2, true>, rg, rb, 0, stream, p));
+    } else if (relu == 0) KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1, 0, false>, rg, rb, 0, stream, p));
+    else if (relu == 1) KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1, 1, false>, rg, rb, 0, stream, p));
+    else if (relu == 2) KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1, 2, false>, rg, rb, 0, stream, p));
+    else KDL_CUDA(kdl_launch_pdl(bn_reduce_kernel<1, 3, false>, rg, rb, 0, stream, p));
+  }
   int64_t nvec = M * C / 8;
   int cvec = C / 8;
   int64_t g64 = (nvec + 256 * 2 - 1) / (256 * 2);
@@ -599,13 +634,13 @@ static int bn_bwd_impl(const void* dy, const void* x, const void* y, void* dx, v
   int g = (int)(g64 < 1 ? 1 : g64);
   bool fixed = (256 % cvec) == 0;
   if (fixed)
-    KDL_CUDA(kdl_launch_pdl(bn_dx_kernel<true>, dim3(g), dim3(256), 0, stream, (const bf16*)dy, (const bf16*)x,
-                            (const bf16*)y, (bf16*)dx, (bf16*)dres, nvec, cvec, C, (const float*)coef, relu, relu_mask,
-                            pool_dp, pool_idx, pool_H, pool_W));
+    KDL_CUDA(launch_bn_dx<true>(relu, pool_dp != nullptr, dim3(g), stream, (const bf16*)dy, (const bf16*)x, (const bf16*)y,
+                                (bf16*)dx, (bf16*)dres, nvec, cvec, C, (const float*)coef, relu_mask, pool_dp, pool_idx,
+                                pool_H, pool_W));
   else
-    KDL_CUDA(kdl_launch_pdl(bn_dx_kernel<false>, dim3(g), dim3(256), 0, stream, (const bf16*)dy, (const bf16*)x,
-                            (const bf16*)y, (bf16*)dx, (bf16*)dres, nvec, cvec, C, (const float*)coef, relu, relu_mask,
-                            pool_dp, pool_idx, pool_H, pool_W));
+    KDL_CUDA(launch_bn_dx<false>(relu, pool_dp != nullptr, dim3(g), stream, (const bf16*)dy, (const bf16*)x, (const bf16*)y,
+                                 (bf16*)dx, (bf16*)dres, nvec, cvec, C, (const float*)coef, relu_mask, pool_dp, pool_idx,
+                                 pool_H, pool_W));
   return KDL_OK;
 }
 

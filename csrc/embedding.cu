@@ -20,7 +20,9 @@
 // provides TASK_NAME / TASK_INDEX / ZK_ADDR for XDL's own PS exchange (reference
 // controllers/xdl/xdljob_controller.go:191-217).
 #include "common.cuh"
+#include "tcgen05.cuh"
 #include "../include/kubedl_b200.h"
+#include <stdlib.h>
 
 namespace kdl {
 
@@ -31,6 +33,8 @@ struct EmbParams {
   float* shard[KDL_MAX_WORLD];    // peer-mapped shard base pointers
   int world;
   int64_t rows_per_rank;
+  int interleaved;                // 1: row id lives on rank id % world at local row id / world; 0: row ranges
+  int wshift;                     // log2(world) when world is a power of two, else -1
   const int64_t* user;            // [B]
   const int64_t* cand;            // [B]
   const int64_t* hist;            // [B, L], -1 = padding
@@ -42,7 +46,19 @@ struct EmbParams {
   float lr;
 };
 
+// Placement of row `id`.  Interleaved (default): consecutive ids go to consecutive ranks, so a skewed id
+// distribution (hot low ids, the usual case for CTR vocabularies sorted by frequency) spreads evenly over the
+// owners and every NVLink port carries the same load; NVSwitch gives the same bandwidth to every peer, so
+// nothing is gained by keeping neighbours together.  With row RANGES half of the Zipf-skewed lookups of the
+// benchmark hit rank 0 and its egress port alone set the kernel time (profiles/r2_din_sharding.md).
 __device__ __forceinline__ const float* row_ptr(const EmbParams& p, int64_t id) {
+  if (p.interleaved) {
+    const uint32_t i = (uint32_t)id;          // host checked: vocab < 2^32
+    uint32_t owner, local;
+    if (p.wshift >= 0) { owner = i & (uint32_t)(p.world - 1); local = i >> p.wshift; }
+    else { local = i / (uint32_t)p.world; owner = i - local * (uint32_t)p.world; }
+    return p.shard[owner] + (size_t)local * kD;
+  }
   const int owner = (int)(id / p.rows_per_rank);
   return p.shard[owner] + (id - (int64_t)owner * p.rows_per_rank) * kD;
 }
@@ -158,6 +174,93 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) din_gather_attend_kernel(
   *reinterpret_cast<__nv_bfloat162*>(x + 3 * kD + 2 * lane) = __floats2bfloat162_rn(pl.x * c.x, pl.y * c.y);
 }
 
+// ---- N4, second version: the rows come in by TMA bulk copies ----------------------------------------------
+// The register version above keeps 8 rows in flight per warp (more costs occupancy) and spends an LSU request
+// per row per warp.  Here every lane ISSUES the rows it is responsible for as 256-byte cp.async.bulk copies
+// (global -> shared, straight from the owner's shard over NVLink when the row is remote) onto one mbarrier per
+// warp: all of a sample's rows (up to 2 + L) are in flight at once, no registers hold them, and the attention
+// pooling then reads them from shared memory.  Plain bulk copies, no multicast.
+constexpr int kTmaWarps = 6;                       // per block: 6 x 16.9 KB of row buffers, 2 blocks per SM
+constexpr int kTmaMaxRows = 66;                    // user + candidate + up to 64 history rows
+
+__global__ void __launch_bounds__(kTmaWarps * 32) din_gather_attend_tma_kernel(EmbParams p) {
+  extern __shared__ __align__(128) uint8_t dsm[];
+  const int lane = threadIdx.x & 31;
+  const int w = threadIdx.x >> 5;
+  float* rows = reinterpret_cast<float*>(dsm) + (size_t)w * kTmaMaxRows * kD;     // [row][64] fp32
+  const uint32_t rows_u32 = smem_u32(rows);
+  const uint32_t bar = smem_u32(dsm + (size_t)kTmaWarps * kTmaMaxRows * kD * 4) + 8u * w;
+  if (lane == 0) mbar_init(bar, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncwarp();
+  const float inv_sqrt_d = rsqrtf((float)kD);
+  uint32_t phase = 0;
+  for (int s = blockIdx.x * kTmaWarps + w; s < p.B; s += gridDim.x * kTmaWarps) {
+    const int64_t* hid = p.hist + (size_t)s * p.L;
+    // slot 0 = user, 1 = candidate, 2 + i = history item i; lane l issues slots l, l + 32, l + 64
+    int64_t id[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int slot = lane + 32 * k;
+      id[k] = slot == 0 ? p.user[s] : slot == 1 ? p.cand[s] : (slot - 2 < p.L ? hid[slot - 2] : -1);
+    }
+    // which slots hold a real row (warp-uniform bit masks)
+    const uint32_t vm0 = __ballot_sync(0xffffffffu, id[0] >= 0), vm1 = __ballot_sync(0xffffffffu, id[1] >= 0),
+                   vm2 = __ballot_sync(0xffffffffu, id[2] >= 0);
+    const int nvalid = __popc(vm0) + __popc(vm1) + __popc(vm2);
+    if (lane == 0) mbar_expect_tx(bar, (uint32_t)nvalid * kD * 4);       // arrive + expected bytes
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int slot = lane + 32 * k;
+      if (id[k] >= 0)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(rows_u32 + (uint32_t)slot * kD * 4), "l"(row_ptr(p, id[k])), "r"(kD * 4), "r"(bar)
+                     : "memory");
+    }
+    mbar_wait(bar, phase);
+    phase ^= 1u;
+
+    const float2 u = *reinterpret_cast<const float2*>(rows + 2 * lane);
+    const float2 c = *reinterpret_cast<const float2*>(rows + kD + 2 * lane);
+    bf16* hs = p.hsave + (size_t)s * p.L * kD;
+    float* as = p.asave + (size_t)s * p.L;
+    float m = -1e30f, denom = 0.f;
+    float2 acc = make_float2(0.f, 0.f);
+    for (int i = 0; i < p.L; ++i) {
+      const int slot = i + 2;
+      const bool valid = (((slot < 32 ? vm0 : slot < 64 ? vm1 : vm2) >> (slot & 31)) & 1u) != 0;
+      const float2 h = valid ? *reinterpret_cast<const float2*>(rows + (size_t)slot * kD + 2 * lane) : make_float2(0.f, 0.f);
+      *reinterpret_cast<__nv_bfloat162*>(hs + (size_t)i * kD + 2 * lane) = __floats2bfloat162_rn(h.x, h.y);
+      if (!valid) {                 // padding: weight 0
+        if (lane == 0) as[i] = -1e30f;
+        continue;
+      }
+      const float sc = warp_sum(h.x * c.x + h.y * c.y) * inv_sqrt_d;
+      if (lane == 0) as[i] = sc;
+      const float mn = fmaxf(m, sc);
+      const float corr = __expf(m - mn), e = __expf(sc - mn);
+      denom = denom * corr + e;
+      acc.x = acc.x * corr + e * h.x;
+      acc.y = acc.y * corr + e * h.y;
+      m = mn;
+    }
+    const float inv = denom > 0.f ? 1.f / denom : 0.f;
+    const float2 pl = make_float2(acc.x * inv, acc.y * inv);
+    __syncwarp();
+    for (int i = lane; i < p.L; i += 32) {
+      const float sc = as[i];
+      as[i] = sc > -1e29f ? __expf(sc - m) * inv : 0.f;
+    }
+    bf16* x = p.x + (size_t)s * 4 * kD;
+    *reinterpret_cast<__nv_bfloat162*>(x + 2 * lane) = __floats2bfloat162_rn(u.x, u.y);
+    *reinterpret_cast<__nv_bfloat162*>(x + kD + 2 * lane) = __floats2bfloat162_rn(c.x, c.y);
+    *reinterpret_cast<__nv_bfloat162*>(x + 2 * kD + 2 * lane) = __floats2bfloat162_rn(pl.x, pl.y);
+    *reinterpret_cast<__nv_bfloat162*>(x + 3 * kD + 2 * lane) = __floats2bfloat162_rn(pl.x * c.x, pl.y * c.y);
+    __syncwarp();      // every lane is done with the row buffers before the next sample's copies land in them
+  }
+}
+
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) din_scatter_update_kernel(EmbParams p) {
   const int lane = threadIdx.x & 31;
   const int hl = lane & 15, half = lane >> 4;
@@ -216,8 +319,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) din_scatter_update_kernel
 
 using namespace kdl;
 
-static int fill(EmbParams* p, void* const* shard_ptrs, int world, int64_t rows_per_rank, const int64_t* user,
-                const int64_t* cand, const int64_t* hist, int B, int L, int D) {
+static int fill(EmbParams* p, void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved,
+                const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L, int D) {
   if (D != kD) {
     kdl_set_error("embedding kernels are specialised for D=%d (got %d)", kD, D);
     return KDL_ERR_UNSUPPORTED;
@@ -226,32 +329,57 @@ static int fill(EmbParams* p, void* const* shard_ptrs, int world, int64_t rows_p
     kdl_set_error("embedding: bad arguments world=%d B=%d L=%d rows_per_rank=%lld", world, B, L, (long long)rows_per_rank);
     return KDL_ERR_ARG;
   }
+  if (interleaved && rows_per_rank * world > (int64_t)1 << 32) {
+    kdl_set_error("embedding: interleaved placement supports vocabularies below 2^32 rows");
+    return KDL_ERR_UNSUPPORTED;
+  }
   for (int r = 0; r < world; ++r) p->shard[r] = (float*)shard_ptrs[r];
   p->world = world; p->rows_per_rank = rows_per_rank;
+  p->interleaved = interleaved ? 1 : 0;
+  p->wshift = -1;
+  for (int b = 0; b < 8; ++b)
+    if ((1 << b) == world) p->wshift = b;
   p->user = user; p->cand = cand; p->hist = hist; p->B = B; p->L = L;
   return KDL_OK;
 }
 
-extern "C" int kdl_din_gather_attend(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+extern "C" int kdl_din_gather_attend(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved,
                                      const int64_t* user, const int64_t* cand, const int64_t* hist, int B,
                                      int L, int D, void* x_bf16, void* hsave_bf16, float* asave,
                                      cudaStream_t stream) {
   EmbParams p = {};
-  int rc = fill(&p, shard_ptrs, world, rows_per_rank, user, cand, hist, B, L, D);
+  int rc = fill(&p, shard_ptrs, world, rows_per_rank, interleaved, user, cand, hist, B, L, D);
   if (rc) return rc;
   p.x = (bf16*)x_bf16; p.hsave = (bf16*)hsave_bf16; p.asave = asave;
-  din_gather_attend_kernel<<<(B + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(p);
+  static int use_tma = -1;      // KDL_DIN_GATHER=ldg keeps the register version (A/B runs)
+  if (use_tma < 0) {
+    const char* e = getenv("KDL_DIN_GATHER");
+    use_tma = (e && e[0] == 'l') ? 0 : 1;
+  }
+  if (use_tma && L + 2 <= kTmaMaxRows) {
+    const size_t smem = (size_t)kTmaWarps * kTmaMaxRows * kD * 4 + kTmaWarps * 8;
+    static bool attr_done = false;
+    if (!attr_done) {
+      KDL_CUDA(cudaFuncSetAttribute(din_gather_attend_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_done = true;
+    }
+    int grid = (B + kTmaWarps - 1) / kTmaWarps;
+    if (grid > 2 * 148) grid = 2 * 148;           // persistent: two blocks per SM, warps stride over the samples
+    din_gather_attend_tma_kernel<<<grid, kTmaWarps * 32, smem, stream>>>(p);
+  } else {
+    din_gather_attend_kernel<<<(B + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(p);
+  }
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }
 
-extern "C" int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+extern "C" int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved,
                                       const int64_t* user, const int64_t* cand, const int64_t* hist, int B,
                                       int L, int D, const void* x_bf16, const void* dx_bf16,
                                       const void* hsave_bf16, const float* asave, float lr,
                                       cudaStream_t stream) {
   EmbParams p = {};
-  int rc = fill(&p, shard_ptrs, world, rows_per_rank, user, cand, hist, B, L, D);
+  int rc = fill(&p, shard_ptrs, world, rows_per_rank, interleaved, user, cand, hist, B, L, D);
   if (rc) return rc;
   p.x = (bf16*)x_bf16; p.dx = (const bf16*)dx_bf16; p.hsave = (bf16*)hsave_bf16; p.asave = const_cast<float*>(asave); p.lr = lr;
   din_scatter_update_kernel<<<(B + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(p);

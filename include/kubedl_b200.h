@@ -245,11 +245,13 @@ int kdl_gbdt_update_pred(float* pred, const int32_t* node_of_row, const float* l
 /* ---- N4/N5: sharded embedding gather (+DIN attention pooling) and scatter-add SGD update ----
  * over NVLink peer memory; replaces all_to_all_single + embedding_bag / index_add_ of a stock
  * PyTorch worker (XDL's PS exchange; reference controllers/xdl/xdljob_controller.go:191-217).
- * shard_ptrs: HOST array of `world` device pointers to the fp32 row shards [rows_per_rank, 64]. */
-int kdl_din_gather_attend(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+ * shard_ptrs: HOST array of `world` device pointers to the fp32 row shards [rows_per_rank, 64].
+ * interleaved = 1: row id lives on rank id % world at local row id / world (skewed ids load every NVLink
+ * port alike); 0: rank r owns ids [r * rows_per_rank, (r + 1) * rows_per_rank). */
+int kdl_din_gather_attend(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved,
                           const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L,
                           int D, void* x_bf16, void* hsave_bf16, float* asave, cudaStream_t stream);
-int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_rank,
+int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved,
                            const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L,
                            int D, const void* x_bf16, const void* dx_bf16, const void* hsave_bf16,
                            const float* asave, float lr, cudaStream_t stream);

@@ -3,7 +3,10 @@
 dispatch/combine over NVSwitch at 8 GPUs").
 
 Per sample: user id, candidate item id and L history item ids index ONE table E[V, 64] (fp32
-rows, sharded by row range over the ranks, each shard in the symmetric heap).  Forward =
+rows, each shard in the symmetric heap).  Rows are INTERLEAVED over the ranks (row id on rank
+id % world): NVSwitch gives every peer the same bandwidth, so the only thing placement can get wrong
+is load — with row ranges a frequency-sorted (Zipf) vocabulary sends half of all lookups to rank 0
+(`sharding="range"` / KUBEDL_DIN_SHARDING=range keeps that layout for A/B runs).  Forward =
 `kdl_din_gather_attend` (remote pull + attention pooling + concat, kernel N4) -> MLP 256-512-256-1
 on the tcgen05 GEMM -> sigmoid BCE.  Backward = MLP backward on the GEMM (nn / tn variants) ->
 device barrier -> `kdl_din_scatter_update` (pooling backward + remote red.add sparse-SGD, kernel N5)
@@ -33,9 +36,9 @@ from ..ops.gemm import Gemm
 from .arena import ParamArena
 
 L.register_signatures({
-    "kdl_din_gather_attend": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+    "kdl_din_gather_attend": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "kdl_din_scatter_update": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+    "kdl_din_scatter_update": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_float, C.c_void_p]),
 })
@@ -45,8 +48,14 @@ D = 64
 
 class DINModel:
     def __init__(self, vocab: int = 10_000_000, hist_len: int = 62, hidden=(512, 256), lr: float = 0.05,
-                 emb_lr: Optional[float] = None, heap=None, group=None, seed: int = 0, device=None):
+                 emb_lr: Optional[float] = None, heap=None, group=None, seed: int = 0, device=None,
+                 sharding: Optional[str] = None):
+        import os as _os
         import torch.distributed as dist
+        sharding = sharding or _os.environ.get("KUBEDL_DIN_SHARDING", "interleaved")
+        assert sharding in ("interleaved", "range"), sharding
+        self.sharding = sharding
+        self.interleaved = 1 if sharding == "interleaved" else 0
         self.lib = L.lib()
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -90,7 +99,7 @@ class DINModel:
         x = torch.empty(B, 4 * D, dtype=torch.bfloat16, device=self.dev)
         hs = torch.empty(B, self.L, D, dtype=torch.bfloat16, device=self.dev)
         aw = torch.empty(B, self.L, dtype=torch.float32, device=self.dev)
-        L.check(self.lib.kdl_din_gather_attend(self._shard_tab, self.world, self.rows_per_rank, user.data_ptr(),
+        L.check(self.lib.kdl_din_gather_attend(self._shard_tab, self.world, self.rows_per_rank, self.interleaved, user.data_ptr(),
                                                cand.data_ptr(), hist.data_ptr(), B, self.L, D, x.data_ptr(),
                                                hs.data_ptr(), aw.data_ptr(), L.stream_ptr()), "kdl_din_gather_attend")
         L.count(1)
@@ -122,7 +131,7 @@ class DINModel:
         if self.gather_done is not None:
             # nobody updates a shard while a slower peer may still be gathering this step's rows from it
             self.gather_done()
-        L.check(self.lib.kdl_din_scatter_update(self._shard_tab, self.world, self.rows_per_rank, user.data_ptr(),
+        L.check(self.lib.kdl_din_scatter_update(self._shard_tab, self.world, self.rows_per_rank, self.interleaved, user.data_ptr(),
                                                 cand.data_ptr(), hist.data_ptr(), B, self.L, D, x.data_ptr(),
                                                 dx.data_ptr(), hs.data_ptr(), aw.data_ptr(), self.emb_lr,
                                                 L.stream_ptr()), "kdl_din_scatter_update")
@@ -172,13 +181,34 @@ class DINModel:
         K.sgd_momentum(a.p32, a.mom, a.g16, a.p16, self.lr, 0.0, 0.0, wd_count=a.wd_count)
         return loss
 
+    # ------------------------------------------------------------------ placement
+    def owner_of(self, ids: torch.Tensor) -> torch.Tensor:
+        """Rank that holds each row id."""
+        if self.interleaved:
+            return ids % self.world
+        return torch.div(ids, self.rows_per_rank, rounding_mode="floor")
+
+    def local_of(self, ids: torch.Tensor) -> torch.Tensor:
+        """Row index inside the owner's shard."""
+        if self.interleaved:
+            return torch.div(ids, self.world, rounding_mode="floor")
+        return ids - self.owner_of(ids) * self.rows_per_rank
+
+    def full_table(self, shards) -> torch.Tensor:
+        """The [world * rows_per_rank, D] table in id order from the list of per-rank shards."""
+        if self.interleaved:
+            return torch.stack(list(shards), dim=1).reshape(-1, shards[0].shape[-1])
+        return torch.cat(list(shards), 0)
+
     # ------------------------------------------------------------------ checkpoint (per-rank shard)
     def state_dict(self) -> dict:
         return {"shard": self.shard.detach().cpu(), "arena": self.arena.state_dict(), "rank": self.rank,
-                "rows_per_rank": self.rows_per_rank}
+                "rows_per_rank": self.rows_per_rank, "sharding": self.sharding, "world": self.world}
 
     def load_state_dict(self, sd: dict) -> None:
         assert sd["rank"] == self.rank and sd["rows_per_rank"] == self.rows_per_rank
+        assert sd.get("sharding", "range") == self.sharding and sd.get("world", self.world) == self.world, \
+            "the checkpoint was written with another row placement"
         self.shard.copy_(sd["shard"])
         self.arena.load_state_dict(sd["arena"])
 

@@ -41,7 +41,7 @@ def ours_exchange():
     # backward exchange with a synthetic upstream gradient
     user, cand, hist, xs, hs, aw, h1, h2 = m.saved; m.saved = None
     from kubedl_b200.ops import lib as L
-    L.check(m.lib.kdl_din_scatter_update(m._shard_tab, m.world, m.rows_per_rank, user.data_ptr(), cand.data_ptr(),
+    L.check(m.lib.kdl_din_scatter_update(m._shard_tab, m.world, m.rows_per_rank, m.interleaved, user.data_ptr(), cand.data_ptr(),
                                          hist.data_ptr(), B, L_, D, xs.data_ptr(), x.data_ptr(), hs.data_ptr(),
                                          aw.data_ptr(), 0.0, L.stream_ptr()))
     if m.ar is not None: m.ar(m.arena.g16_off, 8, torch.bfloat16, channel=6)
@@ -56,7 +56,7 @@ mlp = torch.nn.Sequential(mlp[0], torch.nn.ReLU(), mlp[1], torch.nn.ReLU(), mlp[
 opt = torch.optim.SGD(mlp.parameters(), lr=0.05)
 
 def exchange_ids(ids):
-    owner = torch.div(ids, rows_per_rank, rounding_mode="floor")
+    owner = m.owner_of(ids)              # same row placement as the fused path
     order = torch.argsort(owner, stable=True)
     sorted_ids = ids[order]
     send_counts = torch.bincount(owner, minlength=world)
@@ -74,7 +74,7 @@ def stock():
     mask = hist >= 0
     ids = torch.cat([user, cand, hist[mask]])
     order, sc, rc, recv_ids = exchange_ids(ids)
-    local = recv_ids - rank * rows_per_rank
+    local = m.local_of(recv_ids)
     rows = table.index_select(0, local)                                   # owner-side gather
     back = torch.empty(ids.numel(), D, dtype=rows.dtype, device=dev)
     if world > 1: dist.all_to_all_single(back, rows, sc, rc)

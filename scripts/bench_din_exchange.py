@@ -37,18 +37,47 @@ def gather_only():
     x = torch.empty(B, 4 * D, dtype=torch.bfloat16, device=dev)
     hs = torch.empty(B, L_, D, dtype=torch.bfloat16, device=dev)
     aw = torch.empty(B, L_, dtype=torch.float32, device=dev)
-    L.check(m.lib.kdl_din_gather_attend(m._shard_tab, m.world, m.rows_per_rank, u.data_ptr(), c.data_ptr(), h.data_ptr(),
+    L.check(m.lib.kdl_din_gather_attend(m._shard_tab, m.world, m.rows_per_rank, m.interleaved, u.data_ptr(), c.data_ptr(), h.data_ptr(),
                                         B, L_, D, x.data_ptr(), hs.data_ptr(), aw.data_ptr(), L.stream_ptr()))
     m._last = (u, c, h, x, hs, aw)
 def scatter_only():
     u, c, h, x, hs, aw = m._last
-    L.check(m.lib.kdl_din_scatter_update(m._shard_tab, m.world, m.rows_per_rank, u.data_ptr(), c.data_ptr(), h.data_ptr(),
+    L.check(m.lib.kdl_din_scatter_update(m._shard_tab, m.world, m.rows_per_rank, m.interleaved, u.data_ptr(), c.data_ptr(), h.data_ptr(),
                                          B, L_, D, x.data_ptr(), dx.data_ptr(), hs.data_ptr(), aw.data_ptr(), 0.0,
                                          L.stream_ptr()))
 res = {"world": world, "gather_ms": timed(gather_only)}
 gather_only()
 res["scatter_ms"] = timed(scatter_only)
-res["remote_mb_per_kernel"] = B * (L_ + 2) * D * 4 * (world - 1) / world / 1e6
+# bytes that really cross NVLink per kernel: VALID rows (histories are variable-length, -1 = padding) whose owner
+# is another rank, 256 bytes each, averaged over the batches used; the link roofline is 770 GB/s per direction
+def remote_rows(b):
+    u, c, h, _ = b
+    ids = torch.cat([u, c, h.flatten()])
+    ids = ids[ids >= 0]
+    return int((m.owner_of(ids) != rank).sum()), int(ids.numel())
+rr = [remote_rows(b) for b in batches]
+remote_mb = sum(r for r, _ in rr) / len(rr) * D * 4 / 1e6
+t = torch.tensor([remote_mb], device=dev)
+if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
+res["rows_per_kernel"] = sum(n for _, n in rr) / len(rr)
+res["remote_mb_per_kernel"] = float(t.item())
+res["remote_mb_if_all_slots_were_valid"] = B * (L_ + 2) * D * 4 * (world - 1) / world / 1e6
+for k in ("gather", "scatter"):
+    gbs = res["remote_mb_per_kernel"] / res[k + "_ms"] if world > 1 else 0.0
+    res[k + "_remote_gb_s"] = gbs
+    res[k + "_frac_of_770"] = gbs / 770.0
+res["gather_impl"] = os.environ.get("KDL_DIN_GATHER", "tma")
+res["sharding"] = m.sharding
+# egress of the busiest OWNER: rows every other rank pulls from one shard
+own = torch.zeros(world, device=dev)
+for b in batches:
+    u, c, h, _ = b
+    ids = torch.cat([u, c, h.flatten()]); ids = ids[ids >= 0]
+    o = m.owner_of(ids)
+    own += torch.bincount(o[o != rank], minlength=world).float() / len(batches)
+if world > 1: dist.all_reduce(own)
+res["busiest_owner_egress_mb"] = float(own.max()) * D * 4 / 1e6
+res["gather_busiest_port_gb_s"] = res["busiest_owner_egress_mb"] / res["gather_ms"]
 if rank == 0:
     print(json.dumps(res), flush=True)
 if world > 1:

@@ -35,13 +35,13 @@ V, L_, B = 80_000, 20, 256
 m = DINModel(vocab=V, hist_len=L_, lr=0.1, emb_lr=0.5, seed=1)
 full0 = [torch.empty_like(m.shard) for _ in range(world)]
 dist.all_gather(full0, m.shard.contiguous())
-table0 = torch.cat(full0, 0)
+table0 = m.full_table(full0)
 user, cand, hist, label = synthetic_batch(B, L_, V, dev, seed=100 + rank)
 loss = m.step(user, cand, hist, label)
 torch.cuda.synchronize(); dist.barrier()
 full1 = [torch.empty_like(m.shard) for _ in range(world)]
 dist.all_gather(full1, m.shard.contiguous())
-table1 = torch.cat(full1, 0)
+table1 = m.full_table(full1)
 # oracle: gradient of the summed per-rank mean losses w.r.t. the full table
 sys.path.insert(0, "tests")
 from test_gpu_din import _ref_forward

@@ -11,7 +11,7 @@ from kubedl_b200.ops import build as B
 
 PAT = re.compile(r"\b(UTC[A-Z]*MMA(?:\.2CTA)?|LDTM(?:\.x\d+)?|STTM|UTMALDG(?:\.\dD)?(?:\.IM2COL)?|UTMASTG(?:\.\dD)?|UTMAPF(?:\.L2)?(?:\.\dD)?|"
                  r"UTMAREDG(?:\.\dD)?|UBLKCP(?:\.[A-Z]+)*|UBLKRED(?:\.[A-Z]+)*|UTCBAR(?:\.2CTA)?(?:\.MULTICAST)?|"
-                 r"MULTIMEM(?:\.[A-Z0-9_]+)*|REDG?(?:\.[A-Z0-9_]+)*|ATOMG(?:\.[A-Z0-9_]+)*|ATOMS(?:\.[A-Z0-9_]+)*|"
+                 r"MULTIMEM(?:\.[A-Z0-9_]+)*|LDGMC(?:\.[A-Z0-9_]+)*|STGMC(?:\.[A-Z0-9_]+)*|REDGMC(?:\.[A-Z0-9_]+)*|REDG?(?:\.[A-Z0-9_]+)*|ATOMG(?:\.[A-Z0-9_]+)*|ATOMS(?:\.[A-Z0-9_]+)*|"
                  r"SYNCS(?:\.[A-Z0-9_]+)*|HMMA(?:\.[A-Z0-9_]+)*)\b")
 
 
@@ -43,7 +43,7 @@ def main():
     print("# SASS census of libkubedl_b200.so (cuobjdump -sass): count, kernel, mnemonic.")
     print("# UTCHMMA = tcgen05.mma (.2CTA = cta_group::2), LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA tensor load/store (.IM2COL = im2col mode),")
     print("# UTMAPF = TMA prefetch to L2, UBLKCP = cp.async.bulk, UTCBAR = tcgen05.commit, SYNCS.*TRANS64 = mbarrier with transaction count,")
-    print("# MULTIMEM = NVLS multimem, RED/REDG/ATOMG = global reductions (peer memory in the exchange kernels), ATOMS = shared atomics.")
+    print("# LDGMC / STGMC = NVLS multimem.ld_reduce / multimem.st, RED/REDG/ATOMG = global reductions (peer memory in the exchange kernels), ATOMS = shared atomics.")
     print("# No HMMA (mma.sync / wmma) anywhere.")
     for k, c in counts.items():
         for op, n in sorted(c.items()):

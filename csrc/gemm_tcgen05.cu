@@ -61,7 +61,24 @@ struct GemmParams {
   int conv_s, conv_r;        // filter W, H
   int conv_c;                // channels of the patch operand (K per tap for mode 1, N per tap for mode 2)
   int conv_flip;             // dgrad: filter taps are visited mirrored
+  // parity class of a STRIDE-2 dgrad run as a stride-1 sub-convolution over dy (kdl_conv2d_dgrad_s2):
+  int sub_en;                // 1: the "split" index of a tile is its parity class c = 2 ph + pw (all four classes in one
+                             // persistent launch): 1 or 2 taps per axis, weight tap of sub-tap t = (sub_wtaps[c] >> 4t) & 15,
+                             // and row (n, a, b) is stored at input pixel (2a + ph, 2b + pw)
+  int sub_wtaps[4];          // per class: up to four original filter-tap indices, 4 bits each
 };
+
+// K-block range of a tile: a split-K slice, or (sub_en) all taps of the tile's parity class
+__device__ __forceinline__ void tile_kb_range(const GemmParams& p, int split, int kb_total, int& kb0, int& kb1) {
+  if (p.sub_en) {
+    const int taps = ((split >> 1) ? 2 : 1) * ((split & 1) ? 2 : 1);
+    kb0 = 0;
+    kb1 = taps * (p.conv_c / BK);
+  } else {
+    kb0 = split * p.kb_per_split;
+    kb1 = min(kb0 + p.kb_per_split, kb_total);
+  }
+}
 
 constexpr int kStatsMaxN = 2048;
 constexpr int kStatsBytes = 2 * kStatsMaxN * 4;
@@ -387,6 +404,19 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, const CUtenso
 #pragma unroll
           for (int j = 0; j < 64; ++j) f[j] = fmaxf(f[j], 0.f);
         }
+        if (p.sub_en) {
+          // parity class of a stride-2 dgrad: GEMM row (n, a, b) is input pixel (2a + ph, 2b + pw) — rows of a
+          // chunk are not a TMA box in dx, so every lane stores its own 128 bytes
+          if (row < p.M) {
+            const int pq = p.conv_p * p.conv_q;
+            const int ni = row / pq, rem = row - ni * pq, aa = rem / p.conv_q, bb = rem - aa * p.conv_q;
+            bf16* o = p.C + ((((size_t)ni * (2 * p.conv_p) + 2 * aa + (split >> 1)) * (2 * p.conv_q)) + 2 * bb + (split & 1)) * p.ldc + col;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (col + 8 * j + 8 <= p.N) *reinterpret_cast<uint4*>(o + 8 * j) = pack8(f + 8 * j);
+          }
+          continue;
+        }
         if (lane == 0) tma_store_wait_read<1>();  // the buffer written two chunks ago is free
         __syncwarp();
         uint8_t* dst = stg_ptr + buf * 4096 + lane * 128;
@@ -488,8 +518,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int n_idx = t % p.num_n;
         const int m_idx = (t / p.num_n) % p.num_m;
         const int split = t / (p.num_n * p.num_m);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        int kb0, kb1;
+        tile_kb_range(p, split, kb_total, kb0, kb1);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * SL::kStageBytes;
@@ -499,7 +529,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             // K runs over (tap, channel block): A = 128 output pixels x 64 channels of that tap
             const int cblks = p.conv_c / BK;
             const int tap = kb / cblks, cb = kb - tap * cblks;
-            int kh = tap / p.conv_s, kw = tap - kh * p.conv_s;
+            const int cs = p.sub_en ? ((split & 1) ? 2 : 1) : p.conv_s;     // taps along W of this tile's class
+            int kh = tap / cs, kw = tap - kh * cs;
             const int m0 = m_idx * BM;
             const int pq = p.conv_p * p.conv_q;
             const int n0 = m0 / pq, rem = m0 - n0 * pq, oh0 = rem / p.conv_q, ow0 = rem - oh0 * p.conv_q;
@@ -507,9 +538,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             tma_load_im2col(sa, &tma_a, full_bar(stage), cb * BK, ow0 * p.conv_stride - p.conv_pad,
                             oh0 * p.conv_stride - p.conv_pad, n0, fw, fh);
             if (B_MN) {   // dgrad: weights [Cout][taps*Cin] read as K(cout) x N(cin) tiles of tap (kh,kw)
+              const int wtap = p.sub_en ? ((p.sub_wtaps[split] >> (4 * tap)) & 15) : tap;
 #pragma unroll
               for (int a = 0; a < BN / 64; ++a)
-                tma_load_2d(sb + a * (BK * 128), &tma_b, full_bar(stage), tap * p.N + n_idx * BN + a * 64, cb * BK);
+                tma_load_2d(sb + a * (BK * 128), &tma_b, full_bar(stage), wtap * p.N + n_idx * BN + a * 64, cb * BK);
             } else {      // fprop: weights [Cout][taps*Cin] are already K-major in (tap, channel) order
               tma_load_2d(sb, &tma_b, full_bar(stage), kb * BK, n_idx * BN);
             }
@@ -559,8 +591,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       int iter = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
         const int split = t / (p.num_n * p.num_m);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        int kb0, kb1;
+        tile_kb_range(p, split, kb_total, kb0, kb1);
         const int as = iter & 1;
         const uint32_t aphase = (iter >> 1) & 1;
         mbar_wait(tempty_bar(as), aphase ^ 1);
@@ -701,8 +733,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int n_idx = t % p.num_n;
         const int m_idx = (t / p.num_n) % p.num_m;
         const int split = t / (p.num_n * p.num_m);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        int kb0, kb1;
+        tile_kb_range(p, split, kb_total, kb0, kb1);
         const int m0 = m_idx * 256 + (int)cta * BM;
         const int n0 = n_idx * BN2 + (int)cta * (BN2 / 2);
         const int pq = p.conv_p * p.conv_q;
@@ -714,15 +746,17 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
           if (p.conv_mode == 1) {
             const int cblks = p.conv_c / BK;
             const int tap = kb / cblks, cb = kb - tap * cblks;
-            const int kh = tap / p.conv_s, kw = tap - kh * p.conv_s;
+            const int cs = p.sub_en ? ((split & 1) ? 2 : 1) : p.conv_s;
+            const int kh = tap / cs, kw = tap - kh * cs;
             const int in0 = m0 / pq, rem = m0 - in0 * pq, oh0 = rem / p.conv_q, ow0 = rem - oh0 * p.conv_q;
             const int fh = p.conv_flip ? p.conv_r - 1 - kh : kh, fw = p.conv_flip ? p.conv_s - 1 - kw : kw;
             tma_load_im2col_2sm(sa, &tma_a, lbar, cb * BK, ow0 * p.conv_stride - p.conv_pad,
                                 oh0 * p.conv_stride - p.conv_pad, in0, fw, fh);
             if (B_MN) {
+              const int wtap = p.sub_en ? ((p.sub_wtaps[split] >> (4 * tap)) & 15) : tap;
 #pragma unroll
               for (int a = 0; a < (BN2 / 2) / 64; ++a)
-                tma_load_2d_2sm(sb + a * (BK * 128), &tma_b, lbar, tap * p.N + n0 + a * 64, cb * BK);
+                tma_load_2d_2sm(sb + a * (BK * 128), &tma_b, lbar, wtap * p.N + n0 + a * 64, cb * BK);
             } else {
               tma_load_2d_2sm(sb, &tma_b, lbar, kb * BK, n0);
             }
@@ -768,8 +802,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tma_a,
       int iter = 0;
       for (int t = pair; t < total_tiles; t += num_pairs, ++iter) {
         const int split = t / (p.num_n * p.num_m);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        int kb0, kb1;
+        tile_kb_range(p, split, kb_total, kb0, kb1);
         const int as = iter & 1;
         const uint32_t aphase = (iter >> 1) & 1;
         mbar_wait(tempty_bar(as), aphase ^ 1);
@@ -1251,7 +1285,7 @@ static EncodeIm2colFn get_encode_im2col() {
 
 // NHWC bf16 activation [N,H,W,C] as an im2col tensor map: `pixels` output positions x 64 channels per load.
 static int make_im2col_map(CUtensorMap* map, const void* base, int N, int H, int W, int C, int R, int S,
-                           int stride, int pad, int pixels) {
+                           int stride, int pad, int pixels, const int* corners = nullptr) {
   EncodeIm2colFn enc = get_encode_im2col();
   if (!enc) {
     kdl_set_error("cuTensorMapEncodeIm2col unavailable (no CUDA driver?)");
@@ -1261,6 +1295,7 @@ static int make_im2col_map(CUtensorMap* map, const void* base, int N, int H, int
   cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
   int lower[2] = {-pad, -pad};
   int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  if (corners) { lower[0] = corners[0]; lower[1] = corners[1]; upper[0] = corners[2]; upper[1] = corners[3]; }
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower,
                    upper, 64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -1416,4 +1451,66 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
   }
   kdl_set_error("conv2d: unknown mode %d", mode);
   return KDL_ERR_ARG;
+}
+
+// ---- 3x3 / stride-2 / pad-1 dgrad ------------------------------------------------------------------------
+// dx[n, ih, iw, :] = sum over (kh, kw) with (ih + 1 - kh), (iw + 1 - kw) even of dy[n, (ih+1-kh)/2, (iw+1-kw)/2, :] w[:, kh, kw, :].
+// Split by the parity (ph, pw) of the input pixel, each class is a STRIDE-1 correlation over dy with 1 or 2 taps
+// per axis (even: kh = 1 at offset 0; odd: kh = 2 at offset 0 and kh = 0 at offset +1, which runs off the
+// bottom / right edge and zero-fills), i.e. 1 + 2 + 2 + 4 = 9 tap-GEMMs in total — exactly the useful work, none
+// of the multiplications by the zeros of an up-sampled dy.  ONE persistent launch of the TMA-im2col kernel walks the
+// tiles of all four classes (the class rides in the tile's "split" index): patch operand = dy with map corners
+// {0, 0}, weight tiles picked through a per-class tap map, output rows stored at the class's pixels.
+// Replaces the last cuDNN call of the ResNet-50 step (cutlass implicit_gemm_strided_dgrad via ATen
+// convolution_backward).  dy [N, H/2, W/2, Cout], w [Cout, 3, 3, Cin], dx [N, H, W, Cin]; H, W even.
+extern "C" int kdl_conv2d_dgrad_s2(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                                   cudaStream_t stream) {
+  if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) {
+    kdl_set_error("conv2d_dgrad_s2: need even H, W and Cin, Cout multiples of 64 (H=%d W=%d Cin=%d Cout=%d)", H, W, Cin, Cout);
+    return KDL_ERR_UNSUPPORTED;
+  }
+  const int P = H / 2, Q = W / 2, M = N * P * Q;
+  const int bn = Cin <= 64 ? 64 : 128;
+  static int conv2 = -1;
+  if (conv2 < 0) {
+    const char* e = getenv("KDL_CONV_2CTA");
+    conv2 = e ? atoi(e) : 1;
+  }
+  const bool two = conv2 && M >= 1024 && Cin >= 128;
+  const int bn2 = Cin >= 256 ? 256 : 128;
+  CUtensorMap ma, mb, mc;
+  const int corners[4] = {0, 0, 0, 0};
+  int rc = make_im2col_map(&ma, dy, N, P, Q, Cout, 1, 1, 1, 0, BM, corners);
+  if (rc) return rc;
+  rc = make_map(&mb, w, (uint64_t)(9 * Cin), (uint64_t)Cout, (uint64_t)(9 * Cin), 64, BK);
+  if (rc) return rc;
+  rc = make_c_map(&mc, dx, 0, (uint64_t)N * H * W, (uint64_t)Cin, (uint64_t)Cin, 1);   // unused by the strided store
+  if (rc) return rc;
+  GemmParams p = {};
+  p.C = (bf16*)dx; p.M = M; p.N = Cin; p.K = 4 * Cout; p.ldc = Cin;
+  p.splits = 4;                                   // the four parity classes, one persistent launch
+  p.kb_per_split = 2 * (Cout / BK);               // typical class (only read by the epilogue-warp heuristic)
+  p.conv_mode = 1; p.conv_q = Q; p.conv_p = P; p.conv_c = Cout; p.conv_flip = 0;
+  p.conv_s = 2; p.conv_r = 2; p.conv_stride = 1; p.conv_pad = 0;
+  p.sub_en = 1;
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      const int R = ph ? 2 : 1, S = pw ? 2 : 1;
+      int taps = 0;
+      for (int th = 0; th < R; ++th)
+        for (int tw = 0; tw < S; ++tw) {
+          const int kh = ph ? (th == 0 ? 2 : 0) : 1, kw = pw ? (tw == 0 ? 2 : 0) : 1;
+          taps |= (kh * 3 + kw) << (4 * (th * S + tw));
+        }
+      p.sub_wtaps[2 * ph + pw] = taps;
+    }
+  if (two) {
+    p.num_m = (M + 255) / 256; p.num_n = (Cin + bn2 - 1) / bn2;
+    rc = bn2 == 256 ? launch_2cta<0, 1, 256>(ma, mb, mc, mc, p, stream) : launch_2cta<0, 1, 128>(ma, mb, mc, mc, p, stream);
+  } else {
+    p.num_m = (M + BM - 1) / BM; p.num_n = (Cin + bn - 1) / bn;
+    rc = bn == 64 ? launch<0, 1, 64, 6>(ma, mb, mc, mc, p, stream) : launch<0, 1, 128, 5>(ma, mb, mc, mc, p, stream);
+  }
+  if (rc) return rc;
+  return KDL_OK;
 }

@@ -183,6 +183,12 @@ size_t kdl_conv2d_scratch_bytes(int mode, int N, int H, int W, int Cin, int Cout
 int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N, int H, int W, int Cin,
                     int Cout, int R, int S, int stride, int pad, const void* addend_bf16, void* scratch,
                     size_t scratch_bytes, cudaStream_t stream);
+/* Input gradient of a 3x3 / stride-2 / pad-1 convolution: dy [N, H/2, W/2, Cout], w [Cout, 3, 3, Cin] ->
+ * dx [N, H, W, Cin] (H, W even).  Four stride-1 sub-convolutions by input-pixel parity on the TMA-im2col
+ * kernel (1 + 2 + 2 + 4 taps).  The stock worker gets this from cuDNN through ATen convolution_backward; the
+ * reference operator has no math (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15 names an image). */
+int kdl_conv2d_dgrad_s2(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                        cudaStream_t stream);
 
 /* ---- N7b: 3x3 / stride-1 / pad-1 convolution with the input halo resident in shared memory ----
  * One tiled TMA box per 64 channels brings a (rows+2) x (W+2) input halo into shared memory; the nine

@@ -12,8 +12,9 @@ go to the tcgen05 GEMM kernel (ops.gemm, BatchNorm statistics from its epilogue)
 straight from the uint8 image (csrc/stem_conv.cu; im2col + GEMM for sizes other than 224x224);
 3x3 convolutions go to the halo-resident / TMA-im2col tcgen05 kernels (ops.conv); the 1x1/stride-2
 downsample convolutions use the im2col kernel, their dgrad stays a compact GEMM result that the
-sibling conv1 dgrad adds in its epilogue.  What is left on cuDNN (through ATen) are the three
-stride-2 3x3 dgrads.  With gemm=None everything falls back to cuDNN/cuBLAS (the A/B arm of the tests).
+sibling conv1 dgrad adds in its epilogue; the three stride-2 3x3 dgrads run as four parity
+sub-convolutions each on the same im2col kernel — nothing of the step is left on cuDNN.  With gemm=None
+everything falls back to cuDNN/cuBLAS (the A/B arm of the tests).
 This is config #2 of BASELINE.json ("PyTorchJob ResNet-50 DDP bf16 ... synthetic 224² images").
 """
 from __future__ import annotations
@@ -101,7 +102,12 @@ class Conv:
             dx = None
             if need_dx and self.stride == 1:
                 dx = conv_ops.dgrad(dy, self.w, x.shape[1:3], 1, self.pad, addend=addend)
-            elif need_dx:     # strided dgrad: cuDNN
+            elif need_dx and net.own_strided_dgrad and conv_ops.dgrad_s2_supported(
+                    x.shape[1:3], self.cin, self.cout, self.k, self.k, self.stride, self.pad):
+                dx = conv_ops.dgrad_s2(dy, self.w, x.shape[1:3])       # four parity sub-convolutions
+                if addend is not None:
+                    K.add_(dx, addend)
+            elif need_dx:     # other strided shapes: cuDNN
                 dxn, _, _ = _conv_bwd(_nchw(dy), _nchw(x), self.w_nchw, None, [self.stride] * 2,
                                       [self.pad] * 2, [1, 1], False, [0, 0], 1, [True, False, False])
                 dx = _nhwc(dxn)
@@ -260,6 +266,8 @@ class ResNet50:
         # implicit GEMM for stride 2) instead of cuDNN.  End to end the two are within 1 % of each other
         # (23.1 vs 22.9 ms/step, profiles/bench_1gpu_ownconv_halo.log); KUBEDL_OWN_CONV=0 restores cuDNN.
         self.own_conv = _os.environ.get("KUBEDL_OWN_CONV", "1") == "1"
+        # the three 3x3 / stride-2 input gradients on our im2col kernel too (0: cuDNN)
+        self.own_strided_dgrad = _os.environ.get("KUBEDL_OWN_STRIDED_DGRAD", "1") == "1"
         self.num_classes = num_classes
         self.arena = ParamArena()
         self.gemm = gemm

@@ -14,6 +14,7 @@ L.register_signatures({
     "kdl_conv2d_scratch_bytes": (C.c_size_t, [C.c_int] * 10),
     "kdl_conv2d_bf16": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 9 +
                         [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kdl_conv2d_dgrad_s2": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 + [C.c_void_p]),
     "kdl_conv3x3_halo_supported": (C.c_int, [C.c_int] * 6),
     "kdl_conv3x3_halo_wgrad_scratch_bytes": (C.c_size_t, [C.c_int] * 5),
     "kdl_conv3x3_halo_wgrad_bf16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 +
@@ -82,6 +83,26 @@ def dgrad(dy: torch.Tensor, w: torch.Tensor, in_hw, stride: int, pad: int,
     if _HALO and halo and R == 3 and S == 3 and stride == 1 and pad == 1 and halo_supported(1, N, H, W, Cin, Cout):
         return _run_halo(1, dy, w, dx, N, H, W, Cin, Cout, addend=addend)
     return _run(1, dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad, addend)
+
+
+def dgrad_s2_supported(in_hw, Cin: int, Cout: int, R: int, S: int, stride: int, pad: int) -> bool:
+    H, W = in_hw
+    return R == 3 and S == 3 and stride == 2 and pad == 1 and H % 2 == 0 and W % 2 == 0 and Cin % 64 == 0 and Cout % 64 == 0
+
+
+def dgrad_s2(dy: torch.Tensor, w: torch.Tensor, in_hw) -> torch.Tensor:
+    """Input gradient of a 3x3 / stride-2 / pad-1 convolution: four parity sub-convolutions, one persistent
+    launch of the im2col kernel."""
+    _chk(dy); _chk(w)
+    N, OH, OW, Cout = dy.shape
+    _, R, S, Cin = w.shape
+    H, W = in_hw
+    assert dgrad_s2_supported(in_hw, Cin, Cout, R, S, 2, 1) and OH == H // 2 and OW == W // 2
+    dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device=dy.device)
+    L.check(L.lib().kdl_conv2d_dgrad_s2(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, Cin, Cout, L.stream_ptr()),
+            "kdl_conv2d_dgrad_s2")
+    L.count(1)
+    return dx
 
 
 def wgrad(dy: torch.Tensor, x: torch.Tensor, R: int, S: int, stride: int, pad: int,

@@ -50,3 +50,29 @@ def test_halo_dispatch(cuda):
     from kubedl_b200.ops import conv
     assert conv.halo_supported(0, 256, 56, 56, 64, 64) and conv.halo_supported(1, 256, 28, 28, 128, 128)
     assert not conv.halo_supported(0, 256, 14, 14, 256, 256)     # weights do not fit: im2col kernel
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout", [
+    (2, 8, 8, 64, 64),          # 1-CTA kernel, BN = 64
+    (3, 14, 14, 128, 128),      # CTA pair, 128-wide tiles, odd H/2
+    (4, 28, 28, 256, 256),      # CTA pair, 256-wide tiles (ResNet layer3.0)
+    (16, 56, 56, 128, 128),     # ResNet layer2.0 at a smaller batch
+    (5, 14, 14, 512, 512),      # ResNet layer4.0
+])
+def test_conv3x3_stride2_dgrad_matches_reference(cuda, N, H, W, Cin, Cout):
+    """3x3 / stride-2 / pad-1 input gradient as four parity sub-convolutions == conv_transpose in fp32."""
+    from kubedl_b200.ops import conv as conv_ops
+    torch.manual_seed(31)
+    dy = torch.randn(N, H // 2, W // 2, Cout, device=cuda).bfloat16()
+    w = (torch.randn(Cout, 3, 3, Cin, device=cuda) * 0.05).bfloat16()
+    dx = conv_ops.dgrad_s2(dy, w, (H, W))
+    ref = torch.nn.functional.conv_transpose2d(dy.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2),
+                                               stride=2, padding=1, output_padding=1).permute(0, 2, 3, 1)
+    assert ref.shape == dx.shape
+    err = float((dx.float() - ref).abs().max() / ref.abs().max())
+    assert err < 1.5e-2, err
+    # every parity class was written (no pixel left at its uninitialised value)
+    for ph in (0, 1):
+        for pw in (0, 1):
+            sub, rsub = dx[:, ph::2, pw::2].float(), ref[:, ph::2, pw::2]
+            assert float((sub - rsub).abs().max() / ref.abs().max()) < 1.5e-2, (ph, pw)

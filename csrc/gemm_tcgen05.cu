@@ -1322,9 +1322,35 @@ extern "C" size_t kdl_conv2d_scratch_bytes(int mode, int N, int H, int W, int Ci
 // mode 0 fprop : in0 = x [N,H,W,Cin],   in1 = w [Cout,R,S,Cin] -> out = y  [N,OH,OW,Cout]
 // mode 1 dgrad : in0 = dy [N,OH,OW,Cout], in1 = w              -> out = dx [N,H,W,Cin] (+addend); stride 1, 2*pad = R-1
 // mode 2 wgrad : in0 = dy,               in1 = x               -> out = dw [Cout,R,S,Cin] (split over pixels)
+static int conv2d_impl(int mode, const void* in0, const void* in1, void* out, int N, int H, int W,
+                       int Cin, int Cout, int R, int S, int stride, int pad, const void* addend,
+                       void* scratch, size_t scratch_bytes, float* stats_partial, int* stats_parts_out,
+                       cudaStream_t stream);
+
 extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N, int H, int W,
                                int Cin, int Cout, int R, int S, int stride, int pad, const void* addend,
                                void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  return conv2d_impl(mode, in0, in1, out, N, H, W, Cin, Cout, R, S, stride, pad, addend, scratch, scratch_bytes, nullptr,
+                     nullptr, stream);
+}
+
+// fprop that also returns, from the same epilogue, the per-CTA column sum / sum of squares of y (as stored) for the
+// BatchNorm that follows: stats_partial [kdl_gemm_max_ctas()][2][Cout] fp32, *stats_parts_out rows are valid.
+extern "C" int kdl_conv2d_fprop_stats(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
+                                      int R, int S, int stride, int pad, float* stats_partial, int* stats_parts_out,
+                                      cudaStream_t stream) {
+  if (stats_partial == nullptr || stats_parts_out == nullptr || Cout > kStatsMaxN) {
+    kdl_set_error("conv2d_fprop_stats: need a statistics buffer and Cout <= %d", kStatsMaxN);
+    return KDL_ERR_ARG;
+  }
+  return conv2d_impl(0, x, w, y, N, H, W, Cin, Cout, R, S, stride, pad, nullptr, nullptr, 0, stats_partial, stats_parts_out,
+                     stream);
+}
+
+static int conv2d_impl(int mode, const void* in0, const void* in1, void* out, int N, int H, int W,
+                       int Cin, int Cout, int R, int S, int stride, int pad, const void* addend,
+                       void* scratch, size_t scratch_bytes, float* stats_partial, int* stats_parts_out,
+                       cudaStream_t stream) {
   const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
   if (Cin % 64 || Cout % 64) {
     kdl_set_error("conv2d: Cin and Cout must be multiples of 64 (Cin=%d Cout=%d)", Cin, Cout);
@@ -1376,6 +1402,16 @@ extern "C" int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void*
       rc = make_c_map(&md, const_cast<void*>(addend), 0, (uint64_t)M, (uint64_t)Nout, (uint64_t)Nout, 1);
       if (rc) return rc;
       p.add_tma = 1;
+    }
+    if (mode == 0 && stats_partial != nullptr) {
+      p.stats = stats_partial;        // every CTA (pair) keeps one column tile: see stats_grid()
+      if (two) {
+        const int nm = (M + 255) / 256, nn = (Nout + bn2 - 1) / bn2, tiles2 = nm * nn, pairs = num_sms() / 2;
+        *stats_parts_out = (stats_grid(tiles2 < pairs ? tiles2 : pairs, nn) / nn) * 2;
+      } else {
+        const int tiles1 = p.num_m * p.num_n;
+        *stats_parts_out = stats_grid(tiles1 < num_sms() ? tiles1 : num_sms(), p.num_n) / p.num_n;
+      }
     }
     if (two) {
       p.num_m = (M + 255) / 256;

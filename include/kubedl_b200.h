@@ -189,6 +189,13 @@ int kdl_conv2d_bf16(int mode, const void* in0, const void* in1, void* out, int N
  * reference operator has no math (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15 names an image). */
 int kdl_conv2d_dgrad_s2(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
                         cudaStream_t stream);
+/* fprop (as kdl_conv2d_bf16 mode 0) that also returns the BatchNorm column statistics of y from its epilogue:
+ * stats_partial [kdl_gemm_max_ctas()][2][Cout] fp32, *stats_parts_out valid rows (feed kdl_bn_fwd_from_stats).
+ * The stock worker runs cuDNN's convolution and a separate batch-norm statistics kernel; no counterpart in the
+ * reference operator (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15 names an image). */
+int kdl_conv2d_fprop_stats(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int R,
+                           int S, int stride, int pad, float* stats_partial, int* stats_parts_out,
+                           cudaStream_t stream);
 
 /* ---- N7b: 3x3 / stride-1 / pad-1 convolution with the input halo resident in shared memory ----
  * One tiled TMA box per 64 channels brings a (rows+2) x (W+2) input halo into shared memory; the nine

@@ -72,6 +72,8 @@ class Conv:
             y = net.gemm.nt(x.view(-1, Cin), self.w.view(self.cout, Cin)).view(N, H, W, self.cout)
             return (y, None) if want_stats else y
         if self.own_conv or self.own_strided:
+            if want_stats and net.fuse_bn_stats and net.fuse_conv_stats:   # im2col kernel: statistics from its epilogue
+                return conv_ops.fprop(x, self.w, self.stride, self.pad, want_stats=True)
             y = conv_ops.fprop(x, self.w, self.stride, self.pad)
             return (y, None) if want_stats else y
         y = torch.ops.aten.convolution(_nchw(x), self.w_nchw, None, [self.stride] * 2,
@@ -200,8 +202,8 @@ class Bottleneck:
     def fwd(self, x, train=True):
         c1, s1 = self.c1.fwd(x, want_stats=True)
         a1 = self.b1.fwd(c1, stats=s1)
-        c2 = self.c2.fwd(a1)
-        a2 = self.b2.fwd(c2)
+        c2, s2 = self.c2.fwd(a1, want_stats=True)
+        a2 = self.b2.fwd(c2, stats=s2)
         c3, s3 = self.c3.fwd(a2, want_stats=True)
         if self.cd is not None:
             cdo, sd = self.cd.fwd(x, want_stats=True)
@@ -254,6 +256,7 @@ class ResNet50:
         # (profiles/bench_1gpu_bnstats_ab.log).  The first version used shared-memory float atomics
         # (CAS loops) and a serial finalizer and was slower than the separate pass.
         self.fuse_bn_stats = _os.environ.get("KUBEDL_FUSE_BN_STATS", "1") == "1"
+        self.fuse_conv_stats = _os.environ.get("KUBEDL_FUSE_CONV_STATS", "1") == "1"
         # ReLU masks of the residual BatchNorms as 1 bit per element (0: the backward pass reads y)
         self.bn_relu_bitmask = _os.environ.get("KUBEDL_BN_BITMASK", "1") == "1"
         # identity blocks: the residual gradient is masked inside conv1's dgrad epilogue (no dz tensor)

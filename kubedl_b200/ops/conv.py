@@ -14,6 +14,9 @@ L.register_signatures({
     "kdl_conv2d_scratch_bytes": (C.c_size_t, [C.c_int] * 10),
     "kdl_conv2d_bf16": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 9 +
                         [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kdl_conv2d_fprop_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 9 +
+                               [C.c_void_p, C.POINTER(C.c_int), C.c_void_p]),
+    "kdl_gemm_max_ctas": (C.c_int, []),
     "kdl_conv2d_dgrad_s2": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 + [C.c_void_p]),
     "kdl_conv3x3_halo_supported": (C.c_int, [C.c_int] * 6),
     "kdl_conv3x3_halo_wgrad_scratch_bytes": (C.c_size_t, [C.c_int] * 5),
@@ -62,15 +65,27 @@ def _run(mode, in0, in1, out, N, H, W, Cin, Cout, R, S, stride, pad, addend=None
     return out
 
 
-def fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int, halo: bool = True) -> torch.Tensor:
+def fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int, halo: bool = True, want_stats: bool = False):
+    """y = conv(x, w).  want_stats: returns (y, stats) where stats = (partial, nparts) for ops.nn.bn_fwd(stats=...) when
+    the convolution ran on the TMA-im2col kernel (BatchNorm column statistics from its epilogue), else (y, None)."""
     _chk(x); _chk(w)
     N, H, W, Cin = x.shape
     Cout, R, S, _ = w.shape
     OH, OW = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
     y = torch.empty(N, OH, OW, Cout, dtype=torch.bfloat16, device=x.device)
     if _HALO and halo and R == 3 and S == 3 and stride == 1 and pad == 1 and halo_supported(0, N, H, W, Cin, Cout):
-        return _run_halo(0, x, w, y, N, H, W, Cin, Cout)
-    return _run(0, x, w, y, N, H, W, Cin, Cout, R, S, stride, pad)
+        y = _run_halo(0, x, w, y, N, H, W, Cin, Cout)
+        return (y, None) if want_stats else y
+    if want_stats and Cout <= 2048:
+        lib = L.lib()
+        partial = torch.empty(lib.kdl_gemm_max_ctas(), 2, Cout, dtype=torch.float32, device=x.device)
+        nparts = C.c_int(0)
+        L.check(lib.kdl_conv2d_fprop_stats(x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, R, S, stride, pad,
+                                           partial.data_ptr(), C.byref(nparts), L.stream_ptr()), "kdl_conv2d_fprop_stats")
+        L.count(1)
+        return y, (partial, nparts.value)
+    y = _run(0, x, w, y, N, H, W, Cin, Cout, R, S, stride, pad)
+    return (y, None) if want_stats else y
 
 
 def dgrad(dy: torch.Tensor, w: torch.Tensor, in_hw, stride: int, pad: int,

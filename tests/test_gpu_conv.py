@@ -76,3 +76,33 @@ def test_conv3x3_stride2_dgrad_matches_reference(cuda, N, H, W, Cin, Cout):
         for pw in (0, 1):
             sub, rsub = dx[:, ph::2, pw::2].float(), ref[:, ph::2, pw::2]
             assert float((sub - rsub).abs().max() / ref.abs().max()) < 1.5e-2, (ph, pw)
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad", [
+    (8, 14, 14, 256, 256, 3, 1, 1),      # layer3 3x3 (CTA pair, 256-wide tiles)
+    (6, 28, 28, 256, 256, 3, 2, 1),      # layer3.0 3x3 / stride 2
+    (4, 56, 56, 256, 512, 1, 2, 0),      # layer2.0 downsample 1x1 / stride 2
+    (3, 8, 8, 64, 64, 3, 2, 1),          # 1-CTA kernel, BN = 64
+])
+def test_conv_fprop_fused_bn_statistics(cuda, N, H, W, Cin, Cout, R, stride, pad):
+    """Column statistics from the im2col convolution's epilogue == statistics of the stored output, and the
+    BatchNorm fed by them == the BatchNorm that recomputes them."""
+    from kubedl_b200.ops import conv as conv_ops
+    from kubedl_b200.ops import nn as Kn
+    torch.manual_seed(41)
+    x = torch.randn(N, H, W, Cin, device=cuda).bfloat16()
+    w = (torch.randn(Cout, R, R, Cin, device=cuda) * 0.05).bfloat16()
+    y, stats = conv_ops.fprop(x, w, stride, pad, halo=False, want_stats=True)
+    assert stats is not None
+    partial, nparts = stats
+    y0 = conv_ops.fprop(x, w, stride, pad, halo=False)
+    assert torch.equal(y, y0)
+    tot = partial[:nparts].sum(0)
+    yf = y.float().view(-1, Cout)
+    torch.testing.assert_close(tot[0], yf.sum(0), atol=2e-1, rtol=2e-3)
+    torch.testing.assert_close(tot[1], (yf * yf).sum(0), atol=2e-1, rtol=2e-3)
+    gamma, beta = torch.rand(Cout, device=cuda) + 0.5, torch.randn(Cout, device=cuda)
+    o1, sv1 = Kn.bn_fwd(y, gamma, beta, None, None, relu=True)
+    o2, sv2 = Kn.bn_fwd(y, gamma, beta, None, None, relu=True, stats=stats)
+    torch.testing.assert_close(sv2, sv1, atol=1e-4, rtol=1e-4)
+    torch.testing.assert_close(o2.float(), o1.float(), atol=2e-2, rtol=2e-2)

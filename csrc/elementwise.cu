@@ -183,11 +183,15 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __res
   const int64_t total = (int64_t)N * OH * OW * cvec;
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
-    int cg = (int)(i % cvec);
-    int64_t t = i / cvec;
-    int ow = (int)(t % OW); t /= OW;
-    int oh = (int)(t % OH);
-    int n = (int)(t / OH);
+    // 32-bit index decode (the host checks total < 2^31): 64-bit div / mod are ~100-instruction software
+    // routines each, six of them cost as much as the nine loads
+    const uint32_t iu = (uint32_t)i;
+    uint32_t t = iu / (uint32_t)cvec;
+    const int cg = (int)(iu - t * (uint32_t)cvec);
+    const uint32_t t2 = t / (uint32_t)OW;
+    const int ow = (int)(t - t2 * (uint32_t)OW);
+    const int n = (int)(t2 / (uint32_t)OH);
+    const int oh = (int)(t2 - (uint32_t)n * (uint32_t)OH);
     // Two bf16 values per 32-bit word: the running maximum (HMNMX2), the "new value is larger" mask and the
     // argmax codes (16 bits per value) are all updated with packed instructions — about a third of the
     // instructions of the scalar fp32 version, which was issue-bound at 2.6 TB/s.
@@ -258,11 +262,13 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_quad_kernel(const bf16* 
   const int64_t total = (int64_t)N * HB * WB * cvec;
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += T) {
-    const int cg = (int)(i % cvec);
-    int64_t t = i / cvec;
-    const int b = (int)(t % WB); t /= WB;
-    const int a = (int)(t % HB);
-    const int n = (int)(t / HB);
+    const uint32_t iu = (uint32_t)i;            // 32-bit decode, as in the forward kernel
+    const uint32_t t = iu / (uint32_t)cvec;
+    const int cg = (int)(iu - t * (uint32_t)cvec);
+    const uint32_t t2 = t / (uint32_t)WB;
+    const int b = (int)(t - t2 * (uint32_t)WB);
+    const int n = (int)(t2 / (uint32_t)HB);
+    const int a = (int)(t2 - (uint32_t)n * (uint32_t)HB);
     float acc[4][8];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
@@ -529,6 +535,10 @@ extern "C" int kdl_maxpool3x3s2_fwd(const void* x, void* y, void* idx_u8, int N,
   }
   int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
   int64_t total = (int64_t)N * OH * OW * (C / 8);
+  if (total >= ((int64_t)1 << 31)) {
+    kdl_set_error("maxpool: more than 2^31 output vectors (N=%d H=%d W=%d C=%d)", N, H, W, C);
+    return KDL_ERR_UNSUPPORTED;
+  }
   maxpool3x3s2_fwd_kernel<false><<<grid_for(total, 256), 256, 0, stream>>>(
       (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, OH, OW, nullptr);
   KDL_CHECK_LAUNCH();
@@ -544,6 +554,10 @@ extern "C" int kdl_maxpool3x3s2_affine_relu_fwd(const void* x, const float* coef
   }
   int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
   int64_t total = (int64_t)N * OH * OW * (C / 8);
+  if (total >= ((int64_t)1 << 31)) {
+    kdl_set_error("maxpool: more than 2^31 output vectors (N=%d H=%d W=%d C=%d)", N, H, W, C);
+    return KDL_ERR_UNSUPPORTED;
+  }
   maxpool3x3s2_fwd_kernel<true><<<grid_for(total, 256), 256, 0, stream>>>(
       (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, OH, OW, coef);
   KDL_CHECK_LAUNCH();
@@ -558,7 +572,7 @@ extern "C" int kdl_maxpool3x3s2_bwd(const void* dy, const void* idx_u8, void* dx
   }
   int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
   int64_t total = (int64_t)N * H * W * (C / 8);
-  if ((H % 2) == 0 && (W % 2) == 0) {
+  if ((H % 2) == 0 && (W % 2) == 0 && total / 4 < ((int64_t)1 << 31)) {
     maxpool3x3s2_bwd_quad_kernel<<<grid_for(total / 4, 256), 256, 0, stream>>>(
         (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, N, H, W, C, OH, OW);
     KDL_CHECK_LAUNCH();

@@ -206,6 +206,11 @@ class APIServer:
         with self._lock:
             return self.list(kind, namespace, label_selector), str(self._rv)
 
+    def request_log_snapshot(self) -> List[Tuple[str, str, str]]:
+        """A consistent copy of the recent (verb, kind, ns/name) request log; other threads keep appending."""
+        with self._lock:
+            return list(self.request_log)
+
     def _update(self, obj: dict, status_only: bool, spec_only: bool) -> dict:
         kind = obj.get("kind")
         with self._lock:

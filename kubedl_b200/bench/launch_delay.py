@@ -100,7 +100,9 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
         m = op.reconcilers[kind].metrics
         first = [v for _, v in m.launch_delays["first_pod"]]
         allp = [v for _, v in m.launch_delays["all_pods"]]
-        creates = sum(1 for verb, kd, _ in op.mgr.api.request_log if verb == "create" and kd in ("Pod", "Service"))
+        api = op.mgr.api
+        log_ = api.request_log_snapshot() if hasattr(api, "request_log_snapshot") else list(api.request_log)
+        creates = sum(1 for verb, kd, _ in log_ if verb == "create" and kd in ("Pod", "Service"))
         return {"kind": kind, "jobs": jobs, "replicas": replicas, "worker_seconds": seconds,
                 "first_pod_ms": {"p50": 1e3 * _pct(first, 0.5), "p90": 1e3 * _pct(first, 0.9), "n": len(first)},
                 "all_pods_ms": {"p50": 1e3 * _pct(allp, 0.5), "p90": 1e3 * _pct(allp, 0.9), "n": len(allp)},

@@ -94,7 +94,7 @@ __device__ __forceinline__ uint4 pool_grad_gather(const bf16* __restrict__ dp, c
 // (profiles/r2_bn_backward.md).  The second sum is accumulated as sum(dz * x) and centred once, in the
 // finaliser: sum(dz * xhat) = rstd * (sum(dz * x) - mean * sum(dz)).
 template <int MODE, int RELU, bool POOL>
-__global__ void __launch_bounds__(256, MODE == 1 ? 3 : 4) bn_reduce_kernel(BnReduceParams p) {
+__global__ void __launch_bounds__(256, (MODE == 1 && (RELU == 1 || RELU == 2 || POOL)) ? 3 : 4) bn_reduce_kernel(BnReduceParams p) {
   __shared__ float red[256 * 16];
   __shared__ int is_last;
   pdl_wait();      // programmatic dependent launch: nothing global is touched before the predecessor has finished

@@ -315,9 +315,139 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) din_scatter_update_kernel
   }
 }
 
+// ---- the elementwise glue of the DIN MLP, fused ----------------------------------------------------------------
+// At B = 4096 every tensor of the MLP is a few megabytes, so the step is bound by the NUMBER of launches; the
+// loss and the three "ReLU backward + bias gradient" chains were 29 ATen kernels (profiles/r2_din_step_*.csv).
+
+// Binary cross-entropy with logits on column 0 of z [B, ldz] (bf16), mean over B, and its gradient as the padded
+// 8-column bf16 matrix the wgrad / dgrad GEMMs take: dz[:, 0] = (sigmoid(z) - y) / B, dz[:, 1:8] = 0.  One block.
+__global__ void __launch_bounds__(1024) din_bce_grad_kernel(const bf16* __restrict__ z, int ldz,
+                                                            const float* __restrict__ label, int B,
+                                                            float* __restrict__ loss, bf16* __restrict__ dz) {
+  __shared__ float red[32];
+  const float invB = 1.f / (float)B;
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const float x = __bfloat162float(z[(size_t)i * ldz]);
+    const float y = label[i];
+    acc += fmaxf(x, 0.f) - x * y + log1pf(__expf(-fabsf(x)));
+    const float g = (1.f / (1.f + __expf(-x)) - y) * invB;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    o.x = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(g));
+    *reinterpret_cast<uint4*>(dz + (size_t)i * 8) = o;
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) loss[0] = v * invB;
+  }
+}
+
+// dh = (h > 0 ? dh : 0) in place (RELU) and dbias[n] = sum_m dh[m, n], fixed summation order.  Grid (N / 64
+// column tiles, row chunks); the last block of a column tile to finish adds the chunks' partial rows.
+template <bool RELU>
+__global__ void __launch_bounds__(256) relu_bwd_colsum_kernel(bf16* __restrict__ dh, const bf16* __restrict__ h, int M,
+                                                              int N, float* __restrict__ partial,
+                                                              unsigned* __restrict__ counter, bf16* __restrict__ dbias) {
+  __shared__ float red[32][65];
+  __shared__ int is_last;
+  const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  const int col0 = blockIdx.x * 64 + cg * 8;
+  const bool active = col0 < N;
+  const int rows_per = (M + gridDim.y - 1) / gridDim.y;
+  const int r_end = min(M, (int)(blockIdx.y + 1) * rows_per);
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (active) {
+    for (int r = blockIdx.y * rows_per + rl; r < r_end; r += 32) {
+      bf16* q = dh + (size_t)r * N + col0;
+      float f[8];
+      unpack8(*reinterpret_cast<const uint4*>(q), f);
+      if (RELU) {
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(h + (size_t)r * N + col0), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = g[j] > 0.f ? f[j] : 0.f;
+        *reinterpret_cast<uint4*>(q) = pack8(f);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += f[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[rl][cg * 8 + j] = s[j];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float a = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) a += red[r][threadIdx.x];
+    const int col = blockIdx.x * 64 + threadIdx.x;
+    if (col < N) partial[(size_t)blockIdx.y * N + col] = a;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(counter + blockIdx.x, 1u) == gridDim.y - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  if (threadIdx.x < 64) {
+    const int col = blockIdx.x * 64 + threadIdx.x;
+    if (col < N) {
+      float a = 0.f;
+      for (unsigned c = 0; c < gridDim.y; ++c) a += __ldcg(partial + (size_t)c * N + col);
+      dbias[col] = __float2bfloat16(a);
+    }
+  }
+  if (threadIdx.x == 0) counter[blockIdx.x] = 0u;
+}
+
 }  // namespace kdl
 
 using namespace kdl;
+
+extern "C" int kdl_din_bce_grad(const void* z_bf16, int ldz, const float* label, int B, float* loss, void* dz_bf16,
+                                cudaStream_t stream) {
+  if (B < 1 || ldz < 1) {
+    kdl_set_error("din_bce_grad: bad arguments B=%d ldz=%d", B, ldz);
+    return KDL_ERR_ARG;
+  }
+  din_bce_grad_kernel<<<1, 1024, 0, stream>>>((const bf16*)z_bf16, ldz, label, B, loss, (bf16*)dz_bf16);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" size_t kdl_relu_bwd_colsum_workspace_bytes(int N) { return 256 + (size_t)32 * N * sizeof(float); }
+
+// workspace: kdl_relu_bwd_colsum_workspace_bytes(N) bytes, zeroed ONCE (the counters reset themselves).
+extern "C" int kdl_relu_bwd_colsum(void* dh_bf16, const void* h_bf16, int M, int N, void* dbias_bf16, void* workspace,
+                                   size_t workspace_bytes, cudaStream_t stream) {
+  if (M < 1 || N < 8 || (N & 7) || N > 64 * 64) {
+    kdl_set_error("relu_bwd_colsum: need N %% 8 == 0 and N <= 4096 (M=%d N=%d)", M, N);
+    return KDL_ERR_ARG;
+  }
+  if (workspace == nullptr || workspace_bytes < kdl_relu_bwd_colsum_workspace_bytes(N)) {
+    kdl_set_error("relu_bwd_colsum: workspace too small");
+    return KDL_ERR_WORKSPACE;
+  }
+  int chunks = (M + 255) / 256;
+  if (chunks > 32) chunks = 32;
+  if (chunks < 1) chunks = 1;
+  const dim3 grid((N + 63) / 64, chunks);
+  unsigned* counter = (unsigned*)workspace;
+  float* partial = (float*)((char*)workspace + 256);
+  if (h_bf16 != nullptr)
+    relu_bwd_colsum_kernel<true><<<grid, 256, 0, stream>>>((bf16*)dh_bf16, (const bf16*)h_bf16, M, N, partial, counter,
+                                                           (bf16*)dbias_bf16);
+  else
+    relu_bwd_colsum_kernel<false><<<grid, 256, 0, stream>>>((bf16*)dh_bf16, nullptr, M, N, partial, counter,
+                                                            (bf16*)dbias_bf16);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
 
 static int fill(EmbParams* p, void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved,
                 const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L, int D) {

@@ -268,6 +268,15 @@ int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_
                            const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L,
                            int D, const void* x_bf16, const void* dx_bf16, const void* hsave_bf16,
                            const float* asave, float lr, cudaStream_t stream);
+/* The elementwise glue of the DIN MLP, fused (the stock worker runs ~29 ATen kernels for it; no counterpart in the
+ * reference, see above).  kdl_din_bce_grad: mean BCE-with-logits of column 0 of z [B, ldz] and its gradient as the
+ * padded [B, 8] bf16 matrix (column 0 = (sigmoid(z) - y) / B).  kdl_relu_bwd_colsum: dh = (h > 0 ? dh : 0) in place
+ * (h may be NULL: no mask) and dbias = column sums of dh, deterministic; workspace zeroed once. */
+int kdl_din_bce_grad(const void* z_bf16, int ldz, const float* label, int B, float* loss, void* dz_bf16,
+                     cudaStream_t stream);
+size_t kdl_relu_bwd_colsum_workspace_bytes(int N);
+int kdl_relu_bwd_colsum(void* dh_bf16, const void* h_bf16, int M, int N, void* dbias_bf16, void* workspace,
+                        size_t workspace_bytes, cudaStream_t stream);
 
 /* ---- N1/N2: fused gradient-bucket all-reduce over NVLink peer memory ---------------------
  * Replaces ncclAllReduce + div_ + cast of torch DDP, for which the reference only injects

@@ -41,6 +41,10 @@ L.register_signatures({
     "kdl_din_scatter_update": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_float, C.c_void_p]),
+    "kdl_din_bce_grad": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "kdl_relu_bwd_colsum_workspace_bytes": (C.c_size_t, [C.c_int]),
+    "kdl_relu_bwd_colsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
+                                      C.c_void_p]),
 })
 
 D = 64
@@ -85,6 +89,9 @@ class DINModel:
             self.arena.w32("w3")[1:].zero_()
             self.arena.p16.copy_(self.arena.p32)
         self.gemm = Gemm(self.dev)
+        # scratch of the fused "ReLU backward + bias gradient" kernel (its counters must start at zero, once)
+        self._cs_ws = torch.zeros(self.lib.kdl_relu_bwd_colsum_workspace_bytes(max(self.dims[1:])), dtype=torch.uint8,
+                                  device=self.dev)
         self.ar = self.gather_done = None
         if self.world > 1:
             from ..parallel.collectives import FusedAllReduce, SymmBarrier
@@ -94,7 +101,8 @@ class DINModel:
         self.saved = None
 
     # ------------------------------------------------------------------ forward / backward
-    def forward(self, user: torch.Tensor, cand: torch.Tensor, hist: torch.Tensor) -> torch.Tensor:
+    def forward_z(self, user: torch.Tensor, cand: torch.Tensor, hist: torch.Tensor) -> torch.Tensor:
+        """Gather + attention + MLP; returns the padded [B, 8] bf16 output (column 0 is the logit)."""
         B = user.numel()
         x = torch.empty(B, 4 * D, dtype=torch.bfloat16, device=self.dev)
         hs = torch.empty(B, self.L, D, dtype=torch.bfloat16, device=self.dev)
@@ -108,26 +116,48 @@ class DINModel:
         h2 = self.gemm.nt(h1, a.w16("w2"), bias=a.w16("b2"), relu=True)
         z = self.gemm.nt(h2, a.w16("w3"), bias=a.w16("b3"))
         self.saved = (user, cand, hist, x, hs, aw, h1, h2)
-        return z[:, 0].float()
+        return z
+
+    def forward(self, user: torch.Tensor, cand: torch.Tensor, hist: torch.Tensor) -> torch.Tensor:
+        return self.forward_z(user, cand, hist)[:, 0].float()
+
+    def loss_and_dz(self, z: torch.Tensor, label: torch.Tensor):
+        """Mean BCE-with-logits of z[:, 0] and its gradient as the padded [B, 8] bf16 matrix — one kernel."""
+        B = z.shape[0]
+        loss = torch.empty(1, dtype=torch.float32, device=self.dev)
+        dz = torch.empty(B, 8, dtype=torch.bfloat16, device=self.dev)
+        L.check(self.lib.kdl_din_bce_grad(z.data_ptr(), z.stride(0), label.data_ptr(), B, loss.data_ptr(), dz.data_ptr(),
+                                          L.stream_ptr()), "kdl_din_bce_grad")
+        L.count(1)
+        return loss[0], dz
+
+    def _relu_bwd_bias(self, dh: torch.Tensor, h: Optional[torch.Tensor], dbias: torch.Tensor) -> torch.Tensor:
+        """dh *= (h > 0) in place (h None: no mask) and dbias = column sums of dh — one kernel."""
+        M, N = dh.shape
+        L.check(self.lib.kdl_relu_bwd_colsum(dh.data_ptr(), L.ptr(h), M, N, dbias.data_ptr(), self._cs_ws.data_ptr(),
+                                             self._cs_ws.numel(), L.stream_ptr()), "kdl_relu_bwd_colsum")
+        L.count(1)
+        return dh
 
     def backward(self, dlogit: torch.Tensor) -> None:
+        """dlogit: fp32 [B] gradient of the loss w.r.t. the logits (public API; the training step hands the
+        padded bf16 matrix straight from the loss kernel to backward_dz)."""
+        dz = torch.zeros(dlogit.numel(), 8, dtype=torch.bfloat16, device=self.dev)
+        dz[:, 0] = dlogit.to(torch.bfloat16)
+        self.backward_dz(dz)
+
+    def backward_dz(self, dz: torch.Tensor) -> None:
         user, cand, hist, x, hs, aw, h1, h2 = self.saved
         self.saved = None
         a, B = self.arena, user.numel()
-        dz = torch.zeros(B, 8, dtype=torch.bfloat16, device=self.dev)
-        dz[:, 0] = dlogit.to(torch.bfloat16)
+        # columns 1..7 of dz are zero, so rows 1..7 of grad(w3) and grad(b3) come out exactly zero by themselves
         self.gemm.tn(dz, h2, out=a.grad("w3"))
-        torch.sum(dz.float(), 0, out=None).to(torch.bfloat16, copy=False)
-        a.grad("b3").copy_(dz.float().sum(0))
-        dh2 = self.gemm.nn(dz, a.w16("w3")) * (h2 > 0)
+        self._relu_bwd_bias(dz, None, a.grad("b3"))
+        dh2 = self._relu_bwd_bias(self.gemm.nn(dz, a.w16("w3")), h2, a.grad("b2"))
         self.gemm.tn(dh2, h1, out=a.grad("w2"))
-        a.grad("b2").copy_(dh2.float().sum(0))
-        dh1 = self.gemm.nn(dh2, a.w16("w2")) * (h1 > 0)
+        dh1 = self._relu_bwd_bias(self.gemm.nn(dh2, a.w16("w2")), h1, a.grad("b1"))
         self.gemm.tn(dh1, x, out=a.grad("w1"))
-        a.grad("b1").copy_(dh1.float().sum(0))
         dx = self.gemm.nn(dh1, a.w16("w1"))
-        a.grad("w3")[1:].zero_()            # padded output columns carry no parameters
-        a.grad("b3")[1:].zero_()
         if self.gather_done is not None:
             # nobody updates a shard while a slower peer may still be gathering this step's rows from it
             self.gather_done()
@@ -168,10 +198,9 @@ class DINModel:
         return loss.clone()
 
     def _step_eager(self, user, cand, hist, label) -> torch.Tensor:
-        logit = self.forward(user, cand, hist)
-        loss = torch.nn.functional.binary_cross_entropy_with_logits(logit, label)
-        dlogit = (torch.sigmoid(logit) - label) / label.numel()
-        self.backward(dlogit)
+        z = self.forward_z(user, cand, hist)
+        loss, dz = self.loss_and_dz(z, label)
+        self.backward_dz(dz)
         a = self.arena
         if self.ar is not None:
             # dense-gradient all-reduce; its entry barrier also orders every rank's table updates

@@ -73,3 +73,59 @@ def test_din_training_reduces_loss(cuda):
         losses.append(float(m.step(user, cand, hist, label)))
     assert all(l == l for l in losses)
     assert sum(losses[-5:]) / 5 < sum(losses[:5]) / 5 - 0.02, (losses[:5], losses[-5:])
+
+
+def test_din_fused_loss_and_bias_gradient_kernels(cuda):
+    """kdl_din_bce_grad == BCE-with-logits + its gradient; kdl_relu_bwd_colsum == mask by (h > 0) + column sums."""
+    from kubedl_b200.models.din import DINModel
+    m = DINModel(vocab=4096, hist_len=8, seed=5)
+    torch.manual_seed(7)
+    B = 4096
+    z = (torch.randn(B, 8, device=cuda) * 3).bfloat16()
+    label = (torch.rand(B, device=cuda) < 0.4).float()
+    loss, dz = m.loss_and_dz(z, label)
+    logit = z[:, 0].float()
+    ref_loss = torch.nn.functional.binary_cross_entropy_with_logits(logit, label)
+    ref_dz = ((torch.sigmoid(logit) - label) / B).bfloat16()
+    assert abs(float(loss) - float(ref_loss)) < 1e-5 * max(1.0, float(ref_loss))
+    torch.testing.assert_close(dz[:, 0].float(), ref_dz.float(), atol=1e-8, rtol=1e-2)
+    assert float(dz[:, 1:].abs().max()) == 0.0
+    for (M, N, relu) in [(4096, 512, True), (4096, 256, True), (4096, 8, False), (1000, 64, True), (77, 136, True)]:
+        dh = torch.randn(M, N, device=cuda).bfloat16()
+        h = torch.randn(M, N, device=cuda).bfloat16()
+        dbias = torch.empty(N, dtype=torch.bfloat16, device=cuda)
+        want = dh.float() * (h > 0) if relu else dh.float()
+        got = m._relu_bwd_bias(dh.clone(), h if relu else None, dbias)
+        assert torch.equal(got.float(), want.bfloat16().float())
+        torch.testing.assert_close(dbias.float(), want.sum(0), atol=0.5, rtol=2e-2)
+        dbias2 = torch.empty_like(dbias)
+        m._relu_bwd_bias(dh.clone(), h if relu else None, dbias2)       # counters reset themselves; deterministic
+        assert torch.equal(dbias, dbias2)
+
+
+def test_din_step_matches_autograd_loss_and_bias_grads(cuda):
+    """The fused training step (loss kernel -> backward_dz) produces the reference loss and bias gradients."""
+    from kubedl_b200.models.din import DINModel, synthetic_batch
+    V, L_, B = 50_000, 20, 512
+    m = DINModel(vocab=V, hist_len=L_, lr=0.0, emb_lr=0.0, seed=1)
+    user, cand, hist, label = synthetic_batch(B, L_, V, cuda, seed=3)
+    a = m.arena
+    mlp = [(a.w32(f"w{i}").clone().requires_grad_(True), a.w32(f"b{i}").clone().requires_grad_(True)) for i in (1, 2, 3)]
+    table = m.shard.clone().requires_grad_(True)
+    logit_ref, _ = _ref_forward(table, mlp, user, cand, hist)
+    loss_ref = torch.nn.functional.binary_cross_entropy_with_logits(logit_ref, label)
+    loss_ref.backward()
+    import os
+    os.environ["KUBEDL_DIN_GRAPH"] = "0"
+    try:
+        loss = m.step(user, cand, hist, label)
+    finally:
+        os.environ.pop("KUBEDL_DIN_GRAPH", None)
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(loss_ref)) < 2e-2
+    for i in (1, 2):
+        g, r = a.grad(f"b{i}").float(), mlp[i - 1][1].grad
+        cos = float((g @ r) / (g.norm() * r.norm() + 1e-12))
+        assert cos > 0.99, (i, cos)
+    assert abs(float(a.grad("b3")[0]) - float(mlp[2][1].grad[0])) < 2e-2 * max(1.0, abs(float(mlp[2][1].grad[0])))
+    assert float(a.grad("w3")[1:].float().abs().max()) == 0.0 and float(a.grad("b3")[1:].float().abs().max()) == 0.0

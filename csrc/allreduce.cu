@@ -199,54 +199,25 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(ArParams p) {
   const uint32_t epoch = *epoch_slot(p, rank);
   block_barrier(p, rank, epoch + 1);
   const int64_t ntiles = (p.ngroups + kThreads - 1) / kThreads;
-  // Four reduce-loads in flight per thread: with one, the whole grid had ~1.2 MB outstanding against a
-  // switch round trip of a few microseconds and the kernel sat at half of the link rate
-  // (profiles/allreduce_8gpu.log: 379 GB/s of 770).
-  constexpr int U = 4;
-  for (int64_t k = blockIdx.x;; k += (int64_t)gridDim.x * U) {
-    if (rank + (int64_t)W * k >= ntiles) break;
-    int64_t g[U];
-    bool ok[U];
+  for (int64_t k = blockIdx.x;; k += gridDim.x) {
+    int64_t t = rank + (int64_t)W * k;
+    if (t >= ntiles) break;
+    int64_t g = t * kThreads + threadIdx.x;
+    if (g < p.ngroups) {
+      float f[8];
+      if (sizeof(T) == 2) {
+        mc_ld_reduce_bf16((const bf16*)p.mc_in + g * 8, f);
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int64_t t = rank + (int64_t)W * (k + (int64_t)u * gridDim.x);
-      g[u] = t * kThreads + threadIdx.x;
-      ok[u] = t < ntiles && g[u] < p.ngroups;
-    }
-    if (sizeof(T) == 2) {
-      uint4 v[U];
+        for (int j = 0; j < 8; ++j) f[j] *= p.scale;
+        mc_st_bf16((bf16*)p.mc_out + g * 8, f);
+      } else {
+        mc_ld_reduce_f32((const float*)p.mc_in + g * 8, f);
+        mc_ld_reduce_f32((const float*)p.mc_in + g * 8 + 4, f + 4);
 #pragma unroll
-      for (int u = 0; u < U; ++u)
-        if (ok[u])
-          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-                       : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w)
-                       : "l"((const bf16*)p.mc_in + g[u] * 8)
-                       : "memory");
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-        if (ok[u]) {
-          float f[8];
-          unpack8(v[u], f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] *= p.scale;
-          mc_st_bf16((bf16*)p.mc_out + g[u] * 8, f);
-        }
-    } else {
-      float f[U][8];
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-        if (ok[u]) {
-          mc_ld_reduce_f32((const float*)p.mc_in + g[u] * 8, f[u]);
-          mc_ld_reduce_f32((const float*)p.mc_in + g[u] * 8 + 4, f[u] + 4);
-        }
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-        if (ok[u]) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[u][j] *= p.scale;
-          mc_st_f32((float*)p.mc_out + g[u] * 8, f[u]);
-          mc_st_f32((float*)p.mc_out + g[u] * 8 + 4, f[u] + 4);
-        }
+        for (int j = 0; j < 8; ++j) f[j] *= p.scale;
+        mc_st_f32((float*)p.mc_out + g * 8, f);
+        mc_st_f32((float*)p.mc_out + g * 8 + 4, f + 4);
+      }
     }
   }
   block_barrier(p, rank, epoch + 2);

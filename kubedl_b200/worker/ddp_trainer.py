@@ -49,7 +49,7 @@ def init_distributed(backend: str = "nccl"):
 class DDPTrainer:
     def __init__(self, batch_per_gpu: int = 256, lr: float = 0.1, momentum: float = 0.9,
                  weight_decay: float = 1e-4, comm: str = "fused", use_graph: bool = True,
-                 use_gemm: Optional[bool] = None, bucket_mb: float = 16.0, image_size: int = 224,
+                 use_gemm: Optional[bool] = None, bucket_mb: float = 64.0, image_size: int = 224,
                  num_classes: int = 1000, seed: int = 0):
         import torch.distributed as dist
         self.rank, self.world, self.local_rank = init_distributed("nccl")
@@ -74,6 +74,12 @@ class DDPTrainer:
             except ImportError:
                 gemm = None
         self.model = ResNet50(self.device, num_classes=num_classes, heap=self.heap, gemm=gemm, seed=seed)
+        # One bucket by default (ResNet-50's 51 MB of bf16 gradients fit in 64 MB): on NVLink the all-reduce takes
+        # ~0.15 ms, and overlapping it with backward costs MORE than it hides, because the persistent GEMM /
+        # convolution kernels own whole SMs — a bucket's blocks delay the next such kernel by their whole
+        # duration, barrier skew included.  Measured (ms/step, 16 MB vs 64 MB buckets): 19.37 / 19.23 at 2 GPUs,
+        # 19.57 / 19.45 at 8 (profiles/r2_bucket_size.md).  KUBEDL_BUCKET_MB restores the overlapped schedule.
+        bucket_mb = float(os.environ.get("KUBEDL_BUCKET_MB", bucket_mb))
         self.model.reducer = BucketReducer(self.model.arena, heap=self.heap, bucket_mb=bucket_mb,
                                            backend="fused" if self.comm == "fused" else "nccl",
                                            world=self.world)

@@ -131,8 +131,10 @@ def test_gpu_gang_admission_is_all_or_nothing():
         assert mgr.api.get("PodGroup", "ns", "b")["spec"]["minResources"] == {"nvidia.com/gpu": 2}
         _wait(lambda: _terminal(mgr, "PyTorchJob", "ns", "a"))
         assert _wait(lambda: _terminal(mgr, "PyTorchJob", "ns", "b"))[-1] == "Succeeded"
-        gpus = {e for e in let.free_gpus}
-        assert gpus == {0, 1, 2}
+        # a GPU returns to the pool when its pod's process is really gone (a still-exiting worker deleted by
+        # cleanPodPolicy All is reaped on the agent's next pass), not at the moment of the delete
+        _wait(lambda: set(let.free_gpus) == {0, 1, 2}, timeout=15)
+        assert not let._terminating and not let._gpu_of
     finally:
         let.stop()
         mgr.stop()

@@ -15,7 +15,8 @@ EventStorageBackend), query.go:25-41; registry: backends/registry/registry.go:26
   "aliyun-sls"   event backend.  The reference ships events to an Aliyun SLS logstore with
                  <=10 retries (sls_logstore.go:45-279, env SLS_ENDPOINT/KEY_ID/KEY_SECRET/PROJECT/
                  LOG_STORE); there is no network here, so the logstore is a local JSONL file
-                 (`SLS_LOG_STORE` = path) with the same retry envelope around the write.
+                 (`SLS_LOG_STORE` = path) with the same retry envelope around the write; with SLS_ENDPOINT
+                 set, `sls.SlsEventBackend` ships them to that logstore over the SLS REST API instead.
 """
 from __future__ import annotations
 
@@ -413,4 +414,8 @@ def register_storage_backends() -> None:
     if REGISTRY.get_object_backend("mysql") is None:
         REGISTRY.add_object_backend(SqlObjectBackend())
     if REGISTRY.get_event_backend("aliyun-sls") is None:
-        REGISTRY.add_event_backend(JsonlEventBackend())
+        if os.environ.get("SLS_ENDPOINT"):
+            from .sls import SlsEventBackend          # a real logstore is configured: speak to it
+            REGISTRY.add_event_backend(SlsEventBackend())
+        else:
+            REGISTRY.add_event_backend(JsonlEventBackend())

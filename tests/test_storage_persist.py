@@ -265,3 +265,157 @@ def test_mysql_driver_path_with_a_fake_driver(monkeypatch):
     monkeypatch.delenv("MYSQL_HOST")
     monkeypatch.setenv("MYSQL_DB_NAME", ":memory:")
     assert B.open_object_db().dialect == "sqlite"
+
+
+# ---------------------------------------------------------------- Aliyun SLS event backend over HTTP
+class _FakeSls:
+    """A stand-in for the three SLS REST calls the backend makes: checks the request signature, decodes the
+    protobuf LogGroup, can inject errors, answers histogram / log queries from what it stored."""
+
+    def __init__(self, key_id="kid", secret="s3cret"):
+        import http.server
+        import threading
+        from kubedl_b200.plugins.storage import sls
+        self.key_id, self.secret, self.logs, self.fail, self.requests = key_id, secret, [], [], []
+        outer = self
+
+        class H(http.server.BaseHTTPRequestHandler):
+            def log_message(self, *a):
+                pass
+
+            def _check(self, body):
+                import hashlib
+                import urllib.parse
+                u = urllib.parse.urlsplit(self.path)
+                q = dict(urllib.parse.parse_qsl(u.query, keep_blank_values=True))
+                hd = {k.lower(): v for k, v in self.headers.items()}       # header names are case-insensitive
+                md5 = hashlib.md5(body).hexdigest().upper() if body else ""
+                assert hd.get("content-md5", "") == md5
+                want = sls.sign(outer.secret, self.command, md5, hd.get("content-type", "") if body else "", hd["date"], hd, u.path, q)
+                assert hd["authorization"] == f"LOG {outer.key_id}:{want}", "bad signature"
+                assert hd["x-log-apiversion"] == "0.6.0" and hd["x-log-bodyrawsize"] == str(len(body))
+                assert hd["host"].startswith("proj.")
+                return u.path, q
+
+            def _reply(self, code, body=b"", headers=None):
+                self.send_response(code)
+                for k, v in (headers or {}).items():
+                    self.send_header(k, v)
+                self.send_header("Content-Length", str(len(body)))
+                self.end_headers()
+                self.wfile.write(body)
+
+            def do_POST(self):
+                body = self.rfile.read(int(self.headers.get("Content-Length", 0)))
+                path, _ = self._check(body)
+                outer.requests.append(("POST", path))
+                if outer.fail:
+                    code = outer.fail.pop(0)
+                    return self._reply(500 if code in sls.SERVER_ERRORS else 403,
+                                       json.dumps({"errorCode": code, "errorMessage": "injected"}).encode())
+                assert path == "/logstores/store/shards/lb"
+                g = sls.decode_log_group(body)
+                for lg in g["logs"]:
+                    outer.logs.append(dict(lg["contents"], __time__=str(lg["time"]), __source__=g["source"]))
+                self._reply(200)
+
+            def do_GET(self):
+                path, q = self._check(b"")
+                outer.requests.append(("GET", q.get("type")))
+                assert path == "/logstores/store"
+                ns, _, name = q["query"].partition(" AND ")
+                hit = [l for l in outer.logs if int(q["from"]) <= int(l["__time__"]) <= int(q["to"])
+                       and l["ObjNamespace"] == ns and name in l["ObjName"]]
+                if q["type"] == "histogram":
+                    return self._reply(200, b"[]", {"x-log-count": str(len(hit)), "x-log-progress": "Complete"})
+                page = hit[int(q["offset"]):int(q["offset"]) + int(q["line"])]
+                assert int(q["line"]) <= 100
+                self._reply(200, json.dumps(page).encode(), {"x-log-count": str(len(page)), "x-log-progress": "Complete"})
+
+        self.srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), H)
+        self.url = f"http://127.0.0.1:{self.srv.server_address[1]}"
+        threading.Thread(target=self.srv.serve_forever, daemon=True).start()
+
+    def stop(self):
+        self.srv.shutdown()
+
+
+def _k8s_event(i, uid, name, ns="ns1", reason="SuccessfulCreatePod"):
+    ts = f"2026-01-01T00:{i // 60:02d}:{i % 60:02d}Z"
+    return {"kind": "Event", "metadata": {"name": f"ev-{i}", "namespace": ns}, "type": "Normal", "reason": reason,
+            "message": f"Created pod: {name}", "count": 1, "firstTimestamp": ts, "lastTimestamp": ts,
+            "involvedObject": {"kind": "Pod", "namespace": ns, "name": name, "uid": uid},
+            "source": {"component": "pytorch-controller", "host": "node-0"}}
+
+
+def test_sls_log_group_protobuf_roundtrip():
+    from kubedl_b200.plugins.storage import sls
+    buf = sls.encode_log_group([(1767225600, [("Name", "ev-1"), ("Message", "héllo wörld " * 30)]),
+                                (5, [("Count", "3")])], topic="", source="ctl/host")
+    g = sls.decode_log_group(buf)
+    assert g["source"] == "ctl/host" and g["topic"] == "" and len(g["logs"]) == 2
+    assert g["logs"][0]["time"] == 1767225600 and g["logs"][0]["contents"]["Message"].startswith("héllo wörld")
+    assert g["logs"][1] == {"time": 5, "contents": {"Count": "3"}}
+    # golden bytes of the smallest group: field 1 {Time=1} , Topic "", Source ""
+    assert sls.encode_log_group([(1, [])]) == bytes([0x0A, 0x02, 0x08, 0x01, 0x1A, 0x00, 0x22, 0x00])
+
+
+def test_sls_event_backend_over_http(monkeypatch):
+    """SaveEvent -> signed PutLogs with the reference's fields and retry envelope; ListEvent -> histogram count,
+    GetLogs in pages of 100, sorted by first timestamp, one entry per involved object
+    (reference pkg/storage/backends/events/aliyun_sls/sls_logstore.go:81-140, 231-257)."""
+    from kubedl_b200.plugins.storage import sls
+    fake = _FakeSls()
+    env = {"SLS_ENDPOINT": fake.url, "SLS_KEY_ID": "kid", "SLS_KEY_SECRET": "s3cret", "SLS_PROJECT": "proj",
+           "SLS_LOG_STORE": "store"}
+    holds = []
+    b = sls.SlsEventBackend(env=env, sleep=holds.append)
+    try:
+        with pytest.raises(ValueError, match="empty sls key secret"):
+            sls.SlsEventBackend(env={**env, "SLS_KEY_SECRET": ""}).initialize()
+        b.initialize()
+        assert b.name() == "aliyun-sls"
+        # retry envelope: a quota error (800 ms hold), a server error (200 ms hold), then success
+        fake.fail = ["WriteQuotaExceed", "ServerBusy"]
+        b.save_event(_k8s_event(0, "uid-0", "job1-worker-0"), "cn-test")
+        assert holds == [0.8, 0.2] and len(fake.logs) == 1
+        first = fake.logs[0]
+        assert [k for k in first if not k.startswith("__")] == ["FirstTimestamp", "LastTimestamp", "Count", "Name", "Kind",
+                                                                "ObjUID", "ObjNamespace", "ObjName", "Type", "Reason",
+                                                                "Message", "Region"]
+        assert first["Region"] == "cn-test" and first["__source__"] == "pytorch-controller/node-0"
+        assert first["__time__"] == "1767225600"
+        # a permanent failure is raised after 10 tries
+        fake.fail = ["Unauthorized"] * 10
+        with pytest.raises(sls.SlsError, match="Unauthorized"):
+            b.save_event(_k8s_event(1, "uid-x", "job1-worker-9"), "")
+        assert sum(1 for r in fake.requests if r[0] == "POST") == 3 + 10
+        # 250 events of job1 (50 pods, 5 events each, written newest first), some of another job and namespace
+        for i in reversed(range(1, 251)):
+            b.save_event(_k8s_event(i, f"uid-{i % 50}", f"job1-worker-{i % 50}"), "")
+        b.save_event(_k8s_event(300, "uid-other", "job2-worker-0"), "")
+        b.save_event(_k8s_event(301, "uid-ns", "job1-worker-0", ns="ns2"), "")
+        fake.requests.clear()
+        got = b.list_event("ns1", "job1", "2026-01-01T00:00:00Z", "2026-01-01T01:00:00Z")
+        assert [r[1] for r in fake.requests] == ["histogram", "log", "log", "log"]          # 251 logs -> 3 pages
+        assert len(got) == 50 and {e.obj_uid for e in got} == {f"uid-{i}" for i in range(50)}
+        assert [e.first_timestamp for e in got] == sorted(e.first_timestamp for e in got)
+        assert got[0].obj_uid == "uid-0" and got[0].region == "cn-test" and got[0].count == 1   # the earliest per object
+        assert b.list_event("ns1", "job1", "2027-01-01T00:00:00Z", "2027-01-02T00:00:00Z") == []
+    finally:
+        fake.stop()
+
+
+def test_registry_picks_the_sls_backend_when_an_endpoint_is_configured(monkeypatch):
+    from kubedl_b200.plugins.storage import backends as B
+    from kubedl_b200.plugins.storage import sls
+    B.REGISTRY.remove_event_backend("aliyun-sls")
+    monkeypatch.setenv("SLS_ENDPOINT", "cn-hangzhou.log.aliyuncs.com")
+    try:
+        B.register_storage_backends()
+        assert isinstance(B.REGISTRY.get_event_backend("aliyun-sls"), sls.SlsEventBackend)
+    finally:
+        B.REGISTRY.remove_event_backend("aliyun-sls")
+        monkeypatch.delenv("SLS_ENDPOINT")
+        B.register_storage_backends()
+    assert isinstance(B.REGISTRY.get_event_backend("aliyun-sls"), B.JsonlEventBackend)

@@ -133,7 +133,8 @@ def timed(fn_step, steps, world):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        # max over ranks of the device-timed milliseconds (a CPU tensor when the process group is gloo)
+        t = torch.tensor([ms], dtype=torch.float64, device="cpu" if dist.get_backend() == "gloo" else "cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
         dist.barrier()

@@ -22,7 +22,9 @@ def main(argv=None) -> int:
     t_start = time.time()
     import torch
     from .ddp_trainer import DDPTrainer
+    t_import = time.time() - t_start
     tr = DDPTrainer(batch_per_gpu=args.batch, comm=args.comm, image_size=args.image_size)
+    t_init = time.time() - t_start
     if args.checkpoint:
         tr.load(args.checkpoint)
     g = torch.Generator().manual_seed(tr.rank)
@@ -40,7 +42,9 @@ def main(argv=None) -> int:
     if args.checkpoint:
         tr.save(args.checkpoint)
     print(json.dumps({"rank": tr.rank, "world": tr.world, "samples_per_s_per_gpu": args.batch * args.steps / dt,
-                      "time_to_first_step_s": t_first, "loss": loss, "comm": tr.comm}), flush=True)
+                      "time_to_first_step_s": t_first, "loss": loss, "comm": tr.comm,
+                      "startup_s": {"import": round(t_import, 3), **tr.startup,
+                                    "first_step": round(t_first - t_init, 3)}}), flush=True)
     if tr.world > 1:
         import torch.distributed as dist
         dist.barrier(); dist.destroy_process_group()

@@ -42,6 +42,10 @@ def init_distributed(backend: str = "nccl"):
             # bound the wait for peers that never come (docs/fault_tolerance.md); unset = torch's default
             import datetime
             kw["timeout"] = datetime.timedelta(seconds=float(os.environ["KUBEDL_RENDEZVOUS_TIMEOUT"]))
+        if backend == "gloo" and os.environ["MASTER_ADDR"] in ("127.0.0.1", "localhost", "::1"):
+            # all pods of a job share the box (the node agent rewrites service names to loopback): skip gloo's
+            # resolution of the container hostname, which costs ~0.5 s and may not resolve at all
+            os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")
         dist.init_process_group(backend=backend, init_method="env://", rank=rank, world_size=world, **kw)
     return rank, world, local_rank
 
@@ -51,19 +55,36 @@ class DDPTrainer:
                  weight_decay: float = 1e-4, comm: str = "fused", use_graph: bool = True,
                  use_gemm: Optional[bool] = None, bucket_mb: float = 64.0, image_size: int = 224,
                  num_classes: int = 1000, seed: int = 0):
+        import time as _time
         import torch.distributed as dist
-        self.rank, self.world, self.local_rank = init_distributed("nccl")
+        _t = _time.time()
+        self.startup = {}          # seconds per start-up phase (time to first step is what a user waits for)
+
+        def _mark(name):
+            nonlocal _t
+            now = _time.time()
+            self.startup[name] = round(now - _t, 3)
+            _t = now
+        # torch.distributed is only plumbing on the fused path (handle exchange, barriers at start-up and
+        # capture): a gloo group joins in a fraction of the time NCCL needs to build a communicator that would
+        # never carry a byte (3.6 s of the 6.2 s to the first step at 2 pods).  NCCL is created when it is the
+        # data path (--comm nccl) or asked for (KUBEDL_PLUMBING_BACKEND=nccl).
+        plumbing = os.environ.get("KUBEDL_PLUMBING_BACKEND", "gloo" if comm == "fused" else "nccl")
+        self.rank, self.world, self.local_rank = init_distributed(plumbing)
+        _mark("rendezvous")
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.batch, self.lr, self.momentum, self.wd = batch_per_gpu, lr, momentum, weight_decay
         self.image_size = image_size
         torch.backends.cudnn.benchmark = True
         L.lib()  # fail loudly now if the kernel library is missing
+        _mark("kernel_lib")
         self.heap = None
         self.comm = comm if self.world > 1 else "none"
         if self.comm == "fused":
             from ..parallel.symm import SymmetricHeap
             # ResNet-50: 25.6 M params -> 51 MB of bf16 gradients (+ flags); 128 MB is ample
             self.heap = SymmetricHeap(128 << 20)
+        _mark("symmetric_heap")
         gemm = None
         if use_gemm is None:
             use_gemm = os.environ.get("KUBEDL_GEMM", "1") != "0"
@@ -86,9 +107,12 @@ class DDPTrainer:
         if self.world > 1:
             # identical initial weights on every rank (same seed) — verify cheaply
             chk = self.model.arena.p32[:1024].sum().reshape(1).clone()
+            if dist.get_backend() == "gloo":
+                chk = chk.cpu()
             lst = [torch.empty_like(chk) for _ in range(self.world)]
             dist.all_gather(lst, chk)
             assert all(torch.equal(lst[0], t) for t in lst), "ranks disagree on initial weights"
+        _mark("model")
         S = image_size
         self.images = [torch.zeros(batch_per_gpu, S, S, 3, dtype=torch.uint8, device=self.device)
                        for _ in range(2)]

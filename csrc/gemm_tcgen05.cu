@@ -7,7 +7,8 @@
 //   warp 1   MMA issuer     one thread issues tcgen05.mma (M=128, N=BN, K=16) from smem
 //                           descriptors into a TMEM accumulator; tcgen05.commit frees the stage
 //   warp 2   TMEM allocator tcgen05.alloc / dealloc (2 accumulator stages of BN columns)
-//   warp 4-7 epilogue       tcgen05.ld TMEM -> registers -> bias/addend/ReLU -> bf16 -> global
+//   warp 4.. epilogue       4 or 8 warps: tcgen05.ld TMEM -> registers -> bias / addend (a TMA box in the staging
+//                           buffer) / ReLU / BN column statistics -> bf16 -> swizzled smem -> TMA store
 // so the epilogue of tile i overlaps the loads and MMAs of tile i+1.  Operands may be K-major
 // or MN-major (the transposes needed by dgrad / wgrad are done by the UMMA descriptors, not by
 // copies): nt = fwd (x W^T), nn = dgrad (dy W), tn = wgrad (dy^T x).  wgrad has a tiny output
@@ -33,7 +34,7 @@ constexpr int BM = 128;       // UMMA M (cta_group::1)
 // latencies behind, so tiles with little K per output element (K <= 256..512: the memory-bound 1x1
 // convolutions, and everything with a fused addend or fused statistics) are EPILOGUE-bound with 4 warps;
 // 8 warps cost 32 KB of staging, i.e. one pipeline stage, which only the deep-K compute-bound shapes miss
-// (profiles/gemm_vs_cublas_shapes.log, profiles/r2_epilogue_warps.md).  The host picks per launch.
+// (profiles/gemm_vs_cublas_shapes.log, profiles/r2_addend_epilogue.md).  The host picks per launch.
 constexpr int kEpiWarp0 = 4;
 constexpr int gemm_threads(int epi) { return 128 + 32 * epi; }
 

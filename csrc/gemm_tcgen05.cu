@@ -973,7 +973,14 @@ static int pick_epi(int k_per_tile, bool two_cta) {
     env = e ? atoi(e) : 0;
   }
   if (env == 4 || env == 8) return env;
-  return k_per_tile <= (two_cta ? 512 : 256) ? 8 : 4;
+  static int k1 = -1, k2 = -1;       // thresholds (K per tile), overridable for sweeps
+  if (k1 < 0) {
+    const char* a = getenv("KDL_GEMM_EPI8_MAXK");
+    const char* b = getenv("KDL_GEMM_EPI8_MAXK_2CTA");
+    k1 = a ? atoi(a) : 256;
+    k2 = b ? atoi(b) : 512;
+  }
+  return k_per_tile <= (two_cta ? k2 : k1) ? 8 : 4;
 }
 
 template <int A_MN, int B_MN, int BN, int STAGES, int EPI>

@@ -13,6 +13,7 @@
 // opaque worker images (reference example/pytorch/pytorch_job_mnist_mpi.yaml:15).
 #include "common.cuh"
 #include "../include/kubedl_b200.h"
+#include <stdlib.h>
 
 namespace kdl {
 
@@ -302,7 +303,11 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
                                                        const bf16* __restrict__ res,
                                                        bf16* __restrict__ y, int64_t nvec, int cvec,
                                                        int C, const float* __restrict__ coef,
-                                                       int relu, uint8_t* __restrict__ mask = nullptr) {
+                                                       int relu, uint8_t* __restrict__ mask = nullptr,
+                                                       int evict_first = 0) {
+  // x and the residual are not read again before the backward pass: let them leave L2 first, so that y (read by
+  // the very next kernel) stays
+  const uint64_t pol = l2_policy(evict_first != 0);
   pdl_wait();
   pdl_launch();
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
@@ -323,8 +328,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
     for (int u = 0; u < U; ++u) {
       int64_t k = i + u * T;
       if (k < nvec) {
-        vx[u] = ld_stream(x + k * 8);
-        if (res) vr[u] = ld_stream(res + k * 8);
+        vx[u] = ld_stream_hint(x + k * 8, pol);
+        if (res) vr[u] = ld_stream_hint(res + k * 8, pol);
       }
     }
 #pragma unroll
@@ -376,7 +381,8 @@ __global__ void __launch_bounds__(256, 3) bn_dx_kernel(const bf16* dy,
                                                        const uint8_t* __restrict__ mask,
                                                        const bf16* __restrict__ pool_dp,
                                                        const uint8_t* __restrict__ pool_idx,
-                                                       int pool_H, int pool_W) {
+                                                       int pool_H, int pool_W, int evict_first) {
+  const uint64_t pol = l2_policy(evict_first != 0);     // dy and x: last use (the reduction read them just before)
   pdl_wait();
   pdl_launch();
   const int64_t T = (int64_t)gridDim.x * blockDim.x;
@@ -400,8 +406,8 @@ __global__ void __launch_bounds__(256, 3) bn_dx_kernel(const bf16* dy,
       int64_t k = i + u * T;
       if (k < nvec) {
         if (POOL) vd[u] = pool_grad_gather(pool_dp, pool_idx, k / cvec, (int)(k % cvec) * 8, pool_H, pool_W, C);
-        else vd[u] = ld_plain(dy + k * 8);  // may alias dres: plain (coherent) load
-        vx[u] = ld_stream(x + k * 8);
+        else vd[u] = ld_plain_hint(dy + k * 8, pol);  // may alias dres: plain (coherent) load
+        vx[u] = ld_stream_hint(x + k * 8, pol);
         if (RELU == 1) vy[u] = ld_stream(y + k * 8);
         else if (RELU == 3) vy[u].x = mask[k];
       }
@@ -515,6 +521,16 @@ static int apply_grid(int64_t nvec) {
   return (int)g;
 }
 
+// KDL_BN_EVICT_FIRST=0: default L2 priority for the last-use reads of bn_apply / bn_dx (A/B runs)
+static int bn_evict_first() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("KDL_BN_EVICT_FIRST");
+    v = e ? atoi(e) : 1;
+  }
+  return v;
+}
+
 static int bn_fwd_impl(const void* x, const void* res, void* y, int64_t M, int C, const float* gamma,
                        const float* beta, float* running_mean, float* running_var, float eps, float momentum,
                        int relu, float* save_mean_rstd, uint8_t* relu_mask, void* workspace,
@@ -539,10 +555,10 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int64_t M, int C
   bool fixed = (256 % cvec) == 0;
   if (fixed)
     KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<true>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
-                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask, bn_evict_first()));
   else
     KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<false>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
-                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask, bn_evict_first()));
   return KDL_OK;
 }
 
@@ -574,7 +590,7 @@ static cudaError_t launch_bn_dx(int relu, bool pool, dim3 g, cudaStream_t stream
                                 int pool_W) {
 #define KDL_BN_DX(R, P)                                                                                              \
   return kdl_launch_pdl(bn_dx_kernel<FIXED_CG, R, P>, g, dim3(256), 0, stream, dy, x, y, dx, dres, nvec, cvec, C, coef, \
-                        mask, pool_dp, pool_idx, pool_H, pool_W)
+                        mask, pool_dp, pool_idx, pool_H, pool_W, bn_evict_first())
   if (pool) { KDL_BN_DX(2, true); }
   if (relu == 0) { KDL_BN_DX(0, false); }
   if (relu == 1) { KDL_BN_DX(1, false); }
@@ -758,10 +774,10 @@ static int bn_fwd_from_stats_impl(const void* x, const void* res, void* y, int64
   int g = apply_grid(nvec);
   if ((256 % cvec) == 0)
     KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<true>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
-                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask, bn_evict_first()));
   else
     KDL_CUDA(kdl_launch_pdl(bn_apply_kernel<false>, dim3(g), dim3(256), 0, stream, (const bf16*)x, (const bf16*)res,
-                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask));
+                            (bf16*)y, nvec, cvec, C, (const float*)coef, relu, relu_mask, bn_evict_first()));
   return KDL_OK;
 }
 

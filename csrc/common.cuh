@@ -65,6 +65,32 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return u;
 }
 
+// L2 replacement hints.  Every activation is written by one kernel and read by the next; a kernel's own streaming reads
+// of data that is dead afterwards should not push the freshly written output of its producer (or its own output) out of
+// the 126 MB L2.  l2_policy(true) = evict_first (this line may go first), l2_policy(false) = the default priority.
+__device__ __forceinline__ uint64_t l2_policy(bool evict_first) {
+  uint64_t pol;
+  if (evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+// 128-bit loads with an L2 policy: read-only / no L1 allocation (data read once), and the coherent variant
+__device__ __forceinline__ uint4 ld_stream_hint(const void* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_plain_hint(const void* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return r;
+}
+
 // Streaming 128-bit load that does not allocate in L1 (data read once).
 __device__ __forceinline__ uint4 ld_stream(const void* p) {
   uint4 r;

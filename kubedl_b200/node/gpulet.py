@@ -4,8 +4,10 @@ The reference stops at "create Pod and Service objects"; a real cluster's schedu
 kube-dns do the rest (SURVEY.md §1 boundaries).  On a single box gpulet plays those parts:
 
   * scheduling: every pod gets at most one GPU (`nvidia.com/gpu` limit or the job's gang), bound
-    by index through KUBEDL_GPU_INDEX / LOCAL_RANK — all 8 devices stay visible so CUDA IPC and
-    NVLS multicast work across pods.  Gang-scheduled pods
+    by index through KUBEDL_GPU_INDEX / LOCAL_RANK — all 8 devices stay visible by default; with
+    KUBEDL_GPULET_ISOLATE_GPUS=1 the pod's GPU is its only visible device (CUDA_VISIBLE_DEVICES): the
+    symmetric heap and the NVLS multicast object are shared between pods as POSIX fds of cuMem
+    allocations, which need no visible peer devices.  Gang-scheduled pods
     (`schedulerName: gpu-gang` / `kube-batch`) are admitted all-or-nothing per PodGroup.
   * container runtime: an image name maps to a local command (`ImageRegistry`); otherwise the
     container's own command/args run.  `$(VAR)` references are expanded like the kubelet does;
@@ -165,6 +167,10 @@ class Gpulet:
         self.node_name = node_name
         self.log_dir = log_dir
         self.default_gpu_per_pod = default_gpu_per_pod
+        # KUBEDL_GPULET_ISOLATE_GPUS=1: a GPU pod sees only its own device, as under the NVIDIA device plugin on a
+        # real cluster.  Validated (all three example jobs at 2 and 8 GPUs); off by default because it buys
+        # nothing on this box: time to first step stayed 16 s at 8 pods (profiles/r2_examples_8gpu_isolated.log).
+        self.isolate_gpus = os.environ.get("KUBEDL_GPULET_ISOLATE_GPUS", "0") == "1"
         os.makedirs(log_dir, exist_ok=True)
         self._lock = threading.RLock()
         self._procs: Dict[Tuple[str, str], _Proc] = {}
@@ -544,6 +550,13 @@ class Gpulet:
         if gpu is not None:
             env["KUBEDL_GPU_INDEX"] = str(gpu)
             env["LOCAL_RANK"] = str(gpu)
+            if self.isolate_gpus and not any(e.get("name") == "CUDA_VISIBLE_DEVICES" for e in container.get("env") or []):
+                # the pod sees ONLY its GPU (workers take device LOCAL_RANK % device_count = 0).  The symmetric
+                # heap needs no visible peers: memory is shared as POSIX fds of cuMem allocations and mapped for
+                # the local device, the NVLS multicast object likewise (validated with the fused all-reduce check).
+                mine = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d.strip()]
+                # the agent's own mask, if any, names the devices its indices refer to
+                env["CUDA_VISIBLE_DEVICES"] = mine[gpu].strip() if gpu < len(mine) else str(gpu)
         return env
 
     # ------------------------------------------------------------------ launch / status

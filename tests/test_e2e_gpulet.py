@@ -463,3 +463,26 @@ def test_crash_loop_backoff_paces_in_place_restarts(tmp_path):
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_gpu_pods_can_be_given_only_their_own_device(monkeypatch):
+    """KUBEDL_GPULET_ISOLATE_GPUS=1: a GPU pod's environment makes its GPU the only visible CUDA device (what the
+    NVIDIA device plugin does on a real cluster); a mask the user set on the container wins, the agent's own
+    mask is honoured; by default every pod sees every device."""
+    mgr = Manager()
+    ctr = {"name": "c", "image": "x", "command": ["true"]}
+    pod = {"kind": "Pod", "metadata": {"name": "p", "namespace": "d", "labels": {}}, "spec": {"containers": [ctr]}}
+    monkeypatch.delenv("CUDA_VISIBLE_DEVICES", raising=False)
+    monkeypatch.delenv("KUBEDL_GPULET_ISOLATE_GPUS", raising=False)
+    let0 = Gpulet(mgr.api, num_gpus=8, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}")
+    env = let0.build_env(pod, ctr, 5)
+    assert "CUDA_VISIBLE_DEVICES" not in env and env["KUBEDL_GPU_INDEX"] == "5" and env["LOCAL_RANK"] == "5"
+    monkeypatch.setenv("KUBEDL_GPULET_ISOLATE_GPUS", "1")
+    let = Gpulet(mgr.api, num_gpus=8, log_dir=f"/tmp/kubedl-b200/test-pods-{os.getpid()}")
+    env = let.build_env(pod, ctr, 5)
+    assert env["CUDA_VISIBLE_DEVICES"] == "5" and env["KUBEDL_GPU_INDEX"] == "5" and env["LOCAL_RANK"] == "5"
+    assert "CUDA_VISIBLE_DEVICES" not in let.build_env(pod, ctr, None)              # a pod without a GPU
+    user = dict(ctr, env=[{"name": "CUDA_VISIBLE_DEVICES", "value": "0,1"}])
+    assert let.build_env(pod, user, 5)["CUDA_VISIBLE_DEVICES"] == "0,1"
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "4,5,6,7")                            # the agent itself is masked
+    assert let.build_env(pod, ctr, 2)["CUDA_VISIBLE_DEVICES"] == "6"

@@ -405,9 +405,140 @@ __global__ void __launch_bounds__(256) relu_bwd_colsum_kernel(bf16* __restrict__
   if (threadIdx.x == 0) counter[blockIdx.x] = 0u;
 }
 
+// ---- generic dispatch / combine over the sharded table (any row width) --------------------------------------------
+// The two halves of an embedding all-to-all without the DIN model around them: emb_gather pulls n rows by id from
+// their owners (out[i, :] = E[ids[i], :], fp32 or bf16 output), emb_scatter_add pushes scale * grad[i, :] onto row
+// ids[i] with vectorised red.global.add over NVLink (duplicates coalesce in the atomics).  ids < 0 are padding:
+// gather writes zeros, scatter skips.  A warp takes four rows at a time, 16 bytes per lane and row chunk.
+struct GenEmbParams {
+  float* shard[KDL_MAX_WORLD];
+  int world, interleaved, wshift;
+  int64_t rows_per_rank;
+  const int64_t* ids;
+  int64_t n;
+  int D;                 // floats per row, multiple of 4
+  void* out;             // gather: [n, D] fp32 or bf16
+  int out_bf16;
+  const void* grad;      // scatter: [n, D] fp32 or bf16
+  int grad_bf16;
+  float scale;
+};
+
+__device__ __forceinline__ float* gen_row_ptr(const GenEmbParams& p, int64_t id) {
+  if (p.interleaved) {
+    const uint32_t i = (uint32_t)id;
+    uint32_t owner, local;
+    if (p.wshift >= 0) { owner = i & (uint32_t)(p.world - 1); local = i >> p.wshift; }
+    else { local = i / (uint32_t)p.world; owner = i - local * (uint32_t)p.world; }
+    return p.shard[owner] + (size_t)local * p.D;
+  }
+  const int owner = (int)(id / p.rows_per_rank);
+  return p.shard[owner] + (size_t)(id - (int64_t)owner * p.rows_per_rank) * p.D;
+}
+
+__global__ void __launch_bounds__(256) emb_gather_kernel(GenEmbParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const int chunks = p.D >> 2;
+  constexpr int R = 4;
+  for (int64_t r0 = warp * R; r0 < p.n; r0 += nwarps * R) {
+    const float* src[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      const int64_t id = r0 + k < p.n ? p.ids[r0 + k] : -1;
+      src[k] = id >= 0 ? gen_row_ptr(p, id) : nullptr;
+    }
+    for (int c0 = 0; c0 < chunks; c0 += 32) {
+      const int c = c0 + lane;
+      float4 v[R];
+#pragma unroll
+      for (int k = 0; k < R; ++k)          // all loads of the four rows in flight before any is used
+        v[k] = (src[k] != nullptr && c < chunks) ? ld_row4(src[k], c) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < R; ++k) {
+        if (r0 + k >= p.n || c >= chunks) continue;
+        const size_t o = (size_t)(r0 + k) * p.D + 4 * c;
+        if (p.out_bf16) st_bf16x4(reinterpret_cast<bf16*>(p.out) + o, v[k].x, v[k].y, v[k].z, v[k].w);
+        else *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v[k];
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) emb_scatter_add_kernel(GenEmbParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const int chunks = p.D >> 2;
+  for (int64_t r = warp; r < p.n; r += nwarps) {
+    const int64_t id = p.ids[r];
+    if (id < 0) continue;
+    float* dst = gen_row_ptr(p, id);
+    for (int c = lane; c < chunks; c += 32) {
+      const size_t o = (size_t)r * p.D + 4 * c;
+      float4 g;
+      if (p.grad_bf16) g = ld_bf16x4(reinterpret_cast<const bf16*>(p.grad) + o);
+      else g = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.grad) + o);
+      red_add4(dst, c, p.scale * g.x, p.scale * g.y, p.scale * g.z, p.scale * g.w);
+    }
+  }
+}
+
 }  // namespace kdl
 
 using namespace kdl;
+
+static int gen_fill(GenEmbParams* p, void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved, int D,
+                    const int64_t* ids, int64_t n) {
+  if (world < 1 || world > KDL_MAX_WORLD || rows_per_rank < 1 || D < 4 || (D & 3) || n < 0) {
+    kdl_set_error("embedding: bad arguments world=%d rows_per_rank=%lld D=%d n=%lld (D must be a multiple of 4)", world,
+                  (long long)rows_per_rank, D, (long long)n);
+    return KDL_ERR_ARG;
+  }
+  if (interleaved && rows_per_rank * world > (int64_t)1 << 32) {
+    kdl_set_error("embedding: interleaved placement supports vocabularies below 2^32 rows");
+    return KDL_ERR_UNSUPPORTED;
+  }
+  for (int r = 0; r < world; ++r) p->shard[r] = (float*)shard_ptrs[r];
+  p->world = world; p->interleaved = interleaved ? 1 : 0; p->rows_per_rank = rows_per_rank;
+  p->wshift = -1;
+  for (int b = 0; b < 8; ++b)
+    if ((1 << b) == world) p->wshift = b;
+  p->ids = ids; p->n = n; p->D = D;
+  return KDL_OK;
+}
+
+static int gen_grid(int64_t n, int rows_per_warp) {
+  int64_t g = (n + 8 * rows_per_warp - 1) / (8 * rows_per_warp);
+  if (g > 148 * 8) g = 148 * 8;
+  return (int)(g < 1 ? 1 : g);
+}
+
+extern "C" int kdl_emb_gather(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved, int D,
+                              const int64_t* ids, int64_t n, void* out, int out_bf16, cudaStream_t stream) {
+  GenEmbParams p = {};
+  int rc = gen_fill(&p, shard_ptrs, world, rows_per_rank, interleaved, D, ids, n);
+  if (rc) return rc;
+  if (n == 0) return KDL_OK;
+  p.out = out; p.out_bf16 = out_bf16;
+  emb_gather_kernel<<<gen_grid(n, 4), 256, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
+
+extern "C" int kdl_emb_scatter_add(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved, int D,
+                                   const int64_t* ids, int64_t n, const void* grad, int grad_bf16, float scale,
+                                   cudaStream_t stream) {
+  GenEmbParams p = {};
+  int rc = gen_fill(&p, shard_ptrs, world, rows_per_rank, interleaved, D, ids, n);
+  if (rc) return rc;
+  if (n == 0) return KDL_OK;
+  p.grad = grad; p.grad_bf16 = grad_bf16; p.scale = scale;
+  emb_scatter_add_kernel<<<gen_grid(n, 1), 256, 0, stream>>>(p);
+  KDL_CHECK_LAUNCH();
+  return KDL_OK;
+}
 
 extern "C" int kdl_din_bce_grad(const void* z_bf16, int ldz, const float* label, int B, float* loss, void* dz_bf16,
                                 cudaStream_t stream) {

@@ -268,6 +268,18 @@ int kdl_din_scatter_update(void* const* shard_ptrs, int world, int64_t rows_per_
                            const int64_t* user, const int64_t* cand, const int64_t* hist, int B, int L,
                            int D, const void* x_bf16, const void* dx_bf16, const void* hsave_bf16,
                            const float* asave, float lr, cudaStream_t stream);
+/* Generic dispatch / combine over a sharded fp32 table of any row width D (multiple of 4): the two halves of an
+ * embedding all-to-all as single kernels over NVLink peer memory.  kdl_emb_gather: out[i, :] = E[ids[i], :] (fp32 or
+ * bf16 output; ids < 0 give zero rows).  kdl_emb_scatter_add: E[ids[i], :] += scale * grad[i, :] with vectorised
+ * red.global.add (duplicates coalesce; ids < 0 are skipped) — with scale = -lr it is sparse SGD on the owner.
+ * The stock worker does all_to_all_single(ids) + index_select + all_to_all_single(vectors), and the reverse with
+ * index_add_; the reference only wires TASK_NAME / TASK_INDEX (reference controllers/xdl/xdljob_controller.go:191-217). */
+int kdl_emb_gather(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved, int D,
+                   const int64_t* ids, int64_t n, void* out, int out_bf16, cudaStream_t stream);
+int kdl_emb_scatter_add(void* const* shard_ptrs, int world, int64_t rows_per_rank, int interleaved, int D,
+                        const int64_t* ids, int64_t n, const void* grad, int grad_bf16, float scale,
+                        cudaStream_t stream);
+
 /* The elementwise glue of the DIN MLP, fused (the stock worker runs ~29 ATen kernels for it; no counterpart in the
  * reference, see above).  kdl_din_bce_grad: mean BCE-with-logits of column 0 of z [B, ldz] and its gradient as the
  * padded [B, 8] bf16 matrix (column 0 = (sigmoid(z) - y) / B).  kdl_relu_bwd_colsum: dh = (h > 0 ? dh : 0) in place

@@ -92,6 +92,32 @@ assert all(x == x for x in losses) and losses[-1] < losses[0] and res["din"]["st
 chk = [torch.empty_like(m.arena.p32) for _ in range(world)]
 dist.all_gather(chk, m.arena.p32)
 assert all(torch.equal(chk[0], c_) for c_ in chk)
+# ---- generic sharded embedding (dispatch / combine kernels): lookups and updates vs the gathered full table
+from kubedl_b200.parallel.embedding import ShardedEmbedding
+Ve, De = 40_000, 128
+emb = ShardedEmbedding(Ve, De, seed=4)
+def full(e):
+    parts = [torch.empty_like(e.shard) for _ in range(world)]
+    dist.all_gather(parts, e.shard.contiguous())
+    return (torch.stack(parts, 1).reshape(-1, De) if e.interleaved else torch.cat(parts, 0))[:Ve]
+t0 = full(emb)
+ge = torch.Generator(device=dev).manual_seed(77 + rank)
+ids_e = (torch.rand(6000, device=dev, generator=ge).pow(3) * Ve).long().clamp_(0, Ve - 1)      # skewed, many duplicates
+vec = emb.lookup(ids_e, dtype=torch.float32)
+assert torch.equal(vec, t0[ids_e]), "gather mismatch"
+emb.barrier()
+ge_ = torch.randn(6000, De, device=dev, generator=ge)
+emb.apply_grad(ids_e, ge_, lr=0.25)
+emb.barrier()
+torch.cuda.synchronize(); dist.barrier()
+all_ids = [torch.empty_like(ids_e) for _ in range(world)]; dist.all_gather(all_ids, ids_e)
+all_g = [torch.empty_like(ge_) for _ in range(world)]; dist.all_gather(all_g, ge_)
+want_e = t0.clone()
+for i_, g_ in zip(all_ids, all_g):
+    want_e.index_add_(0, i_, g_, alpha=-0.25)
+err_e = float((full(emb) - want_e).abs().max())
+res["sharded_embedding"] = {"rows": Ve, "dim": De, "sharding": emb.sharding, "update_max_err": err_e}
+assert err_e < 5e-3, err_e
 if rank == 0:
     print(json.dumps(res), flush=True)
 dist.barrier(); dist.destroy_process_group()

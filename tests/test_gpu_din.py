@@ -129,3 +129,30 @@ def test_din_step_matches_autograd_loss_and_bias_grads(cuda):
         assert cos > 0.99, (i, cos)
     assert abs(float(a.grad("b3")[0]) - float(mlp[2][1].grad[0])) < 2e-2 * max(1.0, abs(float(mlp[2][1].grad[0])))
     assert float(a.grad("w3")[1:].float().abs().max()) == 0.0 and float(a.grad("b3")[1:].float().abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("dim,dtype", [(64, torch.bfloat16), (128, torch.float32), (36, torch.float32), (256, torch.bfloat16)])
+def test_sharded_embedding_gather_and_scatter_add(cuda, dim, dtype):
+    """Generic dispatch / combine (kdl_emb_gather / kdl_emb_scatter_add) vs index_select / index_add_."""
+    from kubedl_b200.parallel.embedding import ShardedEmbedding
+    torch.manual_seed(9)
+    V, n = 5000, 3001
+    emb = ShardedEmbedding(V, dim, seed=3)
+    table0 = emb.shard[:V].clone()
+    ids = torch.randint(0, V, (n,), device=cuda)
+    ids[::17] = -1                                     # padding
+    ids[5:40] = 7                                      # duplicates
+    out = emb.lookup(ids.view(-1, 1), dtype=dtype)
+    assert out.shape == (n, 1, dim)
+    ref = table0[ids.clamp(min=0)] * (ids >= 0)[:, None]
+    torch.testing.assert_close(out.view(n, dim).float(), ref.to(dtype).float(), atol=0, rtol=0)
+    grad = torch.randn(n, dim, device=cuda).to(dtype)
+    emb.apply_grad(ids, grad, lr=0.5)
+    want = table0.clone()
+    valid = ids >= 0
+    want.index_add_(0, ids[valid], grad[valid].float(), alpha=-0.5)
+    torch.testing.assert_close(emb.shard[:V], want, atol=2e-4, rtol=1e-4)
+    sd = emb.state_dict()
+    emb.shard.zero_()
+    emb.load_state_dict(sd)
+    torch.testing.assert_close(emb.shard[:V], want, atol=2e-4, rtol=1e-4)

@@ -187,6 +187,7 @@ class Gpulet:
         # 10 s doubling to 5 min, forgotten after 10 min of clean running
         self.restart_backoff = (float(os.environ.get("KUBEDL_GPULET_RESTART_BACKOFF_SECONDS", "10")), 300.0, 600.0)
         self._stop = threading.Event()
+        self._wake = threading.Event()          # set by the watches; the loop otherwise ticks every 10 ms (reaping)
         self._threads: List[threading.Thread] = []
         self._unwatch: List[Callable[[], None]] = []
         self._pool = ThreadPoolExecutor(max_workers=16, thread_name_prefix="gpulet-pod")
@@ -235,6 +236,7 @@ class Gpulet:
 
     def stop(self) -> None:
         self._stop.set()
+        self._wake.set()
         for u in self._unwatch:
             u()
         with self._lock:
@@ -246,7 +248,8 @@ class Gpulet:
             self.zygote.stop()
 
     def _kick(self) -> None:
-        pass  # the loop polls; the hook exists so watches wake it in future revisions
+        """Wake the agent's loop now (a pod or PodGroup arrived): admission does not wait for the next poll."""
+        self._wake.set()
 
     def _on_pod(self, ev: str, pod: dict, old: Optional[dict]) -> None:
         key = (c.namespace_of(pod), c.name_of(pod))
@@ -276,6 +279,7 @@ class Gpulet:
                     self._forget_job(key)
             elif ev == ADDED and not (pod.get("status") or {}).get("phase"):
                 self._pending[key] = pod
+                self._wake.set()
         if ev == DELETED and p is not None:
             self._terminate(p, pod)
 
@@ -336,7 +340,8 @@ class Gpulet:
                 self._heartbeat()
             except Exception as e:  # keep the node alive
                 log.error("gpulet loop error: %s", e)
-            time.sleep(0.01)
+            self._wake.wait(0.01)
+            self._wake.clear()
 
     # ------------------------------------------------------------------ metrics
     def _register_metrics(self, registry) -> None:

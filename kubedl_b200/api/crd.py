@@ -153,14 +153,31 @@ def all_in_one(config_dir: str = "config") -> str:
     return parts[0] + "---\n".join(yaml.safe_dump(d, sort_keys=False) for d in docs)
 
 
+_VALIDATORS: dict = {}
+
+
+def _validator(kind: str):
+    """One compiled validator per kind.  `jsonschema.validate(doc, schema)` re-generates nothing here but re-checks
+    the schema against its metaschema on EVERY call, which cost ~10 ms per job create — more than the reconcile
+    that follows; the schema of a kind never changes inside a process."""
+    v = _VALIDATORS.get(kind)
+    if v is None:
+        import jsonschema
+        schema = crd_for(SCHEME.info(kind))["spec"]["validation"]["openAPIV3Schema"]
+        cls = jsonschema.validators.validator_for(schema)
+        cls.check_schema(schema)
+        v = _VALIDATORS[kind] = cls(schema)
+    return v
+
+
 def validate(obj: dict) -> None:
     """Minimal structural validation of a job against the CRD schema (what the API server's
     OpenAPI validation would reject)."""
     import jsonschema
-    info = SCHEME.info(obj.get("kind", ""))
-    schema = crd_for(info)["spec"]["validation"]["openAPIV3Schema"]
     doc = {k: v for k, v in obj.items() if k != "status"} if "status" not in obj else obj
-    jsonschema.validate(doc, schema)
+    err = jsonschema.exceptions.best_match(_validator(obj.get("kind", "")).iter_errors(doc))
+    if err is not None:
+        raise err
 
 
 if __name__ == "__main__":

@@ -23,7 +23,7 @@ from __future__ import annotations
 
 import base64
 import collections
-import copy
+import copy  # noqa: F401
 import http.client
 import json
 import os
@@ -40,6 +40,7 @@ from typing import Callable, Dict, List, Optional, Tuple
 import yaml
 
 from ..api import common as c
+from ..api.common import deepcopy as _copy
 from ..api.kinds import SCHEME
 from ..utils.logger import logger
 from . import store as st
@@ -281,7 +282,7 @@ class _Reflector:
         with self.lock:
             if replay:
                 for o in list(self.cache.values()):
-                    handler(ADDED, copy.deepcopy(o), None)
+                    handler(ADDED, _copy(o), None)
             self.handlers.append(handler)
 
         def stop():
@@ -306,7 +307,7 @@ class _Reflector:
                 self.cache[key] = obj
             for h in list(self.handlers):
                 try:
-                    h(ev, copy.deepcopy(obj), copy.deepcopy(old) if old is not None else None)
+                    h(ev, _copy(obj), _copy(old) if old is not None else None)
                 except Exception as e:          # a handler must not take the reflector down
                     log.error("watch handler for %s failed: %r", self.kind, e)
 
@@ -484,7 +485,7 @@ class KubeAPIServer:
         kind = obj.get("kind")
         if not kind or not c.name_of(obj):
             raise st.Invalid("object needs kind and metadata.name")
-        o = copy.deepcopy(obj)
+        o = _copy(obj)
         o.setdefault("apiVersion", self.scheme.api_version(kind) if self.scheme.knows(kind) else "v1")
         o.setdefault("metadata", {})["namespace"] = c.namespace_of(obj)
         return o
@@ -583,7 +584,7 @@ class KubeAPIServer:
             return self.create(obj)
         except st.AlreadyExists:
             cur = self.get(obj["kind"], c.namespace_of(obj), c.name_of(obj))
-            merged = copy.deepcopy(obj)
+            merged = _copy(obj)
             merged.setdefault("metadata", {})["resourceVersion"] = cur["metadata"].get("resourceVersion")
             return self.update(merged)
 

@@ -10,12 +10,13 @@ Events.  Objects are Kubernetes wire-format dicts.
 from __future__ import annotations
 
 import collections
-import copy
+import copy  # noqa: F401
 import threading
 import uuid
 from typing import Callable, Deque, Dict, List, Optional, Tuple
 
 from ..api import common as c
+from ..api.common import deepcopy as _copy
 from ..api.kinds import SCHEME
 
 ADDED, MODIFIED, DELETED = "ADDED", "MODIFIED", "DELETED"
@@ -120,7 +121,7 @@ class APIServer:
         with self._lock:
             if since < self._history_floor:
                 raise Gone(f"too old resource version: {since} ({self._history_floor})")
-            return [(ev, copy.deepcopy(o)) for r, k, ev, o in self._history if k == kind and r > since]
+            return [(ev, _copy(o)) for r, k, ev, o in self._history if k == kind and r > since]
 
     def _maybe_fail(self, verb: str, kind: str) -> None:
         err = self.fail_next.pop((verb, kind), None)
@@ -163,7 +164,7 @@ class APIServer:
             self.request_log.append(("create", kind, f"{key[0]}/{key[1]}"))
             if key in self._objs[kind]:
                 raise AlreadyExists(f'{kind.lower()} "{key[1]}" already exists')
-            o = copy.deepcopy(obj)
+            o = _copy(obj)
             o.setdefault("apiVersion", self.scheme.api_version(kind) if self.scheme.knows(kind) else "v1")
             m = o.setdefault("metadata", {})
             m["namespace"] = key[0]
@@ -172,18 +173,18 @@ class APIServer:
             m["creationTimestamp"] = m.get("creationTimestamp") or c.now_precise()
             m.setdefault("generation", 1)
             self._objs[kind][key] = o
-            out = copy.deepcopy(o)
+            out = _copy(o)
             self._record(kind, ADDED, out)
             self._pending.append((kind, ADDED, out, None))
         self._dispatch()
-        return copy.deepcopy(out)
+        return _copy(out)
 
     def get(self, kind: str, namespace: str, name: str) -> dict:
         with self._lock:
             o = self._objs[kind].get((namespace or "default", name))
             if o is None:
                 raise NotFound(f'{kind.lower()} "{name}" not found')
-            return copy.deepcopy(o)
+            return _copy(o)
 
     def list(self, kind: str, namespace: Optional[str] = None,
              label_selector: Optional[Dict[str, str]] = None) -> List[dict]:
@@ -196,7 +197,7 @@ class APIServer:
                     lab = o.get("metadata", {}).get("labels") or {}
                     if any(lab.get(k) != v for k, v in label_selector.items()):
                         continue
-                out.append(copy.deepcopy(o))
+                out.append(_copy(o))
             out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
             return out
 
@@ -224,16 +225,16 @@ class APIServer:
             if rv and rv != cur["metadata"]["resourceVersion"]:
                 raise Conflict(f"Operation cannot be fulfilled on {kind.lower()} \"{key[1]}\": the object "
                                f"has been modified; please apply your changes to the latest version")
-            old = copy.deepcopy(cur)
-            new = copy.deepcopy(cur)
+            old = _copy(cur)
+            new = _copy(cur)
             if status_only:
-                new["status"] = copy.deepcopy(obj.get("status", {}))
+                new["status"] = _copy(obj.get("status", {}))
             else:
-                incoming = copy.deepcopy(obj)
+                incoming = _copy(obj)
                 keep_meta = {k: cur["metadata"][k] for k in ("uid", "creationTimestamp", "namespace") if k in cur["metadata"]}
                 if spec_only:
                     if "status" in cur:
-                        incoming["status"] = copy.deepcopy(cur["status"])
+                        incoming["status"] = _copy(cur["status"])
                     else:
                         incoming.pop("status", None)
                 new = incoming
@@ -244,11 +245,11 @@ class APIServer:
                     new["metadata"]["generation"] = cur["metadata"].get("generation", 1)
             new["metadata"]["resourceVersion"] = self._next_rv()
             self._objs[kind][key] = new
-            out = copy.deepcopy(new)
+            out = _copy(new)
             self._record(kind, MODIFIED, out)
             self._pending.append((kind, MODIFIED, out, old))
         self._dispatch()
-        return copy.deepcopy(out)
+        return _copy(out)
 
     def update(self, obj: dict) -> dict:
         """PUT of the main resource; for workload kinds .status is ignored (status subresource)."""
@@ -278,7 +279,7 @@ class APIServer:
             cur = self._objs[kind].pop(key, None)
             if cur is None:
                 raise NotFound(f'{kind.lower()} "{name}" not found')
-            gone = copy.deepcopy(cur)
+            gone = _copy(cur)
             gone.setdefault("metadata", {})["deletionTimestamp"] = c.now_rfc3339()
             gone["metadata"]["resourceVersion"] = self._next_rv()   # a deletion is a write too
             self._record(kind, DELETED, gone)
@@ -304,7 +305,7 @@ class APIServer:
         """Register a watch.  With replay=True the handler first receives ADDED for every
         existing object (informer LIST+WATCH).  Returns an unsubscribe function."""
         with self._lock:
-            existing = [copy.deepcopy(o) for o in self._objs[kind].values()] if replay else []
+            existing = [_copy(o) for o in self._objs[kind].values()] if replay else []
             self._watchers[kind].append(handler)
         for o in existing:
             handler(ADDED, o, None)
@@ -328,7 +329,7 @@ class APIServer:
                         kind, ev, obj, old = self._pending.popleft()
                         handlers = list(self._watchers.get(kind, ()))
                     for h in handlers:
-                        h(ev, copy.deepcopy(obj), copy.deepcopy(old) if old is not None else None)
+                        h(ev, _copy(obj), _copy(old) if old is not None else None)
             finally:
                 self._dispatching.active = False
 
@@ -375,7 +376,7 @@ class APIServer:
             return self.create(obj)
         except AlreadyExists:
             cur = self.get(obj["kind"], c.namespace_of(obj), c.name_of(obj))
-            merged = copy.deepcopy(obj)
+            merged = _copy(obj)
             merged.setdefault("metadata", {}).pop("resourceVersion", None)
             if "status" in cur:
                 merged["status"] = cur["status"]

@@ -9,10 +9,11 @@ PodControllerRefManager, used at controllers/pytorch/pod.go:53-66).
 """
 from __future__ import annotations
 
-import copy
+import copy  # noqa: F401
 from typing import Callable, Dict, List, Optional
 
 from ..api import common as c
+from ..api.common import deepcopy as _copy
 from ..apiserver.store import NotFound
 from ..utils.k8sutil import match_labels
 
@@ -48,11 +49,11 @@ def get_pod_from_template(template: dict, parent: dict, controller_ref: Optional
     pod = {"apiVersion": "v1", "kind": "Pod",
            "metadata": {"labels": dict(tm.get("labels") or {}), "annotations": dict(tm.get("annotations") or {}),
                         "name": tm.get("name", "")},
-           "spec": copy.deepcopy(template.get("spec") or {})}
+           "spec": _copy(template.get("spec") or {})}
     if tm.get("finalizers"):
         pod["metadata"]["finalizers"] = list(tm["finalizers"])
     if controller_ref is not None:
-        pod["metadata"]["ownerReferences"] = [copy.deepcopy(controller_ref)]
+        pod["metadata"]["ownerReferences"] = [_copy(controller_ref)]
     return pod
 
 
@@ -101,11 +102,11 @@ class ServiceControl:
         validate_controller_ref(controller_ref)
         if not (service.get("metadata", {}).get("labels")):
             raise ValueError("unable to create Services, no labels")
-        svc = copy.deepcopy(service)
+        svc = _copy(service)
         svc.setdefault("apiVersion", "v1")
         svc["kind"] = "Service"
         svc["metadata"]["namespace"] = namespace
-        svc["metadata"]["ownerReferences"] = [copy.deepcopy(controller_ref)]
+        svc["metadata"]["ownerReferences"] = [_copy(controller_ref)]
         try:
             created = self.client.create(svc)
         except Exception as e:
@@ -153,8 +154,8 @@ class FakeServiceControl:
         self.create_call_count += 1
         if self.create_limit and self.create_call_count > self.create_limit:
             raise RuntimeError(f"not creating service, limit {self.create_limit} already reached")
-        self.templates.append(copy.deepcopy(service))
-        self.controller_refs.append(copy.deepcopy(controller_ref))
+        self.templates.append(_copy(service))
+        self.controller_refs.append(_copy(controller_ref))
         if self.err:
             raise self.err
         return service

@@ -13,7 +13,7 @@ drains every queue on the calling thread (deterministic tests — the stronger h
 from __future__ import annotations
 
 import collections
-import copy
+import copy  # noqa: F401
 import fcntl
 import os
 import queue
@@ -24,6 +24,7 @@ from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Tuple
 
 from ..api import common as c
+from ..api.common import deepcopy as _copy
 from ..api.kinds import SCHEME
 from ..apiserver.store import ADDED, DELETED, MODIFIED, APIServer, NotFound
 from ..utils.logger import logger
@@ -96,7 +97,7 @@ class Client:
                 key = (c.namespace_of(obj), c.name_of(obj))
                 cur = cache.get(key)
                 if cur is not None and _older(cur, obj):   # never resurrect what a DELETED event removed
-                    cache[key] = copy.deepcopy(obj)
+                    cache[key] = _copy(obj)
         return obj
 
     def get(self, kind: str, namespace: str, name: str) -> dict:
@@ -105,7 +106,7 @@ class Client:
             o = self._cache[kind].get((namespace or "default", name))
             if o is None:
                 raise NotFound(f'{kind.lower()} "{name}" not found')
-            return copy.deepcopy(o)
+            return _copy(o)
 
     def list(self, kind: str, namespace: Optional[str] = None,
              label_selector: Optional[Dict[str, str]] = None) -> List[dict]:
@@ -119,7 +120,7 @@ class Client:
                     lab = o.get("metadata", {}).get("labels") or {}
                     if any(lab.get(k) != v for k, v in label_selector.items()):
                         continue
-                out.append(copy.deepcopy(o))
+                out.append(_copy(o))
             out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
             return out
 
@@ -177,7 +178,7 @@ class EventRecorder:
                 self._thread.start()
         if self._async:
             try:
-                self._q.put_nowait((copy.deepcopy({k: obj.get(k) for k in ("kind", "apiVersion", "metadata")}),
+                self._q.put_nowait((_copy({k: obj.get(k) for k in ("kind", "apiVersion", "metadata")}),
                                     etype, reason, message))
             except queue.Full:       # dropping beats blocking a reconcile (client-go does the same)
                 pass

@@ -29,6 +29,8 @@ def main(argv=None) -> int:
     ap.add_argument("--node-name", default="b200-node-0")
     ap.add_argument("--log-dir", default="/tmp/kubedl-b200/pods")
     ap.add_argument("--prefork-workers", action="store_true", help="fork pods from a launcher that has torch imported")
+    ap.add_argument("--warm-gpu-workers", action="store_true",
+                    help="keep one pre-forked worker per free GPU with its CUDA context already created")
     ap.add_argument("--multi-node", action="store_true",
                     help="several agents share this API server: bid for each job with a Lease, run only the jobs won")
     args = ap.parse_args(argv)
@@ -37,7 +39,8 @@ def main(argv=None) -> int:
     api = KubeAPIServer(KubeConfig.load(master=args.master, kubeconfig=args.kubeconfig, context=args.context,
                                         token_file=args.token_file))
     let = Gpulet(api, num_gpus=args.gpus, node_name=args.node_name, log_dir=args.log_dir,
-                 prefork=True if args.prefork_workers else None, multi_node=args.multi_node)
+                 prefork=True if args.prefork_workers else None, multi_node=args.multi_node,
+                 warm_gpus=True if args.warm_gpu_workers else None)
     let.start()
     print(f"kubedl-b200 gpulet {args.node_name}: {let.num_gpus} GPUs, API {api.config.server}", flush=True)
     stop = threading.Event()

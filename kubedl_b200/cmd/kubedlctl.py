@@ -132,14 +132,19 @@ def cmd_run(args) -> int:
     margs = M.build_parser().parse_args(["--enable-leader-election=false", "--serve", "", "--metrics-addr", "0",
                                          "--controller-metrics-addr", "0", "--workloads", "*"] + (["--gpus", str(args.gpus)] if args.gpus is not None else [])
                                         + (["--gang-scheduler-name", args.gang] if args.gang else [])
-                                        + (["--prefork-workers"] if args.prefork else []))
+                                        + (["--prefork-workers"] if args.prefork else [])
+                                        + (["--warm-gpu-workers"] if args.warm_gpus else []))
     reg = CollectorRegistry()
     op = M.build_operator(margs, metrics_registry=reg)
     M.start_operator(op, margs, metrics_registry=reg)
     jobs = []
     try:
-        if args.prefork and op.gpulet is not None and op.gpulet.zygote is not None:
+        if (args.prefork or args.warm_gpus) and op.gpulet is not None and op.gpulet.zygote is not None:
             op.gpulet.zygote.ready.wait(300)      # a long-running agent pays this once, not per job
+            if args.warm_gpus:
+                t0 = time.time()
+                n = op.gpulet.wait_warm(300)
+                print(f"warm GPU workers: {n} ready after {time.time() - t0:.1f} s")
         for f in args.filename:
             with open(f) as fh:
                 for d in yaml.safe_load_all(fh):
@@ -269,6 +274,9 @@ def main(argv=None) -> int:
     x.add_argument("--env", action="append", help="NAME=VALUE added to every container of every job")
     x.add_argument("--logs", type=int, default=0, help="print the last N log lines of every pod at the end")
     x.add_argument("--prefork", action="store_true", help="fork worker pods from a launcher that has torch imported")
+    x.add_argument("--warm-gpus", action="store_true",
+                   help="start the job only once a worker with an initialised CUDA context waits on every GPU "
+                        "(what a long-running node agent has between jobs)")
     args = ap.parse_args(argv)
     if args.cmd == "run":
         return cmd_run(args)

@@ -64,6 +64,9 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--no-node-agent", action="store_true", help="control plane only (pods are never started)")
     ap.add_argument("--prefork-workers", action="store_true",
                     help="node agent forks `python -m module` pods from a launcher that has torch imported")
+    ap.add_argument("--warm-gpu-workers", action="store_true",
+                    help="node agent keeps one pre-forked worker per free GPU with its CUDA context already created "
+                         "(implies --prefork-workers)")
     ap.add_argument("--leader-lock", default="/tmp/kubedl-b200-leader.lock")
     # against a cluster
     ap.add_argument("--master", default="", help="URL of a Kubernetes API server to reconcile against "
@@ -132,6 +135,7 @@ def build_operator(args, api: Optional[APIServer] = None, metrics_registry=None)
     # against a cluster the pods belong to its kubelets (or to a separate gpulet process)
     let = None if (args.no_node_agent or remote) else Gpulet(mgr.api, num_gpus=args.gpus,
                                                                   prefork=True if getattr(args, "prefork_workers", False) else None,
+                                                                  warm_gpus=True if getattr(args, "warm_gpu_workers", False) else None,
                                                                   metrics_registry=metrics_registry or metrics_mod.DEFAULT_REGISTRY)
     return Operator(mgr, recs, pers, let)
 

@@ -153,7 +153,7 @@ class Gpulet:
     def __init__(self, api: APIServer, num_gpus: Optional[int] = None, registry: Optional[ImageRegistry] = None,
                  log_dir: str = "/tmp/kubedl-b200/pods", node_name: str = "b200-node-0",
                  default_gpu_per_pod: bool = False, prefork: Optional[bool] = None, multi_node: bool = False,
-                 metrics_registry=None):
+                 metrics_registry=None, warm_gpus: Optional[bool] = None):
         self.api = api
         self.registry = registry or ImageRegistry()
         if num_gpus is None:
@@ -207,18 +207,65 @@ class Gpulet:
         # pre-forked workers (node/zygote.py): pods fork from a process that has imported torch
         if prefork is None:
             prefork = os.environ.get("KUBEDL_GPULET_PREFORK", "0") == "1"
+        # warm GPU workers (node/zygote.py): one pre-forked worker per FREE GPU with its CUDA context up and the
+        # kernel library loaded, waiting to become the next pod bound to that GPU.  Implies pre-forking.
+        if warm_gpus is None:
+            warm_gpus = os.environ.get("KUBEDL_GPULET_WARM_GPUS", "0") == "1"
+        self.warm_gpus = bool(warm_gpus) and num_gpus > 0
         self.zygote = None
-        if prefork:
+        if prefork or self.warm_gpus:
             from .zygote import ZygoteClient
             self.zygote = ZygoteClient()
+            if self.warm_gpus:
+                self.zygote.on_ready.append(self._warm_free_gpus)
 
     # ------------------------------------------------------------------ lifecycle
-    def _spawn(self, argv: List[str], env: Dict[str, str], log_path: str, cwd: Optional[str]):
-        """Fork from the zygote when it is ready and the command is `python -m module`, else exec."""
+    def _gpu_env(self, gpu: int) -> Dict[str, str]:
+        """What a pod bound to `gpu` gets on top of the agent's environment for device selection."""
+        out = {"KUBEDL_GPU_INDEX": str(gpu), "LOCAL_RANK": str(gpu)}
+        if self.isolate_gpus:
+            # the pod sees ONLY its GPU (workers take device LOCAL_RANK % device_count = 0).  The symmetric
+            # heap needs no visible peers: memory is shared as POSIX fds of cuMem allocations and mapped for
+            # the local device, the NVLS multicast object likewise (validated with the fused all-reduce check).
+            mine = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d.strip()]
+            # the agent's own mask, if any, names the devices its indices refer to
+            out["CUDA_VISIBLE_DEVICES"] = mine[gpu].strip() if gpu < len(mine) else str(gpu)
+        return out
+
+    def _warm_gpu(self, gpu: int) -> None:
+        if not self.warm_gpus or self.zygote is None or self._stop.is_set():
+            return
+        sel = self._gpu_env(gpu)
+        cuda_env = {k: v for k, v in sel.items() if k == "CUDA_VISIBLE_DEVICES"}
+        self.zygote.warm(gpu, 0 if self.isolate_gpus else gpu, {**os.environ, **sel}, cuda_env)
+
+    def wait_warm(self, timeout: float = 300.0) -> int:
+        """Block until a worker is ready on every free GPU (or the timeout); returns how many are."""
+        deadline = time.monotonic() + timeout
+        while True:
+            with self._lock:
+                free = list(self.free_gpus)
+            ws = self.zygote.warm_workers if self.zygote is not None else {}
+            ready = [g for g in free if ws.get(g, {}).get("state") == "ready"]
+            if not self.warm_gpus or len(ready) == len(free) or time.monotonic() > deadline:
+                return len(ready)
+            time.sleep(0.05)
+
+    def _warm_free_gpus(self) -> None:
+        with self._lock:
+            free = list(self.free_gpus)
+        for g in free:
+            self._warm_gpu(g)
+
+    def _spawn(self, argv: List[str], env: Dict[str, str], log_path: str, cwd: Optional[str], gpu: Optional[int] = None):
+        """Fork from the zygote when it is ready and the command is `python -m module` (or hand the pod to the
+        worker already waiting on its GPU), else exec."""
         if self.zygote is not None:
-            child = self.zygote.spawn(argv, env, log_path, cwd)
+            child = self.zygote.spawn(argv, env, log_path, cwd, gpu=gpu if self.warm_gpus else None)
             if child is not None:
                 return child
+            if gpu is not None and self.warm_gpus:
+                self.zygote.drop(gpu)
         lf = open(log_path, "ab")
         try:
             return subprocess.Popen(argv, env=env, stdout=lf, stderr=subprocess.STDOUT, cwd=cwd, start_new_session=True)
@@ -287,6 +334,7 @@ class Gpulet:
         if gpu is not None and gpu not in self.free_gpus:
             self.free_gpus.append(gpu)
             self.free_gpus.sort()
+            self._warm_gpu(gpu)              # a worker for the next pod on this GPU starts initialising now
 
     def _forget_job(self, key: Tuple[str, str]) -> None:
         """Last pod of a job gone: forget the job's host-port assignments.  Caller holds the lock."""
@@ -553,15 +601,13 @@ class Gpulet:
         env["KUBEDL_REPLICA_TYPE"] = c.labels_of(pod).get(c.REPLICA_TYPE_LABEL, "")
         env["KUBEDL_REPLICA_INDEX"] = c.labels_of(pod).get(c.REPLICA_INDEX_LABEL, "")
         if gpu is not None:
-            env["KUBEDL_GPU_INDEX"] = str(gpu)
-            env["LOCAL_RANK"] = str(gpu)
-            if self.isolate_gpus and not any(e.get("name") == "CUDA_VISIBLE_DEVICES" for e in container.get("env") or []):
-                # the pod sees ONLY its GPU (workers take device LOCAL_RANK % device_count = 0).  The symmetric
-                # heap needs no visible peers: memory is shared as POSIX fds of cuMem allocations and mapped for
-                # the local device, the NVLS multicast object likewise (validated with the fused all-reduce check).
-                mine = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d.strip()]
-                # the agent's own mask, if any, names the devices its indices refer to
-                env["CUDA_VISIBLE_DEVICES"] = mine[gpu].strip() if gpu < len(mine) else str(gpu)
+            sel = self._gpu_env(gpu)
+            if any(e.get("name") == "CUDA_VISIBLE_DEVICES" for e in container.get("env") or []):
+                sel.pop("CUDA_VISIBLE_DEVICES", None)        # the pod's own mask wins
+            env.update(sel)
+        # the worker reports "pod start -> first step" against this (an adopted warm worker's own clock starts
+        # at adoption, a fresh process's after the interpreter is up: neither is what the user waits for)
+        env["KUBEDL_POD_START_TS"] = repr(time.time())
         return env
 
     # ------------------------------------------------------------------ launch / status
@@ -606,7 +652,7 @@ class Gpulet:
         env = self.build_env(pod, ctr, gpu)
         argv = self.registry.resolve(ctr, env)
         log_path = os.path.join(self.log_dir, f"{key[0]}_{key[1]}.log")
-        popen = self._spawn(argv, env, log_path, ctr.get("workingDir") or None)
+        popen = self._spawn(argv, env, log_path, ctr.get("workingDir") or None, gpu)
         proc = _Proc(key, ctr.get("name", ""), popen, gpu, started_at=c.now_precise(), log_path=log_path,
                      uid=c.uid_of(pod), started_mono=time.monotonic())
         with self._lock:

@@ -32,6 +32,9 @@ def main(argv=None) -> int:
     lab = torch.randint(0, 1000, (args.batch,), dtype=torch.int64, generator=g).pin_memory()
     tr.train_step(img, lab, sync=True)
     t_first = time.time() - t_start
+    # what the user waits for: from the node agent starting this pod (fork / exec / adoption of a waiting worker)
+    pod_start = float(os.environ.get("KUBEDL_POD_START_TS", "0") or 0)
+    t_pod = (time.time() - pod_start) if pod_start else None
     tr.warmup(2)
     torch.cuda.synchronize()
     t0 = time.time()
@@ -42,7 +45,8 @@ def main(argv=None) -> int:
     if args.checkpoint:
         tr.save(args.checkpoint)
     print(json.dumps({"rank": tr.rank, "world": tr.world, "samples_per_s_per_gpu": args.batch * args.steps / dt,
-                      "time_to_first_step_s": t_first, "loss": loss, "comm": tr.comm,
+                      "time_to_first_step_s": t_first,
+                      "pod_start_to_first_step_s": t_pod, "loss": loss, "comm": tr.comm,
                       "startup_s": {"import": round(t_import, 3), **tr.startup,
                                     "first_step": round(t_first - t_init, 3)}}), flush=True)
     if tr.world > 1:

@@ -116,3 +116,79 @@ def test_pytorch_example_through_preforked_workers(tmp_path):
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_warm_worker_is_adopted_not_forked(tmp_path):
+    """A worker asked for ahead of time (on a GPU box it would be holding a CUDA context by now) becomes the
+    pod bound to its GPU: same pid, the pod's env / argv / log, exit code reported like any other child."""
+    z = ZygoteClient(preload=("json", "kubedl_b200.worker.rendezvous"))
+    z.start()
+    try:
+        assert z.ready.wait(30)
+        py = sys.executable
+        base = _env()
+        assert z.warm(0, 0, base)
+        w = _wait(lambda: z.warm_workers.get(0) if z.warm_workers.get(0, {}).get("state") == "ready" else None)
+        assert w["pid"] > 0 and w["cuda"] is False                       # no GPU here: protocol only
+        log = str(tmp_path / "adopted.log")
+        p = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="0.05", MARK="from-pod"), log, gpu=0)
+        assert p is not None and p.pid == w["pid"] and z.adopted == 1 and 0 not in z.warm_workers
+        assert p.wait(20) == 0 and "TF_CONFIG absent" in open(log).read()
+        # a request for a GPU with nobody waiting is a plain fork
+        p2 = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_FAIL_WITH="4", KUBEDL_TF_TRAIN_SECONDS="0.01"),
+                     str(tmp_path / "plain.log"), gpu=0)
+        assert p2.wait(20) == 4 and z.adopted == 1
+        # adoption of a worker that is still initialising: the request waits in its socket
+        assert z.warm(1, 1, base)
+        p3 = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="0.01"), str(tmp_path / "early.log"), gpu=1)
+        assert p3 is not None and p3.wait(20) == 0 and z.adopted == 2
+        # a pod whose CUDA-relevant environment differs from the waiting worker's cannot take it over
+        assert z.warm(2, 2, base)
+        pid2 = _wait(lambda: z.warm_workers.get(2, {}).get("pid"))
+        p4 = z.spawn([py, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="0.01", CUDA_MODULE_LOADING="EAGER"),
+                     str(tmp_path / "other.log"), gpu=2)
+        assert p4.pid != pid2 and p4.wait(20) == 0 and z.adopted == 2 and 2 not in z.warm_workers
+
+        def gone(pid):
+            try:
+                os.kill(pid, 0)
+                return False
+            except ProcessLookupError:
+                return True
+        _wait(lambda: gone(pid2))                                        # the dropped worker left
+        # a waiting worker that dies is reported and forgotten
+        assert z.warm(3, 3, base)
+        pid3 = _wait(lambda: z.warm_workers.get(3, {}).get("pid"))
+        os.killpg(pid3, signal.SIGKILL)                                  # the exact group forked for GPU 3
+        _wait(lambda: 3 not in z.warm_workers)
+    finally:
+        z.stop()
+
+
+def test_node_agent_keeps_a_warm_worker_per_free_gpu(tmp_path):
+    mgr = Manager()
+    gang_schedule.register_gang_schedulers(mgr)
+    setup_with_manager(mgr, JobControllerConfiguration(), "*", CollectorRegistry())
+    let = Gpulet(mgr.api, num_gpus=2, log_dir=str(tmp_path / "pods"), warm_gpus=True, default_gpu_per_pod=True)
+    let.zygote.preload = ("json", "kubedl_b200.worker.rendezvous")
+    mgr.start()
+    let.start()
+    try:
+        assert let.zygote.ready.wait(60)
+        _wait(lambda: sorted(g for g, w in let.zygote.warm_workers.items() if w["state"] == "ready") == [0, 1])
+        first = {g: w["pid"] for g, w in let.zygote.warm_workers.items()}
+        from kubedl_b200.bench.launch_delay import _job
+        mgr.api.create(_job("TFJob", "warm", 2, 0.1))      # PS + worker, both `python -m` workers
+
+        def done():
+            s = mgr.api.get("TFJob", "bench", "warm").get("status", {})
+            return [x["type"] for x in s.get("conditions", [])][-1:] == ["Succeeded"]
+        _wait(done, timeout=60)
+        assert let.zygote.adopted == 2 and let.zygote.spawned == 2          # both pods were adoptions
+        # the GPUs came back, and each got a NEW waiting worker
+        _wait(lambda: sorted(g for g, w in let.zygote.warm_workers.items() if w["state"] == "ready") == [0, 1])
+        again = {g: w["pid"] for g, w in let.zygote.warm_workers.items()}
+        assert set(again.values()).isdisjoint(first.values())
+    finally:
+        let.stop()
+        mgr.stop()

@@ -192,3 +192,17 @@ def test_node_agent_keeps_a_warm_worker_per_free_gpu(tmp_path):
     finally:
         let.stop()
         mgr.stop()
+
+
+def test_forked_pod_honours_its_thread_count(tmp_path):
+    """The launcher loaded OpenMP without the pod's OMP_NUM_THREADS; the fork applies it."""
+    z = ZygoteClient(preload=("torch",))
+    z.start()
+    try:
+        assert z.ready.wait(120)
+        (tmp_path / "show_threads.py").write_text("import torch\nprint('threads', torch.get_num_threads())\n")
+        log = str(tmp_path / "t.log")
+        p = z.spawn([sys.executable, "-m", "show_threads"], _env(OMP_NUM_THREADS="3", PYTHONPATH=f"{tmp_path}:{os.getcwd()}"), log)
+        assert p.wait(60) == 0 and "threads 3" in open(log).read(), open(log).read()
+    finally:
+        z.stop()

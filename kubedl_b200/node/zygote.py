@@ -48,6 +48,7 @@ import time
 import traceback
 from typing import Dict, List, Optional
 
+ORPHAN_GRACE_SECONDS = float(os.environ.get("KUBEDL_ZYGOTE_ORPHAN_GRACE_SECONDS", "2"))
 DEFAULT_PRELOAD = ("torch", "torch.distributed", "numpy", "kubedl_b200.worker.rendezvous")
 
 
@@ -319,7 +320,18 @@ def serve(sock_path: str, preload=DEFAULT_PRELOAD) -> int:
             return send(conn, {"id": req.get("id"), "pid": pid})
         send(conn, {"id": req.get("id"), "error": f"unknown op {req.get('op')!r}"})
 
+    orphaned_at = None                                # when the last agent connection went away
+    had_client = False
     while not stopping:
+        # the launcher lives for its node agent: if the agent is gone (killed, crashed) nobody would ever hear of these
+        # pods again, and waiting workers would sit on their GPUs' memory for good — leave, taking them along
+        if conns:
+            had_client, orphaned_at = True, None
+        elif had_client:
+            orphaned_at = orphaned_at or time.monotonic()
+            if time.monotonic() - orphaned_at > ORPHAN_GRACE_SECONDS:
+                print("zygote: the node agent is gone; shutting down", file=sys.stderr, flush=True)
+                break
         for key, _ in sel.select(timeout=0.05):
             if key.data is not None:
                 warm_readable(key.data[1])

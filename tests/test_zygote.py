@@ -206,3 +206,28 @@ def test_forked_pod_honours_its_thread_count(tmp_path):
         assert p.wait(60) == 0 and "threads 3" in open(log).read(), open(log).read()
     finally:
         z.stop()
+
+
+def test_launcher_does_not_outlive_its_node_agent(tmp_path):
+    """The agent's connection closing without a goodbye (agent killed) takes the launcher, its pods and its waiting
+    workers down after a short grace: nothing is left holding GPU memory with nobody to report to."""
+    z = ZygoteClient(preload=("json",))
+    z.start()
+    try:
+        assert z.ready.wait(30)
+        p = z.spawn([sys.executable, "-m", "kubedl_b200.worker.tf_stub"], _env(KUBEDL_TF_TRAIN_SECONDS="60"), str(tmp_path / "a.log"))
+        assert z.warm(0, 0, _env())
+        wpid = _wait(lambda: z.warm_workers.get(0, {}).get("pid"))
+        z._sock.shutdown(2)                       # what the launcher sees when the agent process dies
+        z._sock.close()
+        assert z._proc.wait(15) == 0              # the launcher left by itself
+
+        def gone(pid):
+            try:
+                os.kill(pid, 0)
+                return False
+            except ProcessLookupError:
+                return True
+        _wait(lambda: gone(p.pid) and gone(wpid), timeout=15)
+    finally:
+        z.stop()

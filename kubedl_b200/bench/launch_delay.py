@@ -53,8 +53,48 @@ def _job(kind: str, name: str, replicas: int, seconds: float) -> dict:
                      cleanPodPolicy="All")
 
 
+def _spawn_control_plane(prefork: bool):
+    """API server and node agent as two processes of their own (`kubedl-b200 apiserver`, `kubedl-b200 gpulet`), the way
+    the three components are deployed; returns (url, [stop callables])."""
+    import os
+    import socket
+    import subprocess
+    import urllib.request
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    url = f"http://127.0.0.1:{port}"
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join(filter(None, [os.getcwd(), os.environ.get("PYTHONPATH", "")])))
+    srv = subprocess.Popen([sys.executable, "-m", "kubedl_b200.cmd.apiserver", "--serve", f"127.0.0.1:{port}"],
+                           env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    deadline = time.time() + 60
+    while True:
+        try:
+            urllib.request.urlopen(url + "/healthz", timeout=1).read()
+            break
+        except Exception:
+            if time.time() > deadline or srv.poll() is not None:
+                srv.kill()
+                raise RuntimeError("API server process did not come up")
+            time.sleep(0.05)
+    let = subprocess.Popen([sys.executable, "-m", "kubedl_b200.cmd.gpulet", "--master", url, "--gpus", "0"]
+                           + (["--prefork-workers"] if prefork else []),
+                           env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+
+    def stop(p):
+        def fn():
+            p.terminate()                  # the exact process started above
+            try:
+                p.wait(10)
+            except subprocess.TimeoutExpired:
+                p.kill()
+        return fn
+    return url, [stop(let), stop(srv)]
+
+
 def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int = 1, remote: bool = False,
-        create_parallelism: int = 1, api_latency: float = 0.0, prefork: bool = False) -> dict:
+        create_parallelism: int = 1, api_latency: float = 0.0, prefork: bool = False, processes: bool = False) -> dict:
     """remote=True puts the API server behind HTTP (`apiserver/rest.py`) with the node agent next to
     it, and makes the operator a client of it (`apiserver/kube.py`) — the reference's deployment
     shape, where every pod / service create and every status write is a round trip."""
@@ -62,7 +102,12 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
              "--gpus", "0", "--max-reconciles", str(max_reconciles), "--pod-create-parallelism", str(create_parallelism)]
     reg = CollectorRegistry()
     extra = []
-    if remote:
+    backing = None
+    if processes:
+        url, extra = _spawn_control_plane(prefork)
+        flags += ["--master", url]
+        remote = True
+    elif remote:
         from ..apiserver import rest
         from ..apiserver.store import APIServer
         from ..node.gpulet import Gpulet
@@ -77,12 +122,15 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
     args = M.build_parser().parse_args(flags)
     op = M.build_operator(args, metrics_registry=reg)
     M.start_operator(op, args, metrics_registry=reg)
-    if prefork:
+    if prefork and not processes:
         z = (let if remote else op.gpulet).zygote
         z.ready.wait(300)
+    if processes:
+        time.sleep(8.0 if prefork else 1.0)       # the agent process: watch established (and its launcher up)
     done_times = []
     # the bench's own polling must not load the wire it is measuring: watch the state where it lives
-    state = backing if remote else op.mgr.api
+    state = backing if backing is not None else op.mgr.api
+    poll = 0.01 if processes else 0.002            # with separate processes every poll is an HTTP GET
     try:
         for i in range(jobs):
             name = f"{kind.lower()}-{i}"
@@ -94,7 +142,7 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
                     break
                 if time.time() - t0 > 120:
                     raise RuntimeError(f"{name} did not finish: {s}")
-                time.sleep(0.002)
+                time.sleep(poll)
             done_times.append(time.time() - t0)
             op.mgr.api.delete(kind, "bench", name)
         m = op.reconcilers[kind].metrics
@@ -107,7 +155,8 @@ def run(kind: str, jobs: int, replicas: int, seconds: float, max_reconciles: int
                 "first_pod_ms": {"p50": 1e3 * _pct(first, 0.5), "p90": 1e3 * _pct(first, 0.9), "n": len(first)},
                 "all_pods_ms": {"p50": 1e3 * _pct(allp, 0.5), "p90": 1e3 * _pct(allp, 0.9), "n": len(allp)},
                 "time_to_succeeded_ms": {"p50": 1e3 * _pct(done_times, 0.5), "p90": 1e3 * _pct(done_times, 0.9)},
-                "api_creates_per_job": creates / jobs, "api": "http" if remote else "in-process",
+                "api_creates_per_job": creates / jobs,
+                "api": "http, 3 processes" if processes else "http" if remote else "in-process",
                 "pod_create_parallelism": create_parallelism, "api_latency_ms": 1e3 * api_latency, "prefork": prefork}
     finally:
         op.stop()
@@ -122,6 +171,8 @@ def main(argv=None) -> int:
     ap.add_argument("--seconds", type=float, default=0.2)
     ap.add_argument("--kinds", default="PyTorchJob,TFJob,XGBoostJob,XDLJob")
     ap.add_argument("--remote", action="store_true", help="operator talks to the API server over HTTP")
+    ap.add_argument("--processes", action="store_true",
+                    help="API server and node agent as separate processes, operator as their HTTP client (implies --remote)")
     ap.add_argument("--max-reconciles", type=int, default=1)
     ap.add_argument("--create-parallelism", type=int, default=1)
     ap.add_argument("--api-latency-ms", type=float, default=0.0, help="with --remote: added to every API request")
@@ -129,7 +180,7 @@ def main(argv=None) -> int:
     a = ap.parse_args(argv)
     for kind in a.kinds.split(","):
         print(json.dumps(run(kind, a.jobs, a.replicas, a.seconds, a.max_reconciles, a.remote, a.create_parallelism,
-                             a.api_latency_ms / 1e3, a.prefork)), flush=True)
+                             a.api_latency_ms / 1e3, a.prefork, a.processes)), flush=True)
     return 0
 
 

@@ -174,3 +174,67 @@ inline cudaError_t kdl_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block,
   return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
 }
 }  // namespace kdl
+
+// ---------------------------------------------------------------------------------------------------------
+// Sum of `planes` fp32 planes of `MN` elements each (plane stride MN) into a bf16 matrix, for SMALL MN: split-K
+// and per-group weight-gradient partials of the narrow layers.  One thread per element walks the planes as a chain
+// of dependent-latency loads (a 64 x 64 gradient over 128 planes: 16 rounds of 8 loads, 16 us for 2 MB); here SUB
+// threads share an element — plane s belongs to sub-lane s % SUB — and combine through shared memory.  The
+// summation order is fixed by (SUB, planes), so results stay bit-reproducible from run to run.
+namespace kdl {
+template <int SUB>
+__global__ void __launch_bounds__(256) plane_reduce_small_kernel(const float* __restrict__ partial,
+                                                                 __nv_bfloat16* __restrict__ out, int64_t MN, int N,
+                                                                 int ldc, int planes) {
+  constexpr int BI = 256 / SUB;                    // elements per block
+  __shared__ float sm[SUB][BI + 1];
+  const int sub = threadIdx.x / BI, ii = threadIdx.x % BI;
+  const int64_t i = (int64_t)blockIdx.x * BI + ii;
+  float acc = 0.f;
+  if (i < MN) {
+    int s = sub;
+    for (; s + 3 * SUB < planes; s += 4 * SUB) {   // four independent loads in flight
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldcg(partial + (size_t)(s + u * SUB) * MN + i);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc += v[u];
+    }
+    for (; s < planes; s += SUB) acc += __ldcg(partial + (size_t)s * MN + i);
+  }
+  sm[sub][ii] = acc;
+  __syncthreads();
+  if (sub == 0 && i < MN) {
+    float t = 0.f;
+#pragma unroll
+    for (int u = 0; u < SUB; ++u) t += sm[u][ii];
+    const int64_t r = i / N, c = i % N;
+    out[r * ldc + c] = __float2bfloat16(t);
+  }
+}
+
+// Launches the shared-element reduction when it pays (few elements, many planes); false = caller's own kernel.
+inline bool launch_plane_reduce_small(const float* partial, __nv_bfloat16* out, int64_t MN, int N, int ldc, int planes,
+                                      cudaStream_t stream) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("KDL_PLANE_REDUCE_SMALL");
+    enabled = e ? atoi(e) : 1;
+  }
+  if (!enabled) return false;
+  const int64_t kThreads = 148LL * 8 * 256;        // one full wave of 256-thread blocks
+  int sub = 1;
+  while (sub < 32 && MN * sub * 2 <= kThreads && sub * 2 * 4 <= planes) sub *= 2;
+  if (sub < 2) return false;
+  const int bi = 256 / sub;
+  const unsigned grid = (unsigned)((MN + bi - 1) / bi);
+  switch (sub) {
+    case 2: plane_reduce_small_kernel<2><<<grid, 256, 0, stream>>>(partial, out, MN, N, ldc, planes); break;
+    case 4: plane_reduce_small_kernel<4><<<grid, 256, 0, stream>>>(partial, out, MN, N, ldc, planes); break;
+    case 8: plane_reduce_small_kernel<8><<<grid, 256, 0, stream>>>(partial, out, MN, N, ldc, planes); break;
+    case 16: plane_reduce_small_kernel<16><<<grid, 256, 0, stream>>>(partial, out, MN, N, ldc, planes); break;
+    default: plane_reduce_small_kernel<32><<<grid, 256, 0, stream>>>(partial, out, MN, N, ldc, planes); break;
+  }
+  return true;
+}
+}  // namespace kdl

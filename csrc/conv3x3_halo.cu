@@ -925,7 +925,8 @@ extern "C" int kdl_conv3x3_halo_wgrad_bf16(const void* dy, const void* x, void* 
   conv3x3_halo_wgrad_kernel<<<3 * p.ci_roles * p.co_roles * p.G, kHaloThreads, smem, stream>>>(mdy, mx, p);
   KDL_CHECK_LAUNCH();
   const int n = Cout * 9 * Cin;
-  halo_wgrad_reduce_kernel<<<(n / 4 + 255) / 256, 256, 0, stream>>>(p.partial, (bf16*)dw, n, p.G);
+  if (!launch_plane_reduce_small(p.partial, (bf16*)dw, n, n, n, p.G, stream))
+    halo_wgrad_reduce_kernel<<<(n / 4 + 255) / 256, 256, 0, stream>>>(p.partial, (bf16*)dw, n, p.G);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }

@@ -1262,7 +1262,8 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
     int64_t MN = (int64_t)M * N;
     int64_t g = (MN + 255) / 256;
     if (g > 148 * 8) g = 148 * 8;
-    splitk_reduce_kernel<<<(int)g, 256, 0, stream>>>(p.partial, (bf16*)C, MN, N, ldc, splits);
+    if (!launch_plane_reduce_small(p.partial, (bf16*)C, MN, N, ldc, splits, stream))
+      splitk_reduce_kernel<<<(int)g, 256, 0, stream>>>(p.partial, (bf16*)C, MN, N, ldc, splits);
     KDL_CHECK_LAUNCH();
   }
   return KDL_OK;
@@ -1488,7 +1489,8 @@ static int conv2d_impl(int mode, const void* in0, const void* in1, void* out, in
       int64_t MN = (int64_t)M * Nn;
       int64_t g = (MN + 255) / 256;
       if (g > 148 * 8) g = 148 * 8;
-      splitk_reduce_kernel<<<(int)g, 256, 0, stream>>>(p.partial, (bf16*)out, MN, Nn, Nn, splits);
+      if (!launch_plane_reduce_small(p.partial, (bf16*)out, MN, Nn, Nn, splits, stream))
+        splitk_reduce_kernel<<<(int)g, 256, 0, stream>>>(p.partial, (bf16*)out, MN, Nn, Nn, splits);
       KDL_CHECK_LAUNCH();
     }
     return KDL_OK;

@@ -206,15 +206,33 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const bf16* __res
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) { best[k] = 0xFF80FF80u; bi[k] = 0x00040004u; }     // -inf, centre tap
+    // All nine taps are loaded before the first compare: with a bounds test (and a `continue`) in front of each
+    // load the compiler kept load -> compare -> next load in program order, nine dependent memory latencies
+    // per thread (ncu: 56 % issue-active, the rest long-scoreboard stalls, 51 % of DRAM throughput).  A tap
+    // outside the image reads the window's centre pixel instead (always inside) and is replaced by -inf.
+    uint4 tap[9];
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh) {
-      int ih = oh * 2 - 1 + kh;
-      if (ih < 0 || ih >= H) continue;
+      const int ih = oh * 2 - 1 + kh;
 #pragma unroll
       for (int kw = 0; kw < 3; ++kw) {
-        int iw = ow * 2 - 1 + kw;
-        if (iw < 0 || iw >= W) continue;
-        const uint4 v = ld_plain(x + (((int64_t)n * H + ih) * W + iw) * C + cg * 8);
+        const int iw = ow * 2 - 1 + kw;
+        const bool ok = (unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W;
+        const int ihc = ok ? ih : oh * 2, iwc = ok ? iw : ow * 2;
+        uint4 v = ld_plain(x + (((int64_t)n * H + ihc) * W + iwc) * C + cg * 8);
+        if (!ok) {                       // -inf AFTER the sign flip applied below
+          constexpr uint32_t kNegInf2 = 0xFF80FF80u;
+          v = AFFINE ? make_uint4(kNegInf2 ^ sgn[0], kNegInf2 ^ sgn[1], kNegInf2 ^ sgn[2], kNegInf2 ^ sgn[3])
+                     : make_uint4(kNegInf2, kNegInf2, kNegInf2, kNegInf2);
+        }
+        tap[kh * 3 + kw] = v;
+      }
+    }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const uint4 v = tap[kh * 3 + kw];
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
         const uint32_t code = (uint32_t)(kh * 3 + kw) * 0x00010001u;
 #pragma unroll
@@ -275,15 +293,27 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_quad_kernel(const bf16* 
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[q][j] = 0.f;
     // (window dh, dw) -> list of (pixel index 2*pr+pc, tap code); pixel (pr, pc) = (2a+pr, 2b+pc)
+    // the four windows' codes and gradients are loaded before any of them is used (the bounds test in front of each
+    // load otherwise serialises them); a window outside the output reads window (a, b) and matches no tap (code 0xFF)
+    uint2 pks[4];
+    uint4 dys[4];
 #pragma unroll
     for (int wdx = 0; wdx < 4; ++wdx) {
       const int dh = wdx >> 1, dw = wdx & 1;
-      const int oh = a + dh, ow = b + dw;
-      if (oh >= OH || ow >= OW) continue;
+      const bool ok = a + dh < OH && b + dw < OW;
+      const int oh = ok ? a + dh : a, ow = ok ? b + dw : b;
       const int64_t o = ((((int64_t)n * OH + oh) * OW + ow) * cvec + cg) * 8;
-      const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+      uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+      if (!ok) pk = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+      pks[wdx] = pk;
+      dys[wdx] = ld_plain(dy + o);
+    }
+#pragma unroll
+    for (int wdx = 0; wdx < 4; ++wdx) {
+      const int dh = wdx >> 1, dw = wdx & 1;
+      const uint2 pk = pks[wdx];
       float f[8];
-      unpack8(ld_plain(dy + o), f);
+      unpack8(dys[wdx], f);
 #pragma unroll
       for (int pr = dh; pr < 2; ++pr)        // a window one block down only reaches the block's second row
 #pragma unroll

@@ -21,3 +21,13 @@ r["fwd_bytes_mb"] = (x.numel() * 2 + y.numel() * 3) / 1e6
 r["bwd_bytes_mb"] = (x.numel() * 2 + y.numel() * 3) / 1e6
 r["fwd_tbs"] = r["fwd_bytes_mb"] / r["fwd_ms"] / 1e3; r["bwd_tbs"] = r["bwd_bytes_mb"] / r["bwd_ms"] / 1e3
 print(json.dumps(r))
+# BatchNorm-apply + ReLU + max-pool in one pass, as the ResNet stem runs it (finalize kernel + pool kernel)
+C = 64
+partial = torch.zeros(8, 2, C, device=dev); partial[:, 1] = x.numel() / C / 8      # mean 0, variance 1
+gamma, beta = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+save = torch.empty(2, C, device=dev)
+fused = lambda: K.bn_relu_maxpool_fwd(x, gamma, beta, None, None, save, (partial, 8))
+y2, _ = fused()
+ref = torch.relu(x.float())
+err = (y2.float() - torch.nn.functional.max_pool2d(ref.permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1)).abs().max().item()
+print(json.dumps({"bn_relu_pool_fwd_ms": timeit(fused), "max_abs_err_vs_torch": err}))

@@ -56,6 +56,9 @@ def test_gemm_nn(cuda, M, N, K):
 @pytest.mark.parametrize("K,M,N,split", [
     (4096, 64, 64, 0), (50000, 256, 64, 0), (1024, 128, 128, 1), (8192, 2048, 512, 0),
     (3000, 1000, 2048, 0), (100352, 64, 256, 0),
+    # few output elements, many partial planes: the shared-element reduction, with plane counts that are not
+    # multiples of its sub-lane count
+    (20000, 64, 64, 23), (30000, 128, 64, 50), (12800, 192, 64, 19), (40000, 64, 128, 101),
 ])
 def test_gemm_tn_splitk(cuda, K, M, N, split):
     from kubedl_b200.ops.gemm import Gemm

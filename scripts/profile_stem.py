@@ -12,3 +12,15 @@ for _ in range(2):
     gw = K.stem_conv_wgrad(img, y)
 torch.cuda.synchronize()
 print("ok")
+# device time per launch (CUDA events, L2 flushed between iterations)
+import json
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+def timeit(fn, iters=8):
+    ts = []
+    for _ in range(iters):
+        flush.zero_(); torch.cuda._sleep(400000)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
+    return sorted(ts)[len(ts) // 2]
+print(json.dumps({"stem_fprop_stats_ms": timeit(lambda: K.stem_conv_fwd(img, wp, want_stats=True)),
+                  "stem_wgrad_ms": timeit(lambda: K.stem_conv_wgrad(img, y))}))

@@ -173,6 +173,22 @@ int kdl_stem_conv_wgrad(const void* img_u8, const void* dy, void* gw_padded, int
                         const float* mean3, const float* std3, void* scratch, size_t scratch_bytes,
                         cudaStream_t stream);
 
+/* ---- N7d: the stem as a 4x4 / stride-1 convolution on a 2x2 space-to-depth image (224x224) ------------
+ * kdl_stem_s2d_pack writes S [N][115][115][16] bf16 (normalised, zero-bordered; kdl_stem_s2d_image_bytes(N)) once per
+ * step; fwd and wgrad then read their operand tiles with TMA through a tensor map whose 32-byte pixel stride is
+ * smaller than its 128-byte inner extent (overlapping 4-pixel windows) — no patch building by threads.  w / gw are
+ * [64][168] in the kh*24 + kw*3 + c column layout as for N7c; w2_scratch is 64*256 bf16.  fwd optionally emits
+ * BatchNorm column statistics ([kdl_stem_conv_max_parts()][2][64]); wgrad needs
+ * kdl_stem_s2d_wgrad_scratch_bytes() of scratch.  No reference counterpart. */
+size_t kdl_stem_s2d_image_bytes(int N);
+size_t kdl_stem_s2d_wgrad_scratch_bytes(void);
+int kdl_stem_s2d_pack(const void* img_u8, void* s2d, int N, int H, int W, const float* mean3, const float* std3,
+                      cudaStream_t stream);
+int kdl_stem_s2d_fwd(const void* s2d, const void* w_padded, void* w2_scratch, void* y, int N, int H, int W,
+                     float* stats_partial, int* stats_parts_out, cudaStream_t stream);
+int kdl_stem_s2d_wgrad(const void* s2d, const void* dy, void* gw_padded, int N, int H, int W, void* scratch,
+                       size_t scratch_bytes, cudaStream_t stream);
+
 /* ---- N7: implicit-GEMM convolution on the same tcgen05 kernel (NHWC bf16) ------------------
  * The activation operand is fetched with TMA im2col loads (no patch matrix in memory).  mode 0 =
  * fprop (x, w -> y), 1 = dgrad (dy, w -> dx [+addend]; stride-1 "same" convolutions), 2 = wgrad

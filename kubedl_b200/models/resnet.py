@@ -263,6 +263,10 @@ class ResNet50:
         self.mask_addend = _os.environ.get("KUBEDL_MASK_ADDEND", "1") == "1"
         # stem convolution straight from the uint8 image (224x224 inputs); 0: im2col patch matrix + GEMM
         self.stem_direct = _os.environ.get("KUBEDL_STEM_DIRECT", "1") == "1"
+        # the stem as a 4x4 convolution on a space-to-depth copy of the image (csrc/stem_s2d.cu): operand tiles come
+        # from TMA instead of being built by threads
+        self.stem_s2d = _os.environ.get("KUBEDL_STEM_S2D", "0") == "1"
+        self._s2d_buf = None
         self.fuse_stem_pool = _os.environ.get("KUBEDL_FUSE_STEM_POOL", "1") == "1"
         self.fuse_stem_pool_bwd = _os.environ.get("KUBEDL_FUSE_STEM_POOL_BWD", "0") == "1"
         # 3x3 convolutions on our own tcgen05 kernels (N7: halo-resident kernels for stride 1, TMA-im2col
@@ -317,7 +321,13 @@ class ResNet50:
         if stem_gemm:
             assert self.gemm is not None
             N, H, W, _ = x.shape
-            if self.stem_direct and K.stem_conv_supported(H, W):
+            if self.stem_s2d and K.stem_conv_supported(H, W):
+                if self._s2d_buf is None or self._s2d_buf.shape[0] != N:
+                    self._s2d_buf = torch.empty(N, 115, 115, 16, dtype=torch.bfloat16, device=x.device)
+                s2d = K.stem_s2d_pack(x, self._s2d_buf)
+                c, stem_stats = K.stem_s2d_fwd(s2d, self._stem_w_padded(), want_stats=self.fuse_bn_stats)
+                x_bf16_nhwc = s2d
+            elif self.stem_direct and K.stem_conv_supported(H, W):
                 # straight from the uint8 image: patch tiles are built in shared memory (csrc/stem_conv.cu)
                 c, stem_stats = K.stem_conv_fwd(x, self._stem_w_padded(), want_stats=self.fuse_bn_stats)
                 x_bf16_nhwc = x
@@ -381,7 +391,11 @@ class ResNet50:
         else:
             da = K.maxpool3x3s2_bwd(dh, idx, c.shape)
             dc = self.stem_bn.bwd(da, c, a)
-        if x.dtype == torch.uint8:    # direct stem kernels: patch tiles rebuilt in shared memory
+        if x.dim() == 4 and x.shape[1:] == (115, 115, 16):     # space-to-depth stem: the same TMA tiles as the forward
+            gw = K.stem_s2d_wgrad(x, dc)
+            self.arena.grad("conv1").view(64, 147).copy_(K.stem_weight_unpad(gw))
+            self.reducer_ready(self.stem.g_end)
+        elif x.dtype == torch.uint8:    # direct stem kernels: patch tiles rebuilt in shared memory
             gw = K.stem_conv_wgrad(x, dc)
             self.arena.grad("conv1").view(64, 147).copy_(K.stem_weight_unpad(gw))
             self.reducer_ready(self.stem.g_end)

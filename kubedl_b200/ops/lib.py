@@ -58,6 +58,13 @@ _SIGS = {
                                   C.POINTER(c_float), c_void_p, C.POINTER(c_int), c_void_p]),
     "kdl_stem_conv_wgrad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, C.POINTER(c_float),
                                     C.POINTER(c_float), c_void_p, c_size_t, c_void_p]),
+    "kdl_stem_s2d_image_bytes": (c_size_t, [c_int]),
+    "kdl_stem_s2d_wgrad_scratch_bytes": (c_size_t, []),
+    "kdl_stem_s2d_pack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, C.POINTER(c_float), C.POINTER(c_float),
+                                  c_void_p]),
+    "kdl_stem_s2d_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
+                                 C.POINTER(c_int), c_void_p]),
+    "kdl_stem_s2d_wgrad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "kdl_softmax_xent_workspace_bytes": (c_size_t, [c_int]),
     "kdl_softmax_xent": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                  c_int, c_float, c_void_p, c_size_t, c_void_p]),

@@ -187,6 +187,50 @@ def stem_conv_wgrad(img_u8: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
     return gw
 
 
+def stem_s2d_pack(img_u8: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Normalised, zero-bordered 2x2 space-to-depth form of the uint8 NHWC image: [N, 115, 115, 16] bf16
+    (csrc/stem_s2d.cu).  Written once per step; both stem kernels read their operand tiles from it with TMA."""
+    assert img_u8.dtype == torch.uint8 and img_u8.shape[-1] == 3 and img_u8.is_contiguous()
+    N, H, W, _ = img_u8.shape
+    if out is None:
+        out = torch.empty(N, 115, 115, 16, dtype=torch.bfloat16, device=img_u8.device)
+    assert out.numel() * 2 == L.lib().kdl_stem_s2d_image_bytes(N)
+    L.check(L.lib().kdl_stem_s2d_pack(img_u8.data_ptr(), out.data_ptr(), N, H, W, _IMAGENET_MEAN, _IMAGENET_STD,
+                                      L.stream_ptr()), "kdl_stem_s2d_pack")
+    L.count(1)
+    return out
+
+
+def stem_s2d_fwd(s2d: torch.Tensor, w_padded: torch.Tensor, want_stats: bool = False):
+    """The stem convolution as a 4x4 convolution on the space-to-depth image.  Same contract as stem_conv_fwd."""
+    assert s2d.dtype == torch.bfloat16 and s2d.shape[1:] == (115, 115, 16) and s2d.is_contiguous()
+    assert w_padded.shape == (64, STEM_KP) and w_padded.is_contiguous()
+    N = s2d.shape[0]
+    lib = L.lib()
+    y = torch.empty(N, 112, 112, 64, dtype=torch.bfloat16, device=s2d.device)
+    w2 = workspace(64 * 256 * 2, s2d.device, key="stem_s2d_w2")
+    partial, nparts = None, C.c_int(0)
+    if want_stats:
+        partial = torch.empty(lib.kdl_stem_conv_max_parts(), 2, 64, dtype=torch.float32, device=s2d.device)
+    L.check(lib.kdl_stem_s2d_fwd(s2d.data_ptr(), w_padded.data_ptr(), w2.data_ptr(), y.data_ptr(), N, 224, 224,
+                                 L.ptr(partial), C.byref(nparts), L.stream_ptr()), "kdl_stem_s2d_fwd")
+    L.count(2)
+    return y, ((partial, nparts.value) if want_stats else None)
+
+
+def stem_s2d_wgrad(s2d: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
+    """Weight gradient of the stem from the space-to-depth image, [64, 168] in the padded column layout."""
+    N = s2d.shape[0]
+    assert dy.dtype == torch.bfloat16 and dy.is_contiguous() and dy.numel() == N * 112 * 112 * 64
+    lib = L.lib()
+    ws = workspace(lib.kdl_stem_s2d_wgrad_scratch_bytes(), s2d.device, key="stem_s2d_wgrad")
+    gw = torch.empty(64, STEM_KP, dtype=torch.bfloat16, device=s2d.device)
+    L.check(lib.kdl_stem_s2d_wgrad(s2d.data_ptr(), dy.data_ptr(), gw.data_ptr(), N, 224, 224, ws.data_ptr(), ws.numel(),
+                                   L.stream_ptr()), "kdl_stem_s2d_wgrad")
+    L.count(2)
+    return gw
+
+
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, V: Optional[int] = None,
                  grad_scale: Optional[float] = None, dlogits: Optional[torch.Tensor] = None,
                  loss: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:

@@ -24,3 +24,8 @@ def timeit(fn, iters=8):
     return sorted(ts)[len(ts) // 2]
 print(json.dumps({"stem_fprop_stats_ms": timeit(lambda: K.stem_conv_fwd(img, wp, want_stats=True)),
                   "stem_wgrad_ms": timeit(lambda: K.stem_conv_wgrad(img, y))}))
+# the same layer on the space-to-depth image (csrc/stem_s2d.cu)
+s2d = K.stem_s2d_pack(img)
+print(json.dumps({"s2d_pack_ms": timeit(lambda: K.stem_s2d_pack(img, s2d)),
+                  "s2d_fprop_stats_ms": timeit(lambda: K.stem_s2d_fwd(s2d, wp, want_stats=True)),
+                  "s2d_wgrad_ms": timeit(lambda: K.stem_s2d_wgrad(s2d, y))}))

@@ -205,3 +205,39 @@ def test_stem_direct_conv_matches_patch_gemm(cuda):
     assert _cos(gw, wr.grad.permute(0, 2, 3, 1)) > 0.999
     err = float((gw.float() - wr.grad.permute(0, 2, 3, 1)).abs().max() / wr.grad.abs().max())
     assert err < 2e-2, err
+
+
+@pytest.mark.parametrize("N", [3, 150])
+def test_stem_space_to_depth_conv_matches_conv2d(cuda, N):
+    """The stem as a 4x4 convolution on the 2x2 space-to-depth image, operand tiles read by TMA through a tensor
+    map with overlapping windows (csrc/stem_s2d.cu): the packed image, forward, BN statistics and weight gradient
+    against conv2d; N = 150 gives every CTA one or two tiles, including an image boundary inside a CTA's range."""
+    from kubedl_b200.ops import nn as K
+    torch.manual_seed(0)
+    S = 224
+    img = torch.randint(0, 256, (N, S, S, 3), dtype=torch.uint8, device=cuda)
+    w = (torch.randn(64, 7, 7, 3, device=cuda) * 0.05).bfloat16()
+    wp = K.stem_weight_padded(w)
+    s2d = K.stem_s2d_pack(img)
+    xn = K.u8_normalize(img)                                             # [N,224,224,3] bf16
+    # reference packing: S[n, R+2, C+2, (dy*2+dx)*3+c] = xn[n, 2R+dy, 2C+dx, c], zero elsewhere
+    ref = torch.zeros(N, 115, 115, 16, dtype=torch.bfloat16, device=cuda)
+    ref[:, 2:114, 2:114, :12] = xn.view(N, 112, 2, 112, 2, 3).permute(0, 1, 3, 2, 4, 5).reshape(N, 112, 112, 12)
+    assert torch.equal(s2d, ref)
+    y, (partial, nparts) = K.stem_s2d_fwd(s2d, wp, want_stats=True)
+    wr = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xn.float().permute(0, 3, 1, 2), wr, stride=2, padding=3)
+    torch.testing.assert_close(y.float(), yr.permute(0, 2, 3, 1), atol=5e-2, rtol=3e-2)
+    s = partial[:nparts].sum(0)
+    yf = y.float().view(-1, 64)
+    torch.testing.assert_close(s[0], yf.sum(0), atol=0.5 * N, rtol=1e-3)
+    torch.testing.assert_close(s[1], (yf * yf).sum(0), atol=0.5 * N, rtol=1e-3)
+    dy = torch.randn_like(y)
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    gwp = K.stem_s2d_wgrad(s2d, dy)
+    assert float(gwp.view(64, 7, 24)[:, :, 21:].abs().max()) == 0.0     # padding columns are written as zeros
+    gw = K.stem_weight_unpad(gwp).view(64, 7, 7, 3)
+    assert _cos(gw, wr.grad.permute(0, 2, 3, 1)) > 0.999
+    err = float((gw.float() - wr.grad.permute(0, 2, 3, 1)).abs().max() / wr.grad.abs().max())
+    assert err < 2e-2, err
+    assert torch.equal(gwp, K.stem_s2d_wgrad(s2d, dy))                   # fixed summation order

@@ -314,40 +314,37 @@ __device__ __forceinline__ uint64_t s2d_desc_mn(uint32_t smem_addr, uint32_t lbo
   return d;
 }
 
-// shared-memory map of the wgrad kernel: whole tiles (4 K-blocks, contiguous: the 64-wide N atoms of the B operand
-// are one block apart) and the dy tile that goes with each
-constexpr int kWTiles = 2;
-constexpr int kWOffA = 0;
-constexpr int kWOffDy = kWOffA + kWTiles * 4 * kS2dBlock;
-constexpr int kWOffBar = kWOffDy + kWTiles * 16384;
+// shared-memory map of the wgrad kernel: stages of HALF a tile (64 pixel rows of the four K-blocks, contiguous — the
+// 64-wide M atoms of the A operand are one block apart — and the 64 dy rows that go with them).  Whole tiles left room
+// for two buffers only, and an 80 KB load could not start before the MMA two tiles back had finished.
+constexpr int kWStages = 5;
+constexpr int kWHalf = 64 * 128;                          // one K-block of a half tile: 64 pixel rows x 128 B
+constexpr int kWStageBytes = 5 * kWHalf;                  // four K-blocks + the dy rows
+constexpr int kWOffBar = kWStages * kWStageBytes;
 constexpr int kWSmem = kWOffBar + 256 + 1024;
 
 __global__ void __launch_bounds__(kS2dThreads, 1)
-stem_s2d_wgrad_kernel(const __grid_constant__ CUtensorMap tma_s,    // S as in the forward kernel
-                      const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112][64], box {64, 112}
+stem_s2d_wgrad_kernel(const __grid_constant__ CUtensorMap tma_s,    // S as in the forward kernel, box {64, 64 px}
+                      const __grid_constant__ CUtensorMap tma_dy,   // dy [rows*112][64], box {64, 64}
                       const S2dParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bar = sbase + kWOffBar;
   auto full = [&](int b) { return bar + 8u * b; };
-  auto empty = [&](int b) { return bar + 8u * (kWTiles + b); };
-  auto done = [&]() { return bar + 8u * (2 * kWTiles); };
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + kWOffBar + 8 * (2 * kWTiles + 1));
+  auto empty = [&](int b) { return bar + 8u * (kWStages + b); };
+  auto done = [&]() { return bar + 8u * (2 * kWStages); };
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + kWOffBar + 8 * (2 * kWStages + 1));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 128;     // D^T: two [128, 64] halves
 
-  // rows 112..127 of the dy tiles are K rows of the MMA that no TMA box writes: they stay zero
-  for (int i = threadIdx.x; i < kWTiles * 16384 / 16; i += kS2dThreads)
-    reinterpret_cast<uint4*>(smem + kWOffDy)[i] = make_uint4(0, 0, 0, 0);
-  fence_proxy_async_smem();
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_s) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_dy) : "memory");
   }
   if (warp == 1 && lane == 0) {
-    for (int b = 0; b < kWTiles; ++b) {
+    for (int b = 0; b < kWStages; ++b) {
       mbar_init(full(b), 1);
       mbar_init(empty(b), 1);
     }
@@ -367,40 +364,47 @@ stem_s2d_wgrad_kernel(const __grid_constant__ CUtensorMap tma_s,    // S as in t
   const int row_lo = min((int)blockIdx.x * p.rows_per_cta, p.rows), row_hi = min(row_lo + p.rows_per_cta, p.rows);
 
   if (warp == 0) {
+    // Pixels 112..127 of the second half are outside the image map and arrive as zeros; the dy rows that go with them
+    // belong to the next output row (or are outside the tensor: zeros) and meet only those zeros.
     if (lane == 0) {
-      int iter = 0;
-      for (int row = row_lo; row < row_hi; ++row, ++iter) {
-        const int b = iter % kWTiles;
+      int it = 0;
+      for (int row = row_lo; row < row_hi; ++row) {
         const int n = row / kS2dOW, oh = row - n * kS2dOW;
-        mbar_wait(empty(b), ((iter / kWTiles) & 1) ^ 1);
-        mbar_expect_tx(full(b), 4 * kS2dBlock + kS2dOW * 128);
-        for (int kh = 0; kh < 4; ++kh)
-          tma_load_4d(sbase + kWOffA + (b * 4 + kh) * kS2dBlock, &tma_s, full(b), 0, 0, oh + kh, n);
-        tma_load_2d(sbase + kWOffDy + b * 16384, &tma_dy, full(b), 0, row * kS2dOW);
+        for (int half = 0; half < 2; ++half, ++it) {
+          const int b = it % kWStages;
+          const uint32_t dst = sbase + b * kWStageBytes;
+          mbar_wait(empty(b), ((it / kWStages) & 1) ^ 1);
+          mbar_expect_tx(full(b), kWStageBytes);
+          for (int kh = 0; kh < 4; ++kh) tma_load_4d(dst + kh * kWHalf, &tma_s, full(b), 0, half * 64, oh + kh, n);
+          tma_load_2d(dst + 4 * kWHalf, &tma_dy, full(b), 0, row * kS2dOW + half * 64);
+        }
       }
     }
   } else if (warp == 1) {
     const uint32_t el = elect_one();
     // The gradient is accumulated TRANSPOSED, D[256 space-to-depth columns, 64 output channels], as two M = 128
-    // halves: A = two K-blocks of the tile (MN-major, 64-wide atoms one block apart), B = the dy tile (MN-major,
+    // halves: A = two K-blocks of the stage (MN-major, 64-wide atoms one block apart), B = the dy rows (MN-major,
     // N = 64), K = 16 pixel rows per instruction.  (With M = 64 output channels the tensor core runs at half rate.)
     constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                                ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-    int iter = 0;
-    for (int row = row_lo; row < row_hi; ++row, ++iter) {
-      const int b = iter % kWTiles;
-      mbar_wait(full(b), (iter / kWTiles) & 1);
-      tcgen05_fence_after();
-      const uint64_t bd0 = s2d_desc_mn(sbase + kWOffDy + b * 16384, 0);
+    int it = 0;
+    for (int row = row_lo; row < row_hi; ++row) {
+      for (int half = 0; half < 2; ++half, ++it) {
+        const int b = it % kWStages;
+        const uint32_t src = sbase + b * kWStageBytes;
+        mbar_wait(full(b), (it / kWStages) & 1);
+        tcgen05_fence_after();
+        const uint64_t bd0 = s2d_desc_mn(src + 4 * kWHalf, 0);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const uint64_t ad0 = s2d_desc_mn(sbase + kWOffA + (b * 4 + h * 2) * kS2dBlock, kS2dBlock);
+        for (int h = 0; h < 2; ++h) {
+          const uint64_t ad0 = s2d_desc_mn(src + h * 2 * kWHalf, kWHalf);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_bf16_pred(tmem_base + h * 64, ad0 + (uint64_t)(k * 128), bd0 + (uint64_t)(k * 128), idesc,
-                         (k > 0 || iter > 0) ? 1u : 0u, el);
+          for (int k = 0; k < 4; ++k)
+            umma_bf16_pred(tmem_base + h * 64, ad0 + (uint64_t)(k * 128), bd0 + (uint64_t)(k * 128), idesc,
+                           (k > 0 || it > 0) ? 1u : 0u, el);
+        }
+        umma_commit_pred(empty(b), el);
       }
-      umma_commit_pred(empty(b), el);
     }
     umma_commit_pred(done(), el);
   } else if (warp >= 4) {
@@ -471,11 +475,11 @@ static int s2d_map(CUtensorMap* map, const void* base, int rank, const cuuint64_
 }
 
 // S [N][115][115][16] seen as windows of four pixels: {64 elements, 112 window starts (32 B apart), 115 rows, N}
-static int s2d_image_map(CUtensorMap* map, const void* s2d, int N) {
+static int s2d_image_map(CUtensorMap* map, const void* s2d, int N, uint32_t box_pixels = 128) {
   const cuuint64_t dims[4] = {64, (cuuint64_t)kS2dOW, (cuuint64_t)kS2dP, (cuuint64_t)N};
   const cuuint64_t strides[3] = {(cuuint64_t)kS2dC * 2, (cuuint64_t)kS2dP * kS2dC * 2,
                                  (cuuint64_t)kS2dP * kS2dP * kS2dC * 2};
-  const cuuint32_t box[4] = {64, 128, 1, 1};
+  const cuuint32_t box[4] = {64, box_pixels, 1, 1};
   return s2d_map(map, s2d, 4, dims, strides, box, "space-to-depth image");
 }
 
@@ -573,8 +577,8 @@ extern "C" int kdl_stem_s2d_wgrad(const void* s2d, const void* dy, void* gw_padd
   }
   p.partial = (float*)scratch;
   CUtensorMap ms, mdy;
-  if ((rc = s2d_image_map(&ms, s2d, N))) return rc;
-  if ((rc = s2d_matrix_map(&mdy, dy, 64, (uint64_t)p.rows * kS2dOW, 64, kS2dOW, "dy"))) return rc;
+  if ((rc = s2d_image_map(&ms, s2d, N, 64))) return rc;
+  if ((rc = s2d_matrix_map(&mdy, dy, 64, (uint64_t)p.rows * kS2dOW, 64, 64, "dy"))) return rc;
   static bool attr = false;
   if (!attr) {
     KDL_CUDA(cudaFuncSetAttribute(stem_s2d_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmem));

@@ -264,8 +264,9 @@ class ResNet50:
         # stem convolution straight from the uint8 image (224x224 inputs); 0: im2col patch matrix + GEMM
         self.stem_direct = _os.environ.get("KUBEDL_STEM_DIRECT", "1") == "1"
         # the stem as a 4x4 convolution on a space-to-depth copy of the image (csrc/stem_s2d.cu): operand tiles come
-        # from TMA instead of being built by threads
-        self.stem_s2d = _os.environ.get("KUBEDL_STEM_S2D", "0") == "1"
+        # from TMA instead of being built by threads.  Pack 0.03 + forward 0.19 + wgrad 0.17 ms against 0.33 + 0.30 for
+        # the direct kernels; 18.85 -> 18.69 ms/step on the same box.  KUBEDL_STEM_S2D=0 selects the direct kernels.
+        self.stem_s2d = _os.environ.get("KUBEDL_STEM_S2D", "1") == "1"
         self._s2d_buf = None
         self.fuse_stem_pool = _os.environ.get("KUBEDL_FUSE_STEM_POOL", "1") == "1"
         self.fuse_stem_pool_bwd = _os.environ.get("KUBEDL_FUSE_STEM_POOL_BWD", "0") == "1"

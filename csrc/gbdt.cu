@@ -344,46 +344,78 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const int32_t*
   for (int i = threadIdx.x; i < nodes; i += kPartThreads) block_counts[(size_t)i * gridDim.x + blockIdx.x] = cnt[i];
 }
 
-// exclusive scan of block_counts (node-major: [nodes][B]) in place; seg[v] = first slot of node v
-__global__ void __launch_bounds__(1024) part_scan_kernel(int32_t* __restrict__ block_counts, int total, int B,
-                                                         int nodes, int32_t* __restrict__ seg,
-                                                         int32_t* __restrict__ counts) {
-  __shared__ int partial[1024];
-  const int per = (total + 1023) / 1024;
-  const int lo = min((int)threadIdx.x * per, total), hi = min(lo + per, total);
+// Exclusive scan of block_counts (node-major: [nodes][B]) in two small launches: every node's B block counts are
+// scanned in place by a block of their own (prefix inside the node), then one block scans the <= 256 node totals into
+// seg[] / counts[].  (One 1024-thread block used to walk all nodes x B entries — up to 300 k — which took 37 us per
+// level whatever the number of rows, a quarter of a boosting round at 8 GPUs.)
+__global__ void __launch_bounds__(256) part_scan_node_kernel(int32_t* __restrict__ block_counts, int B,
+                                                            int32_t* __restrict__ node_total) {
+  __shared__ int wsum[8];
+  int32_t* row = block_counts + (size_t)blockIdx.x * B;
+  const int per = (B + 255) / 256;
+  const int lo = min((int)threadIdx.x * per, B), hi = min(lo + per, B);
   int sum = 0;
-  for (int i = lo; i < hi; ++i) sum += block_counts[i];
-  partial[threadIdx.x] = sum;
-  __syncthreads();
-  for (int off = 1; off < 1024; off <<= 1) {      // Hillis-Steele inclusive scan
-    int v = threadIdx.x >= off ? partial[threadIdx.x - off] : 0;
-    __syncthreads();
-    partial[threadIdx.x] += v;
-    __syncthreads();
+  for (int i = lo; i < hi; ++i) sum += row[i];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = sum;                                    // inclusive scan of the 256 per-thread sums
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, inc, off);
+    if (lane >= off) inc += v;
   }
-  int run = partial[threadIdx.x] - sum;
+  if (lane == 31) wsum[w] = inc;
+  __syncthreads();
+  int before = 0, total = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (k < w) before += wsum[k];
+    total += wsum[k];
+  }
+  int run = before + inc - sum;
   for (int i = lo; i < hi; ++i) {
-    const int c = block_counts[i];
-    block_counts[i] = run;
+    const int c = row[i];
+    row[i] = run;
     run += c;
   }
-  __syncthreads();
-  const int n_all = partial[1023];
-  for (int v = threadIdx.x; v <= nodes; v += 1024) seg[v] = v < nodes ? block_counts[(size_t)v * B] : n_all;
-  __syncthreads();
-  for (int v = threadIdx.x; v < nodes; v += 1024) {
-    const int a = block_counts[(size_t)v * B];
-    const int b = v + 1 < nodes ? block_counts[(size_t)(v + 1) * B] : n_all;
-    counts[v] = b - a;
+  if (threadIdx.x == 0) node_total[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kPartMaxNodes) part_scan_final_kernel(const int32_t* __restrict__ node_total,
+                                                                       int nodes, int32_t* __restrict__ seg,
+                                                                       int32_t* __restrict__ counts) {
+  __shared__ int wsum[kPartMaxNodes / 32];
+  const int v = threadIdx.x;
+  const int c = v < nodes ? node_total[v] : 0;
+  const int lane = v & 31, w = v >> 5;
+  int inc = c;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, inc, off);
+    if (lane >= off) inc += u;
   }
+  if (lane == 31) wsum[w] = inc;
+  __syncthreads();
+  int before = 0, total = 0;
+#pragma unroll
+  for (int k = 0; k < kPartMaxNodes / 32; ++k) {
+    if (k < w) before += wsum[k];
+    total += wsum[k];
+  }
+  if (v < nodes) {
+    seg[v] = before + inc - c;
+    counts[v] = c;
+  }
+  if (v == 0) seg[nodes] = total;
 }
 
 __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const int32_t* __restrict__ node_of_row,
                                                                    int64_t n, int nodes, int64_t chunk,
                                                                    const int32_t* __restrict__ block_offsets,
+                                                                   const int32_t* __restrict__ seg,
                                                                    int32_t* __restrict__ ridx) {
   __shared__ int offs[kPartMaxNodes];
-  for (int i = threadIdx.x; i < nodes; i += kPartThreads) offs[i] = block_offsets[(size_t)i * gridDim.x + blockIdx.x];
+  for (int i = threadIdx.x; i < nodes; i += kPartThreads)       // node start + this block's prefix inside the node
+    offs[i] = seg[i] + block_offsets[(size_t)i * gridDim.x + blockIdx.x];
   __syncthreads();
   const int64_t lo = (int64_t)blockIdx.x * chunk;
   const int64_t hi = min(lo + chunk, n);
@@ -496,7 +528,9 @@ extern "C" int kdl_gbdt_update_pred(float* pred, const int32_t* node_of_row, con
 // Rows grouped by node: ridx[n] (row ids, node-major), seg[nodes+1] (first slot of every node),
 // counts[nodes].  workspace: kdl_gbdt_partition_workspace_bytes(nodes) bytes.
 static int part_blocks() { return 148 * 8; }
-extern "C" size_t kdl_gbdt_partition_workspace_bytes(int nodes) { return (size_t)nodes * part_blocks() * sizeof(int32_t); }
+extern "C" size_t kdl_gbdt_partition_workspace_bytes(int nodes) {
+  return ((size_t)nodes * part_blocks() + kPartMaxNodes) * sizeof(int32_t);
+}
 extern "C" int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nodes, int32_t* ridx, int32_t* seg,
                                   int32_t* counts, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   if (nodes < 1 || nodes > kPartMaxNodes) {
@@ -508,7 +542,7 @@ extern "C" int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nod
     return KDL_ERR_UNSUPPORTED;
   }
   const int B = part_blocks();
-  if (workspace == nullptr || workspace_bytes < (size_t)nodes * B * sizeof(int32_t)) {
+  if (workspace == nullptr || workspace_bytes < ((size_t)nodes * B + kPartMaxNodes) * sizeof(int32_t)) {
     kdl_set_error("gbdt partition: workspace too small");
     return KDL_ERR_WORKSPACE;
   }
@@ -516,9 +550,12 @@ extern "C" int kdl_gbdt_partition(const int32_t* node_of_row, int64_t n, int nod
   int32_t* bc = (int32_t*)workspace;
   part_count_kernel<<<B, kPartThreads, 0, stream>>>(node_of_row, n, nodes, chunk, bc);
   KDL_CHECK_LAUNCH();
-  part_scan_kernel<<<1, 1024, 0, stream>>>(bc, nodes * B, B, nodes, seg, counts);
+  int32_t* node_total = bc + (size_t)nodes * B;
+  part_scan_node_kernel<<<nodes, 256, 0, stream>>>(bc, B, node_total);
   KDL_CHECK_LAUNCH();
-  part_scatter_kernel<<<B, kPartThreads, 0, stream>>>(node_of_row, n, nodes, chunk, bc, ridx);
+  part_scan_final_kernel<<<1, kPartMaxNodes, 0, stream>>>(node_total, nodes, seg, counts);
+  KDL_CHECK_LAUNCH();
+  part_scatter_kernel<<<B, kPartThreads, 0, stream>>>(node_of_row, n, nodes, chunk, bc, seg, ridx);
   KDL_CHECK_LAUNCH();
   return KDL_OK;
 }

@@ -158,7 +158,7 @@ class GBDTTrainer:
         L.check(lib.kdl_gbdt_partition(self.node.data_ptr(), self.n, nodes, self._ridx.data_ptr(), seg.data_ptr(),
                                        counts.data_ptr(), self._part_ws.data_ptr(), self._part_ws.numel(),
                                        L.stream_ptr()), "kdl_gbdt_partition")
-        L.count(3)
+        L.count(4)
         return self._ridx, seg, counts
 
     def _build_hist(self, ridx, seg, build, nbuild) -> torch.Tensor:

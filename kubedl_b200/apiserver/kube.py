@@ -271,12 +271,13 @@ class _Reflector:
         self.synced = threading.Event()
         self.stopping = threading.Event()
         self.relists = 0
+        self.shared: set = set()
         self._conn: Optional[http.client.HTTPConnection] = None
         self.thread = threading.Thread(target=self._run, name=f"reflector-{kind}", daemon=True)
         self.thread.start()
 
     # -- handler management
-    def add(self, handler: WatchHandler, replay: bool) -> Callable[[], None]:
+    def add(self, handler: WatchHandler, replay: bool, shared: bool = False) -> Callable[[], None]:
         if not self.synced.wait(self.client.sync_timeout):
             raise st.Timeout(f"timed out waiting for the {self.kind} cache to sync")
         with self.lock:
@@ -284,11 +285,14 @@ class _Reflector:
                 for o in list(self.cache.values()):
                     handler(ADDED, _copy(o), None)
             self.handlers.append(handler)
+            if shared:
+                self.shared.add(handler)
 
         def stop():
             with self.lock:
                 if handler in self.handlers:
                     self.handlers.remove(handler)
+                self.shared.discard(handler)
         return stop
 
     def _emit(self, ev: str, obj: dict) -> None:
@@ -305,9 +309,15 @@ class _Reflector:
                     return                      # replayed by a re-list / re-watch, nothing new
                 ev = MODIFIED if old is not None else ADDED
                 self.cache[key] = obj
+            snap = None
             for h in list(self.handlers):
                 try:
-                    h(ev, _copy(obj), _copy(old) if old is not None else None)
+                    if h in self.shared:        # read-only handlers share one snapshot (store.APIServer.watch)
+                        if snap is None:
+                            snap = (_copy(obj), _copy(old) if old is not None else None)
+                        h(ev, snap[0], snap[1])
+                    else:
+                        h(ev, _copy(obj), _copy(old) if old is not None else None)
                 except Exception as e:          # a handler must not take the reflector down
                     log.error("watch handler for %s failed: %r", self.kind, e)
 
@@ -589,12 +599,12 @@ class KubeAPIServer:
             return self.update(merged)
 
     # ------------------------------------------------------------------ watch
-    def watch(self, kind: str, handler: WatchHandler, replay: bool = True) -> Callable[[], None]:
+    def watch(self, kind: str, handler: WatchHandler, replay: bool = True, shared: bool = False) -> Callable[[], None]:
         with self._lock:
             r = self._reflectors.get(kind)
             if r is None:
                 r = self._reflectors[kind] = _Reflector(self, kind)
-        return r.add(handler, replay)
+        return r.add(handler, replay, shared)
 
     def reflector(self, kind: str) -> Optional[_Reflector]:
         return self._reflectors.get(kind)

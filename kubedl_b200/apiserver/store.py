@@ -68,6 +68,7 @@ class APIServer:
         self._objs: Dict[str, Dict[Tuple[str, str], dict]] = collections.defaultdict(dict)
         self._rv = 0
         self._watchers: Dict[str, List[WatchHandler]] = collections.defaultdict(list)
+        self._shared_handlers: set = set()        # handlers that take read-only snapshots (watch(shared=True))
         self._pending: Deque[Tuple[str, str, dict, Optional[dict]]] = collections.deque()
         self._dispatch_lock = threading.RLock()
         self._dispatching = threading.local()
@@ -301,12 +302,19 @@ class APIServer:
                 pass
 
     # ------------------------------------------------------------------ watch
-    def watch(self, kind: str, handler: WatchHandler, replay: bool = True) -> Callable[[], None]:
+    def watch(self, kind: str, handler: WatchHandler, replay: bool = True, shared: bool = False) -> Callable[[], None]:
         """Register a watch.  With replay=True the handler first receives ADDED for every
-        existing object (informer LIST+WATCH).  Returns an unsubscribe function."""
+        existing object (informer LIST+WATCH).  Returns an unsubscribe function.
+
+        shared=True is a promise that the handler only READS (or stores, never mutates) the objects it is handed:
+        all such handlers of an event get the same snapshot instead of a private copy each.  With six watchers on
+        Pod (four controllers, the informer cache, the node agent) the private copies were a third of all object
+        copies made for a job; client-go's informers make the same deal (objects from a shared informer are read-only)."""
         with self._lock:
             existing = [_copy(o) for o in self._objs[kind].values()] if replay else []
             self._watchers[kind].append(handler)
+            if shared:
+                self._shared_handlers.add(handler)
         for o in existing:
             handler(ADDED, o, None)
 
@@ -314,6 +322,7 @@ class APIServer:
             with self._lock:
                 if handler in self._watchers[kind]:
                     self._watchers[kind].remove(handler)
+                self._shared_handlers.discard(handler)
         return stop
 
     def _dispatch(self) -> None:
@@ -327,9 +336,15 @@ class APIServer:
                         if not self._pending:
                             break
                         kind, ev, obj, old = self._pending.popleft()
-                        handlers = list(self._watchers.get(kind, ()))
-                    for h in handlers:
-                        h(ev, _copy(obj), _copy(old) if old is not None else None)
+                        handlers = [(h, h in self._shared_handlers) for h in self._watchers.get(kind, ())]
+                    snap = None
+                    for h, shared in handlers:
+                        if shared:
+                            if snap is None:         # one read-only snapshot for every handler that asked for it
+                                snap = (_copy(obj), _copy(old) if old is not None else None)
+                            h(ev, snap[0], snap[1])
+                        else:
+                            h(ev, _copy(obj), _copy(old) if old is not None else None)
             finally:
                 self._dispatching.active = False
 

@@ -275,8 +275,8 @@ class Gpulet:
     def start(self) -> None:
         if self.zygote is not None:
             self.zygote.start()
-        self._unwatch.append(self.api.watch("Pod", self._on_pod, replay=True))
-        self._unwatch.append(self.api.watch("PodGroup", lambda *a: self._kick(), replay=False))
+        self._unwatch.append(self.api.watch("Pod", self._on_pod, replay=True, shared=True))     # pods are only read
+        self._unwatch.append(self.api.watch("PodGroup", lambda *a: self._kick(), replay=False, shared=True))
         t = threading.Thread(target=self._loop, name="gpulet", daemon=True)
         t.start()
         self._threads.append(t)

@@ -83,7 +83,7 @@ class Client:
                     self._cache[kind].pop(key, None)
                 elif not _older(obj, self._cache[kind].get(key)):
                     self._cache[kind][key] = obj
-        self._stops.append(self.api.watch(kind, on_event, replay=True))
+        self._stops.append(self.api.watch(kind, on_event, replay=True, shared=True))   # cache entries are never mutated
 
     def _remember(self, obj: dict) -> dict:
         """Read-your-writes: what a write returned goes into the cache at once if it is newer than
@@ -268,7 +268,8 @@ class Controller:
     def start_watches(self) -> None:
         for kind, handler, pred in self._watches:
             self.manager.client.ensure_informer(kind)
-            self._stops.append(self.manager.api.watch(kind, self._on_event(handler, pred), replay=True))
+            # predicates and request mappers only read the objects of an event
+            self._stops.append(self.manager.api.watch(kind, self._on_event(handler, pred), replay=True, shared=True))
 
     def process_one(self, block: bool = False, timeout: Optional[float] = None) -> bool:
         req, shutdown = self.queue.get(block=block, timeout=timeout)

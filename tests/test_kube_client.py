@@ -670,3 +670,27 @@ def test_bearer_token_guards_the_api(tmp_path, capsys):
         for cli in (anon, bad, good):
             cli.close()
         srv.shutdown()
+
+
+def test_shared_watchers_get_one_snapshot_private_ones_a_copy_each(remote):
+    """watch(shared=True): read-only handlers of an event are handed the same object; every other handler still gets
+    a copy of its own, and what it does to that copy reaches neither the other handlers nor the server.  Same contract
+    on the in-process store and on the remote client."""
+    api, srv, cli = remote
+    for server in (api, cli):
+        a, b, priv = [], [], []
+        stops = [server.watch("Pod", lambda ev, obj, old: a.append(obj), replay=False, shared=True),
+                 server.watch("Pod", lambda ev, obj, old: b.append(obj), replay=False, shared=True)]
+
+        def vandal(ev, obj, old):
+            priv.append(obj)
+            obj["metadata"]["labels"] = {"scribbled": "yes"}
+        stops.append(server.watch("Pod", vandal, replay=False))
+        name = "s-" + type(server).__name__.lower()
+        api.create(pod(name))
+        wait_for(lambda: a and b and priv, what="watch events")
+        assert a[0] is b[0] and priv[0] is not a[0]
+        assert "scribbled" not in (a[0]["metadata"].get("labels") or {})
+        assert "scribbled" not in (api.get("Pod", "default", name)["metadata"].get("labels") or {})
+        for s in stops:
+            s()

@@ -53,6 +53,8 @@ _VAR = re.compile(r"\$\(([A-Za-z_][A-Za-z0-9_]*)\)")
 
 def expand_vars(s: str, env: Dict[str, str]) -> str:
     """Kubernetes `$(VAR)` expansion; `$$(VAR)` escapes; unknown names are left as is."""
+    if "$(" not in s:
+        return s
     out, i = [], 0
     while i < len(s):
         if s.startswith("$$(", i):
@@ -70,6 +72,18 @@ def expand_vars(s: str, env: Dict[str, str]) -> str:
             out.append(s[i])
             i += 1
     return "".join(out)
+
+
+class _LazyServiceNames:
+    """`name in services-of-the-namespace`, listing the services on first use only."""
+
+    def __init__(self, agent, ns: str):
+        self._agent, self._ns, self._names = agent, ns, None
+
+    def __contains__(self, name: str) -> bool:
+        if self._names is None:
+            self._names = self._agent._service_names(self._ns)
+        return name in self._names
 
 
 class ImageRegistry:
@@ -186,6 +200,8 @@ class Gpulet:
         # restart back-off for Always / OnFailure, the kubelet's numbers: first restart at once, then
         # 10 s doubling to 5 min, forgotten after 10 min of clean running
         self.restart_backoff = (float(os.environ.get("KUBEDL_GPULET_RESTART_BACKOFF_SECONDS", "10")), 300.0, 600.0)
+        self._endpoint_pats: Dict[str, "re.Pattern"] = {}
+        self._env_cache = None
         self._stop = threading.Event()
         self._wake = threading.Event()          # set by the watches; the loop otherwise ticks every 10 ms (reaping)
         self._threads: List[threading.Thread] = []
@@ -562,7 +578,7 @@ class Gpulet:
         def repl(m):
             host, port = m.group(1), m.group(3)
             short = host.split(".")[0]
-            if short not in svc_names and not host.startswith(job + "-"):
+            if not host.startswith(job + "-") and short not in svc_names:
                 return m.group(0)
             out = "127.0.0.1"
             if port:
@@ -570,21 +586,40 @@ class Gpulet:
                 # declares the same port on a different DNS name and must stay distinguishable
                 out += ":" + str(self._host_port(ns, short, int(port)))
             return out
-        pat = re.compile(r"\b(" + re.escape(job) + r"-[a-z0-9]+-\d+(\.[A-Za-z0-9.\-]+)?)(?::(\d+))?")
+        if job not in value:
+            return value
+        pat = self._endpoint_pats.get(job)
+        if pat is None:
+            if len(self._endpoint_pats) > 256:
+                self._endpoint_pats.clear()
+            pat = self._endpoint_pats[job] = re.compile(r"\b(" + re.escape(job) + r"-[a-z0-9]+-\d+(\.[A-Za-z0-9.\-]+)?)(?::(\d+))?")
         return pat.sub(repl, value)
+
+    def _base_env(self) -> Dict[str, str]:
+        """The agent's own environment as a dict, decoded once and again only when it has changed (building a pod's
+        environment used to decode all of os.environ per pod: with eight pods starting at once that and the rest of
+        build_env were ~15 ms of interpreter time, most of the all-pods launch delay)."""
+        raw = getattr(os.environ, "_data", None)
+        if raw is None:
+            return dict(os.environ)
+        if self._env_cache is None or self._env_cache[0] != raw:
+            base = dict(os.environ)
+            base["PYTHONPATH"] = os.pathsep.join(filter(None, [os.getcwd(), base.get("PYTHONPATH", "")]))
+            self._env_cache = (dict(raw), base)
+        return dict(self._env_cache[1])
 
     def build_env(self, pod: dict, container: dict, gpu: Optional[int]) -> Dict[str, str]:
         ns = c.namespace_of(pod)
         job = c.labels_of(pod).get(c.JOB_NAME_LABEL, "")
-        svc_names = self._service_names(ns)
-        env = dict(os.environ)
-        env["PYTHONPATH"] = os.pathsep.join(filter(None, [os.getcwd(), env.get("PYTHONPATH", "")]))
+        svc_names = _LazyServiceNames(self, ns)      # only a host that does not carry the job's name needs the list
+        env = self._base_env()
         declared: Dict[str, str] = {}
         for e in container.get("env") or []:
             if "value" in e:
-                declared[e["name"]] = expand_vars(str(e["value"]), {**env, **declared})
+                v = str(e["value"])
+                declared[e["name"]] = expand_vars(v, {**env, **declared}) if "$(" in v else v
         for name, v in list(declared.items()):
-            v2 = self._rewrite_endpoint(v, ns, job, svc_names)
+            v2 = self._rewrite_endpoint(v, ns, job, svc_names) if job else v
             if name == "MASTER_ADDR" and v2 == "localhost":
                 v2 = "127.0.0.1"
             declared[name] = v2

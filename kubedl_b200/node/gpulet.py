@@ -706,7 +706,8 @@ class Gpulet:
         self.launched += 1
         if self._start_hist is not None:
             self._start_hist.observe(time.perf_counter() - t_launch)
-            self._launched_total.labels(self.node_name, "fork" if not isinstance(popen, subprocess.Popen) else "exec").inc()
+            how = "exec" if isinstance(popen, subprocess.Popen) else ("adopt" if getattr(popen, "adopted", False) else "fork")
+            self._launched_total.labels(self.node_name, how).inc()
         ready = c.now_precise()
         self._set_status(pod, c.POD_RUNNING, conditions=[
             {"type": "PodScheduled", "status": "True", "lastTransitionTime": now},

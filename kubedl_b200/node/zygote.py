@@ -404,6 +404,7 @@ class ZygoteProc:
 
     def __init__(self, pid: int):
         self.pid = pid
+        self.adopted = False                # True: a worker that was waiting with its GPU initialised became this pod
         self.returncode: Optional[int] = None
         self._done = threading.Event()
 
@@ -600,6 +601,7 @@ class ZygoteClient:
                 self.warm_workers.pop(gpu, None)
                 if msg.get("warm"):
                     self.adopted += 1
+                    child.adopted = True
             if pid in self._early_exits:
                 child._finish(self._early_exits.pop(pid))
             else:

@@ -169,7 +169,9 @@ def test_node_agent_keeps_a_warm_worker_per_free_gpu(tmp_path):
     mgr = Manager()
     gang_schedule.register_gang_schedulers(mgr)
     setup_with_manager(mgr, JobControllerConfiguration(), "*", CollectorRegistry())
-    let = Gpulet(mgr.api, num_gpus=2, log_dir=str(tmp_path / "pods"), warm_gpus=True, default_gpu_per_pod=True)
+    reg = CollectorRegistry()
+    let = Gpulet(mgr.api, num_gpus=2, log_dir=str(tmp_path / "pods"), warm_gpus=True, default_gpu_per_pod=True,
+                 metrics_registry=reg)
     let.zygote.preload = ("json", "kubedl_b200.worker.rendezvous")
     mgr.start()
     let.start()
@@ -185,6 +187,7 @@ def test_node_agent_keeps_a_warm_worker_per_free_gpu(tmp_path):
             return [x["type"] for x in s.get("conditions", [])][-1:] == ["Succeeded"]
         _wait(done, timeout=60)
         assert let.zygote.adopted == 2 and let.zygote.spawned == 2          # both pods were adoptions
+        assert reg.get_sample_value("kubedl_gpulet_pods_launched_total", {"node": let.node_name, "how": "adopt"}) == 2
         # the GPUs came back, and each got a NEW waiting worker
         _wait(lambda: sorted(g for g, w in let.zygote.warm_workers.items() if w["state"] == "ready") == [0, 1])
         again = {g: w["pid"] for g, w in let.zygote.warm_workers.items()}

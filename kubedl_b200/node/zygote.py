@@ -433,6 +433,7 @@ class ZygoteClient:
         self._proc: Optional[subprocess.Popen] = None
         self._sock: Optional[socket.socket] = None
         self._lock = threading.Lock()
+        self._send_lock = threading.Lock()
         self._next_id = 0
         self._pending: Dict[int, dict] = {}
         self._replies: Dict[int, threading.Event] = {}
@@ -443,6 +444,20 @@ class ZygoteClient:
         self.warm_workers: Dict[int, dict] = {}
         self.adopted = 0                     # pods that took over a waiting worker instead of forking
         self.on_ready = []                   # callbacks run once the launcher answers (e.g. warm every free GPU)
+
+    def _send(self, msg: dict) -> bool:
+        """One request line to the launcher.  Serialised by a lock of its own: the state lock must stay free for the
+        reader thread while a send blocks on a full socket buffer (the launcher may itself be blocked sending replies)."""
+        sock = self._sock
+        if sock is None:
+            return False
+        data = json.dumps(msg).encode() + b"\n"
+        try:
+            with self._send_lock:
+                sock.sendall(data)
+            return True
+        except OSError:
+            return False
 
     def start(self) -> None:
         env = dict(self._env if self._env is not None else os.environ)
@@ -543,23 +558,18 @@ class ZygoteClient:
             if gpu in self.warm_workers:
                 return True
             self.warm_workers[gpu] = {"pid": None, "state": "warming", "sig": self.cuda_signature(base_env)}
-            try:
-                self._sock.sendall(json.dumps({"op": "warm", "gpu": gpu, "device": device,
-                                               "env": cuda_env or {}}).encode() + b"\n")
-            except OSError:
+        if not self._send({"op": "warm", "gpu": gpu, "device": device, "env": cuda_env or {}}):
+            with self._lock:
                 self.warm_workers.pop(gpu, None)
-                return False
+            return False
         return True
 
     def drop(self, gpu: int) -> None:
         """Send the worker waiting on `gpu` away (the GPU goes to a process that cannot be an adoption)."""
         with self._lock:
-            if self.warm_workers.pop(gpu, None) is None or self._sock is None:
+            if self.warm_workers.pop(gpu, None) is None:
                 return
-            try:
-                self._sock.sendall(json.dumps({"op": "drop", "gpu": gpu}).encode() + b"\n")
-            except OSError:
-                pass
+        self._send({"op": "drop", "gpu": gpu})
 
     def spawn(self, argv: List[str], env: Dict[str, str], log_path: str, cwd: Optional[str] = None,
               timeout: float = 10.0, gpu: Optional[int] = None) -> Optional[ZygoteProc]:
@@ -581,11 +591,10 @@ class ZygoteClient:
             req = {"op": "spawn", "id": rid, "argv": argv[1:], "env": env, "log": log_path, "cwd": cwd}
             if gpu is not None:
                 req["gpu"] = gpu
-            try:
-                self._sock.sendall(json.dumps(req).encode() + b"\n")
-            except OSError:
+        if not self._send(req):
+            with self._lock:
                 self._replies.pop(rid, None)
-                return None
+            return None
         if not ev.wait(timeout):
             if gpu is not None:
                 self.drop(gpu)

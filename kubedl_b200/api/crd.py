@@ -160,14 +160,15 @@ def _validator(kind: str):
     """One compiled validator per kind.  `jsonschema.validate(doc, schema)` re-generates nothing here but re-checks
     the schema against its metaschema on EVERY call, which cost ~10 ms per job create — more than the reconcile
     that follows; the schema of a kind never changes inside a process."""
-    v = _VALIDATORS.get(kind)
-    if v is None:
+    info = SCHEME.info(kind)
+    hit = _VALIDATORS.get(kind)
+    if hit is None or hit[0] is not info:         # a kind registered again (custom workloads, tests) gets a new validator
         import jsonschema
-        schema = crd_for(SCHEME.info(kind))["spec"]["validation"]["openAPIV3Schema"]
+        schema = crd_for(info)["spec"]["validation"]["openAPIV3Schema"]
         cls = jsonschema.validators.validator_for(schema)
         cls.check_schema(schema)
-        v = _VALIDATORS[kind] = cls(schema)
-    return v
+        hit = _VALIDATORS[kind] = (info, cls(schema))
+    return hit[1]
 
 
 def validate(obj: dict) -> None:

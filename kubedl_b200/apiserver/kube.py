@@ -315,6 +315,8 @@ class _Reflector:
                     if h in self.shared:        # read-only handlers share one snapshot (store.APIServer.watch)
                         if snap is None:
                             snap = (_copy(obj), _copy(old) if old is not None else None)
+                            if st._FREEZE_SNAPSHOTS:
+                                snap = (st._freeze(snap[0]), st._freeze(snap[1]) if snap[1] is not None else None)
                         h(ev, snap[0], snap[1])
                     else:
                         h(ev, _copy(obj), _copy(old) if old is not None else None)

@@ -22,6 +22,38 @@ from ..api.kinds import SCHEME
 ADDED, MODIFIED, DELETED = "ADDED", "MODIFIED", "DELETED"
 
 
+class _Frozen:
+    """Mix-in that turns every mutator of dict / list into an error (KUBEDL_FREEZE_SNAPSHOTS=1)."""
+
+    def _ro(self, *a, **k):
+        raise TypeError("a shared watch snapshot was modified by a handler registered with shared=True")
+    __setitem__ = __delitem__ = clear = pop = popitem = setdefault = update = _ro
+    append = extend = insert = remove = sort = reverse = __iadd__ = __imul__ = _ro
+
+
+class _FrozenDict(_Frozen, dict):
+    def __deepcopy__(self, memo):            # a copy is an ordinary, writable dict again
+        return {k: copy.deepcopy(v, memo) for k, v in self.items()}
+
+
+class _FrozenList(_Frozen, list):
+    def __deepcopy__(self, memo):
+        return [copy.deepcopy(v, memo) for v in self]
+
+
+def _freeze(o):
+    """Deep read-only view (a copy) of a JSON tree: what shared watchers get when KUBEDL_FREEZE_SNAPSHOTS=1, so that a
+    handler that breaks the shared=True promise fails loudly in the tests instead of corrupting its neighbours."""
+    if isinstance(o, dict):
+        return _FrozenDict({k: _freeze(v) for k, v in o.items()})
+    if isinstance(o, list):
+        return _FrozenList([_freeze(v) for v in o])
+    return o
+
+
+_FREEZE_SNAPSHOTS = __import__("os").environ.get("KUBEDL_FREEZE_SNAPSHOTS", "0") == "1"
+
+
 class ApiError(Exception):
     reason = "InternalError"
     code = 500
@@ -342,6 +374,8 @@ class APIServer:
                         if shared:
                             if snap is None:         # one read-only snapshot for every handler that asked for it
                                 snap = (_copy(obj), _copy(old) if old is not None else None)
+                                if _FREEZE_SNAPSHOTS:
+                                    snap = (_freeze(snap[0]), _freeze(snap[1]) if snap[1] is not None else None)
                             h(ev, snap[0], snap[1])
                         else:
                             h(ev, _copy(obj), _copy(old) if old is not None else None)

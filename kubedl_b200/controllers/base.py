@@ -69,6 +69,7 @@ class BaseJobReconciler(ControllerInterface):
         """Default the new job, stamp the Created condition, count it (reference
         controllers/pytorch/status.go:127-146).  The reference mutates the informer-cache copy and
         relies on the first status write to persist it; we persist it right away."""
+        job = c.deepcopy(job)        # the event object is a snapshot shared with the other watchers: never written to
         SCHEME.default(job)
         status = c.status_of(job)
         if not st.has_condition(status, c.JOB_CREATED):

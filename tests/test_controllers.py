@@ -446,3 +446,23 @@ def test_created_condition_is_added_not_overwritten():
     cl.settle()
     st_ = cl.job("PyTorchJob", "ns", "pt")["status"]
     assert st_["conditions"][0]["type"] == "Created" and st_.get("startTime") == "2026-01-01T00:00:00Z"
+
+
+def test_no_watcher_writes_to_the_shared_event_snapshot(monkeypatch):
+    """Watchers registered with shared=True (informer cache, controllers, node agent) are handed ONE snapshot per event.
+    With the snapshots frozen, a job of every kind goes through create -> pods Running -> Succeeded without any handler
+    trying to write to what it was handed (on_owner_create used to default the event's job in place)."""
+    from kubedl_b200.apiserver import store
+    monkeypatch.setattr(store, "_FREEZE_SNAPSHOTS", True)
+    from kubedl_b200.bench.launch_delay import _job
+    cl = Cluster()
+    for kind in ("PyTorchJob", "TFJob", "XGBoostJob", "XDLJob"):
+        name = "frozen-" + kind.lower()
+        cl.submit(_job(kind, name, 3, 0.0))
+        assert ("Created", "True") in cl.conditions(kind, "bench", name)
+        cl.kubelet.set_all("bench", c.POD_RUNNING, {c.JOB_NAME_LABEL: name})
+        cl.settle()
+        cl.kubelet.set_all("bench", c.POD_SUCCEEDED, {c.JOB_NAME_LABEL: name})
+        cl.settle()
+        assert cl.conditions(kind, "bench", name)[-1] == ("Succeeded", "True"), cl.conditions(kind, "bench", name)
+    assert sum(r.controller.error_count for r in cl.recs.values()) == 0

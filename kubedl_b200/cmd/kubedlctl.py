@@ -74,7 +74,7 @@ def _age(ts: Optional[str]) -> str:
     return f"{s}s" if s < 120 else (f"{s // 60}m" if s < 7200 else f"{s // 3600}h")
 
 
-def print_table(kind: str, items: List[dict]) -> None:
+def print_table(kind: str, items: List[dict], header: bool = True) -> None:
     if SCHEME.is_workload(kind):
         # printer columns of the CRDs (reference config/crd/bases/kubeflow.org_pytorchjobs.yaml:11-32)
         rows = [("NAME", "STATE", "AGE", "FINISHED-TTL", "MAX-LIFETIME")]
@@ -99,8 +99,34 @@ def print_table(kind: str, items: List[dict]) -> None:
     else:
         rows = [("NAME", "AGE")] + [(c.name_of(o), _age(o["metadata"].get("creationTimestamp"))) for o in items]
     w = [max(len(r[i]) for r in rows) for i in range(len(rows[0]))]
-    for r in rows:
-        print("   ".join(x.ljust(w[i]) for i, x in enumerate(r)).rstrip())
+    for r in rows if header else rows[1:]:
+        print("   ".join(x.ljust(w[i]) for i, x in enumerate(r)).rstrip(), flush=True)
+
+
+def watch_table(server: str, kind: str, ns: str, name: Optional[str], rv: str, seconds: float) -> None:
+    """`get -w`: after the table, one row per change, as `kubectl get -w` prints them (DELETED rows are marked).
+    Reads the API server's chunked watch stream (apiserver/rest.py) from `rv` for `seconds`."""
+    path = _path(kind, ns) + f"?watch=true&resourceVersion={rv}&timeoutSeconds={seconds:g}"
+    req = urllib.request.Request(f"http://{server}{path}")
+    try:
+        with urllib.request.urlopen(req, timeout=seconds + 30) as r:
+            for line in r:
+                if not line.strip():
+                    continue
+                ev = json.loads(line)
+                obj = ev.get("object") or {}
+                if ev.get("type") == "ERROR":
+                    raise SystemExit(f"watch ended: {obj.get('message', obj)}")
+                if name and c.name_of(obj) != name:
+                    continue
+                if ev.get("type") == "DELETED":
+                    print(f"{c.name_of(obj)}   <deleted>", flush=True)
+                else:
+                    print_table(kind, [obj], header=False)
+    except urllib.error.URLError as e:
+        raise SystemExit(f"cannot reach the manager at {server}: {e.reason}")
+    except KeyboardInterrupt:
+        pass
 
 
 def _scale_to(job: dict, total: int) -> None:
@@ -265,6 +291,8 @@ def main(argv=None) -> int:
     sub = ap.add_subparsers(dest="cmd", required=True)
     a = sub.add_parser("apply"); a.add_argument("-f", "--filename", required=True, action="append")
     g = sub.add_parser("get"); g.add_argument("kind"); g.add_argument("name", nargs="?"); g.add_argument("-n", "--namespace", default="default"); g.add_argument("-o", "--output", default="")
+    g.add_argument("-w", "--watch", action="store_true", help="after listing, print one row per change until interrupted")
+    g.add_argument("--watch-seconds", type=float, default=3600.0, help="with -w: stop after this long")
     d = sub.add_parser("describe"); d.add_argument("kind"); d.add_argument("name"); d.add_argument("-n", "--namespace", default="default")
     r = sub.add_parser("delete"); r.add_argument("kind"); r.add_argument("name"); r.add_argument("-n", "--namespace", default="default")
     l = sub.add_parser("logs"); l.add_argument("pod"); l.add_argument("-n", "--namespace", default="default")
@@ -300,6 +328,11 @@ def main(argv=None) -> int:
             print(json.dumps(obj, indent=2) if args.output == "json" else yaml.safe_dump(obj, sort_keys=False))
         else:
             print_table(kind, items)
+        if args.watch:
+            rv = "0" if args.name else str(out.get("metadata", {}).get("resourceVersion", "0"))
+            if rv == "0":     # a single object has no list version: follow from "now"
+                rv = str(_http(args.server, "GET", _path(kind, args.namespace)).get("metadata", {}).get("resourceVersion", "0"))
+            watch_table(args.server, kind, args.namespace, args.name, rv, args.watch_seconds)
         return 0
     if args.cmd == "describe":
         obj = _http(args.server, "GET", _path(kind, args.namespace, args.name))

@@ -193,3 +193,40 @@ def test_apiserver_refuses_an_empty_token_file(tmp_path, capsys):
     tf.write_text("  \n")
     assert apiserver.main(["--serve", "127.0.0.1:0", "--token-file", str(tf)]) == 2
     assert "holds no token" in capsys.readouterr().err
+
+
+def test_kubedlctl_get_watch_prints_a_row_per_change(capsys):
+    """`kubedlctl get -w`: the table, then one row for every change that arrives on the API server's watch stream
+    (what `kubectl get -w` does against the reference's CRDs with their printer columns)."""
+    import threading
+    from kubedl_b200.bench.launch_delay import _job
+    port = _free_port()
+    args = manager.build_parser().parse_args(["--enable-leader-election=false", "--serve", f"127.0.0.1:{port}",
+                                              "--metrics-addr", "0", "--controller-metrics-addr", "0",
+                                              "--workloads", "*", "--no-node-agent"])
+    reg = CollectorRegistry()
+    op = manager.build_operator(args, metrics_registry=reg)
+    manager.start_operator(op, args, metrics_registry=reg)
+    try:
+        srv = f"127.0.0.1:{port}"
+        op.mgr.api.create(_job("PyTorchJob", "first", 2, 0.1))
+
+        def later():
+            time.sleep(0.4)
+            op.mgr.api.create(_job("PyTorchJob", "second", 2, 0.1))
+            time.sleep(0.3)
+            op.mgr.api.delete("PyTorchJob", "bench", "first")
+        t = threading.Thread(target=later)
+        t.start()
+        assert kubedlctl.main(["-s", srv, "get", "pytorchjobs", "-n", "bench", "-w", "--watch-seconds", "1.5"]) == 0
+        t.join()
+        out = capsys.readouterr().out.splitlines()
+        assert out[0].split()[:3] == ["NAME", "STATE", "AGE"] and out[1].startswith("first")
+        rest = out[2:]
+        assert any(l.startswith("second") and "Created" in l for l in rest), out
+        assert any(l.startswith("first") and "<deleted>" in l for l in rest), out
+        # following one object only
+        assert kubedlctl.main(["-s", srv, "get", "pytorchjob", "second", "-n", "bench", "-w", "--watch-seconds", "0.3"]) == 0
+        assert all(l.startswith(("NAME", "second")) for l in capsys.readouterr().out.splitlines())
+    finally:
+        op.stop()

@@ -585,6 +585,11 @@ class KubeAPIServer:
                                                {"metadata": {"labels": dict(labels)}},
                                                content_type="application/merge-patch+json"))
 
+    def merge_patch(self, kind: str, namespace: str, name: str, patch: dict) -> dict:
+        self.request_log.append(("patch", kind, f"{namespace or 'default'}/{name}"))
+        return self._stamp(kind, self._request("PATCH", self._object_path(kind, namespace, name), patch,
+                                               content_type="application/merge-patch+json"))
+
     def delete(self, kind: str, namespace: str, name: str, cascade: bool = True) -> None:
         self.request_log.append(("delete", kind, f"{namespace or 'default'}/{name}"))
         policy = "Background" if cascade else "Orphan"

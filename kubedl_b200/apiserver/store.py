@@ -22,6 +22,21 @@ from ..api.kinds import SCHEME
 ADDED, MODIFIED, DELETED = "ADDED", "MODIFIED", "DELETED"
 
 
+def _merge_patch(target, patch):
+    """RFC 7386 JSON merge patch (returns a new tree, shares unpatched subtrees with `target`)."""
+    if not isinstance(patch, dict):
+        return patch
+    if not isinstance(target, dict):
+        target = {}
+    out = dict(target)
+    for k, v in patch.items():
+        if v is None:
+            out.pop(k, None)
+        else:
+            out[k] = _merge_patch(out.get(k), v)
+    return out
+
+
 class _Frozen:
     """Mix-in that turns every mutator of dict / list into an error (KUBEDL_FREEZE_SNAPSHOTS=1)."""
 
@@ -303,6 +318,26 @@ class APIServer:
                 lab[k] = v
         o["metadata"].pop("resourceVersion", None)
         return self._update(o, status_only=False, spec_only=False)
+
+    def merge_patch(self, kind: str, namespace: str, name: str, patch: dict) -> dict:
+        """RFC 7386 merge patch of the whole object, status included: what the REST façade's PATCH does, in one call
+        instead of a get and an update, and atomic — the merge is applied to the version it was computed from
+        (compare-and-swap on resourceVersion, retried), unless the patch itself pins a resourceVersion."""
+        pinned = (patch.get("metadata") or {}).get("resourceVersion")
+        for _ in range(16):
+            with self._lock:
+                cur = self._objs[kind].get((namespace or "default", name))
+                if cur is None:
+                    raise NotFound(f'{kind.lower()} "{name}" not found')
+                new = _merge_patch(cur, patch)
+                new["metadata"] = dict(new.get("metadata") or {})
+                new["metadata"]["resourceVersion"] = pinned or cur["metadata"]["resourceVersion"]
+            try:
+                return self._update(new, status_only=False, spec_only=False)
+            except Conflict:
+                if pinned:
+                    raise
+        raise Conflict(f"{kind.lower()} \"{name}\" kept changing under a merge patch")
 
     def delete(self, kind: str, namespace: str, name: str, cascade: bool = True) -> None:
         with self._lock:

@@ -719,33 +719,30 @@ class Gpulet:
 
     def _set_status(self, pod: dict, phase: str, conditions=None, container_statuses=None, reason: str = "",
                     exit_code: Optional[int] = None, host: bool = False, start: Optional[str] = None) -> None:
-        try:
-            cur = self.api.get("Pod", c.namespace_of(pod), c.name_of(pod))
-        except NotFound:
-            return
-        status = cur.get("status") or {}
-        status["phase"] = phase
+        """One merge patch per status change (the kubelet PATCHes pod status too): only the fields named here change,
+        whatever else the status holds stays.  It used to be a GET and a PUT — two round trips per pod and transition
+        when the API server is remote."""
+        status: Dict[str, object] = {"phase": phase}
         if conditions is not None:
             status["conditions"] = conditions
         if container_statuses is not None:
             status["containerStatuses"] = container_statuses
         if reason:
             status["reason"] = reason[:200]
+        patch: Dict[str, object] = {"status": status}
         if host:
             status["hostIP"] = "127.0.0.1"
             status["podIP"] = "127.0.0.1"
-            cur.setdefault("spec", {})["nodeName"] = self.node_name
+            patch["spec"] = {"nodeName": self.node_name}
         if start:
             status["startTime"] = start
         if exit_code is not None and container_statuses is None:
-            name = (cur.get("spec", {}).get("containers") or [{}])[0].get("name", "")
+            name = (pod.get("spec", {}).get("containers") or [{}])[0].get("name", "")
             status["containerStatuses"] = [{"name": name, "ready": False, "restartCount": 0,
                                             "state": {"terminated": {"exitCode": exit_code, "reason": "Error",
                                                                      "finishedAt": c.now_precise()}}}]
-        cur["status"] = status
-        cur["metadata"].pop("resourceVersion", None)
         try:
-            self.api.update(cur)
+            self.api.merge_patch("Pod", c.namespace_of(pod), c.name_of(pod), patch)
         except NotFound:
             pass
 

@@ -694,3 +694,24 @@ def test_shared_watchers_get_one_snapshot_private_ones_a_copy_each(remote):
         assert "scribbled" not in (api.get("Pod", "default", name)["metadata"].get("labels") or {})
         for s in stops:
             s()
+
+
+def test_merge_patch_is_one_call_status_included_and_atomic(remote):
+    """merge_patch (RFC 7386) on the in-process store and through the REST client: spec, status and label deletion in
+    one call; only named fields change; NotFound and a pinned resourceVersion behave as for update."""
+    api, srv, cli = remote
+    for server, name in ((api, "mp-local"), (cli, "mp-remote")):
+        api.create(pod(name))
+        o = server.merge_patch("Pod", "default", name, {"spec": {"nodeName": "n0"},
+                                                        "status": {"phase": "Running", "hostIP": "127.0.0.1"},
+                                                        "metadata": {"labels": {"extra": "1"}}})
+        assert o["spec"]["nodeName"] == "n0" and o["status"]["phase"] == "Running" and o["metadata"]["labels"]["extra"] == "1"
+        o2 = server.merge_patch("Pod", "default", name, {"status": {"phase": "Succeeded"}, "metadata": {"labels": {"extra": None}}})
+        assert o2["status"] == {"phase": "Succeeded", "hostIP": "127.0.0.1"} and "extra" not in (o2["metadata"].get("labels") or {})
+        assert o2["spec"]["containers"] == o["spec"]["containers"]
+        with pytest.raises(store.NotFound):
+            server.merge_patch("Pod", "default", "nope", {"status": {"phase": "Running"}})
+        with pytest.raises(store.Conflict):
+            server.merge_patch("Pod", "default", name, {"metadata": {"resourceVersion": o["metadata"]["resourceVersion"]},
+                                                        "status": {"phase": "Failed"}})
+        assert api.get("Pod", "default", name)["status"]["phase"] == "Succeeded"

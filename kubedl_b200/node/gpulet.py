@@ -929,6 +929,9 @@ class FakeKubelet:
     def set_all(self, namespace: str, phase: str, selector: Optional[Dict[str, str]] = None, **kw) -> int:
         n = 0
         for pod in self.api.list("Pod", namespace, selector):
-            self.set_phase(namespace, c.name_of(pod), phase, **kw)
+            try:
+                self.set_phase(namespace, c.name_of(pod), phase, **kw)
+            except NotFound:        # deleted since the list (e.g. cleanPodPolicy after the job's last worker finished)
+                continue
             n += 1
         return n

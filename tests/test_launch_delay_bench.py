@@ -8,7 +8,8 @@ from kubedl_b200.bench import launch_delay as LD
 
 @pytest.mark.parametrize("mode", ["in-process", "http", "processes"])
 def test_bench_modes(mode):
-    r = LD.run("PyTorchJob", jobs=2, replicas=3, seconds=0.05, remote=(mode == "http"), processes=(mode == "processes"))
+    # workers live long enough for the operator to see all of them Running at once, also on a loaded box
+    r = LD.run("PyTorchJob", jobs=2, replicas=3, seconds=0.5, remote=(mode == "http"), processes=(mode == "processes"))
     assert r["first_pod_ms"]["n"] == 2 and r["all_pods_ms"]["n"] == 2
     assert 0 < r["first_pod_ms"]["p50"] <= r["all_pods_ms"]["p50"] < 5000
     assert r["api_creates_per_job"] == 4          # 3 pods + the master's service

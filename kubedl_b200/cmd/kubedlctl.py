@@ -296,6 +296,8 @@ def main(argv=None) -> int:
     d = sub.add_parser("describe"); d.add_argument("kind"); d.add_argument("name"); d.add_argument("-n", "--namespace", default="default")
     r = sub.add_parser("delete"); r.add_argument("kind"); r.add_argument("name"); r.add_argument("-n", "--namespace", default="default")
     l = sub.add_parser("logs"); l.add_argument("pod"); l.add_argument("-n", "--namespace", default="default")
+    l.add_argument("-f", "--follow", action="store_true", help="keep printing until the pod finishes")
+    l.add_argument("--follow-seconds", type=float, default=86400.0)
     x = sub.add_parser("run"); x.add_argument("-f", "--filename", required=True, action="append")
     x.add_argument("--gpus", type=int, default=None); x.add_argument("--timeout", type=float, default=600.0); x.add_argument("--gang", default="")
     x.add_argument("--replicas", type=int, default=0, help="scale every job in the manifests to this many pods")
@@ -317,7 +319,22 @@ def main(argv=None) -> int:
                     print(f"{str(res.get('kind', '')).lower()}/{res.get('name')} {res.get('result')}")
         return 0
     if args.cmd == "logs":
-        print(_http(args.server, "GET", f"/logs/{args.namespace}/{args.pod}"), end="")
+        text = _http(args.server, "GET", f"/logs/{args.namespace}/{args.pod}")
+        print(text, end="", flush=True)
+        if args.follow:       # print what is appended until the pod reaches a terminal phase (or is gone)
+            deadline = time.time() + args.follow_seconds
+            done = False
+            while not done and time.time() < deadline:
+                time.sleep(0.3)
+                try:
+                    phase = _http(args.server, "GET", _path("Pod", args.namespace, args.pod)).get("status", {}).get("phase")
+                    done = phase in ("Succeeded", "Failed")
+                except SystemExit:
+                    done = True
+                new = _http(args.server, "GET", f"/logs/{args.namespace}/{args.pod}")
+                if len(new) > len(text):
+                    print(new[len(text):], end="", flush=True)
+                    text = new
         return 0
     kind = resolve_kind(args.kind)
     if args.cmd == "get":

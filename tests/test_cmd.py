@@ -230,3 +230,30 @@ def test_kubedlctl_get_watch_prints_a_row_per_change(capsys):
         assert all(l.startswith(("NAME", "second")) for l in capsys.readouterr().out.splitlines())
     finally:
         op.stop()
+
+
+def test_kubedlctl_logs_follow_prints_until_the_pod_finishes(capsys):
+    """`kubedlctl logs -f`: the log so far, then what the worker appends, until its pod is Succeeded."""
+    import sys
+    from kubedl_b200.api import kinds as k
+    port = _free_port()
+    args = manager.build_parser().parse_args(["--enable-leader-election=false", "--serve", f"127.0.0.1:{port}",
+                                              "--metrics-addr", "0", "--controller-metrics-addr", "0",
+                                              "--workloads", "*", "--gpus", "0"])
+    reg = CollectorRegistry()
+    op = manager.build_operator(args, metrics_registry=reg)
+    manager.start_operator(op, args, metrics_registry=reg)
+    try:
+        srv = f"127.0.0.1:{port}"
+        code = "import time\nfor i in range(4):\n    print('tick', i, flush=True); time.sleep(0.25)"
+        t = {"spec": {"containers": [{"name": "xdl", "image": "python", "command": [sys.executable, "-c", code]}]}}
+        op.mgr.api.create(k.new_job("XDLJob", "talker", "bench", {"Worker": {"replicas": 1, "restartPolicy": "Never", "template": t}}))
+        for _ in range(200):
+            if op.mgr.api.list("Pod", "bench"):
+                break
+            time.sleep(0.02)
+        assert kubedlctl.main(["-s", srv, "logs", "talker-worker-0", "-n", "bench", "-f", "--follow-seconds", "20"]) == 0
+        out = capsys.readouterr().out
+        assert [l for l in out.splitlines() if l.startswith("tick")] == [f"tick {i}" for i in range(4)], out
+    finally:
+        op.stop()

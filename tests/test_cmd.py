@@ -247,12 +247,14 @@ def test_kubedlctl_logs_follow_prints_until_the_pod_finishes(capsys):
         srv = f"127.0.0.1:{port}"
         code = "import time\nfor i in range(4):\n    print('tick', i, flush=True); time.sleep(0.25)"
         t = {"spec": {"containers": [{"name": "xdl", "image": "python", "command": [sys.executable, "-c", code]}]}}
-        op.mgr.api.create(k.new_job("XDLJob", "talker", "bench", {"Worker": {"replicas": 1, "restartPolicy": "Never", "template": t}}))
+        import uuid
+        job = "talker-" + uuid.uuid4().hex[:6]          # pod logs are files named after the pod and appended to
+        op.mgr.api.create(k.new_job("XDLJob", job, "bench", {"Worker": {"replicas": 1, "restartPolicy": "Never", "template": t}}))
         for _ in range(200):
             if op.mgr.api.list("Pod", "bench"):
                 break
             time.sleep(0.02)
-        assert kubedlctl.main(["-s", srv, "logs", "talker-worker-0", "-n", "bench", "-f", "--follow-seconds", "20"]) == 0
+        assert kubedlctl.main(["-s", srv, "logs", f"{job}-worker-0", "-n", "bench", "-f", "--follow-seconds", "20"]) == 0
         out = capsys.readouterr().out
         assert [l for l in out.splitlines() if l.startswith("tick")] == [f"tick {i}" for i in range(4)], out
     finally:

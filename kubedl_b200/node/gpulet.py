@@ -418,6 +418,13 @@ class Gpulet:
         pods = Gauge("kubedl_gpulet_pods", "Pods on the node agent", ["node", "state"], registry=registry)
         pods.labels(self.node_name, "running").set_function(lambda: len(self._procs))
         pods.labels(self.node_name, "pending").set_function(lambda: len(self._pending))
+        def warm(state):
+            z = getattr(self, "zygote", None)
+            return sum(1 for w in list(z.warm_workers.values()) if w.get("state") == state) if z is not None else 0
+        ww = Gauge("kubedl_gpulet_warm_gpu_workers", "Pre-forked workers holding a CUDA context on a free GPU",
+                   ["node", "state"], registry=registry)
+        ww.labels(self.node_name, "ready").set_function(lambda: warm("ready"))
+        ww.labels(self.node_name, "warming").set_function(lambda: warm("warming"))
         self._launched_total = Counter("kubedl_gpulet_pods_launched_total", "Pods started", ["node", "how"], registry=registry)
         self._start_hist = Histogram("kubedl_gpulet_pod_start_seconds", "Admission to process running, per pod", ["node"],
                                      buckets=(0.002, 0.005, 0.01, 0.025, 0.05, 0.1, 0.25, 0.5, 1, 2.5, 5, 10),

@@ -179,6 +179,7 @@ def test_node_agent_keeps_a_warm_worker_per_free_gpu(tmp_path):
         assert let.zygote.ready.wait(60)
         _wait(lambda: sorted(g for g, w in let.zygote.warm_workers.items() if w["state"] == "ready") == [0, 1])
         first = {g: w["pid"] for g, w in let.zygote.warm_workers.items()}
+        assert reg.get_sample_value("kubedl_gpulet_warm_gpu_workers", {"node": let.node_name, "state": "ready"}) == 2
         from kubedl_b200.bench.launch_delay import _job
         mgr.api.create(_job("TFJob", "warm", 2, 0.1))      # PS + worker, both `python -m` workers
 

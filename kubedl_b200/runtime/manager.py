@@ -67,6 +67,10 @@ class Client:
     def __init__(self, api: APIServer):
         self.api = api
         self._cache: Dict[str, Dict[Tuple[str, str], dict]] = {}
+        # kind -> job-name label value -> keys of the cached objects carrying it.  Every reconcile lists the pods and
+        # services of ONE job by {group-name, job-name}; without the index that is a walk over every pod of the
+        # namespace (8 -> 22 ms per job going from 200 to 800 live jobs).
+        self._by_job: Dict[str, Dict[str, set]] = {}
         self._lock = threading.RLock()
         self._stops: List[Callable[[], None]] = []
 
@@ -75,15 +79,36 @@ class Client:
             if kind in self._cache:
                 return
             self._cache[kind] = {}
+            self._by_job[kind] = {}
 
         def on_event(ev, obj, old):
             key = (c.namespace_of(obj), c.name_of(obj))
             with self._lock:
                 if ev == DELETED:
-                    self._cache[kind].pop(key, None)
+                    self._store(kind, key, None)
                 elif not _older(obj, self._cache[kind].get(key)):
-                    self._cache[kind][key] = obj
+                    self._store(kind, key, obj)
         self._stops.append(self.api.watch(kind, on_event, replay=True, shared=True))   # cache entries are never mutated
+
+    def _store(self, kind: str, key: Tuple[str, str], obj: Optional[dict]) -> None:
+        """Put (or, with None, drop) a cache entry and keep the job-name index in step.  Caller holds the lock."""
+        cache, index = self._cache[kind], self._by_job[kind]
+        cur = cache.get(key)
+        if cur is not None:
+            job = (cur.get("metadata", {}).get("labels") or {}).get(c.JOB_NAME_LABEL)
+            if job is not None:
+                keys = index.get(job)
+                if keys is not None:
+                    keys.discard(key)
+                    if not keys:
+                        del index[job]
+        if obj is None:
+            cache.pop(key, None)
+            return
+        cache[key] = obj
+        job = (obj.get("metadata", {}).get("labels") or {}).get(c.JOB_NAME_LABEL)
+        if job is not None:
+            index.setdefault(job, set()).add(key)
 
     def _remember(self, obj: dict) -> dict:
         """Read-your-writes: what a write returned goes into the cache at once if it is newer than
@@ -97,7 +122,7 @@ class Client:
                 key = (c.namespace_of(obj), c.name_of(obj))
                 cur = cache.get(key)
                 if cur is not None and _older(cur, obj):   # never resurrect what a DELETED event removed
-                    cache[key] = _copy(obj)
+                    self._store(kind, key, _copy(obj))
         return obj
 
     def get(self, kind: str, namespace: str, name: str) -> dict:
@@ -113,7 +138,13 @@ class Client:
         self.ensure_informer(kind)
         with self._lock:
             out = []
-            for (ns, _), o in self._cache[kind].items():
+            cache = self._cache[kind]
+            job = (label_selector or {}).get(c.JOB_NAME_LABEL)
+            if job is not None:      # one job's objects: through the index instead of over the whole cache
+                items = [(k, cache[k]) for k in self._by_job[kind].get(job, ()) if k in cache]
+            else:
+                items = list(cache.items())
+            for (ns, _), o in items:
                 if namespace and ns != namespace:
                     continue
                 if label_selector:

@@ -466,3 +466,35 @@ def test_no_watcher_writes_to_the_shared_event_snapshot(monkeypatch):
         cl.settle()
         assert cl.conditions(kind, "bench", name)[-1] == ("Succeeded", "True"), cl.conditions(kind, "bench", name)
     assert sum(r.controller.error_count for r in cl.recs.values()) == 0
+
+
+def test_informer_cache_lists_a_jobs_objects_through_its_index():
+    """Listing by {group-name, job-name} goes through the cache's job-name index; the index follows label changes
+    (adoption / release) and deletions, and the result is what a scan of the whole cache gives."""
+    cl = Cluster()
+    api, client = cl.api, cl.mgr.client
+    client.ensure_informer("Pod")
+
+    def mk(name, job):
+        labels = {c.JOB_NAME_LABEL: job, c.GROUP_NAME_LABEL: "kubeflow.org"} if job else {"other": "x"}
+        return {"apiVersion": "v1", "kind": "Pod", "metadata": {"name": name, "namespace": "ns", "labels": labels},
+                "spec": {"containers": [{"name": "c", "image": "i"}]}}
+    for i in range(3):
+        api.create(mk(f"a-{i}", "job-a"))
+    api.create(mk("b-0", "job-b"))
+    api.create(mk("loose", ""))
+
+    def names(job):
+        return [c.name_of(p) for p in client.list("Pod", "ns", {c.JOB_NAME_LABEL: job, c.GROUP_NAME_LABEL: "kubeflow.org"})]
+
+    def scan(job):
+        return sorted(c.name_of(p) for p in client.list("Pod", "ns") if c.labels_of(p).get(c.JOB_NAME_LABEL) == job)
+    assert names("job-a") == ["a-0", "a-1", "a-2"] == scan("job-a") and names("job-b") == ["b-0"] and names("nope") == []
+    api.patch_labels("Pod", "ns", "a-1", {c.JOB_NAME_LABEL: "job-b"})          # moves between jobs
+    api.patch_labels("Pod", "ns", "loose", {c.JOB_NAME_LABEL: "job-a", c.GROUP_NAME_LABEL: "kubeflow.org"})   # adopted
+    api.patch_labels("Pod", "ns", "a-2", {c.JOB_NAME_LABEL: None})             # released
+    api.delete("Pod", "ns", "a-0")
+    assert names("job-a") == ["loose"] == scan("job-a")
+    assert names("job-b") == ["a-1", "b-0"] == scan("job-b")
+    assert client.list("Pod", "other-ns", {c.JOB_NAME_LABEL: "job-b"}) == []
+    assert not any(not keys for keys in client._by_job["Pod"].values())          # empty buckets are dropped

@@ -72,6 +72,13 @@ def now_precise() -> str:
 def parse_time(s: Optional[str]) -> Optional[float]:
     if not s:
         return None
+    try:        # the C parser (3.11+ reads the trailing Z and fractions): ~20x cheaper than strptime, and this runs
+        d = _dt.datetime.fromisoformat(s)       # per pod per reconcile and per stored Event when Events are pruned
+        if d.tzinfo is None:
+            d = d.replace(tzinfo=_dt.timezone.utc)
+        return d.timestamp()
+    except ValueError:
+        pass
     for fmt in ("%Y-%m-%dT%H:%M:%S.%fZ", "%Y-%m-%dT%H:%M:%SZ"):
         try:
             return _dt.datetime.strptime(s, fmt).replace(tzinfo=_dt.timezone.utc).timestamp()

@@ -101,6 +101,9 @@ class BaseJobReconciler(ControllerInterface):
             job = self.client.get(self.KIND, req.namespace, req.name)
         except NotFound:
             self.metrics.deleted_inc()
+            # the job is gone: so are its pending creations / deletions, and its restart back-off state
+            self.ctrl.expectations.delete_for_job(f"{req.namespace}/{req.name}")
+            self.ctrl.backoff_states_queue.forget(f"{req.namespace}/{req.name}")
             return Result()
         specs = self.info.replica_specs(job)
         if not self.ctrl.satisfy_expectations(job, specs) or job["metadata"].get("deletionTimestamp"):

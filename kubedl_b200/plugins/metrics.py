@@ -14,7 +14,7 @@ launch-delay benchmark can report p50/p90 (default buckets stop at 10 s).
 from __future__ import annotations
 
 import collections
-
+import os
 import threading
 from typing import Callable, Dict, List, Optional, Tuple
 
@@ -80,7 +80,29 @@ class _Families:
                                   "Histogram for recording sync launch delay duration(from job created to all pods running).",
                                   labels, registry=registry)
         self.gauge_sources: Dict[str, Callable[[], Tuple[int, int]]] = {}
+        # The two histograms are labelled per JOB (name, namespace, uid), as in the reference: one pair of series per
+        # job ever launched, never dropped there.  Here the oldest jobs' series go once more than
+        # KUBEDL_LAUNCH_DELAY_SERIES_MAX jobs (2,000) hold one — ~14 KB per job for the two histograms' buckets
+        # (scripts/soak_control_plane.py), and an operator runs for months.
+        self.series_max = int(os.environ.get("KUBEDL_LAUNCH_DELAY_SERIES_MAX", "2000"))
+        self._series: "collections.OrderedDict[Tuple[str, str, str, str], None]" = collections.OrderedDict()
+        self._series_lock = threading.Lock()
         registry.register(self)
+
+    def observe_delay(self, hist: Histogram, labels: Tuple[str, str, str, str], delay: float) -> None:
+        hist.labels(*labels).observe(delay)
+        with self._series_lock:
+            self._series[labels] = None
+            self._series.move_to_end(labels)
+            drop = []
+            while len(self._series) > self.series_max:
+                drop.append(self._series.popitem(last=False)[0])
+        for lv in drop:
+            for h in (self.first_pod, self.all_pods):
+                try:
+                    h.remove(*lv)
+                except KeyError:
+                    pass
 
     # custom collector for the scrape-time gauges (promauto.NewGaugeFunc upstream)
     def collect(self):
@@ -160,7 +182,7 @@ class JobMetrics:
         self._created, self._deleted = fam.created.labels(lk), fam.deleted.labels(lk)
         self._success, self._failure = fam.success.labels(lk), fam.failure.labels(lk)
         self._restart = fam.restart.labels(lk)
-        self._first, self._all = fam.first_pod, fam.all_pods
+        self._first, self._all, self._fam = fam.first_pod, fam.all_pods, fam
         # bounded: an operator runs for months
         self.launch_delays: Dict[str, collections.deque] = {"first_pod": collections.deque(maxlen=100_000),
                                                             "all_pods": collections.deque(maxlen=100_000)}
@@ -201,7 +223,7 @@ class JobMetrics:
             return
         self._seen_first.add(c.uid_of(job))
         delay = earliest - created
-        self._first.labels(self.kind, c.name_of(job), c.namespace_of(job), c.uid_of(job)).observe(delay)
+        self._fam.observe_delay(self._first, (self.kind, c.name_of(job), c.namespace_of(job), c.uid_of(job)), delay)
         self.launch_delays["first_pod"].append((c.key_of(job), delay))
 
     def all_pods_launch_delay_seconds(self, pods: List[dict], job: dict, status: dict) -> None:
@@ -223,7 +245,7 @@ class JobMetrics:
             return
         self._seen_all.add(c.uid_of(job))
         delay = final - created
-        self._all.labels(self.kind, c.name_of(job), c.namespace_of(job), c.uid_of(job)).observe(delay)
+        self._fam.observe_delay(self._all, (self.kind, c.name_of(job), c.namespace_of(job), c.uid_of(job)), delay)
         self.launch_delays["all_pods"].append((c.key_of(job), delay))
 
 

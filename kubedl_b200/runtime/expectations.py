@@ -33,6 +33,7 @@ class ControllerExpectations:
         self._lock = threading.Lock()
         self._store: Dict[str, _Record] = {}
         self.clock, self.ttl = clock, ttl
+        self._sweep_at = 1024
 
     def get(self, key: str) -> Optional[_Record]:
         with self._lock:
@@ -41,6 +42,11 @@ class ControllerExpectations:
     def set_expectations(self, key: str, add: int, dele: int) -> None:
         with self._lock:
             self._store[key] = _Record(add, dele, self.clock())
+            grown = len(self._store) > self._sweep_at
+        if grown:                                   # amortised: a sweep each time the table has doubled
+            self.sweep()
+            with self._lock:
+                self._sweep_at = max(1024, 2 * len(self._store))
 
     def expect_creations(self, key: str, adds: int) -> None:
         self.set_expectations(key, adds, 0)
@@ -94,6 +100,30 @@ class ControllerExpectations:
     def delete_expectations(self, key: str) -> None:
         with self._lock:
             self._store.pop(key, None)
+
+    def delete_for_job(self, job_key: str) -> int:
+        """Forget every record of a job that no longer exists (`<job key>/<replica type>/pods|services`).  The
+        reference keeps its records in a TTL store that drops them after five minutes; a plain dict never does, and a
+        long-running operator kept three to four records per job it had ever seen."""
+        prefix = job_key + "/"
+        with self._lock:
+            dead = [k for k in self._store if k.startswith(prefix)]
+            for k in dead:
+                del self._store[k]
+        return len(dead)
+
+    def sweep(self) -> int:
+        """Drop the records that are both settled and older than the TTL (what the TTL store does by itself)."""
+        now = self.clock()
+        with self._lock:
+            dead = [k for k, r in self._store.items() if now - r.ts > self.ttl]
+            for k in dead:
+                del self._store[k]
+        return len(dead)
+
+    def __len__(self) -> int:
+        with self._lock:
+            return len(self._store)
 
 
 def gen_expectation_pods_key(job_key: str, rtype: str) -> str:

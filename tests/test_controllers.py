@@ -498,3 +498,40 @@ def test_informer_cache_lists_a_jobs_objects_through_its_index():
     assert names("job-b") == ["a-1", "b-0"] == scan("job-b")
     assert client.list("Pod", "other-ns", {c.JOB_NAME_LABEL: "job-b"}) == []
     assert not any(not keys for keys in client._by_job["Pod"].values())          # empty buckets are dropped
+
+
+def test_nothing_is_kept_about_a_deleted_job():
+    """A job that ran and was deleted leaves no expectation record, no back-off state, no cache entry and no index
+    bucket behind (the reference's expectations live in a TTL store; a plain dict kept 3-4 records per job for ever)."""
+    from kubedl_b200.bench.launch_delay import _job
+    cl = Cluster()
+    for kind in ("PyTorchJob", "TFJob", "XGBoostJob", "XDLJob"):
+        for i in range(3):
+            cl.api.create(_job(kind, f"gone-{kind.lower()}-{i}", 3, 0.0))
+    cl.settle()
+    assert sum(len(r.ctrl.expectations) for r in cl.recs.values()) > 0
+    cl.kubelet.set_all("bench", c.POD_RUNNING); cl.settle()
+    cl.kubelet.set_all("bench", c.POD_SUCCEEDED); cl.settle()
+    for kind in ("PyTorchJob", "TFJob", "XGBoostJob", "XDLJob"):
+        for i in range(3):
+            try:                                        # XGBoostJobs may already be gone (TTL after finished)
+                cl.api.delete(kind, "bench", f"gone-{kind.lower()}-{i}")
+            except Exception:
+                pass
+    cl.settle()
+    assert [len(r.ctrl.expectations) for r in cl.recs.values()] == [0, 0, 0, 0]
+    assert all(len(v) == 0 for kind, v in cl.mgr.client._cache.items() if kind in ("Pod", "Service") or kind.endswith("Job"))
+    assert all(len(v) == 0 for v in cl.mgr.client._by_job.values())
+
+
+def test_expectations_sweep_drops_expired_records():
+    from kubedl_b200.runtime.expectations import ControllerExpectations
+    now = [0.0]
+    e = ControllerExpectations(clock=lambda: now[0], ttl=300.0)
+    e.expect_creations("ns/a/worker/pods", 2)
+    e.expect_creations("ns/b/worker/pods", 1)
+    now[0] = 200.0
+    e.expect_creations("ns/c/worker/pods", 1)
+    now[0] = 400.0
+    assert e.sweep() == 2 and len(e) == 1 and e.get("ns/c/worker/pods") is not None
+    assert e.delete_for_job("ns/c") == 1 and len(e) == 0

@@ -11,7 +11,9 @@ from __future__ import annotations
 
 import collections
 import copy  # noqa: F401
+import logging
 import threading
+import traceback
 import uuid
 from typing import Callable, Deque, Dict, List, Optional, Tuple
 
@@ -20,6 +22,7 @@ from ..api.common import deepcopy as _copy
 from ..api.kinds import SCHEME
 
 ADDED, MODIFIED, DELETED = "ADDED", "MODIFIED", "DELETED"
+_log = logging.getLogger("kubedl.apiserver")
 
 
 def _merge_patch(target, patch):
@@ -406,14 +409,20 @@ class APIServer:
                         handlers = [(h, h in self._shared_handlers) for h in self._watchers.get(kind, ())]
                     snap = None
                     for h, shared in handlers:
-                        if shared:
-                            if snap is None:         # one read-only snapshot for every handler that asked for it
-                                snap = (_copy(obj), _copy(old) if old is not None else None)
-                                if _FREEZE_SNAPSHOTS:
-                                    snap = (_freeze(snap[0]), _freeze(snap[1]) if snap[1] is not None else None)
-                            h(ev, snap[0], snap[1])
-                        else:
-                            h(ev, _copy(obj), _copy(old) if old is not None else None)
+                        try:
+                            if shared:
+                                if snap is None:         # one read-only snapshot for every handler that asked for it
+                                    snap = (_copy(obj), _copy(old) if old is not None else None)
+                                    if _FREEZE_SNAPSHOTS:
+                                        snap = (_freeze(snap[0]), _freeze(snap[1]) if snap[1] is not None else None)
+                                h(ev, snap[0], snap[1])
+                            else:
+                                h(ev, _copy(obj), _copy(old) if old is not None else None)
+                        except Exception:
+                            # a watcher's failure is its own: the write that caused the event has happened, and the
+                            # writer (and the watchers after this one) must not pay for it
+                            _log.error("watch handler for %s failed on %s %s/%s:\n%s", kind, ev, c.namespace_of(obj),
+                                       c.name_of(obj), traceback.format_exc())
             finally:
                 self._dispatching.active = False
 

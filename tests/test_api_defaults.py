@@ -215,3 +215,20 @@ def test_events_expire_like_kube_apiserver():
     assert api.prune_events(now=time.time() + 10) == 0
     assert api.prune_events(now=time.time() + 3700) == 3 and api.events_for(job) == []
     assert api.request_log.maxlen == 65536
+
+
+def test_a_failing_watch_handler_costs_neither_the_writer_nor_the_other_watchers(caplog):
+    """A watcher that raises is logged and skipped: the create that caused the event returns normally and the watchers
+    registered after it still see the event (the remote client's reflector already behaves this way)."""
+    from kubedl_b200.apiserver.store import APIServer
+    api = APIServer()
+    seen = []
+
+    def bad(ev, obj, old):
+        raise RuntimeError("boom")
+    api.watch("Pod", bad, replay=False)
+    api.watch("Pod", lambda ev, obj, old: seen.append((ev, obj["metadata"]["name"])), replay=False)
+    out = api.create({"apiVersion": "v1", "kind": "Pod", "metadata": {"name": "p", "namespace": "ns"},
+                      "spec": {"containers": [{"name": "c", "image": "i"}]}})
+    assert out["metadata"]["name"] == "p" and seen == [("ADDED", "p")]
+    assert "watch handler for Pod failed" in caplog.text and "boom" in caplog.text

@@ -240,7 +240,8 @@ def make_handler(api: APIServer, log_reader: Optional[Callable[[str, str], str]]
             rv = r.q("resourceVersion")
             events: "queue.Queue[Tuple[str, dict]]" = queue.Queue()
             # subscribe first, then replay: nothing can fall between the two
-            stop = api.watch(r.kind, lambda ev, obj, old: events.put((ev, obj)), replay=False)
+            # the stream only serialises what it is handed: one snapshot shared with the other read-only watchers
+            stop = api.watch(r.kind, lambda ev, obj, old: events.put((ev, obj)), replay=False, shared=True)
             try:
                 try:
                     if rv in (None, "", "0"):

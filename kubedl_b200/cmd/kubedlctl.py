@@ -13,6 +13,7 @@ import json
 import sys
 import time
 import urllib.error
+import urllib.parse
 import urllib.request
 from typing import List, Optional
 
@@ -354,6 +355,13 @@ def main(argv=None) -> int:
     if args.cmd == "describe":
         obj = _http(args.server, "GET", _path(kind, args.namespace, args.name))
         print(yaml.safe_dump(obj, sort_keys=False))
+        if SCHEME.is_workload(kind):      # the job's pods, as `kubectl get pods -l job-name=<name>` would list them
+            sel = urllib.parse.quote(f"{c.JOB_NAME_LABEL}={args.name}")
+            pods = _http(args.server, "GET", _path("Pod", args.namespace) + f"?labelSelector={sel}")["items"]
+            if pods:
+                print("Pods:")
+                print_table("Pod", sorted(pods, key=c.name_of))
+                print()
         evs = _http(args.server, "GET", f"/api/v1/namespaces/{args.namespace}/events")["items"]
         mine = [e for e in evs if e.get("involvedObject", {}).get("uid") == obj["metadata"]["uid"]]
         if mine:

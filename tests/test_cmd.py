@@ -55,7 +55,9 @@ def test_operator_wiring_and_kubedlctl(capsys, tmp_path):
         obj = json.loads(capsys.readouterr().out)
         assert obj["kind"] == "XDLJob" and obj["spec"]["ttlSecondsAfterFinished"] == 3600
         assert kubedlctl.main(["-s", srv, "describe", "xdljob", "xdl-mnist-example", "-n", "kubedl"]) == 0
-        assert "SuccessfulCreatePod" in capsys.readouterr().out
+        described = capsys.readouterr().out
+        assert "SuccessfulCreatePod" in described
+        assert "Pods:" in described and "xdl-mnist-example-worker-1" in described and "RESTARTS" in described
         assert kubedlctl.main(["-s", srv, "get", "podgroups", "-n", "kubedl"]) == 0
         assert "xdl-mnist-example" in capsys.readouterr().out
         assert kubedlctl.main(["-s", srv, "delete", "xdljob", "xdl-mnist-example", "-n", "kubedl"]) == 0

@@ -140,6 +140,8 @@ def _get_families(registry: CollectorRegistry) -> _Families:
 
 def job_status_counter(kind: str, reader, predicate: Callable[[dict], bool]) -> int:
     """reference status_counter.go:31-48"""
+    if hasattr(reader, "count"):          # the informer cache counts in place; predicates only read the status
+        return reader.count(kind, lambda job: predicate(job.get("status") or {}))
     return sum(1 for job in reader.list(kind) if predicate(c.status_of(job)))
 
 

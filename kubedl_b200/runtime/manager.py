@@ -155,6 +155,13 @@ class Client:
             out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
             return out
 
+    def count(self, kind: str, predicate: Callable[[dict], bool]) -> int:
+        """How many cached objects of `kind` satisfy a READ-ONLY predicate — no copies (list() copies every object,
+        and the running / pending gauges ask about every job of every kind on each scrape)."""
+        self.ensure_informer(kind)
+        with self._lock:
+            return sum(1 for o in self._cache[kind].values() if predicate(o))
+
     def reader(self) -> APIServer:
         return self.api
 

@@ -261,3 +261,15 @@ def test_kubedlctl_logs_follow_prints_until_the_pod_finishes(capsys):
         assert [l for l in out.splitlines() if l.startswith("tick")] == [f"tick {i}" for i in range(4)], out
     finally:
         op.stop()
+
+
+def test_every_flag_is_documented():
+    """docs/startup_flags.md (the reference's docs/startup_flags.md:4-9, extended) names every flag of the three commands."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    doc = open(os.path.join(root, "docs", "startup_flags.md")).read()
+    flags = {o for a in manager.build_parser()._actions for o in a.option_strings if o.startswith("--")} - {"--help"}
+    for mod in ("gpulet", "apiserver"):
+        flags |= set(re.findall(r'add_argument\("(--[a-z\-]+)"', open(os.path.join(root, "kubedl_b200", "cmd", mod + ".py")).read()))
+    assert sorted(f for f in flags if f not in doc) == []
